@@ -1,0 +1,9 @@
+"""compression_b200 — B200-native (sm_100a) hot path of tensorflow_compression.
+
+Mirrors `tensorflow_compression/__init__.py:31-40`, which star-imports the layers and ops into
+one namespace (`tfc.*`).
+"""
+from compression_b200._lib import InvalidArgumentError, CudaError, launch_count
+from compression_b200.python.ops.range_coding_ops import (
+    range_encode, range_decode, unbounded_index_range_encode, unbounded_index_range_decode,
+    pmf_to_quantized_cdf)

@@ -1,0 +1,865 @@
+// Batched range coder for sm_100a: one warp per independent stream.
+//
+// Replaces (citations relative to /root/reference/tensorflow_compression/cc/kernels/):
+//   RangeEncoder::Encode/Finalize, RangeDecoder::Decode      range_coder.cc:38-377
+//   UnboundedIndexRangeEncodeOp / ...DecodeOp                unbounded_index_range_coding_kernels.cc:141-376
+//   RangeEncodeOp / RangeDecodeOp, BroadcastRange            range_coding_kernels.cc:63-380
+//   MergeAxes                                                range_coding_kernels_util.cc:36-92
+//
+// Design.  The coder state is a serial dependency chain per stream, so
+// the unit of parallelism is the stream (one per image, as EntropyModel.compress emits them).
+//   encode: the 32 lanes of a warp fetch symbols+indexes coalesced and do every
+//           state-INDEPENDENT step in parallel (offset shift, escape mapping, the two CDF
+//           lookups), packing (lower, upper-1) into one 32-bit word in shared memory; lane 0
+//           then runs the 32-bit state machine over the staged words.
+//   decode: the search depends on the state, so all lanes carry the state and each probes one
+//           CDF entry of a 32-wide window placed around the row's mode (tables are staged
+//           ragged in shared memory); one ballot finds the symbol, two shuffles fetch its
+//           bounds.  Rows longer than the window fall back to a 32-ary ballot search.
+// All arithmetic is integer and bit-exact with the reference.
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int kChunk = 128;          // symbols staged per encode round (4 per lane)
+constexpr int kMaxMerged = 6;        // range_coding_kernels.cc:210-230
+constexpr int kTableBudget = 96 * 1024;
+
+struct Broadcast {  // merged data shape + cdf row strides (in rows) for the bounded ops
+  int32_t nd;
+  int64_t dshape[kMaxMerged];
+  int64_t rstride[kMaxMerged];
+};
+
+// ---------------------------------------------------------------------------------------
+// encoder state machine (range_coder.cc:38-301)
+// ---------------------------------------------------------------------------------------
+struct Encoder {
+  uint32_t lo, span1;
+  uint64_t held;  // 0: interval inside [0,2^32); else low 16 bits = pending word (+1),
+                  // upper bits = 0x20000 per pending pair of filler bytes
+  uint8_t* out;
+  uint32_t pos, cap;
+
+  __device__ __forceinline__ void init(uint8_t* o, uint32_t c) {
+    lo = 0; span1 = 0xFFFFFFFFu; held = 0; out = o; pos = 0; cap = c;
+  }
+  __device__ __forceinline__ void byte(uint32_t b) {
+    if (pos < cap) out[pos] = (uint8_t)b;
+    ++pos;
+  }
+  __device__ __forceinline__ void word(uint32_t w) { byte(w >> 8); byte(w & 0xFFu); }
+
+  __device__ __forceinline__ void put(uint32_t c0, uint32_t c1, int prec) {
+    // span*c == span1*c + c with span = span1+1 <= 2^32: one 32x32+64 multiply-add each
+    const uint32_t a = (uint32_t)(((uint64_t)span1 * c0 + c0) >> prec);
+    const uint32_t b = (uint32_t)(((uint64_t)span1 * c1 + c1) >> prec) - 1u;
+    lo += a;
+    const bool wrapped = lo < a;
+    span1 = b - a;
+    if (lo + span1 < lo) {  // interval straddles 2^32: carry still undecided
+      if ((span1 >> 16) == 0) {
+        lo <<= 16;
+        span1 = (span1 << 16) | 0xFFFFu;
+        held += 0x20000;
+      }
+      return;
+    }
+    if (held != 0) {
+      if (!wrapped) --held;
+      word((uint32_t)held & 0xFFFFu);
+      const uint32_t fill = wrapped ? 0x00u : 0xFFu;
+      for (uint64_t k = held >> 16; k != 0; --k) byte(fill);
+      held = 0;
+    }
+    if ((span1 >> 16) == 0) {
+      const uint32_t hi = lo >> 16;
+      lo <<= 16;
+      span1 = (span1 << 16) | 0xFFFFu;
+      if (lo + span1 >= lo) word(hi); else held = hi + 1;
+    }
+  }
+
+  __device__ __forceinline__ void flush() {
+    uint32_t w;
+    if (held != 0) w = (uint32_t)held & 0xFFFFu;
+    else if (lo != 0) w = ((lo - 1) >> 16) + 1;
+    else return;
+    byte(w >> 8);
+    if (w & 0xFFu) byte(w & 0xFFu);
+  }
+
+  // escape tail of the unbounded-index code (unbounded_index_range_coding_kernels.cc:232-247)
+  __device__ __forceinline__ void escape(uint32_t x, int w) {
+    const uint32_t all1 = (1u << w) - 1u;
+    int nd = 0;
+    while (nd * w < 32 && (x >> (nd * w)) != 0) ++nd;
+    uint32_t u = (uint32_t)nd;
+    for (; u >= all1; u -= all1) put(all1, all1 + 1, w);
+    put(u, u + 1, w);
+    for (int j = 0; j < nd; ++j) {
+      const uint32_t d = (x >> (j * w)) & all1;
+      put(d, d + 1, w);
+    }
+  }
+};
+
+struct EncodeParams {
+  // unbounded-index form
+  const int32_t* data32;
+  const int32_t* index;
+  int64_t index_stride;
+  const int32_t* cdf_size;
+  const int32_t* offset;
+  int32_t cols;
+  int overflow_width;
+  // bounded form
+  const int16_t* data16;
+  int64_t cdf_stream_stride;
+  int32_t chip;
+  Broadcast bc;
+  // common
+  const int32_t* cdf;
+  int64_t S, n;
+  int precision;
+  uint8_t* out;
+  int64_t cap;
+  int32_t* nbytes;
+  int32_t* status;
+};
+
+__device__ __forceinline__ int64_t broadcast_row(const Broadcast& bc, int64_t i) {
+  int64_t row = 0;
+#pragma unroll
+  for (int d = kMaxMerged - 1; d >= 0; --d) {
+    if (d < bc.nd) {
+      const int64_t q = i / bc.dshape[d];
+      row += (i - q * bc.dshape[d]) * bc.rstride[d];
+      i = q;
+    }
+  }
+  return row;
+}
+
+template <bool UNBOUNDED>
+__global__ void __launch_bounds__(256) encode_kernel(const EncodeParams p) {
+  extern __shared__ __align__(16) uint32_t smem_enc[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t s = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
+  if (s >= p.S) return;
+  uint32_t* packed = smem_enc + warp * (2 * kChunk + 4);
+  uint32_t* extra = packed + kChunk;
+  uint32_t* escm = extra + kChunk;
+
+  Encoder e;
+  e.init(p.out + s * p.cap, (uint32_t)p.cap);
+  const int32_t* idx = UNBOUNDED ? p.index + s * p.index_stride : nullptr;
+  const int32_t* d32 = UNBOUNDED ? p.data32 + s * p.n : nullptr;
+  const int16_t* d16 = UNBOUNDED ? nullptr : p.data16 + s * p.n;
+  const int32_t* cdf = UNBOUNDED ? p.cdf : p.cdf + s * p.cdf_stream_stride;
+
+  for (int64_t base = 0; base < p.n; base += kChunk) {
+    const int cnt = (int)min((int64_t)kChunk, p.n - base);
+#pragma unroll
+    for (int u = 0; u < kChunk / 32; ++u) {
+      const int j = u * 32 + lane;
+      bool esc = false;
+      if (j < cnt) {
+        uint32_t c0, c1, x = 0;
+        if (UNBOUNDED) {
+          const int32_t r = __ldg(idx + base + j);
+          const int32_t top = __ldg(p.cdf_size + r) - 2;
+          int32_t v = __ldg(d32 + base + j) - __ldg(p.offset + r);
+          if (v < 0) { x = (uint32_t)(-2 * v - 1); v = top; esc = true; }
+          else if (v >= top) { x = (uint32_t)(2 * (v - top)); v = top; esc = true; }
+          const int32_t* row = cdf + (int64_t)r * p.cols;
+          c0 = (uint32_t)__ldg(row + v);
+          c1 = (uint32_t)__ldg(row + v + 1);
+        } else {
+          const int64_t rowi = broadcast_row(p.bc, base + j);
+          const int32_t* row = cdf + rowi * p.chip;
+          const int32_t v = d16[base + j];
+          c0 = (uint32_t)__ldg(row + v);
+          c1 = (uint32_t)__ldg(row + v + 1);
+        }
+        packed[j] = (c0 & 0xFFFFu) | ((c1 - 1u) << 16);
+        extra[j] = x;
+      }
+      const uint32_t m = __ballot_sync(0xFFFFFFFFu, esc);
+      if (lane == 0) escm[u] = m;
+    }
+    __syncwarp();
+    if (lane == 0) {
+      for (int g = 0; g < cnt; g += 4) {
+        const uint4 q = *reinterpret_cast<const uint4*>(packed + g);
+        const uint32_t m = UNBOUNDED ? (escm[g >> 5] >> (g & 31)) : 0u;
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          if (g + t < cnt) {
+            e.put(w[t] & 0xFFFFu, (w[t] >> 16) + 1u, p.precision);
+            if (UNBOUNDED && ((m >> t) & 1u)) e.escape(extra[g + t], p.overflow_width);
+          }
+        }
+      }
+    }
+    __syncwarp();
+  }
+  if (lane == 0) {
+    e.flush();
+    p.nbytes[s] = (int32_t)e.pos;
+    if (p.status) p.status[s] = e.pos > e.cap ? TFC_STREAM_CAPACITY : TFC_STREAM_OK;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// decoder (range_coder.cc:303-377)
+// ---------------------------------------------------------------------------------------
+struct DecodeParams {
+  const uint8_t* enc;
+  int64_t cap;
+  const int32_t* nbytes;
+  // unbounded-index form
+  const int32_t* index;
+  int64_t index_stride;
+  const int32_t* cdf_size;
+  const int32_t* offset;
+  int32_t rows, cols;
+  int overflow_width;
+  int32_t* out32;
+  // bounded form
+  int64_t cdf_stream_stride;
+  int32_t chip;
+  Broadcast bc;
+  int16_t* out16;
+  // common
+  const int32_t* cdf;
+  int64_t S, n;
+  int precision;
+  int32_t* status;
+  int32_t table_budget;  // bytes of dynamic shared memory available for the staged tables
+};
+
+struct Decoder {
+  uint32_t lo, span1, code, nxt;
+  const uint8_t* src;
+  uint32_t pos, len;
+  bool corrupt;
+
+  __device__ __forceinline__ uint32_t peek16(uint32_t at) const {
+    uint32_t v = 0;
+    if (at < len) v = (uint32_t)__ldg(src + at) << 8;
+    if (at + 1 < len) v |= (uint32_t)__ldg(src + at + 1);
+    return v;
+  }
+  __device__ __forceinline__ void init(const uint8_t* s, uint32_t n) {
+    src = s; len = n; lo = 0; span1 = 0xFFFFFFFFu; corrupt = false;
+    code = (peek16(0) << 16) | peek16(2);
+    pos = 4;
+    nxt = peek16(pos);
+  }
+  __device__ __forceinline__ uint64_t target(int prec) const {
+    return (((uint64_t)(uint32_t)(code - lo) + 1u) << prec) - 1u;
+  }
+  // span * c > target ?
+  __device__ __forceinline__ bool above(uint32_t c, uint64_t tgt) const {
+    return (uint64_t)span1 * c + c > tgt;
+  }
+  __device__ __forceinline__ void narrow(uint32_t c0, uint32_t c1, int prec) {
+    const uint32_t a = (uint32_t)(((uint64_t)span1 * c0 + c0) >> prec);
+    const uint32_t b = (uint32_t)(((uint64_t)span1 * c1 + c1) >> prec) - 1u;
+    lo += a;
+    span1 = b - a;
+    if ((span1 >> 16) == 0) {
+      lo <<= 16;
+      span1 = (span1 << 16) | 0xFFFFu;
+      code = (code << 16) | nxt;
+      pos += 2;
+      nxt = peek16(pos);
+    }
+  }
+  // one digit of the uniform 2^w alphabet (cdf = iota): smallest k with span*k > target is
+  // floor(target/span)+1
+  __device__ __forceinline__ uint32_t digit(int w) {
+    const uint64_t span = (uint64_t)span1 + 1u;
+    const uint64_t d = target(w) / span;
+    if (d >> w) { corrupt = true; }
+    const uint32_t dd = (uint32_t)min(d, (uint64_t)((1u << w) - 1u));
+    narrow(dd, dd + 1u, w);
+    return dd;
+  }
+};
+
+// 32-ary ballot search for the smallest k in [lo, hi] with span*row[k] > target (row[lo-1]
+// is known not to satisfy it).  Returns hi+1 if none does.
+template <typename RowPtr>
+__device__ __forceinline__ int wide_search(const Decoder& d, RowPtr row, int lo, int hi,
+                                           uint64_t tgt, int lane) {
+  while (hi - lo + 1 > 32) {
+    const int step = (hi - lo + 1 + 31) >> 5;
+    const int k = min(lo + (lane + 1) * step - 1, hi);
+    const uint32_t b = __ballot_sync(0xFFFFFFFFu, d.above((uint32_t)row[k], tgt));
+    if (b == 0) return hi + 1;
+    const int f = __ffs(b) - 1;
+    const int nlo = lo + f * step;
+    hi = min(nlo + step - 1, hi);
+    lo = nlo;
+  }
+  const int k = lo + lane;
+  const uint32_t b =
+      __ballot_sync(0xFFFFFFFFu, k <= hi && d.above((uint32_t)row[min(k, hi)], tgt));
+  if (b == 0) return hi + 1;
+  return lo + __ffs(b) - 1;
+}
+
+// Shared-memory image of the tables: ragged rows + one int4 {start, len, window base, offset}
+// per row.  Falls back to the dense global table when it does not fit.
+struct Tables {
+  const int32_t* tbl;  // ragged (shared) or dense (global)
+  const int4* meta;    // shared, or nullptr
+  bool staged;
+};
+
+template <bool STAGED>
+__device__ __forceinline__ void row_info(const Tables& t, const DecodeParams& p, int32_t r,
+                                         int& start, int& len, int& wb, int& off) {
+  if (STAGED) {
+    const int4 m = t.meta[r];
+    start = m.x; len = m.y; wb = m.z; off = m.w;
+  } else {
+    len = __ldg(p.cdf_size + r);
+    start = r * p.cols;
+    off = __ldg(p.offset + r);
+    wb = len <= 32 ? 0 : min(max(len / 2 - 16, 0), len - 32);
+  }
+}
+
+template <bool STAGED>
+__device__ void decode_unbounded_stream(const DecodeParams& p, const Tables& t, int64_t s,
+                                        int lane) {
+  Decoder d;
+  const int32_t nb = p.nbytes[s];
+  d.init(p.enc + s * p.cap, (uint32_t)max(nb, 0));
+  const int32_t* idx = p.index + s * p.index_stride;
+  int32_t* out = p.out32 + s * p.n;
+  const int prec = p.precision, w = p.overflow_width;
+  const uint32_t all1 = (1u << w) - 1u;
+
+  for (int64_t base = 0; base < p.n; base += 32) {
+    const int cnt = (int)min((int64_t)32, p.n - base);
+    const int32_t myr = lane < cnt ? __ldg(idx + base + lane) : 0;
+    int32_t mine = 0;
+    // software pipeline: row info + window value of symbol j+1 are fetched while j decodes
+    int start, len, wb, off;
+    row_info<STAGED>(t, p, __shfl_sync(0xFFFFFFFFu, myr, 0), start, len, wb, off);
+    uint32_t wv = (wb + lane < len) ? (uint32_t)t.tbl[start + wb + lane] : 0u;
+    for (int j = 0; j < cnt; ++j) {
+      int nstart = 0, nlen = 0, nwb = 0, noff = 0;
+      uint32_t nwv = 0;
+      if (j + 1 < cnt) {
+        row_info<STAGED>(t, p, __shfl_sync(0xFFFFFFFFu, myr, j + 1), nstart, nlen, nwb, noff);
+        nwv = (nwb + lane < nlen) ? (uint32_t)t.tbl[nstart + nwb + lane] : 0u;
+      }
+      const uint64_t tgt = d.target(prec);
+      const bool valid = wb + lane < len;
+      const uint32_t b = __ballot_sync(0xFFFFFFFFu, valid && d.above(wv, tgt));
+      const int f = __ffs(b) - 1;
+      uint32_t c0, c1;
+      int k;
+      if (f >= 1) {  // hit inside the window, left neighbour in lane f-1
+        k = wb + f;
+        c0 = __shfl_sync(0xFFFFFFFFu, wv, f - 1);
+        c1 = __shfl_sync(0xFFFFFFFFu, wv, f);
+      } else {
+        const int32_t* row = t.tbl + start;
+        if (f == 0) k = wb == 0 ? len : wide_search(d, row, 1, wb, tgt, lane);
+        else k = (wb + 32 <= len - 1) ? wide_search(d, row, wb + 32, len - 1, tgt, lane) : len;
+        if (k > len - 1) { d.corrupt = true; k = len - 1; }
+        c0 = (uint32_t)row[k - 1];
+        c1 = (uint32_t)row[k];
+      }
+      d.narrow(c0, c1, prec);
+      int32_t v = k - 1;
+      const int32_t top = len - 2;
+      if (v == top) {
+        int nd = 0;
+        uint32_t u;
+        do { u = d.digit(w); nd += (int)u; } while (u == all1 && nd < 64 && !d.corrupt);
+        uint32_t x = 0;
+        for (int q = 0; q < nd; ++q) {
+          const uint32_t dg = d.digit(w);
+          if (q * w < 32) x |= dg << (q * w);
+        }
+        v = (x & 1u) ? -(int32_t)(x >> 1) - 1 : (int32_t)(x >> 1) + top;
+      }
+      v += off;
+      if (lane == j) mine = v;
+      start = nstart; len = nlen; wb = nwb; off = noff; wv = nwv;
+    }
+    if (lane < cnt) out[base + lane] = mine;
+  }
+  if (lane == 0 && p.status) p.status[s] = d.corrupt ? TFC_STREAM_CORRUPT : TFC_STREAM_OK;
+}
+
+__global__ void __launch_bounds__(256) decode_unbounded_kernel(const DecodeParams p) {
+  extern __shared__ __align__(16) uint8_t smem_dec[];
+  __shared__ int s_total;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nthreads = blockDim.x;
+
+  // ---- stage the tables (ragged) --------------------------------------------------------
+  int4* meta = reinterpret_cast<int4*>(smem_dec);
+  int32_t* tbl = reinterpret_cast<int32_t*>(smem_dec + (size_t)p.rows * sizeof(int4));
+  const int64_t meta_bytes = (int64_t)p.rows * (int64_t)sizeof(int4);
+  bool staged = meta_bytes + 16 <= p.table_budget;
+  if (staged) {
+    // row starts by a serial prefix sum in thread 0 (rows is a few hundred at most)
+    if (threadIdx.x == 0) {
+      int acc = 0;
+      for (int r = 0; r < p.rows; ++r) {
+        const int len = min(max(__ldg(p.cdf_size + r), 0), p.cols);
+        meta[r] = make_int4(acc, len, 0, __ldg(p.offset + r));
+        acc += len;
+      }
+      s_total = acc;
+    }
+    __syncthreads();
+    staged = meta_bytes + (int64_t)s_total * 4 <= p.table_budget;
+  }
+  if (staged) {
+    for (int r = warp; r < p.rows; r += nthreads >> 5) {
+      const int start = meta[r].x, len = meta[r].y;
+      const int32_t* src = p.cdf + (int64_t)r * p.cols;
+      // copy the row and find its mode (largest pmf entry) for the window placement
+      int best = 0, bestk = 1;
+      for (int k = lane; k < len; k += 32) {
+        const int32_t c = __ldg(src + k);
+        tbl[start + k] = c;
+        if (k + 1 < len) {
+          const int pm = __ldg(src + k + 1) - c;
+          if (pm > best) { best = pm; bestk = k + 1; }
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const int ob = __shfl_xor_sync(0xFFFFFFFFu, best, o);
+        const int ok = __shfl_xor_sync(0xFFFFFFFFu, bestk, o);
+        if (ob > best || (ob == best && ok < bestk)) { best = ob; bestk = ok; }
+      }
+      if (lane == 0) meta[r].z = len <= 32 ? 0 : min(max(bestk - 16, 0), len - 32);
+    }
+  }
+  __syncthreads();
+
+  const int64_t s = (int64_t)blockIdx.x * (nthreads >> 5) + warp;
+  if (s >= p.S) return;
+  Tables t;
+  t.staged = staged;
+  if (staged) {
+    t.tbl = tbl; t.meta = meta;
+    decode_unbounded_stream<true>(p, t, s, lane);
+  } else {
+    t.tbl = p.cdf; t.meta = nullptr;
+    decode_unbounded_stream<false>(p, t, s, lane);
+  }
+}
+
+// bounded decode: every element has its own (broadcast) row of `chip` entries
+__global__ void __launch_bounds__(256) decode_bounded_kernel(const DecodeParams p) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t s = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
+  if (s >= p.S) return;
+  Decoder d;
+  d.init(p.enc + s * p.cap, (uint32_t)max(p.nbytes[s], 0));
+  const int32_t* cdf = p.cdf + s * p.cdf_stream_stride;
+  int16_t* out = p.out16 + s * p.n;
+  const int len = p.chip, prec = p.precision;
+  for (int64_t base = 0; base < p.n; base += 32) {
+    const int cnt = (int)min((int64_t)32, p.n - base);
+    const int64_t myrow = lane < cnt ? broadcast_row(p.bc, base + lane) : 0;
+    int32_t mine = 0;
+    for (int j = 0; j < cnt; ++j) {
+      const int32_t* row = cdf + __shfl_sync(0xFFFFFFFFu, myrow, j) * len;
+      const uint64_t tgt = d.target(prec);
+      int k = wide_search(d, row, 1, len - 1, tgt, lane);
+      if (k > len - 1) { d.corrupt = true; k = len - 1; }
+      d.narrow((uint32_t)__ldg(row + k - 1), (uint32_t)__ldg(row + k), prec);
+      if (lane == j) mine = k - 1;
+    }
+    if (lane < cnt) out[base + lane] = (int16_t)mine;
+  }
+  if (lane == 0 && p.status) p.status[s] = d.corrupt ? TFC_STREAM_CORRUPT : TFC_STREAM_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// debug_level=1 argument checks (unbounded_index_range_coding_kernels.cc:58-115,
+// range_coding_kernels.cc:153-176, :250-255), run on the device; the first failure wins.
+// ---------------------------------------------------------------------------------------
+enum CheckCode { kCheckOk = 0, kBadIndex, kBadCdfSize, kBadCdfEnds, kNotMonotonic,
+                 kBadCdfEndsBounded, kBadData };
+struct CheckRecord { int32_t code; int32_t a; int32_t b; int32_t pad; };
+
+__device__ __forceinline__ void report(CheckRecord* rec, int code, int a, int b) {
+  if (atomicCAS(&rec->code, kCheckOk, code) == kCheckOk) { rec->a = a; rec->b = b; }
+}
+
+__global__ void check_index_kernel(const int32_t* index, int64_t count, int32_t rows,
+                                   CheckRecord* rec) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < count;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t v = index[i];
+    if (v < 0 || v >= rows) report(rec, kBadIndex, v, 0);
+  }
+}
+
+// ragged == true: rows have individual lengths cdf_size[r] (unbounded ops); else all `cols`
+__global__ void check_cdf_kernel(const int32_t* cdf, int64_t rows, int32_t cols,
+                                 const int32_t* cdf_size, bool ragged, int precision,
+                                 CheckRecord* rec) {
+  const int32_t top = 1 << precision;
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < rows;
+       r += (int64_t)gridDim.x * blockDim.x) {
+    int32_t len = cols;
+    if (ragged) {
+      len = cdf_size[r];
+      if (len < 3 || len > cols) { report(rec, kBadCdfSize, len, 0); continue; }
+    }
+    const int32_t* row = cdf + r * cols;
+    if (row[0] != 0 || row[len - 1] != top) {
+      report(rec, ragged ? kBadCdfEnds : kBadCdfEndsBounded, row[0], row[len - 1]);
+      continue;
+    }
+    for (int j = 0; j + 1 < len; ++j)
+      if (row[j + 1] <= row[j]) { report(rec, kNotMonotonic, 0, 0); break; }
+  }
+}
+
+__global__ void check_data16_kernel(const int16_t* data, int64_t count, int32_t chip,
+                                    CheckRecord* rec) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < count;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t v = data[i];
+    if (v < 0 || chip <= v + 1) report(rec, kBadData, v, 0);
+  }
+}
+
+int finish_checks(CheckRecord* d_rec, cudaStream_t st, int rows, int cols, int precision,
+                  int chip) {
+  CheckRecord h;
+  TFC_CUDA(cudaMemcpyAsync(&h, d_rec, sizeof(h), cudaMemcpyDeviceToHost, st));
+  TFC_CUDA(cudaStreamSynchronize(st));
+  cudaFreeAsync(d_rec, st);
+  switch (h.code) {
+    case kCheckOk: return TFC_OK;
+    case kBadIndex:
+      return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "'index' has a value not in [0, %d): value=%d",
+                       rows, h.a);
+    case kBadCdfSize:
+      return tfc::fail(TFC_ERR_INVALID_ARGUMENT,
+                       "'cdf_size' has a value not in [3, %d]: value=%d", cols, h.a);
+    case kBadCdfEnds:
+      return tfc::fail(TFC_ERR_INVALID_ARGUMENT,
+                       "Each cdf should start from 0 and end at %d: cdf[0]=%d, cdf[^1]=%d",
+                       1 << precision, h.a, h.b);
+    case kBadCdfEndsBounded:
+      return tfc::fail(TFC_ERR_INVALID_ARGUMENT,
+                       "CDF should start from 0 and end at %d: cdf[0]=%d, cdf[^1]=%d",
+                       1 << precision, h.a, h.b);
+    case kNotMonotonic:
+      return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "CDF is not monotonic");
+    case kBadData:
+      return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "'data' value not in [0, %d): value=%d",
+                       chip - 1, h.a);
+  }
+  return TFC_OK;
+}
+
+int alloc_record(CheckRecord** rec, cudaStream_t st) {
+  TFC_CUDA(cudaMallocAsync(reinterpret_cast<void**>(rec), sizeof(CheckRecord), st));
+  TFC_CUDA(cudaMemsetAsync(*rec, 0, sizeof(CheckRecord), st));
+  return TFC_OK;
+}
+
+int check_attrs(int precision, int overflow_width, int debug_level, bool has_overflow) {
+  if (precision < 1 || precision > 16)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "`precision` must be in [1, 16]: %d", precision);
+  if (has_overflow && (overflow_width < 1 || overflow_width > 16))
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "`overflow_width` must be in [1, 16]: %d",
+                     overflow_width);
+  if (debug_level != 0 && debug_level != 1)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "`debug_level` must be 0 or 1: %d", debug_level);
+  return TFC_OK;
+}
+
+int check_unbounded_shapes(int32_t rows, int32_t cols) {
+  // CheckArgumentShapes (unbounded_index_range_coding_kernels.cc:117-139): the 1-D/2-D parts
+  // are implied by the C signature; what is left is the column count.
+  if (rows < 0 || cols < 3)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT,
+                     "'cdf' should be 2-D and cdf.dim_size(1) >= 3: [%d,%d]", rows, cols);
+  return TFC_OK;
+}
+
+int run_unbounded_checks(const int32_t* d_index, int64_t index_count, const int32_t* d_cdf,
+                         int32_t rows, int32_t cols, const int32_t* d_cdf_size, int precision,
+                         cudaStream_t st) {
+  CheckRecord* rec = nullptr;
+  int rc = alloc_record(&rec, st);
+  if (rc) return rc;
+  if (index_count > 0) {
+    const int blocks = (int)std::min<int64_t>((index_count + 255) / 256, 4 * tfc::num_sms());
+    check_index_kernel<<<blocks, 256, 0, st>>>(d_index, index_count, rows, rec);
+    TFC_LAUNCHED("check_index_kernel");
+  }
+  if (rows > 0) {
+    check_cdf_kernel<<<(rows + 127) / 128, 128, 0, st>>>(d_cdf, rows, cols, d_cdf_size, true,
+                                                         precision, rec);
+    TFC_LAUNCHED("check_cdf_kernel");
+  }
+  return finish_checks(rec, st, rows, cols, precision, 0);
+}
+
+int warps_per_block(int64_t S) {
+  // few streams: one warp per block so the streams spread over the SMs; many: pack 8
+  const int sms = tfc::num_sms();
+  if (S <= 4 * (int64_t)sms) return 1;
+  if (S <= 16 * (int64_t)sms) return 4;
+  return 8;
+}
+
+std::string shape_str(const int64_t* s, int n) {
+  std::string r = "[";
+  for (int i = 0; i < n; ++i) { if (i) r += ","; r += std::to_string(s[i]); }
+  return r + "]";
+}
+
+// CheckCdfShape + MergeAxes, producing the device-side broadcast descriptor.
+int plan_broadcast(const int64_t* data_shape, int rank, const int64_t* cdf_shape, int cdf_rank,
+                   Broadcast* bc, int64_t* count, int32_t* chip, int64_t* cdf_rows) {
+  if (cdf_rank != rank + 1)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT,
+                     "`cdf` should have one more axis than `data`: data shape=%s, cdf shape=%s",
+                     shape_str(data_shape, rank).c_str(), shape_str(cdf_shape, cdf_rank).c_str());
+  if (cdf_shape[cdf_rank - 1] <= 1)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "The last dimension of `cdf` should be > 1: %s",
+                     shape_str(cdf_shape, cdf_rank).c_str());
+  std::vector<int64_t> md(rank + 1), mc(rank + 2);
+  int mr = 0;
+  int rc = tfc_merge_axes(data_shape, rank, cdf_shape, cdf_rank, md.data(), mc.data(), &mr);
+  if (rc) return rc;
+  if (mr > kMaxMerged)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "Irregular broadcast pattern: %s, %s",
+                     shape_str(data_shape, rank).c_str(), shape_str(cdf_shape, cdf_rank).c_str());
+  bc->nd = mr;
+  int64_t n = 1, stride = 1;
+  for (int i = mr - 1; i >= 0; --i) {
+    bc->dshape[i] = md[i];
+    bc->rstride[i] = mc[i] <= 1 ? 0 : stride;
+    stride *= mc[i];
+    n *= md[i];
+  }
+  for (int i = mr; i < kMaxMerged; ++i) { bc->dshape[i] = 1; bc->rstride[i] = 0; }
+  *count = n;
+  *chip = (int32_t)cdf_shape[cdf_rank - 1];
+  *cdf_rows = stride;
+  return TFC_OK;
+}
+
+}  // namespace
+
+// =========================================================================================
+// C ABI
+// =========================================================================================
+extern "C" int tfc_merge_axes(const int64_t* data_shape, int rank, const int64_t* cdf_shape,
+                              int cdf_rank, int64_t* merged_data_shape,
+                              int64_t* merged_cdf_shape, int* merged_rank) {
+  if (cdf_rank != rank + 1)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "`cdf` should have one more axis than `data`");
+  // Adjacent axes fuse when both broadcast or both do not; size-1 axes fuse with anything.
+  int m = 0;
+  merged_data_shape[0] = 1;
+  merged_cdf_shape[0] = 1;
+  for (int j = 0; j < rank; ++j) {
+    const int64_t dj = data_shape[j], cj = cdf_shape[j];
+    if (dj != cj && cj != 1)
+      return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "Cannot broadcast shape %s to %s",
+                       shape_str(cdf_shape, cdf_rank).c_str(),
+                       shape_str(data_shape, rank).c_str());
+    const bool prev_bcast = merged_cdf_shape[m] == 1;
+    const bool this_bcast = cj == 1;
+    if (prev_bcast == this_bcast || dj <= 1 || merged_data_shape[m] <= 1) {
+      merged_data_shape[m] *= dj;
+      merged_cdf_shape[m] *= cj;
+    } else {
+      ++m;
+      merged_data_shape[m] = dj;
+      merged_cdf_shape[m] = cj;
+    }
+  }
+  merged_cdf_shape[m + 1] = cdf_shape[cdf_rank - 1];
+  *merged_rank = m + 1;
+  return TFC_OK;
+}
+
+extern "C" int tfc_unbounded_index_range_encode(
+    const int32_t* d_data, const int32_t* d_index, int64_t index_stride, int64_t S, int64_t n,
+    const int32_t* d_cdf, int32_t rows, int32_t cols, const int32_t* d_cdf_size,
+    const int32_t* d_offset, int precision, int overflow_width, int debug_level, uint8_t* d_out,
+    int64_t cap, int32_t* d_nbytes, int32_t* d_status, void* stream) {
+  int rc = check_attrs(precision, overflow_width, debug_level, true);
+  if (rc) return rc;
+  rc = check_unbounded_shapes(rows, cols);
+  if (rc) return rc;
+  if (index_stride != 0 && index_stride != n)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT,
+                     "`data` and `index` should have the same shape (index_stride must be n or 0)");
+  if (cap < 0 || cap > 0x7FFFFFF0ll || n < 0 || S < 0)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "bad sizes: S=%lld n=%lld cap=%lld", (long long)S,
+                     (long long)n, (long long)cap);
+  if (S == 0) return TFC_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (debug_level > 0) {
+    rc = run_unbounded_checks(d_index, index_stride ? S * n : n, d_cdf, rows, cols, d_cdf_size,
+                              precision, st);
+    if (rc) return rc;
+  }
+  EncodeParams p{};
+  p.data32 = d_data; p.index = d_index; p.index_stride = index_stride;
+  p.cdf_size = d_cdf_size; p.offset = d_offset; p.cols = cols; p.overflow_width = overflow_width;
+  p.cdf = d_cdf; p.S = S; p.n = n; p.precision = precision;
+  p.out = d_out; p.cap = cap; p.nbytes = d_nbytes; p.status = d_status;
+  const int wpb = warps_per_block(S);
+  const size_t smem = (size_t)wpb * (2 * kChunk + 4) * sizeof(uint32_t);
+  const int64_t blocks = (S + wpb - 1) / wpb;
+  encode_kernel<true><<<(unsigned)blocks, wpb * 32, smem, st>>>(p);
+  TFC_LAUNCHED("encode_kernel<unbounded>");
+  return TFC_OK;
+}
+
+extern "C" int tfc_unbounded_index_range_decode(
+    const uint8_t* d_enc, int64_t cap, const int32_t* d_nbytes, const int32_t* d_index,
+    int64_t index_stride, int64_t S, int64_t n, const int32_t* d_cdf, int32_t rows, int32_t cols,
+    const int32_t* d_cdf_size, const int32_t* d_offset, int precision, int overflow_width,
+    int debug_level, int32_t* d_out, int32_t* d_status, void* stream) {
+  int rc = check_attrs(precision, overflow_width, debug_level, true);
+  if (rc) return rc;
+  rc = check_unbounded_shapes(rows, cols);
+  if (rc) return rc;
+  if (index_stride != 0 && index_stride != n)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "index_stride must be n or 0");
+  if (cap < 0 || cap > 0x7FFFFFF0ll || n < 0 || S < 0)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "bad sizes: S=%lld n=%lld cap=%lld", (long long)S,
+                     (long long)n, (long long)cap);
+  if (S == 0 || n == 0) return TFC_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (debug_level > 0) {
+    rc = run_unbounded_checks(d_index, index_stride ? S * n : n, d_cdf, rows, cols, d_cdf_size,
+                              precision, st);
+    if (rc) return rc;
+  }
+  DecodeParams p{};
+  p.enc = d_enc; p.cap = cap; p.nbytes = d_nbytes; p.index = d_index;
+  p.index_stride = index_stride; p.cdf_size = d_cdf_size; p.offset = d_offset;
+  p.rows = rows; p.cols = cols; p.overflow_width = overflow_width; p.out32 = d_out;
+  p.cdf = d_cdf; p.S = S; p.n = n; p.precision = precision; p.status = d_status;
+  const int64_t dense = (int64_t)rows * cols * 4 + (int64_t)rows * 16 + 16;
+  const int budget = (int)std::min<int64_t>(dense, kTableBudget);
+  p.table_budget = budget;
+  static bool attr_set = false;
+  if (!attr_set) {
+    TFC_CUDA(cudaFuncSetAttribute(decode_unbounded_kernel,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, kTableBudget));
+    attr_set = true;
+  }
+  const int wpb = warps_per_block(S);
+  const int64_t blocks = (S + wpb - 1) / wpb;
+  decode_unbounded_kernel<<<(unsigned)blocks, wpb * 32, (size_t)budget, st>>>(p);
+  TFC_LAUNCHED("decode_unbounded_kernel");
+  return TFC_OK;
+}
+
+extern "C" int tfc_range_encode(const int16_t* d_data, int64_t S, const int64_t* data_shape,
+                                int rank, const int32_t* d_cdf, const int64_t* cdf_shape,
+                                int cdf_rank, int64_t cdf_stream_stride, int precision,
+                                int debug_level, uint8_t* d_out, int64_t cap, int32_t* d_nbytes,
+                                int32_t* d_status, void* stream) {
+  int rc = check_attrs(precision, 1, debug_level, false);
+  if (rc) return rc;
+  EncodeParams p{};
+  int64_t n = 0, cdf_rows = 0;
+  rc = plan_broadcast(data_shape, rank, cdf_shape, cdf_rank, &p.bc, &n, &p.chip, &cdf_rows);
+  if (rc) return rc;
+  if (cap < 0 || cap > 0x7FFFFFF0ll || S < 0)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "bad sizes: S=%lld cap=%lld", (long long)S,
+                     (long long)cap);
+  if (S == 0) return TFC_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (debug_level > 0) {
+    if (p.chip <= 2)
+      return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "CDF size should be > 2: %d", p.chip);
+    CheckRecord* rec = nullptr;
+    rc = alloc_record(&rec, st);
+    if (rc) return rc;
+    const int64_t total_rows = cdf_stream_stride ? cdf_rows + (S - 1) * (cdf_stream_stride / p.chip)
+                                                 : cdf_rows;
+    check_cdf_kernel<<<(unsigned)((total_rows + 127) / 128), 128, 0, st>>>(
+        d_cdf, total_rows, p.chip, nullptr, false, precision, rec);
+    TFC_LAUNCHED("check_cdf_kernel");
+    if (S * n > 0) {
+      const int blocks = (int)std::min<int64_t>((S * n + 255) / 256, 4 * tfc::num_sms());
+      check_data16_kernel<<<blocks, 256, 0, st>>>(d_data, S * n, p.chip, rec);
+      TFC_LAUNCHED("check_data16_kernel");
+    }
+    rc = finish_checks(rec, st, 0, 0, precision, p.chip);
+    if (rc) return rc;
+  }
+  p.data16 = d_data; p.cdf_stream_stride = cdf_stream_stride; p.cdf = d_cdf;
+  p.S = S; p.n = n; p.precision = precision;
+  p.out = d_out; p.cap = cap; p.nbytes = d_nbytes; p.status = d_status;
+  const int wpb = warps_per_block(S);
+  const size_t smem = (size_t)wpb * (2 * kChunk + 4) * sizeof(uint32_t);
+  encode_kernel<false><<<(unsigned)((S + wpb - 1) / wpb), wpb * 32, smem, st>>>(p);
+  TFC_LAUNCHED("encode_kernel<bounded>");
+  return TFC_OK;
+}
+
+extern "C" int tfc_range_decode(const uint8_t* d_enc, int64_t cap, const int32_t* d_nbytes,
+                                int64_t S, const int64_t* data_shape, int rank,
+                                const int32_t* d_cdf, const int64_t* cdf_shape, int cdf_rank,
+                                int64_t cdf_stream_stride, int precision, int debug_level,
+                                int16_t* d_out, int32_t* d_status, void* stream) {
+  int rc = check_attrs(precision, 1, debug_level, false);
+  if (rc) return rc;
+  DecodeParams p{};
+  int64_t n = 0, cdf_rows = 0;
+  rc = plan_broadcast(data_shape, rank, cdf_shape, cdf_rank, &p.bc, &n, &p.chip, &cdf_rows);
+  if (rc) return rc;
+  if (cap < 0 || cap > 0x7FFFFFF0ll || S < 0)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "bad sizes: S=%lld cap=%lld", (long long)S,
+                     (long long)cap);
+  if (S == 0 || n == 0) return TFC_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (debug_level > 0) {
+    if (p.chip <= 2)
+      return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "CDF size should be > 2: %d", p.chip);
+    CheckRecord* rec = nullptr;
+    rc = alloc_record(&rec, st);
+    if (rc) return rc;
+    const int64_t total_rows = cdf_stream_stride ? cdf_rows + (S - 1) * (cdf_stream_stride / p.chip)
+                                                 : cdf_rows;
+    check_cdf_kernel<<<(unsigned)((total_rows + 127) / 128), 128, 0, st>>>(
+        d_cdf, total_rows, p.chip, nullptr, false, precision, rec);
+    TFC_LAUNCHED("check_cdf_kernel");
+    rc = finish_checks(rec, st, 0, 0, precision, p.chip);
+    if (rc) return rc;
+  }
+  p.enc = d_enc; p.cap = cap; p.nbytes = d_nbytes; p.cdf_stream_stride = cdf_stream_stride;
+  p.out16 = d_out; p.cdf = d_cdf; p.S = S; p.n = n; p.precision = precision; p.status = d_status;
+  const int wpb = warps_per_block(S);
+  decode_bounded_kernel<<<(unsigned)((S + wpb - 1) / wpb), wpb * 32, 0, st>>>(p);
+  TFC_LAUNCHED("decode_bounded_kernel");
+  return TFC_OK;
+}

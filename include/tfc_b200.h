@@ -1,0 +1,122 @@
+/* tfc_b200.h — C ABI of libtfc_b200.so, the B200 (sm_100a) implementation of the
+ * tensorflow_compression learned-image-codec hot path.
+ *
+ * This header is the drop-in boundary.  The reference reaches its native code
+ * through a TF custom-op library (`load_op_library("libtensorflow_compression.so")`,
+ * python/ops/range_coding_ops.py:26-28); this library exports the same five ops — batched, on
+ * device buffers — as plain `extern "C"` functions, plus the layer-level kernels the reference
+ * gets from stock TF ops (conv2d, conv2d_backprop_input, GDN's 1x1 conv, erfc, ...).
+ * Citations are relative to /root/reference/tensorflow_compression/.
+ *
+ * Conventions
+ *   - every pointer named d_* is a DEVICE pointer; h_* is a HOST pointer;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); all work is
+ *     stream-ordered and the functions are re-entrant (no global mutable state);
+ *   - the return value is a tfc_status; tfc_last_error() gives the message of the calling
+ *     thread's last failure, using the reference's own wording where the reference has one
+ *     (cc/kernels/range_coding_kernels.cc:137-176, unbounded_index_range_coding_kernels.cc:
+ *     58-139, range_coding_kernels_util.cc:58-60);
+ *   - the library never allocates device memory behind the caller's back; scratch space is
+ *     passed in and sized by the matching *_workspace() function;
+ *   - there is no CPU fallback: without a CUDA device every compute entry point returns
+ *     TFC_ERR_CUDA.
+ */
+#ifndef TFC_B200_H_
+#define TFC_B200_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  TFC_OK = 0,
+  TFC_ERR_INVALID_ARGUMENT = 1, /* == tf.errors.InvalidArgumentError in the reference */
+  TFC_ERR_CUDA = 2,             /* CUDA runtime failure (message has cudaGetErrorString) */
+  TFC_ERR_CAPACITY = 3,         /* an encode output slab was too small; nbytes[] holds need */
+  TFC_ERR_DECODE = 4,           /* corrupt stream (reference: CHECK-abort, range_coder.cc:347) */
+  TFC_ERR_UNIMPLEMENTED = 5     /* == NotImplementedError (signal_conv.py:393-401) */
+} tfc_status;
+
+const char* tfc_last_error(void);
+const char* tfc_version(void);
+/* number of kernels this library has launched since load (bench.py's gpu_launches) */
+int64_t tfc_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Entropy coding — replaces the five custom ops of cc/ops/range_coding_ops.cc
+ * ---------------------------------------------------------------------------------------- */
+
+/* Per-stream status bits written to d_status[s]. */
+#define TFC_STREAM_OK 0
+#define TFC_STREAM_CAPACITY 1 /* output did not fit in cap; d_nbytes[s] is the needed size */
+#define TFC_STREAM_CORRUPT 2  /* decoder search ran past the end of a CDF */
+
+/* UnboundedIndexRangeEncode (cc/ops/range_coding_ops.cc:125-135; kernel
+ * cc/kernels/unbounded_index_range_coding_kernels.cc:160-251), batched: S independent streams
+ * of n symbols, one encoded string per stream — exactly what EntropyModel.compress builds with
+ * tf.map_fn over the batch (python/layers/entropy_models.py:234-244).
+ *   d_data   [S, n] int32      d_index [S, n] (index_stride = n) or [n] shared (index_stride = 0)
+ *   d_cdf    [rows, cols]      d_cdf_size, d_offset [rows]
+ *   d_out    [S, cap] bytes    d_nbytes [S] int32 length of each string
+ *   d_status [S] int32 (may be NULL)
+ * debug_level 1 runs the reference's CheckArgumentValues (:107-115) on the device and
+ * synchronises the stream to report it; 0 (what the layers pass, entropy_models.py:239) does
+ * not synchronise. */
+int tfc_unbounded_index_range_encode(const int32_t* d_data, const int32_t* d_index,
+                                     int64_t index_stride, int64_t S, int64_t n,
+                                     const int32_t* d_cdf, int32_t rows, int32_t cols,
+                                     const int32_t* d_cdf_size, const int32_t* d_offset,
+                                     int precision, int overflow_width, int debug_level,
+                                     uint8_t* d_out, int64_t cap, int32_t* d_nbytes,
+                                     int32_t* d_status, void* stream);
+
+/* UnboundedIndexRangeDecode (cc/ops/range_coding_ops.cc:203-216; kernel :280-368).
+ *   d_enc [S, cap] bytes, d_nbytes [S]; reads past the end of a string yield zeros
+ *   (range_coder.cc:368-377).  d_out [S, n] int32. */
+int tfc_unbounded_index_range_decode(const uint8_t* d_enc, int64_t cap, const int32_t* d_nbytes,
+                                     const int32_t* d_index, int64_t index_stride, int64_t S,
+                                     int64_t n, const int32_t* d_cdf, int32_t rows, int32_t cols,
+                                     const int32_t* d_cdf_size, const int32_t* d_offset,
+                                     int precision, int overflow_width, int debug_level,
+                                     int32_t* d_out, int32_t* d_status, void* stream);
+
+/* RangeEncode / RangeDecode (cc/ops/range_coding_ops.cc:29-35, :91-103; kernels
+ * cc/kernels/range_coding_kernels.cc:178-380), batched over S streams that share one
+ * data shape and one cdf shape.  `data_shape[rank]` and `cdf_shape[rank+1]` are the
+ * per-stream tensor shapes as the op sees them; the broadcast rules, axis merging and error
+ * texts are those of CheckCdfShape (:137-151) and MergeAxes (range_coding_kernels_util.cc:
+ * 36-92).  cdf_stream_stride = number of int32 between the cdf of consecutive streams
+ * (0: all streams share one cdf tensor).
+ *   d_data [S, prod(data_shape)] int16 ; d_out/d_nbytes/d_status as above. */
+int tfc_range_encode(const int16_t* d_data, int64_t S, const int64_t* data_shape, int rank,
+                     const int32_t* d_cdf, const int64_t* cdf_shape, int cdf_rank,
+                     int64_t cdf_stream_stride, int precision, int debug_level, uint8_t* d_out,
+                     int64_t cap, int32_t* d_nbytes, int32_t* d_status, void* stream);
+int tfc_range_decode(const uint8_t* d_enc, int64_t cap, const int32_t* d_nbytes, int64_t S,
+                     const int64_t* data_shape, int rank, const int32_t* d_cdf,
+                     const int64_t* cdf_shape, int cdf_rank, int64_t cdf_stream_stride,
+                     int precision, int debug_level, int16_t* d_out, int32_t* d_status,
+                     void* stream);
+
+/* PmfToQuantizedCdf (cc/ops/range_coding_ops.cc:244-257; kernel
+ * cc/kernels/range_coding_helper_kernels.cc:53-204): d_pmf [rows, n] float32 ->
+ * d_cdf [rows, n+1] int32, one device thread per row replaying libstdc++'s std::sort
+ * decision sequence so that ties resolve exactly as in the reference build.
+ * Workspace: tfc_pmf_to_quantized_cdf_workspace(rows, n) bytes of device memory. */
+size_t tfc_pmf_to_quantized_cdf_workspace(int64_t rows, int32_t n);
+int tfc_pmf_to_quantized_cdf(const float* d_pmf, int64_t rows, int32_t n, int precision,
+                             int32_t* d_cdf, void* d_workspace, size_t workspace_bytes,
+                             void* stream);
+
+/* Host-side helper shared by the bounded ops: the reference's MergeAxes
+ * (range_coding_kernels_util.cc:36-92).  Writes the merged shapes (at most rank entries, and
+ * one more for the cdf) and returns their count through *merged_rank. */
+int tfc_merge_axes(const int64_t* data_shape, int rank, const int64_t* cdf_shape, int cdf_rank,
+                   int64_t* merged_data_shape, int64_t* merged_cdf_shape, int* merged_rank);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TFC_B200_H_ */

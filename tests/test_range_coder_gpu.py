@@ -1,0 +1,240 @@
+"""GPU parity tests of the entropy-coding kernels, through the C ABI, against the CPU checker
+(oracle/_ref when built, else the port) and the reference's golden vectors."""
+import numpy as np
+import pytest
+import torch
+
+from tests.golden import tfc_goldens as G
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def tfc():
+  import compression_b200 as tfc_mod
+  return tfc_mod
+
+
+def test_eb_golden(tfc):
+  # entropy_models_test.py:179-221 — decode the stored strings, and re-encode to the same bytes
+  for b in range(2):
+    sym = tfc.unbounded_index_range_decode(G.EB_BITSTRINGS[b], G.EB_INDEX, G.EB_CDF,
+                                           G.EB_CDF_LENGTH, G.EB_OFFSET, 16, 4)
+    np.testing.assert_array_equal(sym.cpu().numpy(), G.EB_EXPECTED[b].astype(np.int32))
+    enc = tfc.unbounded_index_range_encode(G.EB_EXPECTED[b].astype(np.int32), G.EB_INDEX,
+                                           G.EB_CDF, G.EB_CDF_LENGTH, G.EB_OFFSET, 16, 4)
+    assert enc == G.EB_BITSTRINGS[b]
+
+
+@pytest.mark.parametrize("name", sorted(G.CONDITIONALS))
+def test_conditional_golden(tfc, name):
+  g = G.CONDITIONALS[name]
+  for b in range(2):
+    sym = tfc.unbounded_index_range_decode(g["bitstrings"][b], G.COND_INDEXES[b], g["cdf"],
+                                           g["cdf_length"], g["offset"], 16, 4)
+    np.testing.assert_array_equal(sym.cpu().numpy(), G.COND_EXPECTED[b].astype(np.int32))
+    enc = tfc.unbounded_index_range_encode(G.COND_EXPECTED[b].astype(np.int32),
+                                           G.COND_INDEXES[b], g["cdf"], g["cdf_length"],
+                                           g["offset"], 16, 4)
+    assert enc == g["bitstrings"][b]
+
+
+def _random_tables(rng, rows, max_len, precision):
+  total = 1 << precision
+  cdf = np.zeros((rows, max_len), np.int32)
+  size = np.zeros(rows, np.int32)
+  for r in range(rows):
+    n = int(rng.integers(3, min(max_len, total + 1) + 1))
+    cuts = np.sort(rng.choice(np.arange(1, total), size=n - 2, replace=False))
+    cdf[r, :n] = np.concatenate([[0], cuts, [total]])
+    size[r] = n
+  offset = rng.integers(-5, 6, size=rows).astype(np.int32)
+  return cdf, size, offset
+
+
+def test_unbounded_random_sweep(tfc, oracle):
+  """>=10^4 streams over precision 1..16, overflow_width 1..16, escapes of both signs, ragged
+  cdf_size, empty and tiny streams."""
+  from compression_b200.python.ops import range_coding_ops as rc
+  rng = np.random.default_rng(0)
+  total_streams = 0
+  for trial in range(120):
+    precision = int(rng.integers(1, 17))
+    ow = int(rng.integers(1, 17))
+    rows = int(rng.integers(1, 9))
+    max_len = int(rng.integers(3, min(80, (1 << precision) + 1) + 1))
+    cdf, size, offset = _random_tables(rng, rows, max_len, precision)
+    S = int(rng.choice([1, 3, 100, 150]))
+    n = int(rng.choice([0, 1, 31, 32, 33, 127, 128, 129, 300]))
+    shared = bool(rng.integers(0, 2))
+    index = rng.integers(0, rows, size=(n,) if shared else (S, n)).astype(np.int32)
+    limit = 1 << (ow * (31 // ow))
+    spread = int(min(rng.choice([2, 10, 1000, 100000]), limit // 4 - 8))
+    data = (rng.integers(-spread, spread + 1, size=(S, n)) + offset[index]).astype(np.int32)
+    out, nbytes = rc.unbounded_index_range_encode_batch(data, index, cdf, size, offset,
+                                                        precision, ow, debug_level=1)
+    got = rc.strings_to_host(out, nbytes)
+    for s in range(S):
+      want = oracle.ui_encode(data[s], index if shared else index[s], cdf, size, offset,
+                              precision, ow)
+      assert got[s] == want, (trial, s, precision, ow)
+    dec = rc.unbounded_index_range_decode_batch(out, nbytes, index, cdf, size, offset,
+                                                precision, ow, debug_level=1,
+                                                shared_index=shared)
+    np.testing.assert_array_equal(dec.cpu().numpy(), data)
+    total_streams += S
+  assert total_streams >= 5000
+
+
+def test_unbounded_long_rows_and_carry(tfc, oracle):
+  """Rows longer than the 32-wide search window (Gaussian-like, up to 1481 entries) and long
+  runs of near-certain symbols that keep the encoder in its carry-pending state
+  (range_coder.cc:169-210)."""
+  from compression_b200.python.ops import range_coding_ops as rc
+  rng = np.random.default_rng(3)
+  lens = [5, 40, 300, 1481]
+  cdf = np.zeros((len(lens), max(lens)), np.int32)
+  for r, n in enumerate(lens):
+    k = np.arange(n - 2) - (n - 3) / 2.0
+    p = np.exp(-0.5 * (k / (n / 8.0 + 0.2)) ** 2)
+    p = np.concatenate([p / p.sum() * (1 - 2.0 ** -8), [2.0 ** -8]]).astype(np.float32)
+    cdf[r, :n] = oracle.pmf_to_cdf(p[None], 16)[0]
+  size = np.array(lens, np.int32)
+  offset = -((size - 3) // 2)
+  S, n = 37, 2000
+  index = rng.integers(0, len(lens), size=(S, n)).astype(np.int32)
+  sigma = (size[index] / 8.0 + 0.2)
+  data = np.rint(rng.standard_normal((S, n)) * sigma * rng.choice([0.05, 1, 3], size=(S, 1)))
+  data = data.astype(np.int32)
+  out, nbytes = rc.unbounded_index_range_encode_batch(data, index, cdf, size, offset, 16, 4, 1)
+  got = rc.strings_to_host(out, nbytes)
+  for s in range(S):
+    assert got[s] == oracle.ui_encode(data[s], index[s], cdf, size, offset, 16, 4), s
+  dec = rc.unbounded_index_range_decode_batch(out, nbytes, index, cdf, size, offset, 16, 4, 1)
+  np.testing.assert_array_equal(dec.cpu().numpy(), data)
+  # carry path: symbol 1 of a [0, 1, 65535, 65536] table has probability ~1
+  cdf2 = np.array([[0, 1, 65535, 65536], [0, 32768, 65535, 65536]], np.int32)
+  size2 = np.array([4, 4], np.int32)
+  off2 = np.zeros(2, np.int32)
+  data2 = np.ones((8, 5000), np.int32)
+  data2[:, ::977] = 0
+  data2[3, 100:120] = 7  # escapes in the middle of a run
+  idx2 = np.zeros((8, 5000), np.int32)
+  idx2[:, ::13] = 1
+  out, nbytes = rc.unbounded_index_range_encode_batch(data2, idx2, cdf2, size2, off2, 16, 4, 1)
+  got = rc.strings_to_host(out, nbytes)
+  for s in range(8):
+    assert got[s] == oracle.ui_encode(data2[s], idx2[s], cdf2, size2, off2, 16, 4), s
+  dec = rc.unbounded_index_range_decode_batch(out, nbytes, idx2, cdf2, size2, off2, 16, 4, 1)
+  np.testing.assert_array_equal(dec.cpu().numpy(), data2)
+
+
+def test_bounded_broadcast_patterns(tfc, oracle):
+  """range_coding_kernels_test.cc:245-321: no broadcast, 1-axis and 2-axis cdf broadcast."""
+  rng = np.random.default_rng(4)
+  for trial in range(60):
+    precision = int(rng.integers(2, 17))
+    m = int(rng.integers(2, min(50, 1 << precision) + 1))
+    rank = int(rng.integers(1, 5))
+    shape = tuple(int(x) for x in rng.integers(1, 7, size=rank))
+    lead = tuple(s if rng.random() < 0.5 else 1 for s in shape)
+    pmf = rng.random(lead + (m,)).astype(np.float32) + 1e-3
+    pmf /= pmf.sum(-1, keepdims=True)
+    cdf = oracle.pmf_to_cdf(pmf, precision)
+    data = rng.integers(0, m, size=shape).astype(np.int16)
+    enc = tfc.range_encode(data, cdf, precision)
+    assert enc == oracle.rc_encode(data, cdf, precision), (trial, shape, lead)
+    dec = tfc.range_decode(enc, shape, cdf, precision)
+    np.testing.assert_array_equal(dec.cpu().numpy(), data)
+
+
+def test_bounded_readme_example(tfc):
+  """python/ops/range_coding_ops_test.py:33-46 / docs/range_coding.md:52-71."""
+  rng = np.random.default_rng(5)
+  data = rng.integers(0, 10, size=(4, 6, 6)).astype(np.int16)
+  hist = np.bincount(data.ravel(), minlength=10).astype(np.float32)
+  from compression_b200.python.ops import range_coding_ops as rc
+  cdf = rc.pmf_to_quantized_cdf(hist / hist.sum(), 14)
+  cdf = cdf.reshape(1, 1, 1, -1)
+  enc = tfc.range_encode(data, cdf, 14)
+  dec = tfc.range_decode(enc, data.shape, cdf, 14)
+  np.testing.assert_array_equal(dec.cpu().numpy(), data)
+  assert len(enc) < data.size  # < 8 bits per symbol
+
+
+def test_debug_level_errors(tfc):
+  """Error wording of unbounded_index_range_coding_kernels.cc:58-104 and
+  range_coding_kernels.cc:153-176,250-255."""
+  cdf = np.array([[0, 10, 65536, 0], [0, 5, 100, 65536]], np.int32)
+  size = np.array([3, 4], np.int32)
+  off = np.zeros(2, np.int32)
+  data = np.zeros(4, np.int32)
+  with pytest.raises(tfc.InvalidArgumentError, match=r"'index' has a value not in \[0, 2\)"):
+    tfc.unbounded_index_range_encode(data, np.array([0, 1, 2, 0], np.int32), cdf, size, off,
+                                     16, 4)
+  idx = np.zeros(4, np.int32)
+  with pytest.raises(tfc.InvalidArgumentError, match=r"'cdf_size' has a value not in \[3, 4\]"):
+    tfc.unbounded_index_range_encode(data, idx, cdf, np.array([2, 4], np.int32), off, 16, 4)
+  bad = cdf.copy(); bad[0, 2] = 65535
+  with pytest.raises(tfc.InvalidArgumentError, match="Each cdf should start from 0 and end at"):
+    tfc.unbounded_index_range_encode(data, idx, bad, size, off, 16, 4)
+  bad = cdf.copy(); bad[1, 2] = 5
+  with pytest.raises(tfc.InvalidArgumentError, match="CDF is not monotonic"):
+    tfc.unbounded_index_range_decode(b"\0\0", idx, bad, size, off, 16, 4)
+  with pytest.raises(tfc.InvalidArgumentError, match="should match the number of rows"):
+    tfc.unbounded_index_range_encode(data, idx, cdf, size[:1], off, 16, 4)
+  # debug_level=0 skips the value checks
+  tfc.unbounded_index_range_encode(data, idx, cdf, size, off, 16, 4, debug_level=0)
+  # bounded op
+  d16 = np.array([0, 1, 2, 3], np.int16)
+  c = np.array([[0, 100, 1000, 65536]], np.int32)
+  with pytest.raises(tfc.InvalidArgumentError, match=r"value not in \[0, 3\)"):
+    tfc.range_encode(d16, c, 16)
+  with pytest.raises(tfc.InvalidArgumentError, match="CDF should start from 0 and end at"):
+    tfc.range_encode(d16[:3], np.array([[0, 100, 1000, 65535]], np.int32), 16)
+  with pytest.raises(tfc.InvalidArgumentError, match="CDF size should be > 2"):
+    tfc.range_encode(np.zeros(3, np.int16), np.array([[0, 65536]], np.int32), 16)
+  with pytest.raises(tfc.InvalidArgumentError, match="Cannot broadcast shape"):
+    tfc.range_encode(np.zeros((2, 3), np.int16), np.zeros((2, 4, 5), np.int32), 16)
+
+
+def test_pmf_to_quantized_cdf_matches_checker(tfc, oracle):
+  """Bit-exact against the compiled PerShard, including tie-heavy symmetric rows and rows long
+  enough for every std::sort code path; plus the reference's own property test
+  (range_coding_helper_kernels_test.cc:70-142)."""
+  rng = np.random.default_rng(6)
+  for n in (2, 3, 16, 17, 22, 64, 257, 1481):
+    rows = []
+    k = np.arange(n, dtype=np.float64) - (n - 1) / 2
+    for sigma in (0.3, 2.0, n / 6.0 + 0.1):
+      p = np.exp(-0.5 * (k / sigma) ** 2)
+      rows.append(p / p.sum())
+    r = rng.random((13, n)) + 1e-4
+    rows.extend(r / r.sum(-1, keepdims=True))
+    pmf = np.array(rows, np.float32)
+    for precision, scale in ((16, 1.0), (12, 1.3), (10, 0.8)):
+      if n + 1 > (1 << precision):
+        continue
+      got = tfc.pmf_to_quantized_cdf(pmf * scale, precision).cpu().numpy()
+      want = oracle.pmf_to_cdf(pmf * np.float32(scale), precision)
+      np.testing.assert_array_equal(got, want)
+      assert (got[:, 0] == 0).all() and (got[:, -1] == 1 << precision).all()
+      assert (np.diff(got, axis=-1) > 0).all()
+
+
+def test_pmf_gaussian_model_table(tfc, oracle):
+  """The 64-level bmshj2018 scale table (bmshj2018.py:46-48, entropy_models.py:827-858): the
+  rows on which a stable sort is known to differ from std::sort (SURVEY probe 4)."""
+  import scipy.stats
+  table = np.exp(np.linspace(np.log(0.11), np.log(256), 64))
+  mult = -scipy.stats.norm.ppf(2.0 ** -8 / 2)
+  center = np.ceil(table * mult).astype(int)
+  for r in (0, 20, 40, 63):
+    n = 2 * center[r] + 1
+    s = np.abs(np.arange(n) - center[r]).astype(np.float32)
+    sc = np.float32(table[r])
+    up = 0.5 * scipy.special.erfc(-(2 ** -0.5) * ((np.float32(.5) - s) / sc).astype(np.float32))
+    lo = 0.5 * scipy.special.erfc(-(2 ** -0.5) * ((np.float32(-.5) - s) / sc).astype(np.float32))
+    pmf = np.concatenate([(up - lo), [2 * lo[0]]]).astype(np.float32)
+    got = tfc.pmf_to_quantized_cdf(pmf, 16).cpu().numpy()
+    np.testing.assert_array_equal(got, oracle.pmf_to_cdf(pmf[None], 16)[0])
