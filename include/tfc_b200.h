@@ -116,6 +116,64 @@ int tfc_pmf_to_quantized_cdf(const float* d_pmf, int64_t rows, int32_t n, int pr
 int tfc_merge_axes(const int64_t* data_shape, int rank, const int64_t* cdf_shape, int cdf_rank,
                    int64_t* merged_data_shape, int64_t* merged_cdf_shape, int* merged_rank);
 
+
+/* ------------------------------------------------------------------------------------------
+ * Entropy models — the elementwise half of python/layers/entropy_models.py.  All tensors are
+ * channels_last: `count` elements with the channel index fastest (channel = i % channels).
+ * ---------------------------------------------------------------------------------------- */
+
+/* Per-channel density-network parameters of EntropyBottleneck (entropy_models.py:461-489),
+ * already reparameterised (softplus(matrix), tanh(factor)), packed per channel as
+ *   layer 0..L: matrix[f_{i+1}][f_i], bias[f_{i+1}], then (i < L) factor[f_{i+1}]
+ * with f = (1,) + filters + (1,) and L = len(filters).  `filters` must be uniform (all layers
+ * the same width <= 4, at most 4 layers; (3,3,3) is the default and what both models use). */
+
+/* EntropyBottleneck call(training=False) (entropy_models.py:148-187 with :609-614, :626-658):
+ *   d_values[i] = floor(x + (0.5 - median_c)) + median_c
+ *   d_lik[i]    = max(|sigmoid(s*upper) - sigmoid(s*lower)|, likelihood_bound)
+ * mode 0: quantise as above; mode 1: x is used as given (training=True path after the caller
+ * has added its uniform noise, :605-607).  d_values may be NULL in mode 1. */
+int tfc_eb_call(const float* d_x, int64_t count, int32_t channels, const float* d_params,
+                int32_t num_filters, int32_t filter_width, const float* d_medians,
+                float likelihood_bound, int mode, float* d_values, float* d_lik, void* stream);
+
+/* _quantize(mode="symbols") (entropy_models.py:609-618): int32(floor(x + (0.5 - median_c))) */
+int tfc_eb_symbols(const float* d_x, int64_t count, int32_t channels, const float* d_medians,
+                   int32_t* d_symbols, void* stream);
+/* _dequantize (entropy_models.py:620-624): float(symbol) + median_c.
+ * out_bf16 != 0 writes bfloat16 (the form the hyper-synthesis kernels consume). */
+int tfc_eb_dequantize(const int32_t* d_symbols, int64_t count, int32_t channels,
+                      const float* d_medians, void* d_out, int out_bf16, void* stream);
+
+/* Logits of the cumulative (entropy_models.py:402-436) at arbitrary points, used on the host
+ * side to build the PMF tables (:540-559): d_x [channels, samples] -> d_logits same shape. */
+int tfc_eb_logits_cumulative(const float* d_x, int32_t channels, int32_t samples,
+                             const float* d_params, int32_t num_filters, int32_t filter_width,
+                             float* d_logits, void* stream);
+
+/* GaussianConditional call(training=False), mean=None (entropy_models.py:887-932, :965-969):
+ *   d_values = floor(y + 0.5);  s = max(sigma, scale_bound)
+ *   d_lik    = max(Phi((.5-|v|)/s) - Phi((-.5-|v|)/s), likelihood_bound), Phi(t)=.5*erfc(-t/sqrt2)
+ * mode 1: y used as given (noise path). */
+int tfc_gaussian_call(const float* d_y, const float* d_sigma, int64_t count, float scale_bound,
+                      float likelihood_bound, int mode, float* d_values, float* d_lik,
+                      void* stream);
+
+/* Compress-side fusion (entropy_models.py:221 + :869-881 + :895-907):
+ *   d_symbols = int32(floor(y + 0.5))              (d_y / d_symbols may be NULL)
+ *   d_indexes = (levels-1) - #{k < levels-1 : max(sigma, scale_bound) <= table[k]}
+ * d_table: `levels` ascending float32 scales on the device. */
+int tfc_gaussian_symbols_indexes(const float* d_y, const float* d_sigma, int64_t count,
+                                 const float* d_table, int32_t levels, float scale_bound,
+                                 int32_t* d_symbols, int32_t* d_indexes, void* stream);
+
+/* _dequantize for mean=None: float(symbol); out_bf16 as above. */
+int tfc_symbols_to_float(const int32_t* d_symbols, int64_t count, void* d_out, int out_bf16,
+                         void* stream);
+
+/* abs() + cast feeding the hyper-analysis transform (examples/bmshj2018.py:304). */
+int tfc_abs_to_bf16(const float* d_x, int64_t count, void* d_out_bf16, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
