@@ -7,3 +7,13 @@ from compression_b200._lib import InvalidArgumentError, CudaError, launch_count
 from compression_b200.python.ops.range_coding_ops import (
     range_encode, range_decode, unbounded_index_range_encode, unbounded_index_range_decode,
     pmf_to_quantized_cdf)
+from compression_b200.python.ops.math_ops import lower_bound, upper_bound
+from compression_b200.python.ops.padding_ops import same_padding_for_kernel
+from compression_b200.python.ops.spectral_ops import irdft_matrix
+from compression_b200.python.layers.parameterizers import (
+    Parameterizer, StaticParameterizer, RDFTParameterizer, NonnegativeParameterizer)
+from compression_b200.python.layers.gdn import GDN
+from compression_b200.python.layers.signal_conv import SignalConv2D
+from compression_b200.python.layers.entropy_models import (
+    EntropyModel, EntropyBottleneck, SymmetricConditional, GaussianConditional,
+    LogisticConditional, LaplacianConditional)

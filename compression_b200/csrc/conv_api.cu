@@ -1,0 +1,71 @@
+// C-ABI entry points of the transforms: validation + dispatch between the tcgen05 path and
+// the CUDA-core path.
+#include <algorithm>
+
+#include "common.cuh"
+#include "conv_common.cuh"
+
+namespace {
+
+int validate(const tfc_conv_desc* d) {
+  if (!d) return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "null conv descriptor");
+  if (d->n < 0 || d->h <= 0 || d->w <= 0 || d->cin <= 0 || d->ho <= 0 || d->wo <= 0 ||
+      d->cout <= 0 || d->kh <= 0 || d->kw <= 0 || d->sd <= 0 || d->su <= 0)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "bad conv geometry");
+  if (d->act < TFC_ACT_NONE || d->act > TFC_ACT_IGDN)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "bad activation %d", d->act);
+  if ((d->in_dtype != TFC_F32 && d->in_dtype != TFC_BF16) ||
+      (d->out_dtype != TFC_F32 && d->out_dtype != TFC_BF16))
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "bad dtype");
+  return TFC_OK;
+}
+
+bool use_umma(const tfc_conv_desc& d) {
+  if (d.impl == 1) return false;
+  const char* why = nullptr;
+  return tfc::conv_umma_supported(d, &why);
+}
+
+}  // namespace
+
+extern "C" size_t tfc_signal_conv2d_workspace(const tfc_conv_desc* desc) {
+  if (validate(desc)) return 0;
+  size_t need = 256;
+  if (desc->impl != 2) need = std::max(need, tfc::conv_direct_workspace(*desc));
+  const char* why = nullptr;
+  if (desc->impl != 1 && tfc::conv_umma_supported(*desc, &why))
+    need = std::max(need, tfc::conv_umma_workspace(*desc));
+  return need;
+}
+
+extern "C" int tfc_signal_conv2d(const tfc_conv_desc* desc, const void* d_in, const float* d_w,
+                                 const float* d_bias, const float* d_beta, const float* d_gamma,
+                                 void* d_out, void* d_workspace, size_t workspace_bytes,
+                                 void* stream) {
+  int rc = validate(desc);
+  if (rc) return rc;
+  const bool gdn = desc->act == TFC_ACT_GDN || desc->act == TFC_ACT_IGDN;
+  if (gdn && (!d_beta || !d_gamma))
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "GDN activation needs beta and gamma");
+  if (desc->n == 0) return TFC_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (desc->impl == 2) {
+    const char* why = "unknown";
+    if (!tfc::conv_umma_supported(*desc, &why))
+      return tfc::fail(TFC_ERR_UNIMPLEMENTED, "tcgen05 conv path does not support this shape: %s",
+                       why);
+  }
+  if (use_umma(*desc))
+    return tfc::conv_umma(*desc, d_in, d_w, d_bias, d_beta, d_gamma, d_out, d_workspace,
+                          workspace_bytes, st);
+  return tfc::conv_direct(*desc, d_in, d_w, d_bias, d_beta, d_gamma, d_out, d_workspace,
+                          workspace_bytes, st);
+}
+
+extern "C" int tfc_gdn(const void* d_x, int64_t pixels, int32_t channels, const float* d_beta,
+                       const float* d_gamma, int inverse, int in_dtype, int out_dtype,
+                       void* d_out, void* stream) {
+  if (pixels <= 0) return TFC_OK;
+  return tfc::gdn_direct(d_x, pixels, channels, d_beta, d_gamma, inverse != 0, in_dtype,
+                         out_dtype, d_out, static_cast<cudaStream_t>(stream));
+}

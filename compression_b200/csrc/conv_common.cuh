@@ -1,0 +1,27 @@
+// Internal interfaces between the conv dispatcher (conv_api.cu) and its implementations.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "tfc_b200.h"
+
+namespace tfc {
+
+// CUDA-core tiled path (conv_direct.cu): any shape
+size_t conv_direct_workspace(const tfc_conv_desc& d);
+int conv_direct(const tfc_conv_desc& d, const void* in, const float* w, const float* bias,
+                const float* beta, const float* gamma, void* out, void* ws, size_t ws_bytes,
+                cudaStream_t st);
+int gdn_direct(const void* x, int64_t pixels, int channels, const float* beta,
+               const float* gamma, bool inverse, int in_dtype, int out_dtype, void* out,
+               cudaStream_t st);
+
+// tcgen05 implicit-GEMM path (conv_umma.cu): bf16 operands, fp32 accumulation in TMEM
+bool conv_umma_supported(const tfc_conv_desc& d, const char** why);
+size_t conv_umma_workspace(const tfc_conv_desc& d);
+int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const float* bias,
+              const float* beta, const float* gamma, void* out, void* ws, size_t ws_bytes,
+              cudaStream_t st);
+
+}  // namespace tfc

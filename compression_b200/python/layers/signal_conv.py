@@ -1,0 +1,278 @@
+"""SignalConv2D — mirror of `tensorflow_compression/python/layers/signal_conv.py`.
+
+Same constructor arguments as the reference (`signal_conv.py:191-201`).  `call` reproduces the
+reference's dispatch (`:709-814`): kernel flipping for odd supports (`:723-738`), "same"
+padding geometry (`:742-758`, `ops/padding_ops.py`), correlation + downsampling with explicit
+padding (`:487-524`) and upsampled convolution via the transposed-conv formulation
+(`:629-707`) — and reduces each case to the one normalised form the CUDA kernels implement
+(see `tfc_conv_desc` in include/tfc_b200.h).  Combinations the reference itself does not
+implement, and those outside the codecs' hot path (1-D/3-D, `same_reflect`,
+`channel_separable`, `channels_first`), raise NotImplementedError like `:393-401`.
+"""
+import ctypes
+import math
+
+import numpy as np
+import torch
+
+from compression_b200 import _lib
+from compression_b200.python.layers import gdn as gdn_lib
+from compression_b200.python.layers import parameterizers
+from compression_b200.python.ops import padding_ops
+
+__all__ = ["SignalConv2D", "ConvDesc"]
+
+ACT_NONE, ACT_RELU, ACT_GDN, ACT_IGDN = 0, 1, 2, 3
+
+
+class ConvDesc(ctypes.Structure):
+  """ctypes image of tfc_conv_desc."""
+  _fields_ = [(n, ctypes.c_int32) for n in (
+      "n", "h", "w", "cin", "ho", "wo", "cout", "kh", "kw", "sd", "su", "pad_top", "pad_left",
+      "act", "in_dtype", "out_dtype", "impl")]
+
+
+def _dtype_code(dt):
+  if dt == torch.float32:
+    return 0
+  if dt == torch.bfloat16:
+    return 1
+  raise ValueError("unsupported dtype %s (float32 or bfloat16)" % dt)
+
+
+def variance_scaling_init(shape, generator=None, device="cpu", dtype=torch.float32):
+  """tf.initializers.variance_scaling() defaults (scale 1, fan_in, truncated normal), the
+  reference's `kernel_initializer` default (`signal_conv.py:196`)."""
+  kh, kw, cin, _ = shape
+  fan_in = kh * kw * cin
+  stddev = math.sqrt(1.0 / max(1.0, fan_in)) / .87962566103423978
+  t = torch.empty(shape, dtype=torch.float32)
+  torch.nn.init.trunc_normal_(t, mean=0.0, std=stddev, a=-2 * stddev, b=2 * stddev,
+                              generator=generator)
+  return t.to(device=device, dtype=dtype)
+
+
+class SignalConv2D(object):
+  """2-D signal convolution layer (channels_last)."""
+
+  _rank = 2
+
+  def __init__(self, filters, kernel_support, corr=False, strides_down=1, strides_up=1,
+               padding="valid", extra_pad_end=True, channel_separable=False,
+               data_format="channels_last", activation=None, use_bias=False, use_explicit=True,
+               kernel_initializer=None, bias_initializer=None, kernel_regularizer=None,
+               bias_regularizer=None,
+               kernel_parameterizer=parameterizers.RDFTParameterizer(),
+               bias_parameterizer=None, name=None, dtype=torch.float32, impl=0):
+    def pair(v, what):
+      v = tuple(int(x) for x in (v if isinstance(v, (tuple, list)) else (v,) * 2))
+      if len(v) != 2 or any(x < 1 for x in v):
+        raise ValueError("`%s` must be a positive int or a pair of them" % what)
+      return v
+    self.filters = int(filters)
+    self.kernel_support = pair(kernel_support, "kernel_support")
+    self.corr = bool(corr)
+    self.strides_down = pair(strides_down, "strides_down")
+    self.strides_up = pair(strides_up, "strides_up")
+    self.padding = str(padding).lower()
+    if self.padding not in ("valid", "same_zeros", "same_reflect"):
+      raise ValueError("Unsupported padding mode: '{}'".format(padding))
+    self.extra_pad_end = bool(extra_pad_end)
+    self.channel_separable = bool(channel_separable)
+    self.data_format = str(data_format)
+    if self.data_format not in ("channels_first", "channels_last"):
+      raise ValueError("Unknown data format: '{}'.".format(data_format))
+    self.activation = activation
+    self.use_bias = bool(use_bias)
+    self.use_explicit = bool(use_explicit)
+    self.kernel_initializer = kernel_initializer
+    self.bias_initializer = bias_initializer
+    self.kernel_regularizer = kernel_regularizer
+    self.bias_regularizer = bias_regularizer
+    # each layer needs its own parameterizer state (the reference's default object is
+    # stateless; ours remembers the variable shape)
+    self.kernel_parameterizer = (type(kernel_parameterizer)(kernel_parameterizer.dc)
+                                 if isinstance(kernel_parameterizer,
+                                               parameterizers.RDFTParameterizer)
+                                 else kernel_parameterizer)
+    self.bias_parameterizer = bias_parameterizer
+    self.name = name
+    self.dtype = dtype
+    self.impl = int(impl)
+    self.out_dtype = torch.float32  # dtype of the produced activations (float32 | bfloat16)
+    self.built = False
+    self._eff = None
+    self._ws = None
+
+  # ---- reference's capability gaps ------------------------------------------------------
+  def _raise_notimplemented(self):
+    raise NotImplementedError(
+        "The provided combination of SignalConv arguments is not currently implemented "
+        "(kernel_support={}, corr={}, strides_down={}, strides_up={}, channel_separable={}, "
+        "filters={}).".format(self.kernel_support, self.corr, self.strides_down,
+                              self.strides_up, self.channel_separable, self.filters))
+
+  # ---- variables ---------------------------------------------------------------------------
+  def build(self, input_channels, device="cuda", generator=None):
+    cin = int(input_channels)
+    kshape = self.kernel_support + (cin, self.filters)
+    if self.channel_separable:
+      self._raise_notimplemented()
+    init = (self.kernel_initializer(kshape) if self.kernel_initializer is not None
+            else variance_scaling_init(kshape, generator))
+    init = torch.as_tensor(init, dtype=self.dtype).to(device)
+    kp = self.kernel_parameterizer
+    if kp is None:
+      self.kernel_var = init          # variable "kernel"
+    else:
+      self.kernel_var = kp.init(init)  # variable "kernel_rdft"
+    if self.use_bias:
+      b0 = (self.bias_initializer((self.filters,)) if self.bias_initializer is not None
+            else torch.zeros(self.filters))
+      b0 = torch.as_tensor(b0, dtype=self.dtype).to(device)
+      bp = self.bias_parameterizer
+      self.bias_var = b0 if bp is None else bp.init(b0)
+    else:
+      self.bias_var = None
+    if isinstance(self.activation, gdn_lib.GDN) and not self.activation.built:
+      self.activation.build(self.filters, device)
+    self.input_channels = cin
+    self.built = True
+    self._eff = None
+
+  def invalidate(self):
+    """Call after changing kernel_var / bias_var so the effective weights are recomputed."""
+    self._eff = None
+    if isinstance(self.activation, gdn_lib.GDN):
+      self.activation.invalidate()
+
+  @property
+  def kernel(self):
+    kp = self.kernel_parameterizer
+    return self.kernel_var if kp is None else kp(self.kernel_var)
+
+  @property
+  def bias(self):
+    if self.bias_var is None:
+      return None
+    bp = self.bias_parameterizer
+    return self.bias_var if bp is None else bp(self.bias_var)
+
+  # ---- geometry: the reference's dispatch reduced to the normalised form ---------------------
+  def _plan(self):
+    """Returns (flip, pad_begin (top, left), out_len_fn) for the current arguments."""
+    if self.padding == "same_reflect":
+      raise NotImplementedError("padding='same_reflect' is not built (SURVEY §8f rank 4)")
+    if self.data_format != "channels_last":
+      raise NotImplementedError("data_format='channels_first' is not built")
+    if self.strides_down[0] != self.strides_down[1] or self.strides_up[0] != self.strides_up[1]:
+      raise NotImplementedError("anisotropic strides are not built")
+    k = self.kernel_support
+    su, sd = self.strides_up[0], self.strides_down[0]
+    corr, flip = self.corr, False
+    odd = all(s % 2 == 1 for s in k)
+    if not corr and su == 1 and odd:        # signal_conv.py:723-728
+      corr, flip = True, True
+    elif corr and su != 1 and odd:          # signal_conv.py:733-738
+      corr, flip = False, True
+    if self.padding == "valid":
+      padding = [(0, 0), (0, 0)]
+    else:
+      padding = padding_ops.same_padding_for_kernel(k, corr, (su, su))
+    if corr and su == 1:
+      # conv2d / convolution with (explicit or zero) padding, then stride sd (:487-524,444-485)
+      pad_begin = (padding[0][0], padding[1][0])
+      def out_len(l, i):
+        return (l + padding[i][0] + padding[i][1] - k[i]) // sd + 1
+      return flip, pad_begin, out_len
+    if not corr:
+      # conv2d_backprop_input with explicit padding p == zero-stuffed correlation with the
+      # flipped kernel and padding k-1-p (:629-707); prepadding is zero in EXPLICIT mode
+      if self.padding == "valid":
+        p = [(k[0] - 1, k[0] - 1), (k[1] - 1, k[1] - 1)]
+      else:
+        p = [(k[i] // 2, (k[i] - 1) // 2) for i in range(2)]
+      pad_begin = (k[0] - 1 - p[0][0], k[1] - 1 - p[1][0])
+      def out_len(l, i):
+        full = l * su + (k[i] - 1) - (p[i][0] + p[i][1])
+        if not self.extra_pad_end:
+          full -= su - 1
+        return (full - 1) // sd + 1
+      return (not flip), pad_begin, out_len   # true convolution == correlation, kernel flipped
+    self._raise_notimplemented()
+
+  def compute_output_shape(self, input_shape):
+    """signal_conv.py:816-845."""
+    n, h, w, _ = input_shape
+    out = []
+    for i, s in enumerate((h, w)):
+      s = s * self.strides_up[i] if self.extra_pad_end else (s - 1) * self.strides_up[i] + 1
+      if self.padding == "valid":
+        s -= self.kernel_support[i] - 1
+      out.append((s - 1) // self.strides_down[i] + 1)
+    return (n, out[0], out[1], self.filters)
+
+  def _activation_code(self):
+    a = self.activation
+    if a is None:
+      return ACT_NONE, None
+    if isinstance(a, gdn_lib.GDN):
+      return (ACT_IGDN if a.inverse else ACT_GDN), None
+    if a in (torch.relu, torch.nn.functional.relu) or a == "relu":
+      return ACT_RELU, None
+    return ACT_NONE, a  # arbitrary callable: applied after the kernel
+
+  def effective_weights(self):
+    """(kernel [kh,kw,cin,cout] in correlation form, bias|None), float32 contiguous; cached."""
+    if self._eff is None:
+      flip, _, _ = self._plan()
+      w = self.kernel.float()
+      if flip:
+        w = torch.flip(w, dims=(0, 1))
+      b = self.bias
+      self._eff = (w.contiguous(), None if b is None else b.float().contiguous())
+    return self._eff
+
+  # ---- forward -----------------------------------------------------------------------------
+  def __call__(self, inputs, out_dtype=None):
+    x = inputs
+    _lib.require_cuda(x, "inputs")
+    if x.dim() != 4:
+      raise ValueError("SignalConv2D expects [batch, height, width, channels]")
+    if not self.built:
+      self.build(x.shape[-1], x.device)
+    if x.shape[-1] != self.input_channels:
+      raise ValueError("layer built for %d input channels, got %d"
+                       % (self.input_channels, x.shape[-1]))
+    if x.dtype not in (torch.float32, torch.bfloat16):
+      x = x.float()
+    x = x.contiguous()
+    _, pad_begin, out_len = self._plan()
+    n, h, w, cin = x.shape
+    ho, wo = out_len(h, 0), out_len(w, 1)
+    assert (n, ho, wo, self.filters) == tuple(self.compute_output_shape(x.shape)), \
+        "internal: output geometry disagrees with compute_output_shape"
+    act, post = self._activation_code()
+    out_dtype = out_dtype or self.out_dtype
+    wgt, bias = self.effective_weights()
+    beta = gamma = None
+    if act in (ACT_GDN, ACT_IGDN):
+      beta, gamma = self.activation.effective()
+    d = ConvDesc(n=n, h=h, w=w, cin=cin, ho=ho, wo=wo, cout=self.filters,
+                 kh=self.kernel_support[0], kw=self.kernel_support[1],
+                 sd=self.strides_down[0], su=self.strides_up[0], pad_top=pad_begin[0],
+                 pad_left=pad_begin[1], act=act, in_dtype=_dtype_code(x.dtype),
+                 out_dtype=_dtype_code(out_dtype), impl=self.impl)
+    L = _lib.lib()
+    L.tfc_signal_conv2d_workspace.restype = ctypes.c_size_t
+    need = int(L.tfc_signal_conv2d_workspace(ctypes.byref(d)))
+    if self._ws is None or self._ws.numel() < need or self._ws.device != x.device:
+      self._ws = torch.empty((max(need, 256),), dtype=torch.uint8, device=x.device)
+    out = torch.empty((n, ho, wo, self.filters), dtype=out_dtype, device=x.device)
+    _lib.check(L.tfc_signal_conv2d(
+        ctypes.byref(d), _lib.ptr(x), _lib.ptr(wgt), _lib.ptr(bias), _lib.ptr(beta),
+        _lib.ptr(gamma), _lib.ptr(out), _lib.ptr(self._ws), ctypes.c_size_t(self._ws.numel()),
+        _lib.stream_ptr(x.device)))
+    if post is not None:
+      out = post(out)
+    return out

@@ -174,6 +174,56 @@ int tfc_symbols_to_float(const int32_t* d_symbols, int64_t count, void* d_out, i
 /* abs() + cast feeding the hyper-analysis transform (examples/bmshj2018.py:304). */
 int tfc_abs_to_bf16(const float* d_x, int64_t count, void* d_out_bf16, void* stream);
 
+
+/* ------------------------------------------------------------------------------------------
+ * Transforms — SignalConv2D and GDN (python/layers/signal_conv.py, python/layers/gdn.py)
+ * ---------------------------------------------------------------------------------------- */
+
+typedef enum { TFC_F32 = 0, TFC_BF16 = 1 } tfc_dtype;
+typedef enum {
+  TFC_ACT_NONE = 0,
+  TFC_ACT_RELU = 1, /* tf.nn.relu (examples/bmshj2018.py:153,157,183,187) */
+  TFC_ACT_GDN = 2,  /* y = x * rsqrt(beta + gamma^T x^2)   (gdn.py:171-202) */
+  TFC_ACT_IGDN = 3  /* y = x * sqrt (beta + gamma^T x^2)   (gdn.py inverse=True) */
+} tfc_activation;
+
+/* One 2-D signal convolution in its normalised form, channels_last:
+ *   out[n,i,j,o] = act( bias[o] + sum_{a,b,c} U[n, i*sd + a - pad_top, j*sd + b - pad_left, c]
+ *                                              * w[a,b,c,o] )
+ * where U is `in` zero-stuffed by su (U[su*i', su*j'] = in[i',j'], zero elsewhere and outside).
+ * The host side (python/layers/signal_conv.py mirror) reduces every supported combination of
+ * corr / strides_down / strides_up / same_zeros to this form: a true convolution is a
+ * correlation with the flipped kernel, and tf.nn.conv2d_backprop_input with explicit padding p
+ * (signal_conv.py:629-695) is the zero-stuffed correlation with pad = k-1-p.
+ *   d_w     [kh, kw, cin, cout] float32 (effective kernel, after the RDFT reparameterisation)
+ *   d_bias  [cout] float32 or NULL
+ *   d_beta  [cout], d_gamma [cout(k), cout(c)] float32 (effective, after the nonnegative
+ *           reparameterisation) — used when act is GDN/IGDN.
+ * in/out dtypes are tfc_dtype.  `impl`: 0 = pick the fastest kernel that supports the shape,
+ * 1 = force the CUDA-core tiled kernel, 2 = force the tcgen05 implicit-GEMM kernel
+ * (TFC_ERR_UNIMPLEMENTED if the shape is not supported by it).
+ * d_workspace: tfc_signal_conv2d_workspace(...) bytes (weights repacked to bf16 etc.). */
+typedef struct {
+  int32_t n, h, w, cin;     /* input  [n, h, w, cin]  */
+  int32_t ho, wo, cout;     /* output [n, ho, wo, cout] */
+  int32_t kh, kw;
+  int32_t sd, su;           /* strides_down, strides_up (same in both dimensions) */
+  int32_t pad_top, pad_left;
+  int32_t act;              /* tfc_activation */
+  int32_t in_dtype, out_dtype;
+  int32_t impl;
+} tfc_conv_desc;
+
+size_t tfc_signal_conv2d_workspace(const tfc_conv_desc* desc);
+int tfc_signal_conv2d(const tfc_conv_desc* desc, const void* d_in, const float* d_w,
+                      const float* d_bias, const float* d_beta, const float* d_gamma,
+                      void* d_out, void* d_workspace, size_t workspace_bytes, void* stream);
+
+/* Stand-alone GDN / IGDN on a channels_last tensor of `pixels` x `channels` (gdn.py:171-206). */
+int tfc_gdn(const void* d_x, int64_t pixels, int32_t channels, const float* d_beta,
+            const float* d_gamma, int inverse, int in_dtype, int out_dtype, void* d_out,
+            void* stream);
+
 #ifdef __cplusplus
 }
 #endif
