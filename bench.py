@@ -1,0 +1,366 @@
+#!/usr/bin/env python
+"""Headline benchmark: bmshj2018-hyperprior encode+decode throughput (MPix/s) on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c2|tiny]
+
+A step = compress + decompress of one batch of synthetic images (BASELINE.json configs[1]:
+192 filters, 768x512, batch 64 per GPU; random-init weights, seed 0).  N > 1 is launched by
+torchrun, one rank per GPU; every rank codes its own batch (images are independent units, no
+collective on the data path), so scaling is weak.  One JSON line is printed by rank 0.
+
+  value   device-resident: images already in HBM, strings stay in HBM, x_hat stays in HBM
+  e2e     through the public API with HOST buffers: pinned uint8 images -> H2D -> compress ->
+          strings D2H -> strings H2D -> decompress -> uint8 x_hat D2H, all inside the timing
+  roofline      the conv kernels (dominant): algorithmic FLOPs / CUDA-event time vs the
+                measured bf16 tensor peak (MEASURED_PEAKS.json)
+  cpu_baseline  the same pipeline on the host cores (reference range coder from oracle/_ref
+                when built, torch-CPU float32 restatement of the transforms), bounded sample
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (height, width, batch per GPU, filters)
+    "c2": (512, 768, 64, 192),
+    "c3": (1080, 1920, 32, 192),
+    "tiny": (128, 192, 4, 192),
+}
+FLOP_PER_IMAGE_C2 = 149.31e9   # encode 75.61 + decode 73.70 GFLOP per 768x512 image
+
+
+def parse_args():
+  ap = argparse.ArgumentParser()
+  ap.add_argument("--gpus", type=int, default=1)
+  ap.add_argument("--steps", type=int, default=5)
+  ap.add_argument("--warmup", type=int, default=3)
+  ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+  ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+  ap.add_argument("--conv-impl", type=int, default=0, help="0 auto, 1 CUDA-core, 2 tcgen05")
+  ap.add_argument("--cpu-sample-images", type=int, default=1)
+  ap.add_argument("--no-cpu-baseline", action="store_true")
+  return ap.parse_args()
+
+
+def measured_peaks():
+  path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+  if os.path.exists(path):
+    with open(path) as f:
+      p = json.load(f)
+    return dict(hbm_gbs=p["hbm_gbs"], bf16_tflops=p["bf16_tflops"],
+                bf16_tflops_sustained=p.get("bf16_tflops_sustained", p["bf16_tflops"]),
+                source="measured")
+  return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0,
+              source="fallback")
+
+
+# ---- algorithmic work -------------------------------------------------------------------------
+def conv_flops(model, h, w):
+  """Algorithmic FLOPs per image of every conv (+GDN) layer for an h x w input, following
+  SURVEY §8a: 2*MACs of the dense contraction; a transposed conv counts no stuffed zeros."""
+  from compression_b200.python.layers import gdn as gdn_lib
+  total = {}
+
+  def run(seq, name, hh, ww, cin):
+    for i, l in enumerate(seq.layers):
+      ho, wo = l.compute_output_shape((1, hh, ww, cin))[1:3]
+      kk = l.kernel_support[0] * l.kernel_support[1]
+      if l.strides_up[0] > 1:
+        f = 2.0 * hh * ww * cin * l.filters * kk
+      else:
+        f = 2.0 * ho * wo * cin * l.filters * kk
+      if isinstance(l.activation, gdn_lib.GDN):
+        f += 2.0 * ho * wo * l.filters * l.filters
+      total["%s%d" % (name, i)] = f
+      hh, ww, cin = ho, wo, l.filters
+    return hh, ww
+
+  nf = model.num_filters
+  hy, wy = run(model.analysis_transform, "A", h, w, 3)
+  hz, wz = run(model.hyper_analysis_transform, "HA", hy, wy, nf)
+  hs = run(model.hyper_synthesis_transform, "HS", hz, wz, nf)
+  run(model.synthesis_transform, "S", hy, wy, nf)
+  enc = sum(v for k, v in total.items() if k[0] in "AH")     # A + HA + HS
+  dec = sum(v for k, v in total.items() if k.startswith("HS") or k.startswith("S"))
+  return total, enc, dec
+
+
+class ConvTimer(object):
+  """Brackets every SignalConv2D call with CUDA events on the current stream."""
+
+  def __init__(self):
+    self.pairs = []
+    self.on = False
+
+  def install(self):
+    import torch
+    from compression_b200.python.layers import signal_conv
+    timer = self
+    orig = signal_conv.SignalConv2D.__call__
+
+    def timed(layer, inputs, out_dtype=None):
+      if not timer.on:
+        return orig(layer, inputs, out_dtype)
+      a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+      a.record()
+      out = orig(layer, inputs, out_dtype)
+      b.record()
+      timer.pairs.append((layer.name, tuple(inputs.shape), a, b))
+      return out
+
+    signal_conv.SignalConv2D.__call__ = timed
+
+  def total_ms(self):
+    return sum(a.elapsed_time(b) for _, _, a, b in self.pairs)
+
+
+# ---- clocks -------------------------------------------------------------------------------------
+class ClockSampler(object):
+  QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+           "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+           "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+  def __init__(self, index):
+    self.index = index
+    self.proc = None
+    self.path = None
+
+  def start(self):
+    try:
+      fd, self.path = tempfile.mkstemp(suffix=".csv")
+      os.close(fd)
+      self.proc = subprocess.Popen(
+          ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.QUERY,
+           "--format=csv,noheader,nounits", "-lms", "100"],
+          stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+    except OSError:
+      self.proc = None
+
+  def stop(self):
+    if self.proc is None:
+      return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+    self.proc.terminate()
+    try:
+      self.proc.wait(timeout=5)
+    except subprocess.TimeoutExpired:
+      self.proc.kill()
+    sm, mx, reasons = [], [], set()
+    names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    for line in open(self.path):
+      f = [t.strip() for t in line.split(",")]
+      if len(f) < 9:
+        continue
+      try:
+        sm.append(float(f[1])); mx.append(float(f[2]))
+      except ValueError:
+        continue
+      for n, v in zip(names, f[5:9]):
+        if v.lower().startswith("active"):
+          reasons.add(n)
+    os.unlink(self.path)
+    return {"sm_mhz": float(np.median(sm)) if sm else None,
+            "sm_max_mhz": float(max(mx)) if mx else None, "reasons": sorted(reasons),
+            "samples": len(sm)}
+
+
+# ---- CPU arm (cpu_baseline and --impl reference) ---------------------------------------------------
+def host_threads():
+  try:
+    return len(os.sched_getaffinity(0))
+  except AttributeError:
+    return os.cpu_count() or 1
+
+
+def cpu_arm(h, w, images, steps, warmup, weights=None, seed=0):
+  """Times compress+decompress of `images` synthetic images per step on the host cores.
+  Returns (MPix/s, ms_per_step, kind, cores)."""
+  import torch
+  from oracle import cpu_codec, oracle_lib
+  coder = oracle_lib.load("best")
+  threads = host_threads()
+  codec = cpu_codec.CpuBmshj2018(weights or cpu_codec.random_weights(192, seed), coder, threads)
+  g = torch.Generator().manual_seed(seed)
+  x = torch.rand((images, h, w, 3), generator=g, dtype=torch.float32).numpy()
+  times = []
+  for it in range(warmup + steps):
+    t0 = time.perf_counter()
+    c = codec.compress(x)
+    x_hat, _ = codec.decompress(c)
+    t1 = time.perf_counter()
+    if it >= warmup:
+      times.append(t1 - t0)
+  sec = float(np.mean(times))
+  return images * h * w / sec / 1e6, sec * 1e3, coder.kind, threads
+
+
+def run_reference(args):
+  rank = int(os.environ.get("RANK", "0"))
+  if rank != 0:
+    return
+  h, w, batch, nf = WORKLOADS[args.workload]
+  images = max(1, args.cpu_sample_images)
+  mpix, ms, kind, cores = cpu_arm(h, w, images, max(1, args.steps), min(args.warmup, 1))
+  sample = "%d of %d images of %dx%d per step, all %d host threads" % (images, batch, w, h, cores)
+  line = {
+      "impl": "reference", "metric": "MPix/s encode+decode, bmshj2018 hyperprior",
+      "value": mpix, "unit": "MPix/s", "n_gpus": args.gpus, "steps": max(1, args.steps),
+      "warmup": min(args.warmup, 1), "ms_per_step": ms, "higher_is_better": True,
+      "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+      "config": {"workload": "bmshj2018-192 encode+decode %dx%d" % (w, h), "sample": sample,
+                 "note": "CPU restatement (torch-CPU float32 transforms) + %s range coder; "
+                         "TF 1.15 cannot run in this image" % kind},
+      "cpu_baseline": {"value": mpix, "unit": "MPix/s", "cores": cores, "kind": kind,
+                       "sample": sample},
+      "e2e": {"value": mpix, "unit": "MPix/s", "h2d_bytes_per_step": 0,
+              "d2h_bytes_per_step": 0},
+      "gpu_launches": 0,
+  }
+  print(json.dumps(line))
+
+
+# ---- B200 arm ----------------------------------------------------------------------------------------
+def run_b200(args):
+  import torch
+  import torch.distributed as dist
+  import compression_b200 as tfc
+  from compression_b200.examples import bmshj2018
+  from compression_b200.python.ops import range_coding_ops as rc
+
+  world = int(os.environ.get("WORLD_SIZE", "1"))
+  rank = int(os.environ.get("RANK", "0"))
+  local = int(os.environ.get("LOCAL_RANK", "0"))
+  if not torch.cuda.is_available():
+    raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference")
+  torch.cuda.set_device(local)
+  dev = torch.device("cuda", local)
+  if world > 1:
+    dist.init_process_group("nccl", device_id=dev)
+  h, w, batch, nf = WORKLOADS[args.workload]
+  model = bmshj2018.Bmshj2018Model(nf, dev, seed=0, impl=args.conv_impl)
+  g = torch.Generator().manual_seed(1000 + rank)
+  x_u8_host = torch.randint(0, 256, (batch, h, w, 3), generator=g, dtype=torch.uint8).pin_memory()
+  x_dev = (x_u8_host.to(dev).float() / 255).contiguous()
+  timer = ConvTimer()
+  timer.install()
+
+  def barrier():
+    if world > 1:
+      dist.barrier()
+    torch.cuda.synchronize()
+
+  def step_device():
+    c = model.compress(x_dev)
+    return model.decompress(c)
+
+  def step_e2e():
+    xd = x_u8_host.to(dev, non_blocking=True).float() / 255            # H2D + cast
+    c = model.compress(xd)
+    host = model.to_host(c)                                            # strings D2H
+    cd = model.to_device(host)                                         # strings H2D
+    x_hat = bmshj2018.quantize_image(model.decompress(cd))
+    out = x_hat.cpu()                                                  # uint8 image D2H
+    nbytes = sum(len(s) for s in host.string) + sum(len(s) for s in host.side_string)
+    return out, nbytes
+
+  for _ in range(max(args.warmup, 3)):
+    step_device()
+  barrier()
+  clocks = ClockSampler(local)
+  if rank == 0:
+    clocks.start()
+  launches0 = tfc.launch_count()
+  timer.on = True
+  start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  start.record()
+  for _ in range(args.steps):
+    step_device()
+  stop.record()
+  barrier()
+  timer.on = False
+  launches = tfc.launch_count() - launches0
+  clk = clocks.stop() if rank == 0 else None
+  ms = torch.tensor([start.elapsed_time(stop)], device=dev)
+  conv_ms = timer.total_ms()
+  if world > 1:
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+  ms_per_step = float(ms.item()) / args.steps
+
+  # e2e: same metric through host buffers
+  step_e2e()
+  barrier()
+  t0 = time.perf_counter()
+  for _ in range(args.steps):
+    _, string_bytes = step_e2e()
+  torch.cuda.synchronize()
+  e2e_s = torch.tensor([time.perf_counter() - t0], device=dev)
+  if world > 1:
+    dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+  e2e_ms = float(e2e_s.item()) * 1e3 / args.steps
+
+  if rank != 0:
+    if world > 1:
+      dist.destroy_process_group()
+    return
+  pixels = batch * h * w
+  peaks = measured_peaks()
+  per_layer, enc_f, dec_f = conv_flops(model, h, w)
+  flops_step = (enc_f + dec_f) * batch
+  conv_ms_step = conv_ms / args.steps
+  n_conv = len(timer.pairs) // max(args.steps, 1)
+  achieved = flops_step / (conv_ms_step * 1e-3) / 1e12 if conv_ms_step > 0 else 0.0
+  peak = peaks["bf16_tflops_sustained"]
+  line = {
+      "metric": "MPix/s encode+decode, bmshj2018 hyperprior",
+      "value": world * pixels / (ms_per_step * 1e-3) / 1e6, "unit": "MPix/s", "n_gpus": world,
+      "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
+      "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+      "data": "synthetic",
+      "config": {"workload": "bmshj2018-192 encode+decode %dx%d batch %d per GPU (%s)"
+                             % (w, h, batch, args.workload),
+                 "weights": "random-init seed 0", "l2": "inputs_exceed_l2 (%.0f MB images)"
+                 % (x_dev.numel() * 4 / 1e6), "parallelism": "batch-sharded x%d" % world,
+                 "conv_impl": args.conv_impl},
+      "e2e": {"value": world * pixels / (e2e_ms * 1e-3) / 1e6, "unit": "MPix/s",
+              "h2d_bytes_per_step": int(x_u8_host.numel() + string_bytes),
+              "d2h_bytes_per_step": int(x_u8_host.numel() + string_bytes),
+              "ms_per_step": e2e_ms},
+      "gpu_launches": int(launches),
+      "clocks": clk,
+      "roofline": {"bound": "tensor", "kernel": "SignalConv2D kernels (%d launches/step)" % n_conv,
+                   "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                   "frac": achieved / peak, "traffic": None,
+                   "peak_source": peaks["source"] + " bf16 sustained",
+                   "share_of_step": conv_ms_step / ms_per_step,
+                   "flops_per_step": flops_step},
+  }
+  if not args.no_cpu_baseline and world == 1:
+    images = max(1, args.cpu_sample_images)
+    mpix, cms, kind, cores = cpu_arm(h, w, images, 1, 0, weights=model.export_weights())
+    line["cpu_baseline"] = {"value": mpix, "unit": "MPix/s", "cores": cores, "kind": kind,
+                            "sample": "%d of %d images of %dx%d, 1 step, all host threads; "
+                                      "torch-CPU f32 transforms + %s range coder"
+                                      % (images, batch, w, h, kind)}
+  print(json.dumps(line))
+  if world > 1:
+    dist.destroy_process_group()
+
+
+def main():
+  args = parse_args()
+  if args.impl == "reference":
+    run_reference(args)
+  else:
+    run_b200(args)
+
+
+if __name__ == "__main__":
+  main()

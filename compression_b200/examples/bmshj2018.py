@@ -192,3 +192,34 @@ class Bmshj2018Model(object):
     return Compressed(rc.strings_to_device(c.string, self.device),
                       rc.strings_to_device(c.side_string, self.device),
                       c.x_shape, c.y_shape, c.z_shape)
+
+  # ---- export (host copies, for checkpoints and for the CPU checker in tests/bench) --------
+  def export_weights(self):
+    """Effective float32 weights keyed like oracle/cpu_codec.py expects."""
+    w = {}
+    for prefix, seq in (("a", self.analysis_transform), ("s", self.synthesis_transform),
+                        ("ha", self.hyper_analysis_transform),
+                        ("hs", self.hyper_synthesis_transform)):
+      for i, l in enumerate(seq.layers):
+        name = "%s%d" % (prefix, i)
+        w[name + "/kernel"] = l.kernel.float().cpu().numpy()
+        if l.bias is not None:
+          w[name + "/bias"] = l.bias.float().cpu().numpy()
+        if isinstance(l.activation, gdn.GDN):
+          beta, gamma = l.activation.effective()
+          w[name + "/beta"] = beta.cpu().numpy()
+          w[name + "/gamma"] = gamma.cpu().numpy()
+    eb = self.entropy_bottleneck
+    for i, m in enumerate(eb.matrices):
+      w["eb/matrix_%d" % i] = m.cpu().numpy()
+      w["eb/bias_%d" % i] = eb.biases[i].cpu().numpy()
+    for i, f in enumerate(eb.factors):
+      w["eb/factor_%d" % i] = f.cpu().numpy()
+    w["eb/quantiles"] = eb.quantiles.cpu().numpy()
+    return w
+
+  def export_tables(self):
+    eb, gc = self.entropy_bottleneck, self._gc_tables
+    return dict(eb_cdf=eb._quantized_cdf.cpu().numpy(), eb_len=eb._cdf_length.cpu().numpy(),
+                eb_off=eb._offset.cpu().numpy(), gc_cdf=gc._quantized_cdf.cpu().numpy(),
+                gc_len=gc._cdf_length.cpu().numpy(), gc_off=gc._offset.cpu().numpy())

@@ -1,0 +1,248 @@
+"""GPU parity tests of the transform and entropy-model kernels (through the layer classes and
+the C ABI) against oracle/tfc_np.py and the reference's own test properties."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import tfc_np
+from tests.golden import tfc_goldens as G
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def tfc():
+  import compression_b200 as tfc_mod
+  return tfc_mod
+
+
+def _static(kernel):
+  """StaticParameterizer-style fixed kernel (signal_conv_test.py:96-97)."""
+  return lambda shape: torch.as_tensor(kernel, dtype=torch.float32)
+
+
+CONV_CASES = [
+    # corr, kernel, sd, su, padding, extra_pad_end
+    (True, (3, 3), 1, 1, "valid", True), (False, (3, 3), 1, 1, "valid", True),
+    (True, (5, 5), 2, 1, "valid", True), (False, (5, 5), 1, 2, "valid", True),
+    (True, (5, 5), 1, 2, "valid", True), (False, (5, 5), 1, 2, "valid", False),
+    (False, (4, 4), 1, 2, "valid", True), (True, (2, 4), 2, 1, "valid", True),
+    (True, (5, 5), 2, 1, "same_zeros", True), (False, (5, 5), 1, 2, "same_zeros", True),
+    (True, (3, 3), 1, 1, "same_zeros", True), (False, (3, 3), 1, 1, "same_zeros", True),
+    (True, (9, 9), 4, 1, "same_zeros", True), (False, (9, 9), 1, 4, "same_zeros", True),
+    (True, (5, 5), 1, 2, "same_zeros", True), (False, (5, 5), 2, 2, "same_zeros", True),
+    (False, (4, 4), 1, 2, "same_zeros", True), (False, (5, 5), 1, 2, "same_zeros", False),
+]
+
+
+@pytest.mark.parametrize("impl", [1])
+@pytest.mark.parametrize("corr,ks,sd,su,padding,epe", CONV_CASES)
+def test_signal_conv_matches_oracle(tfc, corr, ks, sd, su, padding, epe, impl):
+  """Integer-valued data as in signal_conv_test.py:81-129 (exact in float32), every dispatch
+  branch of signal_conv.py:709-782 that the 2-D same_zeros/valid layer can take."""
+  rng = np.random.default_rng(0)
+  x = rng.integers(0, 32, size=(2, 13, 11, 3)).astype(np.float32)
+  k = rng.integers(0, 16, size=ks + (3, 5)).astype(np.float32)
+  b = rng.integers(-8, 8, size=5).astype(np.float32)
+  layer = tfc.SignalConv2D(5, ks, corr=corr, strides_down=sd, strides_up=su, padding=padding,
+                           extra_pad_end=epe, use_bias=True, kernel_parameterizer=None,
+                           kernel_initializer=_static(k), bias_initializer=_static(b),
+                           impl=impl)
+  got = layer(torch.from_numpy(x).cuda())
+  want = tfc_np.signal_conv2d(x, k, b, corr, sd, su, padding, epe).numpy()
+  assert tuple(got.shape) == want.shape == tuple(layer.compute_output_shape(x.shape))
+  np.testing.assert_allclose(got.cpu().numpy(), want, rtol=0, atol=1e-3)
+
+
+def test_signal_conv_not_implemented(tfc):
+  """signal_conv.py:393-401 / signal_conv_test.py:185-219."""
+  x = torch.zeros((1, 8, 8, 2), device="cuda")
+  with pytest.raises(NotImplementedError):
+    tfc.SignalConv2D(2, (4, 4), corr=True, strides_up=2, padding="valid")(x)
+  with pytest.raises(NotImplementedError):
+    tfc.SignalConv2D(2, (3, 3), corr=True, padding="same_reflect")(x)
+  with pytest.raises(NotImplementedError):
+    tfc.SignalConv2D(2, (3, 3), corr=True, channel_separable=True)(x)
+
+
+def test_rdft_parameterizer_roundtrip(tfc):
+  """parameterizers_test.py:46-52: the RDFT-parameterised kernel equals its initial value."""
+  k = np.random.default_rng(1).normal(size=(5, 5, 3, 4)).astype(np.float32)
+  layer = tfc.SignalConv2D(4, (5, 5), corr=True, padding="same_zeros",
+                           kernel_initializer=_static(k))
+  layer.build(3, "cuda")
+  assert tuple(layer.kernel_var.shape) == (25, 12)
+  np.testing.assert_allclose(layer.kernel.cpu().numpy(), k, atol=1e-5)
+
+
+@pytest.mark.parametrize("inverse", [False, True])
+def test_gdn_default_init_closed_form(tfc, inverse):
+  """gdn_test.py:49-75."""
+  x = np.random.default_rng(2).uniform(size=(1, 2, 3, 4)).astype(np.float32)
+  y = tfc.GDN(inverse=inverse)(torch.from_numpy(x).cuda()).cpu().numpy()
+  want = x * np.sqrt(1 + .1 * x ** 2) if inverse else x / np.sqrt(1 + .1 * x ** 2)
+  np.testing.assert_allclose(y, want, rtol=0, atol=1e-6)
+
+
+@pytest.mark.parametrize("inverse", [False, True])
+def test_conv_gdn_fused_matches_oracle(tfc, inverse):
+  """Analysis/synthesis layer = conv + bias + (I)GDN with a non-trivial gamma."""
+  rng = np.random.default_rng(3)
+  c = 8
+  x = rng.normal(size=(2, 12, 10, c)).astype(np.float32)
+  k = (rng.normal(size=(5, 5, c, c)) / 10).astype(np.float32)
+  b = rng.normal(size=c).astype(np.float32)
+  act = tfc.GDN(inverse=inverse)
+  if inverse:
+    layer = tfc.SignalConv2D(c, (5, 5), corr=False, strides_up=2, padding="same_zeros",
+                             use_bias=True, activation=act, kernel_initializer=_static(k),
+                             bias_initializer=_static(b), impl=1)
+  else:
+    layer = tfc.SignalConv2D(c, (5, 5), corr=True, strides_down=2, padding="same_zeros",
+                             use_bias=True, activation=act, kernel_initializer=_static(k),
+                             bias_initializer=_static(b), impl=1)
+  layer.build(c, "cuda")
+  act.reparam_gamma = act.gamma_parameterizer.init(
+      torch.as_tensor(rng.uniform(0, .2, size=(c, c)), dtype=torch.float32).cuda())
+  act.reparam_beta = act.beta_parameterizer.init(
+      torch.as_tensor(rng.uniform(.5, 2, size=c), dtype=torch.float32).cuda())
+  act.invalidate()
+  got = layer(torch.from_numpy(x).cuda()).cpu().numpy()
+  beta = tfc_np.nonnegative_reparam(act.reparam_beta.cpu().numpy(), 1e-6)
+  gamma = tfc_np.nonnegative_reparam(act.reparam_gamma.cpu().numpy(), 0)
+  pre = tfc_np.signal_conv2d(x, layer.kernel.cpu().numpy(), b, not inverse,
+                             1 if inverse else 2, 2 if inverse else 1, "same_zeros")
+  want = tfc_np.gdn(pre, beta, gamma, inverse).numpy()
+  np.testing.assert_allclose(got, want, rtol=1e-4, atol=1e-4)
+
+
+# ---- entropy models ------------------------------------------------------------------------
+def _eb_oracle_params(eb):
+  m, b, f = tfc_np.eb_params64([t.cpu().numpy() for t in eb.matrices],
+                               [t.cpu().numpy() for t in eb.biases],
+                               [t.cpu().numpy() for t in eb.factors])
+  return m, b, f
+
+
+@pytest.mark.parametrize("filters", [(3, 3, 3), (), (3,), (2, 2), (4, 4, 4, 4)])
+def test_entropy_bottleneck_call(tfc, filters):
+  """values exact; likelihood max-abs <= 1e-3 (north-star tolerance; measured ~1e-6) against
+  the float64 restatement of entropy_models.py:626-658."""
+  rng = np.random.default_rng(4)
+  c = 6
+  eb = tfc.EntropyBottleneck(filters=filters)
+  eb.build(c, "cuda", torch.Generator().manual_seed(1))
+  for t in eb.factors:                       # non-trivial tanh factors
+    t.copy_(torch.as_tensor(rng.normal(size=tuple(t.shape)) * .5, dtype=torch.float32))
+  eb.quantiles[:, 0, 1] = torch.as_tensor(rng.uniform(-.4, .4, size=c), dtype=torch.float32)
+  eb.refresh()
+  x = rng.uniform(-25, 25, size=(3, 7, 5, c)).astype(np.float32)
+  values, lik = eb(torch.from_numpy(x).cuda(), training=False)
+  m, b, f = _eb_oracle_params(eb)
+  med = eb._medians.cpu().numpy()
+  want_v, want_l = tfc_np.eb_call(x, med, m, b, f)
+  np.testing.assert_array_equal(values.cpu().numpy(), want_v)
+  assert np.abs(lik.cpu().numpy() - want_l).max() <= 1e-3
+  np.testing.assert_allclose(lik.cpu().numpy(), want_l, rtol=2e-3, atol=1e-7)
+  sym = eb._quantize_symbols(torch.from_numpy(x).cuda())
+  np.testing.assert_array_equal(sym.cpu().numpy(), tfc_np.eb_symbols(x, med))
+  deq = eb._dequantize(sym)
+  np.testing.assert_array_equal(deq.cpu().numpy(), want_v)
+
+
+def test_entropy_bottleneck_tables_and_codec(tfc, oracle):
+  """update() builds the same tables as the restatement of entropy_models.py:521-596 (up to
+  float32-vs-float64 density evaluation: |cdf diff| <= 2), and compress/decompress round-trips
+  bit-exactly against the CPU coder on the layer's own tables."""
+  rng = np.random.default_rng(5)
+  c = 8
+  eb = tfc.EntropyBottleneck()
+  eb.build(c, "cuda", torch.Generator().manual_seed(2))
+  assert eb._quantized_cdf.cpu().numpy().tolist() == [[0, 32768, 65536]] * c  # :563-583
+  eb.update()
+  m, b, f = _eb_oracle_params(eb)
+  cdf, length, offset, med = tfc_np.eb_tables(
+      eb.quantiles.cpu().numpy(), m, b, f, lambda p: oracle.pmf_to_cdf(p[None], 16)[0])
+  np.testing.assert_array_equal(eb._cdf_length.cpu().numpy(), length)
+  np.testing.assert_array_equal(eb._offset.cpu().numpy(), offset)
+  assert length.tolist() == [23] * c               # init_scale=10
+  got_cdf = eb._quantized_cdf.cpu().numpy()
+  assert np.abs(got_cdf - cdf).max() <= 2
+  assert (got_cdf[:, 0] == 0).all() and (got_cdf[:, 22] == 65536).all()
+  x = rng.normal(scale=6, size=(5, 9, 4, c)).astype(np.float32)
+  x[0, 0, 0, :] = [40, -40, 200, -300, 11, -11, 10, -10]      # escapes
+  xd = torch.from_numpy(x).cuda()
+  strings = eb.compress(xd)
+  sym = tfc_np.eb_symbols(x, med)
+  idx = np.broadcast_to(np.arange(c, dtype=np.int32), x.shape[1:])
+  for s in range(5):
+    assert strings[s] == oracle.ui_encode(sym[s], idx, got_cdf, length, offset, 16, 4)
+  dec = eb.decompress(strings, x.shape[1:], channels=c)
+  np.testing.assert_array_equal(dec.cpu().numpy(), sym.astype(np.float32) + med)
+  assert np.abs(dec.cpu().numpy() - x).max() <= .5 + 1e-5
+
+
+@pytest.mark.parametrize("kind", ["gaussian", "logistic", "laplacian"])
+def test_conditional_tables_golden_and_decode(tfc, kind):
+  """G2-G5: tables built on the GPU equal the golden CDF arrays, and the layer decodes the
+  reference's stored bit strings (entropy_models_test.py:407-425)."""
+  cls = {"gaussian": tfc.GaussianConditional, "logistic": tfc.LogisticConditional,
+         "laplacian": tfc.LaplacianConditional}[kind]
+  g = G.CONDITIONALS[kind]
+  layer = cls(None, G.COND_SCALE_TABLE, indexes=torch.from_numpy(G.COND_INDEXES).cuda())
+  layer.build()
+  np.testing.assert_array_equal(layer._quantized_cdf.cpu().numpy(), g["cdf"])
+  np.testing.assert_array_equal(layer._cdf_length.cpu().numpy(), g["cdf_length"])
+  np.testing.assert_array_equal(layer._offset.cpu().numpy(), g["offset"])
+  dec = layer.decompress(g["bitstrings"])
+  np.testing.assert_array_equal(dec.cpu().numpy(), G.COND_EXPECTED)
+  enc = layer.compress(torch.from_numpy(G.COND_EXPECTED).cuda())
+  assert enc == g["bitstrings"]
+
+
+def test_gaussian_conditional_call_indexes_codec(tfc, oracle):
+  """Likelihood <= 1e-3 max-abs vs float64 (entropy_models.py:916-932, :965-969); indexes and
+  symbols exact (:869-881, :898); strings bit-exact on the 64-level bmshj2018 table."""
+  rng = np.random.default_rng(6)
+  table = np.exp(np.linspace(np.log(0.11), np.log(256), 64))
+  shape = (3, 6, 5, 16)
+  sigma = np.exp(rng.uniform(np.log(0.05), np.log(300), size=shape)).astype(np.float32)
+  sigma.ravel()[:70] = np.concatenate([table.astype(np.float32), [-1, 0, 0.11, 1e-9, 256, 1e4]])
+  y = (rng.standard_normal(shape) * sigma * 1.2).astype(np.float32)
+  y.ravel()[100:104] = [0.5, -0.5, 1.5, -1.5]            # round-half-up, not rint
+  gc = tfc.GaussianConditional(torch.from_numpy(sigma).cuda(), table)
+  values, lik = gc(torch.from_numpy(y).cuda(), training=False)
+  want_v, want_l = tfc_np.conditional_call(y, sigma, table)
+  np.testing.assert_array_equal(values.cpu().numpy(), want_v)
+  assert np.abs(lik.cpu().numpy() - want_l).max() <= 1e-3
+  np.testing.assert_allclose(lik.cpu().numpy(), want_l, rtol=1e-3, atol=1e-7)
+  want_idx = tfc_np.conditional_indexes(sigma, table)
+  np.testing.assert_array_equal(gc.indexes.cpu().numpy(), want_idx)
+  cdf, length, offset = tfc_np.conditional_tables(
+      table, lambda p: oracle.pmf_to_cdf(p[None], 16)[0])
+  np.testing.assert_array_equal(gc._cdf_length.cpu().numpy(), length)
+  np.testing.assert_array_equal(gc._offset.cpu().numpy(), offset)
+  np.testing.assert_array_equal(gc._quantized_cdf.cpu().numpy(), cdf)
+  assert int(length.sum()) == 13014 and cdf.shape == (64, 1481)
+  gc2 = tfc.GaussianConditional(torch.from_numpy(sigma).cuda(), table)
+  strings = gc2.compress(torch.from_numpy(y).cuda())
+  sym = tfc_np.conditional_symbols(y)
+  for s in range(shape[0]):
+    assert strings[s] == oracle.ui_encode(sym[s], want_idx[s], cdf, length, offset, 16, 4)
+  dec = gc2.decompress(strings)
+  np.testing.assert_array_equal(dec.cpu().numpy(), sym.astype(np.float32))
+
+
+def test_lower_bound_gradients(tfc):
+  """math_ops_test.py:28-102."""
+  x = torch.tensor([-1., 1.], requires_grad=True)
+  for mode, want in (("identity_if_towards", [0., 1.]), ("identity", [1., 1.]),
+                     ("disconnected", [0., 1.])):
+    x.grad = None
+    tfc.lower_bound(x, 0., gradient=mode).sum().backward()
+    assert x.grad.tolist() == want
+  x.grad = None
+  (-tfc.lower_bound(x, 0.)).sum().backward()    # gradient pushes the input up -> passes
+  assert x.grad.tolist() == [-1., -1.]
+  with pytest.raises(ValueError):
+    tfc.lower_bound(x, 0., gradient="nope")

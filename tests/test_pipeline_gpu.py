@@ -1,0 +1,113 @@
+"""End-to-end parity of the bmshj2018 pipeline on the GPU against the CPU restatement with the
+SAME weights and tables (SURVEY §8d "parity checks")."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def setup(oracle):
+  from compression_b200.examples import bmshj2018
+  from oracle import cpu_codec
+  model = bmshj2018.Bmshj2018Model(192, "cuda", seed=0)
+  cpu = cpu_codec.CpuBmshj2018(model.export_weights(), oracle, threads=8,
+                               tables=model.export_tables())
+  g = torch.Generator().manual_seed(3)
+  x = torch.rand((2, 80, 112, 3), generator=g, dtype=torch.float32)   # 80, 112: ragged /16
+  return model, cpu, x
+
+
+def _psnr(a, b):
+  return 10 * np.log10(1.0 / np.mean((np.asarray(a, np.float64) - np.asarray(b, np.float64)) ** 2))
+
+
+def test_roundtrip_and_bit_exact_strings(setup, oracle):
+  model, cpu, x = setup
+  xd = x.cuda()
+  c = model.compress(xd)
+  assert c.y_shape == (5, 7) and c.z_shape == (2, 2)        # ceil division on the way down
+  host = model.to_host(c)
+  y, z, sigma = model.analyse(xd)
+  gc = model._conditional(sigma)
+  y_sym, y_idx, _ = gc._symbols_and_indexes(y.contiguous())
+  t = model.export_tables()
+  # (1) same symbols + indexes + tables -> same bytes as the reference coder
+  for b in range(2):
+    want = oracle.ui_encode(y_sym[b].cpu().numpy(), y_idx[b].cpu().numpy(), t["gc_cdf"],
+                            t["gc_len"], t["gc_off"], 16, 4)
+    assert host.string[b] == want
+  z_sym = model.entropy_bottleneck._quantize_symbols(z).cpu().numpy()
+  z_idx = np.broadcast_to(np.arange(192, dtype=np.int32), z_sym.shape[1:])
+  for b in range(2):
+    assert host.side_string[b] == oracle.ui_encode(z_sym[b], z_idx, t["eb_cdf"], t["eb_len"],
+                                                   t["eb_off"], 16, 4)
+  # (2) the decoder, which re-derives sigma from the side string, recovers the same symbols
+  x_hat = model.decompress(model.to_device(host))
+  nf = 192
+  z_hat = model.entropy_bottleneck.decompress_device(c.side_string, c.z_shape + (nf,), nf,
+                                                     torch.bfloat16)
+  sigma2 = model.hyper_synthesis_transform(z_hat)[:, :5, :7, :].contiguous()
+  assert torch.equal(sigma2, sigma), "decoder-side sigma must equal encoder-side bit for bit"
+  y_hat = model._conditional(sigma2).decompress_device(c.string)
+  assert torch.equal(y_hat.to(torch.int32), y_sym)
+  assert tuple(x_hat.shape) == (2, 80, 112, 3)
+
+
+def test_cpu_decoder_reads_gpu_strings_and_psnr_delta(setup):
+  """The CPU pipeline decodes the GPU's strings (interchange), and with the SAME symbols the
+  two synthesis paths agree to |dPSNR| <= 0.01 dB (north-star tolerance)."""
+  model, cpu, x = setup
+  c = model.compress(x.cuda())
+  host = model.to_host(c)
+  from compression_b200.python.ops import range_coding_ops as rc
+
+  def slab(strings):
+    cap = max(len(s) for s in strings) + 8
+    out = np.zeros((len(strings), cap), np.uint8)
+    for i, s in enumerate(strings):
+      out[i, :len(s)] = np.frombuffer(s, np.uint8)
+    return out, np.array([len(s) for s in strings], np.int64)
+
+  cc = dict(string=slab(host.string), side_string=slab(host.side_string), x_shape=c.x_shape,
+            y_shape=c.y_shape, z_shape=c.z_shape)
+  # z symbols decode identically; the CPU's float32 sigma may index a few rows differently
+  # from the GPU's bf16-operand sigma, so y is decoded with the GPU's indexes here
+  y, z, sigma = model.analyse(x.cuda())
+  gc = model._conditional(sigma)
+  y_sym, y_idx, _ = gc._symbols_and_indexes(y.contiguous())
+  t = model.export_tables()
+  n = y_idx[0].numel()
+  dec = cpu.coder.ui_decode_batch(cc["string"][0], cc["string"][1],
+                                  y_idx.cpu().numpy().reshape(2, -1), n, t["gc_cdf"],
+                                  t["gc_len"], t["gc_off"], threads=2)
+  np.testing.assert_array_equal(dec.reshape(y_sym.shape), y_sym.cpu().numpy())
+  # same symbols -> both synthesis transforms
+  y_hat = y_sym.float()
+  x_gpu = model.synthesis_transform(y_hat.to(torch.bfloat16))[:, :80, :112].float().cpu().numpy()
+  x_cpu = cpu._run(__import__("oracle.cpu_codec", fromlist=["SYNTHESIS"]).SYNTHESIS,
+                   y_hat.cpu().numpy())[:, :80, :112].numpy()
+  d = abs(_psnr(x.numpy(), x_gpu) - _psnr(x.numpy(), x_cpu))
+  assert d <= 0.01, d
+  rel = np.abs(x_gpu - x_cpu).max() / (np.abs(x_cpu).max() + 1e-9)
+  assert rel < 0.05, rel
+
+
+def test_analysis_close_to_cpu(setup):
+  """Transforms (bf16 activations between layers) against the float32 CPU restatement."""
+  model, cpu, x = setup
+  y, z, sigma = model.analyse(x.cuda())
+  y_c, z_sym_c, sigma_c = cpu.analyse(x.numpy())
+  scale = np.abs(y_c).max()
+  assert np.abs(y.cpu().numpy() - y_c).max() <= 0.03 * scale
+  agree = np.mean(np.floor(y.cpu().numpy() + .5) == np.floor(y_c + .5))
+  assert agree > 0.97, agree
+
+
+def test_results_independent_of_batch_position(setup):
+  """H4: an image codes to the same bytes whatever batch it is in."""
+  model, cpu, x = setup
+  a = model.to_host(model.compress(x.cuda()))
+  b = model.to_host(model.compress(x[1:].cuda()))
+  assert a.string[1] == b.string[0] and a.side_string[1] == b.side_string[0]
