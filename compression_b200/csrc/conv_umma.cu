@@ -1,17 +1,520 @@
-// tcgen05 / TMEM / TMA implicit-GEMM SignalConv2D with fused bias + GDN/IGDN epilogue.
-// (stub until the kernel lands: reports every shape as unsupported so the dispatcher uses the
-// CUDA-core path)
+// tcgen05 / TMEM / TMA implicit-GEMM SignalConv2D with fused bias + ReLU / GDN / IGDN epilogue.
+//
+// Replaces, for the layers that carry the codecs' FLOPs, the stock TF kernels the reference
+// dispatches to (/root/reference/tensorflow_compression/python/layers/signal_conv.py:516-518
+// tf.nn.conv2d, :693-695 tf.nn.conv2d_backprop_input, :804 bias_add) together with the GDN
+// activation that follows them (gdn.py:183-202: 1x1 conv of x^2 with gamma, bias_add beta,
+// rsqrt/sqrt, multiply) — one kernel per layer instead of six TF ops.
+//
+// Formulation.  GEMM view per CTA tile: D[128 pixels, N=cout] +=
+// A[128, 64] * B[64, N] for every (kernel tap, 64-channel chunk).
+//   * A tiles come straight from the NHWC bf16 activation by TMA: the tensor map views it as
+//     (s*C, W/s, s, H/s, N) for a stride-s correlation, so a tap is a dense box of one parity
+//     plane and out-of-image taps are zero-filled by the TMA unit (no im2col buffer, no
+//     padding copy).  An upsampled (transposed) convolution is split into su*su output
+//     phases, each a stride-1 correlation over the un-stuffed input with its own tap subset —
+//     no multiplications by stuffed zeros.
+//   * B tiles are the weights repacked once per call to bf16 [tap][cout][cin] (K-major).
+//   * Accumulators live in TMEM (fp32).  Warp roles: warp 0 TMA producer, warp 1 MMA issuer
+//     (one elected lane issues tcgen05.mma), warps 2-5 epilogue (tcgen05.ld).
+//   * GDN: the epilogue squares x = D1 + bias into a K-major bf16 tile in shared memory, the
+//     MMA warp runs a second GEMM D2 = x^2 * gamma (gamma tiles ride the same TMA ring), and
+//     the epilogue finishes y = x * rsqrt(beta + D2) (IGDN: * sqrt).
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <algorithm>
+#include <mutex>
+#include <vector>
+
 #include "common.cuh"
 #include "conv_common.cuh"
+#include "umma_ptx.cuh"
+
+namespace {
+
+using namespace tfc::ptx;
+
+constexpr int kTileM = 128;          // output pixels per CTA tile (UMMA M)
+constexpr int kBlockK = 64;          // channels per k-block: 64 bf16 = one 128-byte swizzle row
+constexpr int kStages = 4;
+constexpr int kMaxTaps = 81;         // 9x9
+constexpr int kMaxPhases = 16;       // 4x4 upsampling
+constexpr int kThreads = 192;        // producer warp, MMA warp, 4 epilogue warps
+constexpr int kABytes = kTileM * kBlockK * 2;   // 16 KB
+
+struct Tap {            // one (kernel tap) of one output phase
+  int8_t dh, dw;        // offset of the input box relative to the tile origin (in box rows/cols)
+  int8_t ph, pw;        // parity plane (stride-s correlation): coordinates in the `s` dims
+  int16_t widx;         // index of the weight slab (a*kw + b)
+  int16_t pad;
+};
+
+struct Params {
+  int32_t n, ho, wo, cout;          // output tensor [n, ho, wo, cout]
+  int32_t cin;
+  int32_t su;                       // output phases per dimension
+  int32_t hs, ws;                   // per-phase output sub-grid (ho/su, wo/su)
+  int32_t th, tw;                   // tile shape, th*tw == 128
+  int32_t tiles_h, tiles_w;
+  int32_t num_tiles;
+  int32_t npad;                     // UMMA N (cout rounded up to 16)
+  int32_t act;
+  int32_t out_f32;
+  int32_t phase_start[kMaxPhases + 1];
+  Tap taps[kMaxTaps];
+  const float* bias;
+  const float* beta;
+  void* out;
+};
+
+struct __align__(8) Barriers {
+  uint64_t full[kStages], empty[kStages];
+  uint64_t d1_full[2], d1_empty[2];
+  uint64_t a2_full, d2_full;
+  uint32_t tmem_base;
+  uint32_t pad;
+};
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+template <bool GDN>
+__global__ void __launch_bounds__(kThreads, 1)
+conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
+                 const __grid_constant__ CUtensorMap map_w,
+                 const __grid_constant__ CUtensorMap map_g, const Params p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // carve: [stages x (A 16 KB | B npad*128 B)] [A2: cout/64 x 16 KB] [bias|beta] [barriers]
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  const int b_bytes = p.npad * kBlockK * 2;
+  const int stage_bytes = kABytes + ((b_bytes + 1023) & ~1023);
+  uint8_t* a2 = smem + kStages * stage_bytes;
+  const int gdn_kblocks = GDN ? p.cout / kBlockK : 0;
+  float* s_bias = reinterpret_cast<float*>(a2 + gdn_kblocks * kABytes);
+  float* s_beta = s_bias + 256;
+  Barriers* bars = reinterpret_cast<Barriers*>(s_beta + 256);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kchunks = p.cin / kBlockK;
+
+  for (int i = threadIdx.x; i < 256; i += kThreads) {
+    s_bias[i] = (p.bias && i < p.cout) ? p.bias[i] : 0.f;
+    s_beta[i] = (GDN && i < p.cout) ? p.beta[i] : 1.f;
+  }
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&map_a);
+    prefetch_tmap(&map_w);
+    if (GDN) prefetch_tmap(&map_g);
+    for (int s = 0; s < kStages; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], 128); }
+    mbar_init(&bars->a2_full, 128);
+    mbar_init(&bars->d2_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&bars->tmem_base, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bars->tmem_base;
+  const uint32_t idesc = make_idesc_bf16(kTileM, p.npad);
+
+  auto tile_coords = [&](int tile, int& phase, int& n, int& i0, int& j0) {
+    const int per_img = p.tiles_h * p.tiles_w;
+    const int per_phase = per_img * p.n;
+    phase = tile / per_phase;
+    int r = tile - phase * per_phase;
+    n = r / per_img;
+    r -= n * per_img;
+    const int ti = r / p.tiles_w;
+    i0 = ti * p.th;
+    j0 = (r - ti * p.tiles_w) * p.tw;
+  };
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        int phase, n, i0, j0;
+        tile_coords(tile, phase, n, i0, j0);
+        for (int t = p.phase_start[phase]; t < p.phase_start[phase + 1]; ++t) {
+          const Tap tap = p.taps[t];
+          for (int kc = 0; kc < kchunks; ++kc) {
+            mbar_wait(&bars->empty[stage], ph ^ 1);
+            uint8_t* sa = smem + stage * stage_bytes;
+            mbar_expect_tx(&bars->full[stage], kABytes + b_bytes);
+            tma_load_5d(sa, &map_a, &bars->full[stage], tap.pw * p.cin + kc * kBlockK,
+                        j0 + tap.dw, tap.ph, i0 + tap.dh, n);
+            tma_load_3d(sa + kABytes, &map_w, &bars->full[stage], kc * kBlockK, 0, tap.widx);
+            if (++stage == kStages) { stage = 0; ph ^= 1; }
+          }
+        }
+        if (GDN) {
+          for (int kc = 0; kc < gdn_kblocks; ++kc) {
+            mbar_wait(&bars->empty[stage], ph ^ 1);
+            uint8_t* sa = smem + stage * stage_bytes;
+            mbar_expect_tx(&bars->full[stage], b_bytes);
+            tma_load_2d(sa + kABytes, &map_g, &bars->full[stage], kc * kBlockK, 0);
+            if (++stage == kStages) { stage = 0; ph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t ph = 0, it = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+        int phase, n, i0, j0;
+        tile_coords(tile, phase, n, i0, j0);
+        const int acc = GDN ? 0 : (it & 1);
+        const uint32_t use = GDN ? it : (it >> 1);       // how often this accumulator was used
+        mbar_wait(&bars->d1_empty[acc], (use & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d1 = tmem + acc * 256;
+        const int nk = (p.phase_start[phase + 1] - p.phase_start[phase]) * kchunks;
+        for (int kb = 0; kb < nk; ++kb) {
+          mbar_wait(&bars->full[stage], ph);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+          const uint64_t da = make_desc_sw128(sa), db = make_desc_sw128(sa + kABytes);
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k)
+            umma_bf16(d1, da + (k * 2), db + (k * 2), idesc, (kb | k) != 0);
+          umma_commit(&bars->empty[stage]);
+          if (++stage == kStages) { stage = 0; ph ^= 1; }
+        }
+        umma_commit(&bars->d1_full[acc]);
+        if (GDN) {
+          mbar_wait(&bars->a2_full, it & 1);
+          tc_fence_after();
+          const uint32_t d2 = tmem + 256;
+          for (int kc = 0; kc < gdn_kblocks; ++kc) {
+            mbar_wait(&bars->full[stage], ph);
+            tc_fence_after();
+            const uint32_t sb = smem_u32(smem + stage * stage_bytes) + kABytes;
+            const uint64_t da = make_desc_sw128(smem_u32(a2 + kc * kABytes));
+            const uint64_t db = make_desc_sw128(sb);
+#pragma unroll
+            for (int k = 0; k < kBlockK / 16; ++k)
+              umma_bf16(d2, da + (k * 2), db + (k * 2), idesc, (kc | k) != 0);
+            umma_commit(&bars->empty[stage]);
+            if (++stage == kStages) { stage = 0; ph ^= 1; }
+          }
+          umma_commit(&bars->d2_full);
+        }
+      }
+    }
+  } else {
+    // ===== epilogue: 4 warps, thread <-> TMEM lane <-> tile pixel =====
+    const int quad = warp & 3;
+    const int r = quad * 32 + lane;                  // pixel within the tile / TMEM lane
+    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+    uint32_t it = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      int phase, n, i0, j0;
+      tile_coords(tile, phase, n, i0, j0);
+      const int acc = GDN ? 0 : (it & 1);
+      const uint32_t use = GDN ? it : (it >> 1);
+      const int li = r / p.tw, lj = r - li * p.tw;
+      const int i2 = i0 + li, j2 = j0 + lj;
+      const bool valid = i2 < p.hs && j2 < p.ws;
+      const int pi = phase / p.su, pj = phase - pi * p.su;
+      const int64_t pix = ((int64_t)n * p.ho + (i2 * p.su + pi)) * p.wo + (j2 * p.su + pj);
+      const uint32_t d1 = tmem + acc * 256 + lane_addr;
+      mbar_wait(&bars->d1_full[acc], use & 1);
+      tc_fence_after();
+      if (GDN) {
+        // phase 1: x^2 -> bf16 K-major SW128 tile(s) in shared memory
+        for (int c0 = 0; c0 < p.cout; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(d1 + c0, v);
+          tmem_ld_wait();
+          uint8_t* row = a2 + (c0 / kBlockK) * kABytes + r * 128;
+          const int chunk0 = (c0 % kBlockK) / 8;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            uint32_t w[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float x0 = __uint_as_float(v[q * 8 + 2 * e]) + s_bias[c0 + q * 8 + 2 * e];
+              const float x1 = __uint_as_float(v[q * 8 + 2 * e + 1]) + s_bias[c0 + q * 8 + 2 * e + 1];
+              w[e] = pack_bf16(x0 * x0, x1 * x1);
+            }
+            const int phys = (chunk0 + q) ^ (r & 7);
+            *reinterpret_cast<uint4*>(row + phys * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+          }
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(&bars->a2_full);
+        mbar_wait(&bars->d2_full, it & 1);
+        tc_fence_after();
+      }
+      const uint32_t d2 = tmem + 256 + lane_addr;
+      for (int c0 = 0; c0 < p.npad; c0 += 32) {
+        uint32_t v[32], g[32];
+        tmem_ld_32x32(d1 + c0, v);
+        if (GDN) tmem_ld_32x32(d2 + c0, g);
+        tmem_ld_wait();
+        float y[32];
+#pragma unroll
+        for (int e = 0; e < 32; ++e) {
+          float x = __uint_as_float(v[e]) + s_bias[c0 + e];
+          if (GDN) {
+            const float nrm = __uint_as_float(g[e]) + s_beta[c0 + e];
+            x *= (p.act == TFC_ACT_IGDN) ? sqrtf(nrm) : rsqrtf(nrm);
+          } else if (p.act == TFC_ACT_RELU) {
+            x = fmaxf(x, 0.f);
+          }
+          y[e] = x;
+        }
+        if (valid) {
+          const int nvalid = min(32, p.cout - c0);
+          if (nvalid == 32 && (p.cout & 7) == 0) {
+            if (p.out_f32) {
+              float4* dst = reinterpret_cast<float4*>(static_cast<float*>(p.out) + pix * p.cout + c0);
+#pragma unroll
+              for (int q = 0; q < 8; ++q)
+                dst[q] = make_float4(y[4 * q], y[4 * q + 1], y[4 * q + 2], y[4 * q + 3]);
+            } else {
+              uint4* dst = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + pix * p.cout + c0);
+#pragma unroll
+              for (int q = 0; q < 4; ++q)
+                dst[q] = make_uint4(pack_bf16(y[8 * q], y[8 * q + 1]), pack_bf16(y[8 * q + 2], y[8 * q + 3]),
+                                    pack_bf16(y[8 * q + 4], y[8 * q + 5]), pack_bf16(y[8 * q + 6], y[8 * q + 7]));
+            }
+          } else {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              if (e < nvalid) {
+                if (p.out_f32) static_cast<float*>(p.out)[pix * p.cout + c0 + e] = y[e];
+                else static_cast<__nv_bfloat16*>(p.out)[pix * p.cout + c0 + e] = __float2bfloat16_rn(y[e]);
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&bars->d1_empty[acc]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+
+// ---- weight repack: fp32 [tap][cin][cout] -> bf16 [tap][npad][cin]; gamma [k][c] -> [c][k] -----
+__global__ void repack_weights_kernel(const float* __restrict__ w, int taps, int cin, int cout,
+                                      int npad, __nv_bfloat16* __restrict__ out) {
+  const int64_t total = (int64_t)taps * npad * cin;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cin);
+    const int o = (int)((i / cin) % npad);
+    const int t = (int)(i / ((int64_t)cin * npad));
+    const float v = o < cout ? w[((int64_t)t * cin + c) * cout + o] : 0.f;
+    out[i] = __float2bfloat16_rn(v);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, []() {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+int make_map(CUtensorMap* m, void* base, int rank, const cuuint64_t* dims,
+             const cuuint64_t* strides_bytes, const cuuint32_t* box) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return tfc::fail(TFC_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
+  cuuint32_t ones[5] = {1, 1, 1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, base, dims,
+                  strides_bytes, box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return tfc::fail(TFC_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return TFC_OK;
+}
+
+inline int floor_div(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
+
+// Taps of every output phase (see the header comment).  Returns false if unsupported.
+bool build_taps(const tfc_conv_desc& d, Params* p) {
+  const int su = d.su, sd = d.sd;
+  int count = 0;
+  p->su = su;
+  for (int pi = 0; pi < su; ++pi) {
+    for (int pj = 0; pj < su; ++pj) {
+      p->phase_start[pi * su + pj] = count;
+      for (int a = 0; a < d.kh; ++a) {
+        for (int b = 0; b < d.kw; ++b) {
+          Tap t{};
+          if (su > 1) {  // sd == 1: tap is live for this phase iff it lands on the lattice
+            const int ya = pi + a - d.pad_top, xb = pj + b - d.pad_left;
+            if (((ya % su) + su) % su != 0 || ((xb % su) + su) % su != 0) continue;
+            t.dh = (int8_t)floor_div(ya, su);
+            t.dw = (int8_t)floor_div(xb, su);
+            t.ph = t.pw = 0;
+          } else {       // stride-sd correlation: split the offset into (box shift, parity)
+            const int ya = a - d.pad_top, xb = b - d.pad_left;
+            const int qh = floor_div(ya, sd), qw = floor_div(xb, sd);
+            t.dh = (int8_t)qh; t.dw = (int8_t)qw;
+            t.ph = (int8_t)(ya - qh * sd); t.pw = (int8_t)(xb - qw * sd);
+          }
+          t.widx = (int16_t)(a * d.kw + b);
+          if (count >= kMaxTaps) return false;
+          p->taps[count++] = t;
+        }
+      }
+    }
+  }
+  p->phase_start[su * su] = count;
+  return true;
+}
+
+void pick_tile(int hs, int ws, int* th, int* tw) {
+  const int cand[][2] = {{8, 16}, {4, 32}, {16, 8}, {2, 64}, {32, 4}, {1, 128}, {64, 2}, {128, 1}};
+  double best = -1;
+  for (auto& c : cand) {
+    const double cover = (double)((hs + c[0] - 1) / c[0] * c[0]) * ((ws + c[1] - 1) / c[1] * c[1]);
+    const double util = (double)hs * ws / cover;
+    if (util > best + 1e-9) { best = util; *th = c[0]; *tw = c[1]; }
+  }
+}
+
+size_t smem_bytes(int npad, int cout, bool gdn) {
+  const int b_bytes = npad * kBlockK * 2;
+  const int stage = kABytes + ((b_bytes + 1023) & ~1023);
+  return 1024 + (size_t)kStages * stage + (gdn ? (size_t)(cout / kBlockK) * kABytes : 0) +
+         2 * 256 * sizeof(float) + sizeof(Barriers) + 64;
+}
+
+}  // namespace
 
 namespace tfc {
-bool conv_umma_supported(const tfc_conv_desc&, const char** why) {
-  if (why) *why = "tcgen05 kernel not built yet";
-  return false;
+
+bool conv_umma_supported(const tfc_conv_desc& d, const char** why) {
+  const char* dummy;
+  if (!why) why = &dummy;
+  const bool gdn = d.act == TFC_ACT_GDN || d.act == TFC_ACT_IGDN;
+  if (d.in_dtype != TFC_BF16) { *why = "input must be bfloat16"; return false; }
+  if (d.cin % kBlockK) { *why = "cin must be a multiple of 64"; return false; }
+  if (d.cout > 256) { *why = "cout must be <= 256"; return false; }
+  if (gdn && d.cout % kBlockK) { *why = "GDN needs cout to be a multiple of 64"; return false; }
+  if (d.sd > 1 && d.su > 1) { *why = "strides_down and strides_up together"; return false; }
+  if (d.su > 4 || d.sd > 8) { *why = "stride too large"; return false; }
+  if (d.h % d.sd || d.w % d.sd) { *why = "input size must be a multiple of strides_down"; return false; }
+  if (d.ho % d.su || d.wo % d.su) { *why = "output size must be a multiple of strides_up"; return false; }
+  if (d.kh * d.kw > kMaxTaps || d.kh > 64 || d.kw > 64) { *why = "kernel too large"; return false; }
+  const int npad = (d.cout + 15) / 16 * 16;
+  if (smem_bytes(npad, d.cout, gdn) > 227 * 1024) { *why = "shared memory"; return false; }
+  if ((int64_t)d.n * d.ho * d.wo / 128 > (1 << 30)) { *why = "too many tiles"; return false; }
+  return true;
 }
-size_t conv_umma_workspace(const tfc_conv_desc&) { return 0; }
-int conv_umma(const tfc_conv_desc&, const void*, const float*, const float*, const float*,
-              const float*, void*, void*, size_t, cudaStream_t) {
-  return fail(TFC_ERR_UNIMPLEMENTED, "tcgen05 conv path not built yet");
+
+size_t conv_umma_workspace(const tfc_conv_desc& d) {
+  const int npad = (d.cout + 15) / 16 * 16;
+  size_t w = (size_t)d.kh * d.kw * npad * d.cin * 2;
+  w = (w + 255) & ~size_t(255);
+  return w + (size_t)npad * npad * 2 + 256;
 }
+
+int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const float* bias,
+              const float* beta, const float* gamma, void* out, void* ws, size_t ws_bytes,
+              cudaStream_t st) {
+  const bool gdn = d.act == TFC_ACT_GDN || d.act == TFC_ACT_IGDN;
+  if (ws == nullptr || ws_bytes < conv_umma_workspace(d))
+    return fail(TFC_ERR_INVALID_ARGUMENT, "conv workspace too small: need %zu bytes",
+                conv_umma_workspace(d));
+  if ((reinterpret_cast<uintptr_t>(in) & 15) || (reinterpret_cast<uintptr_t>(ws) & 255) ||
+      (reinterpret_cast<uintptr_t>(out) & 15))
+    return fail(TFC_ERR_INVALID_ARGUMENT, "conv buffers must be 16-byte (workspace 256-byte) aligned");
+  Params p{};
+  p.n = d.n; p.ho = d.ho; p.wo = d.wo; p.cout = d.cout; p.cin = d.cin;
+  p.npad = (d.cout + 15) / 16 * 16;
+  p.act = d.act; p.out_f32 = d.out_dtype == TFC_F32;
+  p.bias = bias; p.beta = beta; p.out = out;
+  if (!build_taps(d, &p)) return fail(TFC_ERR_UNIMPLEMENTED, "too many taps");
+  p.hs = d.ho / d.su; p.ws = d.wo / d.su;
+  pick_tile(p.hs, p.ws, &p.th, &p.tw);
+  p.tiles_h = (p.hs + p.th - 1) / p.th;
+  p.tiles_w = (p.ws + p.tw - 1) / p.tw;
+  p.num_tiles = d.su * d.su * d.n * p.tiles_h * p.tiles_w;
+
+  // weights (+ gamma^T) -> bf16 K-major
+  __nv_bfloat16* wb = static_cast<__nv_bfloat16*>(ws);
+  const int taps = d.kh * d.kw;
+  size_t wbytes = ((size_t)taps * p.npad * d.cin * 2 + 255) & ~size_t(255);
+  __nv_bfloat16* gb = reinterpret_cast<__nv_bfloat16*>(static_cast<uint8_t*>(ws) + wbytes);
+  repack_weights_kernel<<<std::min<int64_t>(((int64_t)taps * p.npad * d.cin + 255) / 256, 2048),
+                          256, 0, st>>>(w, taps, d.cin, d.cout, p.npad, wb);
+  TFC_LAUNCHED("repack_weights_kernel");
+  if (gdn) {
+    // gamma[k][c] is "[1 tap][cin=k][cout=c]" -> [c][k]
+    repack_weights_kernel<<<(d.cout * d.cout + 255) / 256, 256, 0, st>>>(gamma, 1, d.cout,
+                                                                         d.cout, p.npad, gb);
+    TFC_LAUNCHED("repack_weights_kernel");
+  }
+
+  CUtensorMap map_a, map_w, map_g;
+  const cuuint64_t C = d.cin, s = d.sd;
+  {
+    cuuint64_t dims[5] = {s * C, (cuuint64_t)d.w / s, s, (cuuint64_t)d.h / s, (cuuint64_t)d.n};
+    cuuint64_t str[4] = {s * C * 2, (cuuint64_t)d.w * C * 2, s * d.w * C * 2,
+                         (cuuint64_t)d.h * d.w * C * 2};
+    cuuint32_t box[5] = {kBlockK, (cuuint32_t)p.tw, 1, (cuuint32_t)p.th, 1};
+    int rc = make_map(&map_a, const_cast<void*>(in), 5, dims, str, box);
+    if (rc) return rc;
+  }
+  {
+    cuuint64_t dims[3] = {C, (cuuint64_t)p.npad, (cuuint64_t)taps};
+    cuuint64_t str[2] = {C * 2, (cuuint64_t)p.npad * C * 2};
+    cuuint32_t box[3] = {kBlockK, (cuuint32_t)p.npad, 1};
+    int rc = make_map(&map_w, wb, 3, dims, str, box);
+    if (rc) return rc;
+  }
+  if (gdn) {
+    cuuint64_t dims[2] = {(cuuint64_t)d.cout, (cuuint64_t)p.npad};
+    cuuint64_t str[1] = {(cuuint64_t)d.cout * 2};
+    cuuint32_t box[2] = {kBlockK, (cuuint32_t)p.npad};
+    int rc = make_map(&map_g, gb, 2, dims, str, box);
+    if (rc) return rc;
+  } else {
+    map_g = map_w;
+  }
+  const size_t smem = smem_bytes(p.npad, d.cout, gdn);
+  const int grid = std::min(p.num_tiles, num_sms());
+  if (gdn) {
+    TFC_CUDA(cudaFuncSetAttribute(conv_umma_kernel<true>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    conv_umma_kernel<true><<<grid, kThreads, smem, st>>>(map_a, map_w, map_g, p);
+  } else {
+    TFC_CUDA(cudaFuncSetAttribute(conv_umma_kernel<false>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    conv_umma_kernel<false><<<grid, kThreads, smem, st>>>(map_a, map_w, map_g, p);
+  }
+  TFC_LAUNCHED("conv_umma_kernel");
+  return TFC_OK;
+}
+
 }  // namespace tfc

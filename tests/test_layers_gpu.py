@@ -246,3 +246,75 @@ def test_lower_bound_gradients(tfc):
   assert x.grad.tolist() == [-1., -1.]
   with pytest.raises(ValueError):
     tfc.lower_bound(x, 0., gradient="nope")
+
+
+# ---- tcgen05 implicit-GEMM path (impl=2) ------------------------------------------------------
+UMMA_CASES = [
+    # cin, cout, kernel, corr, sd, su, H, W, act
+    (64, 64, 3, True, 1, 1, 8, 16, None),
+    (192, 192, 5, True, 2, 1, 32, 48, None),
+    (192, 192, 5, True, 2, 1, 24, 40, "relu"),
+    (128, 128, 5, True, 2, 1, 16, 16, None),
+    (192, 192, 3, True, 1, 1, 12, 20, "relu"),
+    (192, 192, 3, False, 1, 1, 12, 20, None),
+    (192, 192, 5, False, 1, 2, 12, 20, "relu"),
+    (192, 3, 5, False, 1, 2, 16, 24, None),
+    (128, 3, 9, False, 1, 4, 8, 8, None),
+    (192, 192, 5, True, 2, 1, 32, 48, "gdn"),
+    (192, 192, 5, False, 1, 2, 12, 20, "igdn"),
+    (128, 128, 5, True, 2, 1, 20, 36, "gdn"),
+    (64, 64, 5, False, 1, 2, 6, 10, "igdn"),
+]
+
+
+@pytest.mark.parametrize("cin,cout,k,corr,sd,su,H,W,act", UMMA_CASES)
+@pytest.mark.parametrize("out_dtype", [torch.float32, torch.bfloat16])
+def test_umma_conv_matches_oracle(tfc, cin, cout, k, corr, sd, su, H, W, act, out_dtype):
+  """bf16-exact integer-valued data: products and fp32 sums are exact, so the tensor-core
+  path must agree with the float64 oracle to fp32 rounding (plus the bf16 rounding of x^2 in
+  the GDN GEMM / of the output when it is bfloat16)."""
+  rng = np.random.default_rng(10)
+  n = 3
+  x = rng.integers(-4, 5, size=(n, H, W, cin)).astype(np.float32)
+  kern = (rng.integers(-8, 9, size=(k, k, cin, cout)) / 8.0).astype(np.float32)
+  kern *= (rng.random(size=kern.shape) < 0.3)          # keep magnitudes moderate
+  b = (rng.integers(-8, 9, size=cout) / 4.0).astype(np.float32)
+  activation = None
+  if act == "relu":
+    activation = torch.relu
+  elif act in ("gdn", "igdn"):
+    activation = tfc.GDN(inverse=(act == "igdn"))
+  layer = tfc.SignalConv2D(cout, (k, k), corr=corr, strides_down=sd, strides_up=su,
+                           padding="same_zeros", use_bias=True, activation=activation,
+                           kernel_parameterizer=None, kernel_initializer=_static(kern),
+                           bias_initializer=_static(b), impl=2)
+  layer.build(cin, "cuda")
+  beta = gamma = None
+  if act in ("gdn", "igdn"):
+    g0 = (rng.integers(0, 5, size=(cout, cout)) / 64.0).astype(np.float32)
+    b0 = (rng.integers(4, 12, size=cout) / 4.0).astype(np.float32)
+    activation.reparam_gamma = activation.gamma_parameterizer.init(torch.from_numpy(g0).cuda())
+    activation.reparam_beta = activation.beta_parameterizer.init(torch.from_numpy(b0).cuda())
+    activation.invalidate()
+    beta, gamma = [t.cpu().numpy() for t in activation.effective()]
+  got = layer(torch.from_numpy(x).cuda().to(torch.bfloat16), out_dtype=out_dtype)
+  assert got.dtype == out_dtype
+  want = tfc_np.signal_conv2d(x, kern, b, corr, sd, su, "same_zeros")
+  if act == "relu":
+    want = torch.relu(want)
+  elif act in ("gdn", "igdn"):
+    want = tfc_np.gdn(want, beta, gamma, act == "igdn")
+  want = want.numpy()
+  assert tuple(got.shape) == want.shape
+  got = got.float().cpu().numpy()
+  tol = 2e-2 if (act in ("gdn", "igdn") or out_dtype == torch.bfloat16) else 1e-4
+  scale = np.abs(want).max() + 1e-6
+  err = np.abs(got - want).max() / scale
+  assert err <= tol, (err, scale)
+
+
+def test_umma_unsupported_shape_reports(tfc):
+  x = torch.zeros((1, 8, 8, 3), device="cuda", dtype=torch.bfloat16)
+  layer = tfc.SignalConv2D(8, (3, 3), corr=True, padding="same_zeros", impl=2)
+  with pytest.raises(NotImplementedError, match="cin must be a multiple of 64"):
+    layer(x)
