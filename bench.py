@@ -48,6 +48,7 @@ def parse_args():
   ap.add_argument("--conv-impl", type=int, default=0, help="0 auto, 1 CUDA-core, 2 tcgen05")
   ap.add_argument("--cpu-sample-images", type=int, default=1)
   ap.add_argument("--no-cpu-baseline", action="store_true")
+  ap.add_argument("--verbose", action="store_true", help="stage/layer breakdown on stderr")
   return ap.parse_args()
 
 
@@ -310,6 +311,8 @@ def run_b200(args):
     if world > 1:
       dist.destroy_process_group()
     return
+  if args.verbose:
+    stage_breakdown(model, x_dev, timer, args.steps)
   pixels = batch * h * w
   peaks = measured_peaks()
   per_layer, enc_f, dec_f = conv_flops(model, h, w)
@@ -352,6 +355,41 @@ def run_b200(args):
   print(json.dumps(line))
   if world > 1:
     dist.destroy_process_group()
+
+
+def stage_breakdown(model, x_dev, timer, steps):
+  """One instrumented step (synchronising between stages) + per-layer conv times."""
+  import torch
+
+  def timed(name, fn):
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    out = fn()
+    torch.cuda.synchronize()
+    sys.stderr.write("  %-28s %8.3f ms\n" % (name, (time.perf_counter() - t0) * 1e3))
+    return out
+
+  sys.stderr.write("stage breakdown (one synchronised step):\n")
+  y, z, sigma = timed("analyse (A, HA, HS)", lambda: model.analyse(x_dev))
+  side = timed("EB compress (z)", lambda: model.entropy_bottleneck.compress_device(z))
+  gc = model._conditional(sigma)
+  string = timed("GC compress (y)", lambda: gc.compress_device(y))
+  nf = model.num_filters
+  z_hat = timed("EB decompress (z)", lambda: model.entropy_bottleneck.decompress_device(
+      side, tuple(z.shape[1:3]) + (nf,), nf, torch.bfloat16))
+  sigma2 = timed("hyper synthesis", lambda: model.hyper_synthesis_transform(z_hat)[
+      :, :y.shape[1], :y.shape[2], :].contiguous())
+  gc2 = model._conditional(sigma2)
+  y_hat = timed("GC decompress (y)", lambda: gc2.decompress_device(string, torch.bfloat16))
+  timed("synthesis", lambda: model.synthesis_transform(y_hat))
+  sys.stderr.write("conv layers (mean over %d timed steps):\n" % steps)
+  agg = {}
+  for name, shape, a, b in timer.pairs:
+    key = (name, shape)
+    agg.setdefault(key, []).append(a.elapsed_time(b))
+  for (name, shape), v in agg.items():
+    sys.stderr.write("  %-10s %-24s %8.3f ms x%d\n" % (name, shape, float(np.mean(v)),
+                                                      len(v) // max(steps, 1)))
 
 
 def main():

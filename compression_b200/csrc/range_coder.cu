@@ -114,7 +114,7 @@ struct EncodeParams {
   int64_t index_stride;
   const int32_t* cdf_size;
   const int32_t* offset;
-  int32_t cols;
+  int32_t rows, cols;
   int overflow_width;
   // bounded form
   const int16_t* data16;
@@ -317,156 +317,6 @@ __device__ __forceinline__ int wide_search(const Decoder& d, RowPtr row, int lo,
 
 // Shared-memory image of the tables: ragged rows + one int4 {start, len, window base, offset}
 // per row.  Falls back to the dense global table when it does not fit.
-struct Tables {
-  const int32_t* tbl;  // ragged (shared) or dense (global)
-  const int4* meta;    // shared, or nullptr
-  bool staged;
-};
-
-template <bool STAGED>
-__device__ __forceinline__ void row_info(const Tables& t, const DecodeParams& p, int32_t r,
-                                         int& start, int& len, int& wb, int& off) {
-  if (STAGED) {
-    const int4 m = t.meta[r];
-    start = m.x; len = m.y; wb = m.z; off = m.w;
-  } else {
-    len = __ldg(p.cdf_size + r);
-    start = r * p.cols;
-    off = __ldg(p.offset + r);
-    wb = len <= 32 ? 0 : min(max(len / 2 - 16, 0), len - 32);
-  }
-}
-
-template <bool STAGED>
-__device__ void decode_unbounded_stream(const DecodeParams& p, const Tables& t, int64_t s,
-                                        int lane) {
-  Decoder d;
-  const int32_t nb = p.nbytes[s];
-  d.init(p.enc + s * p.cap, (uint32_t)max(nb, 0));
-  const int32_t* idx = p.index + s * p.index_stride;
-  int32_t* out = p.out32 + s * p.n;
-  const int prec = p.precision, w = p.overflow_width;
-  const uint32_t all1 = (1u << w) - 1u;
-
-  for (int64_t base = 0; base < p.n; base += 32) {
-    const int cnt = (int)min((int64_t)32, p.n - base);
-    const int32_t myr = lane < cnt ? __ldg(idx + base + lane) : 0;
-    int32_t mine = 0;
-    // software pipeline: row info + window value of symbol j+1 are fetched while j decodes
-    int start, len, wb, off;
-    row_info<STAGED>(t, p, __shfl_sync(0xFFFFFFFFu, myr, 0), start, len, wb, off);
-    uint32_t wv = (wb + lane < len) ? (uint32_t)t.tbl[start + wb + lane] : 0u;
-    for (int j = 0; j < cnt; ++j) {
-      int nstart = 0, nlen = 0, nwb = 0, noff = 0;
-      uint32_t nwv = 0;
-      if (j + 1 < cnt) {
-        row_info<STAGED>(t, p, __shfl_sync(0xFFFFFFFFu, myr, j + 1), nstart, nlen, nwb, noff);
-        nwv = (nwb + lane < nlen) ? (uint32_t)t.tbl[nstart + nwb + lane] : 0u;
-      }
-      const uint64_t tgt = d.target(prec);
-      const bool valid = wb + lane < len;
-      const uint32_t b = __ballot_sync(0xFFFFFFFFu, valid && d.above(wv, tgt));
-      const int f = __ffs(b) - 1;
-      uint32_t c0, c1;
-      int k;
-      if (f >= 1) {  // hit inside the window, left neighbour in lane f-1
-        k = wb + f;
-        c0 = __shfl_sync(0xFFFFFFFFu, wv, f - 1);
-        c1 = __shfl_sync(0xFFFFFFFFu, wv, f);
-      } else {
-        const int32_t* row = t.tbl + start;
-        if (f == 0) k = wb == 0 ? len : wide_search(d, row, 1, wb, tgt, lane);
-        else k = (wb + 32 <= len - 1) ? wide_search(d, row, wb + 32, len - 1, tgt, lane) : len;
-        if (k > len - 1) { d.corrupt = true; k = len - 1; }
-        c0 = (uint32_t)row[k - 1];
-        c1 = (uint32_t)row[k];
-      }
-      d.narrow(c0, c1, prec);
-      int32_t v = k - 1;
-      const int32_t top = len - 2;
-      if (v == top) {
-        int nd = 0;
-        uint32_t u;
-        do { u = d.digit(w); nd += (int)u; } while (u == all1 && nd < 64 && !d.corrupt);
-        uint32_t x = 0;
-        for (int q = 0; q < nd; ++q) {
-          const uint32_t dg = d.digit(w);
-          if (q * w < 32) x |= dg << (q * w);
-        }
-        v = (x & 1u) ? -(int32_t)(x >> 1) - 1 : (int32_t)(x >> 1) + top;
-      }
-      v += off;
-      if (lane == j) mine = v;
-      start = nstart; len = nlen; wb = nwb; off = noff; wv = nwv;
-    }
-    if (lane < cnt) out[base + lane] = mine;
-  }
-  if (lane == 0 && p.status) p.status[s] = d.corrupt ? TFC_STREAM_CORRUPT : TFC_STREAM_OK;
-}
-
-__global__ void __launch_bounds__(256) decode_unbounded_kernel(const DecodeParams p) {
-  extern __shared__ __align__(16) uint8_t smem_dec[];
-  __shared__ int s_total;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nthreads = blockDim.x;
-
-  // ---- stage the tables (ragged) --------------------------------------------------------
-  int4* meta = reinterpret_cast<int4*>(smem_dec);
-  int32_t* tbl = reinterpret_cast<int32_t*>(smem_dec + (size_t)p.rows * sizeof(int4));
-  const int64_t meta_bytes = (int64_t)p.rows * (int64_t)sizeof(int4);
-  bool staged = meta_bytes + 16 <= p.table_budget;
-  if (staged) {
-    // row starts by a serial prefix sum in thread 0 (rows is a few hundred at most)
-    if (threadIdx.x == 0) {
-      int acc = 0;
-      for (int r = 0; r < p.rows; ++r) {
-        const int len = min(max(__ldg(p.cdf_size + r), 0), p.cols);
-        meta[r] = make_int4(acc, len, 0, __ldg(p.offset + r));
-        acc += len;
-      }
-      s_total = acc;
-    }
-    __syncthreads();
-    staged = meta_bytes + (int64_t)s_total * 4 <= p.table_budget;
-  }
-  if (staged) {
-    for (int r = warp; r < p.rows; r += nthreads >> 5) {
-      const int start = meta[r].x, len = meta[r].y;
-      const int32_t* src = p.cdf + (int64_t)r * p.cols;
-      // copy the row and find its mode (largest pmf entry) for the window placement
-      int best = 0, bestk = 1;
-      for (int k = lane; k < len; k += 32) {
-        const int32_t c = __ldg(src + k);
-        tbl[start + k] = c;
-        if (k + 1 < len) {
-          const int pm = __ldg(src + k + 1) - c;
-          if (pm > best) { best = pm; bestk = k + 1; }
-        }
-      }
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const int ob = __shfl_xor_sync(0xFFFFFFFFu, best, o);
-        const int ok = __shfl_xor_sync(0xFFFFFFFFu, bestk, o);
-        if (ob > best || (ob == best && ok < bestk)) { best = ob; bestk = ok; }
-      }
-      if (lane == 0) meta[r].z = len <= 32 ? 0 : min(max(bestk - 16, 0), len - 32);
-    }
-  }
-  __syncthreads();
-
-  const int64_t s = (int64_t)blockIdx.x * (nthreads >> 5) + warp;
-  if (s >= p.S) return;
-  Tables t;
-  t.staged = staged;
-  if (staged) {
-    t.tbl = tbl; t.meta = meta;
-    decode_unbounded_stream<true>(p, t, s, lane);
-  } else {
-    t.tbl = p.cdf; t.meta = nullptr;
-    decode_unbounded_stream<false>(p, t, s, lane);
-  }
-}
-
 // bounded decode: every element has its own (broadcast) row of `chip` entries
 __global__ void __launch_bounds__(256) decode_bounded_kernel(const DecodeParams p) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -493,6 +343,10 @@ __global__ void __launch_bounds__(256) decode_bounded_kernel(const DecodeParams 
   }
   if (lane == 0 && p.status) p.status[s] = d.corrupt ? TFC_STREAM_CORRUPT : TFC_STREAM_OK;
 }
+
+}  // namespace
+#include "rc_unbounded.cuh"
+namespace {
 
 // ---------------------------------------------------------------------------------------
 // debug_level=1 argument checks (unbounded_index_range_coding_kernels.cc:58-115,
@@ -731,10 +585,18 @@ extern "C" int tfc_unbounded_index_range_encode(
   p.cdf_size = d_cdf_size; p.offset = d_offset; p.cols = cols; p.overflow_width = overflow_width;
   p.cdf = d_cdf; p.S = S; p.n = n; p.precision = precision;
   p.out = d_out; p.cap = cap; p.nbytes = d_nbytes; p.status = d_status;
-  const int wpb = warps_per_block(S);
-  const size_t smem = (size_t)wpb * (2 * kChunk + 4) * sizeof(uint32_t);
-  const int64_t blocks = (S + wpb - 1) / wpb;
-  encode_kernel<true><<<(unsigned)blocks, wpb * 32, smem, st>>>(p);
+  p.rows = rows;
+  const int64_t dense = (int64_t)rows * cols * 4 + (int64_t)rows * 16 + 16;
+  const int budget = (int)std::min<int64_t>(dense, kTableBudget);
+  const size_t smem = (size_t)4 * kSuper * sizeof(uint32_t) + (size_t)budget;
+  static bool enc_attr_set = false;
+  if (!enc_attr_set) {
+    TFC_CUDA(cudaFuncSetAttribute(encode_unbounded_kernel,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(4 * kSuper * sizeof(uint32_t)) + kTableBudget));
+    enc_attr_set = true;
+  }
+  encode_unbounded_kernel<<<(unsigned)S, 128, smem, st>>>(p, budget);
   TFC_LAUNCHED("encode_kernel<unbounded>");
   return TFC_OK;
 }
@@ -770,13 +632,15 @@ extern "C" int tfc_unbounded_index_range_decode(
   p.table_budget = budget;
   static bool attr_set = false;
   if (!attr_set) {
-    TFC_CUDA(cudaFuncSetAttribute(decode_unbounded_kernel,
-                                  cudaFuncAttributeMaxDynamicSharedMemorySize, kTableBudget));
+    TFC_CUDA(cudaFuncSetAttribute(decode_unbounded_kernel2,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  kTableBudget + 16 + 8 * kDecScratch));
     attr_set = true;
   }
   const int wpb = warps_per_block(S);
   const int64_t blocks = (S + wpb - 1) / wpb;
-  decode_unbounded_kernel<<<(unsigned)blocks, wpb * 32, (size_t)budget, st>>>(p);
+  decode_unbounded_kernel2<<<(unsigned)blocks, wpb * 32,
+                             (size_t)((budget + 15) & ~15) + (size_t)wpb * kDecScratch, st>>>(p);
   TFC_LAUNCHED("decode_unbounded_kernel");
   return TFC_OK;
 }
