@@ -20,10 +20,13 @@ int validate(const tfc_conv_desc* d) {
   return TFC_OK;
 }
 
-bool use_umma(const tfc_conv_desc& d) {
-  if (d.impl == 1) return false;
-  const char* why = nullptr;
-  return tfc::conv_umma_supported(d, &why);
+// 0: CUDA-core path, 1: tcgen05 implicit GEMM, 2: space-to-depth + tcgen05
+int pick_path(const tfc_conv_desc& d, const char** why) {
+  if (d.impl == 1) return 0;
+  if (tfc::conv_umma_supported(d, why)) return 1;
+  const char* why2 = nullptr;
+  if (tfc::conv_s2d_supported(d, &why2)) return 2;
+  return 0;
 }
 
 }  // namespace
@@ -31,10 +34,11 @@ bool use_umma(const tfc_conv_desc& d) {
 extern "C" size_t tfc_signal_conv2d_workspace(const tfc_conv_desc* desc) {
   if (validate(desc)) return 0;
   size_t need = 256;
-  if (desc->impl != 2) need = std::max(need, tfc::conv_direct_workspace(*desc));
   const char* why = nullptr;
-  if (desc->impl != 1 && tfc::conv_umma_supported(*desc, &why))
-    need = std::max(need, tfc::conv_umma_workspace(*desc));
+  const int path = pick_path(*desc, &why);
+  if (path == 0) need = std::max(need, tfc::conv_direct_workspace(*desc));
+  if (path == 1) need = std::max(need, tfc::conv_umma_workspace(*desc));
+  if (path == 2) need = std::max(need, tfc::conv_s2d_workspace(*desc));
   return need;
 }
 
@@ -49,15 +53,17 @@ extern "C" int tfc_signal_conv2d(const tfc_conv_desc* desc, const void* d_in, co
     return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "GDN activation needs beta and gamma");
   if (desc->n == 0) return TFC_OK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (desc->impl == 2) {
-    const char* why = "unknown";
-    if (!tfc::conv_umma_supported(*desc, &why))
-      return tfc::fail(TFC_ERR_UNIMPLEMENTED, "tcgen05 conv path does not support this shape: %s",
-                       why);
-  }
-  if (use_umma(*desc))
+  const char* why = "unknown";
+  const int path = pick_path(*desc, &why);
+  if (desc->impl == 2 && path == 0)
+    return tfc::fail(TFC_ERR_UNIMPLEMENTED, "tcgen05 conv path does not support this shape: %s",
+                     why);
+  if (path == 1)
     return tfc::conv_umma(*desc, d_in, d_w, d_bias, d_beta, d_gamma, d_out, d_workspace,
                           workspace_bytes, st);
+  if (path == 2)
+    return tfc::conv_s2d(*desc, d_in, d_w, d_bias, d_beta, d_gamma, d_out, d_workspace,
+                         workspace_bytes, st);
   return tfc::conv_direct(*desc, d_in, d_w, d_bias, d_beta, d_gamma, d_out, d_workspace,
                           workspace_bytes, st);
 }

@@ -24,4 +24,11 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
               const float* beta, const float* gamma, void* out, void* ws, size_t ws_bytes,
               cudaStream_t st);
 
+// thin-input layers via space-to-depth + conv_umma (conv_s2d.cu)
+bool conv_s2d_supported(const tfc_conv_desc& d, const char** why);
+size_t conv_s2d_workspace(const tfc_conv_desc& d);
+int conv_s2d(const tfc_conv_desc& d, const void* in, const float* w, const float* bias,
+             const float* beta, const float* gamma, void* out, void* ws, size_t ws_bytes,
+             cudaStream_t st);
+
 }  // namespace tfc

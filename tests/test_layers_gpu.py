@@ -314,7 +314,42 @@ def test_umma_conv_matches_oracle(tfc, cin, cout, k, corr, sd, su, H, W, act, ou
 
 
 def test_umma_unsupported_shape_reports(tfc):
-  x = torch.zeros((1, 8, 8, 3), device="cuda", dtype=torch.bfloat16)
+  x = torch.zeros((1, 8, 8, 100), device="cuda", dtype=torch.bfloat16)
   layer = tfc.SignalConv2D(8, (3, 3), corr=True, padding="same_zeros", impl=2)
   with pytest.raises(NotImplementedError, match="cin must be a multiple of 64"):
     layer(x)
+
+
+S2D_CASES = [
+    # cin, cout, kernel, sd, H, W, act, input dtype
+    (3, 192, 5, 2, 32, 48, "gdn", torch.float32),
+    (3, 192, 5, 2, 24, 40, None, torch.bfloat16),
+    (3, 128, 9, 4, 32, 32, "gdn", torch.float32),
+    (3, 64, 3, 1, 12, 20, "relu", torch.float32),
+    (12, 64, 5, 2, 16, 24, None, torch.float32),
+]
+
+
+@pytest.mark.parametrize("cin,cout,k,sd,H,W,act,in_dtype", S2D_CASES)
+def test_thin_input_conv_space_to_depth(tfc, cin, cout, k, sd, H, W, act, in_dtype):
+  """First analysis layer (3 input channels) on the tensor cores via space-to-depth."""
+  rng = np.random.default_rng(11)
+  x = rng.integers(-4, 5, size=(2, H, W, cin)).astype(np.float32)
+  kern = (rng.integers(-8, 9, size=(k, k, cin, cout)) / 8.0).astype(np.float32)
+  b = (rng.integers(-8, 9, size=cout) / 4.0).astype(np.float32)
+  activation = {"relu": torch.relu, "gdn": tfc.GDN(), None: None}[act]
+  layer = tfc.SignalConv2D(cout, (k, k), corr=True, strides_down=sd, padding="same_zeros",
+                           use_bias=True, activation=activation, kernel_parameterizer=None,
+                           kernel_initializer=_static(kern), bias_initializer=_static(b), impl=2)
+  layer.build(cin, "cuda")
+  got = layer(torch.from_numpy(x).cuda().to(in_dtype), out_dtype=torch.float32)
+  want = tfc_np.signal_conv2d(x, kern, b, True, sd, 1, "same_zeros")
+  if act == "relu":
+    want = torch.relu(want)
+  elif act == "gdn":
+    beta, gamma = [t.cpu().numpy() for t in activation.effective()]
+    want = tfc_np.gdn(want, beta, gamma, False)
+  want = want.numpy()
+  assert tuple(got.shape) == want.shape
+  err = np.abs(got.cpu().numpy() - want).max() / (np.abs(want).max() + 1e-6)
+  assert err <= (2e-2 if act == "gdn" else 1e-4), err
