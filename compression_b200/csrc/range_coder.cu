@@ -18,6 +18,7 @@
 //           bounds.  Rows longer than the window fall back to a 32-ary ballot search.
 // All arithmetic is integer and bit-exact with the reference.
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 #include "common.cuh"
@@ -346,6 +347,7 @@ __global__ void __launch_bounds__(256) decode_bounded_kernel(const DecodeParams 
 
 }  // namespace
 #include "rc_unbounded.cuh"
+#include "rc_v4.cuh"
 namespace {
 
 // ---------------------------------------------------------------------------------------
@@ -476,6 +478,30 @@ int run_unbounded_checks(const int32_t* d_index, int64_t index_count, const int3
   return finish_checks(rec, st, rows, cols, precision, 0);
 }
 
+
+// ---- generation-4 unbounded kernels (rc_v4.cuh): launch plumbing -----------------------------
+constexpr int kV4TableBudget = 72 * 1024;
+
+int v4_max_puts(int overflow_width) {   // puts (= stream words at most) one symbol can take
+  const int ndmax = (32 + overflow_width - 1) / overflow_width;
+  const int all1 = (1 << overflow_width) - 1;
+  return 1 + ndmax / all1 + 2 + ndmax;
+}
+
+bool v4_usable(int32_t rows) {
+  static int disabled = -1;
+  if (disabled < 0) {
+    const char* e = getenv("TFC_CODER_V3");
+    disabled = (e && e[0] == '1') ? 1 : 0;
+  }
+  return !disabled && rows >= 1 && rows <= 1024;
+}
+
+int v4_table_budget(int32_t rows, int32_t cols) {
+  const size_t dense = v4::tables_bytes(rows, (int64_t)rows * cols);
+  return (int)((std::min<size_t>(dense, kV4TableBudget) + 15) & ~size_t(15));
+}
+
 int warps_per_block(int64_t S) {
   // few streams: one warp per block so the streams spread over the SMs; many: pack 8
   const int sms = tfc::num_sms();
@@ -580,6 +606,26 @@ extern "C" int tfc_unbounded_index_range_encode(
                               precision, st);
     if (rc) return rc;
   }
+  if (v4_usable(rows)) {
+    v4::EncParamsV4 q{};
+    q.data = d_data; q.index = d_index; q.index_stride = index_stride; q.cdf = d_cdf;
+    q.cdf_size = d_cdf_size; q.offset = d_offset; q.rows = rows; q.cols = cols;
+    q.precision = precision; q.overflow_width = overflow_width; q.out = d_out; q.cap = cap;
+    q.nbytes = d_nbytes; q.status = d_status; q.S = S; q.n = n;
+    q.round = std::max(32, std::min(v4::kRoundMax, v4::kPutCap / v4_max_puts(overflow_width) / 32 * 32));
+    q.table_bytes = v4_table_budget(rows, cols);
+    const size_t smem = (size_t)q.table_bytes + v4::enc_bytes();
+    static bool attr = false;
+    if (!attr) {
+      TFC_CUDA(cudaFuncSetAttribute(v4::encode_unbounded_v4,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)(kV4TableBudget + 16 + v4::enc_bytes())));
+      attr = true;
+    }
+    v4::encode_unbounded_v4<<<(unsigned)S, 96, smem, st>>>(q);
+    TFC_LAUNCHED("encode_unbounded_v4");
+    return TFC_OK;
+  }
   EncodeParams p{};
   p.data32 = d_data; p.index = d_index; p.index_stride = index_stride;
   p.cdf_size = d_cdf_size; p.offset = d_offset; p.cols = cols; p.overflow_width = overflow_width;
@@ -621,6 +667,34 @@ extern "C" int tfc_unbounded_index_range_decode(
     rc = run_unbounded_checks(d_index, index_stride ? S * n : n, d_cdf, rows, cols, d_cdf_size,
                               precision, st);
     if (rc) return rc;
+  }
+  if (v4_usable(rows)) {
+    v4::DecParamsV4 q{};
+    q.enc = d_enc; q.cap = cap; q.nbytes = d_nbytes; q.index = d_index;
+    q.index_stride = index_stride; q.cdf = d_cdf; q.cdf_size = d_cdf_size; q.offset = d_offset;
+    q.rows = rows; q.cols = cols; q.precision = precision; q.overflow_width = overflow_width;
+    q.out = d_out; q.status = d_status; q.S = S; q.n = n;
+    const int mp = v4_max_puts(overflow_width);
+    q.round = std::max(32, std::min(v4::kRoundMax, (v4::kLinMax - 8) / 2 / mp / 32 * 32));
+    q.round_words = q.round * mp;
+    if (2 * q.round_words + 8 > v4::kLinMax)
+      return tfc::fail(TFC_ERR_UNIMPLEMENTED, "overflow_width %d needs a larger stream window", overflow_width);
+    q.max_digits = (32 + overflow_width - 1) / overflow_width;
+    q.table_bytes = v4_table_budget(rows, cols);
+    const int sms = tfc::num_sms();
+    q.streams_per_cta = S <= sms ? 1 : (S <= 2 * (int64_t)sms ? 2 : 4);
+    const size_t smem = (size_t)q.table_bytes + (size_t)q.streams_per_cta * v4::dec_pair_bytes();
+    static bool attr = false;
+    if (!attr) {
+      TFC_CUDA(cudaFuncSetAttribute(v4::decode_unbounded_v4,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)(kV4TableBudget + 16 + 4 * v4::dec_pair_bytes())));
+      attr = true;
+    }
+    const int64_t blocks = (S + q.streams_per_cta - 1) / q.streams_per_cta;
+    v4::decode_unbounded_v4<<<(unsigned)blocks, 64 * q.streams_per_cta, smem, st>>>(q);
+    TFC_LAUNCHED("decode_unbounded_v4");
+    return TFC_OK;
   }
   DecodeParams p{};
   p.enc = d_enc; p.cap = cap; p.nbytes = d_nbytes; p.index = d_index;

@@ -1,0 +1,643 @@
+// Unbounded-index range coder kernels, generation 4 (included by range_coder.cu).
+//
+// The coder state is a serial chain per stream, so everything here is about making that chain
+// short and keeping everything else off it:
+//   * all CDF entries are pre-shifted to precision 16 when the tables are staged in shared
+//     memory (floor(span*c / 2^p) == floor(span*(c << (16-p)) / 2^16)), so the per-symbol code
+//     has no variable shifts;
+//   * decode: one warp runs the chain for a stream with the state REPLICATED in all lanes (no
+//     shuffles, no ballots, no divergence; lane 0 stores).  A second "helper" warp per stream
+//     turns the next round's indexes into per-symbol records {c1, c2, c3, meta} (rows of up to
+//     4 symbols are decided by three independent multiplies + compares — no search), keeps a
+//     ring of big-endian stream words filled in shared memory, and writes the previous
+//     round's symbols back coalesced (adding the row offset).  Longer rows and escapes take an
+//     out-of-line binary search over the staged table.
+//   * encode: see the second half of this file.
+// Bit-exact with RangeEncoder/RangeDecoder (range_coder.cc:38-377) and the op loops of
+// unbounded_index_range_coding_kernels.cc:189-251, :308-368.
+#pragma once
+
+namespace v4 {
+
+constexpr int kRing = 8192;            // stream ring: 16-bit words per stream
+constexpr int kRoundMax = 256;         // symbols per round (upper bound)
+constexpr int kMaxRows = 65535;
+
+extern __shared__ __align__(16) uint8_t smem_v4[];
+
+struct Tables {          // shared-memory image of the CDF tables
+  const uint4* rowrec;   // {c1<<16, c2<<16, c3<<16, row} (precision 16) for 5-entry rows, else c=0
+  const int4* rowinfo;   // {start, len, offset, 0}
+  const uint32_t* tbl;   // ragged rows, entries << (16 - precision); null if they did not fit
+  const int32_t* gcdf;   // the caller's dense table (used when tbl is null; start = row*cols)
+  int sh;
+  __device__ __forceinline__ uint32_t at(int i) const {
+    return tbl ? tbl[i] : ((uint32_t)__ldg(gcdf + i) << sh);
+  }
+};
+
+__host__ __device__ inline size_t tables_bytes(int64_t rows, int64_t total_entries) {
+  return (size_t)rows * 32 + (size_t)total_entries * 4;
+}
+
+// All threads of the block.  The ragged rows are staged if they fit in `budget` bytes (the
+// host cannot know: the row lengths live on the device); row records always are.
+__device__ void stage_tables_v4(const int32_t* __restrict__ cdf, int rows, int cols,
+                                const int32_t* __restrict__ cdf_size,
+                                const int32_t* __restrict__ offset, int precision,
+                                uint8_t* smem, int budget, Tables* t) {
+  __shared__ int s_total;
+  uint4* rowrec = reinterpret_cast<uint4*>(smem);
+  int4* rowinfo = reinterpret_cast<int4*>(smem + (size_t)rows * 16);
+  uint32_t* tbl = reinterpret_cast<uint32_t*>(smem + (size_t)rows * 32);
+  const int sh = 16 - precision;
+  if (threadIdx.x < 32) {       // warp 0: exclusive scan of the row lengths
+    const int lane = threadIdx.x;
+    int carry = 0;
+    for (int r0 = 0; r0 < rows; r0 += 32) {
+      const int r = r0 + lane;
+      const int len = r < rows ? min(max(__ldg(cdf_size + r), 2), cols) : 0;
+      int incl = len;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      if (r < rows) rowinfo[r] = make_int4(carry + incl - len, len, __ldg(offset + r), 0);
+      carry += __shfl_sync(0xFFFFFFFFu, incl, 31);
+    }
+    if (lane == 0) s_total = carry;
+  }
+  __syncthreads();
+  const bool fits = tables_bytes(rows, s_total) <= (size_t)budget;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  for (int r = warp; r < rows; r += nwarps) {
+    int4 ri = rowinfo[r];
+    const int32_t* src = cdf + (int64_t)r * cols;
+    if (fits) {
+      for (int k = lane; k < ri.y; k += 32) tbl[ri.x + k] = (uint32_t)__ldg(src + k) << sh;
+    } else if (lane == 0) {
+      rowinfo[r].x = r * cols;
+    }
+    if (lane == 0) {
+      // fast class: rows of exactly 5 entries (3 coded values + escape; every row of a
+      // SymmetricConditional table with scale < ~0.35).  c' = c << 16 so that
+      // floor(span * c / 2^16) is one IMAD.HI.  Every other row gets c3' = 0, which makes the
+      // fast path's escape test (t3 <= rem) fire and sends the symbol to the general path.
+      uint32_t c1 = 0, c2 = 0, c3 = 0;
+      if (ri.y == 5) {
+        c1 = (uint32_t)__ldg(src + 1) << sh;
+        c2 = (uint32_t)__ldg(src + 2) << sh;
+        c3 = (uint32_t)__ldg(src + 3) << sh;
+        if (c1 > 0xFFFFu || c2 > 0xFFFFu || c3 > 0xFFFFu) c1 = c2 = c3 = 0;  // malformed
+      }
+      rowrec[r] = make_uint4(c1 << 16, c2 << 16, c3 << 16, (uint32_t)r);
+    }
+  }
+  __syncthreads();
+  t->rowrec = rowrec; t->rowinfo = rowinfo; t->tbl = fits ? tbl : nullptr;
+  t->gcdf = cdf; t->sh = sh;
+}
+
+__device__ __forceinline__ uint32_t scale16(uint32_t span1, uint32_t c) {
+  return (uint32_t)(((uint64_t)span1 * c + c) >> 16);
+}
+
+__device__ __forceinline__ void pair_barrier(int id) {
+  asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------
+// decode
+// ------------------------------------------------------------------------------------------
+struct DecState {
+  uint32_t rem;      // code - lo  (all the decoder ever needs of the two)
+  uint32_t span1;    // span - 1
+  uint32_t w0;       // the next stream word
+  uint32_t wa;       // shared-space address of the word after w0 (linear window)
+  bool corrupt;
+
+  __device__ __forceinline__ void narrow(uint32_t a, uint32_t b) {
+    rem -= a;
+    span1 = b - a;
+    if ((span1 >> 16) == 0) {
+      span1 = (span1 << 16) | 0xFFFFu;
+      rem = (rem << 16) | w0;
+      uint16_t v;
+      asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(wa));
+      w0 = v;
+      wa += 2;
+    }
+  }
+  // largest d in [0, all1] with floor(span * d / 2^w) <= rem, then narrow to [d, d+1)
+  __device__ __forceinline__ uint32_t digit(int sh, uint32_t all1) {
+    uint32_t lo = 0, hi = all1;
+    while (lo < hi) {
+      const uint32_t mid = (lo + hi + 1) >> 1;
+      if (scale16(span1, mid << sh) <= rem) lo = mid; else hi = mid - 1;
+    }
+    const uint32_t c1 = (lo + 1) << sh;
+    narrow(scale16(span1, lo << sh), (c1 >> 16) ? span1 : scale16(span1, c1) - 1u);
+    return lo;
+  }
+};
+
+// Out-of-line general symbol: binary search over the staged row, then the escape tail
+// (unbounded_index_range_coding_kernels.cc:336-360).  Returns the value before the row offset.
+__device__ __forceinline__ int32_t decode_general(DecState& d, const Tables& tb, int start,
+                                                  int len, int ow, int max_digits) {
+  int lo = 1, hi = len - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    const uint32_t c = tb.at(start + mid);
+    if ((c >> 16) != 0 || scale16(d.span1, c) > d.rem) hi = mid; else lo = mid + 1;
+  }
+  const uint32_t c1 = tb.at(start + lo);
+  if ((c1 >> 16) == 0 && scale16(d.span1, c1) <= d.rem) d.corrupt = true;  // ran past the row
+  d.narrow(scale16(d.span1, tb.at(start + lo - 1)),
+           (c1 >> 16) ? d.span1 : scale16(d.span1, c1) - 1u);
+  int32_t v = lo - 1;
+  if (v == len - 2) {
+    const uint32_t all1 = (1u << ow) - 1u;
+    const int sh = 16 - ow;
+    int nd = 0, guard = 0;
+    (void)guard;
+    uint32_t u;
+    do { u = d.digit(sh, all1); nd += (int)u; ++guard; } while (u == all1 && nd <= max_digits);
+    if (nd > max_digits) { d.corrupt = true; nd = max_digits; }
+    uint32_t x = 0;
+    for (int q = 0; q < nd; ++q) {
+      const uint32_t dg = d.digit(sh, all1);
+      if (q * ow < 32) x |= dg << (q * ow);
+    }
+    v = (x & 1u) ? -(int32_t)(x >> 1) - 1 : (int32_t)(x >> 1) + v;
+  }
+  return v;
+}
+
+struct DecParamsV4 {
+  const uint8_t* enc;
+  int64_t cap;
+  const int32_t* nbytes;
+  const int32_t* index;
+  int64_t index_stride;
+  const int32_t* cdf;
+  const int32_t* cdf_size;
+  const int32_t* offset;
+  int32_t rows, cols;
+  int32_t precision, overflow_width;
+  int32_t* out;
+  int32_t* status;
+  int64_t S, n;
+  int32_t round;          // symbols per round (multiple of 32, <= kRoundMax)
+  int32_t max_digits;     // bound on the escape digits of one symbol
+  int32_t round_words;    // bound on the stream words one round can consume
+  int32_t table_bytes;    // shared-memory budget of the staged tables (16-byte multiple)
+  int32_t streams_per_cta;
+};
+
+constexpr int kRecPad = 8;     // the chain prefetches records up to 7 past the round's end
+constexpr int kLinMax = 4608;  // words of one linear stream window (>= 2 * round words + 8)
+
+__host__ __device__ inline size_t dec_pair_bytes() {
+  return (size_t)2 * (kRoundMax + kRecPad) * 16   // records
+         + (size_t)2 * kRoundMax * 4              // values decoded by the general path
+         + (size_t)2 * kRoundMax                  // one code byte per symbol
+         + (size_t)2 * kLinMax * 2 + 16;          // two linear stream windows, ctrl
+}
+
+// Stream words reach the chain through per-round LINEAR windows (no index masking on the
+// chain): the window of round r+1 is filled while round r runs and starts at the stream
+// position round r started at (the only position known by then); a round consumes at most
+// p.round_words words, so 2 * round_words + 8 words cover every position round r+1 can need.
+__global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 p) {
+  Tables t;
+  stage_tables_v4(p.cdf, p.rows, p.cols, p.cdf_size, p.offset, p.precision, smem_v4,
+                  p.table_bytes, &t);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int spc = p.streams_per_cta;       // warps [0, spc): chains, [spc, 2 spc): helpers
+  const bool helper = warp >= spc;
+  const int pair = helper ? warp - spc : warp;
+  const int64_t s = (int64_t)blockIdx.x * p.streams_per_cta + pair;
+  if (s >= p.S) return;
+  uint8_t* mine = smem_v4 + p.table_bytes + (size_t)pair * dec_pair_bytes();
+  uint4* recs = reinterpret_cast<uint4*>(mine);                      // [2][kRoundMax + kRecPad]
+  int32_t* vals = reinterpret_cast<int32_t*>(recs + 2 * (kRoundMax + kRecPad));  // [2][kRoundMax]
+  uint8_t* codes = reinterpret_cast<uint8_t*>(vals + 2 * kRoundMax);             // [2][kRoundMax]
+  uint16_t* lin = reinterpret_cast<uint16_t*>(codes + 2 * kRoundMax);            // [2][kLinMax]
+  volatile uint32_t* ctrl = reinterpret_cast<volatile uint32_t*>(lin + 2 * kLinMax);
+  // ctrl[r & 1]: stream position (in words) at which round r starts
+  const int bar = 1 + pair;
+  const int R = p.round;
+  const uint32_t win = 2u * (uint32_t)p.round_words + 8u;    // <= kLinMax
+  const int64_t rounds = (p.n + R - 1) / R;
+  const int32_t* idx = p.index + s * p.index_stride;
+
+  if (helper) {
+    const uint8_t* src = p.enc + s * p.cap;
+    const uint32_t len = (uint32_t)max(p.nbytes[s], 0);
+    const bool even = (reinterpret_cast<uintptr_t>(src) & 1) == 0;
+    int32_t* out = p.out + s * p.n;
+    auto fill = [&](uint16_t* dst, uint32_t first) {   // dst[k] = stream word first + k
+#pragma unroll 4
+      for (uint32_t k = lane; k < win; k += 32) {
+        const uint32_t at = 2u * (first + k);
+        uint32_t v = 0;
+        if (even && at + 1 < len) {
+          const uint32_t h = __ldg(reinterpret_cast<const uint16_t*>(src + at));
+          v = __byte_perm(h, 0, 0x4401);
+        } else {
+          if (at < len) v = (uint32_t)__ldg(src + at) << 8;
+          if (at + 1 < len) v |= (uint32_t)__ldg(src + at + 1);
+        }
+        dst[k] = (uint16_t)v;
+      }
+    };
+    auto build = [&](int64_t r) {
+      const int64_t base = r * R;
+      const int cnt = (int)min((int64_t)R, p.n - base);
+      uint4* dst = recs + (r & 1) * (kRoundMax + kRecPad);
+#pragma unroll 4
+      for (int j = lane; j < cnt; j += 32) dst[j] = t.rowrec[__ldg(idx + base + j)];
+    };
+    auto flush = [&](int64_t r) {
+      const int64_t base = r * R;
+      const int cnt = (int)min((int64_t)R, p.n - base);
+      const int32_t* ev = vals + (r & 1) * kRoundMax;
+      const uint8_t* cb = codes + (r & 1) * kRoundMax;
+#pragma unroll 4
+      for (int j = lane; j < cnt; j += 32) {
+        const int32_t off = t.rowinfo[__ldg(idx + base + j)].z;
+        const uint32_t c = cb[j];
+        out[base + j] = (c == 0xFFu ? ev[j] : (int32_t)c) + off;
+      }
+    };
+    fill(lin, 0);
+    build(0);
+    pair_barrier(bar);
+    for (int64_t r = 0; r < rounds; ++r) {
+      // the chain is working on round r: prepare r+1, flush r-1
+      const uint32_t pos = ctrl[r & 1];
+      if (r + 1 < rounds) {
+        build(r + 1);
+        fill(lin + ((r + 1) & 1) * kLinMax, pos);
+      }
+      if (r > 0) flush(r - 1);
+      pair_barrier(bar);
+    }
+    flush(rounds - 1);
+    return;
+  }
+
+  // ---- the chain (state replicated in every lane of this warp) ----
+  if (lane == 0) ctrl[0] = 2;
+  pair_barrier(bar);
+  DecState d;
+  d.corrupt = false;
+  // fast-path state: span modulo 2^32 (0 stands for 2^32 and always takes the general path);
+  // `wa` is the shared-space address of the word after w0
+  const uint32_t lin_s = (uint32_t)__cvta_generic_to_shared(lin);
+  auto lds16 = [](uint32_t a) {
+    uint16_t v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a));
+    return (uint32_t)v;
+  };
+  uint32_t rem = (lds16(lin_s) << 16) | lds16(lin_s + 2), span = 0;
+  uint32_t w0 = lds16(lin_s + 4), wa = lin_s + 6;
+  uint32_t win_first = 0;      // stream position of the current window's word 0
+  uint32_t p_cur = 2;          // stream position of w0 at the start of the current round
+  const int ow = p.overflow_width;
+  for (int64_t r = 0; r < rounds; ++r) {
+    const int cnt = (int)min((int64_t)R, p.n - r * R);
+    const uint4* rc = recs + (r & 1) * (kRoundMax + kRecPad);
+    int32_t* ev = vals + (r & 1) * kRoundMax;
+    uint8_t* cb = codes + (r & 1) * kRoundMax;
+    const uint32_t lin_r = lin_s + (uint32_t)(r & 1) * (kLinMax * 2);
+
+    // One symbol of a 5-entry row: three multiplies, compares and selects, no branch.  `ok`
+    // goes (and stays) false when a symbol needs the general path — escape, any other row
+    // (c3' == 0), or span == 2^32; the group is then replayed one symbol at a time.
+    auto step = [&](const uint4& q, uint8_t* dst, bool& ok) {
+      const uint32_t t3 = __umulhi(span, q.z);
+      const uint32_t t1 = __umulhi(span, q.x);
+      const uint32_t t2 = __umulhi(span, q.y);
+      ok = ok && (t3 > rem);
+      const bool p1 = t1 <= rem, p2 = t2 <= rem;
+      const uint32_t a = p2 ? t2 : (p1 ? t1 : 0u);
+      const uint32_t hi = p2 ? t3 : (p1 ? t2 : t1);
+      rem -= a;
+      span = hi - a;
+      *dst = (uint8_t)(p2 ? 2 : (p1 ? 1 : 0));
+      if (span <= 65536u) {
+        span <<= 16;
+        rem = rem * 65536u + w0;
+        w0 = lds16(wa);
+        wa += 2;
+      }
+    };
+
+    int j = 0;
+    const uint4* rp = rc;
+    uint8_t* cp = cb;
+    while (j < cnt) {
+      if (j + 4 <= cnt) {
+        uint4 q0 = rp[0], q1 = rp[1], q2 = rp[2], q3 = rp[3];
+        bool ok = true;
+        uint32_t s_rem, s_span, s_w0, s_wa;
+        do {
+          s_rem = rem; s_span = span; s_w0 = w0; s_wa = wa;
+          step(q0, cp, ok);     q0 = rp[4];
+          step(q1, cp + 1, ok); q1 = rp[5];
+          step(q2, cp + 2, ok); q2 = rp[6];
+          step(q3, cp + 3, ok); q3 = rp[7];
+          if (!ok) break;
+          j += 4; rp += 4; cp += 4;
+        } while (j + 4 <= cnt);
+        if (ok) continue;
+        rem = s_rem; span = s_span; w0 = s_w0; wa = s_wa;   // replay this group carefully
+      }
+      const int stop = min(j + 4, cnt);
+      for (; j < stop; ++j, ++rp, ++cp) {
+        const uint4 q = rp[0];
+        bool ok = true;
+        const uint32_t k_rem = rem, k_span = span, k_w0 = w0, k_wa = wa;
+        step(q, cp, ok);
+        if (ok) continue;
+        // general path for symbol j
+        const int4 ri = t.rowinfo[q.w];
+        d.rem = k_rem; d.span1 = k_span - 1u; d.w0 = k_w0; d.wa = k_wa;
+        const int32_t v = decode_general(d, t, ri.x, ri.y, ow, p.max_digits);
+        rem = d.rem; span = d.span1 + 1u; w0 = d.w0; wa = d.wa;
+        ev[j] = v;
+        *cp = 0xFF;
+      }
+    }
+    // P_{r+1}: stream position of w0; the next window starts at P_r (see the kernel comment)
+    const uint32_t p_next = win_first + (wa - lin_r) / 2u - 1u;
+    if (lane == 0) ctrl[(r + 1) & 1] = p_next;
+    pair_barrier(bar);
+    const uint32_t lin_n = lin_s + (uint32_t)((r + 1) & 1) * (kLinMax * 2);
+    wa = lin_n + 2u * (p_next + 1u - p_cur);
+    win_first = p_cur;
+    p_cur = p_next;
+  }
+  if (lane == 0 && p.status) p.status[s] = d.corrupt ? TFC_STREAM_CORRUPT : TFC_STREAM_OK;
+}
+
+
+// ------------------------------------------------------------------------------------------
+// encode
+// ------------------------------------------------------------------------------------------
+// One CTA (3 warps) per stream, three pipeline stages one round apart:
+//   warp 2  stager : symbols + indexes -> "puts" {c0, c1} at precision 16 (escape tails expanded,
+//                    warp scan for the positions); nothing here depends on the coder state;
+//   warp 0  span   : the only truly serial recurrence, span' = f(span, c0, c1): two multiplies,
+//                    a subtract, a compare and a select per put; emits a = floor(span*c0/2^16)
+//                    and the renormalisation flag;
+//   warp 1  low    : lo += a with immediate carry propagation into the words already produced
+//                    (the reference delays the carry, range_coder.cc:169-265; the bytes are the
+//                    same big-number sum), one 16-bit word per flag; flushes coalesced.
+constexpr int kPutCap = 2048;          // puts per round (upper bound)
+
+struct EncParamsV4 {
+  const int32_t* data;
+  const int32_t* index;
+  int64_t index_stride;
+  const int32_t* cdf;
+  const int32_t* cdf_size;
+  const int32_t* offset;
+  int32_t rows, cols;
+  int32_t precision, overflow_width;
+  uint8_t* out;
+  int64_t cap;
+  int32_t* nbytes;
+  int32_t* status;
+  int64_t S, n;
+  int32_t round;          // symbols per round: round * max_puts <= kPutCap, multiple of 32
+  int32_t table_bytes;
+};
+
+__host__ __device__ inline size_t enc_bytes() {
+  return (size_t)2 * kPutCap * 8      // puts
+         + (size_t)2 * kPutCap * 4    // a values
+         + (size_t)2 * (kPutCap / 32) * 4  // flags
+         + (size_t)kPutCap * 2        // words of one round
+         + 64;                        // counts[4], span, ...
+}
+
+__device__ __forceinline__ void put_byte(uint8_t* out, uint32_t cap, uint32_t at, uint32_t b) {
+  if (at < cap) out[at] = (uint8_t)b;
+}
+
+__global__ void __launch_bounds__(96) encode_unbounded_v4(const EncParamsV4 p) {
+  Tables t;
+  stage_tables_v4(p.cdf, p.rows, p.cols, p.cdf_size, p.offset, p.precision, smem_v4,
+                  p.table_bytes, &t);
+  uint8_t* mine = smem_v4 + p.table_bytes;
+  uint2* puts = reinterpret_cast<uint2*>(mine);                                  // [2][kPutCap]
+  uint32_t* avals = reinterpret_cast<uint32_t*>(mine + 2 * kPutCap * 8);         // [2][kPutCap]
+  uint32_t* flags = avals + 2 * kPutCap;                                         // [2][kPutCap/32]
+  uint16_t* words = reinterpret_cast<uint16_t*>(flags + 2 * (kPutCap / 32));     // [kPutCap]
+  volatile uint32_t* counts = reinterpret_cast<volatile uint32_t*>(words + kPutCap);  // [4]
+  volatile uint32_t* fin = counts + 4;                                           // final span1
+
+  const int64_t s = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int R = p.round;
+  const int64_t rounds = (p.n + R - 1) / R;
+  const int32_t* idx = p.index + s * p.index_stride;
+  const int32_t* data = p.data + s * p.n;
+  uint8_t* out = p.out + s * p.cap;
+  const uint32_t cap = (uint32_t)p.cap;
+  const int ow = p.overflow_width;
+  const uint32_t all1 = (1u << ow) - 1u;
+  const int dsh = 16 - ow;
+
+  uint32_t span1 = 0xFFFFFFFFu;          // warp 0
+  uint32_t lo = 0, total = 0;            // warp 1: low word, words flushed so far
+
+  for (int64_t r = 0; r < rounds + 2; ++r) {
+    if (warp == 2) {
+      if (r < rounds) {
+        // ---- stager ----
+        const int64_t base = r * R;
+        const int cnt = (int)min((int64_t)R, p.n - base);
+        uint2* dst = puts + (r & 1) * kPutCap;
+        uint32_t fill = 0;
+        for (int j0 = 0; j0 < cnt; j0 += 32) {
+          const int j = j0 + lane;
+          uint32_t c0 = 0, c1 = 0, x = 0;
+          int np = 0, nd = 0;
+          if (j < cnt) {
+            const int4 ri = t.rowinfo[__ldg(idx + base + j)];
+            const int32_t top = ri.y - 2;
+            int32_t v = __ldg(data + base + j) - ri.z;
+            np = 1;
+            bool esc = false;
+            if (v < 0) { x = (uint32_t)(-2 * v - 1); v = top; esc = true; }
+            else if (v >= top) { x = (uint32_t)(2 * (v - top)); v = top; esc = true; }
+            c0 = t.at(ri.x + v);
+            c1 = t.at(ri.x + v + 1);
+            if (esc) {
+              while (nd * ow < 32 && (x >> (nd * ow)) != 0) ++nd;
+              np += (int)((uint32_t)nd / all1) + 1 + nd;
+            }
+          }
+          int incl = np;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const int u = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += u;
+          }
+          uint32_t at = fill + (uint32_t)(incl - np);
+          if (np > 0) {
+            dst[at++] = make_uint2(c0, c1);
+            if (np > 1) {
+              uint32_t u = (uint32_t)nd;
+              for (; u >= all1; u -= all1) dst[at++] = make_uint2(all1 << dsh, (all1 + 1u) << dsh);
+              dst[at++] = make_uint2(u << dsh, (u + 1u) << dsh);
+              for (int q = 0; q < nd; ++q) {
+                const uint32_t dg = (x >> (q * ow)) & all1;
+                dst[at++] = make_uint2(dg << dsh, (dg + 1u) << dsh);
+              }
+            }
+          }
+          fill += (uint32_t)__shfl_sync(0xFFFFFFFFu, incl, 31);
+        }
+        if (lane == 0) counts[r & 3] = fill;
+      }
+    } else if (warp == 0) {
+      if (r >= 1 && r <= rounds) {
+        // ---- span chain (replicated in all lanes; lane 0 stores) ----
+        const int64_t q = r - 1;
+        const uint32_t cnt = counts[q & 3];
+        const uint2* src = puts + (q & 1) * kPutCap;
+        uint32_t* av = avals + (q & 1) * kPutCap;
+        uint32_t* fl = flags + (q & 1) * (kPutCap / 32);
+        uint2 cur = src[0];
+        uint32_t fm = 0;
+#pragma unroll 1
+        for (uint32_t i = 0; i < cnt; ++i) {
+          const uint2 nxt = src[min(i + 1, (uint32_t)kPutCap - 1)];
+          const uint32_t a = scale16(span1, cur.x);
+          const uint32_t b1 = scale16(span1, cur.y);       // b + 1 (mod 2^32)
+          uint32_t ns = b1 - 1u - a;
+          const bool rn = (ns >> 16) == 0;
+          ns = rn ? ((ns << 16) | 0xFFFFu) : ns;
+          span1 = ns;
+          fm |= (rn ? 1u : 0u) << (i & 31);
+          av[i] = a;
+          if ((i & 31) == 31) { fl[i >> 5] = fm; fm = 0; }
+          cur = nxt;
+        }
+        if ((cnt & 31) != 0 && lane == 0) fl[cnt >> 5] = fm;
+        if (r == rounds && lane == 0) fin[0] = span1;
+      }
+    } else {
+      if (r >= 2) {
+        // ---- low chain + emission (replicated; lane 0 does the rare global fix-ups) ----
+        const int64_t q = r - 2;
+        const uint32_t cnt = counts[q & 3];
+        const uint32_t* av = avals + (q & 1) * kPutCap;
+        const uint32_t* fl = flags + (q & 1) * (kPutCap / 32);
+        uint32_t nw = 0;                   // words produced in this round
+        uint32_t fm = 0;
+        uint32_t a = av[0];
+#pragma unroll 1
+        for (uint32_t i = 0; i < cnt; ++i) {
+          const uint32_t an = av[min(i + 1, (uint32_t)kPutCap - 1)];
+          if ((i & 31) == 0) fm = fl[i >> 5];
+          lo += a;
+          if (lo < a) {
+            // carry out of the window: +1 into the words already produced
+            int32_t k = (int32_t)nw - 1;
+            bool carry = true;
+            __syncwarp();
+            while (carry && k >= 0) {
+              const uint32_t wv = (uint32_t)words[k] + 1u;
+              __syncwarp();
+              words[k] = (uint16_t)wv;
+              carry = (wv >> 16) != 0;
+              --k;
+            }
+            if (carry && lane == 0) {
+              int64_t g = (int64_t)total - 1;     // flushed words live in global memory
+              while (g >= 0) {
+                const uint32_t at = 2u * (uint32_t)g;
+                uint32_t wv = 0;
+                if (at < cap) wv = (uint32_t)out[at] << 8;
+                if (at + 1 < cap) wv |= out[at + 1];
+                wv += 1u;
+                put_byte(out, cap, at, (wv >> 8) & 0xFFu);
+                put_byte(out, cap, at + 1, wv & 0xFFu);
+                if ((wv >> 16) == 0) break;
+                --g;
+              }
+            }
+            __syncwarp();
+          }
+          if (fm & 1u) {
+            words[nw] = (uint16_t)(lo >> 16);
+            ++nw;
+            lo <<= 16;
+          }
+          fm >>= 1;
+          a = an;
+        }
+        __syncwarp();
+        for (uint32_t k = lane; k < nw; k += 32) {
+          const uint32_t wv = words[k];
+          put_byte(out, cap, 2u * (total + k), wv >> 8);
+          put_byte(out, cap, 2u * (total + k) + 1u, wv & 0xFFu);
+        }
+        total += nw;
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+  }
+
+  if (warp == 1) {
+    // Finalize (range_coder.cc:268-301)
+    __threadfence_block();
+    if (lane == 0) {
+      const uint32_t fs = fin[0];
+      uint32_t nbytes = 2u * total;
+      auto rd = [&](uint32_t g) {
+        const uint32_t at = 2u * g;
+        uint32_t wv = 0;
+        if (at < cap) wv = (uint32_t)out[at] << 8;
+        if (at + 1 < cap) wv |= out[at + 1];
+        return wv;
+      };
+      if (p.n > 0 && lo + fs < lo) {
+        // state 1: the pending word is the last one that is not 0xFFFF; it gets the carry and
+        // everything after it (zeros) is dropped
+        int64_t g = (int64_t)total - 1;
+        if (2u * total > cap) {
+          // the stream did not fit: the words are not all there to look at; report the size
+          // of the unfinalised stream (an upper bound) — the caller retries with more room
+          g = -1;
+        } else {
+          while (g >= 0 && rd((uint32_t)g) == 0xFFFFu) --g;
+        }
+        if (g >= 0) {
+          const uint32_t wv = rd((uint32_t)g) + 1u;
+          put_byte(out, cap, 2u * (uint32_t)g, (wv >> 8) & 0xFFu);
+          nbytes = 2u * (uint32_t)g + 1u;
+          if (wv & 0xFFu) { put_byte(out, cap, nbytes, wv & 0xFFu); ++nbytes; }
+        }
+      } else if (p.n > 0 && lo != 0) {
+        const uint32_t mid = ((lo - 1u) >> 16) + 1u;
+        put_byte(out, cap, nbytes, (mid >> 8) & 0xFFu);
+        ++nbytes;
+        if (mid & 0xFFu) { put_byte(out, cap, nbytes, mid & 0xFFu); ++nbytes; }
+      }
+      p.nbytes[s] = (int32_t)nbytes;
+      if (p.status) p.status[s] = (nbytes > cap || 2u * total > cap) ? TFC_STREAM_CAPACITY
+                                                                    : TFC_STREAM_OK;
+    }
+  }
+}
+
+}  // namespace v4

@@ -25,6 +25,7 @@ def main():
   ap.add_argument("--reps", type=int, default=5)
   ap.add_argument("--check", type=int, default=2)
   ap.add_argument("--sigma-scale", type=float, default=1.0)
+  ap.add_argument("--rows-max", type=int, default=40, help="indexes drawn from [0, rows-max)")
   ap.add_argument("--cpu", action="store_true", help="also time the CPU checker, all threads")
   args = ap.parse_args()
   from compression_b200.python.layers import entropy_models
@@ -37,7 +38,7 @@ def main():
   g = torch.Generator(device="cpu").manual_seed(1)
   S, n = args.streams, args.n
   # scales as a trained hyperprior produces them: mostly small, log-uniform over the low rows
-  idx = torch.randint(0, 40, (S, n), generator=g, dtype=torch.int32)
+  idx = torch.randint(0, args.rows_max, (S, n), generator=g, dtype=torch.int32)
   sig = torch.as_tensor(table, dtype=torch.float32)[idx.long()] * args.sigma_scale
   sym = torch.floor(torch.randn((S, n), generator=g) * sig + .5).to(torch.int32)
   idx_d, sym_d = idx.to(dev), sym.to(dev)
