@@ -81,11 +81,32 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
-template <bool GDN>
+__device__ __forceinline__ float rsqrt_approx(float x) {
+  float y;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float sqrt_approx(float x) {
+  float y;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+constexpr int kGdnSlot = 4;   // the GDN GEMM of tile i is issued before k-block 4 of tile i+1
+
+// MODE 0: bias (+ReLU).  MODE 1 / 2: GDN / IGDN with cout == 32 * NC.
+//
+// GDN pipeline (per CTA, tiles i = 0, 1, ...; two TMEM accumulators used alternately):
+//   MMA      : main(i) -> acc[i&1];   GEMM2(i-1) = x^2 * gamma -> acc[(i-1)&1] IN PLACE, slotted
+//              in before k-block kGdnSlot of main(i)
+//   epilogue : phase 1(i): x = D1 + bias kept as packed bf16 in registers, x^2 -> smem (K-major)
+//              phase 2(i): y = x * rsqrt(beta + D2)   (IGDN: * sqrt), overlapping main(i+1)
+template <int MODE, int NC>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
                  const __grid_constant__ CUtensorMap map_w,
                  const __grid_constant__ CUtensorMap map_g, const Params p) {
+  constexpr bool GDN = MODE != 0;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [stages x (A 16 KB | B npad*128 B)] [A2: cout/64 x 16 KB] [bias|beta] [barriers]
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -93,7 +114,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
   const int b_bytes = p.npad * kBlockK * 2;
   const int stage_bytes = kABytes + ((b_bytes + 1023) & ~1023);
   uint8_t* a2 = smem + kStages * stage_bytes;
-  const int gdn_kblocks = GDN ? p.cout / kBlockK : 0;
+  constexpr int gdn_kblocks = GDN ? NC / 2 : 0;
   float* s_bias = reinterpret_cast<float*>(a2 + gdn_kblocks * kABytes);
   float* s_beta = s_bias + 256;
   Barriers* bars = reinterpret_cast<Barriers*>(s_beta + 256);
@@ -138,13 +159,26 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
     // ===== TMA producer =====
     if (lane == 0) {
       int stage = 0;
-      uint32_t ph = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      uint32_t ph = 0, it = 0;
+      auto load_gamma = [&]() {
+        for (int kc = 0; kc < gdn_kblocks; ++kc) {
+          mbar_wait(&bars->empty[stage], ph ^ 1);
+          uint8_t* sa = smem + stage * stage_bytes;
+          mbar_expect_tx(&bars->full[stage], b_bytes);
+          tma_load_2d(sa + kABytes, &map_g, &bars->full[stage], kc * kBlockK, 0);
+          if (++stage == kStages) { stage = 0; ph ^= 1; }
+        }
+      };
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
         int phase, n, i0, j0;
         tile_coords(tile, phase, n, i0, j0);
+        const int nk = (p.phase_start[phase + 1] - p.phase_start[phase]) * kchunks;
+        const int slot = min(kGdnSlot, nk);
+        int kb = 0;
         for (int t = p.phase_start[phase]; t < p.phase_start[phase + 1]; ++t) {
           const Tap tap = p.taps[t];
-          for (int kc = 0; kc < kchunks; ++kc) {
+          for (int kc = 0; kc < kchunks; ++kc, ++kb) {
+            if (GDN && it > 0 && kb == slot) load_gamma();
             mbar_wait(&bars->empty[stage], ph ^ 1);
             uint8_t* sa = smem + stage * stage_bytes;
             mbar_expect_tx(&bars->full[stage], kABytes + b_bytes);
@@ -154,32 +188,45 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
             if (++stage == kStages) { stage = 0; ph ^= 1; }
           }
         }
-        if (GDN) {
-          for (int kc = 0; kc < gdn_kblocks; ++kc) {
-            mbar_wait(&bars->empty[stage], ph ^ 1);
-            uint8_t* sa = smem + stage * stage_bytes;
-            mbar_expect_tx(&bars->full[stage], b_bytes);
-            tma_load_2d(sa + kABytes, &map_g, &bars->full[stage], kc * kBlockK, 0);
-            if (++stage == kStages) { stage = 0; ph ^= 1; }
-          }
-        }
+        if (GDN && it > 0 && slot == nk) load_gamma();
       }
+      if (GDN && it > 0) load_gamma();
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
       int stage = 0;
       uint32_t ph = 0, it = 0;
+      // GEMM2 of tile j: acc[j & 1] = x^2 (smem a2) * gamma, overwriting D1 (already consumed)
+      auto issue_gdn = [&](uint32_t j) {
+        mbar_wait(&bars->a2_full, j & 1);
+        tc_fence_after();
+        const uint32_t d2 = tmem + (j & 1) * 256;
+        for (int kc = 0; kc < gdn_kblocks; ++kc) {
+          mbar_wait(&bars->full[stage], ph);
+          tc_fence_after();
+          const uint32_t sb = smem_u32(smem + stage * stage_bytes) + kABytes;
+          const uint64_t da = make_desc_sw128(smem_u32(a2 + kc * kABytes));
+          const uint64_t db = make_desc_sw128(sb);
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k)
+            umma_bf16(d2, da + (k * 2), db + (k * 2), idesc, (kc | k) != 0);
+          umma_commit(&bars->empty[stage]);
+          if (++stage == kStages) { stage = 0; ph ^= 1; }
+        }
+        umma_commit(&bars->d2_full);
+      };
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
         int phase, n, i0, j0;
         tile_coords(tile, phase, n, i0, j0);
-        const int acc = GDN ? 0 : (it & 1);
-        const uint32_t use = GDN ? it : (it >> 1);       // how often this accumulator was used
-        mbar_wait(&bars->d1_empty[acc], (use & 1) ^ 1);
+        const int acc = it & 1;
+        mbar_wait(&bars->d1_empty[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d1 = tmem + acc * 256;
         const int nk = (p.phase_start[phase + 1] - p.phase_start[phase]) * kchunks;
+        const int slot = min(kGdnSlot, nk);
         for (int kb = 0; kb < nk; ++kb) {
+          if (GDN && it > 0 && kb == slot) issue_gdn(it - 1);
           mbar_wait(&bars->full[stage], ph);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + stage * stage_bytes);
@@ -190,26 +237,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
           umma_commit(&bars->empty[stage]);
           if (++stage == kStages) { stage = 0; ph ^= 1; }
         }
+        if (GDN && it > 0 && slot == nk) issue_gdn(it - 1);
         umma_commit(&bars->d1_full[acc]);
-        if (GDN) {
-          mbar_wait(&bars->a2_full, it & 1);
-          tc_fence_after();
-          const uint32_t d2 = tmem + 256;
-          for (int kc = 0; kc < gdn_kblocks; ++kc) {
-            mbar_wait(&bars->full[stage], ph);
-            tc_fence_after();
-            const uint32_t sb = smem_u32(smem + stage * stage_bytes) + kABytes;
-            const uint64_t da = make_desc_sw128(smem_u32(a2 + kc * kABytes));
-            const uint64_t db = make_desc_sw128(sb);
-#pragma unroll
-            for (int k = 0; k < kBlockK / 16; ++k)
-              umma_bf16(d2, da + (k * 2), db + (k * 2), idesc, (kc | k) != 0);
-            umma_commit(&bars->empty[stage]);
-            if (++stage == kStages) { stage = 0; ph ^= 1; }
-          }
-          umma_commit(&bars->d2_full);
-        }
       }
+      if (GDN && it > 0) issue_gdn(it - 1);
     }
   } else {
     // ===== epilogue: 4 warps, thread <-> TMEM lane <-> tile pixel =====
@@ -217,84 +248,131 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
     const int r = quad * 32 + lane;                  // pixel within the tile / TMEM lane
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     uint32_t it = 0;
+    uint32_t xs[GDN ? NC * 16 : 1];                  // x = D1 + bias as packed bf16 pairs
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
       int phase, n, i0, j0;
       tile_coords(tile, phase, n, i0, j0);
-      const int acc = GDN ? 0 : (it & 1);
-      const uint32_t use = GDN ? it : (it >> 1);
+      const int acc = it & 1;
       const int li = r / p.tw, lj = r - li * p.tw;
       const int i2 = i0 + li, j2 = j0 + lj;
       const bool valid = i2 < p.hs && j2 < p.ws;
       const int pi = phase / p.su, pj = phase - pi * p.su;
       const int64_t pix = ((int64_t)n * p.ho + (i2 * p.su + pi)) * p.wo + (j2 * p.su + pj);
-      const uint32_t d1 = tmem + acc * 256 + lane_addr;
-      mbar_wait(&bars->d1_full[acc], use & 1);
+      const uint32_t dacc = tmem + acc * 256 + lane_addr;
+      mbar_wait(&bars->d1_full[acc], (it >> 1) & 1);
       tc_fence_after();
-      if (GDN) {
-        // phase 1: x^2 -> bf16 K-major SW128 tile(s) in shared memory
-        for (int c0 = 0; c0 < p.cout; c0 += 32) {
+      if constexpr (GDN) {
+        // phase 1: x -> registers (bf16), x^2 -> bf16 K-major SW128 tile(s) in shared memory
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
           uint32_t v[32];
-          tmem_ld_32x32(d1 + c0, v);
+          tmem_ld_32x32(dacc + c * 32, v);
           tmem_ld_wait();
-          uint8_t* row = a2 + (c0 / kBlockK) * kABytes + r * 128;
-          const int chunk0 = (c0 % kBlockK) / 8;
+          uint8_t* row = a2 + (c >> 1) * kABytes + r * 128;
+          const float4* bs = reinterpret_cast<const float4*>(s_bias + c * 32);
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
-            uint32_t w[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float x0 = __uint_as_float(v[q * 8 + 2 * e]) + s_bias[c0 + q * 8 + 2 * e];
-              const float x1 = __uint_as_float(v[q * 8 + 2 * e + 1]) + s_bias[c0 + q * 8 + 2 * e + 1];
-              w[e] = pack_bf16(x0 * x0, x1 * x1);
-            }
-            const int phys = (chunk0 + q) ^ (r & 7);
-            *reinterpret_cast<uint4*>(row + phys * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+            const float4 b0 = bs[2 * q], b1 = bs[2 * q + 1];
+            const float x0 = __uint_as_float(v[8 * q + 0]) + b0.x;
+            const float x1 = __uint_as_float(v[8 * q + 1]) + b0.y;
+            const float x2 = __uint_as_float(v[8 * q + 2]) + b0.z;
+            const float x3 = __uint_as_float(v[8 * q + 3]) + b0.w;
+            const float x4 = __uint_as_float(v[8 * q + 4]) + b1.x;
+            const float x5 = __uint_as_float(v[8 * q + 5]) + b1.y;
+            const float x6 = __uint_as_float(v[8 * q + 6]) + b1.z;
+            const float x7 = __uint_as_float(v[8 * q + 7]) + b1.w;
+            xs[c * 16 + 4 * q + 0] = pack_bf16(x0, x1);
+            xs[c * 16 + 4 * q + 1] = pack_bf16(x2, x3);
+            xs[c * 16 + 4 * q + 2] = pack_bf16(x4, x5);
+            xs[c * 16 + 4 * q + 3] = pack_bf16(x6, x7);
+            const int physc = ((c & 1) * 4 + q) ^ (r & 7);
+            *reinterpret_cast<uint4*>(row + physc * 16) =
+                make_uint4(pack_bf16(x0 * x0, x1 * x1), pack_bf16(x2 * x2, x3 * x3),
+                           pack_bf16(x4 * x4, x5 * x5), pack_bf16(x6 * x6, x7 * x7));
           }
         }
+        tc_fence_before();
         fence_proxy_async_smem();
         mbar_arrive(&bars->a2_full);
         mbar_wait(&bars->d2_full, it & 1);
         tc_fence_after();
-      }
-      const uint32_t d2 = tmem + 256 + lane_addr;
-      for (int c0 = 0; c0 < p.npad; c0 += 32) {
-        uint32_t v[32], g[32];
-        tmem_ld_32x32(d1 + c0, v);
-        if (GDN) tmem_ld_32x32(d2 + c0, g);
-        tmem_ld_wait();
-        float y[32];
+        // phase 2: y = x * rsqrt(beta + D2)  (IGDN: x * sqrt)
 #pragma unroll
-        for (int e = 0; e < 32; ++e) {
-          float x = __uint_as_float(v[e]) + s_bias[c0 + e];
-          if (GDN) {
-            const float nrm = __uint_as_float(g[e]) + s_beta[c0 + e];
-            x *= (p.act == TFC_ACT_IGDN) ? sqrtf(nrm) : rsqrtf(nrm);
-          } else if (p.act == TFC_ACT_RELU) {
-            x = fmaxf(x, 0.f);
+        for (int c = 0; c < NC; ++c) {
+          uint32_t g[32];
+          tmem_ld_32x32(dacc + c * 32, g);
+          tmem_ld_wait();
+          const float4* be = reinterpret_cast<const float4*>(s_beta + c * 32);
+          float y[32];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 b4 = be[q];
+            const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const uint32_t pr = xs[c * 16 + 2 * q + (e >> 1)];
+              const float x = __uint_as_float((e & 1) ? (pr & 0xFFFF0000u) : (pr << 16));
+              const float nrm = __uint_as_float(g[4 * q + e]) + bb[e];
+              y[4 * q + e] = x * (MODE == 2 ? sqrt_approx(nrm) : rsqrt_approx(nrm));
+            }
           }
-          y[e] = x;
-        }
-        if (valid) {
-          const int nvalid = min(32, p.cout - c0);
-          if (nvalid == 32 && (p.cout & 7) == 0) {
+          if (valid) {
             if (p.out_f32) {
-              float4* dst = reinterpret_cast<float4*>(static_cast<float*>(p.out) + pix * p.cout + c0);
+              float4* dst = reinterpret_cast<float4*>(static_cast<float*>(p.out) + pix * p.cout + c * 32);
 #pragma unroll
               for (int q = 0; q < 8; ++q)
                 dst[q] = make_float4(y[4 * q], y[4 * q + 1], y[4 * q + 2], y[4 * q + 3]);
             } else {
-              uint4* dst = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + pix * p.cout + c0);
+              uint4* dst = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + pix * p.cout + c * 32);
 #pragma unroll
               for (int q = 0; q < 4; ++q)
                 dst[q] = make_uint4(pack_bf16(y[8 * q], y[8 * q + 1]), pack_bf16(y[8 * q + 2], y[8 * q + 3]),
                                     pack_bf16(y[8 * q + 4], y[8 * q + 5]), pack_bf16(y[8 * q + 6], y[8 * q + 7]));
             }
-          } else {
+          }
+        }
+      } else {
+        const bool relu = p.act == TFC_ACT_RELU;
+        for (int c0 = 0; c0 < p.npad; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(dacc + c0, v);
+          tmem_ld_wait();
+          const float4* bs = reinterpret_cast<const float4*>(s_bias + c0);
+          float y[32];
 #pragma unroll
-            for (int e = 0; e < 32; ++e) {
-              if (e < nvalid) {
-                if (p.out_f32) static_cast<float*>(p.out)[pix * p.cout + c0 + e] = y[e];
-                else static_cast<__nv_bfloat16*>(p.out)[pix * p.cout + c0 + e] = __float2bfloat16_rn(y[e]);
+          for (int q = 0; q < 8; ++q) {
+            const float4 b4 = bs[q];
+            y[4 * q + 0] = __uint_as_float(v[4 * q + 0]) + b4.x;
+            y[4 * q + 1] = __uint_as_float(v[4 * q + 1]) + b4.y;
+            y[4 * q + 2] = __uint_as_float(v[4 * q + 2]) + b4.z;
+            y[4 * q + 3] = __uint_as_float(v[4 * q + 3]) + b4.w;
+          }
+          if (relu) {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) y[e] = fmaxf(y[e], 0.f);
+          }
+          if (valid) {
+            const int nvalid = min(32, p.cout - c0);
+            if (nvalid == 32 && (p.cout & 7) == 0) {
+              if (p.out_f32) {
+                float4* dst = reinterpret_cast<float4*>(static_cast<float*>(p.out) + pix * p.cout + c0);
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                  dst[q] = make_float4(y[4 * q], y[4 * q + 1], y[4 * q + 2], y[4 * q + 3]);
+              } else {
+                uint4* dst = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + pix * p.cout + c0);
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                  dst[q] = make_uint4(pack_bf16(y[8 * q], y[8 * q + 1]), pack_bf16(y[8 * q + 2], y[8 * q + 3]),
+                                      pack_bf16(y[8 * q + 4], y[8 * q + 5]), pack_bf16(y[8 * q + 6], y[8 * q + 7]));
+              }
+            } else {
+#pragma unroll
+              for (int e = 0; e < 32; ++e) {
+                if (e < nvalid) {
+                  if (p.out_f32) static_cast<float*>(p.out)[pix * p.cout + c0 + e] = y[e];
+                  else static_cast<__nv_bfloat16*>(p.out)[pix * p.cout + c0 + e] = __float2bfloat16_rn(y[e]);
+                }
               }
             }
           }
@@ -504,15 +582,21 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
   }
   const size_t smem = smem_bytes(p.npad, d.cout, gdn);
   const int grid = std::min(p.num_tiles, num_sms());
-  if (gdn) {
-    TFC_CUDA(cudaFuncSetAttribute(conv_umma_kernel<true>,
-                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    conv_umma_kernel<true><<<grid, kThreads, smem, st>>>(map_a, map_w, map_g, p);
+  void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const Params) = nullptr;
+  if (!gdn) {
+    kern = conv_umma_kernel<0, 0>;
   } else {
-    TFC_CUDA(cudaFuncSetAttribute(conv_umma_kernel<false>,
-                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    conv_umma_kernel<false><<<grid, kThreads, smem, st>>>(map_a, map_w, map_g, p);
+    const bool inv = d.act == TFC_ACT_IGDN;
+    switch (d.cout / 32) {
+      case 2: kern = inv ? conv_umma_kernel<2, 2> : conv_umma_kernel<1, 2>; break;
+      case 4: kern = inv ? conv_umma_kernel<2, 4> : conv_umma_kernel<1, 4>; break;
+      case 6: kern = inv ? conv_umma_kernel<2, 6> : conv_umma_kernel<1, 6>; break;
+      case 8: kern = inv ? conv_umma_kernel<2, 8> : conv_umma_kernel<1, 8>; break;
+      default: return fail(TFC_ERR_UNIMPLEMENTED, "GDN needs cout in {64, 128, 192, 256}");
+    }
   }
+  TFC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<grid, kThreads, smem, st>>>(map_a, map_w, map_g, p);
   TFC_LAUNCHED("conv_umma_kernel");
   return TFC_OK;
 }
