@@ -1,5 +1,6 @@
 // Internal interfaces between the conv dispatcher (conv_api.cu) and its implementations.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stddef.h>
 #include <stdint.h>
@@ -23,6 +24,17 @@ size_t conv_umma_workspace(const tfc_conv_desc& d);
 int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const float* bias,
               const float* beta, const float* gamma, void* out, void* ws, size_t ws_bytes,
               cudaStream_t st);
+
+// SWIZZLE_128B bf16 tiled tensor map (cuTensorMapEncodeTiled through the runtime's driver
+// entry point); defined in conv_umma.cu
+int make_tensor_map_bf16(CUtensorMap* m, void* base, int rank, const cuuint64_t* dims,
+                         const cuuint64_t* strides_bytes, const cuuint32_t* box);
+
+// thin-output transposed layers as a scatter GEMM (conv_upthin.cu)
+bool conv_upthin_supported(const tfc_conv_desc& d, const char** why);
+size_t conv_upthin_workspace(const tfc_conv_desc& d);
+int conv_upthin(const tfc_conv_desc& d, const void* in, const float* w, const float* bias,
+                void* out, void* ws, size_t ws_bytes, cudaStream_t st);
 
 // thin-input layers via space-to-depth + conv_umma (conv_s2d.cu)
 bool conv_s2d_supported(const tfc_conv_desc& d, const char** why);

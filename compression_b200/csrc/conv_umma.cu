@@ -491,6 +491,11 @@ size_t smem_bytes(int npad, int cout, bool gdn) {
 
 namespace tfc {
 
+int make_tensor_map_bf16(CUtensorMap* m, void* base, int rank, const cuuint64_t* dims,
+                         const cuuint64_t* strides_bytes, const cuuint32_t* box) {
+  return make_map(m, base, rank, dims, strides_bytes, box);
+}
+
 bool conv_umma_supported(const tfc_conv_desc& d, const char** why) {
   const char* dummy;
   if (!why) why = &dummy;

@@ -320,6 +320,46 @@ def test_umma_unsupported_shape_reports(tfc):
     layer(x)
 
 
+UPTHIN_CASES = [
+    # cin, cout, kernel, su, H, W, act, out dtype
+    (192, 3, 5, 2, 16, 24, None, torch.float32),
+    (192, 3, 5, 2, 13, 31, "relu", torch.float32),     # ragged: tiles overshoot the image
+    (128, 3, 5, 2, 6, 14, None, torch.bfloat16),       # exactly one interior tile
+    (64, 1, 3, 2, 9, 9, None, torch.float32),
+    (192, 4, 5, 2, 20, 33, None, torch.float32),
+    (256, 2, 7, 2, 11, 17, None, torch.float32),       # 7*7*2 = 98 accumulator columns
+]
+
+
+@pytest.mark.parametrize("cin,cout,k,su,H,W,act,out_dtype", UPTHIN_CASES)
+def test_thin_output_transposed_conv_scatter_gemm(tfc, cin, cout, k, su, H, W, act, out_dtype):
+  """Last synthesis layer (192 -> 3, 5x5 up 2; signal_conv.py:629-707) on the scatter-GEMM
+  kernel (impl=3), against the float64 oracle and against the implicit-GEMM kernel."""
+  rng = np.random.default_rng(12)
+  x = rng.integers(-4, 5, size=(3, H, W, cin)).astype(np.float32)
+  kern = (rng.integers(-8, 9, size=(k, k, cin, cout)) / 8.0).astype(np.float32)
+  b = (rng.integers(-8, 9, size=cout) / 4.0).astype(np.float32)
+  outs = {}
+  for impl in (3, 2):
+    layer = tfc.SignalConv2D(cout, (k, k), corr=False, strides_up=su, padding="same_zeros",
+                             use_bias=True, activation=torch.relu if act == "relu" else None,
+                             kernel_parameterizer=None, kernel_initializer=_static(kern),
+                             bias_initializer=_static(b), impl=impl)
+    layer.build(cin, "cuda")
+    outs[impl] = layer(torch.from_numpy(x).cuda().to(torch.bfloat16), out_dtype=out_dtype)
+    assert outs[impl].dtype == out_dtype
+  want = tfc_np.signal_conv2d(x, kern, b, False, 1, su, "same_zeros")
+  if act == "relu":
+    want = torch.relu(want)
+  want = want.numpy()
+  got = outs[3].float().cpu().numpy()
+  assert got.shape == want.shape
+  scale = np.abs(want).max() + 1e-6
+  tol = 1e-2 if out_dtype == torch.bfloat16 else 1e-5
+  assert np.abs(got - want).max() / scale <= tol
+  assert np.abs(got - outs[2].float().cpu().numpy()).max() / scale <= tol
+
+
 S2D_CASES = [
     # cin, cout, kernel, sd, H, W, act, input dtype
     (3, 192, 5, 2, 32, 48, "gdn", torch.float32),
