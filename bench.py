@@ -49,6 +49,11 @@ def parse_args():
   ap.add_argument("--cpu-sample-images", type=int, default=1)
   ap.add_argument("--no-cpu-baseline", action="store_true")
   ap.add_argument("--verbose", action="store_true", help="stage/layer breakdown on stderr")
+  ap.add_argument("--depth", type=int, default=3,
+                  help="batches in flight on separate CUDA streams (1: strictly serial steps)")
+  ap.add_argument("--coder-sms", type=int, default=32,
+                  help="SMs the transform kernels leave to the range coder when depth > 1")
+  ap.add_argument("--coder-pack", type=int, default=4, help="coder streams per CTA (depth > 1)")
   return ap.parse_args()
 
 
@@ -258,61 +263,63 @@ def run_b200(args):
       dist.barrier()
     torch.cuda.synchronize()
 
-  def step_device():
-    c = model.compress(x_dev)
-    return model.decompress(c)
+  pipe = model.pipeline(args.depth, args.coder_sms, args.coder_pack)
 
-  def step_e2e():
-    xd = x_u8_host.to(dev, non_blocking=True).float() / 255            # H2D + cast
-    c = model.compress(xd)
-    host = model.to_host(c)                                            # strings D2H
-    cd = model.to_device(host)                                         # strings H2D
-    x_hat = bmshj2018.quantize_image(model.decompress(cd))
-    out = x_hat.cpu()                                                  # uint8 image D2H
-    nbytes = sum(len(s) for s in host.string) + sum(len(s) for s in host.side_string)
-    return out, nbytes
+  with pipe:
+    pipe.roundtrip_device([x_dev] * max(args.warmup, 3))
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+      clocks.start()
+    launches0 = tfc.launch_count()
+    timer.on = True
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start.record()
+    pipe.roundtrip_device([x_dev] * args.steps)
+    stop.record()
+    barrier()
+    timer.on = False
+    launches = tfc.launch_count() - launches0
+    clk = clocks.stop() if rank == 0 else None
+    ms = torch.tensor([start.elapsed_time(stop)], device=dev)
+    conv_ms = timer.total_ms()
+    if world > 1:
+      dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_per_step = float(ms.item()) / args.steps
 
-  for _ in range(max(args.warmup, 3)):
-    step_device()
-  barrier()
-  clocks = ClockSampler(local)
-  if rank == 0:
-    clocks.start()
-  launches0 = tfc.launch_count()
+    # e2e: same metric through host buffers (H2D image, D2H strings, H2D strings, D2H x_hat)
+    pipe.roundtrip_host([x_u8_host] * min(args.depth, 2))
+    barrier()
+    t0 = time.perf_counter()
+    res = pipe.roundtrip_host([x_u8_host] * args.steps)
+    torch.cuda.synchronize()
+    e2e_s = torch.tensor([time.perf_counter() - t0], device=dev)
+    string_bytes = (sum(len(b) for b in res[-1][0].string) +
+                    sum(len(b) for b in res[-1][0].side_string))
+    del res
+    h2d_bytes, d2h_bytes = int(pipe.h2d_bytes), int(pipe.d2h_bytes)
+    if world > 1:
+      dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_ms = float(e2e_s.item()) * 1e3 / args.steps
+
+  # the conv kernels alone, one batch, nothing else on the GPU (explains the roofline figure
+  # measured under concurrency above)
+  timer.pairs, timed_pairs = [], timer.pairs
   timer.on = True
-  start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-  start.record()
-  for _ in range(args.steps):
-    step_device()
-  stop.record()
-  barrier()
-  timer.on = False
-  launches = tfc.launch_count() - launches0
-  clk = clocks.stop() if rank == 0 else None
-  ms = torch.tensor([start.elapsed_time(stop)], device=dev)
-  conv_ms = timer.total_ms()
-  if world > 1:
-    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-  ms_per_step = float(ms.item()) / args.steps
-
-  # e2e: same metric through host buffers
-  step_e2e()
-  barrier()
-  t0 = time.perf_counter()
-  for _ in range(args.steps):
-    _, string_bytes = step_e2e()
+  model.decompress(model.compress(x_dev))
   torch.cuda.synchronize()
-  e2e_s = torch.tensor([time.perf_counter() - t0], device=dev)
-  if world > 1:
-    dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-  e2e_ms = float(e2e_s.item()) * 1e3 / args.steps
+  timer.on = False
+  conv_ms_isolated = timer.total_ms()
+  timer.pairs, isolated_pairs = timed_pairs, timer.pairs
 
   if rank != 0:
     if world > 1:
       dist.destroy_process_group()
     return
   if args.verbose:
-    stage_breakdown(model, x_dev, timer, args.steps)
+    timer.pairs = isolated_pairs
+    stage_breakdown(model, x_dev, timer, 1)
+    timer.pairs = timed_pairs
   pixels = batch * h * w
   peaks = measured_peaks()
   per_layer, enc_f, dec_f = conv_flops(model, h, w)
@@ -333,9 +340,8 @@ def run_b200(args):
                  % (x_dev.numel() * 4 / 1e6), "parallelism": "batch-sharded x%d" % world,
                  "conv_impl": args.conv_impl},
       "e2e": {"value": world * pixels / (e2e_ms * 1e-3) / 1e6, "unit": "MPix/s",
-              "h2d_bytes_per_step": int(x_u8_host.numel() + string_bytes),
-              "d2h_bytes_per_step": int(x_u8_host.numel() + string_bytes),
-              "ms_per_step": e2e_ms},
+              "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+              "string_bytes_per_step": int(string_bytes), "ms_per_step": e2e_ms},
       "gpu_launches": int(launches),
       "clocks": clk,
       "roofline": {"bound": "tensor", "kernel": "SignalConv2D kernels (%d launches/step)" % n_conv,
@@ -343,7 +349,14 @@ def run_b200(args):
                    "frac": achieved / peak, "traffic": None,
                    "peak_source": peaks["source"] + " bf16 sustained",
                    "share_of_step": conv_ms_step / ms_per_step,
-                   "flops_per_step": flops_step},
+                   "flops_per_step": flops_step,
+                   "isolated": {"ms_per_step": conv_ms_isolated,
+                                "achieved": flops_step / (conv_ms_isolated * 1e-3) / 1e12,
+                                "frac": flops_step / (conv_ms_isolated * 1e-3) / 1e12 / peak,
+                                "note": "same kernels, one batch alone on the GPU (all SMs)"},
+                   "note": "timed region: kernels bracketed per launch while the range coder "
+                           "of other batches shares the GPU (transform kernels on %d SMs)"
+                           % (148 - args.coder_sms if args.depth > 1 else 148)},
   }
   if not args.no_cpu_baseline and world == 1:
     images = max(1, args.cpu_sample_images)

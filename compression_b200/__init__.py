@@ -3,10 +3,10 @@
 Mirrors `tensorflow_compression/__init__.py:31-40`, which star-imports the layers and ops into
 one namespace (`tfc.*`).
 """
-from compression_b200._lib import InvalidArgumentError, CudaError, launch_count
+from compression_b200._lib import InvalidArgumentError, CudaError, launch_count, configure
 from compression_b200.python.ops.range_coding_ops import (
     range_encode, range_decode, unbounded_index_range_encode, unbounded_index_range_decode,
-    pmf_to_quantized_cdf)
+    pmf_to_quantized_cdf, deferred_checks)
 from compression_b200.python.ops.math_ops import lower_bound, upper_bound
 from compression_b200.python.ops.padding_ops import same_padding_for_kernel
 from compression_b200.python.ops.spectral_ops import irdft_matrix

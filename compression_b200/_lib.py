@@ -94,3 +94,17 @@ def to_device(x, dtype, device=None):
   if device is None:
     device = t.device if t.is_cuda else torch.device("cuda", torch.cuda.current_device())
   return t.to(device=device, dtype=dtype).contiguous()
+
+
+CFG_SM_BUDGET, CFG_CODER_STREAMS_PER_CTA = 1, 2
+
+
+def configure(sm_budget=None, coder_streams_per_cta=None):
+  """Process-wide scheduling knobs of the library (tfc_configure): `sm_budget` = SMs the
+  persistent transform kernels may occupy (0: all), `coder_streams_per_cta` = range-coder
+  streams packed into one CTA (0: automatic).  No effect on results."""
+  L = lib()
+  if sm_budget is not None:
+    check(L.tfc_configure(CFG_SM_BUDGET, int(sm_budget)))
+  if coder_streams_per_cta is not None:
+    check(L.tfc_configure(CFG_CODER_STREAMS_PER_CTA, int(coder_streams_per_cta)))

@@ -6,8 +6,26 @@ std::string& last_error_ref() {
   return s;
 }
 std::atomic<int64_t> g_launches{0};
+std::atomic<int> g_sm_budget{0};
+std::atomic<int> g_coder_pack{0};
 }  // namespace tfc
 
 extern "C" const char* tfc_last_error(void) { return tfc::last_error_ref().c_str(); }
 extern "C" const char* tfc_version(void) { return "tfc_b200 0.1 (sm_100a)"; }
 extern "C" int64_t tfc_launch_count(void) { return tfc::g_launches.load(); }
+
+extern "C" int tfc_configure(int key, int value) {
+  switch (key) {
+    case TFC_CFG_SM_BUDGET:
+      if (value < 0) return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "SM budget must be >= 0");
+      tfc::g_sm_budget.store(value);
+      return TFC_OK;
+    case TFC_CFG_CODER_STREAMS_PER_CTA:
+      if (value < 0 || value > 4)
+        return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "coder streams per CTA must be in [0, 4]");
+      tfc::g_coder_pack.store(value);
+      return TFC_OK;
+    default:
+      return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "unknown configuration key %d", key);
+  }
+}

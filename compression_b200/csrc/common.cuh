@@ -14,6 +14,9 @@ namespace tfc {
 
 std::string& last_error_ref();
 extern std::atomic<int64_t> g_launches;
+extern std::atomic<int> g_sm_budget;   // SMs the persistent transform kernels may occupy (0: all)
+extern std::atomic<int> g_coder_pack;  // range-coder streams per CTA (0: one CTA per stream when
+                                       // the SMs allow it — lowest latency)
 
 inline int fail(int code, const char* fmt, ...) {
   char buf[1024];
@@ -42,6 +45,14 @@ inline int cuda_fail(cudaError_t e, const char* what) {
     cudaError_t e__ = cudaGetLastError();                         \
     if (e__ != cudaSuccess) return ::tfc::cuda_fail(e__, name);   \
   } while (0)
+
+inline int num_sms();
+// grid size of a persistent kernel: every SM, or the configured budget (tfc_configure)
+inline int persistent_grid() {
+  const int b = g_sm_budget.load(std::memory_order_relaxed);
+  const int n = num_sms();
+  return (b > 0 && b < n) ? b : n;
+}
 
 inline int num_sms() {
   static int sms = 0;

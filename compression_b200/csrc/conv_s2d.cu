@@ -123,7 +123,7 @@ size_t conv_s2d_workspace(const tfc_conv_desc& d) {
   const tfc_conv_desc e = inner_desc(d);
   const size_t xs = align256((size_t)e.n * e.h * e.w * kPadC * 2);
   const size_t w2 = align256((size_t)e.kh * e.kw * kPadC * d.cout * 4);
-  return xs + w2 + conv_umma_workspace(e) + 256;
+  return xs + w2 + align256(conv_umma_workspace(e)) + 256;
 }
 
 int conv_s2d(const tfc_conv_desc& d, const void* in, const float* w, const float* bias,
@@ -134,12 +134,16 @@ int conv_s2d(const tfc_conv_desc& d, const void* in, const float* w, const float
                 conv_s2d_workspace(d));
   const tfc_conv_desc e = inner_desc(d);
   const Regroup r = regroup(d);
+  // layout: [regrouped fp32 weights][inner conv workspace (bf16 weights, gamma)][xs] — the
+  // weight areas come first so that their offsets do not depend on the image size
   uint8_t* base = static_cast<uint8_t*>(ws);
   const size_t xs_bytes = align256((size_t)e.n * e.h * e.w * kPadC * 2);
   const size_t w2_bytes = align256((size_t)e.kh * e.kw * kPadC * d.cout * 4);
-  __nv_bfloat16* xs = reinterpret_cast<__nv_bfloat16*>(base);
-  float* w2 = reinterpret_cast<float*>(base + xs_bytes);
-  void* inner_ws = base + xs_bytes + w2_bytes;
+  const size_t inner_bytes = align256(conv_umma_workspace(e));
+  float* w2 = reinterpret_cast<float*>(base);
+  void* inner_ws = base + w2_bytes;
+  __nv_bfloat16* xs = reinterpret_cast<__nv_bfloat16*>(base + w2_bytes + inner_bytes);
+  (void)xs_bytes;
   const int64_t pixels = (int64_t)e.n * e.h * e.w;
   const int grid = (int)std::min<int64_t>((pixels + 255) / 256, (int64_t)num_sms() * 16);
   if (d.in_dtype == TFC_F32)
@@ -149,13 +153,14 @@ int conv_s2d(const tfc_conv_desc& d, const void* in, const float* w, const float
     space_to_depth_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(
         static_cast<const __nv_bfloat16*>(in), d.n, d.h, d.w, d.cin, d.sd, xs);
   TFC_LAUNCHED("space_to_depth_kernel");
-  const int64_t wtotal = (int64_t)e.kh * e.kw * kPadC * d.cout;
-  regroup_weights_kernel<<<(int)std::min<int64_t>((wtotal + 255) / 256, 1024), 256, 0, st>>>(
-      w, d.kh, d.kw, d.cin, d.cout, d.sd, d.pad_top, d.pad_left, r.qmin_h, r.qmin_w, e.kh, e.kw,
-      w2);
-  TFC_LAUNCHED("regroup_weights_kernel");
-  return conv_umma(e, xs, w2, bias, beta, gamma, out, inner_ws,
-                   ws_bytes - xs_bytes - w2_bytes, st);
+  if (!(d.flags & TFC_CONV_WEIGHTS_STAGED)) {
+    const int64_t wtotal = (int64_t)e.kh * e.kw * kPadC * d.cout;
+    regroup_weights_kernel<<<(int)std::min<int64_t>((wtotal + 255) / 256, 1024), 256, 0, st>>>(
+        w, d.kh, d.kw, d.cin, d.cout, d.sd, d.pad_top, d.pad_left, r.qmin_h, r.qmin_w, e.kh, e.kw,
+        w2);
+    TFC_LAUNCHED("regroup_weights_kernel");
+  }
+  return conv_umma(e, xs, w2, bias, beta, gamma, out, inner_ws, inner_bytes, st);
 }
 
 }  // namespace tfc

@@ -549,14 +549,16 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
   const int taps = d.kh * d.kw;
   size_t wbytes = ((size_t)taps * p.npad * d.cin * 2 + 255) & ~size_t(255);
   __nv_bfloat16* gb = reinterpret_cast<__nv_bfloat16*>(static_cast<uint8_t*>(ws) + wbytes);
-  repack_weights_kernel<<<std::min<int64_t>(((int64_t)taps * p.npad * d.cin + 255) / 256, 2048),
-                          256, 0, st>>>(w, taps, d.cin, d.cout, p.npad, wb);
-  TFC_LAUNCHED("repack_weights_kernel");
-  if (gdn) {
-    // gamma[k][c] is "[1 tap][cin=k][cout=c]" -> [c][k]
-    repack_weights_kernel<<<(d.cout * d.cout + 255) / 256, 256, 0, st>>>(gamma, 1, d.cout,
-                                                                         d.cout, p.npad, gb);
+  if (!(d.flags & TFC_CONV_WEIGHTS_STAGED)) {
+    repack_weights_kernel<<<std::min<int64_t>(((int64_t)taps * p.npad * d.cin + 255) / 256, 2048),
+                            256, 0, st>>>(w, taps, d.cin, d.cout, p.npad, wb);
     TFC_LAUNCHED("repack_weights_kernel");
+    if (gdn) {
+      // gamma[k][c] is "[1 tap][cin=k][cout=c]" -> [c][k]
+      repack_weights_kernel<<<(d.cout * d.cout + 255) / 256, 256, 0, st>>>(gamma, 1, d.cout,
+                                                                           d.cout, p.npad, gb);
+      TFC_LAUNCHED("repack_weights_kernel");
+    }
   }
 
   CUtensorMap map_a, map_w, map_g;
@@ -586,7 +588,7 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
     map_g = map_w;
   }
   const size_t smem = smem_bytes(p.npad, d.cout, gdn);
-  const int grid = std::min(p.num_tiles, num_sms());
+  const int grid = std::min(p.num_tiles, persistent_grid());
   void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const Params) = nullptr;
   if (!gdn) {
     kern = conv_umma_kernel<0, 0>;

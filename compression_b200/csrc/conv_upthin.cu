@@ -378,9 +378,11 @@ int conv_upthin(const tfc_conv_desc& d, const void* in, const float* w, const fl
   p.bias = bias; p.out = out;
 
   __nv_bfloat16* wb = static_cast<__nv_bfloat16*>(ws);
-  repack_scatter_weights_kernel<<<(pl.npad * d.cin + 255) / 256, 256, 0, st>>>(
-      w, d.kh * d.kw, d.cin, d.cout, pl.npad, wb);
-  TFC_LAUNCHED("repack_scatter_weights_kernel");
+  if (!(d.flags & TFC_CONV_WEIGHTS_STAGED)) {
+    repack_scatter_weights_kernel<<<(pl.npad * d.cin + 255) / 256, 256, 0, st>>>(
+        w, d.kh * d.kw, d.cin, d.cout, pl.npad, wb);
+    TFC_LAUNCHED("repack_scatter_weights_kernel");
+  }
 
   CUtensorMap map_a, map_w;
   {
@@ -404,7 +406,7 @@ int conv_upthin(const tfc_conv_desc& d, const void* in, const float* w, const fl
                     pl.ih == 6 && pl.iw == 14;
   auto kern = fast ? conv_upthin_kernel<true> : conv_upthin_kernel<false>;
   TFC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
-  const int grid = std::min(p.num_tiles, num_sms());
+  const int grid = std::min(p.num_tiles, persistent_grid());
   kern<<<grid, kThreads, pl.smem, st>>>(map_a, map_w, p);
   TFC_LAUNCHED("conv_upthin_kernel");
   return TFC_OK;

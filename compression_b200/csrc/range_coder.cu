@@ -612,17 +612,37 @@ extern "C" int tfc_unbounded_index_range_encode(
     q.cdf_size = d_cdf_size; q.offset = d_offset; q.rows = rows; q.cols = cols;
     q.precision = precision; q.overflow_width = overflow_width; q.out = d_out; q.cap = cap;
     q.nbytes = d_nbytes; q.status = d_status; q.S = S; q.n = n;
-    q.round = std::max(32, std::min(v4::kRoundMax, v4::kPutCap / v4_max_puts(overflow_width) / 32 * 32));
     q.table_bytes = v4_table_budget(rows, cols);
-    const size_t smem = (size_t)q.table_bytes + v4::enc_bytes();
+    // streams per CTA: 1 unless the caller packs the coder (tfc_configure); the per-stream
+    // round buffers shrink until the CTA fits in shared memory
+    const int pack = tfc::g_coder_pack.load(std::memory_order_relaxed);
+    q.streams_per_cta = (int)std::max<int64_t>(1, std::min<int64_t>(pack > 0 ? pack : 1, S));
+    const int min_cap = (32 * v4_max_puts(overflow_width) + 31) / 32 * 32;   // one 32-symbol round
+    q.put_cap = std::max(v4::kPutCap, min_cap);
+    const size_t smem_max = 227 * 1024 - 1024;
+    while (q.put_cap / 2 >= std::max(256, min_cap) &&
+           (size_t)q.table_bytes + q.streams_per_cta * v4::enc_bytes(q.put_cap) > smem_max)
+      q.put_cap /= 2;
+    while (q.streams_per_cta > 1 &&
+           (size_t)q.table_bytes + q.streams_per_cta * v4::enc_bytes(q.put_cap) > smem_max)
+      --q.streams_per_cta;
+    q.round = std::max(32, std::min(v4::kRoundMax, q.put_cap / v4_max_puts(overflow_width) / 32 * 32));
+    if (q.round * v4_max_puts(overflow_width) > q.put_cap)
+      return tfc::fail(TFC_ERR_UNIMPLEMENTED, "overflow_width %d needs larger round buffers", overflow_width);
+    const size_t smem = (size_t)q.table_bytes + q.streams_per_cta * v4::enc_bytes(q.put_cap);
     static bool attr = false;
     if (!attr) {
-      TFC_CUDA(cudaFuncSetAttribute(v4::encode_unbounded_v4,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)(kV4TableBudget + 16 + v4::enc_bytes())));
+      TFC_CUDA(cudaFuncSetAttribute(v4::encode_unbounded_v4<false>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
+      TFC_CUDA(cudaFuncSetAttribute(v4::encode_unbounded_v4<true>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
       attr = true;
     }
-    v4::encode_unbounded_v4<<<(unsigned)S, 96, smem, st>>>(q);
+    const int64_t blocks = (S + q.streams_per_cta - 1) / q.streams_per_cta;
+    if (q.streams_per_cta == 1)
+      v4::encode_unbounded_v4<false><<<(unsigned)blocks, 96, smem, st>>>(q);
+    else
+      v4::encode_unbounded_v4<true><<<(unsigned)blocks, 96 * q.streams_per_cta, smem, st>>>(q);
     TFC_LAUNCHED("encode_unbounded_v4");
     return TFC_OK;
   }
@@ -683,6 +703,8 @@ extern "C" int tfc_unbounded_index_range_decode(
     q.table_bytes = v4_table_budget(rows, cols);
     const int sms = tfc::num_sms();
     q.streams_per_cta = S <= sms ? 1 : (S <= 2 * (int64_t)sms ? 2 : 4);
+    const int pack = tfc::g_coder_pack.load(std::memory_order_relaxed);
+    if (pack > 0) q.streams_per_cta = (int)std::max<int64_t>(1, std::min<int64_t>(pack, S));
     const size_t smem = (size_t)q.table_bytes + (size_t)q.streams_per_cta * v4::dec_pair_bytes();
     static bool attr = false;
     if (!attr) {

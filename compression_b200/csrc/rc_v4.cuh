@@ -91,7 +91,9 @@ __device__ void stage_tables_v4(const int32_t* __restrict__ cdf, int rows, int c
         c3 = (uint32_t)__ldg(src + 3) << sh;
         if (c1 > 0xFFFFu || c2 > 0xFFFFu || c3 > 0xFFFFu) c1 = c2 = c3 = 0;  // malformed
       }
-      rowrec[r] = make_uint4(c1 << 16, c2 << 16, c3 << 16, (uint32_t)r);
+      // rows outside the fast class carry their staged position instead (z == 0 marks them)
+      if (c3 == 0) rowrec[r] = make_uint4((uint32_t)(fits ? ri.x : r * cols), (uint32_t)ri.y, 0u, (uint32_t)r);
+      else rowrec[r] = make_uint4(c1 << 16, c2 << 16, c3 << 16, (uint32_t)r);
     }
   }
   __syncthreads();
@@ -142,28 +144,52 @@ struct DecState {
   }
 };
 
-// Out-of-line general symbol: binary search over the staged row, then the escape tail
-// (unbounded_index_range_coding_kernels.cc:336-360).  Returns the value before the row offset.
+// General symbol (any row), called by the whole chain warp: the decoder state is replicated in
+// every lane, so each lane evaluates ONE candidate entry of the row and a ballot picks the
+// bracket — a 32-ary search, one step for rows of up to 33 entries (every EntropyBottleneck
+// row) — then the escape tail (unbounded_index_range_coding_kernels.cc:336-360).  Returns the
+// value before the row offset.
 __device__ __forceinline__ int32_t decode_general(DecState& d, const Tables& tb, int start,
-                                                  int len, int ow, int max_digits) {
+                                                  int len, int ow, int max_digits, int lane) {
+  // smallest k in [lo, hi] with span * row[k] > target; row[len - 1] = 2^16 always qualifies
   int lo = 1, hi = len - 1;
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    const uint32_t c = tb.at(start + mid);
-    if ((c >> 16) != 0 || scale16(d.span1, c) > d.rem) hi = mid; else lo = mid + 1;
+  while (hi - lo + 1 > 32) {
+    const int step = (hi - lo + 1 + 31) >> 5;
+    const int k = min(lo + (lane + 1) * step - 1, hi);
+    const uint32_t c = tb.at(start + k);
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, (c >> 16) != 0 || scale16(d.span1, c) > d.rem);
+    if (m == 0) { lo = hi; break; }
+    const int f = __ffs(m) - 1;
+    const int nlo = lo + f * step;
+    hi = min(nlo + step - 1, hi);
+    lo = nlo;
   }
-  const uint32_t c1 = tb.at(start + lo);
-  if ((c1 >> 16) == 0 && scale16(d.span1, c1) <= d.rem) d.corrupt = true;  // ran past the row
-  d.narrow(scale16(d.span1, tb.at(start + lo - 1)),
-           (c1 >> 16) ? d.span1 : scale16(d.span1, c1) - 1u);
+  uint32_t a, b1;     // floor(span*row[k-1]/2^16), floor(span*row[k]/2^16) (mod 2^32)
+  bool top;           // row[k] == 2^16
+  {
+    const int k = min(lo + lane, hi);
+    const uint32_t c = tb.at(start + k);
+    const uint32_t tk = scale16(d.span1, c);
+    const bool over = (c >> 16) != 0;
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, over || tk > d.rem);
+    int f = __ffs(m) - 1;
+    if (m == 0) { d.corrupt = true; f = hi - lo; }     // ran past the row: malformed input
+    f = min(f, hi - lo);
+    b1 = __shfl_sync(0xFFFFFFFFu, tk, f);
+    top = __shfl_sync(0xFFFFFFFFu, (int)over, f) != 0;
+    const uint32_t prev = __shfl_sync(0xFFFFFFFFu, tk, max(f - 1, 0));
+    a = prev;
+    if (f == 0) a = scale16(d.span1, tb.at(start + lo - 1));
+    lo += f;
+  }
+  d.narrow(a, top ? d.span1 : b1 - 1u);
   int32_t v = lo - 1;
   if (v == len - 2) {
     const uint32_t all1 = (1u << ow) - 1u;
     const int sh = 16 - ow;
-    int nd = 0, guard = 0;
-    (void)guard;
+    int nd = 0;
     uint32_t u;
-    do { u = d.digit(sh, all1); nd += (int)u; ++guard; } while (u == all1 && nd <= max_digits);
+    do { u = d.digit(sh, all1); nd += (int)u; } while (u == all1 && nd <= max_digits);
     if (nd > max_digits) { d.corrupt = true; nd = max_digits; }
     uint32_t x = 0;
     for (int q = 0; q < nd; ++q) {
@@ -257,8 +283,15 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
       const int64_t base = r * R;
       const int cnt = (int)min((int64_t)R, p.n - base);
       uint4* dst = recs + (r & 1) * (kRoundMax + kRecPad);
+      int slow = 0;       // records of this round that are not in the fast class
 #pragma unroll 4
-      for (int j = lane; j < cnt; j += 32) dst[j] = t.rowrec[__ldg(idx + base + j)];
+      for (int j = lane; j < cnt; j += 32) {
+        const uint4 q = t.rowrec[__ldg(idx + base + j)];
+        dst[j] = q;
+        slow += q.z == 0u;
+      }
+      slow = __reduce_add_sync(0xFFFFFFFFu, slow);
+      if (lane == 0) ctrl[2 + (r & 1)] = (uint32_t)slow;
     };
     auto flush = [&](int64_t r) {
       const int64_t base = r * R;
@@ -339,6 +372,29 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
     int j = 0;
     const uint4* rp = rc;
     uint8_t* cp = cb;
+    // one symbol at a time: fast step for 5-entry rows, the warp-wide search otherwise
+    auto careful = [&](int stop) {
+      for (; j < stop; ++j, ++rp, ++cp) {
+        const uint4 q = rp[0];
+        const uint32_t k_rem = rem, k_span = span, k_w0 = w0, k_wa = wa;
+        int start = (int)q.x, len = (int)q.y;
+        if (q.z != 0u) {
+          bool ok = true;
+          step(q, cp, ok);
+          if (ok) continue;
+          const int4 ri = t.rowinfo[q.w];     // escape (or span == 2^32) on a fast-class row
+          start = ri.x; len = ri.y;
+        }
+        d.rem = k_rem; d.span1 = k_span - 1u; d.w0 = k_w0; d.wa = k_wa;
+        const int32_t v = decode_general(d, t, start, len, ow, p.max_digits, lane);
+        rem = d.rem; span = d.span1 + 1u; w0 = d.w0; wa = d.wa;
+        ev[j] = v;
+        *cp = 0xFF;
+      }
+    };
+    if (ctrl[2 + (r & 1)] * 8u > (uint32_t)cnt) {
+      careful(cnt);     // too many general symbols for speculation in groups of four to pay
+    }
     while (j < cnt) {
       if (j + 4 <= cnt) {
         uint4 q0 = rp[0], q1 = rp[1], q2 = rp[2], q3 = rp[3];
@@ -356,21 +412,7 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
         if (ok) continue;
         rem = s_rem; span = s_span; w0 = s_w0; wa = s_wa;   // replay this group carefully
       }
-      const int stop = min(j + 4, cnt);
-      for (; j < stop; ++j, ++rp, ++cp) {
-        const uint4 q = rp[0];
-        bool ok = true;
-        const uint32_t k_rem = rem, k_span = span, k_w0 = w0, k_wa = wa;
-        step(q, cp, ok);
-        if (ok) continue;
-        // general path for symbol j
-        const int4 ri = t.rowinfo[q.w];
-        d.rem = k_rem; d.span1 = k_span - 1u; d.w0 = k_w0; d.wa = k_wa;
-        const int32_t v = decode_general(d, t, ri.x, ri.y, ow, p.max_digits);
-        rem = d.rem; span = d.span1 + 1u; w0 = d.w0; wa = d.wa;
-        ev[j] = v;
-        *cp = 0xFF;
-      }
+      careful(min(j + 4, cnt));
     }
     // P_{r+1}: stream position of w0; the next window starts at P_r (see the kernel comment)
     const uint32_t p_next = win_first + (wa - lin_r) / 2u - 1u;
@@ -413,36 +455,47 @@ struct EncParamsV4 {
   int32_t* nbytes;
   int32_t* status;
   int64_t S, n;
-  int32_t round;          // symbols per round: round * max_puts <= kPutCap, multiple of 32
+  int32_t round;          // symbols per round: round * max_puts <= put_cap, multiple of 32
   int32_t table_bytes;
+  int32_t put_cap;        // puts per round (<= kPutCap, multiple of 32)
+  int32_t streams_per_cta;
 };
 
-__host__ __device__ inline size_t enc_bytes() {
-  return (size_t)2 * kPutCap * 8      // puts
-         + (size_t)2 * kPutCap * 4    // a values
-         + (size_t)2 * (kPutCap / 32) * 4  // flags
-         + (size_t)kPutCap * 2        // words of one round
-         + 64;                        // counts[4], span, ...
+__host__ __device__ inline size_t enc_bytes(int put_cap) {
+  const size_t b = (size_t)2 * put_cap * 8      // puts
+                   + (size_t)2 * put_cap * 8    // {a, renormalisation flag} per put
+                   + (size_t)put_cap * 2 + 4    // words of one round + the pending one
+                   + 64;                        // counts[4], span, ...
+  return (b + 15) & ~size_t(15);
+}
+
+__device__ __forceinline__ void trio_barrier(int id) {
+  asm volatile("bar.sync %0, 96;" ::"r"(id) : "memory");
 }
 
 __device__ __forceinline__ void put_byte(uint8_t* out, uint32_t cap, uint32_t at, uint32_t b) {
   if (at < cap) out[at] = (uint8_t)b;
 }
 
-__global__ void __launch_bounds__(96) encode_unbounded_v4(const EncParamsV4 p) {
+// streams_per_cta streams share one CTA (and one staged copy of the tables); each stream's three
+// warps synchronise on their own named barrier, so streams never wait for each other.
+template <bool MULTI>
+__global__ void __launch_bounds__(MULTI ? 384 : 96) encode_unbounded_v4(const EncParamsV4 p) {
   Tables t;
   stage_tables_v4(p.cdf, p.rows, p.cols, p.cdf_size, p.offset, p.precision, smem_v4,
                   p.table_bytes, &t);
-  uint8_t* mine = smem_v4 + p.table_bytes;
-  uint2* puts = reinterpret_cast<uint2*>(mine);                                  // [2][kPutCap]
-  uint32_t* avals = reinterpret_cast<uint32_t*>(mine + 2 * kPutCap * 8);         // [2][kPutCap]
-  uint32_t* flags = avals + 2 * kPutCap;                                         // [2][kPutCap/32]
-  uint16_t* words = reinterpret_cast<uint16_t*>(flags + 2 * (kPutCap / 32));     // [kPutCap]
-  volatile uint32_t* counts = reinterpret_cast<volatile uint32_t*>(words + kPutCap);  // [4]
+  const int slot = MULTI ? (int)(threadIdx.x / 96) : 0;
+  const int64_t s = MULTI ? (int64_t)blockIdx.x * p.streams_per_cta + slot : (int64_t)blockIdx.x;
+  if (s >= p.S) return;
+  const int kCap = p.put_cap;
+  uint8_t* mine = smem_v4 + p.table_bytes + (size_t)slot * enc_bytes(kCap);
+  uint2* puts = reinterpret_cast<uint2*>(mine);                                  // [2][kCap]
+  uint2* avals = reinterpret_cast<uint2*>(mine + 2 * kCap * 8);                  // [2][kCap]
+  uint16_t* words = reinterpret_cast<uint16_t*>(avals + 2 * kCap);               // [kCap + 2]
+  volatile uint32_t* counts = reinterpret_cast<volatile uint32_t*>(words + kCap + 2);  // [4]
   volatile uint32_t* fin = counts + 4;                                           // final span1
 
-  const int64_t s = blockIdx.x;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = (int)((threadIdx.x - slot * 96) >> 5), lane = threadIdx.x & 31;
   const int R = p.round;
   const int64_t rounds = (p.n + R - 1) / R;
   const int32_t* idx = p.index + s * p.index_stride;
@@ -455,6 +508,16 @@ __global__ void __launch_bounds__(96) encode_unbounded_v4(const EncParamsV4 p) {
 
   uint32_t span1 = 0xFFFFFFFFu;          // warp 0
   uint32_t lo = 0, total = 0;            // warp 1: low word, words flushed so far
+  uint32_t last = 0, have_last = 0;      // warp 1: the newest word, not flushed yet (words[0])
+  // warp 2: symbols and indexes are fetched two 32-symbol groups ahead of their use
+  int32_t pf_idx[2] = {0, 0}, pf_dat[2] = {0, 0};
+  if (warp == 2) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int64_t at = (int64_t)k * 32 + lane;
+      if (at < p.n) { pf_idx[k] = __ldg(idx + at); pf_dat[k] = __ldg(data + at); }
+    }
+  }
 
   for (int64_t r = 0; r < rounds + 2; ++r) {
     if (warp == 2) {
@@ -462,16 +525,22 @@ __global__ void __launch_bounds__(96) encode_unbounded_v4(const EncParamsV4 p) {
         // ---- stager ----
         const int64_t base = r * R;
         const int cnt = (int)min((int64_t)R, p.n - base);
-        uint2* dst = puts + (r & 1) * kPutCap;
+        uint2* dst = puts + (r & 1) * kCap;
         uint32_t fill = 0;
         for (int j0 = 0; j0 < cnt; j0 += 32) {
           const int j = j0 + lane;
           uint32_t c0 = 0, c1 = 0, x = 0;
           int np = 0, nd = 0;
+          const int32_t cur_idx = pf_idx[0], cur_dat = pf_dat[0];
+          pf_idx[0] = pf_idx[1]; pf_dat[0] = pf_dat[1];
+          {
+            const int64_t at = base + j + 64;
+            if (at < p.n) { pf_idx[1] = __ldg(idx + at); pf_dat[1] = __ldg(data + at); }
+          }
           if (j < cnt) {
-            const int4 ri = t.rowinfo[__ldg(idx + base + j)];
+            const int4 ri = t.rowinfo[cur_idx];
             const int32_t top = ri.y - 2;
-            int32_t v = __ldg(data + base + j) - ri.z;
+            int32_t v = cur_dat - ri.z;
             np = 1;
             bool esc = false;
             if (v < 0) { x = (uint32_t)(-2 * v - 1); v = top; esc = true; }
@@ -511,26 +580,24 @@ __global__ void __launch_bounds__(96) encode_unbounded_v4(const EncParamsV4 p) {
         // ---- span chain (replicated in all lanes; lane 0 stores) ----
         const int64_t q = r - 1;
         const uint32_t cnt = counts[q & 3];
-        const uint2* src = puts + (q & 1) * kPutCap;
-        uint32_t* av = avals + (q & 1) * kPutCap;
-        uint32_t* fl = flags + (q & 1) * (kPutCap / 32);
-        uint2 cur = src[0];
-        uint32_t fm = 0;
-#pragma unroll 1
+        const uint2* src = puts + (q & 1) * kCap;
+        uint2* av = avals + (q & 1) * kCap;
+        // puts are fetched two iterations ahead so that the shared-memory latency is off the
+        // span recurrence (reads past the round's end land in the neighbouring buffers and
+        // are never used)
+        uint2 cur = src[0], nxt = src[1];
+#pragma unroll 4
         for (uint32_t i = 0; i < cnt; ++i) {
-          const uint2 nxt = src[min(i + 1, (uint32_t)kPutCap - 1)];
+          const uint2 nn = src[i + 2];
           const uint32_t a = scale16(span1, cur.x);
           const uint32_t b1 = scale16(span1, cur.y);       // b + 1 (mod 2^32)
-          uint32_t ns = b1 - 1u - a;
+          const uint32_t ns = b1 - 1u - a;
           const bool rn = (ns >> 16) == 0;
-          ns = rn ? ((ns << 16) | 0xFFFFu) : ns;
-          span1 = ns;
-          fm |= (rn ? 1u : 0u) << (i & 31);
-          av[i] = a;
-          if ((i & 31) == 31) { fl[i >> 5] = fm; fm = 0; }
+          span1 = rn ? ((ns << 16) | 0xFFFFu) : ns;
+          av[i] = make_uint2(a, rn ? 1u : 0u);
           cur = nxt;
+          nxt = nn;
         }
-        if ((cnt & 31) != 0 && lane == 0) fl[cnt >> 5] = fm;
         if (r == rounds && lane == 0) fin[0] = span1;
       }
     } else {
@@ -538,63 +605,99 @@ __global__ void __launch_bounds__(96) encode_unbounded_v4(const EncParamsV4 p) {
         // ---- low chain + emission (replicated; lane 0 does the rare global fix-ups) ----
         const int64_t q = r - 2;
         const uint32_t cnt = counts[q & 3];
-        const uint32_t* av = avals + (q & 1) * kPutCap;
-        const uint32_t* fl = flags + (q & 1) * (kPutCap / 32);
-        uint32_t nw = 0;                   // words produced in this round
-        uint32_t fm = 0;
-        uint32_t a = av[0];
-#pragma unroll 1
-        for (uint32_t i = 0; i < cnt; ++i) {
-          const uint32_t an = av[min(i + 1, (uint32_t)kPutCap - 1)];
-          if ((i & 31) == 0) fm = fl[i >> 5];
-          lo += a;
-          if (lo < a) {
-            // carry out of the window: +1 into the words already produced
-            int32_t k = (int32_t)nw - 1;
-            bool carry = true;
-            __syncwarp();
-            while (carry && k >= 0) {
-              const uint32_t wv = (uint32_t)words[k] + 1u;
+        const uint2* av = avals + (q & 1) * kCap;
+        // The newest word of the stream stays pending (register `last`, mirrored in
+        // words[nw - 1]; words[0] at the start of a round) because a carry out of the 32-bit
+        // window lands in it.  Groups of 32 puts (one flag word) run branch-free: add, carry
+        // into `last`, predicated stores.  A carry that has to ripple further (last == 0xFFFF,
+        // probability 2^-16) marks the group; it is rolled back and replayed carefully.
+        uint32_t nw = have_last;           // words of this round, the pending one included
+        for (uint32_t g = 0; g < cnt; g += 32) {
+          const uint32_t m = min(32u, cnt - g);
+          const uint32_t lo0 = lo, nw0 = nw, last0 = last;
+          bool slow = false;
+          uint2 a2 = av[g], a1 = av[g + 1];
+#pragma unroll 4
+          for (uint32_t k = 0; k < m; ++k) {
+            const uint2 an = av[g + k + 2];
+            const uint32_t a = a2.x;
+            lo += a;
+            const bool c = lo < a;
+            last += c ? 1u : 0u;
+            slow |= (last >> 16) != 0u;
+            if (c && nw > 0u) words[nw - 1] = (uint16_t)last;   // (no carry before the first word)
+            const bool emit = a2.y != 0u;
+            const uint32_t w = lo >> 16;
+            if (emit) words[nw] = (uint16_t)w;
+            last = emit ? w : last;
+            nw += emit ? 1u : 0u;
+            lo = emit ? (lo << 16) : lo;
+            a2 = a1;
+            a1 = an;
+          }
+          if (!slow) continue;
+          lo = lo0; nw = nw0;
+          __syncwarp();
+          if (nw0 > 0) words[nw0 - 1] = (uint16_t)last0;
+          __syncwarp();
+          for (uint32_t k = 0; k < m; ++k) {
+            const uint32_t ak = av[g + k].x;
+            const bool emit_k = av[g + k].y != 0u;
+            lo += ak;
+            if (lo < ak) {
+              // carry out of the window: +1 into the words already produced
+              int32_t kk = (int32_t)nw - 1;
+              bool carry = true;
               __syncwarp();
-              words[k] = (uint16_t)wv;
-              carry = (wv >> 16) != 0;
-              --k;
-            }
-            if (carry && lane == 0) {
-              int64_t g = (int64_t)total - 1;     // flushed words live in global memory
-              while (g >= 0) {
-                const uint32_t at = 2u * (uint32_t)g;
-                uint32_t wv = 0;
-                if (at < cap) wv = (uint32_t)out[at] << 8;
-                if (at + 1 < cap) wv |= out[at + 1];
-                wv += 1u;
-                put_byte(out, cap, at, (wv >> 8) & 0xFFu);
-                put_byte(out, cap, at + 1, wv & 0xFFu);
-                if ((wv >> 16) == 0) break;
-                --g;
+              while (carry && kk >= 0) {
+                const uint32_t wv = (uint32_t)words[kk] + 1u;
+                __syncwarp();
+                words[kk] = (uint16_t)wv;
+                carry = (wv >> 16) != 0;
+                --kk;
               }
+              if (carry && lane == 0) {
+                int64_t gw = (int64_t)total - 1;     // flushed words live in global memory
+                while (gw >= 0) {
+                  const uint32_t at = 2u * (uint32_t)gw;
+                  uint32_t wv = 0;
+                  if (at < cap) wv = (uint32_t)out[at] << 8;
+                  if (at + 1 < cap) wv |= out[at + 1];
+                  wv += 1u;
+                  put_byte(out, cap, at, (wv >> 8) & 0xFFu);
+                  put_byte(out, cap, at + 1, wv & 0xFFu);
+                  if ((wv >> 16) == 0) break;
+                  --gw;
+                }
+              }
+              __syncwarp();
             }
-            __syncwarp();
+            if (emit_k) {
+              words[nw] = (uint16_t)(lo >> 16);
+              ++nw;
+              lo <<= 16;
+            }
           }
-          if (fm & 1u) {
-            words[nw] = (uint16_t)(lo >> 16);
-            ++nw;
-            lo <<= 16;
-          }
-          fm >>= 1;
-          a = an;
+          __syncwarp();
+          last = nw > 0 ? (uint32_t)words[nw - 1] : 0u;
         }
         __syncwarp();
-        for (uint32_t k = lane; k < nw; k += 32) {
+        // flush all but the newest word (everything after the last round)
+        const uint32_t keep = (q + 1 < rounds && nw > 0) ? 1u : 0u;
+        const uint32_t nflush = nw - keep;
+        for (uint32_t k = lane; k < nflush; k += 32) {
           const uint32_t wv = words[k];
           put_byte(out, cap, 2u * (total + k), wv >> 8);
           put_byte(out, cap, 2u * (total + k) + 1u, wv & 0xFFu);
         }
-        total += nw;
+        total += nflush;
+        __syncwarp();
+        if (keep) words[0] = (uint16_t)last;
+        have_last = keep;
         __syncwarp();
       }
     }
-    __syncthreads();
+    if (MULTI) trio_barrier(1 + slot); else __syncthreads();
   }
 
   if (warp == 1) {

@@ -107,6 +107,123 @@ class HyperSynthesisTransform(_Sequential):
     ])
 
 
+class Pipeline(object):
+  """Keeps several batches in flight on separate CUDA streams.
+
+  One image = one serial range-coder chain (the reference's string format), so the coder
+  kernels are latency bound and occupy a few SMs for milliseconds while the transforms are
+  throughput bound.  The pipeline runs batch k's coder concurrently with batch k+1's
+  transforms: every batch gets its own stream (its own kernels stay ordered, no events
+  needed), the coder packs `coder_streams_per_cta` images into one CTA and the persistent
+  transform kernels leave `coder_sms` SMs to it.  Results are those of compress()/decompress()
+  called batch by batch.
+  """
+
+  def __init__(self, model, depth=3, coder_sms=32, coder_streams_per_cta=4):
+    from compression_b200 import _lib
+    self.model = model
+    self.depth = max(1, int(depth))
+    self.streams = [torch.cuda.Stream(device=model.device) for _ in range(self.depth)]
+    self._lib = _lib
+    self._sms = torch.cuda.get_device_properties(model.device).multi_processor_count
+    self.coder_sms = int(coder_sms) if self.depth > 1 else 0
+    self.pack = int(coder_streams_per_cta) if self.depth > 1 else 0
+
+  def __enter__(self):
+    if self.depth > 1:
+      self._lib.configure(sm_budget=max(1, self._sms - self.coder_sms),
+                          coder_streams_per_cta=self.pack)
+    return self
+
+  def __exit__(self, *exc):
+    self._lib.configure(sm_budget=0, coder_streams_per_cta=0)
+    return False
+
+  def _fork(self):
+    cur = torch.cuda.current_stream(self.model.device)
+    for s in self.streams:
+      s.wait_stream(cur)
+    return cur
+
+  def _join(self, cur):
+    for s in self.streams:
+      cur.wait_stream(s)
+
+  def roundtrip_device(self, batches):
+    """batches: device float32 [B,H,W,3] tensors -> list of x_hat (device)."""
+    from compression_b200.python.ops import range_coding_ops as rc
+    model, outs = self.model, []
+    cur = self._fork()
+    with rc.deferred_checks():
+      for k, x in enumerate(batches):
+        with torch.cuda.stream(self.streams[k % self.depth]):
+          outs.append(model.decompress(model.compress(x)))
+      self._join(cur)
+    return outs
+
+  def roundtrip_host(self, batches_u8):
+    """batches_u8: pinned host uint8 [B,H,W,3] -> list of (Compressed with host strings,
+    x_hat uint8 on the host).  Per batch: image H2D, compress, strings D2H, strings H2D,
+    decompress, x_hat D2H; the host only waits for batch k's strings after it has queued
+    batch k+depth-1's compress."""
+    from compression_b200.python.ops import range_coding_ops as rc
+    model, dev = self.model, self.model.device
+    front, results = {}, [None] * len(batches_u8)
+    self.h2d_bytes = self.d2h_bytes = 0     # per batch, counted from the tensors copied
+    cur = self._fork()
+
+    def issue_front(k):
+      st = self.streams[k % self.depth]
+      with torch.cuda.stream(st):
+        x = batches_u8[k].to(dev, non_blocking=True).float() / 255
+        c = model.compress(x)
+        pinned = []
+        for slab, nbytes in (c.string, c.side_string):
+          hs = torch.empty(slab.shape, dtype=torch.uint8, pin_memory=True)
+          hn = torch.empty(nbytes.shape, dtype=torch.int32, pin_memory=True)
+          hs.copy_(slab, non_blocking=True)
+          hn.copy_(nbytes, non_blocking=True)
+          pinned.append((hs, hn))
+        if k == 0:
+          self.h2d_bytes += batches_u8[k].numel()
+          self.d2h_bytes += sum(hs.numel() + 4 * hn.numel() for hs, hn in pinned)
+        ev = torch.cuda.Event()
+        ev.record(st)
+      front[k] = (c, pinned, ev)
+
+    def issue_back(k):
+      c, pinned, ev = front.pop(k)
+      ev.synchronize()
+      strings = []
+      for hs, hn in pinned:
+        a, nb = hs.numpy(), hn.numpy()
+        strings.append([a[i, :nb[i]].tobytes() for i in range(len(nb))])
+      host = Compressed(strings[0], strings[1], c.x_shape, c.y_shape, c.z_shape)
+      st = self.streams[k % self.depth]
+      with torch.cuda.stream(st):
+        dc = model.to_device(host)
+        x_hat = quantize_image(model.decompress(dc))
+        out = torch.empty(x_hat.shape, dtype=torch.uint8, pin_memory=True)
+        out.copy_(x_hat, non_blocking=True)
+        if k == 0:
+          self.h2d_bytes += sum(t.numel() * t.element_size() for pair in (dc.string, dc.side_string)
+                                for t in pair)
+          self.d2h_bytes += out.numel()
+      results[k] = (host, out)
+
+    with rc.deferred_checks():
+      n = len(batches_u8)
+      for k in range(n + self.depth - 1):
+        if k < n:
+          issue_front(k)
+        j = k - (self.depth - 1)
+        if 0 <= j < n:
+          issue_back(j)
+      self._join(cur)
+    cur.synchronize()
+    return results
+
+
 class Bmshj2018Model(object):
   """Random-init (or externally loaded) hyperprior model on one GPU."""
 
@@ -177,6 +294,9 @@ class Bmshj2018Model(object):
     bpp = (torch.log(y_lik).sum() + torch.log(z_lik).sum()) / (-np.log(2) * num_pixels)
     return dict(x_hat=x_hat, y=y, z=z, sigma=sigma, y_hat=y_hat, y_likelihoods=y_lik,
                 z_likelihoods=z_lik, eval_bpp=float(bpp))
+
+  def pipeline(self, depth=3, coder_sms=32, coder_streams_per_cta=4):
+    return Pipeline(self, depth, coder_sms, coder_streams_per_cta)
 
   # ---- host-side strings --------------------------------------------------------------------
   @staticmethod

@@ -29,7 +29,9 @@ class ConvDesc(ctypes.Structure):
   """ctypes image of tfc_conv_desc."""
   _fields_ = [(n, ctypes.c_int32) for n in (
       "n", "h", "w", "cin", "ho", "wo", "cout", "kh", "kw", "sd", "su", "pad_top", "pad_left",
-      "act", "in_dtype", "out_dtype", "impl")]
+      "act", "in_dtype", "out_dtype", "impl", "flags")]
+
+CONV_WEIGHTS_STAGED = 1
 
 
 def _dtype_code(dt):
@@ -102,7 +104,7 @@ class SignalConv2D(object):
     self.out_dtype = torch.float32  # dtype of the produced activations (float32 | bfloat16)
     self.built = False
     self._eff = None
-    self._ws = None
+    self._ws = {}   # (device, stream) -> [buffer, effective weights staged in it, GDN params]
 
   # ---- reference's capability gaps ------------------------------------------------------
   def _raise_notimplemented(self):
@@ -262,17 +264,27 @@ class SignalConv2D(object):
                  kh=self.kernel_support[0], kw=self.kernel_support[1],
                  sd=self.strides_down[0], su=self.strides_up[0], pad_top=pad_begin[0],
                  pad_left=pad_begin[1], act=act, in_dtype=_dtype_code(x.dtype),
-                 out_dtype=_dtype_code(out_dtype), impl=self.impl)
+                 out_dtype=_dtype_code(out_dtype), impl=self.impl, flags=0)
     L = _lib.lib()
     L.tfc_signal_conv2d_workspace.restype = ctypes.c_size_t
     need = int(L.tfc_signal_conv2d_workspace(ctypes.byref(d)))
-    if self._ws is None or self._ws.numel() < need or self._ws.device != x.device:
-      self._ws = torch.empty((max(need, 256),), dtype=torch.uint8, device=x.device)
+    # One workspace per CUDA stream (concurrent batches on different streams must not share
+    # scratch); the repacked weights stay valid in it until the effective weights change.
+    stream = _lib.stream_ptr(x.device)
+    key = (x.device.index, stream.value)
+    rec = self._ws.get(key)
+    if rec is None or rec[0].numel() < need:
+      rec = [torch.empty((max(need, 256),), dtype=torch.uint8, device=x.device), None, None]
+      self._ws[key] = rec
+    gdn_params = self.activation._cache if act in (ACT_GDN, ACT_IGDN) else None
+    if rec[1] is self._eff and rec[2] is gdn_params and rec[1] is not None:
+      d.flags |= CONV_WEIGHTS_STAGED
     out = torch.empty((n, ho, wo, self.filters), dtype=out_dtype, device=x.device)
     _lib.check(L.tfc_signal_conv2d(
         ctypes.byref(d), _lib.ptr(x), _lib.ptr(wgt), _lib.ptr(bias), _lib.ptr(beta),
-        _lib.ptr(gamma), _lib.ptr(out), _lib.ptr(self._ws), ctypes.c_size_t(self._ws.numel()),
-        _lib.stream_ptr(x.device)))
+        _lib.ptr(gamma), _lib.ptr(out), _lib.ptr(rec[0]), ctypes.c_size_t(rec[0].numel()),
+        stream))
+    rec[1], rec[2] = self._eff, gdn_params
     if post is not None:
       out = post(out)
     return out

@@ -21,9 +21,52 @@ __all__ = [
     "unbounded_index_range_decode", "pmf_to_quantized_cdf",
     "unbounded_index_range_encode_batch", "unbounded_index_range_decode_batch",
     "range_encode_batch", "range_decode_batch", "strings_to_host", "strings_to_device",
+    "deferred_checks",
 ]
 
 _i64 = ctypes.c_int64
+
+
+class deferred_checks(object):
+  """Context manager: inside it the batched coder calls do not synchronise with the host to
+  look at their per-stream status words (capacity overflow on encode, corrupt string on
+  decode); the status tensors are collected and checked once, on exit.  This is what lets
+  several batches be in flight on different CUDA streams.  An encode that overflowed its slab
+  cannot be retried transparently in this mode: exit raises and the caller re-runs the batch
+  with a larger `cap`.  Per thread."""
+  _tls = __import__("threading").local()
+
+  def __enter__(self):
+    self._prev = getattr(self._tls, "pending", None)
+    self._tls.pending = []
+    return self
+
+  def __exit__(self, exc_type, exc, tb):
+    pending, self._tls.pending = self._tls.pending, self._prev
+    if exc_type is None:
+      self._verify(pending)
+    return False
+
+  def flush(self):
+    pending, self._tls.pending = self._tls.pending, []
+    self._verify(pending)
+
+  @staticmethod
+  def _verify(pending):
+    if not pending:
+      return
+    bad = torch.stack([(st != 0).any() for _, st in pending]).cpu().tolist()
+    for (what, _), b in zip(pending, bad):
+      if b:
+        if what == "encode":
+          raise _lib.CudaError("range encode output slab too small (deferred check): re-run "
+                               "the batch with a larger `cap`")
+        raise InvalidArgumentError(
+            "corrupt range-coded string (decoder ran past the end of a CDF)")
+
+  @classmethod
+  def collector(cls):
+    return getattr(cls._tls, "pending", None)
 
 
 def _shape_arr(shape):
@@ -89,6 +132,10 @@ def unbounded_index_range_encode_batch(data, index, cdf, cdf_size, offset, preci
         ctypes.c_int32(cdf.shape[0]), ctypes.c_int32(cdf.shape[1]), _lib.ptr(cdf_size),
         _lib.ptr(offset), int(precision), int(overflow_width), int(debug_level), _lib.ptr(out),
         _i64(cap), _lib.ptr(nbytes), _lib.ptr(status), _lib.stream_ptr(dev)))
+    pending = deferred_checks.collector()
+    if pending is not None:
+      pending.append(("encode", status))
+      break
     if attempt == 0 and S and bool((status != 0).any()):
       cap = int(nbytes.max().item())
       cap += (-cap) % 16
@@ -122,7 +169,10 @@ def unbounded_index_range_decode_batch(enc, nbytes, index, cdf, cdf_size, offset
       _i64(n), _lib.ptr(cdf), ctypes.c_int32(cdf.shape[0]), ctypes.c_int32(cdf.shape[1]),
       _lib.ptr(cdf_size), _lib.ptr(offset), int(precision), int(overflow_width),
       int(debug_level), _lib.ptr(out), _lib.ptr(status), _lib.stream_ptr(dev)))
-  if check and S and n and bool((status != 0).any()):
+  pending = deferred_checks.collector()
+  if pending is not None:
+    pending.append(("decode", status))
+  elif check and S and n and bool((status != 0).any()):
     raise InvalidArgumentError("corrupt range-coded string (decoder ran past the end of a CDF)")
   return out
 

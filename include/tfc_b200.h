@@ -44,6 +44,16 @@ const char* tfc_version(void);
 /* number of kernels this library has launched since load (bench.py's gpu_launches) */
 int64_t tfc_launch_count(void);
 
+/* Process-wide scheduling knobs (no effect on results).  The range coder is latency bound (one
+ * serial chain per image) and leaves most of each SM idle; a caller that overlaps it with the
+ * transforms of another batch on a second CUDA stream packs several coder streams into one CTA
+ * and keeps the persistent transform kernels off the SMs the coder occupies.
+ *   TFC_CFG_SM_BUDGET              SMs (= CTAs) a persistent transform kernel may use; 0 = all
+ *   TFC_CFG_CODER_STREAMS_PER_CTA  1..4 coder streams per CTA; 0 = automatic (1 while S <= #SMs) */
+#define TFC_CFG_SM_BUDGET 1
+#define TFC_CFG_CODER_STREAMS_PER_CTA 2
+int tfc_configure(int key, int value);
+
 /* ------------------------------------------------------------------------------------------
  * Entropy coding — replaces the five custom ops of cc/ops/range_coding_ops.cc
  * ---------------------------------------------------------------------------------------- */
@@ -213,7 +223,13 @@ typedef struct {
   int32_t act;              /* tfc_activation */
   int32_t in_dtype, out_dtype;
   int32_t impl;
+  int32_t flags;            /* TFC_CONV_* bits */
 } tfc_conv_desc;
+
+/* The workspace already holds the repacked weights (and gamma) written by an earlier call with
+ * the same layer parameters and the same workspace: skip the repack kernels.  The weight area
+ * sits at the start of the workspace and does not depend on n/h/w. */
+#define TFC_CONV_WEIGHTS_STAGED 1
 
 size_t tfc_signal_conv2d_workspace(const tfc_conv_desc* desc);
 int tfc_signal_conv2d(const tfc_conv_desc* desc, const void* d_in, const float* d_w,

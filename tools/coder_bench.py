@@ -27,10 +27,14 @@ def main():
   ap.add_argument("--sigma-scale", type=float, default=1.0)
   ap.add_argument("--rows-max", type=int, default=40, help="indexes drawn from [0, rows-max)")
   ap.add_argument("--cpu", action="store_true", help="also time the CPU checker, all threads")
+  ap.add_argument("--pack", type=int, default=0, help="coder streams per CTA (tfc_configure)")
   args = ap.parse_args()
   from compression_b200.python.layers import entropy_models
   from compression_b200.python.ops import range_coding_ops as rc
   dev = torch.device("cuda", 0)
+  if args.pack:
+    import compression_b200
+    compression_b200.configure(coder_streams_per_cta=args.pack)
   table = np.exp(np.linspace(np.log(0.11), np.log(256), 64))
   gc = entropy_models.GaussianConditional(None, table)
   gc.build_tables(dev)
