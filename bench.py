@@ -41,7 +41,7 @@ FLOP_PER_IMAGE_C2 = 149.31e9   # encode 75.61 + decode 73.70 GFLOP 
 def parse_args():
   ap = argparse.ArgumentParser()
   ap.add_argument("--gpus", type=int, default=1)
-  ap.add_argument("--steps", type=int, default=5)
+  ap.add_argument("--steps", type=int, default=20)
   ap.add_argument("--warmup", type=int, default=3)
   ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
   ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
@@ -49,10 +49,10 @@ def parse_args():
   ap.add_argument("--cpu-sample-images", type=int, default=1)
   ap.add_argument("--no-cpu-baseline", action="store_true")
   ap.add_argument("--verbose", action="store_true", help="stage/layer breakdown on stderr")
-  ap.add_argument("--depth", type=int, default=3,
+  ap.add_argument("--depth", type=int, default=6,
                   help="batches in flight on separate CUDA streams (1: strictly serial steps)")
-  ap.add_argument("--coder-sms", type=int, default=32,
-                  help="SMs the transform kernels leave to the range coder when depth > 1")
+  ap.add_argument("--tiles-per-cta", type=int, default=8,
+                  help="transform kernels: tiles per CTA when depth > 1 (0: persistent grid)")
   ap.add_argument("--coder-pack", type=int, default=4, help="coder streams per CTA (depth > 1)")
   return ap.parse_args()
 
@@ -263,7 +263,8 @@ def run_b200(args):
       dist.barrier()
     torch.cuda.synchronize()
 
-  pipe = model.pipeline(args.depth, args.coder_sms, args.coder_pack)
+  pixels_per_step = batch * h * w
+  pipe = model.pipeline(args.depth, args.tiles_per_cta, args.coder_pack)
 
   with pipe:
     pipe.roundtrip_device([x_dev] * max(args.warmup, 3))
@@ -288,15 +289,25 @@ def run_b200(args):
     ms_per_step = float(ms.item()) / args.steps
 
     # e2e: same metric through host buffers (H2D image, D2H strings, H2D strings, D2H x_hat)
-    pipe.roundtrip_host([x_u8_host] * min(args.depth, 2))
+    seen = {"strings": 0, "pixels": 0}
+
+    def on_result(k, compressed, x_hat_u8):
+      seen["strings"] = (sum(len(b) for b in compressed.string) +
+                         sum(len(b) for b in compressed.side_string))
+      seen["pixels"] += int(x_hat_u8.shape[0]) * int(x_hat_u8.shape[1]) * int(x_hat_u8.shape[2])
+
+    pipe.roundtrip_host([x_u8_host] * (args.depth + 1), on_result)
     barrier()
+    seen["pixels"] = 0
     t0 = time.perf_counter()
-    res = pipe.roundtrip_host([x_u8_host] * args.steps)
+    pipe.roundtrip_host([x_u8_host] * args.steps, on_result)
     torch.cuda.synchronize()
     e2e_s = torch.tensor([time.perf_counter() - t0], device=dev)
-    string_bytes = (sum(len(b) for b in res[-1][0].string) +
-                    sum(len(b) for b in res[-1][0].side_string))
-    del res
+    assert seen["pixels"] == args.steps * pixels_per_step, "e2e: not every batch came back"
+    string_bytes = seen["strings"]
+    if world > 1:
+      dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_ms = float(e2e_s.item()) * 1e3 / args.steps
     h2d_bytes, d2h_bytes = int(pipe.h2d_bytes), int(pipe.d2h_bytes)
     if world > 1:
       dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
@@ -304,6 +315,7 @@ def run_b200(args):
 
   # the conv kernels alone, one batch, nothing else on the GPU (explains the roofline figure
   # measured under concurrency above)
+  model.decompress(model.compress(x_dev))      # stage weights for this stream, warm the caches
   timer.pairs, timed_pairs = [], timer.pairs
   timer.on = True
   model.decompress(model.compress(x_dev))
@@ -338,7 +350,10 @@ def run_b200(args):
                              % (w, h, batch, args.workload),
                  "weights": "random-init seed 0", "l2": "inputs_exceed_l2 (%.0f MB images)"
                  % (x_dev.numel() * 4 / 1e6), "parallelism": "batch-sharded x%d" % world,
-                 "conv_impl": args.conv_impl},
+                 "conv_impl": args.conv_impl,
+                 "pipeline": {"batches_in_flight": args.depth,
+                              "tiles_per_cta": args.tiles_per_cta if args.depth > 1 else 0,
+                              "coder_streams_per_cta": args.coder_pack if args.depth > 1 else 0}},
       "e2e": {"value": world * pixels / (e2e_ms * 1e-3) / 1e6, "unit": "MPix/s",
               "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
               "string_bytes_per_step": int(string_bytes), "ms_per_step": e2e_ms},
@@ -355,8 +370,7 @@ def run_b200(args):
                                 "frac": flops_step / (conv_ms_isolated * 1e-3) / 1e12 / peak,
                                 "note": "same kernels, one batch alone on the GPU (all SMs)"},
                    "note": "timed region: kernels bracketed per launch while the range coder "
-                           "of other batches shares the GPU (transform kernels on %d SMs)"
-                           % (148 - args.coder_sms if args.depth > 1 else 148)},
+                           "of other batches shares the GPU"},
   }
   if not args.no_cpu_baseline and world == 1:
     images = max(1, args.cpu_sample_images)

@@ -96,10 +96,10 @@ def to_device(x, dtype, device=None):
   return t.to(device=device, dtype=dtype).contiguous()
 
 
-CFG_SM_BUDGET, CFG_CODER_STREAMS_PER_CTA = 1, 2
+CFG_SM_BUDGET, CFG_CODER_STREAMS_PER_CTA, CFG_TILES_PER_CTA = 1, 2, 3
 
 
-def configure(sm_budget=None, coder_streams_per_cta=None):
+def configure(sm_budget=None, coder_streams_per_cta=None, tiles_per_cta=None):
   """Process-wide scheduling knobs of the library (tfc_configure): `sm_budget` = SMs the
   persistent transform kernels may occupy (0: all), `coder_streams_per_cta` = range-coder
   streams packed into one CTA (0: automatic).  No effect on results."""
@@ -108,3 +108,5 @@ def configure(sm_budget=None, coder_streams_per_cta=None):
     check(L.tfc_configure(CFG_SM_BUDGET, int(sm_budget)))
   if coder_streams_per_cta is not None:
     check(L.tfc_configure(CFG_CODER_STREAMS_PER_CTA, int(coder_streams_per_cta)))
+  if tiles_per_cta is not None:
+    check(L.tfc_configure(CFG_TILES_PER_CTA, int(tiles_per_cta)))

@@ -8,6 +8,7 @@ std::string& last_error_ref() {
 std::atomic<int64_t> g_launches{0};
 std::atomic<int> g_sm_budget{0};
 std::atomic<int> g_coder_pack{0};
+std::atomic<int> g_tiles_per_cta{0};
 }  // namespace tfc
 
 extern "C" const char* tfc_last_error(void) { return tfc::last_error_ref().c_str(); }
@@ -24,6 +25,11 @@ extern "C" int tfc_configure(int key, int value) {
       if (value < 0 || value > 4)
         return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "coder streams per CTA must be in [0, 4]");
       tfc::g_coder_pack.store(value);
+      return TFC_OK;
+    case TFC_CFG_TILES_PER_CTA:
+      if (value < 0 || value > 4096)
+        return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "tiles per CTA must be in [0, 4096]");
+      tfc::g_tiles_per_cta.store(value);
       return TFC_OK;
     default:
       return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "unknown configuration key %d", key);

@@ -15,6 +15,7 @@ namespace tfc {
 std::string& last_error_ref();
 extern std::atomic<int64_t> g_launches;
 extern std::atomic<int> g_sm_budget;   // SMs the persistent transform kernels may occupy (0: all)
+extern std::atomic<int> g_tiles_per_cta;  // transform kernels: tiles per CTA (0: persistent grid)
 extern std::atomic<int> g_coder_pack;  // range-coder streams per CTA (0: one CTA per stream when
                                        // the SMs allow it — lowest latency)
 
@@ -53,6 +54,8 @@ inline int persistent_grid() {
   const int n = num_sms();
   return (b > 0 && b < n) ? b : n;
 }
+
+inline int tiles_per_cta() { return g_tiles_per_cta.load(std::memory_order_relaxed); }
 
 inline int num_sms() {
   static int sms = 0;

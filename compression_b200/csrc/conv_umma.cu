@@ -58,6 +58,7 @@ struct Params {
   int32_t th, tw;                   // tile shape, th*tw == 128
   int32_t tiles_h, tiles_w;
   int32_t num_tiles;
+  int32_t chunk;                    // tiles per CTA (0: persistent grid)
   int32_t npad;                     // UMMA N (cout rounded up to 16)
   int32_t act;
   int32_t out_f32;
@@ -141,6 +142,12 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = bars->tmem_base;
+  // persistent (chunk == 0): tiles b, b + grid, ...; chunked: `chunk` consecutive tiles per CTA,
+  // many more CTAs than SMs, so the hardware places them on whatever SMs are free (used when
+  // the range coder of another batch occupies part of the GPU)
+  const int tile0 = p.chunk ? (int)blockIdx.x * p.chunk : (int)blockIdx.x;
+  const int tile1 = p.chunk ? min(tile0 + p.chunk, p.num_tiles) : p.num_tiles;
+  const int tile_step = p.chunk ? 1 : (int)gridDim.x;
   const uint32_t idesc = make_idesc_bf16(kTileM, p.npad);
 
   auto tile_coords = [&](int tile, int& phase, int& n, int& i0, int& j0) {
@@ -169,7 +176,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
           if (++stage == kStages) { stage = 0; ph ^= 1; }
         }
       };
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
         int phase, n, i0, j0;
         tile_coords(tile, phase, n, i0, j0);
         const int nk = (p.phase_start[phase + 1] - p.phase_start[phase]) * kchunks;
@@ -216,7 +223,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
         }
         umma_commit(&bars->d2_full);
       };
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
         int phase, n, i0, j0;
         tile_coords(tile, phase, n, i0, j0);
         const int acc = it & 1;
@@ -249,7 +256,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     uint32_t it = 0;
     uint32_t xs[GDN ? NC * 16 : 1];                  // x = D1 + bias as packed bf16 pairs
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
       int phase, n, i0, j0;
       tile_coords(tile, phase, n, i0, j0);
       const int acc = it & 1;
@@ -588,7 +595,9 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
     map_g = map_w;
   }
   const size_t smem = smem_bytes(p.npad, d.cout, gdn);
-  const int grid = std::min(p.num_tiles, persistent_grid());
+  p.chunk = tiles_per_cta();
+  const int grid = p.chunk ? (p.num_tiles + p.chunk - 1) / p.chunk
+                           : std::min(p.num_tiles, persistent_grid());
   void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const Params) = nullptr;
   if (!gdn) {
     kern = conv_umma_kernel<0, 0>;

@@ -44,6 +44,7 @@ struct UpParams {
   int32_t lo_h, lo_w;               // halo before the interior
   int32_t ih, iw;                   // interior (input pixels) per tile
   int32_t tiles_h, tiles_w, num_tiles;
+  int32_t chunk;                    // tiles per CTA (0: persistent grid)
   int32_t npad, ld;                 // GEMM N, row stride (floats) of the staged accumulator tile
   int32_t kchunks, stages;
   int32_t relu, out_f32;
@@ -109,6 +110,12 @@ conv_upthin_kernel(const __grid_constant__ CUtensorMap map_a,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = bars->tmem_base;
+  // persistent (chunk == 0): tiles b, b + grid, ...; chunked: `chunk` consecutive tiles per CTA,
+  // many more CTAs than SMs, so the hardware places them on whatever SMs are free (used when
+  // the range coder of another batch occupies part of the GPU)
+  const int tile0 = p.chunk ? (int)blockIdx.x * p.chunk : (int)blockIdx.x;
+  const int tile1 = p.chunk ? min(tile0 + p.chunk, p.num_tiles) : p.num_tiles;
+  const int tile_step = p.chunk ? 1 : (int)gridDim.x;
 
   auto tile_coords = [&](int tile, int& n, int& i0, int& j0) {
     const int per_img = p.tiles_h * p.tiles_w;
@@ -127,7 +134,7 @@ conv_upthin_kernel(const __grid_constant__ CUtensorMap map_a,
         tma_load_2d(sw + kc * w_chunk, &map_w, &bars->w_full, kc * kBlockK, 0);
       int stage = 0;
       uint32_t ph = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      for (int tile = tile0; tile < tile1; tile += tile_step) {
         int n, i0, j0;
         tile_coords(tile, n, i0, j0);
         for (int kc = 0; kc < p.kchunks; ++kc) {
@@ -145,7 +152,7 @@ conv_upthin_kernel(const __grid_constant__ CUtensorMap map_a,
       mbar_wait(&bars->w_full, 0);
       int stage = 0;
       uint32_t ph = 0, it = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
         const int acc = it & 1;
         mbar_wait(&bars->d_empty[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
@@ -173,7 +180,7 @@ conv_upthin_kernel(const __grid_constant__ CUtensorMap map_a,
     const int nout = OH * OW;
     const int taps_n = p.kw * p.cout;                // accumulator columns per kernel row
     uint32_t it = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
       int n, i0, j0;
       tile_coords(tile, n, i0, j0);
       const int acc = it & 1;
@@ -406,7 +413,9 @@ int conv_upthin(const tfc_conv_desc& d, const void* in, const float* w, const fl
                     pl.ih == 6 && pl.iw == 14;
   auto kern = fast ? conv_upthin_kernel<true> : conv_upthin_kernel<false>;
   TFC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
-  const int grid = std::min(p.num_tiles, persistent_grid());
+  p.chunk = tiles_per_cta() * 4;    // small tiles: four times the chunk of the big-tile kernel
+  const int grid = p.chunk ? (p.num_tiles + p.chunk - 1) / p.chunk
+                           : std::min(p.num_tiles, persistent_grid());
   kern<<<grid, kThreads, pl.smem, st>>>(map_a, map_w, p);
   TFC_LAUNCHED("conv_upthin_kernel");
   return TFC_OK;

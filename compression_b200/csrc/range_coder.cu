@@ -695,9 +695,9 @@ extern "C" int tfc_unbounded_index_range_decode(
     q.rows = rows; q.cols = cols; q.precision = precision; q.overflow_width = overflow_width;
     q.out = d_out; q.status = d_status; q.S = S; q.n = n;
     const int mp = v4_max_puts(overflow_width);
-    q.round = std::max(32, std::min(v4::kRoundMax, (v4::kLinMax - 8) / 2 / mp / 32 * 32));
-    q.round_words = q.round * mp;
-    if (2 * q.round_words + 8 > v4::kLinMax)
+    q.round = std::max(32, std::min(v4::kRoundMax, (v4::kLinMax - 16) / 2 / mp / 32 * 32));
+    q.round_words = (q.round * mp + 3) / 4 * 4;
+    if (2 * q.round_words + 16 > v4::kLinMax)
       return tfc::fail(TFC_ERR_UNIMPLEMENTED, "overflow_width %d needs a larger stream window", overflow_width);
     q.max_digits = (32 + overflow_width - 1) / overflow_width;
     q.table_bytes = v4_table_budget(rows, cols);

@@ -144,6 +144,23 @@ struct DecState {
   }
 };
 
+// Escape tail (unbounded_index_range_coding_kernels.cc:336-360): digits of the uniform 2^ow
+// alphabet; returns the zig-zag decoded value relative to `top` (= max_value of the row).
+__device__ __forceinline__ int32_t decode_escape(DecState& d, int ow, int max_digits, int32_t top) {
+  const uint32_t all1 = (1u << ow) - 1u;
+  const int sh = 16 - ow;
+  int nd = 0;
+  uint32_t u;
+  do { u = d.digit(sh, all1); nd += (int)u; } while (u == all1 && nd <= max_digits);
+  if (nd > max_digits) { d.corrupt = true; nd = max_digits; }
+  uint32_t x = 0;
+  for (int q = 0; q < nd; ++q) {
+    const uint32_t dg = d.digit(sh, all1);
+    if (q * ow < 32) x |= dg << (q * ow);
+  }
+  return (x & 1u) ? -(int32_t)(x >> 1) - 1 : (int32_t)(x >> 1) + top;
+}
+
 // General symbol (any row), called by the whole chain warp: the decoder state is replicated in
 // every lane, so each lane evaluates ONE candidate entry of the row and a ballot picks the
 // bracket — a 32-ary search, one step for rows of up to 33 entries (every EntropyBottleneck
@@ -184,20 +201,7 @@ __device__ __forceinline__ int32_t decode_general(DecState& d, const Tables& tb,
   }
   d.narrow(a, top ? d.span1 : b1 - 1u);
   int32_t v = lo - 1;
-  if (v == len - 2) {
-    const uint32_t all1 = (1u << ow) - 1u;
-    const int sh = 16 - ow;
-    int nd = 0;
-    uint32_t u;
-    do { u = d.digit(sh, all1); nd += (int)u; } while (u == all1 && nd <= max_digits);
-    if (nd > max_digits) { d.corrupt = true; nd = max_digits; }
-    uint32_t x = 0;
-    for (int q = 0; q < nd; ++q) {
-      const uint32_t dg = d.digit(sh, all1);
-      if (q * ow < 32) x |= dg << (q * ow);
-    }
-    v = (x & 1u) ? -(int32_t)(x >> 1) - 1 : (int32_t)(x >> 1) + v;
-  }
+  if (v == len - 2) v = decode_escape(d, ow, max_digits, v);
   return v;
 }
 
@@ -223,7 +227,7 @@ struct DecParamsV4 {
 };
 
 constexpr int kRecPad = 8;     // the chain prefetches records up to 7 past the round's end
-constexpr int kLinMax = 4608;  // words of one linear stream window (>= 2 * round words + 8)
+constexpr int kLinMax = 4608;  // words of one linear stream window (>= 2 * round words + 16)
 
 __host__ __device__ inline size_t dec_pair_bytes() {
   return (size_t)2 * (kRoundMax + kRecPad) * 16   // records
@@ -255,30 +259,44 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
   // ctrl[r & 1]: stream position (in words) at which round r starts
   const int bar = 1 + pair;
   const int R = p.round;
-  const uint32_t win = 2u * (uint32_t)p.round_words + 8u;    // <= kLinMax
+  // Window of round r+1: starts at the stream position round r started at, rounded down to 8
+  // words (16-byte loads), and must reach the last word round r+1 can touch.  Worst case that
+  // is 2 * round_words + 16 words (every symbol an escape with all its digits); the helper
+  // fills only what streams without escape bursts need — a word per symbol — and the chain,
+  // which checks its read position once per group of symbols, completes the window itself in
+  // the rare case it gets near the end of the filled part.
+  const uint32_t win_max = 2u * (uint32_t)p.round_words + 16u;                 // <= kLinMax
+  const uint32_t win_typ = min(win_max, (2u * (uint32_t)p.round + 72u + 7u) & ~7u);
+  const uint8_t* src = p.enc + s * p.cap;
+  const uint32_t len = (uint32_t)max(p.nbytes[s], 0);
+  const bool vec = (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+  // dst[k] = stream word first + k for k in [k0, k1) (big-endian pairs, zeros past the end);
+  // first, k0 and k1 are multiples of 8
+  auto fill = [&](uint16_t* dst, uint32_t first, uint32_t k0, uint32_t k1) {
+#pragma unroll 2
+    for (uint32_t c = k0 / 8u + lane; c < k1 / 8u; c += 32) {
+      const uint32_t at = 2u * (first + 8u * c);
+      if (vec && at + 16u <= len) {
+        uint4 v = __ldg(reinterpret_cast<const uint4*>(src + at));
+        v.x = __byte_perm(v.x, 0, 0x2301); v.y = __byte_perm(v.y, 0, 0x2301);
+        v.z = __byte_perm(v.z, 0, 0x2301); v.w = __byte_perm(v.w, 0, 0x2301);
+        *reinterpret_cast<uint4*>(dst + 8u * c) = v;
+      } else {
+        for (uint32_t e = 0; e < 8u; ++e) {
+          const uint32_t b0 = at + 2u * e;
+          uint32_t v = 0;
+          if (b0 < len) v = (uint32_t)__ldg(src + b0) << 8;
+          if (b0 + 1 < len) v |= (uint32_t)__ldg(src + b0 + 1);
+          dst[8u * c + e] = (uint16_t)v;
+        }
+      }
+    }
+  };
   const int64_t rounds = (p.n + R - 1) / R;
   const int32_t* idx = p.index + s * p.index_stride;
 
   if (helper) {
-    const uint8_t* src = p.enc + s * p.cap;
-    const uint32_t len = (uint32_t)max(p.nbytes[s], 0);
-    const bool even = (reinterpret_cast<uintptr_t>(src) & 1) == 0;
     int32_t* out = p.out + s * p.n;
-    auto fill = [&](uint16_t* dst, uint32_t first) {   // dst[k] = stream word first + k
-#pragma unroll 4
-      for (uint32_t k = lane; k < win; k += 32) {
-        const uint32_t at = 2u * (first + k);
-        uint32_t v = 0;
-        if (even && at + 1 < len) {
-          const uint32_t h = __ldg(reinterpret_cast<const uint16_t*>(src + at));
-          v = __byte_perm(h, 0, 0x4401);
-        } else {
-          if (at < len) v = (uint32_t)__ldg(src + at) << 8;
-          if (at + 1 < len) v |= (uint32_t)__ldg(src + at + 1);
-        }
-        dst[k] = (uint16_t)v;
-      }
-    };
     auto build = [&](int64_t r) {
       const int64_t base = r * R;
       const int cnt = (int)min((int64_t)R, p.n - base);
@@ -305,7 +323,7 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
         out[base + j] = (c == 0xFFu ? ev[j] : (int32_t)c) + off;
       }
     };
-    fill(lin, 0);
+    fill(lin, 0, 0, win_typ);
     build(0);
     pair_barrier(bar);
     for (int64_t r = 0; r < rounds; ++r) {
@@ -313,7 +331,7 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
       const uint32_t pos = ctrl[r & 1];
       if (r + 1 < rounds) {
         build(r + 1);
-        fill(lin + ((r + 1) & 1) * kLinMax, pos);
+        fill(lin + ((r + 1) & 1) * kLinMax, pos & ~7u, 0, win_typ);
       }
       if (r > 0) flush(r - 1);
       pair_barrier(bar);
@@ -346,6 +364,16 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
     int32_t* ev = vals + (r & 1) * kRoundMax;
     uint8_t* cb = codes + (r & 1) * kRoundMax;
     const uint32_t lin_r = lin_s + (uint32_t)(r & 1) * (kLinMax * 2);
+    // reads stay inside the part of the window the helper filled; past `lim` the chain warp
+    // completes the window itself (escape bursts only)
+    uint32_t lim = lin_r + 2u * (win_typ - 16u);
+    auto guard = [&]() {
+      if (wa > lim) {
+        fill(lin + (r & 1) * kLinMax, win_first, win_typ, win_max);
+        __syncwarp();
+        lim = 0xFFFFFFFFu;
+      }
+    };
 
     // One symbol of a 5-entry row: three multiplies, compares and selects, no branch.  `ok`
     // goes (and stays) false when a symbol needs the general path — escape, any other row
@@ -361,12 +389,14 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
       rem -= a;
       span = hi - a;
       *dst = (uint8_t)(p2 ? 2 : (p1 ? 1 : 0));
-      if (span <= 65536u) {
-        span <<= 16;
-        rem = rem * 65536u + w0;
-        w0 = lds16(wa);
-        wa += 2;
-      }
+      // renormalisation without a branch: the word after w0 is read unconditionally (the
+      // window is padded) and everything is a select
+      const bool rn = span <= 65536u;
+      const uint32_t wn = lds16(wa);
+      span = rn ? (span << 16) : span;
+      rem = rn ? (rem * 65536u + w0) : rem;
+      w0 = rn ? wn : w0;
+      wa += rn ? 2u : 0u;
     };
 
     int j = 0;
@@ -375,6 +405,7 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
     // one symbol at a time: fast step for 5-entry rows, the warp-wide search otherwise
     auto careful = [&](int stop) {
       for (; j < stop; ++j, ++rp, ++cp) {
+        guard();
         const uint4 q = rp[0];
         const uint32_t k_rem = rem, k_span = span, k_w0 = w0, k_wa = wa;
         int start = (int)q.x, len = (int)q.y;
@@ -384,6 +415,38 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
           if (ok) continue;
           const int4 ri = t.rowinfo[q.w];     // escape (or span == 2^32) on a fast-class row
           start = ri.x; len = ri.y;
+        } else if (len <= 33) {
+          // Rows of up to 33 entries (every EntropyBottleneck row, Gaussian rows up to
+          // sigma ~ 5): lane l tests entry l + 1, one ballot finds the symbol, two shuffles
+          // fetch its bounds; the renormalisation is all selects.
+          const uint32_t span1 = span - 1u;
+          const int k = min(1 + lane, len - 1);
+          const uint32_t ck = t.at(start + k), cq = t.at(start + k - 1);
+          const uint32_t tk = scale16(span1, ck), tq = scale16(span1, cq);
+          const bool over = (ck >> 16) != 0u;
+          const uint32_t mk = __ballot_sync(0xFFFFFFFFu, over || tk > rem);
+          int f = __ffs(mk) - 1;
+          if (mk == 0u) { d.corrupt = true; f = len - 2; }
+          const uint32_t a = __shfl_sync(0xFFFFFFFFu, tq, f);
+          const uint32_t b1 = __shfl_sync(0xFFFFFFFFu, tk, f);
+          const bool top = __shfl_sync(0xFFFFFFFFu, (int)over, f) != 0;
+          const uint32_t ns1 = (top ? span1 : b1 - 1u) - a;
+          const bool rn = (ns1 >> 16) == 0u;
+          const uint32_t wn = lds16(wa);
+          rem -= a;
+          span = (rn ? ((ns1 << 16) | 0xFFFFu) : ns1) + 1u;
+          rem = rn ? ((rem << 16) | w0) : rem;
+          w0 = rn ? wn : w0;
+          wa += rn ? 2u : 0u;
+          int32_t v = f;
+          if (v == len - 2) {
+            d.rem = rem; d.span1 = span - 1u; d.w0 = w0; d.wa = wa;
+            v = decode_escape(d, ow, p.max_digits, v);
+            rem = d.rem; span = d.span1 + 1u; w0 = d.w0; wa = d.wa;
+          }
+          ev[j] = v;
+          *cp = 0xFF;
+          continue;
         }
         d.rem = k_rem; d.span1 = k_span - 1u; d.w0 = k_w0; d.wa = k_wa;
         const int32_t v = decode_general(d, t, start, len, ow, p.max_digits, lane);
@@ -401,7 +464,9 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
         bool ok = true;
         uint32_t s_rem, s_span, s_w0, s_wa;
         do {
+          guard();
           s_rem = rem; s_span = span; s_w0 = w0; s_wa = wa;
+          if (q0.z == 0u || q1.z == 0u || q2.z == 0u || q3.z == 0u) { ok = false; break; }
           step(q0, cp, ok);     q0 = rp[4];
           step(q1, cp + 1, ok); q1 = rp[5];
           step(q2, cp + 2, ok); q2 = rp[6];
@@ -419,8 +484,8 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
     if (lane == 0) ctrl[(r + 1) & 1] = p_next;
     pair_barrier(bar);
     const uint32_t lin_n = lin_s + (uint32_t)((r + 1) & 1) * (kLinMax * 2);
-    wa = lin_n + 2u * (p_next + 1u - p_cur);
-    win_first = p_cur;
+    win_first = p_cur & ~7u;
+    wa = lin_n + 2u * (p_next + 1u - win_first);
     p_cur = p_next;
   }
   if (lane == 0 && p.status) p.status[s] = d.corrupt ? TFC_STREAM_CORRUPT : TFC_STREAM_OK;

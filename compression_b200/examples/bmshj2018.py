@@ -114,29 +114,28 @@ class Pipeline(object):
   kernels are latency bound and occupy a few SMs for milliseconds while the transforms are
   throughput bound.  The pipeline runs batch k's coder concurrently with batch k+1's
   transforms: every batch gets its own stream (its own kernels stay ordered, no events
-  needed), the coder packs `coder_streams_per_cta` images into one CTA and the persistent
-  transform kernels leave `coder_sms` SMs to it.  Results are those of compress()/decompress()
+  needed), the coder packs `coder_streams_per_cta` images into one CTA and the transform
+  kernels switch from a persistent grid to `tiles_per_cta` tiles per CTA so that the hardware
+  scheduler fills whatever SMs the coder leaves free.  Results are those of compress()/decompress()
   called batch by batch.
   """
 
-  def __init__(self, model, depth=3, coder_sms=32, coder_streams_per_cta=4):
+  def __init__(self, model, depth=3, tiles_per_cta=8, coder_streams_per_cta=4):
     from compression_b200 import _lib
     self.model = model
     self.depth = max(1, int(depth))
     self.streams = [torch.cuda.Stream(device=model.device) for _ in range(self.depth)]
     self._lib = _lib
-    self._sms = torch.cuda.get_device_properties(model.device).multi_processor_count
-    self.coder_sms = int(coder_sms) if self.depth > 1 else 0
+    self.tiles_per_cta = int(tiles_per_cta) if self.depth > 1 else 0
     self.pack = int(coder_streams_per_cta) if self.depth > 1 else 0
 
   def __enter__(self):
     if self.depth > 1:
-      self._lib.configure(sm_budget=max(1, self._sms - self.coder_sms),
-                          coder_streams_per_cta=self.pack)
+      self._lib.configure(coder_streams_per_cta=self.pack, tiles_per_cta=self.tiles_per_cta)
     return self
 
   def __exit__(self, *exc):
-    self._lib.configure(sm_budget=0, coder_streams_per_cta=0)
+    self._lib.configure(coder_streams_per_cta=0, tiles_per_cta=0)
     return False
 
   def _fork(self):
@@ -161,58 +160,96 @@ class Pipeline(object):
       self._join(cur)
     return outs
 
-  def roundtrip_host(self, batches_u8):
-    """batches_u8: pinned host uint8 [B,H,W,3] -> list of (Compressed with host strings,
-    x_hat uint8 on the host).  Per batch: image H2D, compress, strings D2H, strings H2D,
-    decompress, x_hat D2H; the host only waits for batch k's strings after it has queued
-    batch k+depth-1's compress."""
+  def roundtrip_host(self, batches_u8, on_result=None):
+    """batches_u8: pinned host uint8 [B,H,W,3] tensors.  Per batch: image H2D, compress,
+    strings D2H, strings H2D, decompress, x_hat D2H.  The host only waits for batch k's
+    strings after it has queued the compress of the next depth-1 batches.
+
+    Pinned staging buffers are allocated once per pipeline slot and reused (page-locking
+    memory synchronises the device).  Results are delivered in order through
+    `on_result(k, compressed, x_hat_u8)`: `compressed` holds the strings as Python bytes,
+    `x_hat_u8` is a view of the slot's pinned buffer, valid during the callback.  Without a
+    callback the results are copied out and returned as a list."""
     from compression_b200.python.ops import range_coding_ops as rc
     model, dev = self.model, self.model.device
-    front, results = {}, [None] * len(batches_u8)
+    n, nslots = len(batches_u8), self.depth + 1
+    slots = getattr(self, "_slots", None)
+    if slots is None or len(slots) != nslots:
+      slots = self._slots = [dict() for _ in range(nslots)]
+    out_list = [] if on_result is None else None
     self.h2d_bytes = self.d2h_bytes = 0     # per batch, counted from the tensors copied
     cur = self._fork()
 
+    def pinned(slot, name, shape, dtype):
+      t = slot.get(name)
+      if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
+        t = slot[name] = torch.empty(tuple(shape), dtype=dtype, pin_memory=True)
+      return t
+
+    def deliver(slot):
+      k = slot.pop("pending", None)
+      if k is None:
+        return
+      slot["done"].synchronize()
+      if on_result is not None:
+        on_result(k, slot["host"], slot["x_hat"])
+      else:
+        out_list.append((slot["host"], slot["x_hat"].clone()))
+
     def issue_front(k):
-      st = self.streams[k % self.depth]
+      slot, st = slots[k % nslots], self.streams[k % self.depth]
+      deliver(slot)                      # the slot's previous batch must be out of its buffers
       with torch.cuda.stream(st):
         x = batches_u8[k].to(dev, non_blocking=True).float() / 255
         c = model.compress(x)
-        pinned = []
-        for slab, nbytes in (c.string, c.side_string):
-          hs = torch.empty(slab.shape, dtype=torch.uint8, pin_memory=True)
-          hn = torch.empty(nbytes.shape, dtype=torch.int32, pin_memory=True)
+        staged = []
+        for name, (slab, nbytes) in (("y", c.string), ("z", c.side_string)):
+          hs = pinned(slot, name + "_slab", slab.shape, torch.uint8)
+          hn = pinned(slot, name + "_len", nbytes.shape, torch.int32)
           hs.copy_(slab, non_blocking=True)
           hn.copy_(nbytes, non_blocking=True)
-          pinned.append((hs, hn))
-        if k == 0:
-          self.h2d_bytes += batches_u8[k].numel()
-          self.d2h_bytes += sum(hs.numel() + 4 * hn.numel() for hs, hn in pinned)
+          staged.append((hs, hn))
         ev = torch.cuda.Event()
         ev.record(st)
-      front[k] = (c, pinned, ev)
+      slot["front"] = (c, staged, ev)
+      if k == 0:
+        self.h2d_bytes += batches_u8[k].numel()
+        self.d2h_bytes += sum(hs.numel() + 4 * hn.numel() for hs, hn in staged)
 
     def issue_back(k):
-      c, pinned, ev = front.pop(k)
+      slot, st = slots[k % nslots], self.streams[k % self.depth]
+      c, staged, ev = slot.pop("front")
       ev.synchronize()
       strings = []
-      for hs, hn in pinned:
+      for hs, hn in staged:
         a, nb = hs.numpy(), hn.numpy()
         strings.append([a[i, :nb[i]].tobytes() for i in range(len(nb))])
       host = Compressed(strings[0], strings[1], c.x_shape, c.y_shape, c.z_shape)
-      st = self.streams[k % self.depth]
       with torch.cuda.stream(st):
-        dc = model.to_device(host)
+        dev_strings = []
+        for name, ss in (("y", host.string), ("z", host.side_string)):
+          cap = max([len(b) for b in ss] + [1])
+          cap += (-cap) % 16
+          up = pinned(slot, name + "_up", (len(ss), cap), torch.uint8)
+          ul = pinned(slot, name + "_uplen", (len(ss),), torch.int32)
+          ua, la = up.numpy(), ul.numpy()
+          for i, b in enumerate(ss):
+            ua[i, :len(b)] = np.frombuffer(b, np.uint8)
+            la[i] = len(b)
+          dev_strings.append((up.to(dev, non_blocking=True), ul.to(dev, non_blocking=True)))
+          if k == 0:
+            self.h2d_bytes += up.numel() + 4 * ul.numel()
+        dc = Compressed(dev_strings[0], dev_strings[1], c.x_shape, c.y_shape, c.z_shape)
         x_hat = quantize_image(model.decompress(dc))
-        out = torch.empty(x_hat.shape, dtype=torch.uint8, pin_memory=True)
+        out = pinned(slot, "x_hat", x_hat.shape, torch.uint8)
         out.copy_(x_hat, non_blocking=True)
-        if k == 0:
-          self.h2d_bytes += sum(t.numel() * t.element_size() for pair in (dc.string, dc.side_string)
-                                for t in pair)
-          self.d2h_bytes += out.numel()
-      results[k] = (host, out)
+        done = torch.cuda.Event()
+        done.record(st)
+      slot["host"], slot["done"], slot["pending"] = host, done, k
+      if k == 0:
+        self.d2h_bytes += out.numel()
 
     with rc.deferred_checks():
-      n = len(batches_u8)
       for k in range(n + self.depth - 1):
         if k < n:
           issue_front(k)
@@ -220,8 +257,11 @@ class Pipeline(object):
         if 0 <= j < n:
           issue_back(j)
       self._join(cur)
+      first = max(0, n - nslots)
+      for k in range(first, n):           # remaining deliveries, oldest first
+        deliver(slots[k % nslots])
     cur.synchronize()
-    return results
+    return out_list
 
 
 class Bmshj2018Model(object):
@@ -295,8 +335,8 @@ class Bmshj2018Model(object):
     return dict(x_hat=x_hat, y=y, z=z, sigma=sigma, y_hat=y_hat, y_likelihoods=y_lik,
                 z_likelihoods=z_lik, eval_bpp=float(bpp))
 
-  def pipeline(self, depth=3, coder_sms=32, coder_streams_per_cta=4):
-    return Pipeline(self, depth, coder_sms, coder_streams_per_cta)
+  def pipeline(self, depth=3, tiles_per_cta=8, coder_streams_per_cta=4):
+    return Pipeline(self, depth, tiles_per_cta, coder_streams_per_cta)
 
   # ---- host-side strings --------------------------------------------------------------------
   @staticmethod
