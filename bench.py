@@ -35,6 +35,9 @@ WORKLOADS = {
     "c3": (1080, 1920, 32, 192),
     "tiny": (128, 192, 4, 192),
 }
+# DRAM traffic of the conv launches of one step as ncu measures it; per-kernel figures are in
+# profiles/r1d_conv_full_summary.md (the four large layers), the 17-launch sum is not captured
+NCU_TRAFFIC_BYTES_PER_STEP = None
 FLOP_PER_IMAGE_C2 = 149.31e9   # encode 75.61 + decode 73.70 GFLOP per 768x512 image
 
 
@@ -324,6 +327,23 @@ def run_b200(args):
   conv_ms_isolated = timer.total_ms()
   timer.pairs, isolated_pairs = timed_pairs, timer.pairs
 
+  # the range coder alone (latency bound: one serial chain per image): CUDA-event time of the
+  # y encode / decode launches, one CTA per stream
+  y, z, sigma = model.analyse(x_dev)
+  gc = model._conditional(sigma)
+  ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+  string = gc.compress_device(y)
+  gc.decompress_device(string, torch.bfloat16)
+  ev[0].record()
+  string = gc.compress_device(y)
+  ev[1].record()
+  gc.decompress_device(string, torch.bfloat16)
+  ev[2].record()
+  torch.cuda.synchronize()
+  y_symbols = int(y[0].numel())
+  coder_ms = (ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]))
+  del y, z, sigma, string
+
   if rank != 0:
     if world > 1:
       dist.destroy_process_group()
@@ -359,18 +379,29 @@ def run_b200(args):
               "string_bytes_per_step": int(string_bytes), "ms_per_step": e2e_ms},
       "gpu_launches": int(launches),
       "clocks": clk,
+      # The transforms dominate the GPU's SM-time (the coder holds ~16 CTAs for longer, see
+      # "coder").  achieved/frac: the 17 conv launches of one batch timed per launch with CUDA
+      # events, the batch alone on the GPU; "in_pipeline": the same brackets inside the timed
+      # region, where they include waiting for SMs shared with other batches' kernels.
       "roofline": {"bound": "tensor", "kernel": "SignalConv2D kernels (%d launches/step)" % n_conv,
-                   "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                   "frac": achieved / peak, "traffic": None,
+                   "achieved": flops_step / (conv_ms_isolated * 1e-3) / 1e12, "peak": peak,
+                   "unit": "TFLOP/s",
+                   "frac": flops_step / (conv_ms_isolated * 1e-3) / 1e12 / peak,
+                   "traffic": NCU_TRAFFIC_BYTES_PER_STEP,
                    "peak_source": peaks["source"] + " bf16 sustained",
-                   "share_of_step": conv_ms_step / ms_per_step,
-                   "flops_per_step": flops_step,
-                   "isolated": {"ms_per_step": conv_ms_isolated,
-                                "achieved": flops_step / (conv_ms_isolated * 1e-3) / 1e12,
-                                "frac": flops_step / (conv_ms_isolated * 1e-3) / 1e12 / peak,
-                                "note": "same kernels, one batch alone on the GPU (all SMs)"},
-                   "note": "timed region: kernels bracketed per launch while the range coder "
-                           "of other batches shares the GPU"},
+                   "ms_per_step": conv_ms_isolated, "flops_per_step": flops_step,
+                   "in_pipeline": {"ms_per_step": conv_ms_step, "achieved": achieved,
+                                   "frac": achieved / peak,
+                                   "share_of_step": conv_ms_step / ms_per_step}},
+      "coder": {"bound": "latency", "kernel": "encode/decode_unbounded_v4 (y, one CTA per image)",
+                "symbols_per_stream": y_symbols, "streams": batch,
+                "encode_ms": coder_ms[0], "decode_ms": coder_ms[1],
+                "encode_cycles_per_symbol": coder_ms[0] * 1e-3 * (clk["sm_mhz"] or 1965.0) * 1e6
+                                            / y_symbols,
+                "decode_cycles_per_symbol": coder_ms[1] * 1e-3 * (clk["sm_mhz"] or 1965.0) * 1e6
+                                            / y_symbols,
+                "hbm_frac": batch * y_symbols * 12.6 / (sum(coder_ms) * 1e-3) / 1e9
+                            / peaks["hbm_gbs"]},
   }
   if not args.no_cpu_baseline and world == 1:
     images = max(1, args.cpu_sample_images)
