@@ -111,3 +111,51 @@ def test_results_independent_of_batch_position(setup):
   a = model.to_host(model.compress(x.cuda()))
   b = model.to_host(model.compress(x[1:].cuda()))
   assert a.string[1] == b.string[0] and a.side_string[1] == b.side_string[0]
+
+
+def test_sharded_batches_code_to_the_same_strings(setup):
+  """the batch is split contiguously across ranks with no collective; whatever the
+  number of shards, every image must code to the bytes of the unsharded run and decode to the
+  same pixels (here the shards run one after the other on one GPU)."""
+  from compression_b200 import parallel
+  model, cpu, _ = setup
+  g = torch.Generator().manual_seed(9)
+  x = torch.rand((5, 64, 96, 3), generator=g, dtype=torch.float32).cuda()
+  full = model.to_host(model.compress(x))
+  x_hat_full = model.decompress(model.to_device(full))
+  for world in (2, 3, 5):
+    strings, side, recon = [], [], []
+    for lo, hi in parallel.shard_bounds(5, world):
+      part = model.to_host(model.compress(x[lo:hi]))
+      strings += part.string
+      side += part.side_string
+      recon.append(model.decompress(model.to_device(part)))
+    assert strings == full.string and side == full.side_string
+    assert torch.equal(torch.cat(recon), x_hat_full)
+
+
+@pytest.mark.parametrize("depth", [1, 3])
+def test_pipeline_matches_batch_by_batch(setup, depth):
+  """The multi-stream pipeline (packed coder CTAs, chunked transform kernels, deferred status
+  checks) returns exactly what compress()/decompress() return batch by batch."""
+  from compression_b200.examples import bmshj2018
+  model, cpu, _ = setup
+  g = torch.Generator().manual_seed(11)
+  batches = [torch.rand((3, 48, 80, 3), generator=g, dtype=torch.float32) for _ in range(5)]
+  want = []
+  for x in batches:
+    c = model.compress(x.cuda())
+    want.append((model.to_host(c), model.decompress(c)))
+  with model.pipeline(depth=depth) as pipe:
+    got = pipe.roundtrip_device([x.cuda() for x in batches])
+    for (host, x_hat), g_hat in zip(want, got):
+      assert torch.equal(x_hat, g_hat)
+    u8 = [(x * 255).round().to(torch.uint8).pin_memory() for x in batches]
+    seen = []
+    pipe.roundtrip_host(u8, lambda k, c, xh: seen.append((k, c, xh.clone())))
+  assert [k for k, _, _ in seen] == list(range(5))
+  for k, c, xh in seen:
+    ref = model.compress(u8[k].cuda().float() / 255)
+    ref_host = model.to_host(ref)
+    assert c.string == ref_host.string and c.side_string == ref_host.side_string
+    assert torch.equal(xh, bmshj2018.quantize_image(model.decompress(ref)).cpu())
