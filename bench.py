@@ -49,7 +49,8 @@ def parse_args():
   ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
   ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
   ap.add_argument("--conv-impl", type=int, default=0, help="0 auto, 1 CUDA-core, 2 tcgen05")
-  ap.add_argument("--cpu-sample-images", type=int, default=1)
+  ap.add_argument("--cpu-sample-images", type=int, default=0,
+                  help="images per CPU step (0: one per host thread, at most the batch)")
   ap.add_argument("--no-cpu-baseline", action="store_true")
   ap.add_argument("--verbose", action="store_true", help="stage/layer breakdown on stderr")
   ap.add_argument("--depth", type=int, default=6,
@@ -211,22 +212,38 @@ def cpu_arm(h, w, images, steps, warmup, weights=None, seed=0):
   return images * h * w / sec / 1e6, sec * 1e3, coder.kind, threads
 
 
+def workload_name(args):
+  h, w, batch, nf = WORKLOADS[args.workload]
+  return "bmshj2018-%d encode+decode %dx%d batch %d per GPU (%s)" % (nf, w, h, batch, args.workload)
+
+
+def cpu_sample_images(args):
+  h, w, batch, nf = WORKLOADS[args.workload]
+  n = args.cpu_sample_images if args.cpu_sample_images > 0 else host_threads()
+  return max(1, min(n, batch))
+
+
 def run_reference(args):
+  """The reference's CPU implementation of the path on the host cores: its own C++ range coder
+  (oracle/_ref, one thread per image) + the torch-CPU float32 restatement of the transforms
+  (TensorFlow 1.15 cannot run in this image).  Rank 0 only."""
   rank = int(os.environ.get("RANK", "0"))
   if rank != 0:
     return
   h, w, batch, nf = WORKLOADS[args.workload]
-  images = max(1, args.cpu_sample_images)
-  mpix, ms, kind, cores = cpu_arm(h, w, images, max(1, args.steps), min(args.warmup, 1))
+  images = cpu_sample_images(args)
+  steps, warmup = max(1, args.steps), max(0, min(args.warmup, 1))
+  mpix, ms, kind, cores = cpu_arm(h, w, images, steps, warmup)
   sample = "%d of %d images of %dx%d per step, all %d host threads" % (images, batch, w, h, cores)
   line = {
       "impl": "reference", "metric": "MPix/s encode+decode, bmshj2018 hyperprior",
-      "value": mpix, "unit": "MPix/s", "n_gpus": args.gpus, "steps": max(1, args.steps),
-      "warmup": min(args.warmup, 1), "ms_per_step": ms, "higher_is_better": True,
+      "value": mpix, "unit": "MPix/s", "n_gpus": args.gpus, "steps": steps,
+      "warmup": warmup, "ms_per_step": ms, "higher_is_better": True,
       "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-      "config": {"workload": "bmshj2018-192 encode+decode %dx%d" % (w, h), "sample": sample,
-                 "note": "CPU restatement (torch-CPU float32 transforms) + %s range coder; "
-                         "TF 1.15 cannot run in this image" % kind},
+      "config": {"workload": workload_name(args), "weights": "random-init seed 0",
+                 "sample": sample,
+                 "note": "CPU: torch-CPU float32 transforms + %s range coder (one thread per "
+                         "image); TF 1.15 cannot run in this image" % kind},
       "cpu_baseline": {"value": mpix, "unit": "MPix/s", "cores": cores, "kind": kind,
                        "sample": sample},
       "e2e": {"value": mpix, "unit": "MPix/s", "h2d_bytes_per_step": 0,
@@ -366,8 +383,7 @@ def run_b200(args):
       "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
       "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
       "data": "synthetic",
-      "config": {"workload": "bmshj2018-192 encode+decode %dx%d batch %d per GPU (%s)"
-                             % (w, h, batch, args.workload),
+      "config": {"workload": workload_name(args),
                  "weights": "random-init seed 0", "l2": "inputs_exceed_l2 (%.0f MB images)"
                  % (x_dev.numel() * 4 / 1e6), "parallelism": "batch-sharded x%d" % world,
                  "conv_impl": args.conv_impl,
@@ -404,10 +420,10 @@ def run_b200(args):
                             / peaks["hbm_gbs"]},
   }
   if not args.no_cpu_baseline and world == 1:
-    images = max(1, args.cpu_sample_images)
-    mpix, cms, kind, cores = cpu_arm(h, w, images, 1, 0, weights=model.export_weights())
+    images = cpu_sample_images(args)
+    mpix, cms, kind, cores = cpu_arm(h, w, images, 2, 1, weights=model.export_weights())
     line["cpu_baseline"] = {"value": mpix, "unit": "MPix/s", "cores": cores, "kind": kind,
-                            "sample": "%d of %d images of %dx%d, 1 step, all host threads; "
+                            "sample": "%d of %d images of %dx%d, 2 steps after 1 warm-up, all host threads; "
                                       "torch-CPU f32 transforms + %s range coder"
                                       % (images, batch, w, h, kind)}
   print(json.dumps(line))
