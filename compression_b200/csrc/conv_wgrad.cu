@@ -1,0 +1,221 @@
+// Weight gradient of SignalConv2D (bls2017 training step): in the reference this
+// is the filter gradient TF derives for tf.nn.conv2d / conv2d_backprop_input
+// (signal_conv.py:516-518, :693-695).  In the normalised form of tfc_b200.h,
+//     out[n,i,j,o] = sum_{a,b,c} U[n, i*sd + a - pt, j*sd + b - pl, c] * w[a,b,c,o]
+// (U = input zero-stuffed by su), the gradient is, per tap (a,b), a [cin x P] . [P x cout] GEMM
+// over the P pixels where the tap lands inside the image:
+//     dw[a,b,c,o] = sum_{n,i,j} U[n, i*sd + a - pt, j*sd + b - pl, c] * dout[n,i,j,o].
+// NHWC makes both operands pixel-major with the channels contiguous — exactly the col-major A /
+// row-major B fragments of the warp-level MMA (mma.sync via nvcuda::wmma, bf16 in, fp32
+// accumulate), so tiles go global -> shared -> fragments without a transpose.  Pixels are split
+// over `kslices` CTAs per (tap, channel tile); partial sums are added with fp32 atomics.
+//
+// (The forward transforms are tcgen05; the filter gradient is ~1/3 of a training step's FLOPs
+// and is the next candidate for a tcgen05 kernel with MN-major operand descriptors.)
+#include <cuda_bf16.h>
+#include <mma.h>
+
+#include <algorithm>
+#include <cmath>
+
+#include "common.cuh"
+#include "conv_common.cuh"
+
+namespace {
+
+using namespace nvcuda;
+
+constexpr int kBM = 64, kBN = 64, kBK = 32;
+constexpr int kLd = 72;                  // padded leading dimension (multiple of 8)
+constexpr int kThreads = 128;
+
+struct WgradParams {
+  int32_t n, h, w, cin, ho, wo, cout, kh, kw, sd, su, pt, pl;
+  int32_t ctiles, otiles, kslices;
+  int64_t pixels;                        // enumerated pixels: outputs (su == 1) or inputs (su > 1)
+  const __nv_bfloat16* x;
+  const __nv_bfloat16* dy;
+  float* dw;
+};
+
+__global__ void __launch_bounds__(kThreads)
+conv_wgrad_kernel(const WgradParams p) {
+  __shared__ __align__(32) __nv_bfloat16 xs[kBK * kLd];
+  __shared__ __align__(32) __nv_bfloat16 ys[kBK * kLd];
+  __shared__ int64_t x_off[kBK], y_off[kBK];
+  __shared__ __align__(32) float acc_s[kBM * kBN];
+
+  const int tile = blockIdx.x;
+  const int ct = tile / p.otiles, ot = tile - ct * p.otiles;
+  const int tap = blockIdx.y;
+  const int a = tap / p.kw, b = tap - a * p.kw;
+  const int c0 = ct * kBM, o0 = ot * kBN;
+  const int warp = threadIdx.x >> 5;
+  const int wm = (warp >> 1) * 32, wn = (warp & 1) * 32;
+
+  wmma::fragment<wmma::accumulator, 16, 16, 16, float> acc[2][2];
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 2; ++j) wmma::fill_fragment(acc[i][j], 0.f);
+
+  const int64_t per = (p.pixels + p.kslices - 1) / p.kslices;
+  const int64_t p_begin = (int64_t)blockIdx.z * per;
+  const int64_t p_end = min(p.pixels, p_begin + per);
+  const bool vec_x = (p.cin & 7) == 0, vec_y = (p.cout & 7) == 0;
+  const int gw = p.su > 1 ? p.w : p.wo, gh = p.su > 1 ? p.h : p.ho;   // enumeration grid
+
+  for (int64_t base = p_begin; base < p_end; base += kBK) {
+    if (threadIdx.x < kBK) {
+      const int64_t q = base + threadIdx.x;
+      int64_t xo = -1, yo = -1;
+      if (q < p_end) {
+        const int j = (int)(q % gw);
+        const int i = (int)((q / gw) % gh);
+        const int nn = (int)(q / ((int64_t)gw * gh));
+        if (p.su > 1) {           // (i, j) input pixel; the tap sends it to one output pixel
+          const int oi = p.su * i - a + p.pt, oj = p.su * j - b + p.pl;
+          if (oi >= 0 && oi < p.ho && oj >= 0 && oj < p.wo) {
+            xo = (((int64_t)nn * p.h + i) * p.w + j) * p.cin;
+            yo = (((int64_t)nn * p.ho + oi) * p.wo + oj) * p.cout;
+          }
+        } else {                  // (i, j) output pixel; the tap reads one input pixel
+          const int yi = i * p.sd + a - p.pt, xj = j * p.sd + b - p.pl;
+          if (yi >= 0 && yi < p.h && xj >= 0 && xj < p.w) {
+            xo = (((int64_t)nn * p.h + yi) * p.w + xj) * p.cin;
+            yo = (((int64_t)nn * p.ho + i) * p.wo + j) * p.cout;
+          }
+        }
+      }
+      x_off[threadIdx.x] = xo;
+      y_off[threadIdx.x] = yo;
+    }
+    __syncthreads();
+    // tiles: 32 pixel rows x 64 channels, zero where the tap is outside / channels run out
+    for (int e = threadIdx.x; e < kBK * 8; e += kThreads) {
+      const int r = e >> 3, ch = (e & 7) * 8;
+      uint4 vx = make_uint4(0, 0, 0, 0), vy = make_uint4(0, 0, 0, 0);
+      const int64_t xo = x_off[r], yo = y_off[r];
+      if (xo >= 0) {
+        if (vec_x) {
+          if (c0 + ch < p.cin) vx = *reinterpret_cast<const uint4*>(p.x + xo + c0 + ch);
+        } else {
+          __nv_bfloat16 t[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            t[k] = (c0 + ch + k < p.cin) ? p.x[xo + c0 + ch + k] : __float2bfloat16(0.f);
+          vx = *reinterpret_cast<const uint4*>(t);
+        }
+        if (vec_y) {
+          if (o0 + ch < p.cout) vy = *reinterpret_cast<const uint4*>(p.dy + yo + o0 + ch);
+        } else {
+          __nv_bfloat16 t[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            t[k] = (o0 + ch + k < p.cout) ? p.dy[yo + o0 + ch + k] : __float2bfloat16(0.f);
+          vy = *reinterpret_cast<const uint4*>(t);
+        }
+      }
+      *reinterpret_cast<uint4*>(xs + r * kLd + ch) = vx;
+      *reinterpret_cast<uint4*>(ys + r * kLd + ch) = vy;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k0 = 0; k0 < kBK; k0 += 16) {
+      wmma::fragment<wmma::matrix_a, 16, 16, 16, __nv_bfloat16, wmma::col_major> fa[2];
+      wmma::fragment<wmma::matrix_b, 16, 16, 16, __nv_bfloat16, wmma::row_major> fb[2];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) wmma::load_matrix_sync(fa[i], xs + k0 * kLd + wm + 16 * i, kLd);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) wmma::load_matrix_sync(fb[j], ys + k0 * kLd + wn + 16 * j, kLd);
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) wmma::mma_sync(acc[i][j], fa[i], fb[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+      wmma::store_matrix_sync(acc_s + (wm + 16 * i) * kBN + wn + 16 * j, acc[i][j], kBN,
+                              wmma::mem_row_major);
+  __syncthreads();
+  float* dst = p.dw + (int64_t)tap * p.cin * p.cout;
+  for (int e = threadIdx.x; e < kBM * kBN; e += kThreads) {
+    const int c = c0 + e / kBN, o = o0 + e % kBN;
+    if (c < p.cin && o < p.cout) {
+      const float v = acc_s[e];
+      if (p.kslices == 1) dst[(int64_t)c * p.cout + o] = v;
+      else atomicAdd(dst + (int64_t)c * p.cout + o, v);
+    }
+  }
+}
+
+// fused Adam over a flat parameter bucket (tf.train.AdamOptimizer semantics: the bias
+// correction is folded into the step size, epsilon is NOT scaled)
+__global__ void adam_kernel(float* __restrict__ param, const float* __restrict__ grad,
+                            float* __restrict__ m, float* __restrict__ v, int64_t n, float lr_t,
+                            float beta1, float beta2, float eps, float grad_scale) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const float g = grad[i] * grad_scale;
+    const float mi = beta1 * m[i] + (1.f - beta1) * g;
+    const float vi = beta2 * v[i] + (1.f - beta2) * g * g;
+    m[i] = mi;
+    v[i] = vi;
+    param[i] -= lr_t * mi / (sqrtf(vi) + eps);
+  }
+}
+
+}  // namespace
+
+extern "C" int tfc_signal_conv2d_wgrad(const tfc_conv_desc* d, const void* d_x_bf16,
+                                       const void* d_dy_bf16, float* d_dw, void* stream) {
+  if (!d || d->n < 0 || d->h <= 0 || d->w <= 0 || d->cin <= 0 || d->ho <= 0 || d->wo <= 0 ||
+      d->cout <= 0 || d->kh <= 0 || d->kw <= 0 || d->sd <= 0 || d->su <= 0)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "bad conv geometry");
+  if (d->sd > 1 && d->su > 1)
+    return tfc::fail(TFC_ERR_UNIMPLEMENTED, "strides_down and strides_up together");
+  if ((reinterpret_cast<uintptr_t>(d_x_bf16) & 15) || (reinterpret_cast<uintptr_t>(d_dy_bf16) & 15))
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "conv buffers must be 16-byte aligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int taps = d->kh * d->kw;
+  TFC_CUDA(cudaMemsetAsync(d_dw, 0, (size_t)taps * d->cin * d->cout * sizeof(float), st));
+  if (d->n == 0) return TFC_OK;
+  WgradParams p{};
+  p.n = d->n; p.h = d->h; p.w = d->w; p.cin = d->cin; p.ho = d->ho; p.wo = d->wo;
+  p.cout = d->cout; p.kh = d->kh; p.kw = d->kw; p.sd = d->sd; p.su = d->su;
+  p.pt = d->pad_top; p.pl = d->pad_left;
+  p.ctiles = (d->cin + kBM - 1) / kBM;
+  p.otiles = (d->cout + kBN - 1) / kBN;
+  p.pixels = d->su > 1 ? (int64_t)d->n * d->h * d->w : (int64_t)d->n * d->ho * d->wo;
+  const int64_t ctas = (int64_t)taps * p.ctiles * p.otiles;
+  const int64_t want = 4 * (int64_t)tfc::num_sms();
+  int64_t ks = std::max<int64_t>(1, (want + ctas - 1) / ctas);
+  ks = std::min<int64_t>(ks, std::max<int64_t>(1, p.pixels / 1024));
+  p.kslices = (int)std::min<int64_t>(ks, 65535);
+  p.x = static_cast<const __nv_bfloat16*>(d_x_bf16);
+  p.dy = static_cast<const __nv_bfloat16*>(d_dy_bf16);
+  p.dw = d_dw;
+  dim3 grid(p.ctiles * p.otiles, taps, p.kslices);
+  conv_wgrad_kernel<<<grid, kThreads, 0, st>>>(p);
+  TFC_LAUNCHED("conv_wgrad_kernel");
+  return TFC_OK;
+}
+
+extern "C" int tfc_adam_step(float* d_param, const float* d_grad, float* d_m, float* d_v,
+                             int64_t n, float lr, float beta1, float beta2, float eps,
+                             int64_t step, float grad_scale, void* stream) {
+  if (n < 0 || step < 1) return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "bad Adam arguments");
+  if (n == 0) return TFC_OK;
+  // tf.train.AdamOptimizer: lr_t = lr * sqrt(1 - beta2^t) / (1 - beta1^t)
+  const double lr_t = (double)lr * std::sqrt(1.0 - std::pow((double)beta2, (double)step)) /
+                      (1.0 - std::pow((double)beta1, (double)step));
+  const int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)tfc::num_sms() * 8);
+  adam_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      d_param, d_grad, d_m, d_v, n, (float)lr_t, beta1, beta2, eps, grad_scale);
+  TFC_LAUNCHED("adam_kernel");
+  return TFC_OK;
+}

@@ -1,0 +1,247 @@
+"""Factorised-prior codec of Ballé, Laparra & Simoncelli (2017) — mirror of the model in
+`/root/reference/examples/bls2017.py` (transforms :70-127, train :130-202, compress :205-271,
+decompress :274-305) over the B200 kernels.
+
+  Bls2017Model.compress / decompress   inference path: convs with GDN fused in the epilogue,
+                                       EntropyBottleneck symbols + batched range coder
+  Bls2017Trainer.step                  one training step: forward with uniform noise, R-D loss,
+                                       backward (conv gradients through the CUDA kernels),
+                                       gradient all-reduce, two Adam updates, CDF table update
+"""
+import collections
+
+import numpy as np
+import torch
+
+from compression_b200.python.layers import entropy_models
+from compression_b200.python.layers import gdn
+from compression_b200.python.layers import signal_conv
+from compression_b200.python.ops import math_ops
+from compression_b200.python.ops import train_ops
+
+Compressed = collections.namedtuple("Compressed", ["string", "x_shape", "y_shape"])
+
+
+def quantize_image(image):
+  """bls2017.py:57-60."""
+  return torch.clamp(torch.round(image * 255), 0, 255).to(torch.uint8)
+
+
+class _Sequential(object):
+
+  def __init__(self, layers):
+    self._layers = layers
+
+  def build(self, channels, device, generator=None):
+    for l in self._layers:
+      l.build(channels, device, generator)
+      channels = l.filters
+    return self
+
+  def __call__(self, tensor, out_dtype=torch.float32):
+    n = len(self._layers)
+    for i, layer in enumerate(self._layers):
+      tensor = layer(tensor, out_dtype=out_dtype if i == n - 1 else torch.bfloat16)
+    return tensor
+
+  @property
+  def layers(self):
+    return self._layers
+
+
+class AnalysisTransform(_Sequential):
+  """bls2017.py:70-97."""
+
+  def __init__(self, num_filters, impl=0):
+    C = signal_conv.SignalConv2D
+    super(AnalysisTransform, self).__init__([
+        C(num_filters, (9, 9), name="layer_0", corr=True, strides_down=4, padding="same_zeros",
+          use_bias=True, activation=gdn.GDN(name="gdn_0"), impl=impl),
+        C(num_filters, (5, 5), name="layer_1", corr=True, strides_down=2, padding="same_zeros",
+          use_bias=True, activation=gdn.GDN(name="gdn_1"), impl=impl),
+        C(num_filters, (5, 5), name="layer_2", corr=True, strides_down=2, padding="same_zeros",
+          use_bias=False, activation=None, impl=impl),
+    ])
+
+
+class SynthesisTransform(_Sequential):
+  """bls2017.py:100-127."""
+
+  def __init__(self, num_filters, impl=0):
+    C = signal_conv.SignalConv2D
+    super(SynthesisTransform, self).__init__([
+        C(num_filters, (5, 5), name="layer_0", corr=False, strides_up=2, padding="same_zeros",
+          use_bias=True, activation=gdn.GDN(name="igdn_0", inverse=True), impl=impl),
+        C(num_filters, (5, 5), name="layer_1", corr=False, strides_up=2, padding="same_zeros",
+          use_bias=True, activation=gdn.GDN(name="igdn_1", inverse=True), impl=impl),
+        C(3, (9, 9), name="layer_2", corr=False, strides_up=4, padding="same_zeros",
+          use_bias=True, activation=None, impl=impl),
+    ])
+
+
+class Bls2017Model(object):
+
+  def __init__(self, num_filters=128, device=None, seed=0, impl=0):
+    self.num_filters = int(num_filters)
+    self.device = torch.device(device) if device is not None else torch.device(
+        "cuda", torch.cuda.current_device())
+    g = torch.Generator().manual_seed(seed)
+    nf = self.num_filters
+    self.analysis_transform = AnalysisTransform(nf, impl).build(3, self.device, g)
+    self.synthesis_transform = SynthesisTransform(nf, impl).build(nf, self.device, g)
+    self.entropy_bottleneck = entropy_models.EntropyBottleneck()
+    self.entropy_bottleneck.build(nf, self.device, g)
+    self.entropy_bottleneck.update()
+
+  # ---- bls2017.py:205-271 ------------------------------------------------------------------
+  def compress(self, x):
+    x = x.to(self.device)
+    y = self.analysis_transform(x)
+    string = self.entropy_bottleneck.compress_device(y)
+    return Compressed(string, tuple(x.shape[1:-1]), tuple(y.shape[1:-1]))
+
+  # ---- bls2017.py:274-305 ------------------------------------------------------------------
+  def decompress(self, c):
+    nf = self.num_filters
+    y_hat = self.entropy_bottleneck.decompress_device(
+        c.string, tuple(c.y_shape) + (nf,), channels=nf, out_dtype=torch.bfloat16)
+    x_hat = self.synthesis_transform(y_hat)
+    return x_hat[:, :c.x_shape[0], :c.x_shape[1], :]
+
+  def evaluate(self, x):
+    """The --verbose branch of compress (bls2017.py:226-244)."""
+    y = self.analysis_transform(x)
+    y_hat, lik = self.entropy_bottleneck(y, training=False)
+    x_hat = self.synthesis_transform(y_hat.to(torch.bfloat16))[:, :x.shape[1], :x.shape[2], :]
+    num_pixels = float(np.prod(x.shape[:-1]))
+    bpp = torch.log(lik).sum() / (-np.log(2) * num_pixels)
+    mse = torch.mean((x * 255 - torch.clamp(torch.round(x_hat * 255), 0, 255)) ** 2)
+    return dict(x_hat=x_hat, y=y, y_hat=y_hat, likelihoods=lik, eval_bpp=float(bpp),
+                mse=float(mse))
+
+  @staticmethod
+  def to_host(c):
+    from compression_b200.python.ops import range_coding_ops as rc
+    return Compressed(rc.strings_to_host(*c.string), c.x_shape, c.y_shape)
+
+  def to_device(self, c):
+    from compression_b200.python.ops import range_coding_ops as rc
+    if isinstance(c.string, tuple):
+      return c
+    return Compressed(rc.strings_to_device(c.string, self.device), c.x_shape, c.y_shape)
+
+  def conv_layers(self):
+    return self.analysis_transform.layers + self.synthesis_transform.layers
+
+
+class Bls2017Trainer(object):
+  """One synchronous data-parallel training step (bls2017.py:156-185).
+
+  All trainable variables live in two flat buckets (main: kernels, biases, GDN parameters,
+  density network; aux: the quantiles), each with its own Adam state: the gradient exchange
+  is one all-reduce per bucket and each update one kernel.  `updates[0]` (the CDF table
+  rebuild) is a pure function of the then identical parameters, so every rank runs it locally.
+  """
+
+  def __init__(self, model, lmbda=0.01, main_lr=1e-4, aux_lr=1e-3):
+    self.model, self.lmbda = model, float(lmbda)
+    self.main_lr, self.aux_lr = float(main_lr), float(aux_lr)
+    eb = model.entropy_bottleneck
+    slots = []                       # (object, attribute[, index]) of every trainable
+    for l in model.conv_layers():
+      slots.append((l, "kernel_var", None))
+      if l.bias_var is not None:
+        slots.append((l, "bias_var", None))
+      if isinstance(l.activation, gdn.GDN):
+        slots.append((l.activation, "reparam_beta", None))
+        slots.append((l.activation, "reparam_gamma", None))
+    for name in ("matrices", "biases", "factors"):
+      for i in range(len(getattr(eb, name))):
+        slots.append((eb, name, i))
+    self._slots = slots
+    self.main = train_ops.FlatBucket([self._get(s) for s in slots], model.device)
+    for s, v in zip(slots, self.main.views):
+      self._set(s, v)
+    self.aux = train_ops.FlatBucket([eb.quantiles], model.device)
+    eb.quantiles = self.aux.views[0]
+    self._invalidate()
+
+  @staticmethod
+  def _get(slot):
+    obj, name, i = slot
+    v = getattr(obj, name)
+    return v if i is None else v[i]
+
+  @staticmethod
+  def _set(slot, value):
+    obj, name, i = slot
+    if i is None:
+      setattr(obj, name, value)
+    else:
+      getattr(obj, name)[i] = value
+
+  def _invalidate(self):
+    for l in self.model.conv_layers():
+      l.invalidate()
+
+  @property
+  def num_parameters(self):
+    return int(self.main.param.numel() + self.aux.param.numel())
+
+  # ---- forward with the training-time graph (bls2017.py:156-171) ----------------------------
+  @staticmethod
+  def _gdn(act, x):
+    """gdn.py:171-202 in torch ops: the 1x1 contraction is a plain GEMM."""
+    beta, gamma = act.beta_parameterizer(act.reparam_beta), act.gamma_parameterizer(act.reparam_gamma)
+    norm = (x * x).reshape(-1, x.shape[-1]) @ gamma + beta
+    norm = norm.reshape(x.shape)
+    return x * (torch.sqrt(norm) if act.inverse else torch.rsqrt(norm))
+
+  def _transform(self, seq, t):
+    for layer in seq.layers:
+      t = train_ops.signal_conv2d(layer, t if t.shape[-1] == 3 else t.to(torch.bfloat16))
+      if isinstance(layer.activation, gdn.GDN):
+        t = self._gdn(layer.activation, t)
+    return t
+
+  def _likelihood(self, y_tilde):
+    """entropy_models.py:626-658 + the bound of :181-184, differentiable."""
+    eb = self.model.entropy_bottleneck
+    c = y_tilde.shape[-1]
+    v = y_tilde.reshape(-1, c).t().reshape(c, 1, -1)
+    lower = eb._logits_cumulative(v - .5)
+    upper = eb._logits_cumulative(v + .5)
+    sign = -torch.sign(lower + upper).detach()
+    lik = torch.abs(torch.sigmoid(sign * upper) - torch.sigmoid(sign * lower))
+    lik = math_ops.lower_bound(lik, eb.likelihood_bound)
+    return lik.reshape(c, -1).t().reshape(y_tilde.shape)
+
+  def losses(self, x, noise=None):
+    """x float32 [B,H,W,3] in [0,1] -> dict(loss, bpp, mse, aux)."""
+    model = self.model
+    num_pixels = float(np.prod(x.shape[:-1]))
+    y = self._transform(model.analysis_transform, x)
+    if noise is None:
+      noise = torch.rand_like(y) - .5                         # entropy_models.py:605-607
+    y_tilde = y + noise
+    lik = self._likelihood(y_tilde)
+    x_tilde = self._transform(model.synthesis_transform, y_tilde)
+    bpp = torch.log(lik).sum() / (-np.log(2) * num_pixels)
+    mse = torch.mean((x - x_tilde) ** 2) * 255 ** 2
+    return dict(loss=self.lmbda * mse + bpp, bpp=bpp, mse=mse,
+                aux=model.entropy_bottleneck.losses[0], x_tilde=x_tilde)
+
+  def step(self, x, noise=None):
+    """train_op = group(main_step, aux_step, updates[0]) (bls2017.py:173-180)."""
+    self.main.zero_grad()
+    self.aux.zero_grad()
+    out = self.losses(x, noise)
+    out["loss"].backward()
+    out["aux"].backward()
+    scale = self.main.all_reduce()
+    self.aux.all_reduce()
+    train_ops.adam_step(self.main, self.main_lr, scale)
+    train_ops.adam_step(self.aux, self.aux_lr, scale)
+    self._invalidate()
+    self.model.entropy_bottleneck.update()
+    return {k: float(v.detach()) for k, v in out.items() if k != "x_tilde"}

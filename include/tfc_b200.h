@@ -241,6 +241,22 @@ int tfc_signal_conv2d(const tfc_conv_desc* desc, const void* d_in, const float* 
                       const float* d_bias, const float* d_beta, const float* d_gamma,
                       void* d_out, void* d_workspace, size_t workspace_bytes, void* stream);
 
+/* Filter gradient of the same convolution (training step of examples/bls2017.py:156-185; in the
+ * reference TF derives it from tf.nn.conv2d / conv2d_backprop_input):
+ *   d_dw[a,b,c,o] = sum_{n,i,j} U[n, i*sd + a - pad_top, j*sd + b - pad_left, c] * dout[n,i,j,o]
+ * d_x_bf16 [n,h,w,cin] and d_dy_bf16 [n,ho,wo,cout] are bfloat16, d_dw [kh,kw,cin,cout] float32
+ * (overwritten).  The input gradient needs no entry point of its own: it is tfc_signal_conv2d
+ * with sd and su swapped, the kernel flipped and transposed, and padding k-1-pad. */
+int tfc_signal_conv2d_wgrad(const tfc_conv_desc* desc, const void* d_x_bf16,
+                            const void* d_dy_bf16, float* d_dw, void* stream);
+
+/* One Adam update over a flat float32 bucket with tf.train.AdamOptimizer's arithmetic
+ * (bls2017.py:173-178): lr_t = lr*sqrt(1-beta2^t)/(1-beta1^t); p -= lr_t*m/(sqrt(v)+eps);
+ * the gradient is multiplied by grad_scale first (1/world_size after a sum all-reduce). */
+int tfc_adam_step(float* d_param, const float* d_grad, float* d_m, float* d_v, int64_t n,
+                  float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale,
+                  void* stream);
+
 /* Stand-alone GDN / IGDN on a channels_last tensor of `pixels` x `channels` (gdn.py:171-206). */
 int tfc_gdn(const void* d_x, int64_t pixels, int32_t channels, const float* d_beta,
             const float* d_gamma, int inverse, int in_dtype, int out_dtype, void* d_out,

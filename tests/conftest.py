@@ -37,3 +37,10 @@ def oracle():
   """The strongest checker available (reference build if present, else the port)."""
   from oracle import oracle_lib
   return oracle_lib.load("best")
+
+
+@pytest.fixture(scope="session")
+def tfc():
+  """The product package (needs the built libtfc_b200.so)."""
+  import compression_b200 as tfc_mod
+  return tfc_mod

@@ -1,0 +1,180 @@
+"""bls2017 training step: convolution gradients through the CUDA kernels against
+torch autograd on a float64 restatement of the same layer, the fused Adam kernel against
+tf.train.AdamOptimizer's formulas, and the whole step against a float32 torch restatement."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _static(value):
+  return lambda shape: torch.as_tensor(value)
+
+
+def _ref_conv(x, k, b, corr, sd, su):
+  """Differentiable float64 restatement of SignalConv2D (same_zeros, odd kernels), following
+  signal_conv.py:709-782 like oracle/tfc_np.py:signal_conv2d.  x NHWC, k [kh,kw,cin,cout]."""
+  kh, kw = k.shape[:2]
+  xn = x.permute(0, 3, 1, 2)
+  if corr and su == 1:
+    out = F.conv2d(F.pad(xn, (kw // 2, kw // 2, kh // 2, kh // 2)), k.permute(3, 2, 0, 1), stride=sd)
+  else:
+    assert not corr and sd == 1
+    n, _, h, w = xn.shape
+    p = kh // 2
+    full = F.conv_transpose2d(xn, k.permute(2, 3, 0, 1), stride=su)
+    full = F.pad(full, (0, su, 0, su))
+    out = full[:, :, p:p + h * su, p:p + w * su]
+  out = out.permute(0, 2, 3, 1)
+  return out + b if b is not None else out
+
+
+CASES = [
+    # cin, cout, k, corr, sd, su, H, W, input dtype
+    (64, 64, 5, True, 2, 1, 16, 24, torch.bfloat16),
+    (3, 128, 9, True, 4, 1, 32, 32, torch.float32),      # first analysis layer of bls2017
+    (128, 128, 5, True, 2, 1, 16, 16, torch.bfloat16),
+    (128, 128, 5, False, 1, 2, 8, 12, torch.bfloat16),
+    (128, 3, 9, False, 1, 4, 8, 8, torch.bfloat16),      # last synthesis layer of bls2017
+    (192, 192, 3, True, 1, 1, 10, 14, torch.bfloat16),
+]
+
+
+@pytest.mark.parametrize("cin,cout,k,corr,sd,su,H,W,in_dtype", CASES)
+def test_conv_gradients_match_autograd(tfc, cin, cout, k, corr, sd, su, H, W, in_dtype):
+  from compression_b200.python.ops import train_ops
+  rng = np.random.default_rng(21)
+  x = rng.integers(-3, 4, size=(2, H, W, cin)).astype(np.float32)
+  kern = (rng.integers(-4, 5, size=(k, k, cin, cout)) / 4.0).astype(np.float32)
+  kern *= (rng.random(size=kern.shape) < 0.25)
+  b = (rng.integers(-4, 5, size=cout) / 2.0).astype(np.float32)
+  layer = tfc.SignalConv2D(cout, (k, k), corr=corr, strides_down=sd, strides_up=su,
+                           padding="same_zeros", use_bias=True, kernel_parameterizer=None,
+                           kernel_initializer=_static(kern), bias_initializer=_static(b))
+  layer.build(cin, "cuda")
+  layer.kernel_var.requires_grad_()
+  layer.bias_var.requires_grad_()
+  xg = torch.from_numpy(x).cuda().to(in_dtype).requires_grad_()
+  out = train_ops.signal_conv2d(layer, xg)
+  dout = rng.integers(-2, 3, size=tuple(out.shape)).astype(np.float32)
+  out.backward(torch.from_numpy(dout).cuda())
+
+  xr = torch.from_numpy(x).double().requires_grad_()
+  kr = torch.from_numpy(kern).double().requires_grad_()
+  br = torch.from_numpy(b).double().requires_grad_()
+  ref = _ref_conv(xr, kr, br, corr, sd, su)
+  assert tuple(ref.shape) == tuple(out.shape)
+  ref.backward(torch.from_numpy(dout).double())
+
+  def close(got, want, what, tol=1e-5):
+    got, want = got.detach().double().cpu(), want.detach()
+    scale = want.abs().max().item() + 1e-9
+    err = (got - want).abs().max().item() / scale
+    assert err <= tol, (what, err, scale)
+
+  close(out, ref, "forward")
+  close(layer.kernel_var.grad, kr.grad, "filter gradient")
+  close(layer.bias_var.grad, br.grad, "bias gradient")
+  # the gradient of a bfloat16 activation is itself stored in bfloat16 (8 significand bits)
+  close(xg.grad.float(), xr.grad, "input gradient", 1e-5 if in_dtype == torch.float32 else 4e-3)
+
+
+def test_adam_kernel_follows_tf_adam(tfc):
+  from compression_b200.python.ops import train_ops
+  rng = np.random.default_rng(5)
+  p0 = rng.normal(size=1000).astype(np.float32)
+  bucket = train_ops.FlatBucket([torch.from_numpy(p0)], torch.device("cuda"))
+  p, m, v = p0.astype(np.float64), np.zeros(1000), np.zeros(1000)
+  lr, b1, b2, eps = 1e-3, 0.9, 0.999, 1e-8
+  for t in range(1, 6):
+    g = rng.normal(size=1000).astype(np.float32)
+    bucket.grad.copy_(torch.from_numpy(g))
+    train_ops.adam_step(bucket, lr, grad_scale=0.5)
+    gs = g.astype(np.float64) * 0.5
+    m = b1 * m + (1 - b1) * gs
+    v = b2 * v + (1 - b2) * gs * gs
+    p -= lr * np.sqrt(1 - b2 ** t) / (1 - b1 ** t) * m / (np.sqrt(v) + eps)
+    np.testing.assert_allclose(bucket.param.cpu().numpy(), p, rtol=2e-5, atol=2e-6)
+
+
+def _ref_losses(trainer, x, noise):
+  """The same graph in float32 torch ops only (no CUDA kernels of ours)."""
+  from compression_b200.python.layers import gdn
+  model = trainer.model
+
+  def run(seq, t):
+    for layer in seq.layers:
+      flip, _, _ = layer._plan()
+      t = _ref_conv(t, layer.kernel, layer.bias, layer.corr, layer.strides_down[0],
+                    layer.strides_up[0])
+      if isinstance(layer.activation, gdn.GDN):
+        t = trainer._gdn(layer.activation, t)
+    return t
+
+  y = run(model.analysis_transform, x)
+  y_tilde = y + noise
+  lik = trainer._likelihood(y_tilde)
+  x_tilde = run(model.synthesis_transform, y_tilde)
+  num_pixels = float(np.prod(x.shape[:-1]))
+  bpp = torch.log(lik).sum() / (-np.log(2) * num_pixels)
+  mse = torch.mean((x - x_tilde) ** 2) * 255 ** 2
+  return trainer.lmbda * mse + bpp
+
+
+def test_training_step_gradients_and_descent(tfc):
+  from compression_b200.examples import bls2017
+  model = bls2017.Bls2017Model(128, "cuda", seed=3)
+  trainer = bls2017.Bls2017Trainer(model, lmbda=0.01)
+  assert trainer.num_parameters > 1_700_000        # SURVEY: ~1.77 M trainables
+  g = torch.Generator().manual_seed(4)
+  x = torch.rand((4, 64, 64, 3), generator=g).cuda()
+  noise = (torch.rand((4, 4, 4, 128), generator=g) - .5).cuda()
+  # gradients of the kernel-backed graph vs the torch-only graph (bf16 operands vs float32)
+  trainer.main.zero_grad()
+  out = trainer.losses(x, noise)
+  out["loss"].backward()
+  got = trainer.main.grad.clone()
+  trainer.main.zero_grad()
+  ref = _ref_losses(trainer, x, noise)
+  ref.backward()
+  want = trainer.main.grad.clone()
+  assert abs(float(out["loss"]) - float(ref)) <= 2e-2 * abs(float(ref))
+  cos = torch.dot(got, want) / (got.norm() * want.norm())
+  assert cos > 0.995, float(cos)
+  assert (got - want).norm() <= 0.1 * want.norm()
+  # a few steps on a fixed batch: the R-D loss goes down, the aux loss too, tables stay valid
+  first = trainer.step(x, noise)
+  for _ in range(30):
+    last = trainer.step(x, noise)
+  assert np.isfinite(last["loss"]) and last["loss"] < first["loss"]
+  assert last["aux"] < first["aux"]
+  c = model.compress(x)
+  x_hat = model.decompress(c)
+  assert tuple(x_hat.shape) == (4, 64, 64, 3) and bool(torch.isfinite(x_hat).all())
+
+
+def test_bls2017_compress_decompress_roundtrip(tfc, oracle):
+  """BASELINE configs[0] wiring: strings decode (CPU reference coder) to the coded symbols."""
+  from compression_b200.examples import bls2017
+  model = bls2017.Bls2017Model(128, "cuda", seed=0)
+  g = torch.Generator().manual_seed(8)
+  x = torch.rand((2, 64, 96, 3), generator=g).cuda()
+  c = model.compress(x)
+  assert c.y_shape == (4, 6)
+  host = model.to_host(c)
+  eb = model.entropy_bottleneck
+  y = model.analysis_transform(x)
+  sym = eb._quantize_symbols(y).cpu().numpy()
+  idx = np.broadcast_to(np.arange(128, dtype=np.int32), sym.shape[1:])
+  cdf, ln, off = (eb._quantized_cdf.cpu().numpy(), eb._cdf_length.cpu().numpy(),
+                  eb._offset.cpu().numpy())
+  for b in range(2):
+    assert host.string[b] == oracle.ui_encode(sym[b], idx, cdf, ln, off, 16, 4)
+  x_hat = model.decompress(model.to_device(host))
+  assert tuple(x_hat.shape) == (2, 64, 96, 3)
+  y_hat = eb.decompress_device(c.string, (4, 6, 128), 128)
+  assert torch.equal(y_hat, eb._dequantize(eb._quantize_symbols(y)))
