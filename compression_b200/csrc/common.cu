@@ -22,8 +22,8 @@ extern "C" int tfc_configure(int key, int value) {
       tfc::g_sm_budget.store(value);
       return TFC_OK;
     case TFC_CFG_CODER_STREAMS_PER_CTA:
-      if (value < 0 || value > 4)
-        return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "coder streams per CTA must be in [0, 4]");
+      if (value < 0 || value > 8)
+        return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "coder streams per CTA must be in [0, 8]");
       tfc::g_coder_pack.store(value);
       return TFC_OK;
     case TFC_CFG_TILES_PER_CTA:

@@ -695,22 +695,31 @@ extern "C" int tfc_unbounded_index_range_decode(
     q.rows = rows; q.cols = cols; q.precision = precision; q.overflow_width = overflow_width;
     q.out = d_out; q.status = d_status; q.S = S; q.n = n;
     const int mp = v4_max_puts(overflow_width);
-    q.round = std::max(32, std::min(v4::kRoundMax, (v4::kLinMax - 16) / 2 / mp / 32 * 32));
-    q.round_words = (q.round * mp + 3) / 4 * 4;
-    if (2 * q.round_words + 16 > v4::kLinMax)
-      return tfc::fail(TFC_ERR_UNIMPLEMENTED, "overflow_width %d needs a larger stream window", overflow_width);
     q.max_digits = (32 + overflow_width - 1) / overflow_width;
     q.table_bytes = v4_table_budget(rows, cols);
     const int sms = tfc::num_sms();
     q.streams_per_cta = S <= sms ? 1 : (S <= 2 * (int64_t)sms ? 2 : 4);
     const int pack = tfc::g_coder_pack.load(std::memory_order_relaxed);
     if (pack > 0) q.streams_per_cta = (int)std::max<int64_t>(1, std::min<int64_t>(pack, S));
-    const size_t smem = (size_t)q.table_bytes + (size_t)q.streams_per_cta * v4::dec_pair_bytes();
+    // rounds as long as shared memory allows (fewer barriers), shorter when streams are packed
+    const size_t smem_max = 227 * 1024 - 1024;
+    auto geometry = [&](int round) {
+      q.round = round;
+      q.round_words = (round * mp + 3) / 4 * 4;
+      q.lin_words = (2 * q.round_words + 16 + 7) / 8 * 8;
+      return (size_t)q.table_bytes +
+             (size_t)q.streams_per_cta * v4::dec_pair_bytes(q.round, q.lin_words);
+    };
+    int round = std::max(32, std::min(v4::kRoundMax, (v4::kLinMax - 16) / 2 / mp / 32 * 32));
+    while (round > 32 && geometry(round) > smem_max) round -= 32;
+    while (q.streams_per_cta > 1 && geometry(round) > smem_max) --q.streams_per_cta;
+    const size_t smem = geometry(round);
+    if (smem > smem_max)
+      return tfc::fail(TFC_ERR_UNIMPLEMENTED, "overflow_width %d needs a larger stream window", overflow_width);
     static bool attr = false;
     if (!attr) {
       TFC_CUDA(cudaFuncSetAttribute(v4::decode_unbounded_v4,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)(kV4TableBudget + 16 + 4 * v4::dec_pair_bytes())));
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
       attr = true;
     }
     const int64_t blocks = (S + q.streams_per_cta - 1) / q.streams_per_cta;

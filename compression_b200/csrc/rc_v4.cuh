@@ -224,23 +224,26 @@ struct DecParamsV4 {
   int32_t round_words;    // bound on the stream words one round can consume
   int32_t table_bytes;    // shared-memory budget of the staged tables (16-byte multiple)
   int32_t streams_per_cta;
+  int32_t lin_words;      // words of one linear window (>= 2 * round_words + 16, multiple of 8)
 };
 
 constexpr int kRecPad = 8;     // the chain prefetches records up to 7 past the round's end
 constexpr int kLinMax = 4608;  // words of one linear stream window (>= 2 * round words + 16)
 
-__host__ __device__ inline size_t dec_pair_bytes() {
-  return (size_t)2 * (kRoundMax + kRecPad) * 16   // records
-         + (size_t)2 * kRoundMax * 4              // values decoded by the general path
-         + (size_t)2 * kRoundMax                  // one code byte per symbol
-         + (size_t)2 * kLinMax * 2 + 16;          // two linear stream windows, ctrl
+// per-stream shared memory of the decoder for rounds of `round` symbols (multiple of 32) and
+// windows of `lin` words (multiple of 8)
+__host__ __device__ inline size_t dec_pair_bytes(int round, int lin) {
+  return (size_t)2 * (round + kRecPad) * 16   // records
+         + (size_t)2 * round * 4              // values decoded by the general path
+         + (size_t)2 * round                  // one code byte per symbol
+         + (size_t)2 * lin * 2 + 16;          // two linear stream windows, ctrl
 }
 
 // Stream words reach the chain through per-round LINEAR windows (no index masking on the
 // chain): the window of round r+1 is filled while round r runs and starts at the stream
 // position round r started at (the only position known by then); a round consumes at most
 // p.round_words words, so 2 * round_words + 8 words cover every position round r+1 can need.
-__global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 p) {
+__global__ void __launch_bounds__(512, 1) decode_unbounded_v4(const DecParamsV4 p) {
   Tables t;
   stage_tables_v4(p.cdf, p.rows, p.cols, p.cdf_size, p.offset, p.precision, smem_v4,
                   p.table_bytes, &t);
@@ -250,12 +253,13 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
   const int pair = helper ? warp - spc : warp;
   const int64_t s = (int64_t)blockIdx.x * p.streams_per_cta + pair;
   if (s >= p.S) return;
-  uint8_t* mine = smem_v4 + p.table_bytes + (size_t)pair * dec_pair_bytes();
-  uint4* recs = reinterpret_cast<uint4*>(mine);                      // [2][kRoundMax + kRecPad]
-  int32_t* vals = reinterpret_cast<int32_t*>(recs + 2 * (kRoundMax + kRecPad));  // [2][kRoundMax]
-  uint8_t* codes = reinterpret_cast<uint8_t*>(vals + 2 * kRoundMax);             // [2][kRoundMax]
-  uint16_t* lin = reinterpret_cast<uint16_t*>(codes + 2 * kRoundMax);            // [2][kLinMax]
-  volatile uint32_t* ctrl = reinterpret_cast<volatile uint32_t*>(lin + 2 * kLinMax);
+  const int kRmax = p.round, kLmax = p.lin_words;
+  uint8_t* mine = smem_v4 + p.table_bytes + (size_t)pair * dec_pair_bytes(p.round, p.lin_words);
+  uint4* recs = reinterpret_cast<uint4*>(mine);                      // [2][kRmax + kRecPad]
+  int32_t* vals = reinterpret_cast<int32_t*>(recs + 2 * (kRmax + kRecPad));  // [2][kRmax]
+  uint8_t* codes = reinterpret_cast<uint8_t*>(vals + 2 * kRmax);             // [2][kRmax]
+  uint16_t* lin = reinterpret_cast<uint16_t*>(codes + 2 * kRmax);            // [2][kLmax]
+  volatile uint32_t* ctrl = reinterpret_cast<volatile uint32_t*>(lin + 2 * kLmax);
   // ctrl[r & 1]: stream position (in words) at which round r starts
   const int bar = 1 + pair;
   const int R = p.round;
@@ -265,7 +269,7 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
   // fills only what streams without escape bursts need — a word per symbol — and the chain,
   // which checks its read position once per group of symbols, completes the window itself in
   // the rare case it gets near the end of the filled part.
-  const uint32_t win_max = 2u * (uint32_t)p.round_words + 16u;                 // <= kLinMax
+  const uint32_t win_max = 2u * (uint32_t)p.round_words + 16u;                 // <= kLmax
   const uint32_t win_typ = min(win_max, (2u * (uint32_t)p.round + 72u + 7u) & ~7u);
   const uint8_t* src = p.enc + s * p.cap;
   const uint32_t len = (uint32_t)max(p.nbytes[s], 0);
@@ -300,7 +304,7 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
     auto build = [&](int64_t r) {
       const int64_t base = r * R;
       const int cnt = (int)min((int64_t)R, p.n - base);
-      uint4* dst = recs + (r & 1) * (kRoundMax + kRecPad);
+      uint4* dst = recs + (r & 1) * (kRmax + kRecPad);
       int slow = 0;       // records of this round that are not in the fast class
 #pragma unroll 4
       for (int j = lane; j < cnt; j += 32) {
@@ -314,8 +318,8 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
     auto flush = [&](int64_t r) {
       const int64_t base = r * R;
       const int cnt = (int)min((int64_t)R, p.n - base);
-      const int32_t* ev = vals + (r & 1) * kRoundMax;
-      const uint8_t* cb = codes + (r & 1) * kRoundMax;
+      const int32_t* ev = vals + (r & 1) * kRmax;
+      const uint8_t* cb = codes + (r & 1) * kRmax;
 #pragma unroll 4
       for (int j = lane; j < cnt; j += 32) {
         const int32_t off = t.rowinfo[__ldg(idx + base + j)].z;
@@ -331,7 +335,7 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
       const uint32_t pos = ctrl[r & 1];
       if (r + 1 < rounds) {
         build(r + 1);
-        fill(lin + ((r + 1) & 1) * kLinMax, pos & ~7u, 0, win_typ);
+        fill(lin + ((r + 1) & 1) * kLmax, pos & ~7u, 0, win_typ);
       }
       if (r > 0) flush(r - 1);
       pair_barrier(bar);
@@ -360,16 +364,16 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
   const int ow = p.overflow_width;
   for (int64_t r = 0; r < rounds; ++r) {
     const int cnt = (int)min((int64_t)R, p.n - r * R);
-    const uint4* rc = recs + (r & 1) * (kRoundMax + kRecPad);
-    int32_t* ev = vals + (r & 1) * kRoundMax;
-    uint8_t* cb = codes + (r & 1) * kRoundMax;
-    const uint32_t lin_r = lin_s + (uint32_t)(r & 1) * (kLinMax * 2);
+    const uint4* rc = recs + (r & 1) * (kRmax + kRecPad);
+    int32_t* ev = vals + (r & 1) * kRmax;
+    uint8_t* cb = codes + (r & 1) * kRmax;
+    const uint32_t lin_r = lin_s + (uint32_t)(r & 1) * (kLmax * 2);
     // reads stay inside the part of the window the helper filled; past `lim` the chain warp
     // completes the window itself (escape bursts only)
     uint32_t lim = lin_r + 2u * (win_typ - 16u);
     auto guard = [&]() {
       if (wa > lim) {
-        fill(lin + (r & 1) * kLinMax, win_first, win_typ, win_max);
+        fill(lin + (r & 1) * kLmax, win_first, win_typ, win_max);
         __syncwarp();
         lim = 0xFFFFFFFFu;
       }
@@ -483,7 +487,7 @@ __global__ void __launch_bounds__(256, 1) decode_unbounded_v4(const DecParamsV4 
     const uint32_t p_next = win_first + (wa - lin_r) / 2u - 1u;
     if (lane == 0) ctrl[(r + 1) & 1] = p_next;
     pair_barrier(bar);
-    const uint32_t lin_n = lin_s + (uint32_t)((r + 1) & 1) * (kLinMax * 2);
+    const uint32_t lin_n = lin_s + (uint32_t)((r + 1) & 1) * (kLmax * 2);
     win_first = p_cur & ~7u;
     wa = lin_n + 2u * (p_next + 1u - win_first);
     p_cur = p_next;
@@ -545,7 +549,7 @@ __device__ __forceinline__ void put_byte(uint8_t* out, uint32_t cap, uint32_t at
 // streams_per_cta streams share one CTA (and one staged copy of the tables); each stream's three
 // warps synchronise on their own named barrier, so streams never wait for each other.
 template <bool MULTI>
-__global__ void __launch_bounds__(MULTI ? 384 : 96) encode_unbounded_v4(const EncParamsV4 p) {
+__global__ void __launch_bounds__(MULTI ? 768 : 96) encode_unbounded_v4(const EncParamsV4 p) {
   Tables t;
   stage_tables_v4(p.cdf, p.rows, p.cols, p.cdf_size, p.offset, p.precision, smem_v4,
                   p.table_bytes, &t);
