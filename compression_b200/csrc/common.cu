@@ -9,6 +9,7 @@ std::atomic<int64_t> g_launches{0};
 std::atomic<int> g_sm_budget{0};
 std::atomic<int> g_coder_pack{0};
 std::atomic<int> g_tiles_per_cta{0};
+std::atomic<int> g_debug{0};
 }  // namespace tfc
 
 extern "C" const char* tfc_last_error(void) { return tfc::last_error_ref().c_str(); }
@@ -30,6 +31,9 @@ extern "C" int tfc_configure(int key, int value) {
       if (value < 0 || value > 4096)
         return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "tiles per CTA must be in [0, 4096]");
       tfc::g_tiles_per_cta.store(value);
+      return TFC_OK;
+    case 99:   // kernel experiments (tools/conv_bench.py --debug): results are NOT valid when set
+      tfc::g_debug.store(value);
       return TFC_OK;
     default:
       return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "unknown configuration key %d", key);

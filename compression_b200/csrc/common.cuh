@@ -55,6 +55,8 @@ inline int persistent_grid() {
   return (b > 0 && b < n) ? b : n;
 }
 
+extern std::atomic<int> g_debug;
+inline int debug_bits() { return g_debug.load(std::memory_order_relaxed); }
 inline int tiles_per_cta() { return g_tiles_per_cta.load(std::memory_order_relaxed); }
 
 inline int num_sms() {

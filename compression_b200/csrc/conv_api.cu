@@ -20,11 +20,14 @@ int validate(const tfc_conv_desc* d) {
   return TFC_OK;
 }
 
-// 0: CUDA-core path, 1: tcgen05 implicit GEMM, 2: space-to-depth + tcgen05, 3: scatter GEMM
+// 0: CUDA-core path, 1: tcgen05 implicit GEMM, 2: space-to-depth + tcgen05, 3: scatter GEMM,
+// 4: thin-input im2col + tcgen05
 int pick_path(const tfc_conv_desc& d, const char** why) {
   if (d.impl == 1) return 0;
   if (d.impl == 3) return tfc::conv_upthin_supported(d, why) ? 3 : 0;
+  if (d.impl == 4) return tfc::conv_thin_supported(d, why) ? 4 : 0;
   if (d.impl == 0 && tfc::conv_upthin_supported(d, nullptr)) return 3;
+  if (d.impl == 0 && tfc::conv_thin_supported(d, nullptr)) return 4;
   if (tfc::conv_umma_supported(d, why)) return 1;
   const char* why2 = nullptr;
   if (tfc::conv_s2d_supported(d, &why2)) return 2;
@@ -42,6 +45,7 @@ extern "C" size_t tfc_signal_conv2d_workspace(const tfc_conv_desc* desc) {
   if (path == 1) need = std::max(need, tfc::conv_umma_workspace(*desc));
   if (path == 2) need = std::max(need, tfc::conv_s2d_workspace(*desc));
   if (path == 3) need = std::max(need, tfc::conv_upthin_workspace(*desc));
+  if (path == 4) need = std::max(need, tfc::conv_thin_workspace(*desc));
   return need;
 }
 
@@ -58,7 +62,7 @@ extern "C" int tfc_signal_conv2d(const tfc_conv_desc* desc, const void* d_in, co
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const char* why = "unknown";
   const int path = pick_path(*desc, &why);
-  if ((desc->impl == 2 || desc->impl == 3) && path == 0)
+  if (desc->impl >= 2 && path == 0)
     return tfc::fail(TFC_ERR_UNIMPLEMENTED, "tcgen05 conv path does not support this shape: %s",
                      why);
   if (path == 1)
@@ -66,6 +70,9 @@ extern "C" int tfc_signal_conv2d(const tfc_conv_desc* desc, const void* d_in, co
                           workspace_bytes, st);
   if (path == 3)
     return tfc::conv_upthin(*desc, d_in, d_w, d_bias, d_out, d_workspace, workspace_bytes, st);
+  if (path == 4)
+    return tfc::conv_thin(*desc, d_in, d_w, d_bias, d_beta, d_gamma, d_out, d_workspace,
+                          workspace_bytes, st);
   if (path == 2)
     return tfc::conv_s2d(*desc, d_in, d_w, d_bias, d_beta, d_gamma, d_out, d_workspace,
                          workspace_bytes, st);

@@ -30,6 +30,20 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
 int make_tensor_map_bf16(CUtensorMap* m, void* base, int rank, const cuuint64_t* dims,
                          const cuuint64_t* strides_bytes, const cuuint32_t* box);
 
+// un-swizzled float32 / bf16 tiled tensor map (image patches of conv_thin.cu)
+int make_tensor_map_plain(CUtensorMap* m, bool f32, void* base, int rank, const cuuint64_t* dims,
+                          const cuuint64_t* strides_bytes, const cuuint32_t* box);
+
+// 128-pixel tile shape (th x tw) that wastes the fewest pixels on an hs x ws output grid
+void conv_pick_tile(int hs, int ws, int* th, int* tw);
+
+// thin-input layers (3 image channels) with a software im2col feeding tcgen05 (conv_thin.cu)
+bool conv_thin_supported(const tfc_conv_desc& d, const char** why);
+size_t conv_thin_workspace(const tfc_conv_desc& d);
+int conv_thin(const tfc_conv_desc& d, const void* in, const float* w, const float* bias,
+              const float* beta, const float* gamma, void* out, void* ws, size_t ws_bytes,
+              cudaStream_t st);
+
 // thin-output transposed layers as a scatter GEMM (conv_upthin.cu)
 bool conv_upthin_supported(const tfc_conv_desc& d, const char** why);
 size_t conv_upthin_workspace(const tfc_conv_desc& d);

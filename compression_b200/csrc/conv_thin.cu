@@ -1,0 +1,607 @@
+// Thin-input SignalConv2D (the first analysis layer: 3 image channels -> 128/192 filters, 5x5
+// stride 2 in bmshj2018, 9x9 stride 4 in bls2017) as ONE tcgen05 kernel fed by a software
+// im2col, with the bias / GDN epilogue of conv_epilogue.cuh.
+//
+// Reference semantics: signal_conv.py:487-524 (tf.nn.conv2d with explicit same_zeros padding),
+// :804 bias_add, gdn.py:183-202.
+//
+// The whole receptive field of an output pixel is only K = kh*kw*cin values (75 / 243), so the
+// GEMM per 128-pixel tile is D[128, cout] = A[128, K] * W[K, cout] with K padded to 16:
+//   * W (K-major bf16, ceil(K/64) blocks) and gamma stay RESIDENT in shared memory for the life
+//     of the CTA — one TMA load each; the tile loop itself reads only the image.
+//   * A is built by two "builder" warps straight from the fp32 / bf16 NHWC image into the
+//     128-byte-swizzled K-major layout tcgen05.mma expects (row = pixel, 16-byte chunk c of
+//     row r stored at chunk c ^ (r & 7)), through a ring of 16 KB stages.  The k -> (a, b, c)
+//     decomposition is resolved at compile time (kernel templated on kh, kw, cin).
+//   * warp 0: one-time TMA; warp 1: MMA issuer; warps 2-9: epilogue; warps 10-11: builders.
+// Compared with the space-to-depth formulation (conv_s2d.cu, 9 k-blocks of 64 mostly-zero
+// channels per tile, weights streamed per tile) this issues 5 instead of 36 MMAs per tile and
+// takes the shared-memory fill traffic per tile from 360 KB to the 8 KB image patch.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include <algorithm>
+#include <type_traits>
+
+#include "common.cuh"
+#include "conv_common.cuh"
+#include "conv_epilogue.cuh"
+#include "umma_ptx.cuh"
+
+namespace {
+
+using namespace tfc::ptx;
+namespace epi = tfc::epi;
+
+constexpr int kEpiThreads = tfc::epi::kEpilogueThreads;
+constexpr int kThreads = 64 + kEpiThreads + 64;
+constexpr int kBuilders = 64;         // two warps, two tile rows per thread
+constexpr int kABytes = epi::kABytes;
+constexpr int kMaxStages = 4;
+
+struct Params {
+  int32_t n, h, w;                  // input [n, h, w, CIN]
+  int32_t ho, wo, cout, npad;
+  int32_t sd, pt, pl;
+  int32_t th, tw, tiles_h, tiles_w, num_tiles, chunk;
+  int32_t stages;
+  int32_t patch;                    // image patches staged by TMA (else the builders use LDG)
+  int32_t patch_pitch;              // elements per patch row
+  int32_t patch_bytes;              // TMA box bytes
+  int32_t patch_slot;               // bytes reserved per patch buffer
+  int32_t vec;                      // patch reads: elements per shared-memory load (1 or 2)
+  int32_t per16;                    // image elements per 16 bytes
+  int32_t act, out_f32, out_wide, in_f32;
+  int32_t debug;
+  const void* in;
+  const float* bias;
+  const float* beta;
+  void* out;
+};
+
+struct __align__(8) Barriers {
+  uint64_t a_full[kMaxStages], a_empty[kMaxStages];
+  uint64_t w_full;
+  uint64_t p_full[2], p_empty[2];
+  uint64_t d1_full[2], d1_empty[2];
+  uint64_t a2_full, d2_full;
+  uint32_t tmem_base;
+  uint32_t pad;
+};
+
+__device__ __forceinline__ float ldf(const float* p) { return __ldg(p); }
+__device__ __forceinline__ float ldf(const __nv_bfloat16* p) {
+  return __bfloat162float(*p);
+}
+
+// One tile row (= output pixel) of k-block KBI: K-columns [64*KBI, 64*KBI + 16*NM) of the im2col
+// matrix, k = (a*KW + b)*CIN + c.  `src` points at the top-left tap of the pixel's window.
+template <int KH, int KW, int CIN, int KBI, int NM, bool CHECK, typename T>
+__device__ __forceinline__ void build_row(const T* __restrict__ src, int64_t row_stride, int y0,
+                                          int x0, int h, int w, uint8_t* row, int r) {
+  constexpr int K = KH * KW * CIN;
+  constexpr int L = KW * CIN;
+  float v[NM * 16];
+#pragma unroll
+  for (int e = 0; e < NM * 16; ++e) {
+    const int k = KBI * 64 + e;            // compile-time after unrolling
+    const int a = k / L, t = k - a * L, b = t / CIN;
+    if (k < K) {
+      if (CHECK) {
+        const bool ok = (unsigned)(y0 + a) < (unsigned)h && (unsigned)(x0 + b) < (unsigned)w;
+        v[e] = ok ? ldf(src + a * row_stride + t) : 0.f;
+      } else {
+        v[e] = ldf(src + a * row_stride + t);
+      }
+    } else {
+      v[e] = 0.f;
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < NM * 2; ++c) {
+    const int physc = c ^ (r & 7);
+    *reinterpret_cast<uint4*>(row + physc * 16) =
+        make_uint4(epi::pack_bf16(v[8 * c], v[8 * c + 1]), epi::pack_bf16(v[8 * c + 2], v[8 * c + 3]),
+                   epi::pack_bf16(v[8 * c + 4], v[8 * c + 5]), epi::pack_bf16(v[8 * c + 6], v[8 * c + 7]));
+  }
+}
+
+__device__ __forceinline__ void lds_vec(const float* p, float (&o)[2]) {
+  const float2 v = *reinterpret_cast<const float2*>(p);
+  o[0] = v.x; o[1] = v.y;
+}
+__device__ __forceinline__ void lds_vec(const __nv_bfloat16* p, float (&o)[2]) {
+  const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
+  o[0] = v.x; o[1] = v.y;
+}
+
+// The same row from the TMA-staged patch in shared memory (zero padding already applied by the
+// TMA unit).  `src` points at the top-left tap inside the patch; V = 2 reads element pairs
+// (LDS.64 / LDS.32), which needs an even sd*CIN.
+template <int KH, int KW, int CIN, int KBI, int NM, int V, typename T>
+__device__ __forceinline__ void build_row_patch(const T* src, int pitch, uint8_t* row, int r) {
+  constexpr int K = KH * KW * CIN;
+  constexpr int L = KW * CIN;
+  constexpr int lo = KBI * 64, hi = (lo + NM * 16 < K) ? lo + NM * 16 : K;
+  float v[NM * 16];
+#pragma unroll
+  for (int e = 0; e < NM * 16; ++e) v[e] = 0.f;
+#pragma unroll
+  for (int a = 0; a < KH; ++a) {
+#pragma unroll
+    for (int q = 0; q < (L + V - 1) / V; ++q) {
+      const int k0 = a * L + q * V;            // compile-time after unrolling
+      if (k0 + V > lo && k0 < hi) {
+        if (V == 2) {
+          float pr[2];
+          lds_vec(src + a * pitch + q * 2, pr);
+          if (k0 >= lo && k0 < hi) v[k0 - lo] = pr[0];
+          if (q * 2 + 1 < L && k0 + 1 >= lo && k0 + 1 < hi) v[k0 + 1 - lo] = pr[1];
+        } else {
+          v[k0 - lo] = (float)src[a * pitch + q];
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < NM * 2; ++c) {
+    const int physc = c ^ (r & 7);
+    *reinterpret_cast<uint4*>(row + physc * 16) =
+        make_uint4(epi::pack_bf16(v[8 * c], v[8 * c + 1]), epi::pack_bf16(v[8 * c + 2], v[8 * c + 3]),
+                   epi::pack_bf16(v[8 * c + 4], v[8 * c + 5]), epi::pack_bf16(v[8 * c + 6], v[8 * c + 7]));
+  }
+}
+
+template <int KH, int KW, int CIN, int KBI, typename T>
+__device__ __forceinline__ void build_block_patch(const Params& p, const T* patch, int t,
+                                                  uint8_t* sa) {
+  constexpr int NM = (KH * KW * CIN - KBI * 64 >= 64) ? 4 : (KH * KW * CIN - KBI * 64 + 15) / 16;
+#pragma unroll 1
+  for (int rr = 0; rr < 2; ++rr) {
+    const int r = t + rr * kBuilders;
+    const int li = r / p.tw, lj = r - li * p.tw;
+    const T* src = patch + li * p.sd * p.patch_pitch + lj * p.sd * CIN;
+    uint8_t* row = sa + r * 128;
+    if (p.vec == 2)
+      build_row_patch<KH, KW, CIN, KBI, NM, 2>(src, p.patch_pitch, row, r);
+    else
+      build_row_patch<KH, KW, CIN, KBI, NM, 1>(src, p.patch_pitch, row, r);
+  }
+}
+
+template <int K, int KBI>
+struct BlockMmas {   // 16-wide MMA K-steps that k-block KBI really needs
+  static constexpr int rest = K - KBI * 64;
+  static constexpr int value = rest >= 64 ? 4 : (rest + 15) / 16;
+};
+
+template <int KH, int KW, int CIN, int KBI, typename T>
+__device__ __forceinline__ void build_block(const Params& p, const T* img, int n, int i0, int j0,
+                                            int t, uint8_t* sa) {
+  constexpr int NM = BlockMmas<KH * KW * CIN, KBI>::value;
+#pragma unroll 1
+  for (int rr = 0; rr < 2; ++rr) {
+    const int r = t + rr * kBuilders;
+    const int li = r / p.tw, lj = r - li * p.tw;
+    const int y0 = (i0 + li) * p.sd - p.pt, x0 = (j0 + lj) * p.sd - p.pl;
+    const int64_t row_stride = (int64_t)p.w * CIN;
+    const T* src = img + ((int64_t)n * p.h + y0) * row_stride + (int64_t)x0 * CIN;
+    uint8_t* row = sa + r * 128;
+    const bool inside = y0 >= 0 && x0 >= 0 && y0 + KH <= p.h && x0 + KW <= p.w;
+    if (inside)
+      build_row<KH, KW, CIN, KBI, NM, false>(src, row_stride, y0, x0, p.h, p.w, row, r);
+    else
+      build_row<KH, KW, CIN, KBI, NM, true>(src, row_stride, y0, x0, p.h, p.w, row, r);
+  }
+}
+
+// MODE 0: bias (+ReLU).  MODE 1: GDN with cout == 32 * NC.
+template <int MODE, int NC, int KH, int KW, int CIN>
+__global__ void __launch_bounds__(kThreads, 1)
+conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
+                 const __grid_constant__ CUtensorMap map_g,
+                 const __grid_constant__ CUtensorMap map_img, const Params p) {
+  constexpr bool GDN = MODE != 0;
+  constexpr int K = KH * KW * CIN;
+  constexpr int KB = (K + 63) / 64;
+  constexpr int gdn_kblocks = GDN ? NC / 2 : 0;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // carve: [A ring: stages x 16 KB] [W: KB x npad*128 B] [gamma: cout/64 x npad*128 B]
+  //        [A2: cout/64 x 16 KB] [2 image patches] [bias|beta] [barriers]
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  const int b_bytes = p.npad * 128;
+  const int b_slot = (b_bytes + 1023) & ~1023;
+  uint8_t* w_res = smem + p.stages * kABytes;
+  uint8_t* g_res = w_res + KB * b_slot;
+  uint8_t* a2 = g_res + gdn_kblocks * b_slot;
+  uint8_t* patches = a2 + gdn_kblocks * kABytes;
+  float* s_bias = reinterpret_cast<float*>(patches + (p.patch ? 2 * p.patch_slot : 0));
+  float* s_beta = s_bias + 256;
+  Barriers* bars = reinterpret_cast<Barriers*>(s_beta + 256);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < 256; i += kThreads) {
+    s_bias[i] = (p.bias && i < p.cout) ? p.bias[i] : 0.f;
+    s_beta[i] = (GDN && i < p.cout) ? p.beta[i] : 1.f;
+  }
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&map_w);
+    if (GDN) prefetch_tmap(&map_g);
+    for (int s = 0; s < kMaxStages; ++s) {
+      mbar_init(&bars->a_full[s], kBuilders / 32);
+      mbar_init(&bars->a_empty[s], 1);
+    }
+    mbar_init(&bars->w_full, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->p_full[s], 1); mbar_init(&bars->p_empty[s], kBuilders / 32); }
+    if (p.patch) prefetch_tmap(&map_img);
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], kEpiThreads); }
+    mbar_init(&bars->a2_full, kEpiThreads);
+    mbar_init(&bars->d2_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&bars->tmem_base, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bars->tmem_base;
+  const int tile0 = p.chunk ? (int)blockIdx.x * p.chunk : (int)blockIdx.x;
+  const int tile1 = p.chunk ? min(tile0 + p.chunk, p.num_tiles) : p.num_tiles;
+  const int tile_step = p.chunk ? 1 : (int)gridDim.x;
+  const uint32_t idesc = make_idesc_bf16(128, p.npad);
+
+  auto tile_coords = [&](int tile, int& n, int& i0, int& j0) {
+    const int per_img = p.tiles_h * p.tiles_w;
+    n = tile / per_img;
+    const int r = tile - n * per_img;
+    const int ti = r / p.tiles_w;
+    i0 = ti * p.th;
+    j0 = (r - ti * p.tiles_w) * p.tw;
+  };
+
+  if (warp == 0) {
+    // ===== one-time TMA: resident weights and gamma =====
+    if (lane == 0) {
+      mbar_expect_tx(&bars->w_full, (KB + gdn_kblocks) * b_bytes);
+      for (int kb = 0; kb < KB; ++kb)
+        tma_load_3d(w_res + kb * b_slot, &map_w, &bars->w_full, 0, 0, kb);
+      for (int kc = 0; kc < gdn_kblocks; ++kc)
+        tma_load_2d(g_res + kc * b_slot, &map_g, &bars->w_full, kc * 64, 0);
+      if (p.patch) {
+        // ===== image patches: one TMA box per tile, borders zero-filled by the TMA unit =====
+        uint32_t it = 0;
+        for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
+          int n, i0, j0;
+          tile_coords(tile, n, i0, j0);
+          const int pb = it & 1;
+          mbar_wait(&bars->p_empty[pb], ((it >> 1) & 1) ^ 1);
+          mbar_expect_tx(&bars->p_full[pb], p.patch_bytes);
+          // the box must start on a 16-byte boundary of the image row: round the first column
+          // down, the builders skip the difference
+          int c0 = (j0 * p.sd - p.pl) * CIN;
+          c0 -= c0 & (p.per16 - 1);
+          tma_load_3d(patches + pb * p.patch_slot, &map_img, &bars->p_full[pb], c0,
+                      i0 * p.sd - p.pt, n);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t ph = 0, it = 0;
+      auto issue_gdn = [&](uint32_t j) {
+        mbar_wait(&bars->a2_full, j & 1);
+        tc_fence_after();
+        const uint32_t d2 = tmem + (j & 1) * 256;
+        for (int kc = 0; kc < gdn_kblocks; ++kc) {
+          const uint64_t da = make_desc_sw128(smem_u32(a2 + kc * kABytes));
+          const uint64_t db = make_desc_sw128(smem_u32(g_res + kc * b_slot));
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_bf16(d2, da + (k * 2), db + (k * 2), idesc, (kc | k) != 0);
+        }
+        umma_commit(&bars->d2_full);
+      };
+      mbar_wait(&bars->w_full, 0);
+      for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
+        const int acc = it & 1;
+        mbar_wait(&bars->d1_empty[acc], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d1 = tmem + acc * 256;
+#pragma unroll
+        for (int kb = 0; kb < KB; ++kb) {
+          const int nm = (K - kb * 64 >= 64) ? 4 : (K - kb * 64 + 15) / 16;
+          mbar_wait(&bars->a_full[stage], ph);
+          tc_fence_after();
+          const uint64_t da = make_desc_sw128(smem_u32(smem + stage * kABytes));
+          const uint64_t db = make_desc_sw128(smem_u32(w_res + kb * b_slot));
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (k < nm) umma_bf16(d1, da + (k * 2), db + (k * 2), idesc, (kb | k) != 0);
+          umma_commit(&bars->a_empty[stage]);
+          if (++stage == p.stages) { stage = 0; ph ^= 1; }
+        }
+        umma_commit(&bars->d1_full[acc]);
+        // GEMM2 of the previous tile goes AFTER this tile's main GEMM: the main GEMM is short
+        // and its operands are ready long before the epilogue has squared the previous tile
+        if (GDN && it > 0) issue_gdn(it - 1);
+      }
+      if (GDN && it > 0) issue_gdn(it - 1);
+    }
+  } else if (warp < 2 + epi::kEpilogueWarps) {
+    // ===== epilogue: 8 warps, thread <-> TMEM lane <-> tile pixel, two column halves =====
+    const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int r = quad * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+    uint32_t it = 0;
+    for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
+      int n, i0, j0;
+      tile_coords(tile, n, i0, j0);
+      const int acc = it & 1;
+      const int li = r / p.tw, lj = r - li * p.tw;
+      const int i2 = i0 + li, j2 = j0 + lj;
+      const bool valid = i2 < p.ho && j2 < p.wo && !(p.debug & 2);
+      const int64_t elem0 = (((int64_t)n * p.ho + i2) * p.wo + j2) * p.cout;
+      const uint32_t dacc = tmem + acc * 256 + lane_addr;
+      mbar_wait(&bars->d1_full[acc], (it >> 1) & 1);
+      tc_fence_after();
+      if constexpr (GDN)
+        epi::gdn_tile<MODE, NC / 2>(dacc, a2, r, half * (NC / 2), s_bias, s_beta, &bars->a2_full,
+                                    &bars->d2_full, it, valid, p.out, p.out_f32 != 0,
+                                    p.out_wide != 0, elem0);
+      else
+        epi::bias_tile(dacc, half, p.npad, p.cout, s_bias, p.act == TFC_ACT_RELU, valid, p.out,
+                       p.out_f32 != 0, p.out_wide != 0, elem0);
+      tc_fence_before();
+      mbar_arrive(&bars->d1_empty[acc]);
+    }
+  } else {
+    // ===== im2col builders =====
+    const int t = threadIdx.x - (64 + kEpiThreads);
+    int stage = 0;
+    uint32_t ph = 0;
+    const uint8_t* patch = nullptr;
+    auto block = [&](auto kbi, int n, int i0, int j0) {
+      constexpr int KBI = decltype(kbi)::value;
+      if constexpr (KBI < KB) {
+        mbar_wait(&bars->a_empty[stage], ph ^ 1);
+        uint8_t* sa = smem + stage * kABytes;
+        if (p.debug & 1) {
+        } else if (p.patch) {
+          if (p.in_f32)
+            build_block_patch<KH, KW, CIN, KBI>(p, reinterpret_cast<const float*>(patch), t, sa);
+          else
+            build_block_patch<KH, KW, CIN, KBI>(p, reinterpret_cast<const __nv_bfloat16*>(patch), t, sa);
+        } else if (p.in_f32)
+          build_block<KH, KW, CIN, KBI>(p, static_cast<const float*>(p.in), n, i0, j0, t, sa);
+        else
+          build_block<KH, KW, CIN, KBI>(p, static_cast<const __nv_bfloat16*>(p.in), n, i0, j0, t, sa);
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->a_full[stage]);
+        if (++stage == p.stages) { stage = 0; ph ^= 1; }
+      }
+    };
+    uint32_t it = 0;
+    for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
+      int n, i0, j0;
+      tile_coords(tile, n, i0, j0);
+      const int pb = it & 1;
+      if (p.patch) {
+        mbar_wait(&bars->p_full[pb], (it >> 1) & 1);
+        const int skip = ((j0 * p.sd - p.pl) * CIN) & (p.per16 - 1);
+        patch = patches + pb * p.patch_slot + skip * (p.in_f32 ? 4 : 2);
+      }
+      block(std::integral_constant<int, 0>{}, n, i0, j0);
+      block(std::integral_constant<int, 1>{}, n, i0, j0);
+      block(std::integral_constant<int, 2>{}, n, i0, j0);
+      block(std::integral_constant<int, 3>{}, n, i0, j0);
+      if (p.patch) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->p_empty[pb]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+// w fp32 [K][cout] -> bf16 [KB][npad][64] (K-major blocks, zero padded)
+__global__ void repack_thin_weights_kernel(const float* __restrict__ w, int K, int cout, int npad,
+                                           int kblocks, __nv_bfloat16* __restrict__ out) {
+  const int total = kblocks * npad * 64;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int kk = i & 63;
+    const int o = (i >> 6) % npad;
+    const int k = (i / (64 * npad)) * 64 + kk;
+    out[i] = __float2bfloat16_rn((k < K && o < cout) ? w[(int64_t)k * cout + o] : 0.f);
+  }
+}
+
+// gamma fp32 [k][c] -> bf16 [c (npad rows)][k]
+__global__ void repack_gamma_kernel(const float* __restrict__ g, int c_count, int npad,
+                                    __nv_bfloat16* __restrict__ out) {
+  const int total = npad * c_count;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int k = i % c_count, c = i / c_count;
+    out[i] = __float2bfloat16_rn(c < c_count ? g[(int64_t)k * c_count + c] : 0.f);
+  }
+}
+
+struct Plan {
+  int kblocks, npad, stages;
+  int th, tw;
+  bool patch;               // TMA-staged image patches
+  int patch_rows, patch_pitch, patch_slot, vec;
+  size_t smem;
+  bool gdn;
+};
+
+bool shape_ok(const tfc_conv_desc& d) {
+  return d.cin == 3 && d.kh == d.kw && (d.kh == 5 || d.kh == 9);
+}
+
+bool make_plan(const tfc_conv_desc& d, const void* in, Plan* pl) {
+  pl->gdn = d.act == TFC_ACT_GDN;
+  const int K = d.kh * d.kw * d.cin;
+  pl->kblocks = (K + 63) / 64;
+  pl->npad = (d.cout + 15) / 16 * 16;
+  tfc::conv_pick_tile(d.ho, d.wo, &pl->th, &pl->tw);
+  const size_t b_slot = ((size_t)pl->npad * 128 + 1023) & ~size_t(1023);
+  const size_t fixed = 1024 + pl->kblocks * b_slot +
+                       (pl->gdn ? (size_t)(d.cout / 64) * (b_slot + kABytes) : 0) +
+                       2 * 256 * sizeof(float) + sizeof(Barriers) + 64;
+  // image patch of one tile: ((th-1)*sd + kh) rows of ((tw-1)*sd + kw)*cin elements, the row
+  // starting on a 16-byte boundary and padded to 16 bytes (+ one element so that a pair load may
+  // straddle the end)
+  const int esize = d.in_dtype == TFC_F32 ? 4 : 2;
+  const int per16 = 16 / esize;
+  pl->patch_rows = (pl->th - 1) * d.sd + d.kh;
+  pl->patch_pitch = (((pl->tw - 1) * d.sd + d.kw) * d.cin + 1 + (per16 - 1) + per16 - 1) / per16 * per16;
+  pl->patch_slot = (pl->patch_rows * pl->patch_pitch * esize + 16 + 127) & ~127;
+  pl->vec = ((d.sd * d.cin) % 2 == 0 && (d.pad_left * d.cin) % 2 == 0) ? 2 : 1;
+  // TMA needs 16-byte aligned rows in global memory and boxes of at most 256 elements per dim;
+  // `in == nullptr` (workspace / support queries) assumes an aligned image
+  const bool tma_ok = !(tfc::debug_bits() & 4) && ((size_t)d.w * d.cin * esize) % 16 == 0 && pl->patch_pitch <= 256 &&
+                      pl->patch_rows <= 256 && (reinterpret_cast<uintptr_t>(in) & 15) == 0;
+  for (int with_patch = tma_ok ? 1 : 0; with_patch >= 0; --with_patch) {
+    const size_t extra = with_patch ? 2 * (size_t)pl->patch_slot : 0;
+    for (int s = kMaxStages; s >= 2; --s) {
+      if (fixed + extra + (size_t)s * kABytes <= 227 * 1024) {
+        pl->stages = s;
+        pl->patch = with_patch != 0;
+        pl->smem = fixed + extra + (size_t)s * kABytes;
+        return true;
+      }
+    }
+  }
+  return false;
+}
+
+size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
+
+template <int KH, int KW>
+int launch(const tfc_conv_desc& d, const Plan& pl, const CUtensorMap& map_w,
+           const CUtensorMap& map_g, const CUtensorMap& map_img, const Params& p, int grid,
+           cudaStream_t st) {
+  void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const Params) = nullptr;
+  if (!pl.gdn) {
+    kern = conv_thin_kernel<0, 0, KH, KW, 3>;
+  } else {
+    switch (d.cout / 32) {
+      case 4: kern = conv_thin_kernel<1, 4, KH, KW, 3>; break;
+      case 6: kern = conv_thin_kernel<1, 6, KH, KW, 3>; break;
+      default: return tfc::fail(TFC_ERR_UNIMPLEMENTED, "thin-input GDN needs 128 or 192 filters");
+    }
+  }
+  TFC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+  kern<<<grid, kThreads, pl.smem, st>>>(map_w, map_g, map_img, p);
+  TFC_LAUNCHED("conv_thin_kernel");
+  return TFC_OK;
+}
+
+}  // namespace
+
+namespace tfc {
+
+bool conv_thin_supported(const tfc_conv_desc& d, const char** why) {
+  const char* dummy;
+  if (!why) why = &dummy;
+  if (d.su != 1) { *why = "thin-input path needs strides_up == 1"; return false; }
+  if (!shape_ok(d)) { *why = "thin-input path is built for 3 channels and 5x5 / 9x9 kernels"; return false; }
+  if (d.act == TFC_ACT_IGDN) { *why = "thin-input path has no IGDN epilogue"; return false; }
+  if (d.act == TFC_ACT_GDN && d.cout != 128 && d.cout != 192) {
+    *why = "thin-input GDN needs 128 or 192 filters"; return false;
+  }
+  if (d.cout > 256) { *why = "cout must be <= 256"; return false; }
+  if (d.sd > 8) { *why = "stride too large"; return false; }
+  Plan pl;
+  if (!make_plan(d, nullptr, &pl)) { *why = "shared memory"; return false; }
+  if ((int64_t)d.n * d.ho * d.wo / 128 > (1 << 30)) { *why = "too many tiles"; return false; }
+  return true;
+}
+
+size_t conv_thin_workspace(const tfc_conv_desc& d) {
+  Plan pl;
+  if (!make_plan(d, nullptr, &pl)) return 0;
+  return align256((size_t)pl.kblocks * pl.npad * 64 * 2) + align256((size_t)pl.npad * pl.npad * 2) + 256;
+}
+
+int conv_thin(const tfc_conv_desc& d, const void* in, const float* w, const float* bias,
+              const float* beta, const float* gamma, void* out, void* ws, size_t ws_bytes,
+              cudaStream_t st) {
+  Plan pl;
+  if (!make_plan(d, in, &pl)) return fail(TFC_ERR_UNIMPLEMENTED, "thin-input conv: shared memory");
+  if (ws == nullptr || ws_bytes < conv_thin_workspace(d))
+    return fail(TFC_ERR_INVALID_ARGUMENT, "conv workspace too small: need %zu bytes",
+                conv_thin_workspace(d));
+  if ((reinterpret_cast<uintptr_t>(ws) & 255) || (reinterpret_cast<uintptr_t>(out) & 15))
+    return fail(TFC_ERR_INVALID_ARGUMENT, "conv buffers must be 16-byte (workspace 256-byte) aligned");
+  Params p{};
+  p.n = d.n; p.h = d.h; p.w = d.w; p.ho = d.ho; p.wo = d.wo; p.cout = d.cout; p.npad = pl.npad;
+  p.sd = d.sd; p.pt = d.pad_top; p.pl = d.pad_left;
+  p.act = d.act; p.out_f32 = d.out_dtype == TFC_F32; p.in_f32 = d.in_dtype == TFC_F32;
+  p.out_wide = epi::wide_stores_ok(out, d.cout, p.out_f32 != 0);
+  p.in = in; p.bias = bias; p.beta = beta; p.out = out;
+  p.stages = pl.stages;
+  p.debug = debug_bits();
+  p.th = pl.th; p.tw = pl.tw;
+  p.patch = pl.patch; p.patch_pitch = pl.patch_pitch; p.patch_slot = pl.patch_slot; p.vec = pl.vec;
+  p.per16 = p.in_f32 ? 4 : 8;
+  p.patch_bytes = pl.patch_rows * pl.patch_pitch * (p.in_f32 ? 4 : 2);
+  p.tiles_h = (d.ho + p.th - 1) / p.th;
+  p.tiles_w = (d.wo + p.tw - 1) / p.tw;
+  p.num_tiles = d.n * p.tiles_h * p.tiles_w;
+
+  const int K = d.kh * d.kw * d.cin;
+  __nv_bfloat16* wb = static_cast<__nv_bfloat16*>(ws);
+  const size_t wbytes = align256((size_t)pl.kblocks * pl.npad * 64 * 2);
+  __nv_bfloat16* gb = reinterpret_cast<__nv_bfloat16*>(static_cast<uint8_t*>(ws) + wbytes);
+  if (!(d.flags & TFC_CONV_WEIGHTS_STAGED)) {
+    repack_thin_weights_kernel<<<(pl.kblocks * pl.npad * 64 + 255) / 256, 256, 0, st>>>(
+        w, K, d.cout, pl.npad, pl.kblocks, wb);
+    TFC_LAUNCHED("repack_thin_weights_kernel");
+    if (pl.gdn) {
+      repack_gamma_kernel<<<(pl.npad * d.cout + 255) / 256, 256, 0, st>>>(gamma, d.cout, pl.npad, gb);
+      TFC_LAUNCHED("repack_gamma_kernel");
+    }
+  }
+  CUtensorMap map_w, map_g, map_img;
+  {
+    cuuint64_t dims[3] = {64, (cuuint64_t)pl.npad, (cuuint64_t)pl.kblocks};
+    cuuint64_t str[2] = {128, (cuuint64_t)pl.npad * 128};
+    cuuint32_t box[3] = {64, (cuuint32_t)pl.npad, 1};
+    int rc = make_tensor_map_bf16(&map_w, wb, 3, dims, str, box);
+    if (rc) return rc;
+  }
+  if (pl.gdn) {
+    cuuint64_t dims[2] = {(cuuint64_t)d.cout, (cuuint64_t)pl.npad};
+    cuuint64_t str[1] = {(cuuint64_t)d.cout * 2};
+    cuuint32_t box[2] = {64, (cuuint32_t)pl.npad};
+    int rc = make_tensor_map_bf16(&map_g, gb, 2, dims, str, box);
+    if (rc) return rc;
+  } else {
+    map_g = map_w;
+  }
+  if (pl.patch) {
+    const cuuint64_t es = p.in_f32 ? 4 : 2;
+    cuuint64_t dims[3] = {(cuuint64_t)d.w * d.cin, (cuuint64_t)d.h, (cuuint64_t)d.n};
+    cuuint64_t str[2] = {(cuuint64_t)d.w * d.cin * es, (cuuint64_t)d.h * d.w * d.cin * es};
+    cuuint32_t box[3] = {(cuuint32_t)pl.patch_pitch, (cuuint32_t)pl.patch_rows, 1};
+    int rc = make_tensor_map_plain(&map_img, p.in_f32 != 0, const_cast<void*>(in), 3, dims, str, box);
+    if (rc) return rc;
+  } else {
+    map_img = map_w;
+  }
+  // the resident operands cost one 50-120 KB load per CTA: never fewer than 8 tiles per CTA
+  p.chunk = tiles_per_cta() ? std::max(tiles_per_cta(), 8) : 0;
+  const int grid = p.chunk ? (p.num_tiles + p.chunk - 1) / p.chunk
+                           : std::min(p.num_tiles, persistent_grid());
+  if (d.kh == 5) return launch<5, 5>(d, pl, map_w, map_g, map_img, p, grid, st);
+  return launch<9, 9>(d, pl, map_w, map_g, map_img, p, grid, st);
+}
+
+}  // namespace tfc

@@ -29,19 +29,21 @@
 
 #include "common.cuh"
 #include "conv_common.cuh"
+#include "conv_epilogue.cuh"
 #include "umma_ptx.cuh"
 
 namespace {
 
 using namespace tfc::ptx;
+namespace epi = tfc::epi;
 
 constexpr int kTileM = 128;          // output pixels per CTA tile (UMMA M)
 constexpr int kBlockK = 64;          // channels per k-block: 64 bf16 = one 128-byte swizzle row
 constexpr int kStages = 4;
 constexpr int kMaxTaps = 81;         // 9x9
 constexpr int kMaxPhases = 16;       // 4x4 upsampling
-constexpr int kThreads = 192;        // producer warp, MMA warp, 4 epilogue warps
-constexpr int kABytes = kTileM * kBlockK * 2;   // 16 KB
+constexpr int kThreads = 64 + tfc::epi::kEpilogueThreads;   // producer warp, MMA warp, 8 epilogue warps
+constexpr int kABytes = tfc::epi::kABytes;     // 16 KB
 
 struct Tap {            // one (kernel tap) of one output phase
   int8_t dh, dw;        // offset of the input box relative to the tile origin (in box rows/cols)
@@ -62,6 +64,7 @@ struct Params {
   int32_t npad;                     // UMMA N (cout rounded up to 16)
   int32_t act;
   int32_t out_f32;
+  int32_t out_wide;                 // 256-bit stores allowed
   int32_t phase_start[kMaxPhases + 1];
   Tap taps[kMaxTaps];
   const float* bias;
@@ -76,22 +79,6 @@ struct __align__(8) Barriers {
   uint32_t tmem_base;
   uint32_t pad;
 };
-
-__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
-  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&v);
-}
-
-__device__ __forceinline__ float rsqrt_approx(float x) {
-  float y;
-  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-__device__ __forceinline__ float sqrt_approx(float x) {
-  float y;
-  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
 
 constexpr int kGdnSlot = 4;   // the GDN GEMM of tile i is issued before k-block 4 of tile i+1
 
@@ -132,8 +119,8 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
     prefetch_tmap(&map_w);
     if (GDN) prefetch_tmap(&map_g);
     for (int s = 0; s < kStages; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], 128); }
-    mbar_init(&bars->a2_full, 128);
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], epi::kEpilogueThreads); }
+    mbar_init(&bars->a2_full, epi::kEpilogueThreads);
     mbar_init(&bars->d2_full, 1);
     fence_barrier_init();
   }
@@ -250,12 +237,12 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
       if (GDN && it > 0) issue_gdn(it - 1);
     }
   } else {
-    // ===== epilogue: 4 warps, thread <-> TMEM lane <-> tile pixel =====
+    // ===== epilogue: 8 warps, thread <-> TMEM lane <-> tile pixel, two column halves =====
     const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int r = quad * 32 + lane;                  // pixel within the tile / TMEM lane
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     uint32_t it = 0;
-    uint32_t xs[GDN ? NC * 16 : 1];                  // x = D1 + bias as packed bf16 pairs
     for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
       int phase, n, i0, j0;
       tile_coords(tile, phase, n, i0, j0);
@@ -268,123 +255,14 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
       const uint32_t dacc = tmem + acc * 256 + lane_addr;
       mbar_wait(&bars->d1_full[acc], (it >> 1) & 1);
       tc_fence_after();
-      if constexpr (GDN) {
-        // phase 1: x -> registers (bf16), x^2 -> bf16 K-major SW128 tile(s) in shared memory
-#pragma unroll
-        for (int c = 0; c < NC; ++c) {
-          uint32_t v[32];
-          tmem_ld_32x32(dacc + c * 32, v);
-          tmem_ld_wait();
-          uint8_t* row = a2 + (c >> 1) * kABytes + r * 128;
-          const float4* bs = reinterpret_cast<const float4*>(s_bias + c * 32);
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const float4 b0 = bs[2 * q], b1 = bs[2 * q + 1];
-            const float x0 = __uint_as_float(v[8 * q + 0]) + b0.x;
-            const float x1 = __uint_as_float(v[8 * q + 1]) + b0.y;
-            const float x2 = __uint_as_float(v[8 * q + 2]) + b0.z;
-            const float x3 = __uint_as_float(v[8 * q + 3]) + b0.w;
-            const float x4 = __uint_as_float(v[8 * q + 4]) + b1.x;
-            const float x5 = __uint_as_float(v[8 * q + 5]) + b1.y;
-            const float x6 = __uint_as_float(v[8 * q + 6]) + b1.z;
-            const float x7 = __uint_as_float(v[8 * q + 7]) + b1.w;
-            xs[c * 16 + 4 * q + 0] = pack_bf16(x0, x1);
-            xs[c * 16 + 4 * q + 1] = pack_bf16(x2, x3);
-            xs[c * 16 + 4 * q + 2] = pack_bf16(x4, x5);
-            xs[c * 16 + 4 * q + 3] = pack_bf16(x6, x7);
-            const int physc = ((c & 1) * 4 + q) ^ (r & 7);
-            *reinterpret_cast<uint4*>(row + physc * 16) =
-                make_uint4(pack_bf16(x0 * x0, x1 * x1), pack_bf16(x2 * x2, x3 * x3),
-                           pack_bf16(x4 * x4, x5 * x5), pack_bf16(x6 * x6, x7 * x7));
-          }
-        }
-        tc_fence_before();
-        fence_proxy_async_smem();
-        mbar_arrive(&bars->a2_full);
-        mbar_wait(&bars->d2_full, it & 1);
-        tc_fence_after();
-        // phase 2: y = x * rsqrt(beta + D2)  (IGDN: x * sqrt)
-#pragma unroll
-        for (int c = 0; c < NC; ++c) {
-          uint32_t g[32];
-          tmem_ld_32x32(dacc + c * 32, g);
-          tmem_ld_wait();
-          const float4* be = reinterpret_cast<const float4*>(s_beta + c * 32);
-          float y[32];
-#pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const float4 b4 = be[q];
-            const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const uint32_t pr = xs[c * 16 + 2 * q + (e >> 1)];
-              const float x = __uint_as_float((e & 1) ? (pr & 0xFFFF0000u) : (pr << 16));
-              const float nrm = __uint_as_float(g[4 * q + e]) + bb[e];
-              y[4 * q + e] = x * (MODE == 2 ? sqrt_approx(nrm) : rsqrt_approx(nrm));
-            }
-          }
-          if (valid) {
-            if (p.out_f32) {
-              float4* dst = reinterpret_cast<float4*>(static_cast<float*>(p.out) + pix * p.cout + c * 32);
-#pragma unroll
-              for (int q = 0; q < 8; ++q)
-                dst[q] = make_float4(y[4 * q], y[4 * q + 1], y[4 * q + 2], y[4 * q + 3]);
-            } else {
-              uint4* dst = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + pix * p.cout + c * 32);
-#pragma unroll
-              for (int q = 0; q < 4; ++q)
-                dst[q] = make_uint4(pack_bf16(y[8 * q], y[8 * q + 1]), pack_bf16(y[8 * q + 2], y[8 * q + 3]),
-                                    pack_bf16(y[8 * q + 4], y[8 * q + 5]), pack_bf16(y[8 * q + 6], y[8 * q + 7]));
-            }
-          }
-        }
-      } else {
-        const bool relu = p.act == TFC_ACT_RELU;
-        for (int c0 = 0; c0 < p.npad; c0 += 32) {
-          uint32_t v[32];
-          tmem_ld_32x32(dacc + c0, v);
-          tmem_ld_wait();
-          const float4* bs = reinterpret_cast<const float4*>(s_bias + c0);
-          float y[32];
-#pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const float4 b4 = bs[q];
-            y[4 * q + 0] = __uint_as_float(v[4 * q + 0]) + b4.x;
-            y[4 * q + 1] = __uint_as_float(v[4 * q + 1]) + b4.y;
-            y[4 * q + 2] = __uint_as_float(v[4 * q + 2]) + b4.z;
-            y[4 * q + 3] = __uint_as_float(v[4 * q + 3]) + b4.w;
-          }
-          if (relu) {
-#pragma unroll
-            for (int e = 0; e < 32; ++e) y[e] = fmaxf(y[e], 0.f);
-          }
-          if (valid) {
-            const int nvalid = min(32, p.cout - c0);
-            if (nvalid == 32 && (p.cout & 7) == 0) {
-              if (p.out_f32) {
-                float4* dst = reinterpret_cast<float4*>(static_cast<float*>(p.out) + pix * p.cout + c0);
-#pragma unroll
-                for (int q = 0; q < 8; ++q)
-                  dst[q] = make_float4(y[4 * q], y[4 * q + 1], y[4 * q + 2], y[4 * q + 3]);
-              } else {
-                uint4* dst = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + pix * p.cout + c0);
-#pragma unroll
-                for (int q = 0; q < 4; ++q)
-                  dst[q] = make_uint4(pack_bf16(y[8 * q], y[8 * q + 1]), pack_bf16(y[8 * q + 2], y[8 * q + 3]),
-                                      pack_bf16(y[8 * q + 4], y[8 * q + 5]), pack_bf16(y[8 * q + 6], y[8 * q + 7]));
-              }
-            } else {
-#pragma unroll
-              for (int e = 0; e < 32; ++e) {
-                if (e < nvalid) {
-                  if (p.out_f32) static_cast<float*>(p.out)[pix * p.cout + c0 + e] = y[e];
-                  else static_cast<__nv_bfloat16*>(p.out)[pix * p.cout + c0 + e] = __float2bfloat16_rn(y[e]);
-                }
-              }
-            }
-          }
-        }
-      }
+      const int64_t elem0 = pix * p.cout;
+      if constexpr (GDN)
+        epi::gdn_tile<MODE, NC / 2>(dacc, a2, r, half * (NC / 2), s_bias, s_beta, &bars->a2_full,
+                                    &bars->d2_full, it, valid, p.out, p.out_f32 != 0,
+                                    p.out_wide != 0, elem0);
+      else
+        epi::bias_tile(dacc, half, p.npad, p.cout, s_bias, p.act == TFC_ACT_RELU, valid, p.out,
+                       p.out_f32 != 0, p.out_wide != 0, elem0);
       tc_fence_before();
       mbar_arrive(&bars->d1_empty[acc]);
     }
@@ -427,18 +305,24 @@ EncodeTiledFn encode_fn() {
   return fn;
 }
 
-int make_map(CUtensorMap* m, void* base, int rank, const cuuint64_t* dims,
-             const cuuint64_t* strides_bytes, const cuuint32_t* box) {
+int make_map_any(CUtensorMap* m, CUtensorMapDataType dtype, CUtensorMapSwizzle swizzle, void* base,
+                 int rank, const cuuint64_t* dims, const cuuint64_t* strides_bytes,
+                 const cuuint32_t* box) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return tfc::fail(TFC_ERR_CUDA, "cuTensorMapEncodeTiled entry point not found");
   cuuint32_t ones[5] = {1, 1, 1, 1, 1};
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, base, dims,
-                  strides_bytes, box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+  CUresult r = fn(m, dtype, (cuuint32_t)rank, base, dims, strides_bytes, box, ones,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
     return tfc::fail(TFC_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
   return TFC_OK;
+}
+
+int make_map(CUtensorMap* m, void* base, int rank, const cuuint64_t* dims,
+             const cuuint64_t* strides_bytes, const cuuint32_t* box) {
+  return make_map_any(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, CU_TENSOR_MAP_SWIZZLE_128B, base, rank,
+                      dims, strides_bytes, box);
 }
 
 inline int floor_div(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
@@ -498,6 +382,14 @@ size_t smem_bytes(int npad, int cout, bool gdn) {
 
 namespace tfc {
 
+int make_tensor_map_plain(CUtensorMap* m, bool f32, void* base, int rank, const cuuint64_t* dims,
+                          const cuuint64_t* strides_bytes, const cuuint32_t* box) {
+  return make_map_any(m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16,
+                      CU_TENSOR_MAP_SWIZZLE_NONE, base, rank, dims, strides_bytes, box);
+}
+
+void conv_pick_tile(int hs, int ws, int* th, int* tw) { pick_tile(hs, ws, th, tw); }
+
 int make_tensor_map_bf16(CUtensorMap* m, void* base, int rank, const cuuint64_t* dims,
                          const cuuint64_t* strides_bytes, const cuuint32_t* box) {
   return make_map(m, base, rank, dims, strides_bytes, box);
@@ -543,6 +435,7 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
   p.n = d.n; p.ho = d.ho; p.wo = d.wo; p.cout = d.cout; p.cin = d.cin;
   p.npad = (d.cout + 15) / 16 * 16;
   p.act = d.act; p.out_f32 = d.out_dtype == TFC_F32;
+  p.out_wide = epi::wide_stores_ok(out, d.cout, p.out_f32 != 0);
   p.bias = bias; p.beta = beta; p.out = out;
   if (!build_taps(d, &p)) return fail(TFC_ERR_UNIMPLEMENTED, "too many taps");
   p.hs = d.ho / d.su; p.ws = d.wo / d.su;

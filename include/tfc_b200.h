@@ -216,8 +216,9 @@ typedef enum {
  *           reparameterisation) — used when act is GDN/IGDN.
  * in/out dtypes are tfc_dtype.  `impl`: 0 = pick the fastest kernel that supports the shape,
  * 1 = force the CUDA-core tiled kernel, 2 = force the tcgen05 implicit-GEMM kernel, 3 = force
- * the tcgen05 scatter-GEMM kernel for thin-output transposed layers (TFC_ERR_UNIMPLEMENTED if
- * the shape is not supported by the forced kernel).
+ * the tcgen05 scatter-GEMM kernel for thin-output transposed layers, 4 = force the tcgen05
+ * kernel with a software im2col for thin-input layers (TFC_ERR_UNIMPLEMENTED if the shape is
+ * not supported by the forced kernel).
  * d_workspace: tfc_signal_conv2d_workspace(...) bytes (weights repacked to bf16 etc.). */
 typedef struct {
   int32_t n, h, w, cin;     /* input  [n, h, w, cin]  */

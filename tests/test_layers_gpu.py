@@ -393,3 +393,52 @@ def test_thin_input_conv_space_to_depth(tfc, cin, cout, k, sd, H, W, act, in_dty
   assert tuple(got.shape) == want.shape
   err = np.abs(got.cpu().numpy() - want).max() / (np.abs(want).max() + 1e-6)
   assert err <= (2e-2 if act == "gdn" else 1e-4), err
+
+
+THIN_CASES = [
+    # cout, kernel, sd, H, W, act, input dtype
+    (192, 5, 2, 32, 48, "gdn", torch.float32),
+    (192, 5, 2, 33, 47, "gdn", torch.float32),        # odd sizes: ragged tiles and borders
+    (192, 5, 2, 24, 40, None, torch.bfloat16),
+    (128, 5, 2, 64, 64, "gdn", torch.bfloat16),
+    (128, 9, 4, 32, 32, "gdn", torch.float32),        # first analysis layer of bls2017
+    (128, 9, 4, 61, 35, "relu", torch.float32),
+    (64, 9, 4, 16, 16, None, torch.float32),
+    (100, 5, 1, 12, 20, "relu", torch.float32),       # cout not a multiple of 32, stride 1
+    (192, 5, 2, 4, 4, "gdn", torch.float32),          # smaller than one tile
+]
+
+
+@pytest.mark.parametrize("cout,k,sd,H,W,act,in_dtype", THIN_CASES)
+def test_thin_input_conv_im2col(tfc, cout, k, sd, H, W, act, in_dtype):
+  """First analysis layer on the software-im2col tcgen05 kernel (impl=4; signal_conv.py:487-524
+  + gdn.py:183-202) against the float64 oracle."""
+  rng = np.random.default_rng(13)
+  x = rng.integers(-4, 5, size=(3, H, W, 3)).astype(np.float32)
+  kern = (rng.integers(-8, 9, size=(k, k, 3, cout)) / 8.0).astype(np.float32)
+  b = (rng.integers(-8, 9, size=cout) / 4.0).astype(np.float32)
+  activation = {"relu": torch.relu, "gdn": tfc.GDN(), None: None}[act]
+  layer = tfc.SignalConv2D(cout, (k, k), corr=True, strides_down=sd, padding="same_zeros",
+                           use_bias=True, activation=activation, kernel_parameterizer=None,
+                           kernel_initializer=_static(kern), bias_initializer=_static(b), impl=4)
+  layer.build(3, "cuda")
+  xin = torch.from_numpy(x).cuda().to(in_dtype)
+  got = layer(xin, out_dtype=torch.float32)
+  again = layer(xin, out_dtype=torch.float32)        # second call: weights already staged
+  assert torch.equal(got, again)
+  want = tfc_np.signal_conv2d(x, kern, b, True, sd, 1, "same_zeros")
+  if act == "relu":
+    want = torch.relu(want)
+  elif act == "gdn":
+    beta, gamma = [t.cpu().numpy() for t in activation.effective()]
+    want = tfc_np.gdn(want, beta, gamma, False)
+  want = want.numpy()
+  assert tuple(got.shape) == want.shape
+  err = np.abs(got.cpu().numpy() - want).max() / (np.abs(want).max() + 1e-6)
+  assert err <= (2e-2 if act == "gdn" else 1e-4), err
+
+
+def test_thin_input_conv_unsupported_reports(tfc):
+  layer = tfc.SignalConv2D(8, (3, 3), corr=True, padding="same_zeros", impl=4)
+  with pytest.raises(NotImplementedError, match="3 channels and 5x5 / 9x9"):
+    layer(torch.zeros((1, 8, 8, 3), device="cuda"))

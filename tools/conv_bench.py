@@ -23,9 +23,16 @@ def main():
   ap.add_argument("--layers", default="")
   ap.add_argument("--reps", type=int, default=5)
   ap.add_argument("--check", action="store_true", help="compare with the CUDA-core kernel")
+  ap.add_argument("--debug", type=int, default=0, help="kernel experiment bits (timing only)")
+  ap.add_argument("--tiles-per-cta", type=int, default=0)
   args = ap.parse_args()
   from compression_b200.examples import bmshj2018
   from compression_b200.python.layers import gdn as gdn_lib
+  from compression_b200 import _lib
+  if args.debug:
+    _lib.check(_lib.lib().tfc_configure(99, args.debug))
+  if args.tiles_per_cta:
+    _lib.configure(tiles_per_cta=args.tiles_per_cta)
   dev = torch.device("cuda", 0)
   model = bmshj2018.Bmshj2018Model(192, dev, seed=0)
   B, H, W = args.batch, args.height, args.width
