@@ -96,13 +96,15 @@ def to_device(x, dtype, device=None):
   return t.to(device=device, dtype=dtype).contiguous()
 
 
-CFG_SM_BUDGET, CFG_CODER_STREAMS_PER_CTA, CFG_TILES_PER_CTA = 1, 2, 3
+CFG_SM_BUDGET, CFG_CODER_STREAMS_PER_CTA, CFG_TILES_PER_CTA, CFG_CONV_CLUSTER = 1, 2, 3, 4
 
 
-def configure(sm_budget=None, coder_streams_per_cta=None, tiles_per_cta=None):
+def configure(sm_budget=None, coder_streams_per_cta=None, tiles_per_cta=None, conv_cluster=None):
   """Process-wide scheduling knobs of the library (tfc_configure): `sm_budget` = SMs the
   persistent transform kernels may occupy (0: all), `coder_streams_per_cta` = range-coder
-  streams packed into one CTA (0: automatic).  No effect on results."""
+  streams packed into one CTA (0: automatic), `tiles_per_cta` = chunked instead of persistent
+  transform kernels, `conv_cluster` = thread-block cluster size of the implicit-GEMM kernel
+  (0: automatic).  No effect on results."""
   L = lib()
   if sm_budget is not None:
     check(L.tfc_configure(CFG_SM_BUDGET, int(sm_budget)))
@@ -110,3 +112,5 @@ def configure(sm_budget=None, coder_streams_per_cta=None, tiles_per_cta=None):
     check(L.tfc_configure(CFG_CODER_STREAMS_PER_CTA, int(coder_streams_per_cta)))
   if tiles_per_cta is not None:
     check(L.tfc_configure(CFG_TILES_PER_CTA, int(tiles_per_cta)))
+  if conv_cluster is not None:
+    check(L.tfc_configure(CFG_CONV_CLUSTER, int(conv_cluster)))

@@ -10,6 +10,7 @@ std::atomic<int> g_sm_budget{0};
 std::atomic<int> g_coder_pack{0};
 std::atomic<int> g_tiles_per_cta{0};
 std::atomic<int> g_debug{0};
+std::atomic<int> g_conv_cluster{0};
 }  // namespace tfc
 
 extern "C" const char* tfc_last_error(void) { return tfc::last_error_ref().c_str(); }
@@ -31,6 +32,11 @@ extern "C" int tfc_configure(int key, int value) {
       if (value < 0 || value > 4096)
         return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "tiles per CTA must be in [0, 4096]");
       tfc::g_tiles_per_cta.store(value);
+      return TFC_OK;
+    case TFC_CFG_CONV_CLUSTER:
+      if (value != 0 && value != 1 && value != 2 && value != 4)
+        return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "conv cluster size must be 0 (auto), 1, 2 or 4");
+      tfc::g_conv_cluster.store(value);
       return TFC_OK;
     case 99:   // kernel experiments (tools/conv_bench.py --debug): results are NOT valid when set
       tfc::g_debug.store(value);

@@ -56,6 +56,8 @@ inline int persistent_grid() {
 }
 
 extern std::atomic<int> g_debug;
+extern std::atomic<int> g_conv_cluster;
+inline int conv_cluster() { return g_conv_cluster.load(std::memory_order_relaxed); }
 inline int debug_bits() { return g_debug.load(std::memory_order_relaxed); }
 inline int tiles_per_cta() { return g_tiles_per_cta.load(std::memory_order_relaxed); }
 

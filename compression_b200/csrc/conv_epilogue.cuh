@@ -84,13 +84,26 @@ constexpr int kEpilogueThreads = kEpilogueWarps * 32;
 // MODE 1 / 2: GDN / IGDN.  This thread handles channels [32*cbase, 32*(cbase + NCH)) of pixel
 // `r`.  `dacc`: TMEM address of this warp's lanes of the accumulator, `a2`: the x^2 tile(s),
 // `elem0`: pixel * cout.
+//
+// Output: with `map_out` (bf16, cout a multiple of 64) the finished tile is written back into
+// the x^2 buffer — free once the second GEMM has completed, same swizzled layout — and leaves
+// as one TMA tile store per 64 channels, issued by the `leader` thread; ragged tiles are clipped
+// by the TMA unit.  The leader waits for the store to have read the buffer before the next
+// tile's x^2 goes in.  Without `map_out` every thread stores its own channels (store_chunk).
+struct TileOrigin { int j, i, n; };   // tensor-map coordinates of the tile's first pixel (n < 0: no store)
+
 template <int MODE, int NCH>
 __device__ __forceinline__ void gdn_tile(uint32_t dacc, uint8_t* a2, int r, int cbase,
                                          const float* s_bias, const float* s_beta,
                                          uint64_t* a2_full, uint64_t* d2_full, uint32_t it,
                                          bool valid, void* out, bool out_f32, bool wide,
-                                         int64_t elem0) {
+                                         int64_t elem0, const CUtensorMap* map_out,
+                                         TileOrigin org, bool leader, int nblocks) {
   uint32_t xs[NCH * 16];                           // x = D1 + bias as packed bf16 pairs
+  if (map_out != nullptr && it > 0) {
+    if (leader) bulk_wait_read();
+    named_barrier(1, kEpilogueThreads);
+  }
   // phase 1: x -> registers (bf16), x^2 -> bf16 K-major SW128 tile(s) in shared memory
 #pragma unroll
   for (int c = 0; c < NCH; ++c) {
@@ -147,7 +160,27 @@ __device__ __forceinline__ void gdn_tile(uint32_t dacc, uint8_t* a2, int r, int 
         y[4 * q + e] = x * (MODE == 2 ? sqrt_approx(nrm) : rsqrt_approx(nrm));
       }
     }
-    if (valid) store_chunk(out, out_f32, wide, elem0 + cc * 32, y);
+    if (map_out != nullptr) {
+      uint8_t* row = a2 + (cc >> 1) * kABytes + r * 128;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int physc = ((cc & 1) * 4 + q) ^ (r & 7);
+        *reinterpret_cast<uint4*>(row + physc * 16) =
+            make_uint4(pack_bf16(y[8 * q], y[8 * q + 1]), pack_bf16(y[8 * q + 2], y[8 * q + 3]),
+                       pack_bf16(y[8 * q + 4], y[8 * q + 5]), pack_bf16(y[8 * q + 6], y[8 * q + 7]));
+      }
+    } else if (valid) {
+      store_chunk(out, out_f32, wide, elem0 + cc * 32, y);
+    }
+  }
+  if (map_out != nullptr) {
+    fence_proxy_async_smem();
+    named_barrier(1, kEpilogueThreads);
+    if (leader) {
+      for (int kc = 0; kc < nblocks && org.n >= 0; ++kc)
+        tma_store_4d(map_out, a2 + kc * kABytes, kc * 64, org.j, org.i, org.n);
+      bulk_commit();
+    }
   }
 }
 

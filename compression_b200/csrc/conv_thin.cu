@@ -52,6 +52,7 @@ struct Params {
   int32_t vec;                      // patch reads: elements per shared-memory load (1 or 2)
   int32_t per16;                    // image elements per 16 bytes
   int32_t act, out_f32, out_wide, in_f32;
+  int32_t out_tma;                  // GDN output leaves by TMA tile stores
   int32_t debug;
   const void* in;
   const float* bias;
@@ -200,7 +201,8 @@ template <int MODE, int NC, int KH, int KW, int CIN>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
                  const __grid_constant__ CUtensorMap map_g,
-                 const __grid_constant__ CUtensorMap map_img, const Params p) {
+                 const __grid_constant__ CUtensorMap map_img,
+                 const __grid_constant__ CUtensorMap map_out, const Params p) {
   constexpr bool GDN = MODE != 0;
   constexpr int K = KH * KW * CIN;
   constexpr int KB = (K + 63) / 64;
@@ -350,13 +352,15 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
       if constexpr (GDN)
         epi::gdn_tile<MODE, NC / 2>(dacc, a2, r, half * (NC / 2), s_bias, s_beta, &bars->a2_full,
                                     &bars->d2_full, it, valid, p.out, p.out_f32 != 0,
-                                    p.out_wide != 0, elem0);
+                                    p.out_wide != 0, elem0, p.out_tma ? &map_out : nullptr,
+                                    epi::TileOrigin{j0, i0, n}, threadIdx.x == 64, NC / 2);
       else
         epi::bias_tile(dacc, half, p.npad, p.cout, s_bias, p.act == TFC_ACT_RELU, valid, p.out,
                        p.out_f32 != 0, p.out_wide != 0, elem0);
       tc_fence_before();
       mbar_arrive(&bars->d1_empty[acc]);
     }
+    if (GDN && p.out_tma && threadIdx.x == 64) bulk_wait_read();
   } else {
     // ===== im2col builders =====
     const int t = threadIdx.x - (64 + kEpiThreads);
@@ -485,9 +489,10 @@ size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
 
 template <int KH, int KW>
 int launch(const tfc_conv_desc& d, const Plan& pl, const CUtensorMap& map_w,
-           const CUtensorMap& map_g, const CUtensorMap& map_img, const Params& p, int grid,
-           cudaStream_t st) {
-  void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const Params) = nullptr;
+           const CUtensorMap& map_g, const CUtensorMap& map_img, const CUtensorMap& map_out,
+           const Params& p, int grid, cudaStream_t st) {
+  void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap,
+               const Params) = nullptr;
   if (!pl.gdn) {
     kern = conv_thin_kernel<0, 0, KH, KW, 3>;
   } else {
@@ -498,7 +503,7 @@ int launch(const tfc_conv_desc& d, const Plan& pl, const CUtensorMap& map_w,
     }
   }
   TFC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
-  kern<<<grid, kThreads, pl.smem, st>>>(map_w, map_g, map_img, p);
+  kern<<<grid, kThreads, pl.smem, st>>>(map_w, map_g, map_img, map_out, p);
   TFC_LAUNCHED("conv_thin_kernel");
   return TFC_OK;
 }
@@ -569,7 +574,7 @@ int conv_thin(const tfc_conv_desc& d, const void* in, const float* w, const floa
       TFC_LAUNCHED("repack_gamma_kernel");
     }
   }
-  CUtensorMap map_w, map_g, map_img;
+  CUtensorMap map_w, map_g, map_img, map_out;
   {
     cuuint64_t dims[3] = {64, (cuuint64_t)pl.npad, (cuuint64_t)pl.kblocks};
     cuuint64_t str[2] = {128, (cuuint64_t)pl.npad * 128};
@@ -596,12 +601,23 @@ int conv_thin(const tfc_conv_desc& d, const void* in, const float* w, const floa
   } else {
     map_img = map_w;
   }
+  p.out_tma = pl.gdn && !p.out_f32 && d.cout % 64 == 0 && !(debug_bits() & 16);
+  if (p.out_tma) {
+    cuuint64_t dims[4] = {(cuuint64_t)d.cout, (cuuint64_t)d.wo, (cuuint64_t)d.ho, (cuuint64_t)d.n};
+    cuuint64_t str[3] = {(cuuint64_t)d.cout * 2, (cuuint64_t)d.wo * d.cout * 2,
+                         (cuuint64_t)d.ho * d.wo * d.cout * 2};
+    cuuint32_t box[4] = {64, (cuuint32_t)p.tw, (cuuint32_t)p.th, 1};
+    int rc = make_tensor_map_bf16(&map_out, out, 4, dims, str, box);
+    if (rc) return rc;
+  } else {
+    map_out = map_w;
+  }
   // the resident operands cost one 50-120 KB load per CTA: never fewer than 8 tiles per CTA
   p.chunk = tiles_per_cta() ? std::max(tiles_per_cta(), 8) : 0;
   const int grid = p.chunk ? (p.num_tiles + p.chunk - 1) / p.chunk
                            : std::min(p.num_tiles, persistent_grid());
-  if (d.kh == 5) return launch<5, 5>(d, pl, map_w, map_g, map_img, p, grid, st);
-  return launch<9, 9>(d, pl, map_w, map_g, map_img, p, grid, st);
+  if (d.kh == 5) return launch<5, 5>(d, pl, map_w, map_g, map_img, map_out, p, grid, st);
+  return launch<9, 9>(d, pl, map_w, map_g, map_img, map_out, p, grid, st);
 }
 
 }  // namespace tfc

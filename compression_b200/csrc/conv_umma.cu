@@ -61,15 +61,21 @@ struct Params {
   int32_t tiles_h, tiles_w;
   int32_t num_tiles;
   int32_t chunk;                    // tiles per CTA (0: persistent grid)
+  int32_t cs;                       // cluster size: the CTAs of a cluster share the B loads
   int32_t npad;                     // UMMA N (cout rounded up to 16)
   int32_t act;
   int32_t out_f32;
   int32_t out_wide;                 // 256-bit stores allowed
+  int32_t out_tma;                  // GDN output leaves by TMA tile stores
   int32_t phase_start[kMaxPhases + 1];
   Tap taps[kMaxTaps];
   const float* bias;
   const float* beta;
   void* out;
+};
+
+struct OutMaps {          // one output tensor map per phase of an upsampling layer (su <= 2)
+  CUtensorMap m[4];
 };
 
 struct __align__(8) Barriers {
@@ -93,7 +99,8 @@ template <int MODE, int NC>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
                  const __grid_constant__ CUtensorMap map_w,
-                 const __grid_constant__ CUtensorMap map_g, const Params p) {
+                 const __grid_constant__ CUtensorMap map_g,
+                 const __grid_constant__ OutMaps maps_out, const Params p) {
   constexpr bool GDN = MODE != 0;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [stages x (A 16 KB | B npad*128 B)] [A2: cout/64 x 16 KB] [bias|beta] [barriers]
@@ -118,7 +125,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
     prefetch_tmap(&map_a);
     prefetch_tmap(&map_w);
     if (GDN) prefetch_tmap(&map_g);
-    for (int s = 0; s < kStages; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
+    for (int s = 0; s < kStages; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], p.cs); }
     for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], epi::kEpilogueThreads); }
     mbar_init(&bars->a2_full, epi::kEpilogueThreads);
     mbar_init(&bars->d2_full, 1);
@@ -129,12 +136,24 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = bars->tmem_base;
-  // persistent (chunk == 0): tiles b, b + grid, ...; chunked: `chunk` consecutive tiles per CTA,
-  // many more CTAs than SMs, so the hardware places them on whatever SMs are free (used when
-  // the range coder of another batch occupies part of the GPU)
-  const int tile0 = p.chunk ? (int)blockIdx.x * p.chunk : (int)blockIdx.x;
-  const int tile1 = p.chunk ? min(tile0 + p.chunk, p.num_tiles) : p.num_tiles;
-  const int tile_step = p.chunk ? 1 : (int)gridDim.x;
+  // Clusters (cs > 1): the cs CTAs of a cluster walk cs ADJACENT tiles in lockstep — same output
+  // phase, hence the same taps in the same order — so each loads npad/cs rows of every weight
+  // (and gamma) tile and multicasts them to all: the B share of the L2 -> shared-memory traffic
+  // drops by cs.  A stage may be refilled once the MMAs of ALL CTAs have read it: every MMA warp
+  // commits to the `empty` barrier of every CTA (count cs).
+  const int rank = p.cs > 1 ? (int)cluster_ctarank() : 0;
+  const uint16_t mc_mask = (uint16_t)((1u << p.cs) - 1);
+  const int b_rows = p.npad / p.cs;
+  if (p.cs > 1) cluster_sync();      // the peers' barriers are initialised
+  // tile groups g, g + step, ... (a group = cs adjacent tiles, this CTA takes tile g + rank).
+  // persistent (chunk == 0): one group per cluster and round; chunked: `chunk` consecutive groups
+  // per cluster, many more CTAs than SMs, so the hardware places them on whatever SMs are free
+  // (used when the range coder of another batch occupies part of the GPU).  A tile index past
+  // the end (ragged last group) is a dummy: it repeats the last tile with its stores masked.
+  const int cluster_id = (int)blockIdx.x / p.cs;
+  const int tile0 = p.chunk ? cluster_id * p.chunk * p.cs : cluster_id * p.cs;
+  const int tile1 = p.chunk ? min(tile0 + p.chunk * p.cs, p.num_tiles) : p.num_tiles;
+  const int tile_step = p.chunk ? p.cs : (int)gridDim.x;
   const uint32_t idesc = make_idesc_bf16(kTileM, p.npad);
 
   auto tile_coords = [&](int tile, int& phase, int& n, int& i0, int& j0) {
@@ -159,13 +178,17 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
           mbar_wait(&bars->empty[stage], ph ^ 1);
           uint8_t* sa = smem + stage * stage_bytes;
           mbar_expect_tx(&bars->full[stage], b_bytes);
-          tma_load_2d(sa + kABytes, &map_g, &bars->full[stage], kc * kBlockK, 0);
+          if (p.cs > 1)
+            tma_load_2d_mc(sa + kABytes + rank * b_rows * 128, &map_g, &bars->full[stage],
+                           kc * kBlockK, rank * b_rows, mc_mask);
+          else
+            tma_load_2d(sa + kABytes, &map_g, &bars->full[stage], kc * kBlockK, 0);
           if (++stage == kStages) { stage = 0; ph ^= 1; }
         }
       };
-      for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
+      for (int g = tile0; g < tile1; g += tile_step, ++it) {
         int phase, n, i0, j0;
-        tile_coords(tile, phase, n, i0, j0);
+        tile_coords(min(g + rank, p.num_tiles - 1), phase, n, i0, j0);
         const int nk = (p.phase_start[phase + 1] - p.phase_start[phase]) * kchunks;
         const int slot = min(kGdnSlot, nk);
         int kb = 0;
@@ -178,7 +201,11 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
             mbar_expect_tx(&bars->full[stage], kABytes + b_bytes);
             tma_load_5d(sa, &map_a, &bars->full[stage], tap.pw * p.cin + kc * kBlockK,
                         j0 + tap.dw, tap.ph, i0 + tap.dh, n);
-            tma_load_3d(sa + kABytes, &map_w, &bars->full[stage], kc * kBlockK, 0, tap.widx);
+            if (p.cs > 1)
+              tma_load_3d_mc(sa + kABytes + rank * b_rows * 128, &map_w, &bars->full[stage],
+                             kc * kBlockK, rank * b_rows, tap.widx, mc_mask);
+            else
+              tma_load_3d(sa + kABytes, &map_w, &bars->full[stage], kc * kBlockK, 0, tap.widx);
             if (++stage == kStages) { stage = 0; ph ^= 1; }
           }
         }
@@ -205,14 +232,15 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k)
             umma_bf16(d2, da + (k * 2), db + (k * 2), idesc, (kc | k) != 0);
-          umma_commit(&bars->empty[stage]);
+          if (p.cs > 1) umma_commit_mc(&bars->empty[stage], mc_mask);
+          else umma_commit(&bars->empty[stage]);
           if (++stage == kStages) { stage = 0; ph ^= 1; }
         }
         umma_commit(&bars->d2_full);
       };
-      for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
+      for (int g = tile0; g < tile1; g += tile_step, ++it) {
         int phase, n, i0, j0;
-        tile_coords(tile, phase, n, i0, j0);
+        tile_coords(min(g + rank, p.num_tiles - 1), phase, n, i0, j0);
         const int acc = it & 1;
         mbar_wait(&bars->d1_empty[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
@@ -228,7 +256,8 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k)
             umma_bf16(d1, da + (k * 2), db + (k * 2), idesc, (kb | k) != 0);
-          umma_commit(&bars->empty[stage]);
+          if (p.cs > 1) umma_commit_mc(&bars->empty[stage], mc_mask);
+          else umma_commit(&bars->empty[stage]);
           if (++stage == kStages) { stage = 0; ph ^= 1; }
         }
         if (GDN && it > 0 && slot == nk) issue_gdn(it - 1);
@@ -243,13 +272,14 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
     const int r = quad * 32 + lane;                  // pixel within the tile / TMEM lane
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     uint32_t it = 0;
-    for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
+    for (int g = tile0; g < tile1; g += tile_step, ++it) {
       int phase, n, i0, j0;
-      tile_coords(tile, phase, n, i0, j0);
+      const bool dummy = g + rank >= p.num_tiles;
+      tile_coords(min(g + rank, p.num_tiles - 1), phase, n, i0, j0);
       const int acc = it & 1;
       const int li = r / p.tw, lj = r - li * p.tw;
       const int i2 = i0 + li, j2 = j0 + lj;
-      const bool valid = i2 < p.hs && j2 < p.ws;
+      const bool valid = i2 < p.hs && j2 < p.ws && !dummy;
       const int pi = phase / p.su, pj = phase - pi * p.su;
       const int64_t pix = ((int64_t)n * p.ho + (i2 * p.su + pi)) * p.wo + (j2 * p.su + pj);
       const uint32_t dacc = tmem + acc * 256 + lane_addr;
@@ -259,17 +289,22 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
       if constexpr (GDN)
         epi::gdn_tile<MODE, NC / 2>(dacc, a2, r, half * (NC / 2), s_bias, s_beta, &bars->a2_full,
                                     &bars->d2_full, it, valid, p.out, p.out_f32 != 0,
-                                    p.out_wide != 0, elem0);
+                                    p.out_wide != 0, elem0,
+                                    p.out_tma ? &maps_out.m[phase] : nullptr,
+                                    epi::TileOrigin{j0, i0, dummy ? -1 : n}, threadIdx.x == 64,
+                                    NC / 2);
       else
         epi::bias_tile(dacc, half, p.npad, p.cout, s_bias, p.act == TFC_ACT_RELU, valid, p.out,
                        p.out_f32 != 0, p.out_wide != 0, elem0);
       tc_fence_before();
       mbar_arrive(&bars->d1_empty[acc]);
     }
+    if (GDN && p.out_tma && threadIdx.x == 64) bulk_wait_read();
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem, 512);
+  if (p.cs > 1) cluster_sync();      // no CTA leaves while a peer may still signal its barriers
 }
 
 
@@ -443,6 +478,18 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
   p.tiles_h = (p.hs + p.th - 1) / p.th;
   p.tiles_w = (p.ws + p.tw - 1) / p.tw;
   p.num_tiles = d.su * d.su * d.n * p.tiles_h * p.tiles_w;
+  // cluster size: groups of cs adjacent tiles must not straddle an output phase, and every CTA
+  // loads npad/cs weight rows (whole 8-row swizzle atoms)
+  p.cs = 1;
+  {
+    const int per_phase = d.n * p.tiles_h * p.tiles_w;
+    const int want = conv_cluster();
+    for (int cs = 4; cs >= 2; cs /= 2) {
+      if (want != 0 && want != cs) continue;
+      if (per_phase % cs == 0 && p.npad % (8 * cs) == 0 && p.num_tiles >= 2 * cs) { p.cs = cs; break; }
+    }
+    if (want == 0 && p.cs == 4) p.cs = 2;      // default: pairs
+  }
 
   // weights (+ gamma^T) -> bf16 K-major
   __nv_bfloat16* wb = static_cast<__nv_bfloat16*>(ws);
@@ -474,14 +521,14 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
   {
     cuuint64_t dims[3] = {C, (cuuint64_t)p.npad, (cuuint64_t)taps};
     cuuint64_t str[2] = {C * 2, (cuuint64_t)p.npad * C * 2};
-    cuuint32_t box[3] = {kBlockK, (cuuint32_t)p.npad, 1};
+    cuuint32_t box[3] = {kBlockK, (cuuint32_t)(p.npad / p.cs), 1};
     int rc = make_map(&map_w, wb, 3, dims, str, box);
     if (rc) return rc;
   }
   if (gdn) {
     cuuint64_t dims[2] = {(cuuint64_t)d.cout, (cuuint64_t)p.npad};
     cuuint64_t str[1] = {(cuuint64_t)d.cout * 2};
-    cuuint32_t box[2] = {kBlockK, (cuuint32_t)p.npad};
+    cuuint32_t box[2] = {kBlockK, (cuuint32_t)(p.npad / p.cs)};
     int rc = make_map(&map_g, gb, 2, dims, str, box);
     if (rc) return rc;
   } else {
@@ -489,9 +536,28 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
   }
   const size_t smem = smem_bytes(p.npad, d.cout, gdn);
   p.chunk = tiles_per_cta();
-  const int grid = p.chunk ? (p.num_tiles + p.chunk - 1) / p.chunk
-                           : std::min(p.num_tiles, persistent_grid());
-  void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const Params) = nullptr;
+  const int groups = (p.num_tiles + p.cs - 1) / p.cs;
+  const int grid = p.cs * (p.chunk ? (groups + p.chunk - 1) / p.chunk
+                                   : std::max(1, std::min(groups, persistent_grid() / p.cs)));
+  OutMaps maps_out;
+  p.out_tma = gdn && !p.out_f32 && d.cout % 64 == 0 && d.su <= 2 && !(debug_bits() & 16);
+  for (int ph = 0; ph < 4; ++ph) {
+    if (p.out_tma && ph < d.su * d.su) {
+      // phase (pi, pj): pixels (su*i + pi, su*j + pj) of the output
+      const int pi = ph / d.su, pj = ph % d.su;
+      const cuuint64_t co2 = (cuuint64_t)d.cout * 2;
+      cuuint64_t dims[4] = {(cuuint64_t)d.cout, (cuuint64_t)p.ws, (cuuint64_t)p.hs, (cuuint64_t)d.n};
+      cuuint64_t str[3] = {d.su * co2, (cuuint64_t)d.su * d.wo * co2, (cuuint64_t)d.ho * d.wo * co2};
+      cuuint32_t box[4] = {kBlockK, (cuuint32_t)p.tw, (cuuint32_t)p.th, 1};
+      void* base = static_cast<uint8_t*>(out) + ((size_t)pi * d.wo + pj) * co2;
+      int rc = make_map(&maps_out.m[ph], base, 4, dims, str, box);
+      if (rc) return rc;
+    } else {
+      maps_out.m[ph] = map_w;
+    }
+  }
+  void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const OutMaps,
+               const Params) = nullptr;
   if (!gdn) {
     kern = conv_umma_kernel<0, 0>;
   } else {
@@ -505,7 +571,23 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
     }
   }
   TFC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<grid, kThreads, smem, st>>>(map_a, map_w, map_g, p);
+  if (p.cs > 1) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = p.cs;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    TFC_CUDA(cudaLaunchKernelEx(&cfg, kern, map_a, map_w, map_g, maps_out, p));
+  } else {
+    kern<<<grid, kThreads, smem, st>>>(map_a, map_w, map_g, maps_out, p);
+  }
   TFC_LAUNCHED("conv_umma_kernel");
   return TFC_OK;
 }

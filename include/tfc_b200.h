@@ -53,10 +53,14 @@ int64_t tfc_launch_count(void);
  *   TFC_CFG_TILES_PER_CTA          0 = persistent transform kernels (one CTA per SM walks the
  *                                  tile list); k > 0 = k consecutive tiles per CTA and as many
  *                                  CTAs as that takes, so the hardware scheduler fills whatever
- *                                  SMs the coder leaves free */
+ *                                  SMs the coder leaves free
+ *   TFC_CFG_CONV_CLUSTER           thread-block cluster size of the implicit-GEMM kernel (its CTAs
+ *                                  share each weight tile by TMA multicast): 0 = automatic (pairs
+ *                                  where the shape allows), 1 = off, 2, 4 */
 #define TFC_CFG_SM_BUDGET 1
 #define TFC_CFG_CODER_STREAMS_PER_CTA 2
 #define TFC_CFG_TILES_PER_CTA 3
+#define TFC_CFG_CONV_CLUSTER 4
 int tfc_configure(int key, int value);
 
 /* ------------------------------------------------------------------------------------------

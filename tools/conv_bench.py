@@ -25,12 +25,15 @@ def main():
   ap.add_argument("--check", action="store_true", help="compare with the CUDA-core kernel")
   ap.add_argument("--debug", type=int, default=0, help="kernel experiment bits (timing only)")
   ap.add_argument("--tiles-per-cta", type=int, default=0)
+  ap.add_argument("--cluster", type=int, default=0, help="0 auto, 1 off, 2, 4")
   args = ap.parse_args()
   from compression_b200.examples import bmshj2018
   from compression_b200.python.layers import gdn as gdn_lib
   from compression_b200 import _lib
   if args.debug:
     _lib.check(_lib.lib().tfc_configure(99, args.debug))
+  if args.cluster:
+    _lib.configure(conv_cluster=args.cluster)
   if args.tiles_per_cta:
     _lib.configure(tiles_per_cta=args.tiles_per_cta)
   dev = torch.device("cuda", 0)
