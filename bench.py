@@ -53,7 +53,7 @@ def parse_args():
                   help="images per CPU step (0: one per host thread, at most the batch)")
   ap.add_argument("--no-cpu-baseline", action="store_true")
   ap.add_argument("--verbose", action="store_true", help="stage/layer breakdown on stderr")
-  ap.add_argument("--depth", type=int, default=6,
+  ap.add_argument("--depth", type=int, default=8,
                   help="batches in flight on separate CUDA streams (1: strictly serial steps)")
   ap.add_argument("--tiles-per-cta", type=int, default=8,
                   help="transform kernels: tiles per CTA when depth > 1 (0: persistent grid)")
@@ -312,8 +312,7 @@ def run_b200(args):
     seen = {"strings": 0, "pixels": 0}
 
     def on_result(k, compressed, x_hat_u8):
-      seen["strings"] = (sum(len(b) for b in compressed.string) +
-                         sum(len(b) for b in compressed.side_string))
+      seen["strings"] = compressed.string.total_bytes + compressed.side_string.total_bytes
       seen["pixels"] += int(x_hat_u8.shape[0]) * int(x_hat_u8.shape[1]) * int(x_hat_u8.shape[2])
 
     pipe.roundtrip_host([x_u8_host] * (args.depth + 1), on_result)

@@ -17,3 +17,4 @@ from compression_b200.python.layers.signal_conv import SignalConv2D
 from compression_b200.python.layers.entropy_models import (
     EntropyModel, EntropyBottleneck, SymmetricConditional, GaussianConditional,
     LogisticConditional, LaplacianConditional)
+from compression_b200.python.util.packed_tensors import PackedTensors

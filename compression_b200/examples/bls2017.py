@@ -130,6 +130,23 @@ class Bls2017Model(object):
       return c
     return Compressed(rc.strings_to_device(c.string, self.device), c.x_shape, c.y_shape)
 
+  # ---- .tfci files (bls2017.py:247-254 write, :276-282 read): one image per file -----------
+  @staticmethod
+  def pack_tfci(c, image=0, model_id=None):
+    from compression_b200.python.util.packed_tensors import PackedTensors
+    packed = PackedTensors()
+    if model_id is not None:
+      packed.model = model_id
+    packed.pack(["string", "int32", "int32"],
+                [[c.string[image]], list(c.x_shape), list(c.y_shape)])
+    return packed.string
+
+  @staticmethod
+  def unpack_tfci(data):
+    from compression_b200.python.util.packed_tensors import PackedTensors
+    s, xs, ys = PackedTensors(data).unpack(["string", "int32", "int32"])
+    return Compressed([bytes(s[0])], tuple(int(v) for v in xs), tuple(int(v) for v in ys))
+
   def conv_layers(self):
     return self.analysis_transform.layers + self.synthesis_transform.layers
 

@@ -107,6 +107,35 @@ class HyperSynthesisTransform(_Sequential):
     ])
 
 
+class HostStrings(object):
+  """The byte strings of one batch as they sit in host memory after the device-to-host copy: a
+  [S, cap] uint8 slab and the S lengths.  Behaves like a list of `bytes` (materialised on
+  access); `total_bytes` needs no copy."""
+
+  def __init__(self, slab, nbytes):
+    self._slab, self._nbytes = slab.numpy(), nbytes.numpy()
+
+  def __len__(self):
+    return len(self._nbytes)
+
+  def __getitem__(self, i):
+    if isinstance(i, slice):
+      return [self[j] for j in range(*i.indices(len(self)))]
+    if i < 0:
+      i += len(self)
+    return self._slab[i, :self._nbytes[i]].tobytes()
+
+  def __iter__(self):
+    return (self[i] for i in range(len(self)))
+
+  def __eq__(self, other):
+    return list(self) == list(other)
+
+  @property
+  def total_bytes(self):
+    return int(self._nbytes.sum())
+
+
 class Pipeline(object):
   """Keeps several batches in flight on separate CUDA streams.
 
@@ -167,9 +196,10 @@ class Pipeline(object):
 
     Pinned staging buffers are allocated once per pipeline slot and reused (page-locking
     memory synchronises the device).  Results are delivered in order through
-    `on_result(k, compressed, x_hat_u8)`: `compressed` holds the strings as Python bytes,
-    `x_hat_u8` is a view of the slot's pinned buffer, valid during the callback.  Without a
-    callback the results are copied out and returned as a list."""
+    `on_result(k, compressed, x_hat_u8)`: `compressed.string` / `.side_string` are HostStrings
+    (sequences of bytes over the slot's pinned slab) and `x_hat_u8` is a view of the slot's
+    pinned buffer, all valid during the callback.  Without a callback the results are copied
+    out (strings as lists of bytes) and returned as a list."""
     from compression_b200.python.ops import range_coding_ops as rc
     model, dev = self.model, self.model.device
     n, nslots = len(batches_u8), self.depth + 1
@@ -194,7 +224,9 @@ class Pipeline(object):
       if on_result is not None:
         on_result(k, slot["host"], slot["x_hat"])
       else:
-        out_list.append((slot["host"], slot["x_hat"].clone()))
+        h = slot["host"]
+        out_list.append((Compressed(list(h.string), list(h.side_string), h.x_shape, h.y_shape,
+                                    h.z_shape), slot["x_hat"].clone()))
 
     def issue_front(k):
       slot, st = slots[k % nslots], self.streams[k % self.depth]
@@ -219,26 +251,16 @@ class Pipeline(object):
     def issue_back(k):
       slot, st = slots[k % nslots], self.streams[k % self.depth]
       c, staged, ev = slot.pop("front")
-      ev.synchronize()
-      strings = []
-      for hs, hn in staged:
-        a, nb = hs.numpy(), hn.numpy()
-        strings.append([a[i, :nb[i]].tobytes() for i in range(len(nb))])
-      host = Compressed(strings[0], strings[1], c.x_shape, c.y_shape, c.z_shape)
+      ev.synchronize()                   # the strings are in host memory now
+      host = Compressed(HostStrings(*staged[0]), HostStrings(*staged[1]), c.x_shape, c.y_shape,
+                        c.z_shape)
       with torch.cuda.stream(st):
+        # back to the device straight from the pinned slabs the strings arrived in
         dev_strings = []
-        for name, ss in (("y", host.string), ("z", host.side_string)):
-          cap = max([len(b) for b in ss] + [1])
-          cap += (-cap) % 16
-          up = pinned(slot, name + "_up", (len(ss), cap), torch.uint8)
-          ul = pinned(slot, name + "_uplen", (len(ss),), torch.int32)
-          ua, la = up.numpy(), ul.numpy()
-          for i, b in enumerate(ss):
-            ua[i, :len(b)] = np.frombuffer(b, np.uint8)
-            la[i] = len(b)
-          dev_strings.append((up.to(dev, non_blocking=True), ul.to(dev, non_blocking=True)))
+        for hs, hn in staged:
+          dev_strings.append((hs.to(dev, non_blocking=True), hn.to(dev, non_blocking=True)))
           if k == 0:
-            self.h2d_bytes += up.numel() + 4 * ul.numel()
+            self.h2d_bytes += hs.numel() + 4 * hn.numel()
         dc = Compressed(dev_strings[0], dev_strings[1], c.x_shape, c.y_shape, c.z_shape)
         x_hat = quantize_image(model.decompress(dc))
         out = pinned(slot, "x_hat", x_hat.shape, torch.uint8)
@@ -352,6 +374,28 @@ class Bmshj2018Model(object):
     return Compressed(rc.strings_to_device(c.string, self.device),
                       rc.strings_to_device(c.side_string, self.device),
                       c.x_shape, c.y_shape, c.z_shape)
+
+  # ---- .tfci files (bmshj2018.py:339-347 write, :369-377 read): one image per file ---------
+  @staticmethod
+  def pack_tfci(c, image=0, model_id=None):
+    """Host-side Compressed -> bytes of the reference's container for image `image`: tensors
+    [string, side_string, x_shape, y_shape, z_shape], each of the strings a length-1 vector."""
+    from compression_b200.python.util.packed_tensors import PackedTensors
+    packed = PackedTensors()
+    if model_id is not None:
+      packed.model = model_id
+    packed.pack(["string", "string", "int32", "int32", "int32"],
+                [[c.string[image]], [c.side_string[image]], list(c.x_shape), list(c.y_shape),
+                 list(c.z_shape)])
+    return packed.string
+
+  @staticmethod
+  def unpack_tfci(data):
+    """bytes of a .tfci file -> host-side Compressed holding that one image."""
+    from compression_b200.python.util.packed_tensors import PackedTensors
+    s, ss, xs, ys, zs = PackedTensors(data).unpack(["string", "string", "int32", "int32", "int32"])
+    return Compressed([bytes(s[0])], [bytes(ss[0])], tuple(int(v) for v in xs),
+                      tuple(int(v) for v in ys), tuple(int(v) for v in zs))
 
   # ---- export (host copies, for checkpoints and for the CPU checker in tests/bench) --------
   def export_weights(self):

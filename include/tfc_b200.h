@@ -55,8 +55,8 @@ int64_t tfc_launch_count(void);
  *                                  CTAs as that takes, so the hardware scheduler fills whatever
  *                                  SMs the coder leaves free
  *   TFC_CFG_CONV_CLUSTER           thread-block cluster size of the implicit-GEMM kernel (its CTAs
- *                                  share each weight tile by TMA multicast): 0 = automatic (pairs
- *                                  where the shape allows), 1 = off, 2, 4 */
+ *                                  share each weight tile by TMA multicast): 0 = automatic (currently
+ *                                  off: no gain measured), 1 = off, 2, 4 (where the shape allows) */
 #define TFC_CFG_SM_BUDGET 1
 #define TFC_CFG_CODER_STREAMS_PER_CTA 2
 #define TFC_CFG_TILES_PER_CTA 3

@@ -152,10 +152,50 @@ def test_pipeline_matches_batch_by_batch(setup, depth):
       assert torch.equal(x_hat, g_hat)
     u8 = [(x * 255).round().to(torch.uint8).pin_memory() for x in batches]
     seen = []
-    pipe.roundtrip_host(u8, lambda k, c, xh: seen.append((k, c, xh.clone())))
-  assert [k for k, _, _ in seen] == list(range(5))
-  for k, c, xh in seen:
+    # the callback's strings and pixels are views of pinned staging buffers: copy them out
+    pipe.roundtrip_host(u8, lambda k, c, xh: seen.append(
+        (k, list(c.string), list(c.side_string), c.string.total_bytes, xh.clone())))
+    listed = pipe.roundtrip_host(u8[:2])
+  assert [k for k, _, _, _, _ in seen] == list(range(5))
+  for k, string, side_string, total, xh in seen:
     ref = model.compress(u8[k].cuda().float() / 255)
     ref_host = model.to_host(ref)
-    assert c.string == ref_host.string and c.side_string == ref_host.side_string
+    assert string == ref_host.string and side_string == ref_host.side_string
+    assert total == sum(len(b) for b in ref_host.string)
+    if k < 2:
+      assert listed[k][0].string == string and torch.equal(listed[k][1], xh)
     assert torch.equal(xh, bmshj2018.quantize_image(model.decompress(ref)).cpu())
+
+
+def test_tfci_files_round_trip_one_image_each(setup, tmp_path):
+  """every image leaves as a `.tfci` file in the reference's container
+  (bmshj2018.py:339-347) and decodes from it (`:369-377`) to what the batch decode produces."""
+  model, _, x = setup
+  xd = x.cuda()
+  c = model.compress(xd)
+  host = model.to_host(c)
+  want = model.decompress(c)
+  for b in range(x.shape[0]):
+    path = tmp_path / ("img%d.tfci" % b)
+    path.write_bytes(model.pack_tfci(host, image=b, model_id="bmshj2018-b200"))
+    one = model.unpack_tfci(path.read_bytes())
+    assert one.string == [host.string[b]] and one.side_string == [host.side_string[b]]
+    assert (one.x_shape, one.y_shape, one.z_shape) == (host.x_shape, host.y_shape, host.z_shape)
+    got = model.decompress(model.to_device(one))
+    assert torch.equal(got[0], want[b])
+
+
+def test_cluster_multicast_conv_gives_the_same_strings(setup):
+  """TFC_CFG_CONV_CLUSTER: CTA pairs sharing the weight tiles by TMA multicast change nothing."""
+  import compression_b200 as tfc
+  model, _, x = setup
+  xd = x.cuda()
+  base = model.to_host(model.compress(xd))
+  try:
+    tfc.configure(conv_cluster=2)
+    paired = model.to_host(model.compress(xd))
+    x_hat = model.decompress(model.to_device(paired))
+  finally:
+    tfc.configure(conv_cluster=0)
+  assert paired.string == base.string and paired.side_string == base.side_string
+  assert torch.equal(x_hat, model.decompress(model.to_device(base)))
