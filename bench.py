@@ -35,9 +35,9 @@ WORKLOADS = {
     "c3": (1080, 1920, 32, 192),
     "tiny": (128, 192, 4, 192),
 }
-# DRAM traffic of the conv launches of one step as ncu measures it; per-kernel figures are in
-# profiles/r1d_conv_full_summary.md (the four large layers), the 17-launch sum is not captured
-NCU_TRAFFIC_BYTES_PER_STEP = None
+# DRAM traffic (read + write) of the conv launches of one step as ncu measures it: the sum over
+# the 14 layers in profiles/r1e_conv_full_summary.md (batch 64, 768x512); other workloads: null
+NCU_TRAFFIC_BYTES_PER_STEP = {"c2": 15.67e9}
 FLOP_PER_IMAGE_C2 = 149.31e9   # encode 75.61 + decode 73.70 GFLOP per 768x512 image
 
 
@@ -402,7 +402,7 @@ def run_b200(args):
                    "achieved": flops_step / (conv_ms_isolated * 1e-3) / 1e12, "peak": peak,
                    "unit": "TFLOP/s",
                    "frac": flops_step / (conv_ms_isolated * 1e-3) / 1e12 / peak,
-                   "traffic": NCU_TRAFFIC_BYTES_PER_STEP,
+                   "traffic": NCU_TRAFFIC_BYTES_PER_STEP.get(args.workload),
                    "peak_source": peaks["source"] + " bf16 sustained",
                    "ms_per_step": conv_ms_isolated, "flops_per_step": flops_step,
                    "in_pipeline": {"ms_per_step": conv_ms_step, "achieved": achieved,

@@ -612,8 +612,9 @@ int conv_thin(const tfc_conv_desc& d, const void* in, const float* w, const floa
   } else {
     map_out = map_w;
   }
-  // the resident operands cost one 50-120 KB load per CTA: never fewer than 8 tiles per CTA
-  p.chunk = tiles_per_cta() ? std::max(tiles_per_cta(), 8) : 0;
+  // the resident operands cost one 50-120 KB load per CTA (and a tile takes ~4 us): never fewer
+  // than 32 tiles per CTA
+  p.chunk = tiles_per_cta() ? std::max(tiles_per_cta(), 32) : 0;
   const int grid = p.chunk ? (p.num_tiles + p.chunk - 1) / p.chunk
                            : std::min(p.num_tiles, persistent_grid());
   if (d.kh == 5) return launch<5, 5>(d, pl, map_w, map_g, map_img, map_out, p, grid, st);
