@@ -53,7 +53,7 @@ def parse_args():
                   help="images per CPU step (0: one per host thread, at most the batch)")
   ap.add_argument("--no-cpu-baseline", action="store_true")
   ap.add_argument("--verbose", action="store_true", help="stage/layer breakdown on stderr")
-  ap.add_argument("--depth", type=int, default=8,
+  ap.add_argument("--depth", type=int, default=12,
                   help="batches in flight on separate CUDA streams (1: strictly serial steps)")
   ap.add_argument("--tiles-per-cta", type=int, default=8,
                   help="transform kernels: tiles per CTA when depth > 1 (0: persistent grid)")

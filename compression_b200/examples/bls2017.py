@@ -219,6 +219,8 @@ class Bls2017Trainer(object):
       t = train_ops.signal_conv2d(layer, t if t.shape[-1] == 3 else t.to(torch.bfloat16))
       if isinstance(layer.activation, gdn.GDN):
         t = self._gdn(layer.activation, t)
+      elif layer.activation is not None:
+        t = layer.activation(t)                     # torch.relu of the hyper transforms
     return t
 
   def _likelihood(self, y_tilde):

@@ -375,6 +375,10 @@ class Bmshj2018Model(object):
                       rc.strings_to_device(c.side_string, self.device),
                       c.x_shape, c.y_shape, c.z_shape)
 
+  def conv_layers(self):
+    return (self.analysis_transform.layers + self.synthesis_transform.layers +
+            self.hyper_analysis_transform.layers + self.hyper_synthesis_transform.layers)
+
   # ---- .tfci files (bmshj2018.py:339-347 write, :369-377 read): one image per file ---------
   @staticmethod
   def pack_tfci(c, image=0, model_id=None):
@@ -427,3 +431,49 @@ class Bmshj2018Model(object):
     return dict(eb_cdf=eb._quantized_cdf.cpu().numpy(), eb_len=eb._cdf_length.cpu().numpy(),
                 eb_off=eb._offset.cpu().numpy(), gc_cdf=gc._quantized_cdf.cpu().numpy(),
                 gc_len=gc._cdf_length.cpu().numpy(), gc_off=gc._offset.cpu().numpy())
+
+
+def _trainer_base():
+  from compression_b200.examples import bls2017
+  return bls2017.Bls2017Trainer
+
+
+class Bmshj2018Trainer(_trainer_base()):
+  """One synchronous data-parallel training step of the hyperprior model
+  (`/root/reference/examples/bmshj2018.py:201-282`), on the machinery of
+  `bls2017.Bls2017Trainer`: all trainables in one flat bucket (+ the quantiles in a second),
+  conv gradients through the CUDA kernels, one all-reduce per bucket, fused TF-Adam updates,
+  CDF table rebuild per rank.  The Gaussian likelihood and its gradient
+  (entropy_models.py:916-932, :965-969) are torch ops."""
+
+  def _gaussian_likelihood(self, y_tilde, sigma):
+    from compression_b200.python.ops import math_ops
+    model = self.model
+    # entropy_models.py:822-825: scales are bounded below by the smallest table entry
+    scale = math_ops.lower_bound(sigma, float(np.float32(model.scale_table[0])))
+    values = torch.abs(y_tilde)
+    const = -(2 ** -0.5)
+    upper = 0.5 * torch.erfc(const * ((0.5 - values) / scale))
+    lower = 0.5 * torch.erfc(const * ((-0.5 - values) / scale))
+    return math_ops.lower_bound(upper - lower, model._gc_tables.likelihood_bound)
+
+  def losses(self, x, noise=None):
+    """x float32 [B,H,W,3] in [0,1]; noise = (noise_y, noise_z) or None for fresh U(-.5,.5)
+    -> dict(loss, bpp, mse, aux)."""
+    model = self.model
+    num_pixels = float(np.prod(x.shape[:-1]))
+    y = self._transform(model.analysis_transform, x)
+    z = self._transform(model.hyper_analysis_transform, torch.abs(y))
+    noise_y, noise_z = noise if noise is not None else (None, None)
+    z_tilde = z + (noise_z if noise_z is not None else torch.rand_like(z) - .5)
+    z_lik = self._likelihood(z_tilde)
+    sigma = self._transform(model.hyper_synthesis_transform, z_tilde)
+    sigma = sigma[:, :y.shape[1], :y.shape[2], :]
+    y_tilde = y + (noise_y if noise_y is not None else torch.rand_like(y) - .5)
+    y_lik = self._gaussian_likelihood(y_tilde, sigma)
+    x_tilde = self._transform(model.synthesis_transform, y_tilde)
+    x_tilde = x_tilde[:, :x.shape[1], :x.shape[2], :]
+    bpp = (torch.log(y_lik).sum() + torch.log(z_lik).sum()) / (-np.log(2) * num_pixels)
+    mse = torch.mean((x - x_tilde) ** 2) * 255 ** 2
+    return dict(loss=self.lmbda * mse + bpp, bpp=bpp, mse=mse,
+                aux=model.entropy_bottleneck.losses[0], x_tilde=x_tilde)

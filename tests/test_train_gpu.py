@@ -178,3 +178,57 @@ def test_bls2017_compress_decompress_roundtrip(tfc, oracle):
   assert tuple(x_hat.shape) == (2, 64, 96, 3)
   y_hat = eb.decompress_device(c.string, (4, 6, 128), 128)
   assert torch.equal(y_hat, eb._dequantize(eb._quantize_symbols(y)))
+
+
+def _ref_transform(trainer, seq, t):
+  """A transform in float32 torch ops only (no CUDA kernels of ours)."""
+  from compression_b200.python.layers import gdn
+  for layer in seq.layers:
+    t = _ref_conv(t, layer.kernel, layer.bias, layer.corr, layer.strides_down[0],
+                  layer.strides_up[0])
+    if isinstance(layer.activation, gdn.GDN):
+      t = trainer._gdn(layer.activation, t)
+    elif layer.activation is not None:
+      t = layer.activation(t)
+  return t
+
+
+def test_bmshj2018_training_step_gradients_and_descent(tfc):
+  """SURVEY §8f rank 3 (bmshj2018.py:201-282): hyperprior R-D loss through the CUDA conv
+  kernels against the same graph in float32 torch ops, then a few descending steps."""
+  from compression_b200.examples import bmshj2018
+  model = bmshj2018.Bmshj2018Model(64, "cuda", seed=5)
+  trainer = bmshj2018.Bmshj2018Trainer(model, lmbda=0.01)
+  g = torch.Generator().manual_seed(6)
+  x = torch.rand((2, 64, 64, 3), generator=g).cuda()
+  noise = ((torch.rand((2, 4, 4, 64), generator=g) - .5).cuda(),
+           (torch.rand((2, 1, 1, 64), generator=g) - .5).cuda())
+  trainer.main.zero_grad()
+  out = trainer.losses(x, noise)
+  out["loss"].backward()
+  got = trainer.main.grad.clone()
+
+  trainer.main.zero_grad()
+  y = _ref_transform(trainer, model.analysis_transform, x)
+  z = _ref_transform(trainer, model.hyper_analysis_transform, torch.abs(y))
+  z_tilde = z + noise[1]
+  sigma = _ref_transform(trainer, model.hyper_synthesis_transform, z_tilde)[:, :4, :4, :]
+  y_tilde = y + noise[0]
+  x_tilde = _ref_transform(trainer, model.synthesis_transform, y_tilde)
+  bpp = (torch.log(trainer._gaussian_likelihood(y_tilde, sigma)).sum() +
+         torch.log(trainer._likelihood(z_tilde)).sum()) / (-np.log(2) * 2 * 64 * 64)
+  ref = 0.01 * torch.mean((x - x_tilde) ** 2) * 255 ** 2 + bpp
+  ref.backward()
+  want = trainer.main.grad.clone()
+  assert abs(float(out["loss"]) - float(ref)) <= 2e-2 * abs(float(ref))
+  cos = torch.dot(got, want) / (got.norm() * want.norm())
+  assert cos > 0.99, float(cos)
+  assert (got - want).norm() <= 0.15 * want.norm()
+
+  first = trainer.step(x, noise)
+  for _ in range(20):
+    last = trainer.step(x, noise)
+  assert np.isfinite(last["loss"]) and last["loss"] < first["loss"]
+  c = model.compress(x)
+  x_hat = model.decompress(c)
+  assert tuple(x_hat.shape) == (2, 64, 64, 3) and bool(torch.isfinite(x_hat).all())
