@@ -53,11 +53,14 @@ def parse_args():
                   help="images per CPU step (0: one per host thread, at most the batch)")
   ap.add_argument("--no-cpu-baseline", action="store_true")
   ap.add_argument("--verbose", action="store_true", help="stage/layer breakdown on stderr")
-  ap.add_argument("--depth", type=int, default=12,
-                  help="batches in flight on separate CUDA streams (1: strictly serial steps)")
+  ap.add_argument("--depth", type=int, default=0,
+                  help="batches in flight on separate CUDA streams (1: strictly serial steps; "
+                       "0: 12, or fewer if 12 batches of activations would not fit in HBM)")
   ap.add_argument("--tiles-per-cta", type=int, default=8,
                   help="transform kernels: tiles per CTA when depth > 1 (0: persistent grid)")
-  ap.add_argument("--coder-pack", type=int, default=4, help="coder streams per CTA (depth > 1)")
+  ap.add_argument("--coder-pack", type=int, default=0,
+                  help="coder streams per CTA when depth > 1 (0: by the number of streams in "
+                       "flight: 4 at batch 64 x 12, 2 at batch 32 x 8)")
   return ap.parse_args()
 
 
@@ -284,6 +287,15 @@ def run_b200(args):
     torch.cuda.synchronize()
 
   pixels_per_step = batch * h * w
+  if args.depth <= 0:
+    # ~230 bytes of activations per input pixel stay reserved per batch in flight (measured:
+    # 15.2 GB for 32 x 1080p, 5.8 GB for 64 x 768x512); keep the pipeline inside 3/4 of HBM
+    total_mem = torch.cuda.get_device_properties(dev).total_memory
+    args.depth = max(1, min(12, int(0.75 * total_mem / (230.0 * pixels_per_step))))
+  if args.coder_pack <= 0:
+    # streams in flight / CTAs wanted: the coder is latency bound per stream, and 4 streams per
+    # CTA is the measured optimum once there are more streams than ~4 per SM
+    args.coder_pack = max(1, min(4, int(round(batch * args.depth / 150.0))))
   pipe = model.pipeline(args.depth, args.tiles_per_cta, args.coder_pack)
 
   with pipe:

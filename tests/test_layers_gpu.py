@@ -264,6 +264,10 @@ UMMA_CASES = [
     (192, 192, 5, False, 1, 2, 12, 20, "igdn"),
     (128, 128, 5, True, 2, 1, 20, 36, "gdn"),
     (64, 64, 5, False, 1, 2, 6, 10, "igdn"),
+    # sizes that are not multiples of the stride (1080p: 135 -> 68 rows): zero-extended copy
+    (192, 192, 5, True, 2, 1, 27, 45, "gdn"),
+    (192, 192, 5, True, 2, 1, 33, 48, None),
+    (64, 128, 5, True, 2, 1, 16, 21, "relu"),
 ]
 
 
