@@ -184,10 +184,25 @@ class Pipeline(object):
     cur = self._fork()
     with rc.deferred_checks():
       for k, x in enumerate(batches):
-        with torch.cuda.stream(self.streams[k % self.depth]):
-          outs.append(model.decompress(model.compress(x)))
+        st = self.streams[k % self.depth]
+        with torch.cuda.stream(st):
+          outs.append(model.decompress(model.compress(x, self._stagger(k, st))))
       self._join(cur)
     return outs
+
+  def _stagger(self, k, st):
+    """First wave only: batch k starts its transforms when batch k-1 has finished its own, so
+    the `depth` batches that start together do not run transforms, then coders, in lockstep
+    (the GPU is transform-bound during that time either way).  Later batches inherit the
+    stagger from their predecessors on the same stream."""
+    if k == 0:
+      self._wave_ev = None
+    if k >= self.depth:
+      return None
+    if self._wave_ev is not None:
+      st.wait_event(self._wave_ev)
+    ev = self._wave_ev = torch.cuda.Event()
+    return lambda: ev.record(st)
 
   def roundtrip_host(self, batches_u8, on_result=None):
     """batches_u8: pinned host uint8 [B,H,W,3] tensors.  Per batch: image H2D, compress,
@@ -233,7 +248,7 @@ class Pipeline(object):
       deliver(slot)                      # the slot's previous batch must be out of its buffers
       with torch.cuda.stream(st):
         x = batches_u8[k].to(dev, non_blocking=True).float() / 255
-        c = model.compress(x)
+        c = model.compress(x, self._stagger(k, st))
         staged = []
         for name, (slab, nbytes) in (("y", c.string), ("z", c.side_string)):
           hs = pinned(slot, name + "_slab", slab.shape, torch.uint8)
@@ -325,9 +340,13 @@ class Bmshj2018Model(object):
     sigma = sigma[:, :y.shape[1], :y.shape[2], :].contiguous()
     return y, z, sigma
 
-  def compress(self, x):
+  def compress(self, x, after_analysis=None):
+    """`after_analysis`: called once the transforms are queued and before the entropy coder is
+    (the pipeline records an event there to stagger its first wave of batches)."""
     x = x.to(self.device)
     y, z, sigma = self.analyse(x)
+    if after_analysis is not None:
+      after_analysis()
     side_string = self.entropy_bottleneck.compress_device(z)
     string = self._conditional(sigma).compress_device(y)
     return Compressed(string, side_string, tuple(x.shape[1:-1]), tuple(y.shape[1:-1]),
