@@ -248,7 +248,7 @@ class EntropyBottleneck(EntropyModel):
         _lib.ptr(self._medians), _f32(max(self.likelihood_bound, 0.0)), mode,
         _lib.ptr(values) if not training else ctypes.c_void_p(0), _lib.ptr(lik),
         _lib.stream_ptr(x.device)))
-    return values, lik
+    return self._uncentered(values), lik
 
   def _quantize_symbols(self, x):
     sym = torch.empty(x.shape, dtype=torch.int32, device=x.device)
@@ -298,9 +298,7 @@ class SymmetricConditional(EntropyModel):
     if any(s <= 0 for s in self.scale_table):
       raise ValueError("`scale_table` must be an iterable of positive numbers.")
     self._scale_bound = None if scale_bound is None else float(scale_bound)
-    if mean is not None:
-      raise NotImplementedError("`mean=` is not built (SURVEY §8f rank 2)")
-    self._mean = None
+    self._mean = mean      # entropy_models.py:734-735: same shape as the inputs, or None
     self._indexes = None
     if indexes is not None:
       if indexes.dtype != torch.int32:
@@ -389,6 +387,13 @@ class SymmetricConditional(EntropyModel):
       self._indexes = self.compute_indexes(self._scale)
     self.built = True
 
+  def _centered(self, x):
+    """inputs minus `mean` (entropy_models.py:895-897, :917-919)."""
+    return x if self._mean is None else x - self._mean.to(x.dtype)
+
+  def _uncentered(self, values):
+    return values if self._mean is None else values + self._mean.to(values.dtype)
+
   def _bounded_scale(self):
     b = self._effective_bound()
     s = self._scale.float()
@@ -398,18 +403,19 @@ class SymmetricConditional(EntropyModel):
     x = self._check_inputs(inputs)
     if not self.built:
       self.build()
+    x = self._centered(x)
     values = x + (torch.rand_like(x) - .5) if training else torch.floor(x + .5)
     a = torch.abs(values)
     s = self._bounded_scale()
     lik = self._standardized_cumulative((.5 - a) / s) - self._standardized_cumulative((-.5 - a) / s)
     if self.likelihood_bound > 0:
       lik = math_ops.lower_bound(lik, self.likelihood_bound)
-    return values, lik
+    return self._uncentered(values), lik
 
   def _symbols_and_indexes(self, x):
     if not self.built:
       self.build()
-    sym = torch.floor(x + .5).to(torch.int32)
+    sym = torch.floor(self._centered(x) + .5).to(torch.int32)
     return sym, self._indexes, False
 
   def _dequantize(self, symbols, out_dtype=torch.float32):
@@ -417,7 +423,7 @@ class SymmetricConditional(EntropyModel):
     _lib.check(_lib.lib().tfc_symbols_to_float(
         _lib.ptr(symbols), _i64(symbols.numel()), _lib.ptr(out),
         1 if out_dtype == torch.bfloat16 else 0, _lib.stream_ptr(symbols.device)))
-    return out
+    return self._uncentered(out)
 
   def _prepare_indexes(self, shape=None):
     del shape
@@ -453,6 +459,7 @@ class GaussianConditional(SymmetricConditional):
     if not self.built:
       self.build()
     mode = 0
+    x = self._centered(x).contiguous()
     if training:
       x = x + (torch.rand_like(x) - .5)
       mode = 1
@@ -467,12 +474,13 @@ class GaussianConditional(SymmetricConditional):
         _f32(max(self.likelihood_bound, 0.0)), mode,
         _lib.ptr(values) if not training else ctypes.c_void_p(0), _lib.ptr(lik),
         _lib.stream_ptr(x.device)))
-    return values, lik
+    return self._uncentered(values), lik
 
   def _symbols_and_indexes(self, x):
     """Quantise and look the scale index up in one pass over (y, sigma)."""
     if not getattr(self, "_tables_built", False):
       self.build_tables(x.device)
+    x = self._centered(x).contiguous()
     sym = torch.empty(x.shape, dtype=torch.int32, device=x.device)
     if self._indexes is not None:
       idx, sigma, idx_ptr = self._indexes, x, ctypes.c_void_p(0)

@@ -233,6 +233,36 @@ def test_gaussian_conditional_call_indexes_codec(tfc, oracle):
   np.testing.assert_array_equal(dec.cpu().numpy(), sym.astype(np.float32))
 
 
+@pytest.mark.parametrize("kind", ["gaussian", "logistic", "laplacian"])
+def test_conditional_quantization_and_codec_with_mean(tfc, kind):
+  """entropy_models_test.py:300-320 (test_quantization_mean) and :339-361 (test_codec_mean):
+  values are quantised to integers offset by the mean, through call and through the codec;
+  the likelihood is that of the centred value."""
+  cls = {"gaussian": tfc.GaussianConditional, "logistic": tfc.LogisticConditional,
+         "laplacian": tfc.LaplacianConditional}[kind]
+  rng = np.random.default_rng(15)
+  values = np.linspace(-50, 50, 100).astype(np.float32)
+  mean = rng.standard_normal(values.shape).astype(np.float32)
+  scale = rng.uniform(1, 10, size=values.shape).astype(np.float32)
+  layer = cls(torch.from_numpy(scale).cuda(), [1], mean=torch.from_numpy(mean).cuda())
+  quantized, lik = layer(torch.from_numpy(values).cuda(), training=False)
+  want = np.floor(values - mean + np.float32(.5)) + mean
+  np.testing.assert_allclose(quantized.cpu().numpy(), want, rtol=0, atol=1e-5)
+  plain = cls(torch.from_numpy(scale).cuda(), [1])
+  _, lik0 = plain(torch.from_numpy(values - mean).cuda(), training=False)
+  np.testing.assert_allclose(lik.cpu().numpy(), lik0.cpu().numpy(), rtol=1e-6, atol=1e-9)
+
+  values2 = values[None]
+  mean2 = rng.standard_normal(values2.shape).astype(np.float32)
+  scale2 = rng.uniform(25, 75, size=values2.shape).astype(np.float32)
+  codec = cls(torch.from_numpy(scale2).cuda(), [2.0 ** x for x in range(-10, 10)],
+              mean=torch.from_numpy(mean2).cuda())
+  strings = codec.compress(torch.from_numpy(values2).cuda())
+  decoded = codec.decompress(strings)
+  want2 = np.floor(values2 - mean2 + np.float32(.5)) + mean2
+  np.testing.assert_allclose(decoded.cpu().numpy(), want2, rtol=0, atol=1e-5)
+
+
 def test_lower_bound_gradients(tfc):
   """math_ops_test.py:28-102."""
   x = torch.tensor([-1., 1.], requires_grad=True)
