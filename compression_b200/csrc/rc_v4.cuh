@@ -236,7 +236,7 @@ __host__ __device__ inline size_t dec_pair_bytes(int round, int lin) {
   return (size_t)2 * (round + kRecPad) * 16   // records
          + (size_t)2 * round * 4              // values decoded by the general path
          + (size_t)2 * round                  // one code byte per symbol
-         + (size_t)2 * lin * 2 + 16;          // two linear stream windows, ctrl
+         + (size_t)2 * lin * 2 + 32;          // two linear stream windows, ctrl[8]
 }
 
 // Stream words reach the chain through per-round LINEAR windows (no index masking on the
@@ -306,14 +306,17 @@ __global__ void __launch_bounds__(512, 1) decode_unbounded_v4(const DecParamsV4 
       const int cnt = (int)min((int64_t)R, p.n - base);
       uint4* dst = recs + (r & 1) * (kRmax + kRecPad);
       int slow = 0;       // records of this round that are not in the fast class
+      uint32_t longest = 5;   // entries of the longest row of this round (fast class: 5)
 #pragma unroll 4
       for (int j = lane; j < cnt; j += 32) {
         const uint4 q = t.rowrec[__ldg(idx + base + j)];
         dst[j] = q;
         slow += q.z == 0u;
+        longest = max(longest, q.z == 0u ? q.y : 5u);
       }
       slow = __reduce_add_sync(0xFFFFFFFFu, slow);
-      if (lane == 0) ctrl[2 + (r & 1)] = (uint32_t)slow;
+      longest = __reduce_max_sync(0xFFFFFFFFu, longest);
+      if (lane == 0) { ctrl[2 + (r & 1)] = (uint32_t)slow; ctrl[4 + (r & 1)] = longest; }
     };
     auto flush = [&](int64_t r) {
       const int64_t base = r * R;
@@ -459,8 +462,71 @@ __global__ void __launch_bounds__(512, 1) decode_unbounded_v4(const DecParamsV4 
         *cp = 0xFF;
       }
     };
+    // A round with many general symbols whose rows all have <= 33 entries (every
+    // EntropyBottleneck stream; Gaussian streams of a trained model at moderate scales): ONE
+    // branch-free body for every symbol, whatever its class — lane l tests entry l + 1 of the
+    // row, a ballot finds the symbol, two shuffles fetch its bounds.  Everything that does not
+    // depend on the coder state (record -> row info -> the lane's two table entries) is loaded
+    // one to three symbols ahead, so the serial chain is multiply, compare, ballot, shuffle,
+    // select.
+    auto uniform = [&]() {
+      const uint32_t last_row = (uint32_t)(p.rows - 1);
+      auto row_of = [&](int jj) {     // records past the round's end are uninitialised: clamp
+        return (int)min(reinterpret_cast<const uint32_t*>(rc + jj)[3], last_row);
+      };
+      uint32_t span1 = span - 1u;
+      uint32_t ck, cq;
+      int len;
+      auto entries = [&](const int4& ri) {
+        len = ri.y;
+        const int k = min(1 + lane, len - 1);
+        ck = t.at(ri.x + k);
+        cq = t.at(ri.x + k - 1);
+      };
+      entries(t.rowinfo[row_of(0)]);
+      int4 ri1 = t.rowinfo[row_of(1)];
+      int row2 = row_of(2);
+      for (; j < cnt; ++j) {
+        if ((j & 7) == 0) guard();
+        const uint32_t c_k = ck, c_q = cq;
+        const int c_len = len;
+        entries(ri1);                       // symbol j + 1
+        ri1 = t.rowinfo[row2];              // symbol j + 2
+        row2 = row_of(j + 3);               // symbol j + 3 (the records are padded past the round)
+        const uint32_t wn = lds16(wa);
+        const bool over = (c_k >> 16) != 0u;
+        const uint32_t tk = over ? span1 + 1u : scale16(span1, c_k);
+        const uint32_t tq = scale16(span1, c_q);
+        const uint32_t mk = __ballot_sync(0xFFFFFFFFu, over || tk > rem);
+        int f = __ffs(mk) - 1;
+        if (mk == 0u) { d.corrupt = true; f = c_len - 2; }
+        const uint32_t a = __shfl_sync(0xFFFFFFFFu, tq, f);
+        const uint32_t hi = __shfl_sync(0xFFFFFFFFu, tk, f);
+        const uint32_t ns1 = hi - 1u - a;
+        const bool rn = (ns1 >> 16) == 0u;
+        rem -= a;
+        span1 = rn ? ((ns1 << 16) | 0xFFFFu) : ns1;
+        rem = rn ? ((rem << 16) | w0) : rem;
+        w0 = rn ? wn : w0;
+        wa += rn ? 2u : 0u;
+        int32_t v = f;
+        if (v == c_len - 2) {
+          d.rem = rem; d.span1 = span1; d.w0 = w0; d.wa = wa;
+          v = decode_escape(d, ow, p.max_digits, v);
+          rem = d.rem; span1 = d.span1; w0 = d.w0; wa = d.wa;
+          guard();
+        }
+        ev[j] = v;
+        cb[j] = 0xFF;
+      }
+      span = span1 + 1u;
+      rp = rc + cnt;
+      cp = cb + cnt;
+    };
     if (ctrl[2 + (r & 1)] * 8u > (uint32_t)cnt) {
-      careful(cnt);     // too many general symbols for speculation in groups of four to pay
+      // too many general symbols for speculation in groups of four to pay
+      if (ctrl[4 + (r & 1)] <= 33u) uniform();
+      else careful(cnt);
     }
     while (j < cnt) {
       if (j + 4 <= cnt) {

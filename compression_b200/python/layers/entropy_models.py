@@ -248,7 +248,7 @@ class EntropyBottleneck(EntropyModel):
         _lib.ptr(self._medians), _f32(max(self.likelihood_bound, 0.0)), mode,
         _lib.ptr(values) if not training else ctypes.c_void_p(0), _lib.ptr(lik),
         _lib.stream_ptr(x.device)))
-    return self._uncentered(values), lik
+    return values, lik
 
   def _quantize_symbols(self, x):
     sym = torch.empty(x.shape, dtype=torch.int32, device=x.device)
