@@ -17,6 +17,8 @@
 // unbounded_index_range_coding_kernels.cc:189-251, :308-368.
 #pragma once
 
+#include <type_traits>
+
 namespace v4 {
 
 constexpr int kRing = 8192;            // stream ring: 16-bit words per stream
@@ -469,55 +471,64 @@ __global__ void __launch_bounds__(512, 1) decode_unbounded_v4(const DecParamsV4 
     // depend on the coder state (record -> row info -> the lane's two table entries) is loaded
     // one to three symbols ahead, so the serial chain is multiply, compare, ballot, shuffle,
     // select.
-    auto uniform = [&]() {
+    auto uniform = [&](auto staged) {
+      constexpr bool kStaged = decltype(staged)::value;     // tables in shared memory
       const uint32_t last_row = (uint32_t)(p.rows - 1);
       auto row_of = [&](int jj) {     // records past the round's end are uninitialised: clamp
         return (int)min(reinterpret_cast<const uint32_t*>(rc + jj)[3], last_row);
       };
+      auto entry = [&](int i) {
+        return kStaged ? t.tbl[i] : ((uint32_t)__ldg(t.gcdf + i) << t.sh);
+      };
       uint32_t span1 = span - 1u;
-      uint32_t ck, cq;
+      uint32_t ck;
       int len;
       auto entries = [&](const int4& ri) {
         len = ri.y;
-        const int k = min(1 + lane, len - 1);
-        ck = t.at(ri.x + k);
-        cq = t.at(ri.x + k - 1);
+        ck = entry(ri.x + min(1 + lane, len - 1));
       };
       entries(t.rowinfo[row_of(0)]);
       int4 ri1 = t.rowinfo[row_of(1)];
       int row2 = row_of(2);
-      for (; j < cnt; ++j) {
-        if ((j & 7) == 0) guard();
-        const uint32_t c_k = ck, c_q = cq;
-        const int c_len = len;
-        entries(ri1);                       // symbol j + 1
-        ri1 = t.rowinfo[row2];              // symbol j + 2
-        row2 = row_of(j + 3);               // symbol j + 3 (the records are padded past the round)
-        const uint32_t wn = lds16(wa);
-        const bool over = (c_k >> 16) != 0u;
-        const uint32_t tk = over ? span1 + 1u : scale16(span1, c_k);
-        const uint32_t tq = scale16(span1, c_q);
-        const uint32_t mk = __ballot_sync(0xFFFFFFFFu, over || tk > rem);
-        int f = __ffs(mk) - 1;
-        if (mk == 0u) { d.corrupt = true; f = c_len - 2; }
-        const uint32_t a = __shfl_sync(0xFFFFFFFFu, tq, f);
-        const uint32_t hi = __shfl_sync(0xFFFFFFFFu, tk, f);
-        const uint32_t ns1 = hi - 1u - a;
-        const bool rn = (ns1 >> 16) == 0u;
-        rem -= a;
-        span1 = rn ? ((ns1 << 16) | 0xFFFFu) : ns1;
-        rem = rn ? ((rem << 16) | w0) : rem;
-        w0 = rn ? wn : w0;
-        wa += rn ? 2u : 0u;
-        int32_t v = f;
-        if (v == c_len - 2) {
-          d.rem = rem; d.span1 = span1; d.w0 = w0; d.wa = wa;
-          v = decode_escape(d, ow, p.max_digits, v);
-          rem = d.rem; span1 = d.span1; w0 = d.w0; wa = d.wa;
-          guard();
+      while (j < cnt) {
+        guard();
+        const int stop = min(j + 8, cnt);
+        for (; j < stop; ++j) {
+          const uint32_t c_k = ck;
+          const int c_len = len;
+          entries(ri1);                       // symbol j + 1
+          ri1 = t.rowinfo[row2];              // symbol j + 2
+          row2 = row_of(j + 3);               // symbol j + 3 (records are padded past the round)
+          const uint32_t wn = lds16(wa);
+          // lane l holds T_l = floor(span * row[l + 1] / 2^16) (nondecreasing in l; the entry
+          // 2^16 stands for span itself).  With P_l = (T_l > rem) the symbol is the first lane
+          // with P, its lower bound the largest T without P (0 if none: row[0] = 0) and its
+          // upper bound the smallest T with P — two warp reductions, no ballot / find-first.
+          const bool over = (c_k >> 16) != 0u;
+          const uint32_t tk = scale16(span1, c_k);
+          const bool pl = over || tk > rem;
+          const uint32_t hi1 = over ? span1 : tk - 1u;       // upper bound - 1
+          const uint32_t a = __reduce_max_sync(0xFFFFFFFFu, pl ? 0u : tk);
+          const uint32_t b1 = __reduce_min_sync(0xFFFFFFFFu, pl ? hi1 : 0xFFFFFFFFu);
+          const uint32_t below = __ballot_sync(0xFFFFFFFFu, !pl);
+          const uint32_t ns1 = b1 - a;
+          const bool rn = (ns1 >> 16) == 0u;
+          rem -= a;
+          span1 = rn ? ((ns1 << 16) | 0xFFFFu) : ns1;
+          rem = rn ? ((rem << 16) | w0) : rem;
+          w0 = rn ? wn : w0;
+          wa += rn ? 2u : 0u;
+          int32_t v = __popc(below);
+          if (v >= c_len - 2) {
+            if (v > c_len - 2) { d.corrupt = true; v = c_len - 2; }   // ran past the row
+            d.rem = rem; d.span1 = span1; d.w0 = w0; d.wa = wa;
+            v = decode_escape(d, ow, p.max_digits, v);
+            rem = d.rem; span1 = d.span1; w0 = d.w0; wa = d.wa;
+            guard();
+          }
+          ev[j] = v;
+          cb[j] = 0xFF;
         }
-        ev[j] = v;
-        cb[j] = 0xFF;
       }
       span = span1 + 1u;
       rp = rc + cnt;
@@ -525,8 +536,9 @@ __global__ void __launch_bounds__(512, 1) decode_unbounded_v4(const DecParamsV4 
     };
     if (ctrl[2 + (r & 1)] * 8u > (uint32_t)cnt) {
       // too many general symbols for speculation in groups of four to pay
-      if (ctrl[4 + (r & 1)] <= 33u) uniform();
-      else careful(cnt);
+      if (ctrl[4 + (r & 1)] > 33u) careful(cnt);
+      else if (t.tbl != nullptr) uniform(std::true_type{});
+      else uniform(std::false_type{});
     }
     while (j < cnt) {
       if (j + 4 <= cnt) {
