@@ -161,12 +161,13 @@ class SignalConv2D(object):
     return self.bias_var if bp is None else bp(self.bias_var)
 
   # ---- geometry: the reference's dispatch reduced to the normalised form ---------------------
-  def _plan(self):
-    """Returns (flip, pad_begin (top, left), out_len_fn) for the current arguments."""
-    if self.padding == "same_reflect":
-      raise NotImplementedError("padding='same_reflect' is not built (SURVEY §8f rank 4)")
-    if self.data_format != "channels_last":
-      raise NotImplementedError("data_format='channels_first' is not built")
+  def _plan(self, mode=None):
+    """Returns (flip, pad_begin (top, left), out_len_fn) for the current arguments, the input
+    being channels_last.  `mode` overrides the padding mode (the pre-padded same_reflect path
+    runs as "valid" / "same_zeros" over the reflected image, see `_reflect`)."""
+    mode = mode or self.padding
+    if mode == "same_reflect":
+      raise NotImplementedError("same_reflect is planned on the pre-padded input: use __call__")
     if self.strides_down[0] != self.strides_down[1] or self.strides_up[0] != self.strides_up[1]:
       raise NotImplementedError("anisotropic strides are not built")
     k = self.kernel_support
@@ -177,7 +178,7 @@ class SignalConv2D(object):
       corr, flip = True, True
     elif corr and su != 1 and odd:          # signal_conv.py:733-738
       corr, flip = False, True
-    if self.padding == "valid":
+    if mode == "valid":
       padding = [(0, 0), (0, 0)]
     else:
       padding = padding_ops.same_padding_for_kernel(k, corr, (su, su))
@@ -190,7 +191,7 @@ class SignalConv2D(object):
     if not corr:
       # conv2d_backprop_input with explicit padding p == zero-stuffed correlation with the
       # flipped kernel and padding k-1-p (:629-707); prepadding is zero in EXPLICIT mode
-      if self.padding == "valid":
+      if mode == "valid":
         p = [(k[0] - 1, k[0] - 1), (k[1] - 1, k[1] - 1)]
       else:
         p = [(k[i] // 2, (k[i] - 1) // 2) for i in range(2)]
@@ -227,7 +228,7 @@ class SignalConv2D(object):
   def effective_weights(self):
     """(kernel [kh,kw,cin,cout] in correlation form, bias|None), float32 contiguous; cached."""
     if self._eff is None:
-      flip, _, _ = self._plan()
+      flip, _, _ = self._plan("same_zeros" if self.padding == "same_reflect" else None)
       w = self.kernel.float()
       if flip:
         w = torch.flip(w, dims=(0, 1))
@@ -236,7 +237,47 @@ class SignalConv2D(object):
     return self._eff
 
   # ---- forward -----------------------------------------------------------------------------
+  def _reflect(self, x):
+    """same_reflect (signal_conv.py:744-758): the reference pre-pads with tf.pad(REFLECT) and
+    then runs its VALID ops; for upsampled convolutions the pre-padding is folded into the
+    explicit padding of conv2d_backprop_input (`:651-666`), which equals the same_zeros result
+    over the reflected image cropped by `prepad * strides_up`.  Returns (padded x, mode to plan
+    with, crop (top, left) of the output or None)."""
+    k, su = self.kernel_support, self.strides_up[0]
+    corr = self.corr
+    odd = all(s % 2 == 1 for s in k)
+    if not corr and su == 1 and odd:
+      corr = True
+    elif corr and su != 1 and odd:
+      corr = False
+    pad = padding_ops.same_padding_for_kernel(k, corr, (su, su))
+    n, h, w, _ = x.shape
+    if max(pad[0]) >= h or max(pad[1]) >= w:
+      raise ValueError("same_reflect needs the image to be larger than the padding")
+
+    def idx(length, lo, hi):
+      i = torch.arange(-lo, length + hi, device=x.device)
+      i = torch.where(i < 0, -i, i)
+      return torch.where(i >= length, 2 * (length - 1) - i, i)
+
+    x = x.index_select(1, idx(h, *pad[0])).index_select(2, idx(w, *pad[1]))
+    if corr and su == 1:
+      return x, "valid", None
+    if self.strides_down[0] != 1:
+      self._raise_notimplemented()
+    return x, "same_zeros", (pad[0][0] * su, pad[1][0] * su)
+
   def __call__(self, inputs, out_dtype=None):
+    """inputs: [batch, height, width, channels] (channels_last) or [batch, channels, height,
+    width] (channels_first; converted on the way in and out — the kernels are channels_last)."""
+    if self.data_format == "channels_first":
+      if inputs.dim() != 4:
+        raise ValueError("SignalConv2D expects a 4-D input")
+      out = self._call_nhwc(inputs.permute(0, 2, 3, 1), out_dtype)
+      return out.permute(0, 3, 1, 2).contiguous()
+    return self._call_nhwc(inputs, out_dtype)
+
+  def _call_nhwc(self, inputs, out_dtype=None):
     x = inputs
     _lib.require_cuda(x, "inputs")
     if x.dim() != 4:
@@ -248,12 +289,17 @@ class SignalConv2D(object):
                        % (self.input_channels, x.shape[-1]))
     if x.dtype not in (torch.float32, torch.bfloat16):
       x = x.float()
+    want_shape = tuple(self.compute_output_shape(x.shape))
+    mode, crop = None, None
+    if self.padding == "same_reflect":
+      x, mode, crop = self._reflect(x)
     x = x.contiguous()
-    _, pad_begin, out_len = self._plan()
+    _, pad_begin, out_len = self._plan(mode)
     n, h, w, cin = x.shape
     ho, wo = out_len(h, 0), out_len(w, 1)
-    assert (n, ho, wo, self.filters) == tuple(self.compute_output_shape(x.shape)), \
-        "internal: output geometry disagrees with compute_output_shape"
+    if crop is None:
+      assert (n, ho, wo, self.filters) == want_shape, \
+          "internal: output geometry disagrees with compute_output_shape"
     act, post = self._activation_code()
     out_dtype = out_dtype or self.out_dtype
     wgt, bias = self.effective_weights()
@@ -285,6 +331,9 @@ class SignalConv2D(object):
         _lib.ptr(gamma), _lib.ptr(out), _lib.ptr(rec[0]), ctypes.c_size_t(rec[0].numel()),
         stream))
     rec[1], rec[2] = self._eff, gdn_params
+    if crop is not None:
+      out = out[:, crop[0]:crop[0] + want_shape[1], crop[1]:crop[1] + want_shape[2], :].contiguous()
+      assert tuple(out.shape) == want_shape
     if post is not None:
       out = post(out)
     return out

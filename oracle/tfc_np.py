@@ -49,10 +49,15 @@ def signal_conv2d(x, kernel, bias=None, corr=False, strides_down=1, strides_up=1
     corr, k = True, torch.flip(k, (0, 1))
   elif corr and su != 1 and odd:
     corr, k = False, torch.flip(k, (0, 1))
+  prepad = [(0, 0), (0, 0)]
   if padding == "valid":
     pad = [(0, 0), (0, 0)]
   else:
     pad = same_padding_for_kernel((kh, kw), corr, (su, su))
+    if padding == "same_reflect":
+      # signal_conv.py:752-758: pre-pad with tf.pad(REFLECT), then the VALID ops
+      x = F.pad(x, (pad[1][0], pad[1][1], pad[0][0], pad[0][1]), mode="reflect")
+      prepad, pad = pad, [(0, 0), (0, 0)]
   if corr and su == 1:
     xp = F.pad(x, (pad[1][0], pad[1][1], pad[0][0], pad[0][1]))
     out = F.conv2d(xp, k.permute(3, 2, 0, 1), stride=sd)                  # cross-correlation
@@ -61,8 +66,9 @@ def signal_conv2d(x, kernel, bias=None, corr=False, strides_down=1, strides_up=1
     # gradient of a stride-su correlation == full transposed conv cropped by p at the start
     if padding == "valid":
       p = [(kh - 1, kh - 1), (kw - 1, kw - 1)]
-    else:
-      p = [(kh // 2, (kh - 1) // 2), (kw // 2, (kw - 1) // 2)]
+    else:       # signal_conv.py:657-663, pre-padding folded into the explicit padding
+      p = [(prepad[0][0] * su + kh // 2, prepad[0][1] * su + (kh - 1) // 2),
+           (prepad[1][0] * su + kw // 2, prepad[1][1] * su + (kw - 1) // 2)]
     n, _, h, w = x.shape
     def length(l, s, kk, ps):
       return l * s + ((kk - 1) - ps) if extra_pad_end else l * s + ((kk - 1) - (s - 1) - ps)

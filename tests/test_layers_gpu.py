@@ -32,6 +32,11 @@ CONV_CASES = [
     (True, (9, 9), 4, 1, "same_zeros", True), (False, (9, 9), 1, 4, "same_zeros", True),
     (True, (5, 5), 1, 2, "same_zeros", True), (False, (5, 5), 2, 2, "same_zeros", True),
     (False, (4, 4), 1, 2, "same_zeros", True), (False, (5, 5), 1, 2, "same_zeros", False),
+    # same_reflect (signal_conv.py:744-758; signal_conv_test.py sweeps it like same_zeros)
+    (True, (3, 3), 1, 1, "same_reflect", True), (False, (3, 3), 1, 1, "same_reflect", True),
+    (True, (5, 5), 2, 1, "same_reflect", True), (False, (5, 5), 1, 2, "same_reflect", True),
+    (True, (5, 5), 1, 2, "same_reflect", True), (False, (4, 4), 1, 2, "same_reflect", True),
+    (True, (2, 4), 2, 1, "same_reflect", True),
 ]
 
 
@@ -59,10 +64,30 @@ def test_signal_conv_not_implemented(tfc):
   x = torch.zeros((1, 8, 8, 2), device="cuda")
   with pytest.raises(NotImplementedError):
     tfc.SignalConv2D(2, (4, 4), corr=True, strides_up=2, padding="valid")(x)
-  with pytest.raises(NotImplementedError):
-    tfc.SignalConv2D(2, (3, 3), corr=True, padding="same_reflect")(x)
+  with pytest.raises(NotImplementedError):        # upsampling + downsampling over a reflection
+    tfc.SignalConv2D(2, (5, 5), corr=False, strides_up=2, strides_down=2,
+                     padding="same_reflect")(x)
   with pytest.raises(NotImplementedError):
     tfc.SignalConv2D(2, (3, 3), corr=True, channel_separable=True)(x)
+
+
+def test_signal_conv_channels_first(tfc):
+  """data_format="channels_first" (signal_conv.py:216-218, :790-800): same numbers as the
+  channels_last layer on the transposed tensors, bias and activation included."""
+  rng = np.random.default_rng(3)
+  x = rng.integers(0, 16, size=(2, 12, 10, 3)).astype(np.float32)
+  k = rng.integers(-4, 5, size=(5, 5, 3, 6)).astype(np.float32)
+  b = rng.integers(-8, 8, size=6).astype(np.float32)
+  outs = {}
+  for fmt in ("channels_last", "channels_first"):
+    layer = tfc.SignalConv2D(6, (5, 5), corr=True, strides_down=2, padding="same_zeros",
+                             data_format=fmt, use_bias=True, activation=torch.relu,
+                             kernel_parameterizer=None, kernel_initializer=_static(k),
+                             bias_initializer=_static(b))
+    xin = torch.from_numpy(x).cuda()
+    outs[fmt] = layer(xin if fmt == "channels_last" else xin.permute(0, 3, 1, 2).contiguous())
+  assert tuple(outs["channels_first"].shape) == (2, 6, 6, 5)
+  assert torch.equal(outs["channels_first"].permute(0, 2, 3, 1), outs["channels_last"])
 
 
 def test_rdft_parameterizer_roundtrip(tfc):
