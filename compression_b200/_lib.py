@@ -97,14 +97,17 @@ def to_device(x, dtype, device=None):
 
 
 CFG_SM_BUDGET, CFG_CODER_STREAMS_PER_CTA, CFG_TILES_PER_CTA, CFG_CONV_CLUSTER = 1, 2, 3, 4
+CFG_CODER_LANES = 5
 
 
-def configure(sm_budget=None, coder_streams_per_cta=None, tiles_per_cta=None, conv_cluster=None):
+def configure(sm_budget=None, coder_streams_per_cta=None, tiles_per_cta=None, conv_cluster=None,
+              coder_lanes=None):
   """Process-wide scheduling knobs of the library (tfc_configure): `sm_budget` = SMs the
   persistent transform kernels may occupy (0: all), `coder_streams_per_cta` = range-coder
   streams packed into one CTA (0: automatic), `tiles_per_cta` = chunked instead of persistent
   transform kernels, `conv_cluster` = thread-block cluster size of the implicit-GEMM kernel
-  (0: automatic).  No effect on results."""
+  (0: automatic), `coder_lanes` = one range-coder stream per lane (0: automatic, for thousands
+  of streams; 1: never; 2: always).  No effect on results."""
   L = lib()
   if sm_budget is not None:
     check(L.tfc_configure(CFG_SM_BUDGET, int(sm_budget)))
@@ -114,3 +117,5 @@ def configure(sm_budget=None, coder_streams_per_cta=None, tiles_per_cta=None, co
     check(L.tfc_configure(CFG_TILES_PER_CTA, int(tiles_per_cta)))
   if conv_cluster is not None:
     check(L.tfc_configure(CFG_CONV_CLUSTER, int(conv_cluster)))
+  if coder_lanes is not None:
+    check(L.tfc_configure(CFG_CODER_LANES, int(coder_lanes)))

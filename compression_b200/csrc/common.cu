@@ -8,6 +8,7 @@ std::string& last_error_ref() {
 std::atomic<int64_t> g_launches{0};
 std::atomic<int> g_sm_budget{0};
 std::atomic<int> g_coder_pack{0};
+std::atomic<int> g_coder_lanes{0};
 std::atomic<int> g_tiles_per_cta{0};
 std::atomic<int> g_debug{0};
 std::atomic<int> g_conv_cluster{0};
@@ -37,6 +38,11 @@ extern "C" int tfc_configure(int key, int value) {
       if (value != 0 && value != 1 && value != 2 && value != 4)
         return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "conv cluster size must be 0 (auto), 1, 2 or 4");
       tfc::g_conv_cluster.store(value);
+      return TFC_OK;
+    case TFC_CFG_CODER_LANES:
+      if (value < 0 || value > 2)
+        return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "coder lanes mode must be 0 (auto), 1 (off) or 2 (on)");
+      tfc::g_coder_lanes.store(value);
       return TFC_OK;
     case 99:   // kernel experiments (tools/conv_bench.py --debug): results are NOT valid when set
       tfc::g_debug.store(value);

@@ -16,6 +16,7 @@ std::string& last_error_ref();
 extern std::atomic<int64_t> g_launches;
 extern std::atomic<int> g_sm_budget;   // SMs the persistent transform kernels may occupy (0: all)
 extern std::atomic<int> g_tiles_per_cta;  // transform kernels: tiles per CTA (0: persistent grid)
+extern std::atomic<int> g_coder_lanes; // unbounded coder, one stream per lane: 0 auto, 1 off, 2 on
 extern std::atomic<int> g_coder_pack;  // range-coder streams per CTA (0: one CTA per stream when
                                        // the SMs allow it — lowest latency)
 

@@ -348,6 +348,7 @@ __global__ void __launch_bounds__(256) decode_bounded_kernel(const DecodeParams 
 }  // namespace
 #include "rc_unbounded.cuh"
 #include "rc_v4.cuh"
+#include "rc_lanes.cuh"
 namespace {
 
 // ---------------------------------------------------------------------------------------
@@ -502,6 +503,26 @@ int v4_table_budget(int32_t rows, int32_t cols) {
   return (int)((std::min<size_t>(dense, kV4TableBudget) + 15) & ~size_t(15));
 }
 
+// ---- one stream per lane (rc_lanes.cuh): thousands of streams ------------------------------
+bool lanes_wanted(int64_t S, int32_t rows) {
+  const int mode = tfc::g_coder_lanes.load(std::memory_order_relaxed);
+  if (!v4_usable(rows) || mode == 1) return false;
+  return mode == 2 || S >= 2048;
+}
+
+// warps per CTA: spread the ceil(S / 32) warps over the SMs, at most 16 per CTA (they share one
+// staged table); returns the dynamic shared memory of the launch
+size_t lanes_geometry(int64_t S, int table_bytes, int* wpc, int64_t* blocks) {
+  const int64_t warps = (S + 31) / 32;
+  const int sms = tfc::num_sms();
+  int w = (int)std::max<int64_t>(1, std::min<int64_t>(lanes::kMaxWarps, (warps + sms - 1) / sms));
+  const size_t smem_max = 227 * 1024 - 1024;
+  while (w > 1 && (size_t)table_bytes + w * lanes::kWarpBytes > smem_max) --w;
+  *wpc = w;
+  *blocks = (warps + w - 1) / w;
+  return (size_t)table_bytes + w * lanes::kWarpBytes;
+}
+
 int warps_per_block(int64_t S) {
   // few streams: one warp per block so the streams spread over the SMs; many: pack 8
   const int sms = tfc::num_sms();
@@ -606,6 +627,26 @@ extern "C" int tfc_unbounded_index_range_encode(
                               precision, st);
     if (rc) return rc;
   }
+  if (lanes_wanted(S, rows)) {
+    lanes::Params q{};
+    q.data = d_data; q.index = d_index; q.index_stride = index_stride; q.cdf = d_cdf;
+    q.cdf_size = d_cdf_size; q.offset = d_offset; q.rows = rows; q.cols = cols;
+    q.precision = precision; q.overflow_width = overflow_width; q.out = d_out; q.cap = cap;
+    q.nbytes = d_nbytes; q.status = d_status; q.S = S; q.n = n;
+    q.table_bytes = v4_table_budget(rows, cols);
+    int wpc = 1;
+    int64_t blocks = 0;
+    const size_t smem = lanes_geometry(S, q.table_bytes, &wpc, &blocks);
+    static bool attr = false;
+    if (!attr) {
+      TFC_CUDA(cudaFuncSetAttribute(lanes::encode_unbounded_lanes,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+      attr = true;
+    }
+    lanes::encode_unbounded_lanes<<<(unsigned)blocks, wpc * 32, smem, st>>>(q);
+    TFC_LAUNCHED("encode_unbounded_lanes");
+    return TFC_OK;
+  }
   if (v4_usable(rows)) {
     v4::EncParamsV4 q{};
     q.data = d_data; q.index = d_index; q.index_stride = index_stride; q.cdf = d_cdf;
@@ -687,6 +728,27 @@ extern "C" int tfc_unbounded_index_range_decode(
     rc = run_unbounded_checks(d_index, index_stride ? S * n : n, d_cdf, rows, cols, d_cdf_size,
                               precision, st);
     if (rc) return rc;
+  }
+  if (lanes_wanted(S, rows)) {
+    lanes::Params q{};
+    q.enc = d_enc; q.cap = cap; q.nbytes = const_cast<int32_t*>(d_nbytes); q.index = d_index;
+    q.index_stride = index_stride; q.cdf = d_cdf; q.cdf_size = d_cdf_size; q.offset = d_offset;
+    q.rows = rows; q.cols = cols; q.precision = precision; q.overflow_width = overflow_width;
+    q.values = d_out; q.status = d_status; q.S = S; q.n = n;
+    q.max_digits = (32 + overflow_width - 1) / overflow_width;
+    q.table_bytes = v4_table_budget(rows, cols);
+    int wpc = 1;
+    int64_t blocks = 0;
+    const size_t smem = lanes_geometry(S, q.table_bytes, &wpc, &blocks);
+    static bool attr = false;
+    if (!attr) {
+      TFC_CUDA(cudaFuncSetAttribute(lanes::decode_unbounded_lanes,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+      attr = true;
+    }
+    lanes::decode_unbounded_lanes<<<(unsigned)blocks, wpc * 32, smem, st>>>(q);
+    TFC_LAUNCHED("decode_unbounded_lanes");
+    return TFC_OK;
   }
   if (v4_usable(rows)) {
     v4::DecParamsV4 q{};

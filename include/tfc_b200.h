@@ -56,11 +56,15 @@ int64_t tfc_launch_count(void);
  *                                  SMs the coder leaves free
  *   TFC_CFG_CONV_CLUSTER           thread-block cluster size of the implicit-GEMM kernel (its CTAs
  *                                  share each weight tile by TMA multicast): 0 = automatic (currently
- *                                  off: no gain measured), 1 = off, 2, 4 (where the shape allows) */
+ *                                  off: no gain measured), 1 = off, 2, 4 (where the shape allows)
+ *   TFC_CFG_CODER_LANES            unbounded-index coder with one stream per LANE (many short
+ *                                  streams) instead of 2-3 warps per stream (few long ones):
+ *                                  0 = automatic (S >= 2048 streams), 1 = never, 2 = always */
 #define TFC_CFG_SM_BUDGET 1
 #define TFC_CFG_CODER_STREAMS_PER_CTA 2
 #define TFC_CFG_TILES_PER_CTA 3
 #define TFC_CFG_CONV_CLUSTER 4
+#define TFC_CFG_CODER_LANES 5
 int tfc_configure(int key, int value);
 
 /* ------------------------------------------------------------------------------------------

@@ -52,7 +52,16 @@ def _random_tables(rng, rows, max_len, precision):
   return cdf, size, offset
 
 
-def test_unbounded_random_sweep(tfc, oracle):
+@pytest.fixture(params=[0, 2], ids=["warps_per_stream", "lane_per_stream"])
+def coder_lanes(request, tfc):
+  """Both unbounded coder designs: 2-3 warps per stream (rc_v4.cuh) and one stream per lane
+  (rc_lanes.cuh, automatic from 2048 streams on, forced here)."""
+  tfc.configure(coder_lanes=request.param)
+  yield request.param
+  tfc.configure(coder_lanes=0)
+
+
+def test_unbounded_random_sweep(tfc, oracle, coder_lanes):
   """>=10^4 streams over precision 1..16, overflow_width 1..16, escapes of both signs, ragged
   cdf_size, empty and tiny streams."""
   from compression_b200.python.ops import range_coding_ops as rc
@@ -86,7 +95,27 @@ def test_unbounded_random_sweep(tfc, oracle):
   assert total_streams >= 5000
 
 
-def test_unbounded_long_rows_and_carry(tfc, oracle):
+def test_unbounded_many_streams_capacity_retry(tfc, oracle):
+  """2100 ragged streams (the automatic lane-per-stream path), output slab deliberately too
+  small: the kernel reports the size it needs per stream and the retry produces the
+  reference's bytes."""
+  from compression_b200.python.ops import range_coding_ops as rc
+  rng = np.random.default_rng(11)
+  cdf, size, offset = _random_tables(rng, 6, 40, 16)
+  S, n = 2100, 77
+  index = rng.integers(0, 6, size=(S, n)).astype(np.int32)
+  data = (rng.integers(-60, 61, size=(S, n)) + offset[index]).astype(np.int32)
+  out, nbytes = rc.unbounded_index_range_encode_batch(data, index, cdf, size, offset, 16, 4,
+                                                      debug_level=0, cap=32)
+  got = rc.strings_to_host(out, nbytes)
+  assert max(len(g) for g in got) > 32
+  for s in list(range(0, S, 50)) + [S - 1]:
+    assert got[s] == oracle.ui_encode(data[s], index[s], cdf, size, offset, 16, 4), s
+  dec = rc.unbounded_index_range_decode_batch(out, nbytes, index, cdf, size, offset, 16, 4, 0)
+  np.testing.assert_array_equal(dec.cpu().numpy(), data)
+
+
+def test_unbounded_long_rows_and_carry(tfc, oracle, coder_lanes):
   """Rows longer than the 32-wide search window (Gaussian-like, up to 1481 entries) and long
   runs of near-certain symbols that keep the encoder in its carry-pending state
   (range_coder.cc:169-210)."""

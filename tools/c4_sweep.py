@@ -46,12 +46,17 @@ def main():
   ap.add_argument("--check-streams", type=int, default=1024)
   ap.add_argument("--pmf-n", default="22,64,256,1480")
   ap.add_argument("--skip", default="", help="comma list of: unbounded,bounded,pmf")
+  ap.add_argument("--coder-lanes", type=int, default=0,
+                  help="0: automatic (lane per stream from 2048 streams on), 1: warps per stream "
+                       "always, 2: lane per stream always")
   args = ap.parse_args()
   skip = set(args.skip.split(","))
   from compression_b200.python.layers import entropy_models
   from compression_b200.python.ops import range_coding_ops as rc
   from oracle import oracle_lib
   coder = oracle_lib.load("best")
+  import compression_b200
+  compression_b200.configure(coder_lanes=args.coder_lanes)
   threads = len(os.sched_getaffinity(0))
   dev = torch.device("cuda", 0)
   table = np.exp(np.linspace(np.log(0.11), np.log(256), 64))
@@ -102,7 +107,7 @@ def main():
           out, nbytes, idx, cdf, size, off, 16, 4, 0, check=False), args.reps)
       out_bytes = float(nbytes.sum().item())
       print(json.dumps({
-          "op": "unbounded_index_range_encode/decode", "streams": S, "symbols_per_stream": n,
+          "op": "unbounded_index_range_encode/decode", "coder_lanes": args.coder_lanes, "streams": S, "symbols_per_stream": n,
           "bits_per_symbol": out_bytes * 8 / total, "escape_fraction": escapes,
           "bit_exact_streams_checked": int(len(pick)), "checker": coder.kind,
           "encode_ms": enc_ms, "decode_ms": dec_ms,
