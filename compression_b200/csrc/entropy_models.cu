@@ -189,6 +189,222 @@ abs_bf16_kernel(const float* __restrict__ x, int64_t count, __nv_bfloat16* __res
     out[i] = __float2bfloat16_rn(fabsf(x[i]));
 }
 
+
+// ---- 128-bit versions ------------------------------------------------------------------------
+// One float4 / int4 per thread and array, 2048 threads per SM: ~64 KB of loads in flight per SM,
+// what a B200 needs to cover HBM latency at full bandwidth.  Used whenever the buffers are 16-byte
+// aligned (the scalar kernels above take everything else and the count % 4 tail).
+inline int grid_vec(int64_t nvec) {
+  const int64_t blocks = (nvec + kThreads - 1) / kThreads;
+  return (int)std::max<int64_t>(1, std::min(blocks, (int64_t)tfc::num_sms() * 8));
+}
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+__device__ __forceinline__ float gaussian_lik(float v, float sg, float scale_bound, float bound) {
+  const float s = fmaxf(sg, scale_bound);
+  const float a = fabsf(v);
+  return fmaxf(std_normal_cdf((0.5f - a) / s) - std_normal_cdf((-0.5f - a) / s), bound);
+}
+
+__global__ void __launch_bounds__(kThreads)
+gaussian_call_vec_kernel(const float4* __restrict__ y, const float4* __restrict__ sigma,
+                         int64_t nvec, float scale_bound, float bound, int mode,
+                         float4* __restrict__ values, float4* __restrict__ lik) {
+  for (int64_t i = blockIdx.x * (int64_t)kThreads + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * kThreads) {
+    float4 v = __ldg(y + i);
+    const float4 s = __ldg(sigma + i);
+    if (mode == 0) {
+      v.x = floorf(v.x + 0.5f); v.y = floorf(v.y + 0.5f);
+      v.z = floorf(v.z + 0.5f); v.w = floorf(v.w + 0.5f);
+    }
+    if (values) values[i] = v;
+    float4 l;
+    l.x = gaussian_lik(v.x, s.x, scale_bound, bound);
+    l.y = gaussian_lik(v.y, s.y, scale_bound, bound);
+    l.z = gaussian_lik(v.z, s.z, scale_bound, bound);
+    l.w = gaussian_lik(v.w, s.w, scale_bound, bound);
+    lik[i] = l;
+  }
+}
+
+__device__ __forceinline__ int table_index(const float* s_table, int levels, float s) {
+  int lo = 0, hi = levels - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (s_table[mid] < s) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+__global__ void __launch_bounds__(kThreads)
+gaussian_symbols_indexes_vec_kernel(const float4* __restrict__ y, const float4* __restrict__ sigma,
+                                    int64_t nvec, const float* __restrict__ table, int levels,
+                                    float scale_bound, int4* __restrict__ sym,
+                                    int4* __restrict__ idx) {
+  __shared__ float s_table[kMaxLevels];
+  for (int k = threadIdx.x; k < levels; k += kThreads) s_table[k] = table[k];
+  __syncthreads();
+  for (int64_t i = blockIdx.x * (int64_t)kThreads + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * kThreads) {
+    if (sym) {
+      const float4 v = __ldg(y + i);
+      sym[i] = make_int4((int32_t)floorf(v.x + 0.5f), (int32_t)floorf(v.y + 0.5f),
+                         (int32_t)floorf(v.z + 0.5f), (int32_t)floorf(v.w + 0.5f));
+    }
+    if (idx) {
+      const float4 s = __ldg(sigma + i);
+      idx[i] = make_int4(table_index(s_table, levels, fmaxf(s.x, scale_bound)),
+                         table_index(s_table, levels, fmaxf(s.y, scale_bound)),
+                         table_index(s_table, levels, fmaxf(s.z, scale_bound)),
+                         table_index(s_table, levels, fmaxf(s.w, scale_bound)));
+    }
+  }
+}
+
+// channels % 4 == 0: the four elements of a vector are four consecutive channels
+__global__ void __launch_bounds__(kThreads)
+eb_symbols_vec_kernel(const float4* __restrict__ x, int64_t nvec, int channels,
+                      const float4* __restrict__ medians, int4* __restrict__ sym) {
+  const int cvec = channels >> 2;
+  for (int64_t i = blockIdx.x * (int64_t)kThreads + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * kThreads) {
+    const float4 m = __ldg(medians + (int)(i % cvec));
+    const float4 v = __ldg(x + i);
+    sym[i] = make_int4((int32_t)floorf(v.x + (0.5f - m.x)), (int32_t)floorf(v.y + (0.5f - m.y)),
+                       (int32_t)floorf(v.z + (0.5f - m.z)), (int32_t)floorf(v.w + (0.5f - m.w)));
+  }
+}
+
+template <typename OutT>
+__global__ void __launch_bounds__(kThreads)
+dequantize_vec_kernel(const int4* __restrict__ sym, int64_t nvec, int channels,
+                      const float4* __restrict__ medians, OutT* __restrict__ out) {
+  const int cvec = channels >> 2;
+  for (int64_t i = blockIdx.x * (int64_t)kThreads + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * kThreads) {
+    const int4 q = __ldg(sym + i);
+    float4 v = make_float4((float)q.x, (float)q.y, (float)q.z, (float)q.w);
+    if (medians) {
+      const float4 m = __ldg(medians + (int)(i % cvec));
+      v.x += m.x; v.y += m.y; v.z += m.z; v.w += m.w;
+    }
+    if (sizeof(OutT) == 4) {
+      reinterpret_cast<float4*>(out)[i] = v;
+    } else {
+      __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+      uint2 w;
+      w.x = *reinterpret_cast<uint32_t*>(&a);
+      w.y = *reinterpret_cast<uint32_t*>(&b);
+      reinterpret_cast<uint2*>(out)[i] = w;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+abs_bf16_vec_kernel(const float4* __restrict__ x, int64_t nvec, uint2* __restrict__ out) {
+  for (int64_t i = blockIdx.x * (int64_t)kThreads + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * kThreads) {
+    const float4 v = __ldg(x + i);
+    __nv_bfloat162 a = __floats2bfloat162_rn(fabsf(v.x), fabsf(v.y));
+    __nv_bfloat162 b = __floats2bfloat162_rn(fabsf(v.z), fabsf(v.w));
+    uint2 w;
+    w.x = *reinterpret_cast<uint32_t*>(&a);
+    w.y = *reinterpret_cast<uint32_t*>(&b);
+    out[i] = w;
+  }
+}
+
+// EntropyBottleneck.__call__, four channels per thread.  The packed per-channel parameters are
+// staged TRANSPOSED in shared memory ([parameter][channel]) so a warp's float4 reads of one
+// parameter are contiguous (in global memory consecutive channels are `stride` floats apart:
+// every lane would touch its own sector, ~230 of them per vector).  tanh and the sigmoid use
+// ex2.approx / rcp.approx (absolute error ~1e-7; the bar on likelihoods is 1e-3): the
+// likelihood needs 18 tanh + 2 sigmoid per element and is otherwise bound by the SFU pipe far
+// below HBM speed.
+__device__ __forceinline__ float fast_tanh(float t) {
+  return 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * t));
+}
+__device__ __forceinline__ float fast_sigmoid(float t) {
+  return __fdividef(1.0f, 1.0f + __expf(-t));
+}
+__device__ __forceinline__ float4 f4(float a) { return make_float4(a, a, a, a); }
+__device__ __forceinline__ float4 f4_fma(float4 a, float4 b, float4 c) {
+  return make_float4(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y), fmaf(a.z, b.z, c.z),
+                     fmaf(a.w, b.w, c.w));
+}
+__device__ __forceinline__ float4 f4_gate(float4 t, float4 a) {   // t + a * tanh(t)
+  return make_float4(fmaf(a.x, fast_tanh(t.x), t.x), fmaf(a.y, fast_tanh(t.y), t.y),
+                     fmaf(a.z, fast_tanh(t.z), t.z), fmaf(a.w, fast_tanh(t.w), t.w));
+}
+
+template <int L, int F>
+__device__ __forceinline__ float4 eb_logits4(const float* __restrict__ sp, int channels, int c0,
+                                             float4 v) {
+  auto P = [&](int j) { return *reinterpret_cast<const float4*>(sp + (size_t)j * channels + c0); };
+  if (L == 0) return f4_fma(P(0), v, P(1));
+  float4 h[F];
+#pragma unroll
+  for (int j = 0; j < F; ++j) h[j] = f4_gate(f4_fma(P(j), v, P(F + j)), P(2 * F + j));
+  int base = 3 * F;
+#pragma unroll
+  for (int l = 1; l < L; ++l) {
+    float4 g[F];
+#pragma unroll
+    for (int j = 0; j < F; ++j) {
+      float4 t = P(base + F * F + j);
+#pragma unroll
+      for (int k = 0; k < F; ++k) t = f4_fma(P(base + j * F + k), h[k], t);
+      g[j] = f4_gate(t, P(base + F * F + F + j));
+    }
+#pragma unroll
+    for (int j = 0; j < F; ++j) h[j] = g[j];
+    base += F * F + 2 * F;
+  }
+  float4 out = P(base + F);
+#pragma unroll
+  for (int k = 0; k < F; ++k) out = f4_fma(P(base + k), h[k], out);
+  return out;
+}
+
+__device__ __forceinline__ float eb_lik_from_logits(float lower, float upper, float bound) {
+  const float t = lower + upper;
+  const float sgn = t > 0.f ? -1.f : (t < 0.f ? 1.f : 0.f);
+  return fmaxf(fabsf(fast_sigmoid(sgn * upper) - fast_sigmoid(sgn * lower)), bound);
+}
+
+template <int L, int F>
+__global__ void __launch_bounds__(kThreads)
+eb_call_vec_kernel(const float4* __restrict__ x, int64_t nvec, int channels,
+                   const float* __restrict__ params, const float4* __restrict__ medians,
+                   float bound, int mode, float4* __restrict__ values, float4* __restrict__ lik) {
+  extern __shared__ __align__(16) float sp[];
+  constexpr int stride = eb_param_stride(L, F);
+  for (int e = threadIdx.x; e < channels * stride; e += kThreads) {
+    const int c = e / stride, j = e - c * stride;
+    sp[(size_t)j * channels + c] = params[e];
+  }
+  __syncthreads();
+  const int cvec = channels >> 2;
+  for (int64_t i = blockIdx.x * (int64_t)kThreads + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * kThreads) {
+    const int cv = (int)(i % cvec);
+    float4 v = __ldg(x + i);
+    if (mode == 0) {
+      const float4 m = __ldg(medians + cv);
+      v.x = floorf(v.x + (0.5f - m.x)) + m.x; v.y = floorf(v.y + (0.5f - m.y)) + m.y;
+      v.z = floorf(v.z + (0.5f - m.z)) + m.z; v.w = floorf(v.w + (0.5f - m.w)) + m.w;
+    }
+    if (values) values[i] = v;
+    const float4 lo = eb_logits4<L, F>(sp, channels, 4 * cv,
+                                       make_float4(v.x - .5f, v.y - .5f, v.z - .5f, v.w - .5f));
+    const float4 up = eb_logits4<L, F>(sp, channels, 4 * cv,
+                                       make_float4(v.x + .5f, v.y + .5f, v.z + .5f, v.w + .5f));
+    lik[i] = make_float4(eb_lik_from_logits(lo.x, up.x, bound), eb_lik_from_logits(lo.y, up.y, bound),
+                         eb_lik_from_logits(lo.z, up.z, bound), eb_lik_from_logits(lo.w, up.w, bound));
+  }
+}
+
 #define EB_DISPATCH(L_, F_, CALL)                                              \
   if (num_filters == L_ && (L_ == 0 || filter_width == F_)) { CALL(L_, F_); } else
 
@@ -210,10 +426,26 @@ extern "C" int tfc_eb_call(const float* d_x, int64_t count, int32_t channels,
                      (long long)count, channels);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int grid = grid_for(count);
+  const size_t sp_bytes = (size_t)channels * eb_param_stride(num_filters, filter_width) * 4;
+  const bool vec = (channels & 3) == 0 && aligned16(d_x) && aligned16(d_lik) &&
+                   aligned16(d_values) && aligned16(d_medians) && sp_bytes <= 160 * 1024;
+  const int64_t nvec = count / 4;
+  const int vgrid = (int)std::max<int64_t>(1, std::min<int64_t>((nvec + kThreads - 1) / kThreads,
+                                                                (int64_t)tfc::num_sms() * 4));
 #define CALL(L_, F_)                                                                        \
-  eb_call_kernel<L_, F_><<<grid, kThreads, 0, st>>>(d_x, count, channels, d_params,         \
-                                                    d_medians, likelihood_bound, mode,      \
-                                                    d_values, d_lik)
+  if (vec) {                                                                                \
+    if (sp_bytes > 48 * 1024)                                                               \
+      TFC_CUDA(cudaFuncSetAttribute(eb_call_vec_kernel<L_, F_>,                             \
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize,            \
+                                    (int)sp_bytes));                                        \
+    eb_call_vec_kernel<L_, F_><<<vgrid, kThreads, sp_bytes, st>>>(                          \
+        reinterpret_cast<const float4*>(d_x), nvec, channels, d_params,                     \
+        reinterpret_cast<const float4*>(d_medians), likelihood_bound, mode,                 \
+        reinterpret_cast<float4*>(d_values), reinterpret_cast<float4*>(d_lik));             \
+  } else                                                                                    \
+    eb_call_kernel<L_, F_><<<grid, kThreads, 0, st>>>(d_x, count, channels, d_params,       \
+                                                      d_medians, likelihood_bound, mode,    \
+                                                      d_values, d_lik)
   EB_DISPATCH(3, 3, CALL) EB_DISPATCH(0, 1, CALL) EB_DISPATCH(1, 3, CALL) EB_DISPATCH(2, 3, CALL)
   EB_DISPATCH(4, 3, CALL) EB_DISPATCH(1, 1, CALL) EB_DISPATCH(2, 1, CALL) EB_DISPATCH(3, 1, CALL)
   EB_DISPATCH(1, 2, CALL) EB_DISPATCH(2, 2, CALL) EB_DISPATCH(3, 2, CALL) EB_DISPATCH(1, 4, CALL)
@@ -246,8 +478,14 @@ extern "C" int tfc_eb_logits_cumulative(const float* d_x, int32_t channels, int3
 extern "C" int tfc_eb_symbols(const float* d_x, int64_t count, int32_t channels,
                               const float* d_medians, int32_t* d_symbols, void* stream) {
   if (count <= 0) return TFC_OK;
-  eb_symbols_kernel<<<grid_for(count), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      d_x, count, channels, d_medians, d_symbols);
+  if (channels > 0 && (channels & 3) == 0 && count % channels == 0 && aligned16(d_x) &&
+      aligned16(d_symbols) && aligned16(d_medians))
+    eb_symbols_vec_kernel<<<grid_vec(count / 4), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const float4*>(d_x), count / 4, channels,
+        reinterpret_cast<const float4*>(d_medians), reinterpret_cast<int4*>(d_symbols));
+  else
+    eb_symbols_kernel<<<grid_for(count), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        d_x, count, channels, d_medians, d_symbols);
   TFC_LAUNCHED("eb_symbols_kernel");
   return TFC_OK;
 }
@@ -257,6 +495,22 @@ extern "C" int tfc_eb_dequantize(const int32_t* d_symbols, int64_t count, int32_
                                  void* stream) {
   if (count <= 0) return TFC_OK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool chan_ok = d_medians == nullptr ||
+                       (channels > 0 && (channels & 3) == 0 && count % channels == 0 &&
+                        aligned16(d_medians));
+  if (chan_ok && (count & 3) == 0 && aligned16(d_symbols) && aligned16(d_out)) {
+    const float4* med = reinterpret_cast<const float4*>(d_medians);
+    const int4* q = reinterpret_cast<const int4*>(d_symbols);
+    const int ch = d_medians ? channels : 4;
+    if (out_bf16)
+      dequantize_vec_kernel<__nv_bfloat16><<<grid_vec(count / 4), kThreads, 0, st>>>(
+          q, count / 4, ch, med, static_cast<__nv_bfloat16*>(d_out));
+    else
+      dequantize_vec_kernel<float><<<grid_vec(count / 4), kThreads, 0, st>>>(
+          q, count / 4, ch, med, static_cast<float*>(d_out));
+    TFC_LAUNCHED("dequantize_kernel");
+    return TFC_OK;
+  }
   if (out_bf16)
     dequantize_kernel<__nv_bfloat16><<<grid_for(count), kThreads, 0, st>>>(
         d_symbols, count, channels, d_medians, static_cast<__nv_bfloat16*>(d_out));
@@ -276,8 +530,19 @@ extern "C" int tfc_gaussian_call(const float* d_y, const float* d_sigma, int64_t
                                  float scale_bound, float likelihood_bound, int mode,
                                  float* d_values, float* d_lik, void* stream) {
   if (count <= 0) return TFC_OK;
-  gaussian_call_kernel<<<grid_for(count), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      d_y, d_sigma, count, scale_bound, likelihood_bound, mode, d_values, d_lik);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int64_t done = 0;
+  if (count >= 4 && aligned16(d_y) && aligned16(d_sigma) && aligned16(d_values) && aligned16(d_lik)) {
+    done = count & ~(int64_t)3;
+    gaussian_call_vec_kernel<<<grid_vec(done / 4), kThreads, 0, st>>>(
+        reinterpret_cast<const float4*>(d_y), reinterpret_cast<const float4*>(d_sigma), done / 4,
+        scale_bound, likelihood_bound, mode, reinterpret_cast<float4*>(d_values),
+        reinterpret_cast<float4*>(d_lik));
+  }
+  if (done < count)
+    gaussian_call_kernel<<<grid_for(count - done), kThreads, 0, st>>>(
+        d_y + done, d_sigma + done, count - done, scale_bound, likelihood_bound, mode,
+        d_values ? d_values + done : nullptr, d_lik + done);
   TFC_LAUNCHED("gaussian_call_kernel");
   return TFC_OK;
 }
@@ -290,15 +555,33 @@ extern "C" int tfc_gaussian_symbols_indexes(const float* d_y, const float* d_sig
   if (levels < 1 || levels > kMaxLevels)
     return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "scale table must have 1..%d levels, got %d",
                      kMaxLevels, levels);
-  gaussian_symbols_indexes_kernel<<<grid_for(count), kThreads, 0,
-                                    static_cast<cudaStream_t>(stream)>>>(
-      d_y, d_sigma, count, d_table, levels, scale_bound, d_symbols, d_indexes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int64_t done = 0;
+  if (count >= 4 && aligned16(d_y) && aligned16(d_sigma) && aligned16(d_symbols) &&
+      aligned16(d_indexes)) {
+    done = count & ~(int64_t)3;
+    gaussian_symbols_indexes_vec_kernel<<<grid_vec(done / 4), kThreads, 0, st>>>(
+        reinterpret_cast<const float4*>(d_y), reinterpret_cast<const float4*>(d_sigma), done / 4,
+        d_table, levels, scale_bound, reinterpret_cast<int4*>(d_symbols),
+        reinterpret_cast<int4*>(d_indexes));
+  }
+  if (done < count)
+    gaussian_symbols_indexes_kernel<<<grid_for(count - done), kThreads, 0, st>>>(
+        d_y ? d_y + done : nullptr, d_sigma ? d_sigma + done : nullptr, count - done, d_table,
+        levels, scale_bound, d_symbols ? d_symbols + done : nullptr,
+        d_indexes ? d_indexes + done : nullptr);
   TFC_LAUNCHED("gaussian_symbols_indexes_kernel");
   return TFC_OK;
 }
 
 extern "C" int tfc_abs_to_bf16(const float* d_x, int64_t count, void* d_out_bf16, void* stream) {
   if (count <= 0) return TFC_OK;
+  if ((count & 3) == 0 && aligned16(d_x) && (reinterpret_cast<uintptr_t>(d_out_bf16) & 7) == 0) {
+    abs_bf16_vec_kernel<<<grid_vec(count / 4), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const float4*>(d_x), count / 4, static_cast<uint2*>(d_out_bf16));
+    TFC_LAUNCHED("abs_bf16_kernel");
+    return TFC_OK;
+  }
   abs_bf16_kernel<<<grid_for(count), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       d_x, count, static_cast<__nv_bfloat16*>(d_out_bf16));
   TFC_LAUNCHED("abs_bf16_kernel");
