@@ -32,6 +32,12 @@ constexpr int kThreads = 128;
 struct WgradParams {
   int32_t n, h, w, cin, ho, wo, cout, kh, kw, sd, su, pt, pl;
   int32_t ctiles, otiles, kslices;
+  // thin layers (3 image channels): the kw taps of one kernel row are contiguous in memory on
+  // the thin side ((column, channel) of NHWC), so one "tap" is a whole kernel row and the thin
+  // dimension becomes kw * channels wide (27 of a 64-wide tile instead of 3).
+  //   fuse 1: su == 1, thin cin:  x element e = b * cin + c of row a
+  //   fuse 2: su  > 1, thin cout: dy element e = (kw - 1 - b) * cout + o of row a
+  int32_t fuse;
   int64_t pixels;                        // enumerated pixels: outputs (su == 1) or inputs (su > 1)
   const __nv_bfloat16* x;
   const __nv_bfloat16* dy;
@@ -43,12 +49,15 @@ conv_wgrad_kernel(const WgradParams p) {
   __shared__ __align__(32) __nv_bfloat16 xs[kBK * kLd];
   __shared__ __align__(32) __nv_bfloat16 ys[kBK * kLd];
   __shared__ int64_t x_off[kBK], y_off[kBK];
+  __shared__ int32_t e_lo[kBK], e_hi[kBK];   // fused side: valid element range of the row
   __shared__ __align__(32) float acc_s[kBM * kBN];
 
   const int tile = blockIdx.x;
   const int ct = tile / p.otiles, ot = tile - ct * p.otiles;
   const int tap = blockIdx.y;
-  const int a = tap / p.kw, b = tap - a * p.kw;
+  const int a = p.fuse ? tap : tap / p.kw, b = p.fuse ? 0 : tap - a * p.kw;
+  const int cin_t = p.fuse == 1 ? p.kw * p.cin : p.cin;      // tile extents of the two sides
+  const int cout_t = p.fuse == 2 ? p.kw * p.cout : p.cout;
   const int c0 = ct * kBM, o0 = ot * kBN;
   const int warp = threadIdx.x >> 5;
   const int wm = (warp >> 1) * 32, wn = (warp & 1) * 32;
@@ -62,14 +71,37 @@ conv_wgrad_kernel(const WgradParams p) {
   const int64_t per = (p.pixels + p.kslices - 1) / p.kslices;
   const int64_t p_begin = (int64_t)blockIdx.z * per;
   const int64_t p_end = min(p.pixels, p_begin + per);
-  const bool vec_x = (p.cin & 7) == 0, vec_y = (p.cout & 7) == 0;
+  const bool vec_x = (p.cin & 7) == 0 && p.fuse != 1, vec_y = (p.cout & 7) == 0 && p.fuse != 2;
   const int gw = p.su > 1 ? p.w : p.wo, gh = p.su > 1 ? p.h : p.ho;   // enumeration grid
 
   for (int64_t base = p_begin; base < p_end; base += kBK) {
     if (threadIdx.x < kBK) {
       const int64_t q = base + threadIdx.x;
       int64_t xo = -1, yo = -1;
-      if (q < p_end) {
+      int lo = 0, hi = 0x7FFFFFFF;
+      if (q < p_end && p.fuse == 1) {        // whole kernel row a of output pixel (i, j)
+        const int j = (int)(q % gw);
+        const int i = (int)((q / gw) % gh);
+        const int nn = (int)(q / ((int64_t)gw * gh));
+        const int yi = i * p.sd + a - p.pt, xj0 = j * p.sd - p.pl;
+        if (yi >= 0 && yi < p.h) {
+          xo = (((int64_t)nn * p.h + yi) * p.w + xj0) * p.cin + ((int64_t)1 << 40);  // may be < 0
+          yo = (((int64_t)nn * p.ho + i) * p.wo + j) * p.cout;
+          lo = max(0, -xj0) * p.cin;
+          hi = min(p.kw, p.w - xj0) * p.cin;
+        }
+      } else if (q < p_end && p.fuse == 2) { // input pixel (i, j) against kernel row a of dy
+        const int j = (int)(q % gw);
+        const int i = (int)((q / gw) % gh);
+        const int nn = (int)(q / ((int64_t)gw * gh));
+        const int oi = p.su * i - a + p.pt, oj0 = p.su * j + p.pl - (p.kw - 1);
+        if (oi >= 0 && oi < p.ho) {
+          xo = (((int64_t)nn * p.h + i) * p.w + j) * p.cin;
+          yo = (((int64_t)nn * p.ho + oi) * p.wo + oj0) * p.cout + ((int64_t)1 << 40);
+          lo = max(0, -oj0) * p.cout;
+          hi = min(p.kw, p.wo - oj0) * p.cout;
+        }
+      } else if (q < p_end) {
         const int j = (int)(q % gw);
         const int i = (int)((q / gw) % gh);
         const int nn = (int)(q / ((int64_t)gw * gh));
@@ -89,30 +121,41 @@ conv_wgrad_kernel(const WgradParams p) {
       }
       x_off[threadIdx.x] = xo;
       y_off[threadIdx.x] = yo;
+      e_lo[threadIdx.x] = lo;
+      e_hi[threadIdx.x] = hi;
     }
     __syncthreads();
     // tiles: 32 pixel rows x 64 channels, zero where the tap is outside / channels run out
     for (int e = threadIdx.x; e < kBK * 8; e += kThreads) {
       const int r = e >> 3, ch = (e & 7) * 8;
       uint4 vx = make_uint4(0, 0, 0, 0), vy = make_uint4(0, 0, 0, 0);
-      const int64_t xo = x_off[r], yo = y_off[r];
+      int64_t xo = x_off[r], yo = y_off[r];
       if (xo >= 0) {
+        const int lo = e_lo[r], hi = e_hi[r];
+        if (p.fuse == 1) xo -= (int64_t)1 << 40;
+        if (p.fuse == 2) yo -= (int64_t)1 << 40;
         if (vec_x) {
           if (c0 + ch < p.cin) vx = *reinterpret_cast<const uint4*>(p.x + xo + c0 + ch);
         } else {
+          const int xl = p.fuse == 1 ? lo : 0, xh = p.fuse == 1 ? hi : p.cin;
           __nv_bfloat16 t[8];
 #pragma unroll
-          for (int k = 0; k < 8; ++k)
-            t[k] = (c0 + ch + k < p.cin) ? p.x[xo + c0 + ch + k] : __float2bfloat16(0.f);
+          for (int k = 0; k < 8; ++k) {
+            const int e = c0 + ch + k;
+            t[k] = (e >= xl && e < xh) ? p.x[xo + e] : __float2bfloat16(0.f);
+          }
           vx = *reinterpret_cast<const uint4*>(t);
         }
         if (vec_y) {
           if (o0 + ch < p.cout) vy = *reinterpret_cast<const uint4*>(p.dy + yo + o0 + ch);
         } else {
+          const int yl = p.fuse == 2 ? lo : 0, yh = p.fuse == 2 ? hi : p.cout;
           __nv_bfloat16 t[8];
 #pragma unroll
-          for (int k = 0; k < 8; ++k)
-            t[k] = (o0 + ch + k < p.cout) ? p.dy[yo + o0 + ch + k] : __float2bfloat16(0.f);
+          for (int k = 0; k < 8; ++k) {
+            const int e = o0 + ch + k;
+            t[k] = (e >= yl && e < yh) ? p.dy[yo + e] : __float2bfloat16(0.f);
+          }
           vy = *reinterpret_cast<const uint4*>(t);
         }
       }
@@ -142,13 +185,19 @@ conv_wgrad_kernel(const WgradParams p) {
       wmma::store_matrix_sync(acc_s + (wm + 16 * i) * kBN + wn + 16 * j, acc[i][j], kBN,
                               wmma::mem_row_major);
   __syncthreads();
-  float* dst = p.dw + (int64_t)tap * p.cin * p.cout;
+  float* dst = p.dw + (int64_t)tap * (p.fuse ? p.kw : 1) * p.cin * p.cout;   // row a / tap (a, b)
   for (int e = threadIdx.x; e < kBM * kBN; e += kThreads) {
     const int c = c0 + e / kBN, o = o0 + e % kBN;
-    if (c < p.cin && o < p.cout) {
+    if (c < cin_t && o < cout_t) {
       const float v = acc_s[e];
-      if (p.kslices == 1) dst[(int64_t)c * p.cout + o] = v;
-      else atomicAdd(dst + (int64_t)c * p.cout + o, v);
+      // fuse 1: c = b * cin + c' is already the offset inside row a;  fuse 2: o = (kw-1-b)*cout + o'
+      int64_t at = (int64_t)c * p.cout + o;
+      if (p.fuse == 2) {
+        const int bb = p.kw - 1 - o / p.cout, oo = o - (o / p.cout) * p.cout;
+        at = ((int64_t)bb * p.cin + c) * p.cout + oo;
+      }
+      if (p.kslices == 1) dst[at] = v;
+      else atomicAdd(dst + at, v);
     }
   }
 }
@@ -188,10 +237,14 @@ extern "C" int tfc_signal_conv2d_wgrad(const tfc_conv_desc* d, const void* d_x_b
   p.n = d->n; p.h = d->h; p.w = d->w; p.cin = d->cin; p.ho = d->ho; p.wo = d->wo;
   p.cout = d->cout; p.kh = d->kh; p.kw = d->kw; p.sd = d->sd; p.su = d->su;
   p.pt = d->pad_top; p.pl = d->pad_left;
-  p.ctiles = (d->cin + kBM - 1) / kBM;
-  p.otiles = (d->cout + kBN - 1) / kBN;
+  p.fuse = 0;
+  if (d->su == 1 && d->cin < 16 && d->kw * d->cin <= kBM) p.fuse = 1;
+  if (d->su > 1 && d->cout < 16 && d->kw * d->cout <= kBN) p.fuse = 2;
+  p.ctiles = ((p.fuse == 1 ? d->kw * d->cin : d->cin) + kBM - 1) / kBM;
+  p.otiles = ((p.fuse == 2 ? d->kw * d->cout : d->cout) + kBN - 1) / kBN;
   p.pixels = d->su > 1 ? (int64_t)d->n * d->h * d->w : (int64_t)d->n * d->ho * d->wo;
-  const int64_t ctas = (int64_t)taps * p.ctiles * p.otiles;
+  const int grid_taps = p.fuse ? d->kh : taps;
+  const int64_t ctas = (int64_t)grid_taps * p.ctiles * p.otiles;
   const int64_t want = 4 * (int64_t)tfc::num_sms();
   int64_t ks = std::max<int64_t>(1, (want + ctas - 1) / ctas);
   ks = std::min<int64_t>(ks, std::max<int64_t>(1, p.pixels / 1024));
@@ -199,7 +252,7 @@ extern "C" int tfc_signal_conv2d_wgrad(const tfc_conv_desc* d, const void* d_x_b
   p.x = static_cast<const __nv_bfloat16*>(d_x_bf16);
   p.dy = static_cast<const __nv_bfloat16*>(d_dy_bf16);
   p.dw = d_dw;
-  dim3 grid(p.ctiles * p.otiles, taps, p.kslices);
+  dim3 grid(p.ctiles * p.otiles, grid_taps, p.kslices);
   conv_wgrad_kernel<<<grid, kThreads, 0, st>>>(p);
   TFC_LAUNCHED("conv_wgrad_kernel");
   return TFC_OK;

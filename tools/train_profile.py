@@ -40,11 +40,18 @@ def main():
       trainer.step(x)
     torch.cuda.synchronize()
   agg = collections.defaultdict(lambda: [0, 0.0])
+  wgrad = []
   for ev in prof.events():
     if ev.device_type == torch.autograd.DeviceType.CUDA:
       a = agg[ev.name[:90]]
       a[0] += 1
       a[1] += ev.device_time
+      if "wgrad" in ev.name:
+        wgrad.append(ev.device_time / 1e3)
+  if wgrad:
+    per = len(wgrad) // args.steps
+    print("filter-gradient launches of the last step, in backward order (ms): " +
+          " ".join("%.3f" % t for t in wgrad[-per:]))
   total = sum(v[1] for v in agg.values())
   print("device time per step: %.3f ms over %d kernel launches" % (
       total / args.steps / 1e3, sum(v[0] for v in agg.values()) // args.steps))
