@@ -151,6 +151,37 @@ class Bls2017Model(object):
     return self.analysis_transform.layers + self.synthesis_transform.layers
 
 
+class _tf32_matmul(object):
+  """Scoped `torch.backends.cuda.matmul.allow_tf32`."""
+
+  def __enter__(self):
+    self._old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+
+  def __exit__(self, *exc):
+    torch.backends.cuda.matmul.allow_tf32 = self._old
+    return False
+
+
+class _GdnContraction(torch.autograd.Function):
+  """[P, C] x [C, C] contraction of GDN (gdn.py:183-185) and its two gradients as TF32
+  tensor-core GEMMs (fp32 accumulate).  The transforms around it run on bf16 operands, so TF32
+  here keeps the step's precision policy; everything else in the step (the density network in
+  particular) stays in fp32 SIMT arithmetic."""
+
+  @staticmethod
+  def forward(ctx, x2, gamma):
+    ctx.save_for_backward(x2, gamma)
+    with _tf32_matmul():
+      return x2 @ gamma
+
+  @staticmethod
+  def backward(ctx, g):
+    x2, gamma = ctx.saved_tensors
+    with _tf32_matmul():
+      return g @ gamma.t(), x2.t() @ g
+
+
 class Bls2017Trainer(object):
   """One synchronous data-parallel training step (bls2017.py:156-185).
 
@@ -210,7 +241,7 @@ class Bls2017Trainer(object):
   def _gdn(act, x):
     """gdn.py:171-202 in torch ops: the 1x1 contraction is a plain GEMM."""
     beta, gamma = act.beta_parameterizer(act.reparam_beta), act.gamma_parameterizer(act.reparam_gamma)
-    norm = (x * x).reshape(-1, x.shape[-1]) @ gamma + beta
+    norm = _GdnContraction.apply((x * x).reshape(-1, x.shape[-1]), gamma) + beta
     norm = norm.reshape(x.shape)
     return x * (torch.sqrt(norm) if act.inverse else torch.rsqrt(norm))
 
