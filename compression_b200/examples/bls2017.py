@@ -281,13 +281,47 @@ class Bls2017Trainer(object):
     return dict(loss=self.lmbda * mse + bpp, bpp=bpp, mse=mse,
                 aux=model.entropy_bottleneck.losses[0], x_tilde=x_tilde)
 
-  def step(self, x, noise=None):
-    """train_op = group(main_step, aux_step, updates[0]) (bls2017.py:173-180)."""
+  def _forward_backward(self, x, noise):
     self.main.zero_grad()
     self.aux.zero_grad()
     out = self.losses(x, noise)
     out["loss"].backward()
     out["aux"].backward()
+    return out
+
+  def _replay(self, x, noise):
+    """Forward + backward of one step as ONE CUDA graph launch (captured on first use per input
+    shape): the step is ~600 small launches and host-bound when they are issued one by one.
+    The gradient all-reduce, the Adam updates and the table rebuild stay outside the graph."""
+    graphs = self.__dict__.setdefault("_graphs", {})
+    key = (tuple(x.shape), x.dtype, noise is not None)
+    rec = graphs.get(key)
+    if rec is None:
+      sx = x.clone()
+      sn = noise.clone() if noise is not None else None
+      side = torch.cuda.Stream(device=x.device)
+      side.wait_stream(torch.cuda.current_stream(x.device))
+      with torch.cuda.stream(side):       # warm-up: allocator pools, lazily set attributes
+        for _ in range(2):
+          self._forward_backward(sx, sn)
+      torch.cuda.current_stream(x.device).wait_stream(side)
+      graph = torch.cuda.CUDAGraph()
+      with torch.cuda.graph(graph):
+        out = self._forward_backward(sx, sn)
+      stats = {k: v.detach() for k, v in out.items() if k != "x_tilde"}
+      rec = graphs[key] = (graph, sx, sn, stats)
+    graph, sx, sn, stats = rec
+    sx.copy_(x)
+    if sn is not None:
+      sn.copy_(noise)
+    graph.replay()
+    return stats
+
+  def step(self, x, noise=None, graph=False):
+    """train_op = group(main_step, aux_step, updates[0]) (bls2017.py:173-180).  `graph=True`
+    replays the forward + backward as a captured CUDA graph (same kernels, same results up to
+    the order of the filter gradient's atomic adds)."""
+    out = self._replay(x, noise) if graph else self._forward_backward(x, noise)
     scale = self.main.all_reduce()
     self.aux.all_reduce()
     train_ops.adam_step(self.main, self.main_lr, scale)

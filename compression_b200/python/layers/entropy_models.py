@@ -199,8 +199,11 @@ class EntropyBottleneck(EntropyModel):
   @property
   def losses(self):
     """[aux loss] = sum |logits_cumulative(quantiles) - target| (entropy_models.py:502-518)."""
-    target = float(np.log(2 / self.tail_mass - 1))
-    t = torch.tensor([-target, 0., target], dtype=torch.float32, device=self.quantiles.device)
+    t = getattr(self, "_aux_target", None)
+    if t is None or t.device != self.quantiles.device:
+      target = float(np.log(2 / self.tail_mass - 1))
+      t = self._aux_target = torch.tensor([-target, 0., target], dtype=torch.float32,
+                                          device=self.quantiles.device)
     logits = self._logits_cumulative(self.quantiles, stop_gradient=True)
     return [torch.sum(torch.abs(logits - t))]
 

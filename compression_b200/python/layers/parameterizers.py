@@ -37,8 +37,14 @@ class RDFTParameterizer(Parameterizer):
   def __init__(self, dc=True):
     self.dc = bool(dc)
 
+  _matrices = {}     # (support, device, dtype) -> irdft matrix on the device (built once)
+
   def _matrix(self, shape, like):
-    m = torch.from_numpy(spectral_ops.irdft_matrix(shape[:-2])).to(like.device, like.dtype)
+    key = (tuple(shape[:-2]), str(like.device), like.dtype)
+    m = RDFTParameterizer._matrices.get(key)
+    if m is None:
+      m = torch.from_numpy(spectral_ops.irdft_matrix(shape[:-2])).to(like.device, like.dtype)
+      RDFTParameterizer._matrices[key] = m
     return m if self.dc else m[:, 1:]
 
   def init(self, value):
@@ -71,5 +77,5 @@ class NonnegativeParameterizer(Parameterizer):
   def __call__(self, stored):
     pedestal = self.reparam_offset ** 2
     bound = (self.minimum + self.reparam_offset ** 2) ** .5
-    v = math_ops.lower_bound(stored, torch.tensor(bound, dtype=stored.dtype, device=stored.device))
-    return torch.square(v) - torch.tensor(pedestal, dtype=stored.dtype, device=stored.device)
+    v = math_ops.lower_bound(stored, bound)
+    return torch.square(v) - pedestal

@@ -9,14 +9,23 @@ class _Bound(torch.autograd.Function):
 
   @staticmethod
   def forward(ctx, inputs, bound, lower, gradient):
-    bound = torch.as_tensor(bound, dtype=inputs.dtype, device=inputs.device)
-    ctx.save_for_backward(inputs, bound)
     ctx.lower, ctx.gradient = lower, gradient
+    if not isinstance(bound, torch.Tensor):
+      # a Python number stays on the host (no H2D copy per call; CUDA-graph capturable)
+      ctx.scalar = float(bound)
+      ctx.save_for_backward(inputs)
+      return torch.clamp(inputs, min=ctx.scalar) if lower else torch.clamp(inputs, max=ctx.scalar)
+    ctx.scalar = None
+    bound = bound.to(dtype=inputs.dtype, device=inputs.device)
+    ctx.save_for_backward(inputs, bound)
     return torch.maximum(inputs, bound) if lower else torch.minimum(inputs, bound)
 
   @staticmethod
   def backward(ctx, grad):
-    inputs, bound = ctx.saved_tensors
+    if ctx.scalar is not None:
+      (inputs,), bound = ctx.saved_tensors, ctx.scalar
+    else:
+      inputs, bound = ctx.saved_tensors
     if ctx.gradient == "identity":
       return grad, None, None, None
     ok = inputs >= bound if ctx.lower else inputs <= bound

@@ -157,6 +157,25 @@ def test_training_step_gradients_and_descent(tfc):
   assert tuple(x_hat.shape) == (4, 64, 64, 3) and bool(torch.isfinite(x_hat).all())
 
 
+def test_training_step_cuda_graph_matches_eager(tfc):
+  """step(graph=True) replays forward + backward as one CUDA graph: same parameters after a few
+  steps as the launch-by-launch step (up to the order of the filter gradient's atomic adds)."""
+  from compression_b200.examples import bls2017
+  g = torch.Generator().manual_seed(5)
+  x = torch.rand((4, 64, 64, 3), generator=g).cuda()
+  noise = (torch.rand((4, 4, 4, 128), generator=g) - .5).cuda()
+  params, losses = [], []
+  for use_graph in (False, True):
+    trainer = bls2017.Bls2017Trainer(bls2017.Bls2017Model(128, "cuda", seed=3), lmbda=0.01)
+    for k in range(4):
+      out = trainer.step(x * (1 - 0.1 * k), noise, graph=use_graph)   # inputs change per step
+    params.append(trainer.main.param.clone())
+    losses.append(out["loss"])
+  assert abs(losses[0] - losses[1]) <= 1e-3 * abs(losses[0])
+  diff = (params[0] - params[1]).abs().max()
+  assert float(diff) <= 2e-4, float(diff)          # 4 Adam steps of 1e-4 each move <= 4e-4
+
+
 def test_bls2017_compress_decompress_roundtrip(tfc, oracle):
   """BASELINE configs[0] wiring: strings decode (CPU reference coder) to the coded symbols."""
   from compression_b200.examples import bls2017

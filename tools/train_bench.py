@@ -23,6 +23,9 @@ def main():
   ap.add_argument("--patch", type=int, default=256)
   ap.add_argument("--steps", type=int, default=10)
   ap.add_argument("--warmup", type=int, default=3)
+  ap.add_argument("--no-graph", action="store_true",
+                  help="issue the ~600 launches of a step one by one instead of replaying the "
+                       "captured CUDA graph of its forward + backward")
   args = ap.parse_args()
   from compression_b200.examples import bls2017
   world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -38,14 +41,14 @@ def main():
   torch.manual_seed(200 + rank)
   x = torch.rand((args.batch, args.patch, args.patch, 3), generator=g, device=dev)
   for _ in range(args.warmup):
-    out = trainer.step(x)
+    out = trainer.step(x, graph=not args.no_graph)
   if world > 1:
     dist.barrier()
   torch.cuda.synchronize()
   a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
   a.record()
   for _ in range(args.steps):
-    out = trainer.step(x)
+    out = trainer.step(x, graph=not args.no_graph)
   b.record()
   torch.cuda.synchronize()
   ms = torch.tensor([a.elapsed_time(b) / args.steps], device=dev)
@@ -60,7 +63,7 @@ def main():
     flop = 8.83e9 * args.batch * (args.patch / 256.0) ** 2      # fwd + bwd per image
     print(json.dumps({
         "metric": "bls2017 training step", "n_gpus": world, "batch_per_gpu": args.batch,
-        "ms_per_step": float(ms), "images_per_s": world * args.batch / float(ms) * 1e3,
+        "ms_per_step": float(ms), "cuda_graph": not args.no_graph, "images_per_s": world * args.batch / float(ms) * 1e3,
         "tflops_per_gpu": flop / float(ms) / 1e9, "parameters": trainer.num_parameters,
         "loss": out["loss"], "bpp": out["bpp"], "mse": out["mse"], "aux": out["aux"],
         "replicas_identical": True}))
