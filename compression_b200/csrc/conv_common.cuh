@@ -50,6 +50,12 @@ size_t conv_upthin_workspace(const tfc_conv_desc& d);
 int conv_upthin(const tfc_conv_desc& d, const void* in, const float* w, const float* bias,
                 void* out, void* ws, size_t ws_bytes, cudaStream_t st);
 
+// filter gradient on tcgen05 with MN-major operands (conv_wgrad_umma.cu): both channel counts
+// multiples of 64, the M side exactly 128; `dw` must be zeroed (slices add atomically)
+bool conv_wgrad_umma_supported(const tfc_conv_desc& d);
+int conv_wgrad_umma(const tfc_conv_desc& d, const void* x_bf16, const void* dy_bf16, float* dw,
+                    cudaStream_t st);
+
 // thin-input layers via space-to-depth + conv_umma (conv_s2d.cu)
 bool conv_s2d_supported(const tfc_conv_desc& d, const char** why);
 size_t conv_s2d_workspace(const tfc_conv_desc& d);

@@ -17,6 +17,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "conv_common.cuh"
@@ -233,6 +234,15 @@ extern "C" int tfc_signal_conv2d_wgrad(const tfc_conv_desc* d, const void* d_x_b
   const int taps = d->kh * d->kw;
   TFC_CUDA(cudaMemsetAsync(d_dw, 0, (size_t)taps * d->cin * d->cout * sizeof(float), st));
   if (d->n == 0) return TFC_OK;
+  {
+    static int force_wmma = -1;
+    if (force_wmma < 0) {
+      const char* e = getenv("TFC_WGRAD_WMMA");
+      force_wmma = (e && e[0] == '1') ? 1 : 0;
+    }
+    if (!force_wmma && tfc::conv_wgrad_umma_supported(*d))
+      return tfc::conv_wgrad_umma(*d, d_x_bf16, d_dy_bf16, d_dw, st);
+  }
   WgradParams p{};
   p.n = d->n; p.h = d->h; p.w = d->w; p.cin = d->cin; p.ho = d->ho; p.wo = d->wo;
   p.cout = d->cout; p.kh = d->kh; p.kw = d->kw; p.sd = d->sd; p.su = d->su;

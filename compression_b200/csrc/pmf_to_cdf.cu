@@ -7,6 +7,7 @@
 //   penalty/gain            -> IEEE double subtract + multiply (exact on both sides)
 //   std::sort tie order     -> StdSortReplay (stdsort_replay.cuh)
 //   find_if + rotate        -> the same linear scan + shift
+#include <algorithm>
 #include <cmath>
 #include <mutex>
 #include <vector>
@@ -89,6 +90,107 @@ __global__ void pmf_to_cdf_kernel(const float* __restrict__ pmf, int64_t rows, i
   for (int i = 0; i < n; ++i) { run += c[i]; c[i] = run; }
 }
 
+// ---- long rows: one WARP per row, everything in shared memory --------------------------------
+// One thread per row leaves the GPU empty when there are few long rows (a Gaussian scale table
+// is 64 rows of up to 1481 entries) and walks its row through global memory one dependent load
+// at a time.  Here the row's items {key, index, count} live in shared memory; the keys are
+// computed and the result is scanned by the whole warp; lane 0 replays std::sort (its decision
+// sequence is what fixes the order of equal keys and cannot be reordered); the re-insertion of
+// the adjusted head — `find_if` + `rotate` in the reference (:165-181, :182-199) — is a ballot
+// over 32 candidates at a time and a cooperative shift.
+struct SmemAcc {
+  tfc::SortItem* base;
+  __device__ __forceinline__ tfc::SortItem get(int i) const { return base[i]; }
+  __device__ __forceinline__ void set(int i, const tfc::SortItem& v) const { base[i] = v; }
+};
+
+constexpr int kWarpRowBytesPerEntry = (int)sizeof(tfc::SortItem) + 8;   // item + pmf + count
+
+template <bool OVER>
+__device__ void rebalance_warp(tfc::SortItem* it, const float* sp, int32_t* cnt, int n, int todo,
+                               int lane) {
+  for (int i = lane; i < n; i += 32) {
+    tfc::SortItem v;
+    v.idx = i; v.pad = cnt[i];
+    v.key = OVER ? steal_cost((double)sp[i], cnt[i]) : give_gain((double)sp[i], cnt[i]);
+    it[i] = v;
+  }
+  __syncwarp();
+  if (lane == 0) {
+    tfc::StdSortReplay<SmemAcc, !OVER> sorter(SmemAcc{it});
+    sorter.sort(n);
+  }
+  __syncwarp();
+  for (; todo > 0; --todo) {
+    tfc::SortItem head = it[0];
+    head.pad += OVER ? -1 : 1;
+    head.key = OVER ? steal_cost((double)sp[head.idx], head.pad)
+                    : give_gain((double)sp[head.idx], head.pad);
+    int pos = n;
+    for (int base = 1; base < n; base += 32) {
+      const int j = base + lane;
+      tfc::SortItem o;
+      bool stop = false;
+      if (j < n) {
+        o = it[j];
+        stop = OVER ? head.key < o.key : head.key > o.key;
+      }
+      const unsigned m = __ballot_sync(0xFFFFFFFFu, stop);
+      const int lim = m ? base + __ffs(m) - 1 : min(base + 32, n);
+      __syncwarp();
+      if (j < lim) it[j - 1] = o;
+      __syncwarp();
+      if (m) { pos = lim; break; }
+    }
+    if (lane == 0) it[pos - 1] = head;
+    __syncwarp();
+  }
+  for (int i = lane; i < n; i += 32) cnt[it[i].idx] = it[i].pad;
+  __syncwarp();
+}
+
+__global__ void pmf_to_cdf_warp_kernel(const float* __restrict__ pmf, int64_t rows, int n,
+                                       int precision, int32_t* __restrict__ cdf) {
+  extern __shared__ __align__(16) uint8_t smem_rows[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpc = blockDim.x >> 5;
+  const int64_t r = (int64_t)blockIdx.x * wpc + warp;
+  if (r >= rows) return;
+  const int npad = (n + 3) & ~3;
+  uint8_t* mine = smem_rows + (size_t)warp * npad * kWarpRowBytesPerEntry;
+  tfc::SortItem* it = reinterpret_cast<tfc::SortItem*>(mine);
+  float* sp = reinterpret_cast<float*>(it + npad);
+  int32_t* cnt = reinterpret_cast<int32_t*>(sp + npad);
+  const float* p = pmf + r * n;
+  int32_t* c = cdf + r * (int64_t)(n + 1);
+  const int32_t total = 1 << precision;
+  int32_t sum = 0;
+  for (int i = lane; i < n; i += 32) {
+    const float pv = p[i];
+    const int32_t v = max((int32_t)rintf(pv * (float)total), 1);
+    sp[i] = pv;
+    cnt[i] = v;
+    sum += v;
+  }
+  sum = __reduce_add_sync(0xFFFFFFFFu, sum);
+  __syncwarp();
+  if (sum > total) rebalance_warp<true>(it, sp, cnt, n, sum - total, lane);
+  else if (sum < total) rebalance_warp<false>(it, sp, cnt, n, total - sum, lane);
+  // cdf = [0, cumsum(count)]
+  int32_t run = 0;
+  if (lane == 0) c[0] = 0;
+  for (int base = 0; base < n; base += 32) {
+    const int i = base + lane;
+    int32_t v = i < n ? cnt[i] : 0;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int32_t u = __shfl_up_sync(0xFFFFFFFFu, v, o);
+      if (lane >= o) v += u;
+    }
+    if (i < n) c[i + 1] = run + v;
+    run += __shfl_sync(0xFFFFFFFFu, v, 31);
+  }
+}
+
 int ensure_lut() {
   static std::mutex mu;
   static std::vector<int> done;  // per-device flag
@@ -128,6 +230,22 @@ extern "C" int tfc_pmf_to_quantized_cdf(const float* d_pmf, int64_t rows, int32_
   int rc = ensure_lut();
   if (rc) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // long rows: a warp per row in shared memory, as many warps per CTA as fit (at most 4)
+  const size_t row_bytes = (size_t)((n + 3) & ~3) * kWarpRowBytesPerEntry;
+  if (n >= 64 && row_bytes <= 200 * 1024) {
+    const int wpc = (int)std::max<size_t>(1, std::min<size_t>(4, (200 * 1024) / row_bytes));
+    const size_t smem = wpc * row_bytes;
+    static bool attr = false;
+    if (!attr) {
+      TFC_CUDA(cudaFuncSetAttribute(pmf_to_cdf_warp_kernel,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      attr = true;
+    }
+    pmf_to_cdf_warp_kernel<<<(unsigned)((rows + wpc - 1) / wpc), wpc * 32, smem, st>>>(
+        d_pmf, rows, n, precision, d_cdf);
+    TFC_LAUNCHED("pmf_to_cdf_kernel");
+    return TFC_OK;
+  }
   const int64_t stride = (rows + 31) / 32 * 32;
   const int threads = 32;
   pmf_to_cdf_kernel<<<(unsigned)((rows + threads - 1) / threads), threads, 0, st>>>(

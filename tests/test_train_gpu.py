@@ -41,6 +41,11 @@ CASES = [
     (128, 128, 5, False, 1, 2, 8, 12, torch.bfloat16),
     (128, 3, 9, False, 1, 4, 8, 8, torch.bfloat16),      # last synthesis layer of bls2017
     (192, 192, 3, True, 1, 1, 10, 14, torch.bfloat16),
+    # filter gradient on tcgen05 (MN-major operands): M side 128, N side 64 / 128 / 192
+    (128, 192, 3, True, 1, 1, 10, 14, torch.bfloat16),
+    (128, 64, 5, True, 2, 1, 12, 20, torch.bfloat16),
+    (192, 128, 5, False, 1, 2, 6, 10, torch.bfloat16),
+    (128, 128, 5, True, 2, 1, 64, 64, torch.bfloat16),   # several tiles per image and per CTA
 ]
 
 
@@ -172,8 +177,12 @@ def test_training_step_cuda_graph_matches_eager(tfc):
     params.append(trainer.main.param.clone())
     losses.append(out["loss"])
   assert abs(losses[0] - losses[1]) <= 1e-3 * abs(losses[0])
-  diff = (params[0] - params[1]).abs().max()
-  assert float(diff) <= 2e-4, float(diff)          # 4 Adam steps of 1e-4 each move <= 4e-4
+  # Adam normalises the step, so a gradient near zero whose sign the summation order decides
+  # moves its parameter by up to lr = 1e-4 per step either way: bounded difference for those
+  # few, agreement on average
+  diff = (params[0] - params[1]).abs()
+  assert float(diff.max()) <= 8e-4, float(diff.max())
+  assert float(diff.mean()) <= 2e-5, float(diff.mean())
 
 
 def test_bls2017_compress_decompress_roundtrip(tfc, oracle):
