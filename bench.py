@@ -291,7 +291,9 @@ def run_b200(args):
     # ~230 bytes of activations per input pixel stay reserved per batch in flight (measured:
     # 15.2 GB for 32 x 1080p, 5.8 GB for 64 x 768x512); keep the pipeline inside 3/4 of HBM
     total_mem = torch.cuda.get_device_properties(dev).total_memory
-    args.depth = max(1, min(12, int(0.75 * total_mem / (230.0 * pixels_per_step))))
+    # measured (profiles/r1h_pipeline_sweep.txt): C2 device 1632 / e2e 1471 MPix/s at 12 batches in
+    # flight, 1738 / 1569 at 16, 1731 / 1640 at 20, 1734 / 1621 at 24
+    args.depth = max(1, min(20, int(0.85 * total_mem / (230.0 * pixels_per_step))))
   if args.coder_pack <= 0:
     # streams in flight / CTAs wanted: the coder is latency bound per stream, and 4 streams per
     # CTA is the measured optimum once there are more streams than ~4 per SM
