@@ -55,7 +55,7 @@ def parse_args():
   ap.add_argument("--verbose", action="store_true", help="stage/layer breakdown on stderr")
   ap.add_argument("--depth", type=int, default=0,
                   help="batches in flight on separate CUDA streams (1: strictly serial steps; "
-                       "0: 12, or fewer if 12 batches of activations would not fit in HBM)")
+                       "0: 20, or fewer if 20 batches of activations would not fit in HBM)")
   ap.add_argument("--tiles-per-cta", type=int, default=8,
                   help="transform kernels: tiles per CTA when depth > 1 (0: persistent grid)")
   ap.add_argument("--coder-pack", type=int, default=0,
