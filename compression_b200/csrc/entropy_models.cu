@@ -405,6 +405,132 @@ eb_call_vec_kernel(const float4* __restrict__ x, int64_t nvec, int channels,
   }
 }
 
+
+// ---- EntropyBottleneck likelihood: backward (training step) ---------------------
+// Gradient of lik = max(|sigmoid(s*upper) - sigmoid(s*lower)|, bound) (entropy_models.py:626-658,
+// bound with the lower_bound gradient rule of ops/math_ops.py:61-74) with respect to the input
+// and to the PACKED effective parameters (softplus / tanh already applied; autograd carries the
+// gradient on to the stored variables).  The forward pass is recomputed per element; one thread
+// owns one channel over a chunk of pixels, so the 43 parameter gradients of a channel accumulate
+// in registers and reach memory as one atomic add per parameter and chunk.
+template <int L, int F>
+struct EbTape {          // activations of one evaluation of the density network
+  float t0v;             // the input v
+  float th[L][F];        // tanh(t) of every gated layer
+  float h[L][F];         // layer outputs
+};
+
+template <int L, int F>
+__device__ __forceinline__ float eb_forward_tape(const float* __restrict__ p, float v,
+                                                 EbTape<L, F>& tp) {
+  tp.t0v = v;
+#pragma unroll
+  for (int j = 0; j < F; ++j) {
+    const float t = p[j] * v + p[F + j];
+    tp.th[0][j] = tanhf(t);
+    tp.h[0][j] = t + p[2 * F + j] * tp.th[0][j];
+  }
+  int base = 3 * F;
+#pragma unroll
+  for (int l = 1; l < L; ++l) {
+#pragma unroll
+    for (int j = 0; j < F; ++j) {
+      float t = p[base + F * F + j];
+#pragma unroll
+      for (int k = 0; k < F; ++k) t = fmaf(p[base + j * F + k], tp.h[l - 1][k], t);
+      tp.th[l][j] = tanhf(t);
+      tp.h[l][j] = t + p[base + F * F + F + j] * tp.th[l][j];
+    }
+    base += F * F + 2 * F;
+  }
+  float out = p[base + F];
+#pragma unroll
+  for (int k = 0; k < F; ++k) out = fmaf(p[base + k], tp.h[L - 1][k], out);
+  return out;
+}
+
+// adds dout * d(logit)/d(params) to g[], returns dout * d(logit)/dv
+template <int L, int F>
+__device__ __forceinline__ float eb_backward_tape(const float* __restrict__ p,
+                                                  const EbTape<L, F>& tp, float dout, float* g) {
+  constexpr int last = 3 * F + (L - 1) * (F * F + 2 * F);
+  float dh[F];
+  g[last + F] += dout;
+#pragma unroll
+  for (int k = 0; k < F; ++k) {
+    g[last + k] += dout * tp.h[L - 1][k];
+    dh[k] = dout * p[last + k];
+  }
+  int base = last;
+#pragma unroll
+  for (int l = L - 1; l >= 1; --l) {
+    base -= F * F + 2 * F;
+    float dprev[F];
+#pragma unroll
+    for (int k = 0; k < F; ++k) dprev[k] = 0.f;
+#pragma unroll
+    for (int j = 0; j < F; ++j) {
+      const float th = tp.th[l][j];
+      g[base + F * F + F + j] += dh[j] * th;
+      const float dt = dh[j] * (1.f + p[base + F * F + F + j] * (1.f - th * th));
+      g[base + F * F + j] += dt;
+#pragma unroll
+      for (int k = 0; k < F; ++k) {
+        g[base + j * F + k] += dt * tp.h[l - 1][k];
+        dprev[k] = fmaf(dt, p[base + j * F + k], dprev[k]);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < F; ++k) dh[k] = dprev[k];
+  }
+  float dv = 0.f;
+#pragma unroll
+  for (int j = 0; j < F; ++j) {
+    const float th = tp.th[0][j];
+    g[2 * F + j] += dh[j] * th;
+    const float dt = dh[j] * (1.f + p[2 * F + j] * (1.f - th * th));
+    g[F + j] += dt;
+    g[j] += dt * tp.t0v;
+    dv = fmaf(dt, p[j], dv);
+  }
+  return dv;
+}
+
+template <int L, int F>
+__global__ void __launch_bounds__(128)
+eb_likelihood_backward_kernel(const float* __restrict__ x, int64_t pixels, int channels,
+                              int pixels_per_cta, const float* __restrict__ params, float bound,
+                              const float* __restrict__ grad_lik, float* __restrict__ grad_x,
+                              float* __restrict__ grad_params) {
+  constexpr int stride = eb_param_stride(L, F);
+  const int c = blockIdx.y * 128 + threadIdx.x;
+  if (c >= channels) return;
+  float p[stride], g[stride];
+#pragma unroll
+  for (int j = 0; j < stride; ++j) { p[j] = params[(int64_t)c * stride + j]; g[j] = 0.f; }
+  const int64_t p0 = (int64_t)blockIdx.x * pixels_per_cta;
+  const int64_t p1 = min(pixels, p0 + pixels_per_cta);
+  for (int64_t q = p0; q < p1; ++q) {
+    const int64_t i = q * channels + c;
+    const float v = x[i];
+    EbTape<L, F> lo, up;
+    const float l = eb_forward_tape<L, F>(p, v - 0.5f, lo);
+    const float u = eb_forward_tape<L, F>(p, v + 0.5f, up);
+    const float t = l + u;
+    const float s = t > 0.f ? -1.f : (t < 0.f ? 1.f : 0.f);
+    const float su = 1.0f / (1.0f + expf(-s * u)), sl = 1.0f / (1.0f + expf(-s * l));
+    const float diff = su - sl;
+    const float sg = diff > 0.f ? 1.f : (diff < 0.f ? -1.f : 0.f);
+    float gl = grad_lik[i];
+    if (!(fabsf(diff) >= bound || gl < 0.f)) gl = 0.f;      // lower_bound: identity_if_towards
+    const float du = gl * sg * s * su * (1.f - su);
+    const float dl = -gl * sg * s * sl * (1.f - sl);
+    grad_x[i] = eb_backward_tape<L, F>(p, up, du, g) + eb_backward_tape<L, F>(p, lo, dl, g);
+  }
+#pragma unroll
+  for (int j = 0; j < stride; ++j) atomicAdd(grad_params + (int64_t)c * stride + j, g[j]);
+}
+
 #define EB_DISPATCH(L_, F_, CALL)                                              \
   if (num_filters == L_ && (L_ == 0 || filter_width == F_)) { CALL(L_, F_); } else
 
@@ -472,6 +598,40 @@ extern "C" int tfc_eb_logits_cumulative(const float* d_x, int32_t channels, int3
   return eb_unsupported(num_filters, filter_width);
 #undef CALL
   TFC_LAUNCHED("eb_logits_kernel");
+  return TFC_OK;
+}
+
+extern "C" int tfc_eb_likelihood_backward(const float* d_x, int64_t count, int32_t channels,
+                                          const float* d_params, int32_t num_filters,
+                                          int32_t filter_width, float likelihood_bound,
+                                          const float* d_grad_lik, float* d_grad_x,
+                                          float* d_grad_params, void* stream) {
+  if (channels <= 0 || count < 0 || count % channels)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "count %lld is not a multiple of channels %d",
+                     (long long)count, channels);
+  if (num_filters < 1)
+    return eb_unsupported(num_filters, filter_width);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t pbytes = (size_t)channels * eb_param_stride(num_filters, filter_width) * 4;
+  TFC_CUDA(cudaMemsetAsync(d_grad_params, 0, pbytes, st));
+  if (count == 0) return TFC_OK;
+  const int64_t pixels = count / channels;
+  const int ygrid = (channels + 127) / 128;
+  // ~4 CTAs per SM; every CTA ends with one atomic per parameter and thread
+  const int64_t want = std::max<int64_t>(1, (int64_t)tfc::num_sms() * 4 / ygrid);
+  const int ppc = (int)std::max<int64_t>(1, (pixels + want - 1) / want);
+  const dim3 grid((unsigned)((pixels + ppc - 1) / ppc), (unsigned)ygrid, 1);
+#define CALL(L_, F_)                                                                          \
+  eb_likelihood_backward_kernel<L_, F_><<<grid, 128, 0, st>>>(                                \
+      d_x, pixels, channels, ppc, d_params, likelihood_bound, d_grad_lik, d_grad_x,           \
+      d_grad_params)
+  EB_DISPATCH(3, 3, CALL) EB_DISPATCH(1, 3, CALL) EB_DISPATCH(2, 3, CALL) EB_DISPATCH(4, 3, CALL)
+  EB_DISPATCH(1, 1, CALL) EB_DISPATCH(2, 1, CALL) EB_DISPATCH(3, 1, CALL) EB_DISPATCH(1, 2, CALL)
+  EB_DISPATCH(2, 2, CALL) EB_DISPATCH(3, 2, CALL) EB_DISPATCH(1, 4, CALL) EB_DISPATCH(2, 4, CALL)
+  EB_DISPATCH(3, 4, CALL)
+  return eb_unsupported(num_filters, filter_width);
+#undef CALL
+  TFC_LAUNCHED("eb_likelihood_backward_kernel");
   return TFC_OK;
 }
 

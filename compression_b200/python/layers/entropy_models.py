@@ -101,6 +101,38 @@ class EntropyModel(object):
     return tuple(input_shape), tuple(input_shape)
 
 
+class _EbLikelihood(torch.autograd.Function):
+  """EntropyBottleneck._likelihood + likelihood bound (entropy_models.py:626-658, :181-184) as
+  one CUDA kernel each way; `params` is the packed effective parameter matrix [channels, 43]."""
+
+  @staticmethod
+  def forward(ctx, x, params, eb):
+    lik = torch.empty_like(x)
+    p = params.detach().contiguous()
+    nl, fw = eb._filter_args()
+    _lib.check(_lib.lib().tfc_eb_call(
+        _lib.ptr(x), _i64(x.numel()), _i32(eb.channels), _lib.ptr(p), nl, fw,
+        ctypes.c_void_p(0), _f32(max(eb.likelihood_bound, 0.0)), 1, ctypes.c_void_p(0),
+        _lib.ptr(lik), _lib.stream_ptr(x.device)))
+    ctx.save_for_backward(x, p)
+    ctx.eb = eb
+    return lik
+
+  @staticmethod
+  def backward(ctx, grad):
+    x, p = ctx.saved_tensors
+    eb = ctx.eb
+    grad = grad.contiguous()
+    gx = torch.empty_like(x)
+    gp = torch.empty_like(p)
+    nl, fw = eb._filter_args()
+    _lib.check(_lib.lib().tfc_eb_likelihood_backward(
+        _lib.ptr(x), _i64(x.numel()), _i32(eb.channels), _lib.ptr(p), nl, fw,
+        _f32(max(eb.likelihood_bound, 0.0)), _lib.ptr(grad), _lib.ptr(gx), _lib.ptr(gp),
+        _lib.stream_ptr(x.device)))
+    return gx, gp, None
+
+
 class EntropyBottleneck(EntropyModel):
   """Entropy bottleneck layer (factorised prior) — entropy_models.py:298-704."""
 
@@ -156,15 +188,23 @@ class EntropyBottleneck(EntropyModel):
     self._pmf_length = maxima + minima + 1
     self._params = self._pack_params()
 
-  def _pack_params(self):
-    """Reparameterised density-net weights in the per-channel layout tfc_eb_call expects."""
+  def _pack_params(self, detach=True):
+    """Reparameterised density-net weights in the per-channel layout tfc_eb_call expects
+    (`detach=False`: as a differentiable function of the variables, for the training step)."""
     parts = []
     for i in range(len(self.filters) + 1):
       parts.append(torch.nn.functional.softplus(self.matrices[i]).reshape(self.channels, -1))
       parts.append(self.biases[i].reshape(self.channels, -1))
       if i < len(self.factors):
         parts.append(torch.tanh(self.factors[i]).reshape(self.channels, -1))
-    return torch.cat(parts, dim=1).detach().float().contiguous()
+    packed = torch.cat(parts, dim=1).float().contiguous()
+    return packed.detach() if detach else packed
+
+  def likelihood_training(self, x):
+    """Likelihood of `x` as given (the caller has added its uniform noise), differentiable with
+    respect to x and the density variables: forward tfc_eb_call (mode 1), backward
+    tfc_eb_likelihood_backward.  Needs at least one hidden layer."""
+    return _EbLikelihood.apply(x.contiguous(), self._pack_params(detach=False), self)
 
   def _filter_args(self):
     return _i32(len(self.filters)), _i32(self.filters[0] if self.filters else 1)

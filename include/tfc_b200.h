@@ -160,6 +160,16 @@ int tfc_eb_call(const float* d_x, int64_t count, int32_t channels, const float* 
                 int32_t num_filters, int32_t filter_width, const float* d_medians,
                 float likelihood_bound, int mode, float* d_values, float* d_lik, void* stream);
 
+/* Gradient of the likelihood above in mode 1 (the training graph, examples/bls2017.py:156-171;
+ * TF derives it through entropy_models.py:626-658 and the lower_bound rule of
+ * ops/math_ops.py:61-74): d_grad_x[i] = d_grad_lik[i] * d lik / d x, d_grad_params [channels,
+ * stride] = sum over the elements of each channel of d_grad_lik * d lik / d params, params in
+ * the packed effective layout of tfc_eb_call.  num_filters >= 1. */
+int tfc_eb_likelihood_backward(const float* d_x, int64_t count, int32_t channels,
+                               const float* d_params, int32_t num_filters, int32_t filter_width,
+                               float likelihood_bound, const float* d_grad_lik, float* d_grad_x,
+                               float* d_grad_params, void* stream);
+
 /* _quantize(mode="symbols") (entropy_models.py:609-618): int32(floor(x + (0.5 - median_c))) */
 int tfc_eb_symbols(const float* d_x, int64_t count, int32_t channels, const float* d_medians,
                    int32_t* d_symbols, void* stream);

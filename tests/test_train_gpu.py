@@ -162,6 +162,46 @@ def test_training_step_gradients_and_descent(tfc):
   assert tuple(x_hat.shape) == (4, 64, 64, 3) and bool(torch.isfinite(x_hat).all())
 
 
+def test_eb_likelihood_kernel_gradients_match_autograd(tfc):
+  """EntropyBottleneck.likelihood_training (one CUDA kernel each way) against the same function
+  in torch ops under autograd (entropy_models.py:626-658 + the lower_bound gradient rule)."""
+  from compression_b200.python.layers import entropy_models
+  from compression_b200.python.ops import math_ops
+  g = torch.Generator().manual_seed(9)
+  eb = entropy_models.EntropyBottleneck()
+  eb.build(12, "cuda", g)
+  for group in (eb.matrices, eb.biases, eb.factors):
+    for i in range(len(group)):
+      group[i] = (group[i] + 0.3 * torch.randn(group[i].shape, generator=g).cuda()).requires_grad_()
+  x = (torch.randn((3, 5, 7, 12), generator=g) * 6).cuda().requires_grad_()
+  x.data[0, 0, 0, :] = 40.0                           # likelihood below the bound: gradient rule
+  up = torch.randn((3, 5, 7, 12), generator=g).cuda()
+
+  def torch_path(v4):
+    c = v4.shape[-1]
+    v = v4.reshape(-1, c).t().reshape(c, 1, -1)
+    lower = eb._logits_cumulative(v - .5)
+    upper = eb._logits_cumulative(v + .5)
+    sign = -torch.sign(lower + upper).detach()
+    lik = torch.abs(torch.sigmoid(sign * upper) - torch.sigmoid(sign * lower))
+    lik = math_ops.lower_bound(lik, eb.likelihood_bound)
+    return lik.reshape(c, -1).t().reshape(v4.shape)
+
+  results = []
+  for fn in (torch_path, eb.likelihood_training):
+    for t in [x] + eb.matrices + eb.biases + eb.factors:
+      t.grad = None
+    lik = fn(x)
+    (lik * up).sum().backward()
+    results.append([lik.detach().clone(), x.grad.clone()] +
+                   [t.grad.clone() for t in eb.matrices + eb.biases + eb.factors])
+  names = ["likelihood", "d/dx"] + ["d/dparam %d" % i for i in range(len(results[0]) - 2)]
+  for name, want, got in zip(names, results[0], results[1]):
+    scale = float(want.abs().max()) + 1e-12
+    err = float((got - want).abs().max()) / scale
+    assert err <= 2e-4, (name, err, scale)
+
+
 def test_training_step_cuda_graph_matches_eager(tfc):
   """step(graph=True) replays forward + backward as one CUDA graph: same parameters after a few
   steps as the launch-by-launch step (up to the order of the filter gradient's atomic adds)."""
