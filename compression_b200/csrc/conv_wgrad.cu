@@ -203,6 +203,50 @@ conv_wgrad_kernel(const WgradParams p) {
   }
 }
 
+// bias gradient: column sums of a [pixels, channels] float32 tensor (channels % 4 == 0: one float4
+// per thread, 32 pixel rows per CTA pass, shared-memory tree over the rows, one atomic per
+// channel and CTA)
+__global__ void __launch_bounds__(256)
+column_sums_kernel(const float4* __restrict__ x, int64_t pixels, int cvec,
+                   float* __restrict__ out) {
+  extern __shared__ float4 part[];             // [rows_per_pass][cvec]
+  const int rows = 256 / min(cvec, 256) > 0 ? 256 / min(cvec, 256) : 1;
+  const int col = threadIdx.x % cvec, row = threadIdx.x / cvec;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (row < rows) {
+    for (int64_t q = (int64_t)blockIdx.x * rows + row; q < pixels; q += (int64_t)gridDim.x * rows) {
+      const float4 v = __ldg(x + q * cvec + col);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    part[row * cvec + col] = acc;
+  }
+  __syncthreads();
+  if (row == 0) {
+    for (int r = 1; r < rows; ++r) {
+      const float4 v = part[r * cvec + col];
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    atomicAdd(out + 4 * col + 0, acc.x);
+    atomicAdd(out + 4 * col + 1, acc.y);
+    atomicAdd(out + 4 * col + 2, acc.z);
+    atomicAdd(out + 4 * col + 3, acc.w);
+  }
+}
+
+// any channel count: thread = (row, channel), same scheme with scalars
+__global__ void __launch_bounds__(256)
+column_sums_scalar_kernel(const float* __restrict__ x, int64_t total, int channels,
+                          float* __restrict__ out) {
+  // every thread walks elements with a fixed residue modulo `channels`: the stride is the thread
+  // count rounded DOWN to a multiple of channels (the launch has at least `channels` threads)
+  const int64_t stride = (int64_t)gridDim.x * 256 / channels * channels;
+  const int64_t i0 = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (i0 >= stride) return;
+  float acc = 0.f;
+  for (int64_t i = i0; i < total; i += stride) acc += x[i];
+  atomicAdd(out + (int)(i0 % channels), acc);
+}
+
 // fused Adam over a flat parameter bucket (tf.train.AdamOptimizer semantics: the bias
 // correction is folded into the step size, epsilon is NOT scaled)
 __global__ void adam_kernel(float* __restrict__ param, const float* __restrict__ grad,
@@ -265,6 +309,30 @@ extern "C" int tfc_signal_conv2d_wgrad(const tfc_conv_desc* d, const void* d_x_b
   dim3 grid(p.ctiles * p.otiles, grid_taps, p.kslices);
   conv_wgrad_kernel<<<grid, kThreads, 0, st>>>(p);
   TFC_LAUNCHED("conv_wgrad_kernel");
+  return TFC_OK;
+}
+
+extern "C" int tfc_column_sums(const float* d_x, int64_t pixels, int32_t channels, float* d_out,
+                               void* stream) {
+  if (pixels < 0 || channels <= 0)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "bad column-sum shape");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  TFC_CUDA(cudaMemsetAsync(d_out, 0, (size_t)channels * sizeof(float), st));
+  if (pixels == 0) return TFC_OK;
+  const int sms = tfc::num_sms();
+  if ((channels & 3) == 0 && channels <= 1024 && (reinterpret_cast<uintptr_t>(d_x) & 15) == 0) {
+    const int cvec = channels / 4;
+    const int rows = std::max(1, 256 / cvec);
+    const int grid = (int)std::min<int64_t>((pixels + rows - 1) / rows, (int64_t)sms * 8);
+    column_sums_kernel<<<grid, 256, (size_t)rows * cvec * sizeof(float4), st>>>(
+        reinterpret_cast<const float4*>(d_x), pixels, cvec, d_out);
+  } else {
+    const int64_t total = pixels * channels;
+    const int grid = (int)std::max<int64_t>((channels + 255) / 256,
+                                            std::min<int64_t>((total + 255) / 256, (int64_t)sms * 8));
+    column_sums_scalar_kernel<<<grid, 256, 0, st>>>(d_x, total, channels, d_out);
+  }
+  TFC_LAUNCHED("column_sums_kernel");
   return TFC_OK;
 }
 

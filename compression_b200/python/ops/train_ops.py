@@ -85,7 +85,11 @@ class _SignalConv(torch.autograd.Function):
           ctypes.byref(d), _lib.ptr(xb), _lib.ptr(dy), _lib.ptr(dw), _lib.stream_ptr(x.device)))
       dw = dw.to(w.dtype)
     if ctx.has_bias and ctx.needs_input_grad[2]:
-      db = dout.sum(dim=(0, 1, 2))
+      do = dout.float().contiguous()
+      db = torch.empty((do.shape[-1],), dtype=torch.float32, device=do.device)
+      _lib.check(_lib.lib().tfc_column_sums(
+          _lib.ptr(do), ctypes.c_int64(do.numel() // do.shape[-1]), ctypes.c_int32(do.shape[-1]),
+          _lib.ptr(db), _lib.stream_ptr(do.device)))
     return dx, dw, db, None
 
 

@@ -276,6 +276,11 @@ int tfc_adam_step(float* d_param, const float* d_grad, float* d_m, float* d_v, i
                   float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale,
                   void* stream);
 
+/* Bias gradient of a layer (the reduction TF derives for tf.nn.bias_add, signal_conv.py:785-804):
+ * d_out[c] = sum over pixels of d_x[pixel, c], float32. */
+int tfc_column_sums(const float* d_x, int64_t pixels, int32_t channels, float* d_out,
+                    void* stream);
+
 /* Stand-alone GDN / IGDN on a channels_last tensor of `pixels` x `channels` (gdn.py:171-206). */
 int tfc_gdn(const void* d_x, int64_t pixels, int32_t channels, const float* d_beta,
             const float* d_gamma, int inverse, int in_dtype, int out_dtype, void* d_out,
