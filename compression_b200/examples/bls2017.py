@@ -182,6 +182,55 @@ class _GdnContraction(torch.autograd.Function):
       return g @ gamma.t(), x2.t() @ g
 
 
+class _GdnTrain(torch.autograd.Function):
+  """GDN / IGDN of the training graph (gdn.py:171-202): contraction and its gradients as TF32
+  GEMMs, everything around them as three elementwise CUDA passes (csrc/gdn_train.cu) instead of
+  ~12 autograd launches per layer over the largest activations of the step."""
+
+  @staticmethod
+  def forward(ctx, x, beta, gamma, inverse):
+    import ctypes
+    from compression_b200 import _lib
+    shape, c = x.shape, x.shape[-1]
+    x2d = x.reshape(-1, c).contiguous()
+    x2 = x2d * x2d
+    with _tf32_matmul():
+      nraw = x2 @ gamma
+    y = torch.empty_like(x2d)
+    b = beta.detach().float().contiguous()
+    _lib.check(_lib.lib().tfc_gdn_train_forward(
+        _lib.ptr(x2d), _lib.ptr(nraw), _lib.ptr(b), ctypes.c_int64(x2d.shape[0]),
+        ctypes.c_int32(c), int(bool(inverse)), _lib.ptr(y), _lib.ptr(nraw),
+        _lib.stream_ptr(x.device)))
+    ctx.save_for_backward(x2d, x2, nraw, gamma)
+    ctx.inverse, ctx.shape = bool(inverse), shape
+    return y.reshape(shape)
+
+  @staticmethod
+  def backward(ctx, gy):
+    import ctypes
+    from compression_b200 import _lib
+    x2d, x2, norm, gamma = ctx.saved_tensors
+    p, c = x2d.shape
+    gy2d = gy.reshape(p, c).float().contiguous()
+    gx = torch.empty_like(x2d)
+    gnorm = torch.empty_like(x2d)
+    L = _lib.lib()
+    st = _lib.stream_ptr(x2d.device)
+    _lib.check(L.tfc_gdn_train_backward_pre(
+        _lib.ptr(gy2d), _lib.ptr(x2d), _lib.ptr(norm), ctypes.c_int64(p), ctypes.c_int32(c),
+        int(ctx.inverse), _lib.ptr(gx), _lib.ptr(gnorm), st))
+    with _tf32_matmul():
+      gx2 = gnorm @ gamma.t()
+      ggamma = x2.t() @ gnorm
+    _lib.check(L.tfc_gdn_train_backward_post(
+        _lib.ptr(gx), _lib.ptr(x2d), _lib.ptr(gx2), ctypes.c_int64(p), ctypes.c_int32(c), st))
+    gbeta = torch.empty((c,), dtype=torch.float32, device=x2d.device)
+    _lib.check(L.tfc_column_sums(_lib.ptr(gnorm), ctypes.c_int64(p), ctypes.c_int32(c),
+                                 _lib.ptr(gbeta), st))
+    return gx.reshape(ctx.shape), gbeta, ggamma, None
+
+
 class Bls2017Trainer(object):
   """One synchronous data-parallel training step (bls2017.py:156-185).
 
@@ -241,6 +290,8 @@ class Bls2017Trainer(object):
   def _gdn(act, x):
     """gdn.py:171-202 in torch ops: the 1x1 contraction is a plain GEMM."""
     beta, gamma = act.beta_parameterizer(act.reparam_beta), act.gamma_parameterizer(act.reparam_gamma)
+    if x.dtype == torch.float32 and x.shape[-1] % 4 == 0:
+      return _GdnTrain.apply(x, beta, gamma.float().contiguous(), act.inverse)
     norm = _GdnContraction.apply((x * x).reshape(-1, x.shape[-1]), gamma) + beta
     norm = norm.reshape(x.shape)
     return x * (torch.sqrt(norm) if act.inverse else torch.rsqrt(norm))

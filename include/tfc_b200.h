@@ -281,6 +281,22 @@ int tfc_adam_step(float* d_param, const float* d_grad, float* d_m, float* d_v, i
 int tfc_column_sums(const float* d_x, int64_t pixels, int32_t channels, float* d_out,
                     void* stream);
 
+/* Elementwise halves of GDN / IGDN in the training graph (gdn.py:171-202 and its gradient); the
+ * C x C contraction x^2 . gamma and its two gradients are GEMMs issued by the caller.  float32,
+ * channels_last [pixels, channels], channels a multiple of 4, buffers 16-byte aligned.
+ *   forward:        d_norm = d_x2_gamma + beta ;  d_y = x * rsqrt(norm)      (inverse: x * sqrt(norm))
+ *   backward_pre:   d_gx1 = gy * rsqrt(norm) ; d_gnorm = -gy * x * norm^-3/2 / 2
+ *                   (inverse: gy * sqrt(norm) ; gy * x / sqrt(norm) / 2)
+ *   backward_post:  d_gx += 2 * x * d_gx2          with d_gx2 = gnorm . gamma^T */
+int tfc_gdn_train_forward(const float* d_x, const float* d_x2_gamma, const float* d_beta,
+                          int64_t pixels, int32_t channels, int inverse, float* d_y,
+                          float* d_norm, void* stream);
+int tfc_gdn_train_backward_pre(const float* d_gy, const float* d_x, const float* d_norm,
+                               int64_t pixels, int32_t channels, int inverse, float* d_gx1,
+                               float* d_gnorm, void* stream);
+int tfc_gdn_train_backward_post(float* d_gx, const float* d_x, const float* d_gx2, int64_t pixels,
+                                int32_t channels, void* stream);
+
 /* Stand-alone GDN / IGDN on a channels_last tensor of `pixels` x `channels` (gdn.py:171-206). */
 int tfc_gdn(const void* d_x, int64_t pixels, int32_t channels, const float* d_beta,
             const float* d_gamma, int inverse, int in_dtype, int out_dtype, void* d_out,
