@@ -45,7 +45,7 @@ struct WgradParams {
   float* dw;
 };
 
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 8)
 conv_wgrad_kernel(const WgradParams p) {
   __shared__ __align__(32) __nv_bfloat16 xs[kBK * kLd];
   __shared__ __align__(32) __nv_bfloat16 ys[kBK * kLd];
@@ -81,9 +81,12 @@ conv_wgrad_kernel(const WgradParams p) {
       int64_t xo = -1, yo = -1;
       int lo = 0, hi = 0x7FFFFFFF;
       if (q < p_end && p.fuse == 1) {        // whole kernel row a of output pixel (i, j)
-        const int j = (int)(q % gw);
-        const int i = (int)((q / gw) % gh);
-        const int nn = (int)(q / ((int64_t)gw * gh));
+        // 32-bit division (pixels < 2^31 is checked on the host): this decomposition sits on the
+        // serial part of every iteration
+        const uint32_t qq = (uint32_t)q, row = qq / (uint32_t)gw;
+        const int j = (int)(qq - row * (uint32_t)gw);
+        const int nn = (int)(row / (uint32_t)gh);
+        const int i = (int)(row - (uint32_t)nn * (uint32_t)gh);
         const int yi = i * p.sd + a - p.pt, xj0 = j * p.sd - p.pl;
         if (yi >= 0 && yi < p.h) {
           xo = (((int64_t)nn * p.h + yi) * p.w + xj0) * p.cin + ((int64_t)1 << 40);  // may be < 0
@@ -92,9 +95,12 @@ conv_wgrad_kernel(const WgradParams p) {
           hi = min(p.kw, p.w - xj0) * p.cin;
         }
       } else if (q < p_end && p.fuse == 2) { // input pixel (i, j) against kernel row a of dy
-        const int j = (int)(q % gw);
-        const int i = (int)((q / gw) % gh);
-        const int nn = (int)(q / ((int64_t)gw * gh));
+        // 32-bit division (pixels < 2^31 is checked on the host): this decomposition sits on the
+        // serial part of every iteration
+        const uint32_t qq = (uint32_t)q, row = qq / (uint32_t)gw;
+        const int j = (int)(qq - row * (uint32_t)gw);
+        const int nn = (int)(row / (uint32_t)gh);
+        const int i = (int)(row - (uint32_t)nn * (uint32_t)gh);
         const int oi = p.su * i - a + p.pt, oj0 = p.su * j + p.pl - (p.kw - 1);
         if (oi >= 0 && oi < p.ho) {
           xo = (((int64_t)nn * p.h + i) * p.w + j) * p.cin;
@@ -103,9 +109,12 @@ conv_wgrad_kernel(const WgradParams p) {
           hi = min(p.kw, p.wo - oj0) * p.cout;
         }
       } else if (q < p_end) {
-        const int j = (int)(q % gw);
-        const int i = (int)((q / gw) % gh);
-        const int nn = (int)(q / ((int64_t)gw * gh));
+        // 32-bit division (pixels < 2^31 is checked on the host): this decomposition sits on the
+        // serial part of every iteration
+        const uint32_t qq = (uint32_t)q, row = qq / (uint32_t)gw;
+        const int j = (int)(qq - row * (uint32_t)gw);
+        const int nn = (int)(row / (uint32_t)gh);
+        const int i = (int)(row - (uint32_t)nn * (uint32_t)gh);
         if (p.su > 1) {           // (i, j) input pixel; the tap sends it to one output pixel
           const int oi = p.su * i - a + p.pt, oj = p.su * j - b + p.pl;
           if (oi >= 0 && oi < p.ho && oj >= 0 && oj < p.wo) {
@@ -297,9 +306,20 @@ extern "C" int tfc_signal_conv2d_wgrad(const tfc_conv_desc* d, const void* d_x_b
   p.ctiles = ((p.fuse == 1 ? d->kw * d->cin : d->cin) + kBM - 1) / kBM;
   p.otiles = ((p.fuse == 2 ? d->kw * d->cout : d->cout) + kBN - 1) / kBN;
   p.pixels = d->su > 1 ? (int64_t)d->n * d->h * d->w : (int64_t)d->n * d->ho * d->wo;
+  if (p.pixels >= ((int64_t)1 << 31))
+    return tfc::fail(TFC_ERR_UNIMPLEMENTED, "filter gradient over 2^31 or more pixels");
   const int grid_taps = p.fuse ? d->kh : taps;
   const int64_t ctas = (int64_t)grid_taps * p.ctiles * p.otiles;
-  const int64_t want = 4 * (int64_t)tfc::num_sms();
+  // CTAs per SM: the kernel is latency bound per CTA (index decomposition -> gather -> MMA with
+  // a barrier between each), so time falls with the CTAs resident per SM until the partial sums'
+  // atomics take over; measured on the 3-channel layers of bls2017: 1.71 / 0.93 / 0.66 / 0.53 /
+  // 0.46 / 0.53 ms at 1 / 2 / 3 / 4 / 6 / 8 per SM (TFC_WGRAD_WANT overrides, for experiments)
+  static int want_mult = -1;
+  if (want_mult < 0) {
+    const char* e = getenv("TFC_WGRAD_WANT");
+    want_mult = e ? std::max(1, atoi(e)) : 0;
+  }
+  const int64_t want = (want_mult ? want_mult : (p.fuse ? 6 : 4)) * (int64_t)tfc::num_sms();
   int64_t ks = std::max<int64_t>(1, (want + ctas - 1) / ctas);
   ks = std::min<int64_t>(ks, std::max<int64_t>(1, p.pixels / 1024));
   p.kslices = (int)std::min<int64_t>(ks, 65535);
