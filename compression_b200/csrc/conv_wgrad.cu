@@ -242,18 +242,25 @@ column_sums_kernel(const float4* __restrict__ x, int64_t pixels, int cvec,
   }
 }
 
-// any channel count: thread = (row, channel), same scheme with scalars
+// any channel count (<= 256 here): every thread walks elements with a fixed residue modulo
+// `channels` — the stride is the thread count rounded DOWN to a multiple of channels (the launch
+// has at least `channels` threads) — then the CTA folds its threads' sums per channel in shared
+// memory, so memory sees one atomic per channel and CTA instead of one per thread
 __global__ void __launch_bounds__(256)
 column_sums_scalar_kernel(const float* __restrict__ x, int64_t total, int channels,
                           float* __restrict__ out) {
-  // every thread walks elements with a fixed residue modulo `channels`: the stride is the thread
-  // count rounded DOWN to a multiple of channels (the launch has at least `channels` threads)
+  __shared__ float part[256];
+  for (int c = threadIdx.x; c < channels; c += 256) part[c] = 0.f;
+  __syncthreads();
   const int64_t stride = (int64_t)gridDim.x * 256 / channels * channels;
   const int64_t i0 = (int64_t)blockIdx.x * 256 + threadIdx.x;
-  if (i0 >= stride) return;
-  float acc = 0.f;
-  for (int64_t i = i0; i < total; i += stride) acc += x[i];
-  atomicAdd(out + (int)(i0 % channels), acc);
+  if (i0 < stride) {
+    float acc = 0.f;
+    for (int64_t i = i0; i < total; i += stride) acc += x[i];
+    atomicAdd(part + (int)(i0 % channels), acc);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < channels; c += 256) atomicAdd(out + c, part[c]);
 }
 
 // fused Adam over a flat parameter bucket (tf.train.AdamOptimizer semantics: the bias
@@ -347,6 +354,9 @@ extern "C" int tfc_column_sums(const float* d_x, int64_t pixels, int32_t channel
     column_sums_kernel<<<grid, 256, (size_t)rows * cvec * sizeof(float4), st>>>(
         reinterpret_cast<const float4*>(d_x), pixels, cvec, d_out);
   } else {
+    if (channels > 256)
+      return tfc::fail(TFC_ERR_UNIMPLEMENTED,
+                       "column sums over %d channels need a 16-byte aligned float4 layout", channels);
     const int64_t total = pixels * channels;
     const int grid = (int)std::max<int64_t>((channels + 255) / 256,
                                             std::min<int64_t>((total + 255) / 256, (int64_t)sms * 8));

@@ -232,7 +232,10 @@ extern "C" int tfc_pmf_to_quantized_cdf(const float* d_pmf, int64_t rows, int32_
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   // long rows: a warp per row in shared memory, as many warps per CTA as fit (at most 4)
   const size_t row_bytes = (size_t)((n + 3) & ~3) * kWarpRowBytesPerEntry;
-  if (n >= 64 && row_bytes <= 200 * 1024) {
+  // (also for short rows when there are few of them: a thread per row would leave the GPU empty
+  // and walk its row through global memory — the EntropyBottleneck table of a training step is
+  // 128 rows of 22 entries)
+  if ((n >= 64 || rows <= 2048) && row_bytes <= 200 * 1024) {
     const int wpc = (int)std::max<size_t>(1, std::min<size_t>(4, (200 * 1024) / row_bytes));
     const size_t smem = wpc * row_bytes;
     static bool attr = false;
