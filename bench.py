@@ -293,7 +293,9 @@ def run_b200(args):
     total_mem = torch.cuda.get_device_properties(dev).total_memory
     # measured (profiles/r1h_pipeline_sweep.txt): C2 device 1632 / e2e 1471 MPix/s at 12 batches in
     # flight, 1738 / 1569 at 16, 1731 / 1640 at 20, 1734 / 1621 at 24
-    args.depth = max(1, min(20, int(0.85 * total_mem / (230.0 * pixels_per_step))))
+    # (C3 ran at 12 batches in flight, 1299 device / 1196 e2e MPix/s, which 230 B/pixel would put at
+    # 183 GB: the figure is an upper bound, 200 B/pixel admits that depth)
+    args.depth = max(1, min(20, int(0.85 * total_mem / (200.0 * pixels_per_step))))
   if args.coder_pack <= 0:
     # streams in flight / CTAs wanted: the coder is latency bound per stream, and 4 streams per
     # CTA is the measured optimum once there are more streams than ~4 per SM
@@ -406,7 +408,9 @@ def run_b200(args):
                  "conv_impl": args.conv_impl,
                  "pipeline": {"batches_in_flight": args.depth,
                               "tiles_per_cta": args.tiles_per_cta if args.depth > 1 else 0,
-                              "coder_streams_per_cta": args.coder_pack if args.depth > 1 else 0}},
+                              "coder_streams_per_cta": args.coder_pack if args.depth > 1 else 0,
+                              "hbm_peak_allocated_gb": round(
+                                  torch.cuda.max_memory_allocated(dev) / 1e9, 1)}},
       "e2e": {"value": world * pixels / (e2e_ms * 1e-3) / 1e6, "unit": "MPix/s",
               "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
               "string_bytes_per_step": int(string_bytes), "ms_per_step": e2e_ms},
