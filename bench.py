@@ -26,6 +26,9 @@ import time
 
 import numpy as np
 
+# before the CUDA context exists (see compression_b200/__init__.py): one hardware queue per stream
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
