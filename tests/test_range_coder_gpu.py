@@ -115,6 +115,33 @@ def test_unbounded_many_streams_capacity_retry(tfc, oracle):
   np.testing.assert_array_equal(dec.cpu().numpy(), data)
 
 
+def test_unbounded_sweep_size_round_trip(tfc, oracle):
+  """BASELINE configs[3] scale: 16 384 streams x 4096 symbols over the bmshj2018 Gaussian table
+  (rows of 5..1481 entries, ~0.2 % escapes): decode(encode(x)) == x for every stream, and an
+  evenly spaced sample of streams is byte-identical to the CPU checker."""
+  from compression_b200.python.layers import entropy_models
+  from compression_b200.python.ops import range_coding_ops as rc
+  dev = torch.device("cuda", 0)
+  table = np.exp(np.linspace(np.log(0.11), np.log(256), 64))
+  gc = entropy_models.GaussianConditional(None, table)
+  gc.build_tables(dev)
+  cdf, size, off = gc._quantized_cdf, gc._cdf_length, gc._offset
+  g = torch.Generator(device=dev).manual_seed(5)
+  S, n = 16384, 4096
+  idx = torch.randint(0, 64, (S, n), generator=g, dtype=torch.int32, device=dev)
+  sig = torch.as_tensor(table, dtype=torch.float32, device=dev)[idx.long()]
+  sym = torch.floor(torch.randn((S, n), generator=g, device=dev) * sig + .5).to(torch.int32)
+  out, nbytes = rc.unbounded_index_range_encode_batch(sym, idx, cdf, size, off, 16, 4, 0)
+  dec = rc.unbounded_index_range_decode_batch(out, nbytes, idx, cdf, size, off, 16, 4, 0)
+  assert torch.equal(dec, sym)
+  pick = torch.linspace(0, S - 1, 48).long().to(dev)
+  got = rc.strings_to_host(out[pick], nbytes[pick])
+  c, s_, o = cdf.cpu().numpy(), size.cpu().numpy(), off.cpu().numpy()
+  sym_h, idx_h = sym[pick].cpu().numpy(), idx[pick].cpu().numpy()
+  for k in range(len(got)):
+    assert got[k] == oracle.ui_encode(sym_h[k], idx_h[k], c, s_, o, 16, 4), int(pick[k])
+
+
 def test_unbounded_long_rows_and_carry(tfc, oracle, coder_lanes):
   """Rows longer than the 32-wide search window (Gaussian-like, up to 1481 entries) and long
   runs of near-certain symbols that keep the encoder in its carry-pending state
