@@ -523,6 +523,20 @@ size_t lanes_geometry(int64_t S, int table_bytes, int* wpc, int64_t* blocks) {
   return (size_t)table_bytes + w * lanes::kWarpBytes;
 }
 
+bool bounded_lanes_wanted(int64_t S) {
+  const int mode = tfc::g_coder_lanes.load(std::memory_order_relaxed);
+  // measured (m = 64, 4096 symbols): warp per stream 14.0 / 5.8 Gsym/s at 4 K streams and
+  // 18.5 / 7.5 at 16 K; lane per stream 6.7 / 5.0 and 25.5 / 18.0 (87.9 / 64.4 at 64 K)
+  return mode == 2 || (mode == 0 && S >= 8192);
+}
+
+// a table shared by all streams is staged in shared memory when it fits in 64 KB
+int bounded_table_bytes(int64_t cdf_rows, int chip, int64_t cdf_stream_stride) {
+  const int64_t bytes = cdf_rows * chip * 4;
+  if (cdf_stream_stride != 0 || bytes > 64 * 1024) return 0;
+  return (int)((bytes + 15) & ~int64_t(15));
+}
+
 int warps_per_block(int64_t S) {
   // few streams: one warp per block so the streams spread over the SMs; many: pack 8
   const int sms = tfc::num_sms();
@@ -847,6 +861,25 @@ extern "C" int tfc_range_encode(const int16_t* d_data, int64_t S, const int64_t*
     rc = finish_checks(rec, st, 0, 0, precision, p.chip);
     if (rc) return rc;
   }
+  if (bounded_lanes_wanted(S)) {
+    lanes::BoundedParams q{};
+    q.data = d_data; q.cdf = d_cdf; q.cdf_stream_stride = cdf_stream_stride; q.cdf_rows = cdf_rows;
+    q.chip = p.chip; q.precision = precision; q.bc = p.bc; q.out = d_out; q.cap = cap;
+    q.nbytes = d_nbytes; q.status = d_status; q.S = S; q.n = n;
+    q.table_bytes = bounded_table_bytes(cdf_rows, p.chip, cdf_stream_stride);
+    int wpc = 1;
+    int64_t blocks = 0;
+    const size_t smem = lanes_geometry(S, q.table_bytes, &wpc, &blocks);
+    static bool attr = false;
+    if (!attr) {
+      TFC_CUDA(cudaFuncSetAttribute(lanes::encode_bounded_lanes,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+      attr = true;
+    }
+    lanes::encode_bounded_lanes<<<(unsigned)blocks, wpc * 32, smem, st>>>(q);
+    TFC_LAUNCHED("encode_bounded_lanes");
+    return TFC_OK;
+  }
   p.data16 = d_data; p.cdf_stream_stride = cdf_stream_stride; p.cdf = d_cdf;
   p.S = S; p.n = n; p.precision = precision;
   p.out = d_out; p.cap = cap; p.nbytes = d_nbytes; p.status = d_status;
@@ -886,6 +919,26 @@ extern "C" int tfc_range_decode(const uint8_t* d_enc, int64_t cap, const int32_t
     TFC_LAUNCHED("check_cdf_kernel");
     rc = finish_checks(rec, st, 0, 0, precision, p.chip);
     if (rc) return rc;
+  }
+  if (bounded_lanes_wanted(S)) {
+    lanes::BoundedParams q{};
+    q.cdf = d_cdf; q.cdf_stream_stride = cdf_stream_stride; q.cdf_rows = cdf_rows;
+    q.chip = p.chip; q.precision = precision; q.bc = p.bc; q.enc = d_enc; q.cap = cap;
+    q.nbytes = const_cast<int32_t*>(d_nbytes); q.values = d_out; q.status = d_status;
+    q.S = S; q.n = n;
+    q.table_bytes = bounded_table_bytes(cdf_rows, p.chip, cdf_stream_stride);
+    int wpc = 1;
+    int64_t blocks = 0;
+    const size_t smem = lanes_geometry(S, q.table_bytes, &wpc, &blocks);
+    static bool attr = false;
+    if (!attr) {
+      TFC_CUDA(cudaFuncSetAttribute(lanes::decode_bounded_lanes,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
+      attr = true;
+    }
+    lanes::decode_bounded_lanes<<<(unsigned)blocks, wpc * 32, smem, st>>>(q);
+    TFC_LAUNCHED("decode_bounded_lanes");
+    return TFC_OK;
   }
   p.enc = d_enc; p.cap = cap; p.nbytes = d_nbytes; p.cdf_stream_stride = cdf_stream_stride;
   p.out16 = d_out; p.cdf = d_cdf; p.S = S; p.n = n; p.precision = precision; p.status = d_status;

@@ -302,4 +302,140 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) decode_unbounded_lanes(cons
   if (active && p.status) p.status[s] = d.corrupt ? TFC_STREAM_CORRUPT : TFC_STREAM_OK;
 }
 
+
+// ---- bounded RangeEncode / RangeDecode (range_coding_kernels.cc:178-380), one stream per lane ---
+// data int16 in [0, chip - 1), cdf rows of `chip` entries picked per element through the merged
+// broadcast pattern (the same row for every stream at element i unless the CDF is per stream).
+// The table is staged in shared memory (pre-shifted to precision 16) when it is shared by the
+// streams and fits; otherwise entries come from global memory through L1.
+struct BoundedParams {
+  const int16_t* data;        // encode: [S, n]
+  const int32_t* cdf;
+  int64_t cdf_stream_stride;  // elements between the tables of consecutive streams (0: shared)
+  int64_t cdf_rows;           // rows of one table
+  int32_t chip, precision;
+  Broadcast bc;
+  uint8_t* out;
+  const uint8_t* enc;
+  int64_t cap;
+  int32_t* nbytes;
+  int16_t* values;            // decode: [S, n]
+  int32_t* status;
+  int64_t S, n;
+  int32_t table_bytes;        // > 0: shared table staged in shared memory
+};
+
+struct BoundedTable {
+  const uint32_t* smem;       // staged, pre-shifted (or null)
+  const int32_t* gmem;        // this lane's table in global memory
+  int sh;
+  __device__ __forceinline__ uint32_t at(int64_t i) const {
+    return smem ? smem[i] : ((uint32_t)__ldg(gmem + i) << sh);
+  }
+};
+
+__device__ __forceinline__ const uint32_t* stage_bounded(const BoundedParams& p) {
+  if (p.table_bytes <= 0) return nullptr;
+  uint32_t* tbl = reinterpret_cast<uint32_t*>(v4::smem_v4);
+  const int64_t total = p.cdf_rows * p.chip;
+  const int sh = 16 - p.precision;
+  for (int64_t i = threadIdx.x; i < total; i += blockDim.x) tbl[i] = (uint32_t)__ldg(p.cdf + i) << sh;
+  __syncthreads();
+  return tbl;
+}
+
+__global__ void __launch_bounds__(kMaxWarps * 32, 1) encode_bounded_lanes(const BoundedParams p) {
+  const uint32_t* staged = stage_bounded(p);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpc = blockDim.x >> 5;
+  const int64_t s0 = ((int64_t)blockIdx.x * wpc + warp) * 32;
+  if (s0 >= p.S) return;
+  int32_t* td = reinterpret_cast<int32_t*>(v4::smem_v4 + p.table_bytes + (size_t)warp * kWarpBytes);
+  const int64_t s = s0 + lane;
+  const bool active = s < p.S;
+  const int rows_here = (int)min((int64_t)32, p.S - s0);
+  BoundedTable t{staged, p.cdf + (active ? s : s0) * p.cdf_stream_stride, 16 - p.precision};
+  Enc e;
+  e.lo = 0; e.span1 = 0xFFFFFFFFu; e.pos = 0; e.cap = (uint32_t)p.cap; e.held = 0;
+  e.out = p.out + (active ? s : s0) * p.cap;
+  e.even = (reinterpret_cast<uintptr_t>(e.out) & 1) == 0;
+  for (int64_t i0 = 0; i0 < p.n; i0 += kTile) {
+    const bool col = i0 + lane < p.n;
+#pragma unroll 8
+    for (int r = 0; r < rows_here; ++r)
+      td[r * kLd + lane] = col ? (int32_t)__ldg(p.data + (s0 + r) * p.n + i0 + lane) : 0;
+    __syncwarp();
+    if (active) {
+      const int cnt = (int)min((int64_t)kTile, p.n - i0);
+      for (int j = 0; j < cnt; ++j) {
+        const int64_t row = broadcast_row(p.bc, i0 + j) * p.chip;
+        const int32_t v = min(max(td[lane * kLd + j], 0), p.chip - 2);
+        e.put(t.at(row + v), t.at(row + v + 1));
+      }
+    }
+    __syncwarp();
+  }
+  if (active) {
+    e.flush();
+    p.nbytes[s] = (int32_t)e.pos;
+    if (p.status) p.status[s] = e.pos > e.cap ? TFC_STREAM_CAPACITY : TFC_STREAM_OK;
+  }
+}
+
+__global__ void __launch_bounds__(kMaxWarps * 32, 1) decode_bounded_lanes(const BoundedParams p) {
+  const uint32_t* staged = stage_bounded(p);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpc = blockDim.x >> 5;
+  const int64_t s0 = ((int64_t)blockIdx.x * wpc + warp) * 32;
+  if (s0 >= p.S) return;
+  int32_t* tv = reinterpret_cast<int32_t*>(v4::smem_v4 + p.table_bytes + (size_t)warp * kWarpBytes);
+  const int64_t s = s0 + lane;
+  const bool active = s < p.S;
+  const int rows_here = (int)min((int64_t)32, p.S - s0);
+  BoundedTable t{staged, p.cdf + (active ? s : s0) * p.cdf_stream_stride, 16 - p.precision};
+  Dec d;
+  d.src = p.enc + (active ? s : s0) * p.cap;
+  d.len = active ? (uint32_t)max(min((int64_t)p.nbytes[s], p.cap), (int64_t)0) : 0u;
+  d.pos = 0; d.win = 0; d.avail = 0; d.corrupt = false;
+  d.vec = (reinterpret_cast<uintptr_t>(d.src) & 7) == 0;
+  d.span1 = 0xFFFFFFFFu;
+  d.rem = 0;
+  if (active) {
+    const uint32_t hi = d.next16();
+    d.rem = (hi << 16) | d.next16();
+  }
+  for (int64_t i0 = 0; i0 < p.n; i0 += kTile) {
+    const bool col = i0 + lane < p.n;
+    if (active) {
+      const int cnt = (int)min((int64_t)kTile, p.n - i0);
+      for (int j = 0; j < cnt; ++j) {
+        const int64_t row = broadcast_row(p.bc, i0 + j) * p.chip;
+        // smallest k in [1, chip-1] with floor(span * row[k] / 2^16) > rem  (range_coder.cc:323-340)
+        const uint64_t span = (uint64_t)d.span1 + 1u;
+        int first = 1, count = p.chip - 1;
+        while (count > 0) {
+          const int step = count >> 1;
+          if (((span * t.at(row + first + step)) >> 16) <= (uint64_t)d.rem) {
+            first += step + 1;
+            count -= step + 1;
+          } else {
+            count = step;
+          }
+        }
+        if (first > p.chip - 1) { d.corrupt = true; first = p.chip - 1; }
+        const uint32_t a = (uint32_t)((span * t.at(row + first - 1)) >> 16);
+        const uint32_t b = (uint32_t)((span * t.at(row + first)) >> 16) - 1u;
+        d.narrow(a, b);
+        tv[lane * kLd + j] = first - 1;
+      }
+    }
+    __syncwarp();
+    if (col) {
+#pragma unroll 8
+      for (int r = 0; r < rows_here; ++r)
+        p.values[(s0 + r) * p.n + i0 + lane] = (int16_t)tv[r * kLd + lane];
+    }
+    __syncwarp();
+  }
+  if (active && p.status) p.status[s] = d.corrupt ? TFC_STREAM_CORRUPT : TFC_STREAM_OK;
+}
+
 }  // namespace lanes

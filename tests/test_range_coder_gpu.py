@@ -185,7 +185,7 @@ def test_unbounded_long_rows_and_carry(tfc, oracle, coder_lanes):
   np.testing.assert_array_equal(dec.cpu().numpy(), data2)
 
 
-def test_bounded_broadcast_patterns(tfc, oracle):
+def test_bounded_broadcast_patterns(tfc, oracle, coder_lanes):
   """range_coding_kernels_test.cc:245-321: no broadcast, 1-axis and 2-axis cdf broadcast."""
   rng = np.random.default_rng(4)
   for trial in range(60):
@@ -204,7 +204,27 @@ def test_bounded_broadcast_patterns(tfc, oracle):
     np.testing.assert_array_equal(dec.cpu().numpy(), data)
 
 
-def test_bounded_readme_example(tfc):
+def test_bounded_batch_per_stream_tables(tfc, oracle, coder_lanes):
+  """Batched bounded coder: 70 ragged streams, one shared table and one table per stream."""
+  from compression_b200.python.ops import range_coding_ops as rc
+  rng = np.random.default_rng(12)
+  S, n, m, precision = 70, 333, 40, 13
+  pmf = rng.random((S, 1, m)).astype(np.float32) + 1e-3
+  pmf /= pmf.sum(-1, keepdims=True)
+  cdfs = oracle.pmf_to_cdf(pmf, precision)                 # [S, 1, m + 1]
+  data = rng.integers(0, m, size=(S, n)).astype(np.int16)
+  for shared in (True, False):
+    cdf = cdfs[0] if shared else cdfs
+    out, nbytes = rc.range_encode_batch(data, cdf, precision, debug_level=0, shared_cdf=shared)
+    got = rc.strings_to_host(out, nbytes)
+    for s in range(S):
+      assert got[s] == oracle.rc_encode(data[s], cdfs[0 if shared else s], precision), (shared, s)
+    dec = rc.range_decode_batch(out, nbytes, (n,), cdf, precision, debug_level=0,
+                                shared_cdf=shared)
+    np.testing.assert_array_equal(dec.cpu().numpy(), data)
+
+
+def test_bounded_readme_example(tfc, coder_lanes):
   """python/ops/range_coding_ops_test.py:33-46 / docs/range_coding.md:52-71."""
   rng = np.random.default_rng(5)
   data = rng.integers(0, 10, size=(4, 6, 6)).astype(np.int16)
