@@ -59,7 +59,8 @@ int64_t tfc_launch_count(void);
  *                                  off: no gain measured), 1 = off, 2, 4 (where the shape allows)
  *   TFC_CFG_CODER_LANES            unbounded-index coder with one stream per LANE (many short
  *                                  streams) instead of 2-3 warps per stream (few long ones):
- *                                  0 = automatic (S >= 2048 streams), 1 = never, 2 = always */
+ *                                  0 = automatic (unbounded-index: from 2048 streams; bounded: from 8192), 1 = never,
+ *                                  2 = always */
 #define TFC_CFG_SM_BUDGET 1
 #define TFC_CFG_CODER_STREAMS_PER_CTA 2
 #define TFC_CFG_TILES_PER_CTA 3
