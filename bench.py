@@ -59,6 +59,12 @@ def parse_args():
   ap.add_argument("--depth", type=int, default=0,
                   help="batches in flight on separate CUDA streams (1: strictly serial steps; "
                        "0: 20, or fewer if 20 batches of activations would not fit in HBM)")
+  ap.add_argument("--back-lag", type=int, default=0,
+                  help="e2e leg: batches queued between a compress and the host's return for its "
+                       "strings (0: the batches in flight, at most 12)")
+  ap.add_argument("--host-slots", type=int, default=0,
+                  help="e2e leg: sets of pinned staging buffers (0: twice the batches in flight, "
+                       "at most 8 GB)")
   ap.add_argument("--tiles-per-cta", type=int, default=8,
                   help="transform kernels: tiles per CTA when depth > 1 (0: persistent grid)")
   ap.add_argument("--coder-pack", type=int, default=0,
@@ -303,7 +309,19 @@ def run_b200(args):
     # streams in flight / CTAs wanted: the coder is latency bound per stream, and 4 streams per
     # CTA is the measured optimum once there are more streams than ~4 per SM
     args.coder_pack = max(1, min(4, int(round(batch * args.depth / 150.0))))
-  pipe = model.pipeline(args.depth, args.tiles_per_cta, args.coder_pack)
+  if args.host_slots <= 0:
+    # e2e leg: twice as many sets of pinned staging buffers as batches in flight, so that neither
+    # host wait (strings of batch k, x_hat of the batch whose buffers are reused) comes before the
+    # GPU can have finished that work; at most 8 GB pinned per rank (a set is x_hat
+    # plus the string slabs at capacity, ~1.6 bytes per image byte).  Measured
+    # (profiles/r1l_e2e_host_waits.txt): C3 e2e 1189 MPix/s at depth + 1 sets and a lag of
+    # depth - 1, 1384 at lag 6, 1504 at 24 sets and lag 12; C2 1592 -> 1675.
+    args.host_slots = max(args.depth + 1,
+                          min(2 * args.depth, int(8e9 / (1.6 * 3 * pixels_per_step))))
+  if args.back_lag <= 0:
+    args.back_lag = max(1, min(args.depth, 12, args.host_slots // 2))
+  pipe = model.pipeline(args.depth, args.tiles_per_cta, args.coder_pack, args.back_lag,
+                        args.host_slots)
 
   with pipe:
     # every stream of the pipeline must have run once before the timed region: a stream's first
@@ -338,7 +356,7 @@ def run_b200(args):
       seen["strings"] = compressed.string.total_bytes + compressed.side_string.total_bytes
       seen["pixels"] += int(x_hat_u8.shape[0]) * int(x_hat_u8.shape[1]) * int(x_hat_u8.shape[2])
 
-    pipe.roundtrip_host([x_u8_host] * (args.depth + 1), on_result)
+    pipe.roundtrip_host([x_u8_host] * (pipe.host_slots), on_result)
     barrier()
     seen["pixels"] = 0
     t0 = time.perf_counter()
@@ -409,7 +427,7 @@ def run_b200(args):
                  "weights": "random-init seed 0", "l2": "inputs_exceed_l2 (%.0f MB images)"
                  % (x_dev.numel() * 4 / 1e6), "parallelism": "batch-sharded x%d" % world,
                  "conv_impl": args.conv_impl,
-                 "pipeline": {"batches_in_flight": args.depth,
+                 "pipeline": {"batches_in_flight": args.depth, "e2e_back_lag": pipe.back_lag, "e2e_host_slots": pipe.host_slots,
                               "tiles_per_cta": args.tiles_per_cta if args.depth > 1 else 0,
                               "coder_streams_per_cta": args.coder_pack if args.depth > 1 else 0,
                               "hbm_peak_allocated_gb": round(

@@ -149,10 +149,16 @@ class Pipeline(object):
   called batch by batch.
   """
 
-  def __init__(self, model, depth=3, tiles_per_cta=8, coder_streams_per_cta=4):
+  def __init__(self, model, depth=3, tiles_per_cta=8, coder_streams_per_cta=4, back_lag=None,
+               host_slots=None):
     from compression_b200 import _lib
     self.model = model
     self.depth = max(1, int(depth))
+    # roundtrip_host: how many batches later the host comes back for a batch's strings
+    # and how many sets of pinned staging buffers it cycles through
+    self.host_slots = max(self.depth + 1, int(host_slots)) if host_slots else self.depth + 1
+    self.back_lag = (min(self.host_slots - 1, max(1, int(back_lag))) if back_lag
+                     else max(1, self.host_slots // 2))
     self.streams = [torch.cuda.Stream(device=model.device) for _ in range(self.depth)]
     self._lib = _lib
     self.tiles_per_cta = int(tiles_per_cta) if self.depth > 1 else 0
@@ -206,8 +212,11 @@ class Pipeline(object):
 
   def roundtrip_host(self, batches_u8, on_result=None):
     """batches_u8: pinned host uint8 [B,H,W,3] tensors.  Per batch: image H2D, compress,
-    strings D2H, strings H2D, decompress, x_hat D2H.  The host only waits for batch k's
-    strings after it has queued the compress of the next depth-1 batches.
+    strings D2H, strings H2D, decompress, x_hat D2H.  The host waits twice per batch: for batch
+    k's strings after it has queued the compress of the next `back_lag` batches, and for its
+    x_hat when the slot is reused, host_slots - back_lag batches after the decompress was queued.
+    Both waits have to span several batch times or the host, not the GPU, sets the pace (a
+    decompress is one serial decode per image and takes longer than two batch times).
 
     Pinned staging buffers are allocated once per pipeline slot and reused (page-locking
     memory synchronises the device).  Results are delivered in order through
@@ -217,7 +226,7 @@ class Pipeline(object):
     out (strings as lists of bytes) and returned as a list."""
     from compression_b200.python.ops import range_coding_ops as rc
     model, dev = self.model, self.model.device
-    n, nslots = len(batches_u8), self.depth + 1
+    n, nslots = len(batches_u8), self.host_slots
     slots = getattr(self, "_slots", None)
     if slots is None or len(slots) != nslots:
       slots = self._slots = [dict() for _ in range(nslots)]
@@ -287,10 +296,10 @@ class Pipeline(object):
         self.d2h_bytes += out.numel()
 
     with rc.deferred_checks():
-      for k in range(n + self.depth - 1):
+      for k in range(n + self.back_lag):
         if k < n:
           issue_front(k)
-        j = k - (self.depth - 1)
+        j = k - self.back_lag
         if 0 <= j < n:
           issue_back(j)
       self._join(cur)
@@ -376,8 +385,9 @@ class Bmshj2018Model(object):
     return dict(x_hat=x_hat, y=y, z=z, sigma=sigma, y_hat=y_hat, y_likelihoods=y_lik,
                 z_likelihoods=z_lik, eval_bpp=float(bpp))
 
-  def pipeline(self, depth=3, tiles_per_cta=8, coder_streams_per_cta=4):
-    return Pipeline(self, depth, tiles_per_cta, coder_streams_per_cta)
+  def pipeline(self, depth=3, tiles_per_cta=8, coder_streams_per_cta=4, back_lag=None,
+               host_slots=None):
+    return Pipeline(self, depth, tiles_per_cta, coder_streams_per_cta, back_lag, host_slots)
 
   # ---- host-side strings --------------------------------------------------------------------
   @staticmethod

@@ -167,6 +167,30 @@ def test_pipeline_matches_batch_by_batch(setup, depth):
     assert torch.equal(xh, bmshj2018.quantize_image(model.decompress(ref)).cpu())
 
 
+@pytest.mark.parametrize("back_lag,host_slots", [(1, None), (3, None), (2, 7), (6, 7), (9, 10)])
+def test_pipeline_host_waits_do_not_change_results(setup, back_lag, host_slots):
+  """roundtrip_host's two host waits (back_lag batches after a compress for its strings;
+  host_slots - back_lag batches after a decompress for the slot's buffers) only move when the
+  host blocks: strings and pixels are those of the batch-by-batch calls whatever the schedule,
+  also when the lag exceeds the batches in flight and when slots are reused several times."""
+  from compression_b200.examples import bmshj2018
+  model, _, _ = setup
+  g = torch.Generator().manual_seed(23)
+  u8 = [torch.randint(0, 256, (2, 40, 56, 3), generator=g, dtype=torch.uint8).pin_memory()
+        for _ in range(17)]
+  with model.pipeline(depth=3, back_lag=back_lag, host_slots=host_slots) as pipe:
+    assert pipe.back_lag < pipe.host_slots
+    seen = []
+    pipe.roundtrip_host(u8, lambda k, c, xh: seen.append(
+        (k, list(c.string), list(c.side_string), xh.clone())))
+  assert [k for k, _, _, _ in seen] == list(range(len(u8)))
+  for k, string, side_string, xh in seen:
+    ref = model.compress(u8[k].cuda().float() / 255)
+    ref_host = model.to_host(ref)
+    assert string == ref_host.string and side_string == ref_host.side_string
+    assert torch.equal(xh, bmshj2018.quantize_image(model.decompress(ref)).cpu())
+
+
 def test_tfci_files_round_trip_one_image_each(setup, tmp_path):
   """every image leaves as a `.tfci` file in the reference's container
   (bmshj2018.py:339-347) and decodes from it (`:369-377`) to what the batch decode produces."""
