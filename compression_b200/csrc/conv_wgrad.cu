@@ -213,8 +213,13 @@ conv_wgrad_kernel(const WgradParams p) {
 }
 
 // bias gradient: column sums of a [pixels, channels] float32 tensor (channels % 4 == 0: one float4
-// per thread, 32 pixel rows per CTA pass, shared-memory tree over the rows, one atomic per
-// channel and CTA)
+// per thread, 32 pixel rows per CTA pass and four passes in flight per thread, shared-memory tree
+// over the rows, one atomic per channel quad and CTA).  All CTAs add into the same `channels`
+// floats — a handful of cache lines, where L2 retires about one atomic per clock — so the grid is
+// two CTAs per SM and the add is the 16-byte vector atomic when `out` is aligned for it: with
+// 8 CTAs per SM and scalar atomics the 150 K adds took ~28 us whatever the input size
+// (profiles/r1l_train_elementwise_full_summary.md).
+template <bool VEC_ATOMIC>
 __global__ void __launch_bounds__(256)
 column_sums_kernel(const float4* __restrict__ x, int64_t pixels, int cvec,
                    float* __restrict__ out) {
@@ -223,10 +228,25 @@ column_sums_kernel(const float4* __restrict__ x, int64_t pixels, int cvec,
   const int col = threadIdx.x % cvec, row = threadIdx.x / cvec;
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   if (row < rows) {
-    for (int64_t q = (int64_t)blockIdx.x * rows + row; q < pixels; q += (int64_t)gridDim.x * rows) {
+    const int64_t step = (int64_t)gridDim.x * rows;
+    int64_t q = (int64_t)blockIdx.x * rows + row;
+    float4 a1 = acc, a2 = acc, a3 = acc;
+    for (; q + 3 * step < pixels; q += 4 * step) {
+      const float4 v0 = __ldg(x + q * cvec + col);
+      const float4 v1 = __ldg(x + (q + step) * cvec + col);
+      const float4 v2 = __ldg(x + (q + 2 * step) * cvec + col);
+      const float4 v3 = __ldg(x + (q + 3 * step) * cvec + col);
+      acc.x += v0.x; acc.y += v0.y; acc.z += v0.z; acc.w += v0.w;
+      a1.x += v1.x; a1.y += v1.y; a1.z += v1.z; a1.w += v1.w;
+      a2.x += v2.x; a2.y += v2.y; a2.z += v2.z; a2.w += v2.w;
+      a3.x += v3.x; a3.y += v3.y; a3.z += v3.z; a3.w += v3.w;
+    }
+    for (; q < pixels; q += step) {
       const float4 v = __ldg(x + q * cvec + col);
       acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
     }
+    acc.x += a1.x + (a2.x + a3.x); acc.y += a1.y + (a2.y + a3.y);
+    acc.z += a1.z + (a2.z + a3.z); acc.w += a1.w + (a2.w + a3.w);
     part[row * cvec + col] = acc;
   }
   __syncthreads();
@@ -235,10 +255,14 @@ column_sums_kernel(const float4* __restrict__ x, int64_t pixels, int cvec,
       const float4 v = part[r * cvec + col];
       acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
     }
-    atomicAdd(out + 4 * col + 0, acc.x);
-    atomicAdd(out + 4 * col + 1, acc.y);
-    atomicAdd(out + 4 * col + 2, acc.z);
-    atomicAdd(out + 4 * col + 3, acc.w);
+    if (VEC_ATOMIC) {
+      atomicAdd(reinterpret_cast<float4*>(out) + col, acc);
+    } else {
+      atomicAdd(out + 4 * col + 0, acc.x);
+      atomicAdd(out + 4 * col + 1, acc.y);
+      atomicAdd(out + 4 * col + 2, acc.z);
+      atomicAdd(out + 4 * col + 3, acc.w);
+    }
   }
 }
 
@@ -255,8 +279,15 @@ column_sums_scalar_kernel(const float* __restrict__ x, int64_t total, int channe
   const int64_t stride = (int64_t)gridDim.x * 256 / channels * channels;
   const int64_t i0 = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (i0 < stride) {
-    float acc = 0.f;
-    for (int64_t i = i0; i < total; i += stride) acc += x[i];
+    float acc = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;      // four loads in flight per thread
+    int64_t i = i0;
+    for (; i + 3 * stride < total; i += 4 * stride) {
+      const float v0 = __ldg(x + i), v1 = __ldg(x + i + stride), v2 = __ldg(x + i + 2 * stride),
+                  v3 = __ldg(x + i + 3 * stride);
+      acc += v0; a1 += v1; a2 += v2; a3 += v3;
+    }
+    for (; i < total; i += stride) acc += __ldg(x + i);
+    acc += a1 + (a2 + a3);
     atomicAdd(part + (int)(i0 % channels), acc);
   }
   __syncthreads();
@@ -350,9 +381,14 @@ extern "C" int tfc_column_sums(const float* d_x, int64_t pixels, int32_t channel
   if ((channels & 3) == 0 && channels <= 1024 && (reinterpret_cast<uintptr_t>(d_x) & 15) == 0) {
     const int cvec = channels / 4;
     const int rows = std::max(1, 256 / cvec);
-    const int grid = (int)std::min<int64_t>((pixels + rows - 1) / rows, (int64_t)sms * 8);
-    column_sums_kernel<<<grid, 256, (size_t)rows * cvec * sizeof(float4), st>>>(
-        reinterpret_cast<const float4*>(d_x), pixels, cvec, d_out);
+    const int grid = (int)std::min<int64_t>((pixels + rows - 1) / rows, (int64_t)sms * 2);
+    const size_t smem = (size_t)rows * cvec * sizeof(float4);
+    if ((reinterpret_cast<uintptr_t>(d_out) & 15) == 0)
+      column_sums_kernel<true><<<grid, 256, smem, st>>>(reinterpret_cast<const float4*>(d_x),
+                                                        pixels, cvec, d_out);
+    else
+      column_sums_kernel<false><<<grid, 256, smem, st>>>(reinterpret_cast<const float4*>(d_x),
+                                                         pixels, cvec, d_out);
   } else {
     if (channels > 256)
       return tfc::fail(TFC_ERR_UNIMPLEMENTED,

@@ -300,3 +300,29 @@ def test_bmshj2018_training_step_gradients_and_descent(tfc):
   c = model.compress(x)
   x_hat = model.decompress(c)
   assert tuple(x_hat.shape) == (2, 64, 64, 3) and bool(torch.isfinite(x_hat).all())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pixels,channels", [(1, 4), (37, 128), (64 * 128 * 128 + 5, 128),
+                                             (64 * 64 * 64, 192), (100003, 3), (4099, 5),
+                                             (9 * 296 * 2 + 1, 1024)])
+@pytest.mark.parametrize("misalign", [0, 1])
+def test_column_sums_match_torch(pixels, channels, misalign):
+  """tfc_column_sums (the bias gradients of the training step): float4 kernel with four passes
+  in flight and the 16-byte vector atomic, its scalar-atomic variant when the destination is
+  only 4-byte aligned (a slot inside a flat gradient bucket), and the scalar kernel for odd
+  channel counts, against a float64 sum."""
+  import ctypes
+  from compression_b200 import _lib
+  dev = torch.device("cuda", 0)
+  g = torch.Generator(device=dev).manual_seed(pixels % 1000 + channels)
+  x = torch.randn((pixels, channels), generator=g, device=dev, dtype=torch.float32)
+  buf = torch.full((channels + 4,), 7.0, device=dev, dtype=torch.float32)
+  out = buf[misalign:misalign + channels]
+  _lib.check(_lib.lib().tfc_column_sums(
+      _lib.ptr(x), ctypes.c_int64(pixels), ctypes.c_int32(channels),
+      ctypes.c_void_p(buf.data_ptr() + 4 * misalign), _lib.stream_ptr(dev)))
+  want = x.double().sum(0)
+  tol = 1e-6 * float(x.abs().double().sum(0).max()) + 1e-6
+  assert float((out.double() - want).abs().max()) <= tol
+  assert float(buf[misalign + channels]) == 7.0 and (misalign == 0 or float(buf[0]) == 7.0)
