@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """Headline benchmark: bmshj2018-hyperprior encode+decode throughput (MPix/s) on B200.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c2|tiny]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c2|c3|tiny]
+                  [--blocks parity,c3,c4,c5,c1 | none]
 
 A step = compress + decompress of one batch of synthetic images (BASELINE.json configs[1]:
 192 filters, 768x512, batch 64 per GPU; random-init weights, seed 0).  N > 1 is launched by
@@ -11,12 +12,23 @@ collective on the data path), so scaling is weak.  One JSON line is printed by r
   value   device-resident: images already in HBM, strings stay in HBM, x_hat stays in HBM
   e2e     through the public API with HOST buffers: pinned uint8 images -> H2D -> compress ->
           strings D2H -> strings H2D -> decompress -> uint8 x_hat D2H, all inside the timing
-  roofline      the conv kernels (dominant): algorithmic FLOPs / CUDA-event time vs the
-                measured bf16 tensor peak (MEASURED_PEAKS.json)
+  roofline      the conv kernels (dominant): algorithmic FLOPs / CUDA-event time.  `frac` =
+                `frac_burst`: the 17 conv launches of one batch alone on the GPU against the
+                measured BURST bf16 peak; `frac_step`: the same FLOPs over the whole timed step
+                (ms_per_step) against the measured SUSTAINED peak (MEASURED_PEAKS.json)
+  parity        after the timed region: images 0, 1, B/2, B-1 of the benched batch — the CPU
+                checker (oracle/) must encode the GPU's symbols to the GPU's bytes and decode
+                the GPU's bytes to the GPU's symbols, and the last image coded alone must give
+                the bytes it gave inside the batch; the run fails otherwise
   cpu_baseline  the same pipeline on the host cores (reference range coder from oracle/_ref
                 when built, torch-CPU float32 restatement of the transforms), bounded sample
+  c1 c3 c4 c5   the other BASELINE.json configs, one block each in the same line: bls2017 on
+                the host cores next to the GPU; 1920x1080 batch 256 split over the N ranks
+                (strong scaling); the coder / pmf_to_quantized_cdf sweep; the bls2017 training
+                step with its NCCL all-reduce at the N the run was launched with
 """
 import argparse
+import glob
 import json
 import os
 import subprocess
@@ -28,6 +40,10 @@ import numpy as np
 
 # before the CUDA context exists (see compression_b200/__init__.py): one hardware queue per stream
 os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+# BASELINE.json: "gradient allreduce uses NCCL over NVLink only" — no InfiniBand / socket transport
+os.environ.setdefault("NCCL_P2P_LEVEL", "NVL")
+os.environ.setdefault("NCCL_IB_DISABLE", "1")
+os.environ.setdefault("NCCL_NET_DISABLE", "1")
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -38,10 +54,8 @@ WORKLOADS = {
     "c3": (1080, 1920, 32, 192),
     "tiny": (128, 192, 4, 192),
 }
-# DRAM traffic (read + write) of the conv launches of one step as ncu measures it: the sum over
-# the 14 layers in profiles/r1e_conv_full_summary.md (batch 64, 768x512); other workloads: null
-NCU_TRAFFIC_BYTES_PER_STEP = {"c2": 15.67e9}
-FLOP_PER_IMAGE_C2 = 149.31e9   # encode 75.61 + decode 73.70 GFLOP per 768x512 image
+ALL_BLOCKS = ("parity", "c3", "c4", "c5", "c1")
+METRIC = "MPix/s encode+decode, bmshj2018 hyperprior"
 
 
 def parse_args():
@@ -51,6 +65,9 @@ def parse_args():
   ap.add_argument("--warmup", type=int, default=3)
   ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
   ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+  ap.add_argument("--blocks", default="",
+                  help="comma list of extra blocks (%s), 'none', or empty for the default: all "
+                       "of them on the c2 workload" % ",".join(ALL_BLOCKS))
   ap.add_argument("--conv-impl", type=int, default=0, help="0 auto, 1 CUDA-core, 2 tcgen05")
   ap.add_argument("--cpu-sample-images", type=int, default=0,
                   help="images per CPU step (0: one per host thread, at most the batch)")
@@ -73,6 +90,14 @@ def parse_args():
   return ap.parse_args()
 
 
+def wanted_blocks(args):
+  if args.blocks == "none":
+    return ()
+  if args.blocks:
+    return tuple(b for b in args.blocks.split(",") if b in ALL_BLOCKS)
+  return ALL_BLOCKS if args.workload == "c2" else ("parity",)
+
+
 def measured_peaks():
   path = os.path.join(ROOT, "MEASURED_PEAKS.json")
   if os.path.exists(path):
@@ -83,6 +108,22 @@ def measured_peaks():
                 source="measured")
   return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0,
               source="fallback")
+
+
+def ncu_conv_traffic(workload):
+  """DRAM bytes (read + write) of the conv launches of one step as ncu measured them on the build
+  that is being benched: the newest committed profiles/r*_conv_traffic.json whose `workload`
+  matches.  (value, file) or (None, None): bench.py never invents this number."""
+  best = (None, None)
+  for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_conv_traffic.json"))):
+    try:
+      with open(path) as f:
+        rec = json.load(f)
+    except (OSError, ValueError):
+      continue
+    if rec.get("workload") == workload and rec.get("dram_bytes_per_step"):
+      best = (float(rec["dram_bytes_per_step"]), os.path.relpath(path, ROOT))
+  return best
 
 
 # ---- algorithmic work -------------------------------------------------------------------------
@@ -109,7 +150,7 @@ def conv_flops(model, h, w):
   nf = model.num_filters
   hy, wy = run(model.analysis_transform, "A", h, w, 3)
   hz, wz = run(model.hyper_analysis_transform, "HA", hy, wy, nf)
-  hs = run(model.hyper_synthesis_transform, "HS", hz, wz, nf)
+  run(model.hyper_synthesis_transform, "HS", hz, wz, nf)
   run(model.synthesis_transform, "S", hy, wy, nf)
   enc = sum(v for k, v in total.items() if k[0] in "AH")     # A + HA + HS
   dec = sum(v for k, v in total.items() if k.startswith("HS") or k.startswith("S"))
@@ -248,7 +289,7 @@ def run_reference(args):
   mpix, ms, kind, cores = cpu_arm(h, w, images, steps, warmup)
   sample = "%d of %d images of %dx%d per step, all %d host threads" % (images, batch, w, h, cores)
   line = {
-      "impl": "reference", "metric": "MPix/s encode+decode, bmshj2018 hyperprior",
+      "impl": "reference", "metric": METRIC,
       "value": mpix, "unit": "MPix/s", "n_gpus": args.gpus, "steps": steps,
       "warmup": warmup, "ms_per_step": ms, "higher_is_better": True,
       "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -265,23 +306,373 @@ def run_reference(args):
   print(json.dumps(line))
 
 
+# ---- parity of the benched batch (after the timed region) -----------------------------------------
+def parity_block(model, x_dev, tag):
+  """Images 0, 1, B/2, B-1 of `x_dev`: the CPU checker encodes the GPU's symbols + indexes to the
+  GPU's bytes and decodes the GPU's bytes back to them (y and z), the GPU decoder returns the
+  same symbols, and the last image coded alone gives the bytes it gave inside the batch.
+  Raises on any mismatch."""
+  import torch
+  from oracle import oracle_lib
+  coder = oracle_lib.load("best")
+  t = model.export_tables()
+  nf = model.num_filters
+  b = int(x_dev.shape[0])
+  picks = sorted(set([0, min(1, b - 1), b // 2, b - 1]))
+  c = model.compress(x_dev)
+  host = model.to_host(c)
+  y, z, sigma = model.analyse(x_dev)
+  gc = model._conditional(sigma)
+  y_sym, y_idx, _ = gc._symbols_and_indexes(y.contiguous())
+  z_sym = model.entropy_bottleneck._quantize_symbols(z)
+  z_idx = np.broadcast_to(np.arange(nf, dtype=np.int32), tuple(z_sym.shape[1:])).copy()
+  # the GPU decoder (which re-derives sigma from the side string) returns the coded symbols
+  z_hat = model.entropy_bottleneck.decompress_device(c.side_string, tuple(c.z_shape) + (nf,), nf,
+                                                     torch.bfloat16)
+  sigma2 = model.hyper_synthesis_transform(z_hat)[:, :c.y_shape[0], :c.y_shape[1], :].contiguous()
+  y_hat = model._conditional(sigma2).decompress_device(c.string)
+  gpu_roundtrip = bool(torch.equal(y_hat.to(torch.int32), y_sym)) and bool(torch.equal(sigma2, sigma))
+  strings_equal = symbols_equal = True
+  for i in picks:
+    ys, yi = y_sym[i].cpu().numpy(), y_idx[i].cpu().numpy()
+    zs = z_sym[i].cpu().numpy()
+    strings_equal &= host.string[i] == coder.ui_encode(ys, yi, t["gc_cdf"], t["gc_len"],
+                                                       t["gc_off"], 16, 4)
+    strings_equal &= host.side_string[i] == coder.ui_encode(zs, z_idx, t["eb_cdf"], t["eb_len"],
+                                                            t["eb_off"], 16, 4)
+    symbols_equal &= np.array_equal(
+        coder.ui_decode(host.string[i], yi, t["gc_cdf"], t["gc_len"], t["gc_off"], 16, 4), ys)
+    symbols_equal &= np.array_equal(
+        coder.ui_decode(host.side_string[i], z_idx, t["eb_cdf"], t["eb_len"], t["eb_off"], 16, 4),
+        zs)
+  alone = model.to_host(model.compress(x_dev[b - 1:].contiguous()))
+  alone_equal = alone.string[0] == host.string[b - 1] and \
+      alone.side_string[0] == host.side_string[b - 1]
+  out = {"config": tag, "images_checked": len(picks), "images": picks,
+         "strings_equal": bool(strings_equal), "symbols_equal": bool(symbols_equal),
+         "gpu_decoder_returns_symbols": gpu_roundtrip,
+         "last_image_alone_equals_in_batch": bool(alone_equal),
+         "symbols_per_image": int(y_sym[0].numel() + z_sym[0].numel()),
+         "checker": coder.kind}
+  if not (strings_equal and symbols_equal and gpu_roundtrip and alone_equal):
+    raise SystemExit("PARITY FAILURE: %s" % json.dumps(out))
+  return out
+
+
+# ---- BASELINE config 3: 1920x1080, batch 256 split over the ranks ---------------------------------
+def c3_block(args, model, world, rank, dev, barrier, allmax):
+  import torch
+  h, w, total = 1080, 1920, 256
+  share = total // world
+  micro = max(4, min(16, share // 8))       # images per micro-batch: 8 micro-batches per pass
+  nmicro = share // micro
+  passes = 2 * world                        # every rank codes 512 images in the timed region
+  depth = 8
+  g = torch.Generator().manual_seed(3000 + rank)
+  xs_u8 = [torch.randint(0, 256, (micro, h, w, 3), generator=g, dtype=torch.uint8).pin_memory()
+           for _ in range(2)]
+  xs_dev = [(x.to(dev).float() / 255).contiguous() for x in xs_u8]
+  pack = max(1, min(4, int(round(micro * depth / 150.0))))
+  pipe = model.pipeline(depth, args.tiles_per_cta, pack, back_lag=6, host_slots=12)
+  out = {"workload": "bmshj2018-192 encode+decode 1920x1080, batch 256 split over %d GPU(s)" % world,
+         "images_per_gpu": share, "micro_batch": micro, "passes_timed": passes,
+         "batches_in_flight": depth, "scaling": "strong"}
+  with pipe:
+    n = nmicro * passes
+    seq = [xs_dev[k % 2] for k in range(n)]
+    pipe.roundtrip_device(seq[:depth + 1])
+    barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    pipe.roundtrip_device(seq)
+    b.record()
+    barrier()
+    ms = allmax(a.elapsed_time(b))
+    pix = world * n * micro * h * w
+    out["value"] = pix / (ms * 1e-3) / 1e6
+    out["ms_per_256_images"] = ms / passes
+    seen = {"pixels": 0}
+
+    def on_result(k, c, xh):
+      seen["pixels"] += int(xh.shape[0]) * int(xh.shape[1]) * int(xh.shape[2])
+
+    seq8 = [xs_u8[k % 2] for k in range(n)]
+    pipe.roundtrip_host(seq8[:pipe.host_slots], on_result)
+    barrier()
+    seen["pixels"] = 0
+    t0 = time.perf_counter()
+    pipe.roundtrip_host(seq8, on_result)
+    torch.cuda.synchronize()
+    sec = allmax(time.perf_counter() - t0)
+    assert seen["pixels"] == n * micro * h * w
+    out["e2e"] = {"value": pix / sec / 1e6, "unit": "MPix/s",
+                  "h2d_bytes_per_micro_batch": int(pipe.h2d_bytes),
+                  "d2h_bytes_per_micro_batch": int(pipe.d2h_bytes)}
+  out["unit"] = "MPix/s"
+  if rank == 0:
+    out["parity"] = parity_block(model, xs_dev[0][:4].contiguous(), "c3 (4 of a micro-batch)")
+  barrier()
+  return out
+
+
+# ---- BASELINE config 5: bls2017 training step + NCCL all-reduce -----------------------------------
+def c5_block(args, world, rank, dev, barrier, allmax):
+  import torch
+  import torch.distributed as dist
+  from compression_b200.examples import bls2017
+  batch, patch, steps, warmup = 64, 256, 10, 3
+  model = bls2017.Bls2017Model(128, dev, seed=0)          # same seed: identical replicas
+  trainer = bls2017.Bls2017Trainer(model, lmbda=0.01)
+  g = torch.Generator(device=dev).manual_seed(100 + rank)  # per-rank crops and noise
+  torch.manual_seed(200 + rank)
+  x = torch.rand((batch, patch, patch, 3), generator=g, device=dev)
+  for _ in range(warmup):
+    stats = trainer.step(x, graph=True)
+  barrier()
+  a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  a.record()
+  for _ in range(steps):
+    stats = trainer.step(x, graph=True)
+  b.record()
+  torch.cuda.synchronize()
+  ms = allmax(a.elapsed_time(b) / steps)
+  # the exchange step alone: both flat buckets, as the step issues them
+  ar_ms = 0.0
+  if world > 1:
+    barrier()
+    a.record()
+    for _ in range(20):
+      trainer.main.all_reduce()
+      trainer.aux.all_reduce()
+    b.record()
+    torch.cuda.synchronize()
+    ar_ms = allmax(a.elapsed_time(b) / 20)
+  check = trainer.main.param.double().sum().reshape(1)
+  identical = True
+  if world > 1:
+    lo, hi = check.clone(), check.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    identical = float(hi - lo) == 0.0
+  flop = 8.83e9 * batch                                    # SURVEY §8a: fwd + bwd per image
+  out = {"workload": "bls2017-128 training step, 256x256 crops, batch 64 per GPU, NCCL all-reduce",
+         "n_gpus": world, "ms_per_step": ms, "allreduce_ms": ar_ms,
+         "allreduce_bytes": int(4 * (trainer.main.param.numel() + trainer.aux.param.numel())),
+         "images_per_s": world * batch / ms * 1e3, "tflops_per_gpu": flop / ms / 1e9,
+         "parameters": trainer.num_parameters, "replicas_identical": bool(identical),
+         "loss": stats["loss"], "bpp": stats["bpp"], "mse": stats["mse"], "cuda_graph": True,
+         "nccl_env": {k: os.environ.get(k) for k in ("NCCL_P2P_LEVEL", "NCCL_IB_DISABLE",
+                                                     "NCCL_NET_DISABLE")}}
+  if not identical:
+    raise SystemExit("c5: replicas diverged: %s" % json.dumps(out))
+  del trainer, model
+  torch.cuda.empty_cache()
+  return out
+
+
+# ---- BASELINE config 4: coder + pmf_to_quantized_cdf sweep ----------------------------------------
+def c4_block(dev):
+  import torch
+  from compression_b200.python.layers import entropy_models
+  from compression_b200.python.ops import range_coding_ops as rc
+  from oracle import oracle_lib
+  coder = oracle_lib.load("best")
+  threads = host_threads()
+
+  def timeit(fn, reps=3):
+    fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+      fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps
+
+  table = np.exp(np.linspace(np.log(0.11), np.log(256), 64))
+  gc = entropy_models.GaussianConditional(None, table)
+  gc.build_tables(dev)
+  cdf, size, off = gc._quantized_cdf, gc._cdf_length, gc._offset
+  c_h, s_h, o_h = cdf.cpu().numpy(), size.cpu().numpy(), off.cpu().numpy()
+  table_d = torch.as_tensor(table, dtype=torch.float32, device=dev)
+  k = np.arange(64, dtype=np.float64) - 31.5
+  pmf64 = np.exp(-0.5 * (k / 6.0) ** 2)
+  pmf64 = (pmf64 / pmf64.sum()).astype(np.float32)
+  cdf64 = rc.pmf_to_quantized_cdf(torch.as_tensor(pmf64, device=dev), 16)
+  cdf64_h = cdf64.cpu().numpy()
+  n, checked = 4096, 0
+  rows_out = {"unbounded": [], "bounded": [], "pmf": []}
+  for S in (1024, 4096, 16384, 65536):
+    g = torch.Generator(device=dev).manual_seed(1)
+    pick = np.linspace(0, S - 1, 16).astype(np.int64)
+    pick_d = torch.as_tensor(pick, device=dev)
+    total = S * n
+    idx = torch.randint(0, 64, (S, n), generator=g, dtype=torch.int32, device=dev)
+    sym = torch.floor(torch.randn((S, n), generator=g, device=dev) * table_d[idx.long()] + .5)
+    sym = sym.to(torch.int32)
+    out, nbytes = rc.unbounded_index_range_encode_batch(sym, idx, cdf, size, off, 16, 4, 0)
+    dec = rc.unbounded_index_range_decode_batch(out, nbytes, idx, cdf, size, off, 16, 4, 0)
+    assert torch.equal(dec, sym), "c4: unbounded round trip failed at %d streams" % S
+    del dec
+    sym_h, idx_h = sym[pick_d].cpu().numpy(), idx[pick_d].cpu().numpy()
+    got = rc.strings_to_host(out[pick_d], nbytes[pick_d])
+    for i in range(len(pick)):
+      want = coder.ui_encode(sym_h[i], idx_h[i], c_h, s_h, o_h, 16, 4)
+      assert got[i] == want, "c4: stream %d of %d differs from the %s coder" % (pick[i], S, coder.kind)
+    checked += len(pick)
+    cap = out.shape[1]
+    enc_ms = timeit(lambda: rc.unbounded_index_range_encode_batch(
+        sym, idx, cdf, size, off, 16, 4, 0, cap=cap))
+    dec_ms = timeit(lambda: rc.unbounded_index_range_decode_batch(
+        out, nbytes, idx, cdf, size, off, 16, 4, 0, check=False))
+    rows_out["unbounded"].append({"streams": S, "encode_gsym_s": total / enc_ms / 1e6,
+                                  "decode_gsym_s": total / dec_ms / 1e6,
+                                  "encode_ms": enc_ms, "decode_ms": dec_ms})
+    del idx, sym, out, nbytes
+    u = torch.randn((S, n), generator=g, device=dev) * 6.0 + 31.5
+    data = torch.clamp(torch.floor(u + .5), 0, 63).to(torch.int16)
+    del u
+    out, nbytes = rc.range_encode_batch(data, cdf64.reshape(1, 65), 16, debug_level=0)
+    dec = rc.range_decode_batch(out, nbytes, (n,), cdf64.reshape(1, 65), 16, debug_level=0)
+    assert torch.equal(dec, data), "c4: bounded round trip failed at %d streams" % S
+    del dec
+    data_h = data[pick_d].cpu().numpy()
+    got = rc.strings_to_host(out[pick_d], nbytes[pick_d])
+    for i in range(len(pick)):
+      assert got[i] == coder.rc_encode(data_h[i], cdf64_h.reshape(1, 65), 16), \
+          "c4: bounded stream %d of %d differs from the %s coder" % (pick[i], S, coder.kind)
+    checked += len(pick)
+    cap = out.shape[1]
+    enc_ms = timeit(lambda: rc.range_encode_batch(data, cdf64.reshape(1, 65), 16, debug_level=0,
+                                                  cap=cap))
+    dec_ms = timeit(lambda: rc.range_decode_batch(out, nbytes, (n,), cdf64.reshape(1, 65), 16,
+                                                  debug_level=0))
+    rows_out["bounded"].append({"streams": S, "encode_gsym_s": total / enc_ms / 1e6,
+                                "decode_gsym_s": total / dec_ms / 1e6,
+                                "encode_ms": enc_ms, "decode_ms": dec_ms})
+    del data, out, nbytes
+  rows_checked = 0
+  S = 65536
+  g = torch.Generator(device=dev).manual_seed(2)
+  for pn in (22, 64, 256, 1480):
+    rec = {"rows": S, "n": pn}
+    for kind in ("uniform", "gaussian"):
+      if kind == "uniform":
+        p = torch.rand((S, pn), generator=g, device=dev) + 1e-6
+      else:
+        sig = torch.rand((S, 1), generator=g, device=dev) * (pn / 6.0) + 0.2
+        kk = torch.arange(pn, device=dev, dtype=torch.float32) - (pn - 1) / 2
+        p = torch.exp(-0.5 * (kk / sig) ** 2)
+      p = (p / p.sum(-1, keepdim=True)).contiguous()
+      got = rc.pmf_to_quantized_cdf(p, 16)
+      rows = np.linspace(0, S - 1, 32).astype(np.int64)
+      rows_d = torch.as_tensor(rows, device=dev)
+      want = coder.pmf_to_cdf(p[rows_d].cpu().numpy(), 16, threads=threads)
+      assert np.array_equal(got[rows_d].cpu().numpy(), want), \
+          "c4: pmf_to_quantized_cdf differs (%s, n=%d)" % (kind, pn)
+      rows_checked += len(rows)
+      ms = timeit(lambda: rc.pmf_to_quantized_cdf(p, 16), 2)
+      rec["%s_ms" % kind] = ms
+      rec["%s_mrows_s" % kind] = S / ms / 1e3
+      del p, got
+    rows_out["pmf"].append(rec)
+  torch.cuda.empty_cache()
+  return {"workload": "range coder sweep: S streams x 4096 symbols, precision 16, overflow_width 4, "
+                      "64-row Gaussian table (unbounded) / m=64 shared CDF (bounded); "
+                      "pmf_to_quantized_cdf on 65536 rows x n",
+          "unbounded_index": rows_out["unbounded"], "bounded": rows_out["bounded"],
+          "pmf_to_quantized_cdf": rows_out["pmf"], "bit_exact_streams_checked": checked,
+          "bit_exact_rows_checked": rows_checked, "checker": coder.kind}
+
+
+# ---- BASELINE config 1: bls2017 compress/decompress of [8,256,256,3] on the host cores ------------
+def c1_block(dev):
+  import torch
+  from compression_b200.examples import bls2017
+  from oracle import cpu_codec, oracle_lib
+  coder = oracle_lib.load("best")
+  threads = host_threads()
+  model = bls2017.Bls2017Model(128, dev, seed=0)
+  cpu = cpu_codec.CpuBls2017(model.export_weights(), coder, threads, tables=model.export_tables())
+  g = torch.Generator().manual_seed(8)
+  x = torch.rand((8, 256, 256, 3), generator=g, dtype=torch.float32)
+  xn = x.numpy()
+  times = []
+  for it in range(4):
+    t0 = time.perf_counter()
+    c = cpu.compress(xn)
+    x_hat_cpu, y_sym_cpu = cpu.decompress(c)
+    if it:
+      times.append(time.perf_counter() - t0)
+  cpu_ms = float(np.mean(times)) * 1e3
+  xd = x.to(dev)
+  model.decompress(model.compress(xd))
+  torch.cuda.synchronize()
+  a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  a.record()
+  for _ in range(10):
+    cg = model.compress(xd)
+    x_hat = model.decompress(cg)
+  b.record()
+  torch.cuda.synchronize()
+  gpu_ms = a.elapsed_time(b) / 10
+  # the GPU's strings are the CPU coder's strings of the GPU's symbols, and decode on the CPU
+  host = model.to_host(cg)
+  eb = model.entropy_bottleneck
+  sym = eb._quantize_symbols(model.analysis_transform(xd)).cpu().numpy()
+  idx = np.broadcast_to(np.arange(128, dtype=np.int32), sym.shape[1:]).copy()
+  t = model.export_tables()
+  ok = all(host.string[i] == coder.ui_encode(sym[i], idx, t["eb_cdf"], t["eb_len"], t["eb_off"],
+                                             16, 4) for i in range(8))
+  agree = float(np.mean(sym == c["y_sym"]))
+  if not ok:
+    raise SystemExit("c1: GPU strings differ from the CPU coder's")
+  pix = 8 * 256 * 256
+  out = {"workload": "bls2017-128 compress+decompress of [8,256,256,3] (BASELINE configs[0])",
+         "cpu": {"ms": cpu_ms, "mpix_s": pix / cpu_ms / 1e3, "cores": threads,
+                 "kind": "torch-CPU f32 transforms + %s range coder" % coder.kind},
+         "gpu": {"ms": gpu_ms, "mpix_s": pix / gpu_ms / 1e3, "note": "one batch at a time, "
+                 "device-resident, launch-latency bound at this size"},
+         "strings_equal_cpu_coder": bool(ok),
+         "symbols_agree_with_f32_cpu_transforms": agree}
+  del model
+  torch.cuda.empty_cache()
+  return out
+
+
+def pin_to_cores(local, world):
+  """One contiguous slice of the host cores per rank: the ranks' issue threads and CUDA worker
+  threads stop migrating over each other's cores."""
+  try:
+    cores = sorted(os.sched_getaffinity(0))
+    per = len(cores) // max(1, world)
+    if world > 1 and per >= 2:
+      os.sched_setaffinity(0, set(cores[local * per:(local + 1) * per]))
+      return per
+  except (AttributeError, OSError):
+    pass
+  return None
+
+
 # ---- B200 arm ----------------------------------------------------------------------------------------
 def run_b200(args):
+  world = int(os.environ.get("WORLD_SIZE", "1"))
+  rank = int(os.environ.get("RANK", "0"))
+  local = int(os.environ.get("LOCAL_RANK", "0"))
+  pinned_cores = pin_to_cores(local, world)
   import torch
   import torch.distributed as dist
   import compression_b200 as tfc
   from compression_b200.examples import bmshj2018
-  from compression_b200.python.ops import range_coding_ops as rc
 
-  world = int(os.environ.get("WORLD_SIZE", "1"))
-  rank = int(os.environ.get("RANK", "0"))
-  local = int(os.environ.get("LOCAL_RANK", "0"))
   if not torch.cuda.is_available():
     raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference")
   torch.cuda.set_device(local)
   dev = torch.device("cuda", local)
   if world > 1:
     dist.init_process_group("nccl", device_id=dev)
+  blocks = wanted_blocks(args)
   h, w, batch, nf = WORKLOADS[args.workload]
   model = bmshj2018.Bmshj2018Model(nf, dev, seed=0, impl=args.conv_impl)
   g = torch.Generator().manual_seed(1000 + rank)
@@ -295,15 +686,17 @@ def run_b200(args):
       dist.barrier()
     torch.cuda.synchronize()
 
+  def allmax(v):
+    t = torch.tensor([float(v)], device=dev, dtype=torch.float64)
+    if world > 1:
+      dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
   pixels_per_step = batch * h * w
   if args.depth <= 0:
     # ~230 bytes of activations per input pixel stay reserved per batch in flight (measured:
     # 15.2 GB for 32 x 1080p, 5.8 GB for 64 x 768x512); keep the pipeline inside 3/4 of HBM
     total_mem = torch.cuda.get_device_properties(dev).total_memory
-    # measured (profiles/r1h_pipeline_sweep.txt): C2 device 1632 / e2e 1471 MPix/s at 12 batches in
-    # flight, 1738 / 1569 at 16, 1731 / 1640 at 20, 1734 / 1621 at 24
-    # (C3 ran at 12 batches in flight, 1299 device / 1196 e2e MPix/s, which 230 B/pixel would put at
-    # 183 GB: the figure is an upper bound, 200 B/pixel admits that depth)
     args.depth = max(1, min(20, int(0.85 * total_mem / (200.0 * pixels_per_step))))
   if args.coder_pack <= 0:
     # streams in flight / CTAs wanted: the coder is latency bound per stream, and 4 streams per
@@ -312,10 +705,7 @@ def run_b200(args):
   if args.host_slots <= 0:
     # e2e leg: twice as many sets of pinned staging buffers as batches in flight, so that neither
     # host wait (strings of batch k, x_hat of the batch whose buffers are reused) comes before the
-    # GPU can have finished that work; at most 8 GB pinned per rank (a set is x_hat
-    # plus the string slabs at capacity, ~1.6 bytes per image byte).  Measured
-    # (profiles/r1l_e2e_host_waits.txt): C3 e2e 1189 MPix/s at depth + 1 sets and a lag of
-    # depth - 1, 1384 at lag 6, 1504 at 24 sets and lag 12; C2 1592 -> 1675.
+    # GPU can have finished that work; at most 8 GB pinned per rank
     args.host_slots = max(args.depth + 1,
                           min(2 * args.depth, int(8e9 / (1.6 * 3 * pixels_per_step))))
   if args.back_lag <= 0:
@@ -343,11 +733,8 @@ def run_b200(args):
     timer.on = False
     launches = tfc.launch_count() - launches0
     clk = clocks.stop() if rank == 0 else None
-    ms = torch.tensor([start.elapsed_time(stop)], device=dev)
     conv_ms = timer.total_ms()
-    if world > 1:
-      dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms_per_step = float(ms.item()) / args.steps
+    ms_per_step = allmax(start.elapsed_time(stop)) / args.steps
 
     # e2e: same metric through host buffers (H2D image, D2H strings, H2D strings, D2H x_hat)
     seen = {"strings": 0, "pixels": 0}
@@ -362,16 +749,12 @@ def run_b200(args):
     t0 = time.perf_counter()
     pipe.roundtrip_host([x_u8_host] * args.steps, on_result)
     torch.cuda.synchronize()
-    e2e_s = torch.tensor([time.perf_counter() - t0], device=dev)
+    e2e_ms = allmax(time.perf_counter() - t0) * 1e3 / args.steps
     assert seen["pixels"] == args.steps * pixels_per_step, "e2e: not every batch came back"
     string_bytes = seen["strings"]
-    if world > 1:
-      dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_ms = float(e2e_s.item()) * 1e3 / args.steps
     h2d_bytes, d2h_bytes = int(pipe.h2d_bytes), int(pipe.d2h_bytes)
-    if world > 1:
-      dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_ms = float(e2e_s.item()) * 1e3 / args.steps
+    host_busy_ms = pipe.host_busy_s * 1e3 / args.steps
+    host_wait_ms = pipe.host_wait_s * 1e3 / args.steps
 
   # the conv kernels alone, one batch, nothing else on the GPU (explains the roofline figure
   # measured under concurrency above)
@@ -399,10 +782,25 @@ def run_b200(args):
   torch.cuda.synchronize()
   y_symbols = int(y[0].numel())
   coder_ms = (ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]))
-  del y, z, sigma, string
+  del y, z, sigma, string, gc
 
+  extra = {}
+  if "parity" in blocks:
+    extra["parity"] = parity_block(model, x_dev, args.workload) if rank == 0 else None
+    barrier()
+  if "c3" in blocks:
+    extra["c3"] = c3_block(args, model, world, rank, dev, barrier, allmax)
+  torch.cuda.empty_cache()
+  if "c5" in blocks:
+    extra["c5"] = c5_block(args, world, rank, dev, barrier, allmax)
+  if rank == 0:
+    if "c4" in blocks:
+      extra["c4"] = c4_block(dev)
+    if "c1" in blocks:
+      extra["c1"] = c1_block(dev)
   if rank != 0:
     if world > 1:
+      dist.barrier()
       dist.destroy_process_group()
     return
   if args.verbose:
@@ -415,10 +813,12 @@ def run_b200(args):
   flops_step = (enc_f + dec_f) * batch
   conv_ms_step = conv_ms / args.steps
   n_conv = len(timer.pairs) // max(args.steps, 1)
-  achieved = flops_step / (conv_ms_step * 1e-3) / 1e12 if conv_ms_step > 0 else 0.0
-  peak = peaks["bf16_tflops_sustained"]
+  tf_isolated = flops_step / (conv_ms_isolated * 1e-3) / 1e12
+  tf_step = flops_step / (ms_per_step * 1e-3) / 1e12
+  traffic, traffic_file = ncu_conv_traffic(args.workload)
+  sm_mhz = (clk or {}).get("sm_mhz") or 1965.0
   line = {
-      "metric": "MPix/s encode+decode, bmshj2018 hyperprior",
+      "metric": METRIC,
       "value": world * pixels / (ms_per_step * 1e-3) / 1e6, "unit": "MPix/s", "n_gpus": world,
       "steps": args.steps, "warmup": n_warm, "ms_per_step": ms_per_step,
       "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
@@ -426,41 +826,51 @@ def run_b200(args):
       "config": {"workload": workload_name(args),
                  "weights": "random-init seed 0", "l2": "inputs_exceed_l2 (%.0f MB images)"
                  % (x_dev.numel() * 4 / 1e6), "parallelism": "batch-sharded x%d" % world,
-                 "conv_impl": args.conv_impl,
-                 "pipeline": {"batches_in_flight": args.depth, "e2e_back_lag": pipe.back_lag, "e2e_host_slots": pipe.host_slots,
+                 "conv_impl": args.conv_impl, "pinned_cores_per_rank": pinned_cores,
+                 "timed_window": "%d steps = %.2f pipeline waves of %d batches in flight"
+                 % (args.steps, args.steps / float(args.depth), args.depth),
+                 "pipeline": {"batches_in_flight": args.depth, "e2e_back_lag": pipe.back_lag,
+                              "e2e_host_slots": pipe.host_slots,
                               "tiles_per_cta": args.tiles_per_cta if args.depth > 1 else 0,
                               "coder_streams_per_cta": args.coder_pack if args.depth > 1 else 0,
                               "hbm_peak_allocated_gb": round(
                                   torch.cuda.max_memory_allocated(dev) / 1e9, 1)}},
       "e2e": {"value": world * pixels / (e2e_ms * 1e-3) / 1e6, "unit": "MPix/s",
               "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-              "string_bytes_per_step": int(string_bytes), "ms_per_step": e2e_ms},
+              "string_bytes_per_step": int(string_bytes), "ms_per_step": e2e_ms,
+              "host_busy_ms_per_step": host_busy_ms, "host_wait_ms_per_step": host_wait_ms,
+              "image_dtype": "uint8 in, uint8 out (scaling and quantize_image fused into the "
+                             "first / last transform kernel)"},
       "gpu_launches": int(launches),
       "clocks": clk,
-      # The transforms dominate the GPU's SM-time (the coder holds ~16 CTAs for longer, see
-      # "coder").  achieved/frac: the 17 conv launches of one batch timed per launch with CUDA
-      # events, the batch alone on the GPU; "in_pipeline": the same brackets inside the timed
-      # region, where they include waiting for SMs shared with other batches' kernels.
+      # The transforms dominate the GPU's SM-time (the coder holds a few CTAs for longer, see
+      # "coder").  achieved / frac (= frac_burst): the conv launches of one batch timed per launch
+      # with CUDA events, the batch alone on the GPU, against the BURST peak; frac_step: the same
+      # FLOPs over the whole driver-timed step against the SUSTAINED peak; "in_pipeline": the
+      # per-launch brackets inside the timed region, where they include waiting for shared SMs.
       "roofline": {"bound": "tensor", "kernel": "SignalConv2D kernels (%d launches/step)" % n_conv,
-                   "achieved": flops_step / (conv_ms_isolated * 1e-3) / 1e12, "peak": peak,
-                   "unit": "TFLOP/s",
-                   "frac": flops_step / (conv_ms_isolated * 1e-3) / 1e12 / peak,
-                   "traffic": NCU_TRAFFIC_BYTES_PER_STEP.get(args.workload),
-                   "peak_source": peaks["source"] + " bf16 sustained",
+                   "achieved": tf_isolated, "peak": peaks["bf16_tflops"], "unit": "TFLOP/s",
+                   "frac": tf_isolated / peaks["bf16_tflops"],
+                   "frac_burst": tf_isolated / peaks["bf16_tflops"],
+                   "achieved_step": tf_step, "peak_sustained": peaks["bf16_tflops_sustained"],
+                   "frac_step": tf_step / peaks["bf16_tflops_sustained"],
+                   "traffic": traffic, "traffic_source": traffic_file,
+                   "peak_source": peaks["source"] + " bf16 (burst for the isolated launches, "
+                                                    "sustained for the step)",
                    "ms_per_step": conv_ms_isolated, "flops_per_step": flops_step,
-                   "in_pipeline": {"ms_per_step": conv_ms_step, "achieved": achieved,
-                                   "frac": achieved / peak,
+                   "in_pipeline": {"ms_per_step": conv_ms_step,
                                    "share_of_step": conv_ms_step / ms_per_step}},
       "coder": {"bound": "latency", "kernel": "encode/decode_unbounded_v4 (y, one CTA per image)",
                 "symbols_per_stream": y_symbols, "streams": batch,
                 "encode_ms": coder_ms[0], "decode_ms": coder_ms[1],
-                "encode_cycles_per_symbol": coder_ms[0] * 1e-3 * (clk["sm_mhz"] or 1965.0) * 1e6
-                                            / y_symbols,
-                "decode_cycles_per_symbol": coder_ms[1] * 1e-3 * (clk["sm_mhz"] or 1965.0) * 1e6
-                                            / y_symbols,
+                "encode_cycles_per_symbol": coder_ms[0] * 1e-3 * sm_mhz * 1e6 / y_symbols,
+                "decode_cycles_per_symbol": coder_ms[1] * 1e-3 * sm_mhz * 1e6 / y_symbols,
                 "hbm_frac": batch * y_symbols * 12.6 / (sum(coder_ms) * 1e-3) / 1e9
                             / peaks["hbm_gbs"]},
   }
+  for k, v in extra.items():
+    if v is not None:
+      line[k] = v
   if not args.no_cpu_baseline and world == 1:
     images = cpu_sample_images(args)
     mpix, cms, kind, cores = cpu_arm(h, w, images, 2, 1, weights=model.export_weights())
@@ -470,6 +880,7 @@ def run_b200(args):
                                       % (images, batch, w, h, kind)}
   print(json.dumps(line))
   if world > 1:
+    dist.barrier()
     dist.destroy_process_group()
 
 

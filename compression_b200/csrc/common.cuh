@@ -62,15 +62,41 @@ inline int conv_cluster() { return g_conv_cluster.load(std::memory_order_relaxed
 inline int debug_bits() { return g_debug.load(std::memory_order_relaxed); }
 inline int tiles_per_cta() { return g_tiles_per_cta.load(std::memory_order_relaxed); }
 
+// SM count of the CURRENT device (cached per device: a process may drive several GPUs)
 inline int num_sms() {
-  static int sms = 0;
+  static std::atomic<int> cache[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  std::atomic<int>& slot = cache[dev & 63];
+  int sms = slot.load(std::memory_order_relaxed);
   if (sms == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
       sms = 148;
+    slot.store(sms, std::memory_order_relaxed);
   }
   return sms;
+}
+
+// "done once" flag kept PER DEVICE: function attributes (cudaFuncSetAttribute) belong to the
+// device that was current when they were set, so a process-wide static bool would leave every
+// other GPU of the process without them.  Thread-safe.
+struct PerDeviceOnce {
+  std::atomic<uint64_t> bits{0};
+  // true the first time it is called with this device current
+  bool first() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return true;
+    const uint64_t m = 1ull << (dev & 63);
+    return (bits.fetch_or(m, std::memory_order_relaxed) & m) == 0;
+  }
+};
+
+// Length of an encoded string as a decoder may read it: the caller's nbytes clamped to the slab
+// row (an encode that overflowed its slab reports the size it NEEDED, which is larger than cap;
+// reading that many bytes would run into the next stream's row or past the allocation).
+__host__ __device__ inline uint32_t clamp_stream_len(int32_t nbytes, int64_t cap) {
+  const int64_t n = nbytes < 0 ? 0 : (int64_t)nbytes;
+  return (uint32_t)(n < cap ? n : cap);
 }
 
 }  // namespace tfc

@@ -52,8 +52,8 @@ int validate(const tfc_conv_desc* d) {
     return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "bad conv geometry");
   if (d->act < TFC_ACT_NONE || d->act > TFC_ACT_IGDN)
     return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "bad activation %d", d->act);
-  if ((d->in_dtype != TFC_F32 && d->in_dtype != TFC_BF16) ||
-      (d->out_dtype != TFC_F32 && d->out_dtype != TFC_BF16))
+  if (d->in_dtype < TFC_F32 || d->in_dtype > TFC_U8 || d->out_dtype < TFC_F32 ||
+      d->out_dtype > TFC_U8)
     return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "bad dtype");
   return TFC_OK;
 }
@@ -93,6 +93,12 @@ extern "C" size_t tfc_signal_conv2d_workspace(const tfc_conv_desc* desc) {
   return need;
 }
 
+extern "C" int tfc_signal_conv2d_path(const tfc_conv_desc* desc) {
+  if (validate(desc)) return -1;
+  const char* why = nullptr;
+  return pick_path(*desc, &why);
+}
+
 extern "C" int tfc_signal_conv2d(const tfc_conv_desc* desc, const void* d_in, const float* d_w,
                                  const float* d_bias, const float* d_beta, const float* d_gamma,
                                  void* d_out, void* d_workspace, size_t workspace_bytes,
@@ -109,6 +115,10 @@ extern "C" int tfc_signal_conv2d(const tfc_conv_desc* desc, const void* d_in, co
   if (desc->impl >= 2 && path == 0)
     return tfc::fail(TFC_ERR_UNIMPLEMENTED, "tcgen05 conv path does not support this shape: %s",
                      why);
+  if ((desc->in_dtype == TFC_U8 && path != 4) || (desc->out_dtype == TFC_U8 && path != 3))
+    return tfc::fail(TFC_ERR_UNIMPLEMENTED,
+                     "uint8 images are read by the thin-input kernel and written by the "
+                     "thin-output kernel only (this shape takes kernel path %d)", path);
   if (path == 1)
     return tfc::conv_umma(*desc, d_in, d_w, d_bias, d_beta, d_gamma, d_out, d_workspace,
                           workspace_bytes, st);

@@ -30,8 +30,8 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
 int make_tensor_map_bf16(CUtensorMap* m, void* base, int rank, const cuuint64_t* dims,
                          const cuuint64_t* strides_bytes, const cuuint32_t* box);
 
-// un-swizzled float32 / bf16 tiled tensor map (image patches of conv_thin.cu)
-int make_tensor_map_plain(CUtensorMap* m, bool f32, void* base, int rank, const cuuint64_t* dims,
+// un-swizzled float32 / bf16 / uint8 (tfc_dtype) tiled tensor map (image patches of conv_thin.cu)
+int make_tensor_map_plain(CUtensorMap* m, int dtype, void* base, int rank, const cuuint64_t* dims,
                           const cuuint64_t* strides_bytes, const cuuint32_t* box);
 
 // 128-pixel tile shape (th x tw) that wastes the fewest pixels on an hs x ws output grid

@@ -51,7 +51,8 @@ struct Params {
   int32_t patch_slot;               // bytes reserved per patch buffer
   int32_t vec;                      // patch reads: elements per shared-memory load (1 or 2)
   int32_t per16;                    // image elements per 16 bytes
-  int32_t act, out_f32, out_wide, in_f32;
+  int32_t act, out_f32, out_wide, in_dtype;   // in_dtype: tfc_dtype (uint8: byte / 255)
+  int32_t esize;                    // bytes per image element
   int32_t out_tma;                  // GDN output leaves by TMA tile stores
   int32_t debug;
   const void* in;
@@ -70,10 +71,20 @@ struct __align__(8) Barriers {
   uint32_t pad;
 };
 
+// image element -> float.  A uint8 image stands for byte / 255 (read_png, examples/
+// bmshj2018.py:53-57); float(b) * (1/255.f) rounds to the same bfloat16 operand as float(b) / 255
+// for all 256 bytes (checked exhaustively), so the layer's result does not depend on which of the
+// two forms the caller feeds.
+constexpr float kInv255 = 1.0f / 255.0f;
 __device__ __forceinline__ float ldf(const float* p) { return __ldg(p); }
 __device__ __forceinline__ float ldf(const __nv_bfloat16* p) {
   return __bfloat162float(*p);
 }
+__device__ __forceinline__ float ldf(const uint8_t* p) { return (float)__ldg(p) * kInv255; }
+// the same from shared memory (TMA-staged patch)
+__device__ __forceinline__ float lds1(const float* p) { return *p; }
+__device__ __forceinline__ float lds1(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+__device__ __forceinline__ float lds1(const uint8_t* p) { return (float)(*p) * kInv255; }
 
 // One tile row (= output pixel) of k-block KBI: K-columns [64*KBI, 64*KBI + 16*NM) of the im2col
 // matrix, k = (a*KW + b)*CIN + c.  `src` points at the top-left tap of the pixel's window.
@@ -115,6 +126,10 @@ __device__ __forceinline__ void lds_vec(const __nv_bfloat16* p, float (&o)[2]) {
   const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
   o[0] = v.x; o[1] = v.y;
 }
+__device__ __forceinline__ void lds_vec(const uint8_t* p, float (&o)[2]) {
+  const uchar2 v = *reinterpret_cast<const uchar2*>(p);
+  o[0] = (float)v.x * kInv255; o[1] = (float)v.y * kInv255;
+}
 
 // The same row from the TMA-staged patch in shared memory (zero padding already applied by the
 // TMA unit).  `src` points at the top-left tap inside the patch; V = 2 reads element pairs
@@ -139,7 +154,7 @@ __device__ __forceinline__ void build_row_patch(const T* src, int pitch, uint8_t
           if (k0 >= lo && k0 < hi) v[k0 - lo] = pr[0];
           if (q * 2 + 1 < L && k0 + 1 >= lo && k0 + 1 < hi) v[k0 + 1 - lo] = pr[1];
         } else {
-          v[k0 - lo] = (float)src[a * pitch + q];
+          v[k0 - lo] = lds1(src + a * pitch + q);
         }
       }
     }
@@ -374,12 +389,16 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
         uint8_t* sa = smem + stage * kABytes;
         if (p.debug & 1) {
         } else if (p.patch) {
-          if (p.in_f32)
+          if (p.in_dtype == TFC_F32)
             build_block_patch<KH, KW, CIN, KBI>(p, reinterpret_cast<const float*>(patch), t, sa);
+          else if (p.in_dtype == TFC_U8)
+            build_block_patch<KH, KW, CIN, KBI>(p, patch, t, sa);
           else
             build_block_patch<KH, KW, CIN, KBI>(p, reinterpret_cast<const __nv_bfloat16*>(patch), t, sa);
-        } else if (p.in_f32)
+        } else if (p.in_dtype == TFC_F32)
           build_block<KH, KW, CIN, KBI>(p, static_cast<const float*>(p.in), n, i0, j0, t, sa);
+        else if (p.in_dtype == TFC_U8)
+          build_block<KH, KW, CIN, KBI>(p, static_cast<const uint8_t*>(p.in), n, i0, j0, t, sa);
         else
           build_block<KH, KW, CIN, KBI>(p, static_cast<const __nv_bfloat16*>(p.in), n, i0, j0, t, sa);
         fence_proxy_async_smem();
@@ -396,7 +415,7 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
       if (p.patch) {
         mbar_wait(&bars->p_full[pb], (it >> 1) & 1);
         const int skip = ((j0 * p.sd - p.pl) * CIN) & (p.per16 - 1);
-        patch = patches + pb * p.patch_slot + skip * (p.in_f32 ? 4 : 2);
+        patch = patches + pb * p.patch_slot + skip * p.esize;
       }
       block(std::integral_constant<int, 0>{}, n, i0, j0);
       block(std::integral_constant<int, 1>{}, n, i0, j0);
@@ -461,7 +480,7 @@ bool make_plan(const tfc_conv_desc& d, const void* in, Plan* pl) {
   // image patch of one tile: ((th-1)*sd + kh) rows of ((tw-1)*sd + kw)*cin elements, the row
   // starting on a 16-byte boundary and padded to 16 bytes (+ one element so that a pair load may
   // straddle the end)
-  const int esize = d.in_dtype == TFC_F32 ? 4 : 2;
+  const int esize = d.in_dtype == TFC_F32 ? 4 : (d.in_dtype == TFC_U8 ? 1 : 2);
   const int per16 = 16 / esize;
   pl->patch_rows = (pl->th - 1) * d.sd + d.kh;
   pl->patch_pitch = (((pl->tw - 1) * d.sd + d.kw) * d.cin + 1 + (per16 - 1) + per16 - 1) / per16 * per16;
@@ -516,6 +535,7 @@ bool conv_thin_supported(const tfc_conv_desc& d, const char** why) {
   const char* dummy;
   if (!why) why = &dummy;
   if (d.su != 1) { *why = "thin-input path needs strides_up == 1"; return false; }
+  if (d.out_dtype == TFC_U8) { *why = "thin-input path does not write uint8"; return false; }
   if (!shape_ok(d)) { *why = "thin-input path is built for 3 channels and 5x5 / 9x9 kernels"; return false; }
   if (d.act == TFC_ACT_IGDN) { *why = "thin-input path has no IGDN epilogue"; return false; }
   if (d.act == TFC_ACT_GDN && d.cout != 128 && d.cout != 192) {
@@ -548,15 +568,16 @@ int conv_thin(const tfc_conv_desc& d, const void* in, const float* w, const floa
   Params p{};
   p.n = d.n; p.h = d.h; p.w = d.w; p.ho = d.ho; p.wo = d.wo; p.cout = d.cout; p.npad = pl.npad;
   p.sd = d.sd; p.pt = d.pad_top; p.pl = d.pad_left;
-  p.act = d.act; p.out_f32 = d.out_dtype == TFC_F32; p.in_f32 = d.in_dtype == TFC_F32;
+  p.act = d.act; p.out_f32 = d.out_dtype == TFC_F32; p.in_dtype = d.in_dtype;
+  p.esize = d.in_dtype == TFC_F32 ? 4 : (d.in_dtype == TFC_U8 ? 1 : 2);
   p.out_wide = epi::wide_stores_ok(out, d.cout, p.out_f32 != 0);
   p.in = in; p.bias = bias; p.beta = beta; p.out = out;
   p.stages = pl.stages;
   p.debug = debug_bits();
   p.th = pl.th; p.tw = pl.tw;
   p.patch = pl.patch; p.patch_pitch = pl.patch_pitch; p.patch_slot = pl.patch_slot; p.vec = pl.vec;
-  p.per16 = p.in_f32 ? 4 : 8;
-  p.patch_bytes = pl.patch_rows * pl.patch_pitch * (p.in_f32 ? 4 : 2);
+  p.per16 = 16 / p.esize;
+  p.patch_bytes = pl.patch_rows * pl.patch_pitch * p.esize;
   p.tiles_h = (d.ho + p.th - 1) / p.th;
   p.tiles_w = (d.wo + p.tw - 1) / p.tw;
   p.num_tiles = d.n * p.tiles_h * p.tiles_w;
@@ -592,11 +613,11 @@ int conv_thin(const tfc_conv_desc& d, const void* in, const float* w, const floa
     map_g = map_w;
   }
   if (pl.patch) {
-    const cuuint64_t es = p.in_f32 ? 4 : 2;
+    const cuuint64_t es = p.esize;
     cuuint64_t dims[3] = {(cuuint64_t)d.w * d.cin, (cuuint64_t)d.h, (cuuint64_t)d.n};
     cuuint64_t str[2] = {(cuuint64_t)d.w * d.cin * es, (cuuint64_t)d.h * d.w * d.cin * es};
     cuuint32_t box[3] = {(cuuint32_t)pl.patch_pitch, (cuuint32_t)pl.patch_rows, 1};
-    int rc = make_tensor_map_plain(&map_img, p.in_f32 != 0, const_cast<void*>(in), 3, dims, str, box);
+    int rc = make_tensor_map_plain(&map_img, d.in_dtype, const_cast<void*>(in), 3, dims, str, box);
     if (rc) return rc;
   } else {
     map_img = map_w;

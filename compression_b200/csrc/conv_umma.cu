@@ -417,10 +417,12 @@ size_t smem_bytes(int npad, int cout, bool gdn) {
 
 namespace tfc {
 
-int make_tensor_map_plain(CUtensorMap* m, bool f32, void* base, int rank, const cuuint64_t* dims,
+int make_tensor_map_plain(CUtensorMap* m, int dtype, void* base, int rank, const cuuint64_t* dims,
                           const cuuint64_t* strides_bytes, const cuuint32_t* box) {
-  return make_map_any(m, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16,
-                      CU_TENSOR_MAP_SWIZZLE_NONE, base, rank, dims, strides_bytes, box);
+  const CUtensorMapDataType t = dtype == TFC_F32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                : dtype == TFC_U8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                                                  : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  return make_map_any(m, t, CU_TENSOR_MAP_SWIZZLE_NONE, base, rank, dims, strides_bytes, box);
 }
 
 void conv_pick_tile(int hs, int ws, int* th, int* tw) { pick_tile(hs, ws, th, tw); }

@@ -47,7 +47,7 @@ struct UpParams {
   int32_t chunk;                    // tiles per CTA (0: persistent grid)
   int32_t npad, ld;                 // GEMM N, row stride (floats) of the staged accumulator tile
   int32_t kchunks, stages;
-  int32_t relu, out_f32;
+  int32_t relu, out_dtype;          // out_dtype: tfc_dtype (uint8: quantize_image)
   const float* bias;
   void* out;
 };
@@ -62,6 +62,11 @@ struct __align__(8) UpBarriers {
 
 __device__ __forceinline__ void named_bar_sync(int id, int count) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+
+// quantize_image (examples/bmshj2018.py:60-63): saturate_cast<uint8>(round(x * 255)), half to even
+__device__ __forceinline__ uint32_t quantize_u8(float x) {
+  return (uint32_t)fminf(fmaxf(rintf(x * 255.0f), 0.f), 255.f);
 }
 
 __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&r)[16]) {
@@ -239,9 +244,15 @@ conv_upthin_kernel(const __grid_constant__ CUtensorMap map_a,
               y[pj * 3 + 0] = s0; y[pj * 3 + 1] = s1; y[pj * 3 + 2] = s2;
             }
             const int64_t pix = ((int64_t)n * p.ho + (2 * ii + pi)) * p.wo + 2 * jj;
-            if (p.out_f32) {
+            if (p.out_dtype == TFC_F32) {
               float2* o2 = reinterpret_cast<float2*>(static_cast<float*>(p.out) + pix * 3);
               o2[0] = make_float2(y[0], y[1]); o2[1] = make_float2(y[2], y[3]); o2[2] = make_float2(y[4], y[5]);
+            } else if (p.out_dtype == TFC_U8) {
+              // two pixels = 6 bytes at an even offset (wo is even): three 16-bit stores
+              uint16_t* o3 = reinterpret_cast<uint16_t*>(static_cast<uint8_t*>(p.out) + pix * 3);
+              o3[0] = (uint16_t)(quantize_u8(y[0]) | (quantize_u8(y[1]) << 8));
+              o3[1] = (uint16_t)(quantize_u8(y[2]) | (quantize_u8(y[3]) << 8));
+              o3[2] = (uint16_t)(quantize_u8(y[4]) | (quantize_u8(y[5]) << 8));
             } else {
               uint32_t* o1 = reinterpret_cast<uint32_t*>(static_cast<__nv_bfloat16*>(p.out) + pix * 3);
               __nv_bfloat162 h0 = __floats2bfloat162_rn(y[0], y[1]), h1 = __floats2bfloat162_rn(y[2], y[3]),
@@ -280,7 +291,8 @@ conv_upthin_kernel(const __grid_constant__ CUtensorMap map_a,
         for (int o = 0; o < 4; ++o) {
           if (o < p.cout) {
             const float v = p.relu ? fmaxf(y[o], 0.f) : y[o];
-            if (p.out_f32) static_cast<float*>(p.out)[pix * p.cout + o] = v;
+            if (p.out_dtype == TFC_F32) static_cast<float*>(p.out)[pix * p.cout + o] = v;
+            else if (p.out_dtype == TFC_U8) static_cast<uint8_t*>(p.out)[pix * p.cout + o] = (uint8_t)quantize_u8(v);
             else static_cast<__nv_bfloat16*>(p.out)[pix * p.cout + o] = __float2bfloat16_rn(v);
           }
         }
@@ -381,7 +393,7 @@ int conv_upthin(const tfc_conv_desc& d, const void* in, const float* w, const fl
   p.tiles_w = (d.w + pl.iw - 1) / pl.iw;
   p.num_tiles = d.n * p.tiles_h * p.tiles_w;
   p.npad = pl.npad; p.ld = pl.ld; p.kchunks = d.cin / kBlockK; p.stages = pl.stages;
-  p.relu = d.act == TFC_ACT_RELU; p.out_f32 = d.out_dtype == TFC_F32;
+  p.relu = d.act == TFC_ACT_RELU; p.out_dtype = d.out_dtype;
   p.bias = bias; p.out = out;
 
   __nv_bfloat16* wb = static_cast<__nv_bfloat16*>(ws);

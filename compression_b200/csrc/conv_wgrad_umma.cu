@@ -262,11 +262,10 @@ int conv_wgrad_umma(const tfc_conv_desc& d, const void* x, const void* dy, float
     int rc = make_tensor_map_bf16(&map_small, const_cast<void*>(small), 4, dims, str, box);
     if (rc) return rc;
   }
-  static bool attr = false;
-  if (!attr) {
+  static tfc::PerDeviceOnce attr;
+  if (attr.first()) {
     TFC_CUDA(cudaFuncSetAttribute(conv_wgrad_umma_kernel,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr = true;
   }
   dim3 grid(count, p.kslices, 1);
   conv_wgrad_umma_kernel<<<grid, kThreads, smem, st>>>(map_big, map_small, p);

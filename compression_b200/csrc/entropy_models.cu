@@ -230,6 +230,60 @@ gaussian_call_vec_kernel(const float4* __restrict__ y, const float4* __restrict_
   }
 }
 
+// Gradient of the Gaussian likelihood of the training graph (entropy_models.py:916-932 with
+// :965-969; TF derives it through erfc, abs, the division by scale and the two lower_bound ops,
+// math_ops.py:61-74).  With a = |v|, r = 1 / max(sigma, scale_bound), u = (.5 - a) r,
+// l = (-.5 - a) r, phi(t) = exp(-t^2 / 2) / sqrt(2 pi):
+//   d lik / d v     = sign(v) (phi(l) - phi(u)) r
+//   d lik / d sigma = (l phi(l) - u phi(u)) r
+// The likelihood bound passes the gradient where lik >= bound or the gradient is negative, the
+// scale bound where sigma >= bound or the gradient (w.r.t. the bounded scale) is negative.
+__device__ __forceinline__ void gaussian_lik_grad(float v, float sg, float g, float scale_bound,
+                                                  float bound, float* gv, float* gs) {
+  const float r = 1.0f / (scale_bound > 0.f ? fmaxf(sg, scale_bound) : sg);
+  const float a = fabsf(v);
+  const float u = (0.5f - a) * r, l = (-0.5f - a) * r;
+  const float lik = std_normal_cdf(u) - std_normal_cdf(l);
+  if (bound > 0.f && !(lik >= bound || g < 0.f)) g = 0.f;
+  const float kInvSqrt2Pi = 0.3989422804014327f;
+  const float pu = kInvSqrt2Pi * __expf(-0.5f * u * u), pl = kInvSqrt2Pi * __expf(-0.5f * l * l);
+  const float sgn = v > 0.f ? 1.f : (v < 0.f ? -1.f : 0.f);
+  *gv = g * sgn * (pl - pu) * r;
+  float ds = g * (l * pl - u * pu) * r;
+  if (scale_bound > 0.f && !(sg >= scale_bound || ds < 0.f)) ds = 0.f;
+  *gs = ds;
+}
+
+__global__ void __launch_bounds__(kThreads)
+gaussian_backward_kernel(const float* __restrict__ y, const float* __restrict__ sigma,
+                         const float* __restrict__ grad, int64_t count, float scale_bound,
+                         float bound, float* __restrict__ gy, float* __restrict__ gs) {
+  for (int64_t i = blockIdx.x * (int64_t)kThreads + threadIdx.x; i < count;
+       i += (int64_t)gridDim.x * kThreads) {
+    float a, b;
+    gaussian_lik_grad(y[i], sigma[i], grad[i], scale_bound, bound, &a, &b);
+    gy[i] = a;
+    gs[i] = b;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+gaussian_backward_vec_kernel(const float4* __restrict__ y, const float4* __restrict__ sigma,
+                             const float4* __restrict__ grad, int64_t nvec, float scale_bound,
+                             float bound, float4* __restrict__ gy, float4* __restrict__ gs) {
+  for (int64_t i = blockIdx.x * (int64_t)kThreads + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * kThreads) {
+    const float4 v = __ldg(y + i), s = __ldg(sigma + i), g = __ldg(grad + i);
+    float4 a, b;
+    gaussian_lik_grad(v.x, s.x, g.x, scale_bound, bound, &a.x, &b.x);
+    gaussian_lik_grad(v.y, s.y, g.y, scale_bound, bound, &a.y, &b.y);
+    gaussian_lik_grad(v.z, s.z, g.z, scale_bound, bound, &a.z, &b.z);
+    gaussian_lik_grad(v.w, s.w, g.w, scale_bound, bound, &a.w, &b.w);
+    gy[i] = a;
+    gs[i] = b;
+  }
+}
+
 __device__ __forceinline__ int table_index(const float* s_table, int levels, float s) {
   int lo = 0, hi = levels - 1;
   while (lo < hi) {
@@ -706,6 +760,32 @@ extern "C" int tfc_gaussian_call(const float* d_y, const float* d_sigma, int64_t
         d_y + done, d_sigma + done, count - done, scale_bound, likelihood_bound, mode,
         d_values ? d_values + done : nullptr, d_lik + done);
   TFC_LAUNCHED("gaussian_call_kernel");
+  return TFC_OK;
+}
+
+extern "C" int tfc_gaussian_likelihood_backward(const float* d_y, const float* d_sigma,
+                                                const float* d_grad_lik, int64_t count,
+                                                float scale_bound, float likelihood_bound,
+                                                float* d_grad_y, float* d_grad_sigma,
+                                                void* stream) {
+  if (count <= 0) return TFC_OK;
+  if (!d_y || !d_sigma || !d_grad_lik || !d_grad_y || !d_grad_sigma)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "gaussian likelihood backward: null buffer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int64_t done = 0;
+  if (count >= 4 && aligned16(d_y) && aligned16(d_sigma) && aligned16(d_grad_lik) &&
+      aligned16(d_grad_y) && aligned16(d_grad_sigma)) {
+    done = count & ~(int64_t)3;
+    gaussian_backward_vec_kernel<<<grid_vec(done / 4), kThreads, 0, st>>>(
+        reinterpret_cast<const float4*>(d_y), reinterpret_cast<const float4*>(d_sigma),
+        reinterpret_cast<const float4*>(d_grad_lik), done / 4, scale_bound, likelihood_bound,
+        reinterpret_cast<float4*>(d_grad_y), reinterpret_cast<float4*>(d_grad_sigma));
+  }
+  if (done < count)
+    gaussian_backward_kernel<<<grid_for(count - done), kThreads, 0, st>>>(
+        d_y + done, d_sigma + done, d_grad_lik + done, count - done, scale_bound,
+        likelihood_bound, d_grad_y + done, d_grad_sigma + done);
+  TFC_LAUNCHED("gaussian_backward_kernel");
   return TFC_OK;
 }
 

@@ -238,11 +238,10 @@ extern "C" int tfc_pmf_to_quantized_cdf(const float* d_pmf, int64_t rows, int32_
   if ((n >= 64 || rows <= 2048) && row_bytes <= 200 * 1024) {
     const int wpc = (int)std::max<size_t>(1, std::min<size_t>(4, (200 * 1024) / row_bytes));
     const size_t smem = wpc * row_bytes;
-    static bool attr = false;
-    if (!attr) {
+    static tfc::PerDeviceOnce attr;
+    if (attr.first()) {
       TFC_CUDA(cudaFuncSetAttribute(pmf_to_cdf_warp_kernel,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      attr = true;
     }
     pmf_to_cdf_warp_kernel<<<(unsigned)((rows + wpc - 1) / wpc), wpc * 32, smem, st>>>(
         d_pmf, rows, n, precision, d_cdf);

@@ -324,7 +324,8 @@ __global__ void __launch_bounds__(256) decode_bounded_kernel(const DecodeParams 
   const int64_t s = (int64_t)blockIdx.x * (blockDim.x >> 5) + warp;
   if (s >= p.S) return;
   Decoder d;
-  d.init(p.enc + s * p.cap, (uint32_t)max(p.nbytes[s], 0));
+  d.init(p.enc + s * p.cap, tfc::clamp_stream_len(p.nbytes[s], p.cap));
+  d.corrupt = (int64_t)p.nbytes[s] > p.cap;   // a truncated string
   const int32_t* cdf = p.cdf + s * p.cdf_stream_stride;
   int16_t* out = p.out16 + s * p.n;
   const int len = p.chip, prec = p.precision;
@@ -651,11 +652,10 @@ extern "C" int tfc_unbounded_index_range_encode(
     int wpc = 1;
     int64_t blocks = 0;
     const size_t smem = lanes_geometry(S, q.table_bytes, &wpc, &blocks);
-    static bool attr = false;
-    if (!attr) {
+    static tfc::PerDeviceOnce attr;
+    if (attr.first()) {
       TFC_CUDA(cudaFuncSetAttribute(lanes::encode_unbounded_lanes,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
-      attr = true;
     }
     lanes::encode_unbounded_lanes<<<(unsigned)blocks, wpc * 32, smem, st>>>(q);
     TFC_LAUNCHED("encode_unbounded_lanes");
@@ -685,13 +685,12 @@ extern "C" int tfc_unbounded_index_range_encode(
     if (q.round * v4_max_puts(overflow_width) > q.put_cap)
       return tfc::fail(TFC_ERR_UNIMPLEMENTED, "overflow_width %d needs larger round buffers", overflow_width);
     const size_t smem = (size_t)q.table_bytes + q.streams_per_cta * v4::enc_bytes(q.put_cap);
-    static bool attr = false;
-    if (!attr) {
+    static tfc::PerDeviceOnce attr;
+    if (attr.first()) {
       TFC_CUDA(cudaFuncSetAttribute(v4::encode_unbounded_v4<false>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
       TFC_CUDA(cudaFuncSetAttribute(v4::encode_unbounded_v4<true>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
-      attr = true;
     }
     const int64_t blocks = (S + q.streams_per_cta - 1) / q.streams_per_cta;
     if (q.streams_per_cta == 1)
@@ -710,12 +709,11 @@ extern "C" int tfc_unbounded_index_range_encode(
   const int64_t dense = (int64_t)rows * cols * 4 + (int64_t)rows * 16 + 16;
   const int budget = (int)std::min<int64_t>(dense, kTableBudget);
   const size_t smem = (size_t)4 * kSuper * sizeof(uint32_t) + (size_t)budget;
-  static bool enc_attr_set = false;
-  if (!enc_attr_set) {
+  static tfc::PerDeviceOnce enc_attr_set;
+  if (enc_attr_set.first()) {
     TFC_CUDA(cudaFuncSetAttribute(encode_unbounded_kernel,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)(4 * kSuper * sizeof(uint32_t)) + kTableBudget));
-    enc_attr_set = true;
   }
   encode_unbounded_kernel<<<(unsigned)S, 128, smem, st>>>(p, budget);
   TFC_LAUNCHED("encode_kernel<unbounded>");
@@ -754,11 +752,10 @@ extern "C" int tfc_unbounded_index_range_decode(
     int wpc = 1;
     int64_t blocks = 0;
     const size_t smem = lanes_geometry(S, q.table_bytes, &wpc, &blocks);
-    static bool attr = false;
-    if (!attr) {
+    static tfc::PerDeviceOnce attr;
+    if (attr.first()) {
       TFC_CUDA(cudaFuncSetAttribute(lanes::decode_unbounded_lanes,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
-      attr = true;
     }
     lanes::decode_unbounded_lanes<<<(unsigned)blocks, wpc * 32, smem, st>>>(q);
     TFC_LAUNCHED("decode_unbounded_lanes");
@@ -792,11 +789,10 @@ extern "C" int tfc_unbounded_index_range_decode(
     const size_t smem = geometry(round);
     if (smem > smem_max)
       return tfc::fail(TFC_ERR_UNIMPLEMENTED, "overflow_width %d needs a larger stream window", overflow_width);
-    static bool attr = false;
-    if (!attr) {
+    static tfc::PerDeviceOnce attr;
+    if (attr.first()) {
       TFC_CUDA(cudaFuncSetAttribute(v4::decode_unbounded_v4,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
-      attr = true;
     }
     const int64_t blocks = (S + q.streams_per_cta - 1) / q.streams_per_cta;
     v4::decode_unbounded_v4<<<(unsigned)blocks, 64 * q.streams_per_cta, smem, st>>>(q);
@@ -811,12 +807,11 @@ extern "C" int tfc_unbounded_index_range_decode(
   const int64_t dense = (int64_t)rows * cols * 4 + (int64_t)rows * 16 + 16;
   const int budget = (int)std::min<int64_t>(dense, kTableBudget);
   p.table_budget = budget;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static tfc::PerDeviceOnce attr_set;
+  if (attr_set.first()) {
     TFC_CUDA(cudaFuncSetAttribute(decode_unbounded_kernel2,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   kTableBudget + 16 + 8 * kDecScratch));
-    attr_set = true;
   }
   const int wpb = warps_per_block(S);
   const int64_t blocks = (S + wpb - 1) / wpb;
@@ -870,11 +865,10 @@ extern "C" int tfc_range_encode(const int16_t* d_data, int64_t S, const int64_t*
     int wpc = 1;
     int64_t blocks = 0;
     const size_t smem = lanes_geometry(S, q.table_bytes, &wpc, &blocks);
-    static bool attr = false;
-    if (!attr) {
+    static tfc::PerDeviceOnce attr;
+    if (attr.first()) {
       TFC_CUDA(cudaFuncSetAttribute(lanes::encode_bounded_lanes,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
-      attr = true;
     }
     lanes::encode_bounded_lanes<<<(unsigned)blocks, wpc * 32, smem, st>>>(q);
     TFC_LAUNCHED("encode_bounded_lanes");
@@ -930,11 +924,10 @@ extern "C" int tfc_range_decode(const uint8_t* d_enc, int64_t cap, const int32_t
     int wpc = 1;
     int64_t blocks = 0;
     const size_t smem = lanes_geometry(S, q.table_bytes, &wpc, &blocks);
-    static bool attr = false;
-    if (!attr) {
+    static tfc::PerDeviceOnce attr;
+    if (attr.first()) {
       TFC_CUDA(cudaFuncSetAttribute(lanes::decode_bounded_lanes,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024));
-      attr = true;
     }
     lanes::decode_bounded_lanes<<<(unsigned)blocks, wpc * 32, smem, st>>>(q);
     TFC_LAUNCHED("decode_bounded_lanes");

@@ -254,7 +254,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) decode_unbounded_lanes(cons
   Dec d;
   d.src = p.enc + (active ? s : s0) * p.cap;
   d.len = active ? (uint32_t)max(min((int64_t)p.nbytes[s], p.cap), (int64_t)0) : 0u;
-  d.pos = 0; d.win = 0; d.avail = 0; d.corrupt = false;
+  d.pos = 0; d.win = 0; d.avail = 0;
+  d.corrupt = active && (int64_t)p.nbytes[s] > p.cap;   // a truncated string
   d.vec = (reinterpret_cast<uintptr_t>(d.src) & 7) == 0;
   d.span1 = 0xFFFFFFFFu;
   d.rem = 0;
@@ -394,7 +395,8 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) decode_bounded_lanes(const 
   Dec d;
   d.src = p.enc + (active ? s : s0) * p.cap;
   d.len = active ? (uint32_t)max(min((int64_t)p.nbytes[s], p.cap), (int64_t)0) : 0u;
-  d.pos = 0; d.win = 0; d.avail = 0; d.corrupt = false;
+  d.pos = 0; d.win = 0; d.avail = 0;
+  d.corrupt = active && (int64_t)p.nbytes[s] > p.cap;   // a truncated string
   d.vec = (reinterpret_cast<uintptr_t>(d.src) & 7) == 0;
   d.span1 = 0xFFFFFFFFu;
   d.rem = 0;

@@ -405,7 +405,8 @@ __device__ void decode_stream2(const DecodeParams& p, int64_t s, int lane, uint8
   uint32_t* s_win = reinterpret_cast<uint32_t*>(scratch);            // [symbol][lane]
   int4* s_gm = reinterpret_cast<int4*>(scratch + 32 * 32 * 4);       // {start, len, wb, off}
   FastDecoder d;
-  d.init(p.enc + s * p.cap, (uint32_t)max(p.nbytes[s], 0), lane);
+  d.init(p.enc + s * p.cap, tfc::clamp_stream_len(p.nbytes[s], p.cap), lane);
+  d.corrupt = (int64_t)p.nbytes[s] > p.cap;   // a truncated string
   const int32_t* idx = p.index + s * p.index_stride;
   int32_t* out = p.out32 + s * p.n;
   const int prec = p.precision, w = p.overflow_width;

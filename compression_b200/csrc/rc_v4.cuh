@@ -274,7 +274,8 @@ __global__ void __launch_bounds__(512, 1) decode_unbounded_v4(const DecParamsV4 
   const uint32_t win_max = 2u * (uint32_t)p.round_words + 16u;                 // <= kLmax
   const uint32_t win_typ = min(win_max, (2u * (uint32_t)p.round + 72u + 7u) & ~7u);
   const uint8_t* src = p.enc + s * p.cap;
-  const uint32_t len = (uint32_t)max(p.nbytes[s], 0);
+  const uint32_t len = tfc::clamp_stream_len(p.nbytes[s], p.cap);
+  const bool oversize = (int64_t)p.nbytes[s] > p.cap;   // a truncated string: reported corrupt
   const bool vec = (reinterpret_cast<uintptr_t>(src) & 15) == 0;
   // dst[k] = stream word first + k for k in [k0, k1) (big-endian pairs, zeros past the end);
   // first, k0 and k1 are multiples of 8
@@ -353,7 +354,7 @@ __global__ void __launch_bounds__(512, 1) decode_unbounded_v4(const DecParamsV4 
   if (lane == 0) ctrl[0] = 2;
   pair_barrier(bar);
   DecState d;
-  d.corrupt = false;
+  d.corrupt = oversize;
   // fast-path state: span modulo 2^32 (0 stands for 2^32 and always takes the general path);
   // `wa` is the shared-space address of the word after w0
   const uint32_t lin_s = (uint32_t)__cvta_generic_to_shared(lin);

@@ -22,9 +22,7 @@ from compression_b200.python.ops import train_ops
 Compressed = collections.namedtuple("Compressed", ["string", "x_shape", "y_shape"])
 
 
-def quantize_image(image):
-  """bls2017.py:57-60."""
-  return torch.clamp(torch.round(image * 255), 0, 255).to(torch.uint8)
+quantize_image = signal_conv.quantize_image     # bls2017.py:57-60
 
 
 class _Sequential(object):
@@ -95,17 +93,18 @@ class Bls2017Model(object):
 
   # ---- bls2017.py:205-271 ------------------------------------------------------------------
   def compress(self, x):
+    """x: float32 [B,H,W,3] in [0,1] or the uint8 image (a byte b stands for b / 255)."""
     x = x.to(self.device)
     y = self.analysis_transform(x)
     string = self.entropy_bottleneck.compress_device(y)
     return Compressed(string, tuple(x.shape[1:-1]), tuple(y.shape[1:-1]))
 
   # ---- bls2017.py:274-305 ------------------------------------------------------------------
-  def decompress(self, c):
+  def decompress(self, c, out_dtype=torch.float32):
     nf = self.num_filters
     y_hat = self.entropy_bottleneck.decompress_device(
         c.string, tuple(c.y_shape) + (nf,), channels=nf, out_dtype=torch.bfloat16)
-    x_hat = self.synthesis_transform(y_hat)
+    x_hat = self.synthesis_transform(y_hat, out_dtype=out_dtype)
     return x_hat[:, :c.x_shape[0], :c.x_shape[1], :]
 
   def evaluate(self, x):
@@ -149,6 +148,34 @@ class Bls2017Model(object):
 
   def conv_layers(self):
     return self.analysis_transform.layers + self.synthesis_transform.layers
+
+  # ---- export (host copies, for checkpoints and for the CPU checker in tests/bench) --------
+  def export_weights(self):
+    """Effective float32 weights keyed like oracle/cpu_codec.py (CpuBls2017) expects."""
+    w = {}
+    for prefix, seq in (("a", self.analysis_transform), ("s", self.synthesis_transform)):
+      for i, l in enumerate(seq.layers):
+        name = "%s%d" % (prefix, i)
+        w[name + "/kernel"] = l.kernel.detach().float().cpu().numpy()
+        if l.bias is not None:
+          w[name + "/bias"] = l.bias.detach().float().cpu().numpy()
+        if isinstance(l.activation, gdn.GDN):
+          beta, gamma = l.activation.effective()
+          w[name + "/beta"] = beta.detach().cpu().numpy()
+          w[name + "/gamma"] = gamma.detach().cpu().numpy()
+    eb = self.entropy_bottleneck
+    for i, m in enumerate(eb.matrices):
+      w["eb/matrix_%d" % i] = m.detach().cpu().numpy()
+      w["eb/bias_%d" % i] = eb.biases[i].detach().cpu().numpy()
+    for i, f in enumerate(eb.factors):
+      w["eb/factor_%d" % i] = f.detach().cpu().numpy()
+    w["eb/quantiles"] = eb.quantiles.detach().cpu().numpy()
+    return w
+
+  def export_tables(self):
+    eb = self.entropy_bottleneck
+    return dict(eb_cdf=eb._quantized_cdf.cpu().numpy(), eb_len=eb._cdf_length.cpu().numpy(),
+                eb_off=eb._offset.cpu().numpy())
 
 
 class _tf32_matmul(object):

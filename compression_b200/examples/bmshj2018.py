@@ -27,9 +27,7 @@ Compressed = collections.namedtuple(
     "Compressed", ["string", "side_string", "x_shape", "y_shape", "z_shape"])
 
 
-def quantize_image(image):
-  """bmshj2018.py:60-63."""
-  return torch.clamp(torch.round(image * 255), 0, 255).to(torch.uint8)
+quantize_image = signal_conv.quantize_image     # bmshj2018.py:60-63
 
 
 class _Sequential(object):
@@ -163,6 +161,9 @@ class Pipeline(object):
     self._lib = _lib
     self.tiles_per_cta = int(tiles_per_cta) if self.depth > 1 else 0
     self.pack = int(coder_streams_per_cta) if self.depth > 1 else 0
+    self.h2d_bytes = self.d2h_bytes = 0
+    self.host_busy_s = self.host_wait_s = 0.0
+    self._cap = None          # (string, side string) slab bytes per image, learnt from traffic
 
   def __enter__(self):
     if self.depth > 1:
@@ -184,15 +185,19 @@ class Pipeline(object):
       cur.wait_stream(s)
 
   def roundtrip_device(self, batches):
-    """batches: device float32 [B,H,W,3] tensors -> list of x_hat (device)."""
+    """batches: device float32 [B,H,W,3] tensors -> list of x_hat (device).  The coder's status
+    words of batch k are looked at 2 * depth batches later (long after it finished) and the rest
+    on return."""
     from compression_b200.python.ops import range_coding_ops as rc
     model, outs = self.model, []
     cur = self._fork()
-    with rc.deferred_checks():
+    with rc.deferred_checks() as checks:
       for k, x in enumerate(batches):
         st = self.streams[k % self.depth]
+        checks.tag = k
         with torch.cuda.stream(st):
           outs.append(model.decompress(model.compress(x, self._stagger(k, st))))
+        checks.drain(2 * self.depth)
       self._join(cur)
     return outs
 
@@ -211,12 +216,20 @@ class Pipeline(object):
     return lambda: ev.record(st)
 
   def roundtrip_host(self, batches_u8, on_result=None):
-    """batches_u8: pinned host uint8 [B,H,W,3] tensors.  Per batch: image H2D, compress,
-    strings D2H, strings H2D, decompress, x_hat D2H.  The host waits twice per batch: for batch
-    k's strings after it has queued the compress of the next `back_lag` batches, and for its
-    x_hat when the slot is reused, host_slots - back_lag batches after the decompress was queued.
-    Both waits have to span several batch times or the host, not the GPU, sets the pace (a
-    decompress is one serial decode per image and takes longer than two batch times).
+    """batches_u8: pinned host uint8 [B,H,W,3] tensors.  Per batch: image H2D (the bytes
+    themselves: the first analysis layer reads uint8), compress, strings D2H, strings H2D,
+    decompress (the last synthesis layer writes the quantised uint8 image), x_hat D2H.  The host
+    waits twice per batch: for batch k's strings after it has queued the compress of the next
+    `back_lag` batches, and for its x_hat when the slot is reused, host_slots - back_lag batches
+    after the decompress was queued.  Both waits have to span several batch times or the host,
+    not the GPU, sets the pace (a decompress is one serial decode per image and takes longer
+    than two batch times).
+
+    The coder's status words travel with the strings: a batch whose encode overflowed its slab
+    is re-run with the safe slab size before its decode is queued, and a batch is delivered only
+    after its decode status has been looked at.  String slabs are sized from the traffic seen
+    (1.25 x the longest string so far) instead of the 2-bytes-per-symbol bound, which halves the
+    string bytes that cross PCIe.
 
     Pinned staging buffers are allocated once per pipeline slot and reused (page-locking
     memory synchronises the device).  Results are delivered in order through
@@ -224,6 +237,7 @@ class Pipeline(object):
     (sequences of bytes over the slot's pinned slab) and `x_hat_u8` is a view of the slot's
     pinned buffer, all valid during the callback.  Without a callback the results are copied
     out (strings as lists of bytes) and returned as a list."""
+    import time
     from compression_b200.python.ops import range_coding_ops as rc
     model, dev = self.model, self.model.device
     n, nslots = len(batches_u8), self.host_slots
@@ -232,19 +246,30 @@ class Pipeline(object):
       slots = self._slots = [dict() for _ in range(nslots)]
     out_list = [] if on_result is None else None
     self.h2d_bytes = self.d2h_bytes = 0     # per batch, counted from the tensors copied
+    waited = [0.0]
+    t_start = time.perf_counter()
     cur = self._fork()
 
-    def pinned(slot, name, shape, dtype):
-      t = slot.get(name)
-      if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
-        t = slot[name] = torch.empty(tuple(shape), dtype=dtype, pin_memory=True)
-      return t
+    def wait(ev):
+      t0 = time.perf_counter()
+      ev.synchronize()
+      waited[0] += time.perf_counter() - t0
 
-    def deliver(slot):
+    def pinned(slot, name, shape, dtype):
+      # a view of the slot's page-locked storage for `name`, grown (never shrunk) on demand:
+      # the slab sizes settle after the first batches and no page-locking happens after that
+      need = int(np.prod(shape)) * torch.empty((), dtype=dtype).element_size()
+      store = slot.get(name)
+      if store is None or store.numel() < need:
+        store = slot[name] = torch.empty((max(need, 16),), dtype=torch.uint8, pin_memory=True)
+      return store[:need].view(dtype).view(tuple(shape))
+
+    def deliver(slot, checks):
       k = slot.pop("pending", None)
       if k is None:
         return
-      slot["done"].synchronize()
+      wait(slot["done"])
+      checks.verify(("back", k))        # corrupt string: raises before anything is delivered
       if on_result is not None:
         on_result(k, slot["host"], slot["x_hat"])
       else:
@@ -252,12 +277,12 @@ class Pipeline(object):
         out_list.append((Compressed(list(h.string), list(h.side_string), h.x_shape, h.y_shape,
                                     h.z_shape), slot["x_hat"].clone()))
 
-    def issue_front(k):
-      slot, st = slots[k % nslots], self.streams[k % self.depth]
-      deliver(slot)                      # the slot's previous batch must be out of its buffers
+    def front_work(k, slot, st, checks, cap):
+      checks.tag = ("front", k)
       with torch.cuda.stream(st):
-        x = batches_u8[k].to(dev, non_blocking=True).float() / 255
-        c = model.compress(x, self._stagger(k, st))
+        x = batches_u8[k].to(dev, non_blocking=True)
+        c = model.compress(x, self._stagger(k, st) if cap is not False else None,
+                           cap=cap or None)
         staged = []
         for name, (slab, nbytes) in (("y", c.string), ("z", c.side_string)):
           hs = pinned(slot, name + "_slab", slab.shape, torch.uint8)
@@ -267,46 +292,66 @@ class Pipeline(object):
           staged.append((hs, hn))
         ev = torch.cuda.Event()
         ev.record(st)
-      slot["front"] = (c, staged, ev)
+      return c, staged, ev
+
+    def issue_front(k, checks):
+      slot, st = slots[k % nslots], self.streams[k % self.depth]
+      deliver(slot, checks)              # the slot's previous batch must be out of its buffers
+      slot["front"] = front_work(k, slot, st, checks, self._cap)
       if k == 0:
         self.h2d_bytes += batches_u8[k].numel()
-        self.d2h_bytes += sum(hs.numel() + 4 * hn.numel() for hs, hn in staged)
 
-    def issue_back(k):
+    def issue_back(k, checks):
       slot, st = slots[k % nslots], self.streams[k % self.depth]
       c, staged, ev = slot.pop("front")
-      ev.synchronize()                   # the strings are in host memory now
+      wait(ev)                           # the strings and their status are in host memory now
+      try:
+        checks.verify(("front", k))
+      except self._lib.CudaError:
+        # a string outgrew the learnt slab size: once more with the safe default (rare)
+        self._cap = None
+        c, staged, ev = front_work(k, slot, st, checks, False)
+        wait(ev)
+        checks.verify(("front", k))
+      longest = (int(staged[0][1].max()), int(staged[1][1].max()))
+      if self._cap is None or longest[0] > self._cap[0] / 1.125 or longest[1] > self._cap[1] / 1.125:
+        want = tuple(int(1.25 * v) + 64 + (-(int(1.25 * v) + 64)) % 16 for v in longest)
+        self._cap = want if self._cap is None else (max(want[0], self._cap[0]),
+                                                    max(want[1], self._cap[1]))
       host = Compressed(HostStrings(*staged[0]), HostStrings(*staged[1]), c.x_shape, c.y_shape,
                         c.z_shape)
+      checks.tag = ("back", k)
       with torch.cuda.stream(st):
         # back to the device straight from the pinned slabs the strings arrived in
         dev_strings = []
         for hs, hn in staged:
           dev_strings.append((hs.to(dev, non_blocking=True), hn.to(dev, non_blocking=True)))
-          if k == 0:
-            self.h2d_bytes += hs.numel() + 4 * hn.numel()
         dc = Compressed(dev_strings[0], dev_strings[1], c.x_shape, c.y_shape, c.z_shape)
-        x_hat = quantize_image(model.decompress(dc))
+        x_hat = model.decompress(dc, out_dtype=torch.uint8)
         out = pinned(slot, "x_hat", x_hat.shape, torch.uint8)
         out.copy_(x_hat, non_blocking=True)
         done = torch.cuda.Event()
         done.record(st)
       slot["host"], slot["done"], slot["pending"] = host, done, k
-      if k == 0:
-        self.d2h_bytes += out.numel()
+      if k == n - 1:                     # bytes per batch at the steady-state slab size
+        strings = sum(hs.numel() + 4 * hn.numel() for hs, hn in staged)
+        self.d2h_bytes = strings + out.numel()
+        self.h2d_bytes = batches_u8[k].numel() + strings
 
-    with rc.deferred_checks():
+    with rc.deferred_checks() as checks:
       for k in range(n + self.back_lag):
         if k < n:
-          issue_front(k)
+          issue_front(k, checks)
         j = k - self.back_lag
         if 0 <= j < n:
-          issue_back(j)
+          issue_back(j, checks)
       self._join(cur)
       first = max(0, n - nslots)
       for k in range(first, n):           # remaining deliveries, oldest first
-        deliver(slots[k % nslots])
+        deliver(slots[k % nslots], checks)
     cur.synchronize()
+    total = time.perf_counter() - t_start
+    self.host_wait_s, self.host_busy_s = waited[0], total - waited[0]
     return out_list
 
 
@@ -349,27 +394,34 @@ class Bmshj2018Model(object):
     sigma = sigma[:, :y.shape[1], :y.shape[2], :].contiguous()
     return y, z, sigma
 
-  def compress(self, x, after_analysis=None):
-    """`after_analysis`: called once the transforms are queued and before the entropy coder is
-    (the pipeline records an event there to stagger its first wave of batches)."""
+  def compress(self, x, after_analysis=None, cap=None):
+    """x: float32 [B,H,W,3] in [0,1], or the uint8 image itself (a byte b stands for b / 255 as
+    in read_png, bmshj2018.py:53-57; the first analysis layer reads the bytes directly).
+    `after_analysis`: called once the transforms are queued and before the entropy coder is
+    (the pipeline records an event there to stagger its first wave of batches).  `cap`:
+    (bytes per image of the string slab, of the side-string slab) or None for the safe default
+    of 2 bytes per symbol; a too small slab is reported through the coder's status words."""
     x = x.to(self.device)
     y, z, sigma = self.analyse(x)
     if after_analysis is not None:
       after_analysis()
-    side_string = self.entropy_bottleneck.compress_device(z)
-    string = self._conditional(sigma).compress_device(y)
+    cap_y, cap_z = cap if cap is not None else (None, None)
+    side_string = self.entropy_bottleneck.compress_device(z, cap=cap_z)
+    string = self._conditional(sigma).compress_device(y, cap=cap_y)
     return Compressed(string, side_string, tuple(x.shape[1:-1]), tuple(y.shape[1:-1]),
                       tuple(z.shape[1:-1]))
 
   # ---- bmshj2018.py:383-399 ----------------------------------------------------------------
-  def decompress(self, c):
+  def decompress(self, c, out_dtype=torch.float32):
+    """-> x_hat [B,H,W,3]: float32, or with out_dtype=torch.uint8 the quantised image
+    (quantize_image, bmshj2018.py:60-63, fused into the last synthesis layer)."""
     nf = self.num_filters
     z_hat = self.entropy_bottleneck.decompress_device(
         c.side_string, tuple(c.z_shape) + (nf,), channels=nf, out_dtype=torch.bfloat16)
     sigma = self.hyper_synthesis_transform(z_hat)
     sigma = sigma[:, :c.y_shape[0], :c.y_shape[1], :].contiguous()
     y_hat = self._conditional(sigma).decompress_device(c.string, out_dtype=torch.bfloat16)
-    x_hat = self.synthesis_transform(y_hat)
+    x_hat = self.synthesis_transform(y_hat, out_dtype=out_dtype)
     return x_hat[:, :c.x_shape[0], :c.x_shape[1], :]
 
   # ---- verbose branch of compress (bmshj2018.py:314-333) ----------------------------------
@@ -473,18 +525,13 @@ class Bmshj2018Trainer(_trainer_base()):
   `bls2017.Bls2017Trainer`: all trainables in one flat bucket (+ the quantiles in a second),
   conv gradients through the CUDA kernels, one all-reduce per bucket, fused TF-Adam updates,
   CDF table rebuild per rank.  The Gaussian likelihood and its gradient
-  (entropy_models.py:916-932, :965-969) are torch ops."""
+  (entropy_models.py:916-932, :965-969, with the lower bounds on the scale, :822-825, and on the
+  likelihood, :181-184) are one CUDA kernel each way (`_GaussianLikelihood`)."""
 
   def _gaussian_likelihood(self, y_tilde, sigma):
-    from compression_b200.python.ops import math_ops
-    model = self.model
-    # entropy_models.py:822-825: scales are bounded below by the smallest table entry
-    scale = math_ops.lower_bound(sigma, float(np.float32(model.scale_table[0])))
-    values = torch.abs(y_tilde)
-    const = -(2 ** -0.5)
-    upper = 0.5 * torch.erfc(const * ((0.5 - values) / scale))
-    lower = 0.5 * torch.erfc(const * ((-0.5 - values) / scale))
-    return math_ops.lower_bound(upper - lower, model._gc_tables.likelihood_bound)
+    gc = self.model._gc_tables
+    return entropy_models._GaussianLikelihood.apply(
+        y_tilde.float(), sigma.float(), gc._effective_bound(), max(gc.likelihood_bound, 0.0))
 
   def losses(self, x, noise=None):
     """x float32 [B,H,W,3] in [0,1]; noise = (noise_y, noise_z) or None for fresh U(-.5,.5)

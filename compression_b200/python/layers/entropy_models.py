@@ -133,6 +133,41 @@ class _EbLikelihood(torch.autograd.Function):
     return gx, gp, None
 
 
+class _GaussianLikelihood(torch.autograd.Function):
+  """GaussianConditional._likelihood with both lower bounds (entropy_models.py:822-825, :916-932,
+  :965-969, :181-184) as one CUDA kernel each way: forward tfc_gaussian_call (mode 1), backward
+  tfc_gaussian_likelihood_backward (the lower_bound gradient rule of math_ops.py:61-74 on the
+  scale and on the likelihood)."""
+
+  @staticmethod
+  def forward(ctx, values, sigma, scale_bound, likelihood_bound):
+    values, sigma = values.contiguous(), sigma.contiguous()
+    lik = torch.empty_like(values)
+    _lib.check(_lib.lib().tfc_gaussian_call(
+        _lib.ptr(values), _lib.ptr(sigma), _i64(values.numel()), _f32(scale_bound),
+        _f32(likelihood_bound), 1, ctypes.c_void_p(0), _lib.ptr(lik),
+        _lib.stream_ptr(values.device)))
+    ctx.save_for_backward(values, sigma)
+    ctx.bounds = (scale_bound, likelihood_bound)
+    return lik
+
+  @staticmethod
+  def backward(ctx, grad):
+    values, sigma = ctx.saved_tensors
+    grad = grad.contiguous()
+    gv, gs = torch.empty_like(values), torch.empty_like(sigma)
+    _lib.check(_lib.lib().tfc_gaussian_likelihood_backward(
+        _lib.ptr(values), _lib.ptr(sigma), _lib.ptr(grad), _i64(values.numel()),
+        _f32(ctx.bounds[0]), _f32(ctx.bounds[1]), _lib.ptr(gv), _lib.ptr(gs),
+        _lib.stream_ptr(values.device)))
+    return gv, gs, None, None
+
+
+def _wants_grad(*tensors):
+  return torch.is_grad_enabled() and any(
+      isinstance(t, torch.Tensor) and t.requires_grad for t in tensors)
+
+
 class EntropyBottleneck(EntropyModel):
   """Entropy bottleneck layer (factorised prior) — entropy_models.py:298-704."""
 
@@ -176,9 +211,22 @@ class EntropyBottleneck(EntropyModel):
     self.built = True
     self.refresh()
 
+  def variables(self):
+    return list(self.matrices) + list(self.biases) + list(self.factors) + [self.quantiles]
+
+  def _versions(self):
+    return tuple((id(v), v._version) for v in self.variables())
+
+  def _sync(self):
+    """The packed density parameters and the medians are caches of the variables: re-derive
+    them when a variable was replaced or written in place (an optimizer step) since."""
+    if getattr(self, "_derived_from", None) != self._versions():
+      self.refresh()
+
   def refresh(self):
     """Re-derives everything that is a pure function of the variables except the CDF tables
     (those change only through `update()`, like the reference's update op)."""
+    self._derived_from = self._versions()
     q = self.quantiles
     self._medians = q[:, 0, 1].detach().contiguous()
     minima = torch.clamp(torch.ceil(self._medians - q[:, 0, 0]).to(torch.int32), min=0)
@@ -279,10 +327,17 @@ class EntropyBottleneck(EntropyModel):
     """entropy_models.py:148-187 -> (values, likelihood)."""
     x = self._check_inputs(inputs)
     self._ensure_built(x)
+    self._sync()
     mode = 0
     if training:  # additive uniform noise (entropy_models.py:605-607)
       x = x + (torch.rand_like(x) - .5)
       mode = 1
+      if _wants_grad(x, *self.variables()):
+        # the reference's differentiable training entry point: gradients flow to the inputs
+        # and to the density variables through the likelihood kernels
+        if not self.filters:
+          raise NotImplementedError("the likelihood gradient kernel needs a hidden layer")
+        return x, self.likelihood_training(x)
     values = torch.empty_like(x) if not training else x
     lik = torch.empty_like(x)
     nl, fw = self._filter_args()
@@ -294,6 +349,7 @@ class EntropyBottleneck(EntropyModel):
     return values, lik
 
   def _quantize_symbols(self, x):
+    self._sync()
     sym = torch.empty(x.shape, dtype=torch.int32, device=x.device)
     _lib.check(_lib.lib().tfc_eb_symbols(
         _lib.ptr(x), _i64(x.numel()), _i32(self.channels), _lib.ptr(self._medians),
@@ -301,6 +357,7 @@ class EntropyBottleneck(EntropyModel):
     return sym
 
   def _dequantize(self, symbols, out_dtype=torch.float32):
+    self._sync()
     out = torch.empty(symbols.shape, dtype=out_dtype, device=symbols.device)
     _lib.check(_lib.lib().tfc_eb_dequantize(
         _lib.ptr(symbols), _i64(symbols.numel()), _i32(self.channels), _lib.ptr(self._medians),
@@ -510,6 +567,10 @@ class GaussianConditional(SymmetricConditional):
     if sigma.shape != x.shape:
       raise ValueError("`scale` %s and inputs %s differ in shape" % (tuple(sigma.shape),
                                                                      tuple(x.shape)))
+    if training and _wants_grad(x, sigma):
+      lik = _GaussianLikelihood.apply(x, sigma, self._effective_bound(),
+                                      max(self.likelihood_bound, 0.0))
+      return self._uncentered(x), lik
     values = torch.empty_like(x) if not training else x
     lik = torch.empty_like(x)
     _lib.check(_lib.lib().tfc_gaussian_call(

@@ -6,8 +6,9 @@ padding geometry (`:742-758`, `ops/padding_ops.py`), correlation + downsampling 
 padding (`:487-524`) and upsampled convolution via the transposed-conv formulation
 (`:629-707`) — and reduces each case to the one normalised form the CUDA kernels implement
 (see `tfc_conv_desc` in include/tfc_b200.h).  Combinations the reference itself does not
-implement, and those outside the codecs' hot path (1-D/3-D, `same_reflect`,
-`channel_separable`, `channels_first`), raise NotImplementedError like `:393-401`.
+implement, and those outside the codecs' hot path (1-D/3-D, `channel_separable`), raise
+NotImplementedError like `:393-401`; `same_reflect` and `channels_first` are reduced on the host
+side to the same kernels (reflection pre-pad by gather, layout conversion in and out).
 """
 import ctypes
 import math
@@ -39,7 +40,14 @@ def _dtype_code(dt):
     return 0
   if dt == torch.bfloat16:
     return 1
-  raise ValueError("unsupported dtype %s (float32 or bfloat16)" % dt)
+  if dt == torch.uint8:
+    return 2   # TFC_U8: an 8-bit image (input: byte / 255; output: quantize_image)
+  raise ValueError("unsupported dtype %s (float32, bfloat16 or uint8 images)" % dt)
+
+
+def quantize_image(image):
+  """examples/bmshj2018.py:60-63: saturate_cast<uint8>(round(image * 255))."""
+  return torch.clamp(torch.round(image * 255), 0, 255).to(torch.uint8)
 
 
 def variance_scaling_init(shape, generator=None, device="cpu", dtype=torch.float32):
@@ -104,7 +112,10 @@ class SignalConv2D(object):
     self.out_dtype = torch.float32  # dtype of the produced activations (float32 | bfloat16)
     self.built = False
     self._eff = None
-    self._ws = {}   # (device, stream) -> [buffer, effective weights staged in it, GDN params]
+    self._geom = {}
+    # (device, stream) -> [buffer, effective weights staged in it, GDN params, kernel path that
+    # staged them] — the repacked layout belongs to the path (tfc_signal_conv2d_path)
+    self._ws = {}
 
   # ---- reference's capability gaps ------------------------------------------------------
   def _raise_notimplemented(self):
@@ -141,6 +152,7 @@ class SignalConv2D(object):
     self.input_channels = cin
     self.built = True
     self._eff = None
+    self._geom = {}
 
   def invalidate(self):
     """Call after changing kernel_var / bias_var so the effective weights are recomputed."""
@@ -287,8 +299,10 @@ class SignalConv2D(object):
     if x.shape[-1] != self.input_channels:
       raise ValueError("layer built for %d input channels, got %d"
                        % (self.input_channels, x.shape[-1]))
-    if x.dtype not in (torch.float32, torch.bfloat16):
+    if x.dtype not in (torch.float32, torch.bfloat16, torch.uint8):
       x = x.float()
+    if x.dtype == torch.uint8 and self.padding == "same_reflect":
+      x = x.float() / 255
     want_shape = tuple(self.compute_output_shape(x.shape))
     mode, crop = None, None
     if self.padding == "same_reflect":
@@ -312,28 +326,56 @@ class SignalConv2D(object):
                  pad_left=pad_begin[1], act=act, in_dtype=_dtype_code(x.dtype),
                  out_dtype=_dtype_code(out_dtype), impl=self.impl, flags=0)
     L = _lib.lib()
-    L.tfc_signal_conv2d_workspace.restype = ctypes.c_size_t
-    need = int(L.tfc_signal_conv2d_workspace(ctypes.byref(d)))
+    # kernel path and workspace size of this geometry (two C calls, cached per layer)
+    gkey = (n, h, w, d.in_dtype, d.out_dtype, mode, post is not None, self.impl)
+    geom = self._geom.get(gkey)
+    if geom is None:
+      L.tfc_signal_conv2d_workspace.restype = ctypes.c_size_t
+      path = int(L.tfc_signal_conv2d_path(ctypes.byref(d)))
+      # 8-bit images are read / written by the thin-input / thin-output kernels only (paths 4,
+      # 3); anywhere else the scaling and the quantisation are torch ops around a float32 call
+      scale_before = quantize_after = False
+      if x.dtype == torch.uint8 and path != 4:
+        scale_before, d.in_dtype = True, _dtype_code(torch.float32)
+        path = int(L.tfc_signal_conv2d_path(ctypes.byref(d)))
+      if out_dtype == torch.uint8 and (path != 3 or post is not None):
+        quantize_after, d.out_dtype = True, _dtype_code(torch.float32)
+        path = int(L.tfc_signal_conv2d_path(ctypes.byref(d)))
+      need = int(L.tfc_signal_conv2d_workspace(ctypes.byref(d)))
+      geom = self._geom[gkey] = (path, need, scale_before, quantize_after)
+    path, need, scale_before, quantize_after = geom
+    if scale_before:
+      x = x.float() / 255
+      d.in_dtype = _dtype_code(torch.float32)
+    if quantize_after:
+      out_dtype = torch.float32
+      d.out_dtype = _dtype_code(torch.float32)
     # One workspace per CUDA stream (concurrent batches on different streams must not share
     # scratch); the repacked weights stay valid in it until the effective weights change.
     stream = _lib.stream_ptr(x.device)
     key = (x.device.index, stream.value)
     rec = self._ws.get(key)
     if rec is None or rec[0].numel() < need:
-      rec = [torch.empty((max(need, 256),), dtype=torch.uint8, device=x.device), None, None]
+      rec = [torch.empty((max(need, 256),), dtype=torch.uint8, device=x.device), None, None, -1]
       self._ws[key] = rec
     gdn_params = self.activation._cache if act in (ACT_GDN, ACT_IGDN) else None
-    if rec[1] is self._eff and rec[2] is gdn_params and rec[1] is not None:
+    # The staged weights are reusable only by the kernel path that wrote them: the path depends
+    # on the input dtype and on h % sd / w % sd as well as on the layer, every path has its own
+    # layout, and the CUDA-core path (0) uses the workspace as scratch.
+    if (path > 0 and rec[3] == path and rec[1] is self._eff and rec[2] is gdn_params
+        and rec[1] is not None):
       d.flags |= CONV_WEIGHTS_STAGED
     out = torch.empty((n, ho, wo, self.filters), dtype=out_dtype, device=x.device)
     _lib.check(L.tfc_signal_conv2d(
         ctypes.byref(d), _lib.ptr(x), _lib.ptr(wgt), _lib.ptr(bias), _lib.ptr(beta),
         _lib.ptr(gamma), _lib.ptr(out), _lib.ptr(rec[0]), ctypes.c_size_t(rec[0].numel()),
         stream))
-    rec[1], rec[2] = self._eff, gdn_params
+    rec[1], rec[2], rec[3] = (self._eff, gdn_params, path) if path > 0 else (None, None, -1)
     if crop is not None:
       out = out[:, crop[0]:crop[0] + want_shape[1], crop[1]:crop[1] + want_shape[2], :].contiguous()
       assert tuple(out.shape) == want_shape
     if post is not None:
       out = post(out)
+    if quantize_after:
+      out = quantize_image(out)
     return out

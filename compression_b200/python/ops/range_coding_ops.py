@@ -30,39 +30,75 @@ _i64 = ctypes.c_int64
 class deferred_checks(object):
   """Context manager: inside it the batched coder calls do not synchronise with the host to
   look at their per-stream status words (capacity overflow on encode, corrupt string on
-  decode); the status tensors are collected and checked once, on exit.  This is what lets
-  several batches be in flight on different CUDA streams.  An encode that overflowed its slab
-  cannot be retried transparently in this mode: exit raises and the caller re-runs the batch
-  with a larger `cap`.  Per thread."""
+  decode).  Each call's status words are copied to a small pinned host buffer on the stream that
+  produced them (one 4*S-byte copy and an event, no reduction kernel) and filed under the
+  current `tag`; the owner of the block verifies a tag when its results are about to be used —
+  `verify(tag)` waits for that call's event only — and everything still pending is verified on
+  exit.  This is what lets several batches be in flight on different CUDA streams while no
+  result is delivered, and no decode queued, before the status of what it depends on has been
+  looked at.  An encode that overflowed its slab cannot be retried transparently in this mode:
+  verify raises and the caller re-runs the batch with a larger `cap`.  Per thread."""
   _tls = __import__("threading").local()
 
   def __enter__(self):
     self._prev = getattr(self._tls, "pending", None)
-    self._tls.pending = []
+    self._tls.pending = self
+    self._by_tag = {}        # tag -> [(what, pinned host words, count, event)]
+    self._order = []         # tags in the order they first appeared
+    self._pool = []          # pinned int32 buffers ready for reuse
+    self.tag = None
     return self
 
   def __exit__(self, exc_type, exc, tb):
-    pending, self._tls.pending = self._tls.pending, self._prev
+    self._tls.pending = self._prev
     if exc_type is None:
-      self._verify(pending)
+      self.flush()
     return False
 
-  def flush(self):
-    pending, self._tls.pending = self._tls.pending, []
-    self._verify(pending)
+  def add(self, what, status):
+    n = int(status.numel())
+    host = None
+    for i, buf in enumerate(self._pool):
+      if buf.numel() >= n:
+        host = self._pool.pop(i)
+        break
+    if host is None:
+      host = torch.empty((max(n, 256),), dtype=torch.int32, pin_memory=True)
+    host[:n].copy_(status.reshape(-1), non_blocking=True)
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(status.device))
+    if self.tag not in self._by_tag:
+      self._by_tag[self.tag] = []
+      self._order.append(self.tag)
+    self._by_tag[self.tag].append((what, host, n, ev))
 
-  @staticmethod
-  def _verify(pending):
-    if not pending:
+  def verify(self, tag):
+    """Waits for the calls filed under `tag` and raises if any of their streams failed."""
+    entries = self._by_tag.pop(tag, None)
+    if entries is None:
       return
-    bad = torch.stack([(st != 0).any() for _, st in pending]).cpu().tolist()
-    for (what, _), b in zip(pending, bad):
-      if b:
-        if what == "encode":
-          raise _lib.CudaError("range encode output slab too small (deferred check): re-run "
-                               "the batch with a larger `cap`")
-        raise InvalidArgumentError(
-            "corrupt range-coded string (decoder ran past the end of a CDF)")
+    self._order.remove(tag)
+    bad = None
+    for what, host, n, ev in entries:
+      ev.synchronize()
+      if bad is None and n and bool(host[:n].numpy().any()):
+        bad = what
+      self._pool.append(host)
+    if bad == "encode":
+      raise _lib.CudaError("range encode output slab too small (deferred check): re-run "
+                           "the batch with a larger `cap`")
+    if bad is not None:
+      raise InvalidArgumentError(
+          "corrupt range-coded string (decoder ran past the end of a CDF)")
+
+  def drain(self, keep):
+    """Verifies the oldest tags until at most `keep` are pending (bounds the backlog of a long
+    pipeline; the calls verified are `keep` tags old and have long finished)."""
+    while len(self._order) > max(0, int(keep)):
+      self.verify(self._order[0])
+
+  def flush(self):
+    self.drain(0)
 
   @classmethod
   def collector(cls):
@@ -134,7 +170,7 @@ def unbounded_index_range_encode_batch(data, index, cdf, cdf_size, offset, preci
         _i64(cap), _lib.ptr(nbytes), _lib.ptr(status), _lib.stream_ptr(dev)))
     pending = deferred_checks.collector()
     if pending is not None:
-      pending.append(("encode", status))
+      pending.add("encode", status)
       break
     if attempt == 0 and S and bool((status != 0).any()):
       cap = int(nbytes.max().item())
@@ -171,7 +207,7 @@ def unbounded_index_range_decode_batch(enc, nbytes, index, cdf, cdf_size, offset
       int(debug_level), _lib.ptr(out), _lib.ptr(status), _lib.stream_ptr(dev)))
   pending = deferred_checks.collector()
   if pending is not None:
-    pending.append(("decode", status))
+    pending.add("decode", status)
   elif check and S and n and bool((status != 0).any()):
     raise InvalidArgumentError("corrupt range-coded string (decoder ran past the end of a CDF)")
   return out
@@ -220,6 +256,11 @@ def range_decode_batch(enc, nbytes, shape, cdf, precision, debug_level=1, shared
       _lib.ptr(enc), _i64(cap), _lib.ptr(nbytes), _i64(S), _shape_arr(dshape), len(dshape),
       _lib.ptr(cdf), _shape_arr(cshape), len(cshape), _i64(cstride), int(precision),
       int(debug_level), _lib.ptr(out), _lib.ptr(status), _lib.stream_ptr(dev)))
+  pending = deferred_checks.collector()
+  if pending is not None:
+    pending.add("decode", status)
+  elif S and out.numel() and bool((status != 0).any()):
+    raise InvalidArgumentError("corrupt range-coded string (decoder ran past the end of a CDF)")
   return out
 
 

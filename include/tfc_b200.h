@@ -193,6 +193,17 @@ int tfc_gaussian_call(const float* d_y, const float* d_sigma, int64_t count, flo
                       float likelihood_bound, int mode, float* d_values, float* d_lik,
                       void* stream);
 
+/* Gradient of the likelihood above in mode 1 (the training graph of examples/bmshj2018.py:
+ * 201-282; TF derives it through entropy_models.py:916-932, :965-969 and the two lower_bound
+ * ops, ops/math_ops.py:61-74, on the scale and on the likelihood):
+ *   d_grad_y[i]     = g * d lik / d y        d_grad_sigma[i] = g * d lik / d sigma
+ * with g = d_grad_lik[i] passed where lik >= likelihood_bound or g < 0, and the scale gradient
+ * passed where sigma >= scale_bound or it is negative.  A bound <= 0 is disabled. */
+int tfc_gaussian_likelihood_backward(const float* d_y, const float* d_sigma,
+                                     const float* d_grad_lik, int64_t count, float scale_bound,
+                                     float likelihood_bound, float* d_grad_y,
+                                     float* d_grad_sigma, void* stream);
+
 /* Compress-side fusion (entropy_models.py:221 + :869-881 + :895-907):
  *   d_symbols = int32(floor(y + 0.5))              (d_y / d_symbols may be NULL)
  *   d_indexes = (levels-1) - #{k < levels-1 : max(sigma, scale_bound) <= table[k]}
@@ -213,7 +224,12 @@ int tfc_abs_to_bf16(const float* d_x, int64_t count, void* d_out_bf16, void* str
  * Transforms — SignalConv2D and GDN (python/layers/signal_conv.py, python/layers/gdn.py)
  * ---------------------------------------------------------------------------------------- */
 
-typedef enum { TFC_F32 = 0, TFC_BF16 = 1 } tfc_dtype;
+/* TFC_U8: 8-bit images at the two ends of the codec.  As an INPUT dtype (thin-input kernel,
+ * cin == 3) a byte b stands for b / 255, the scaling of read_png (examples/bmshj2018.py:53-57);
+ * as an OUTPUT dtype (thin-output kernel, cout <= 4) the result is quantize_image
+ * (examples/bmshj2018.py:60-63): saturate_cast<uint8>(round(x * 255)), round half to even.  Other
+ * kernels return TFC_ERR_UNIMPLEMENTED for it. */
+typedef enum { TFC_F32 = 0, TFC_BF16 = 1, TFC_U8 = 2 } tfc_dtype;
 typedef enum {
   TFC_ACT_NONE = 0,
   TFC_ACT_RELU = 1, /* tf.nn.relu (examples/bmshj2018.py:153,157,183,187) */
@@ -255,6 +271,15 @@ typedef struct {
  * the same layer parameters and the same workspace: skip the repack kernels.  The weight area
  * sits at the start of the workspace and does not depend on n/h/w. */
 #define TFC_CONV_WEIGHTS_STAGED 1
+
+/* Which kernel tfc_signal_conv2d will run for this descriptor (it depends on in_dtype and on
+ * h % sd / w % sd, not only on the layer): 0 CUDA-core tiled kernel, 1 tcgen05 implicit GEMM,
+ * 2 space-to-depth + tcgen05, 3 scatter GEMM (thin output), 4 software im2col + tcgen05 (thin
+ * input), 5 zero-extended copy + tcgen05 implicit GEMM; -1 for an invalid descriptor.  Each path
+ * keeps its own weight layout at the start of the workspace, and path 0 uses the workspace as
+ * plain scratch: TFC_CONV_WEIGHTS_STAGED is only valid when the previous call on the same
+ * workspace took the same non-zero path with the same weights. */
+int tfc_signal_conv2d_path(const tfc_conv_desc* desc);
 
 size_t tfc_signal_conv2d_workspace(const tfc_conv_desc* desc);
 int tfc_signal_conv2d(const tfc_conv_desc* desc, const void* d_in, const float* d_w,
