@@ -271,11 +271,11 @@ class Pipeline(object):
       wait(slot["done"])
       checks.verify(("back", k))        # corrupt string: raises before anything is delivered
       if on_result is not None:
-        on_result(k, slot["host"], slot["x_hat"])
+        on_result(k, slot["host"], slot["x_hat_view"])
       else:
         h = slot["host"]
         out_list.append((Compressed(list(h.string), list(h.side_string), h.x_shape, h.y_shape,
-                                    h.z_shape), slot["x_hat"].clone()))
+                                    h.z_shape), slot["x_hat_view"].clone()))
 
     def front_work(k, slot, st, checks, cap):
       checks.tag = ("front", k)
@@ -332,7 +332,7 @@ class Pipeline(object):
         out.copy_(x_hat, non_blocking=True)
         done = torch.cuda.Event()
         done.record(st)
-      slot["host"], slot["done"], slot["pending"] = host, done, k
+      slot["host"], slot["done"], slot["pending"], slot["x_hat_view"] = host, done, k, out
       if k == n - 1:                     # bytes per batch at the steady-state slab size
         strings = sum(hs.numel() + 4 * hn.numel() for hs, hn in staged)
         self.d2h_bytes = strings + out.numel()

@@ -501,3 +501,108 @@ def test_thin_input_conv_unsupported_reports(tfc):
   layer = tfc.SignalConv2D(8, (3, 3), corr=True, padding="same_zeros", impl=4)
   with pytest.raises(NotImplementedError, match="3 channels and 5x5 / 9x9"):
     layer(torch.zeros((1, 8, 8, 3), device="cuda"))
+
+
+def test_one_layer_alternating_dtypes_and_sizes(tfc):
+  """the repacked weights in a layer's workspace belong to the kernel path that wrote
+  them (tfc_signal_conv2d_path).  One layer, one stream: bf16 / fp32 inputs and even / odd sizes
+  interleaved — every call must equal a fresh layer's result for the same input."""
+  rng = np.random.default_rng(31)
+  cin, cout, k = 64, 64, 5
+  kern = (rng.integers(-8, 9, size=(k, k, cin, cout)) / 8.0).astype(np.float32)
+  b = (rng.integers(-8, 9, size=cout) / 4.0).astype(np.float32)
+
+  def make():
+    layer = tfc.SignalConv2D(cout, (k, k), corr=True, strides_down=2, padding="same_zeros",
+                             use_bias=True, activation=tfc.GDN(), kernel_parameterizer=None,
+                             kernel_initializer=_static(kern), bias_initializer=_static(b))
+    layer.build(cin, "cuda")
+    return layer
+
+  shared = make()
+  cases = [(torch.bfloat16, 16, 24), (torch.float32, 16, 24), (torch.bfloat16, 16, 24),
+           (torch.bfloat16, 15, 23), (torch.float32, 15, 23), (torch.bfloat16, 16, 24),
+           (torch.bfloat16, 15, 23), (torch.bfloat16, 16, 24)]
+  paths = set()
+  for dt, h, w in cases:
+    x = torch.from_numpy(rng.integers(-3, 4, size=(2, h, w, cin)).astype(np.float32)).cuda().to(dt)
+    got = shared(x, out_dtype=torch.float32)
+    want = make()(x, out_dtype=torch.float32)
+    assert torch.equal(got, want), (dt, h, w)
+    paths.add(next(iter(shared._ws.values()))[3])
+  assert len(paths) >= 2, paths           # the sequence really crossed kernel paths
+
+
+def test_uint8_images_first_and_last_layer(tfc):
+  """TFC_U8: the first analysis layer reads the image bytes (b / 255, read_png) and the last
+  synthesis layer writes quantize_image(x) = saturate_cast<uint8>(round(x * 255)); both must
+  equal the float path followed / preceded by the torch ops, also where the thin kernels do not
+  apply (fallback)."""
+  from compression_b200.python.layers import signal_conv
+  g = torch.Generator().manual_seed(5)
+  for h, w in ((64, 96), (33, 47)):         # TMA patches | rows that are not 16-byte multiples
+    u8 = torch.randint(0, 256, (2, h, w, 3), generator=g, dtype=torch.uint8).cuda()
+    a0 = tfc.SignalConv2D(192, (5, 5), corr=True, strides_down=2, padding="same_zeros",
+                          use_bias=True, activation=tfc.GDN())
+    a0.build(3, "cuda", g)
+    got = a0(u8, out_dtype=torch.bfloat16)
+    want = a0(u8.float() / 255, out_dtype=torch.bfloat16)
+    assert torch.equal(got, want), (h, w)
+  # a layer the thin-input kernel does not take (3x3): scaling by torch, same result
+  c3 = tfc.SignalConv2D(8, (3, 3), corr=True, padding="same_zeros")
+  c3.build(3, "cuda", g)
+  assert torch.equal(c3(u8), c3(u8.float() / 255))
+  for h, w in ((16, 24), (13, 31)):
+    y = (torch.randn((2, h, w, 192), generator=g) * 0.5).cuda().to(torch.bfloat16)
+    s3 = tfc.SignalConv2D(3, (5, 5), corr=False, strides_up=2, padding="same_zeros",
+                          use_bias=True, bias_initializer=_static(np.array([.3, .5, .7], np.float32)))
+    s3.build(192, "cuda", g)
+    q = s3(y, out_dtype=torch.uint8)
+    f = s3(y, out_dtype=torch.float32)
+    assert q.dtype == torch.uint8 and tuple(q.shape) == (2, 2 * h, 2 * w, 3)
+    assert torch.equal(q, signal_conv.quantize_image(f))
+    assert int(q.min()) == 0 and int(q.max()) == 255      # both saturations exercised
+  # fallback: a layer the scatter kernel does not take
+  s = tfc.SignalConv2D(8, (3, 3), corr=True, padding="same_zeros")
+  s.build(3, "cuda", g)
+  x = torch.rand((1, 9, 9, 3), generator=g).cuda()
+  assert torch.equal(s(x, out_dtype=torch.uint8), signal_conv.quantize_image(s(x)))
+
+
+def test_entropy_models_training_true_is_differentiable(tfc):
+  """`entropy_bottleneck(y, training=True)` / `conditional(y, training=True)` are the
+  reference's differentiable training entry points (entropy_models.py:148-187): the rate term
+  must reach the inputs, the scale and the density variables, and the cached parameters must
+  follow the variables."""
+  from compression_b200.python.layers import entropy_models
+  g = torch.Generator().manual_seed(2)
+  eb = entropy_models.EntropyBottleneck()
+  eb.build(8, "cuda", g)
+  for group in (eb.matrices, eb.biases, eb.factors):
+    for i in range(len(group)):
+      group[i] = group[i].clone().requires_grad_()
+  y = (torch.randn((2, 4, 4, 8), generator=g) * 3).cuda().requires_grad_()
+  y_tilde, lik = eb(y, training=True)
+  assert lik.requires_grad and y_tilde.requires_grad
+  torch.log(lik).sum().backward()
+  assert y.grad is not None and float(y.grad.abs().sum()) > 0
+  assert all(m.grad is not None and float(m.grad.abs().sum()) > 0 for m in eb.matrices)
+  # no gradient wanted: the plain kernel path, same likelihood values for the same noise
+  with torch.no_grad():
+    torch.manual_seed(7)
+    _, lik0 = eb(y.detach(), training=True)
+  torch.manual_seed(7)
+  _, lik1 = eb(y, training=True)
+  assert torch.allclose(lik0, lik1.detach(), rtol=1e-5, atol=1e-7)
+  # the packed parameters follow an in-place update of a variable
+  before = eb(y.detach(), training=False)[1].clone()
+  with torch.no_grad():
+    eb.biases[0].add_(0.25)
+  after = eb(y.detach(), training=False)[1]
+  assert not torch.equal(before, after)
+  sigma = (torch.rand((2, 4, 4, 8), generator=g) * 2 + 0.05).cuda().requires_grad_()
+  gc = entropy_models.GaussianConditional(sigma, np.exp(np.linspace(np.log(0.11), np.log(256), 64)))
+  y2 = (torch.randn((2, 4, 4, 8), generator=g) * 2).cuda().requires_grad_()
+  _, lik2 = gc(y2, training=True)
+  torch.log(lik2).sum().backward()
+  assert float(y2.grad.abs().sum()) > 0 and float(sigma.grad.abs().sum()) > 0

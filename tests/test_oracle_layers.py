@@ -135,3 +135,21 @@ def test_eb_density_normalised_and_quantised():
   np.testing.assert_allclose(pm.sum(0), 1, atol=1e-4)
   sym = tfc_np.eb_symbols(x, medians)
   np.testing.assert_allclose(sym + medians, values, atol=1e-5)
+
+
+def test_cpu_bls2017_codec_round_trip():
+  """BASELINE configs[0] on the host (oracle/cpu_codec.py CpuBls2017, restating
+  /root/reference/examples/bls2017.py:205-305): the decoder returns the coded symbols and an
+  image of the input's size; different images give different strings."""
+  from oracle import cpu_codec, oracle_lib
+  coder = oracle_lib.load("best")
+  codec = cpu_codec.CpuBls2017(cpu_codec.random_weights_bls2017(128, 0), coder, threads=2)
+  rng = np.random.default_rng(0)
+  x = rng.random((2, 72, 104, 3)).astype(np.float32)          # not multiples of 16
+  c = codec.compress(x)
+  assert tuple(c["y_shape"]) == (5, 7) and c["y_sym"].shape == (2, 5, 7, 128)
+  x_hat, y_sym = codec.decompress(c)
+  assert x_hat.shape == x.shape and np.isfinite(x_hat).all()
+  np.testing.assert_array_equal(y_sym, c["y_sym"])
+  n = c["string"][1]
+  assert bytes(c["string"][0][0, :n[0]]) != bytes(c["string"][0][1, :n[1]])

@@ -223,3 +223,115 @@ def test_cluster_multicast_conv_gives_the_same_strings(setup):
     tfc.configure(conv_cluster=0)
   assert paired.string == base.string and paired.side_string == base.side_string
   assert torch.equal(x_hat, model.decompress(model.to_device(base)))
+
+
+# ---- a model that really reconstructs (the random-init PSNR test was vacuous) -------
+def _structured_model(seed=0, quant=24.0, jitter=8e-4):
+  """bmshj2018 wiring with identity-preserving kernels: the analysis transform is three
+  space-to-depth steps and a scaled 2x2 average, the synthesis transform its (pseudo-)inverse,
+  GDN / IGDN are the identity (gamma = 0, beta = 1), and EVERY weight carries a small random
+  jitter so that all taps and channels contribute.  PSNR of smooth images is ~27-30 dB."""
+  from compression_b200.examples import bmshj2018
+  from compression_b200.python.layers import gdn as gdn_lib
+  model = bmshj2018.Bmshj2018Model(192, "cuda", seed=seed)
+  g = torch.Generator().manual_seed(seed + 1)
+
+  def put(layer, w):
+    w = w + jitter * float(w.abs().max()) * torch.randn(w.shape, generator=g)
+    kp = layer.kernel_parameterizer
+    wd = w.to(layer.kernel_var.device)
+    layer.kernel_var = kp.init(wd) if kp is not None else wd
+    if isinstance(layer.activation, gdn_lib.GDN):
+      act = layer.activation
+      c = act.num_channels
+      act.reparam_gamma = act.gamma_parameterizer.init(torch.zeros((c, c), device=wd.device))
+      act.reparam_beta = act.beta_parameterizer.init(torch.ones((c,), device=wd.device))
+    layer.invalidate()
+
+  a, s = model.analysis_transform.layers, model.synthesis_transform.layers
+  cins = [3, 12, 48]
+  for li, cin in enumerate(cins):                    # space to depth: 3 -> 12 -> 48 -> 192
+    w = torch.zeros((5, 5, a[li].input_channels, 192))
+    for da in range(2):
+      for db in range(2):
+        for c in range(cin):
+          w[2 + da, 2 + db, c, (da * 2 + db) * cin + c] = 1.0
+    put(a[li], w)
+  w = torch.zeros((5, 5, 192, 192))
+  for da in range(2):
+    for db in range(2):
+      w[2 + da, 2 + db, torch.arange(192), torch.arange(192)] = quant / 4
+  put(a[3], w)
+  w = torch.zeros((5, 5, 192, 192))                  # nearest-neighbour upsampling / quant
+  for di in range(2):
+    for dj in range(2):
+      w[2 + di, 2 + dj, torch.arange(192), torch.arange(192)] = 1.0 / quant
+  put(s[0], w)
+  for li, cout in ((1, 48), (2, 12), (3, 3)):        # depth to space: 192 -> 48 -> 12 -> 3
+    w = torch.zeros((5, 5, 192, s[li].filters))
+    for di in range(2):
+      for dj in range(2):
+        for o in range(cout):
+          w[2 + di, 2 + dj, (di * 2 + dj) * cout + o, o] = 1.0
+    put(s[li], w)
+  return model
+
+
+def _smooth_images(batch, h, w, seed):
+  rng = np.random.default_rng(seed)
+  yy, xx = np.meshgrid(np.arange(h), np.arange(w), indexing="ij")
+  out = np.zeros((batch, h, w, 3), np.float32)
+  for b in range(batch):
+    for c in range(3):
+      f = rng.uniform(1 / 160.0, 1 / 90.0, size=2)
+      ph = rng.uniform(0, 2 * np.pi, size=2)
+      out[b, :, :, c] = 0.5 + 0.22 * np.sin(2 * np.pi * f[0] * yy + ph[0]) * \
+          np.cos(2 * np.pi * f[1] * xx + ph[1]) + 0.1 * (xx / w - 0.5)
+  return np.clip(out, 0, 1)
+
+
+def test_reconstructing_model_psnr_and_per_transform_l2(oracle):
+  """With weights that reconstruct (PSNR > 25 dB) the GPU transforms (bf16 operands and
+  activations) must agree with the float32 CPU restatement to relative L2 <= 1e-2 per transform,
+  and with the SAME symbols fed to both synthesis paths the PSNR may move by at most 0.01 dB
+  (north-star tolerance) — a wrong tile tail, tap or channel shows up here as a PSNR drop."""
+  from oracle import cpu_codec
+  model = _structured_model()
+  cpu = cpu_codec.CpuBmshj2018(model.export_weights(), oracle, threads=8,
+                               tables=model.export_tables())
+  x = _smooth_images(2, 144, 208, 5)                 # 144, 208: ragged tiles at every level
+  xd = torch.from_numpy(x).cuda()
+
+  def rel_l2(got, want):
+    got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
+    return float(np.sqrt(((got - want) ** 2).sum() / ((want ** 2).sum() + 1e-30)))
+
+  y, z, sigma = model.analyse(xd)
+  y_c, z_sym_c, sigma_c = cpu.analyse(x)
+  assert rel_l2(y.cpu().numpy(), y_c) <= 1e-2
+  assert rel_l2(sigma.cpu().numpy(), sigma_c) <= 2e-2     # three more layers after a rounding
+  assert np.mean(np.floor(y.cpu().numpy() + .5) == np.floor(y_c + .5)) > 0.9
+  c = model.compress(xd)
+  x_hat = model.decompress(c).cpu().numpy()
+  psnr_e2e = _psnr(x, np.clip(x_hat, 0, 1))
+  assert psnr_e2e > 25.0, psnr_e2e
+  # same symbols into both synthesis transforms
+  y_sym = torch.floor(y + .5)
+  x_gpu = model.synthesis_transform(y_sym.to(torch.bfloat16))[:, :144, :208].float().cpu().numpy()
+  x_cpu = cpu._run(cpu_codec.SYNTHESIS, y_sym.cpu().numpy())[:, :144, :208].numpy()
+  assert rel_l2(x_gpu, x_cpu) <= 1e-2
+  p_gpu, p_cpu = _psnr(x, x_gpu), _psnr(x, x_cpu)
+  assert p_cpu > 25.0 and abs(p_gpu - p_cpu) <= 0.01, (p_gpu, p_cpu)
+  # the uint8 output of the e2e leg is the quantised float reconstruction
+  from compression_b200.examples import bmshj2018
+  xq = model.decompress(c, out_dtype=torch.uint8)
+  assert torch.equal(xq, bmshj2018.quantize_image(model.decompress(c)))
+  # and the strings still are the CPU coder's strings of the GPU's symbols (escape-heavy here:
+  # |y| reaches `quant` while the random hyperprior predicts small scales)
+  host = model.to_host(c)
+  gc = model._conditional(sigma)
+  ys, yi, _ = gc._symbols_and_indexes(y.contiguous())
+  t = model.export_tables()
+  for b in range(2):
+    assert host.string[b] == oracle.ui_encode(ys[b].cpu().numpy(), yi[b].cpu().numpy(),
+                                              t["gc_cdf"], t["gc_len"], t["gc_off"], 16, 4)

@@ -314,3 +314,38 @@ def test_pmf_gaussian_model_table(tfc, oracle):
     pmf = np.concatenate([(up - lo), [2 * lo[0]]]).astype(np.float32)
     got = tfc.pmf_to_quantized_cdf(pmf, 16).cpu().numpy()
     np.testing.assert_array_equal(got, oracle.pmf_to_cdf(pmf[None], 16)[0])
+
+
+def test_decoder_clamps_oversize_nbytes(tfc, oracle, coder_lanes):
+  """an encode that overflowed its slab reports the size it NEEDED (> cap).  A decoder
+  handed that (slab, nbytes) pair must stay inside the slab row and flag the stream corrupt —
+  here the slab is the very end of an allocation guarded by a canary row."""
+  from compression_b200.python.ops import range_coding_ops as rc
+  rng = np.random.default_rng(17)
+  cdf, size, offset = _random_tables(rng, 4, 30, 16)
+  S, n, cap = 5, 400, 64
+  index = rng.integers(0, 4, size=(S, n)).astype(np.int32)
+  data = (rng.integers(-3, 20, size=(S, n)) + offset[index]).astype(np.int32)
+  with rc.deferred_checks() as checks:
+    checks.tag = "enc"
+    out, nbytes = rc.unbounded_index_range_encode_batch(data, index, cdf, size, offset, 16, 4,
+                                                        debug_level=0, cap=cap)
+    assert int(nbytes.max()) > cap                       # the need, not what was written
+    with pytest.raises(tfc.CudaError if hasattr(tfc, "CudaError") else Exception):
+      checks.verify("enc")
+    checks.tag = "dec"
+    dec = rc.unbounded_index_range_decode_batch(out, nbytes, index, cdf, size, offset, 16, 4, 0)
+    with pytest.raises(rc.InvalidArgumentError, match="corrupt"):
+      checks.verify("dec")
+  assert tuple(dec.shape) == (S, n)
+  # outside deferred mode the same call raises by itself
+  with pytest.raises(rc.InvalidArgumentError, match="corrupt"):
+    rc.unbounded_index_range_decode_batch(out, nbytes, index, cdf, size, offset, 16, 4, 0)
+  # bounded decoder: status is looked at too
+  cdf1 = np.array([[0, 20000, 50000, 65536]], np.int32)
+  d16 = rng.integers(0, 3, size=(3, 200)).astype(np.int16)
+  o2, n2 = rc.range_encode_batch(d16, cdf1, 16, debug_level=0)
+  back = rc.range_decode_batch(o2, n2, (200,), cdf1, 16, debug_level=0)
+  np.testing.assert_array_equal(back.cpu().numpy(), d16)
+  with pytest.raises(rc.InvalidArgumentError, match="corrupt"):
+    rc.range_decode_batch(o2[:, :16].contiguous(), n2, (200,), cdf1, 16, debug_level=0)

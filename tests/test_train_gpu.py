@@ -261,6 +261,48 @@ def _ref_transform(trainer, seq, t):
   return t
 
 
+def _torch_gaussian_likelihood(y, sigma, scale_bound, likelihood_bound):
+  """entropy_models.py:822-825, :916-932, :965-969, :181-184 in torch ops (autograd)."""
+  from compression_b200.python.ops import math_ops
+  scale = math_ops.lower_bound(sigma, float(np.float32(scale_bound)))
+  values = torch.abs(y)
+  const = -(2 ** -0.5)
+  upper = 0.5 * torch.erfc(const * ((0.5 - values) / scale))
+  lower = 0.5 * torch.erfc(const * ((-0.5 - values) / scale))
+  return math_ops.lower_bound(upper - lower, likelihood_bound)
+
+
+def test_gaussian_likelihood_kernel_gradients_match_autograd(tfc):
+  """`_GaussianLikelihood` (forward tfc_gaussian_call mode 1, backward
+  tfc_gaussian_likelihood_backward) against the same function in float64 torch ops under
+  autograd, including both lower_bound gradient rules (scale below the bound, likelihood below
+  the bound, gradients of either sign)."""
+  from compression_b200.python.layers import entropy_models
+  g = torch.Generator().manual_seed(12)
+  shape = (3, 5, 7, 16)
+  y = (torch.randn(shape, generator=g) * 3).cuda()
+  sigma = (torch.rand(shape, generator=g) * 3 - 0.3).cuda()      # some below the bound 0.11
+  y[0, 0, 0, :] = 60.0                                           # likelihood below its bound
+  y[0, 0, 1, :8] = 0.0                                           # |.| at zero
+  up = torch.randn(shape, generator=g).cuda()
+  bound, lb = float(np.float32(0.11)), 1e-9
+  yk, sk = y.clone().requires_grad_(), sigma.clone().requires_grad_()
+  lik = entropy_models._GaussianLikelihood.apply(yk, sk, bound, lb)
+  (lik * up).sum().backward()
+  yr, sr = y.double().requires_grad_(), sigma.double().requires_grad_()
+  ref = _torch_gaussian_likelihood(yr, sr, bound, lb)
+  (ref * up.double()).sum().backward()
+  for name, got, want in (("likelihood", lik.detach(), ref.detach()), ("d/dy", yk.grad, yr.grad),
+                          ("d/dsigma", sk.grad, sr.grad)):
+    scale = float(want.abs().max()) + 1e-12
+    err = float((got.double() - want).abs().max()) / scale
+    assert err <= 2e-5, (name, err, scale)
+  # elements clamped by a bound pass only negative gradients (math_ops.py:61-74)
+  low = sigma < bound
+  assert bool(((sk.grad[low] == 0) | (sk.grad[low] < 0)).all())
+  assert bool((sk.grad[low] != 0).any()) and bool((sk.grad[low] == 0).any())
+
+
 def test_bmshj2018_training_step_gradients_and_descent(tfc):
   """SURVEY §8f rank 3 (bmshj2018.py:201-282): hyperprior R-D loss through the CUDA conv
   kernels against the same graph in float32 torch ops, then a few descending steps."""
@@ -283,7 +325,7 @@ def test_bmshj2018_training_step_gradients_and_descent(tfc):
   sigma = _ref_transform(trainer, model.hyper_synthesis_transform, z_tilde)[:, :4, :4, :]
   y_tilde = y + noise[0]
   x_tilde = _ref_transform(trainer, model.synthesis_transform, y_tilde)
-  bpp = (torch.log(trainer._gaussian_likelihood(y_tilde, sigma)).sum() +
+  bpp = (torch.log(_torch_gaussian_likelihood(y_tilde, sigma, 0.11, 1e-9)).sum() +
          torch.log(trainer._likelihood(z_tilde)).sum()) / (-np.log(2) * 2 * 64 * 64)
   ref = 0.01 * torch.mean((x - x_tilde) ** 2) * 255 ** 2 + bpp
   ref.backward()
