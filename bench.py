@@ -84,6 +84,8 @@ def parse_args():
                        "at most 8 GB)")
   ap.add_argument("--tiles-per-cta", type=int, default=8,
                   help="transform kernels: tiles per CTA when depth > 1 (0: persistent grid)")
+  ap.add_argument("--coder-lanes", type=int, default=0,
+                  help="range coder design: 0 automatic, 1 warps per stream, 2 one stream per lane")
   ap.add_argument("--coder-pack", type=int, default=0,
                   help="coder streams per CTA when depth > 1 (0: by the number of streams in "
                        "flight: 4 at batch 64 x 12, 2 at batch 32 x 8)")
@@ -674,6 +676,8 @@ def run_b200(args):
     dist.init_process_group("nccl", device_id=dev)
   blocks = wanted_blocks(args)
   h, w, batch, nf = WORKLOADS[args.workload]
+  if args.coder_lanes:
+    tfc.configure(coder_lanes=args.coder_lanes)
   model = bmshj2018.Bmshj2018Model(nf, dev, seed=0, impl=args.conv_impl)
   g = torch.Generator().manual_seed(1000 + rank)
   x_u8_host = torch.randint(0, 256, (batch, h, w, 3), generator=g, dtype=torch.uint8).pin_memory()

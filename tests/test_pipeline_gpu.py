@@ -309,7 +309,14 @@ def test_reconstructing_model_psnr_and_per_transform_l2(oracle):
   y, z, sigma = model.analyse(xd)
   y_c, z_sym_c, sigma_c = cpu.analyse(x)
   assert rel_l2(y.cpu().numpy(), y_c) <= 1e-2
-  assert rel_l2(sigma.cpu().numpy(), sigma_c) <= 2e-2     # three more layers after a rounding
+  # hyper-analysis on the SAME input (|y| of the CPU), hyper-synthesis on the SAME z symbols: a
+  # z that rounds differently on the two sides would otherwise move sigma by a whole step
+  z_gpu = model.hyper_analysis_transform(torch.from_numpy(np.abs(y_c)).cuda().to(torch.bfloat16))
+  z_cpu = cpu._run(cpu_codec.HYPER_ANALYSIS, torch.abs(torch.from_numpy(y_c))).numpy()
+  assert rel_l2(z_gpu.cpu().numpy(), z_cpu) <= 1e-2
+  z_hat_c = z_sym_c.astype(np.float32) + cpu.medians
+  s_gpu = model.hyper_synthesis_transform(torch.from_numpy(z_hat_c).cuda().to(torch.bfloat16))
+  assert rel_l2(s_gpu[:, :y.shape[1], :y.shape[2]].cpu().numpy(), sigma_c) <= 1e-2
   assert np.mean(np.floor(y.cpu().numpy() + .5) == np.floor(y_c + .5)) > 0.9
   c = model.compress(xd)
   x_hat = model.decompress(c).cpu().numpy()
