@@ -255,3 +255,89 @@ extern "C" int tfc_pmf_to_quantized_cdf(const float* d_pmf, int64_t rows, int32_
   TFC_LAUNCHED("pmf_to_cdf_kernel");
   return TFC_OK;
 }
+
+
+// =========================================================================================
+// tfc_pmf_to_quantized_cdf_static — the same op for callers that cannot allocate
+// =========================================================================================
+// No counterpart in the reference: added for callers that
+// cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+// forbid it).  It runs the thread-per-row kernel above (pmf_to_cdf_kernel, the one kernel of this
+// op that needs scratch memory: the sort items of every row) with its scratch in a FILE-SCOPE
+// device array instead of a caller-provided workspace.
+//
+//   * The array is kStaticScratchBytes = 8 MiB and every GPU that loads this library holds it
+//     until the process exits.  It holds round_up(rows, 32) * n sort items of 16 bytes:
+//     round_up(rows, 32) * n <= 524 288 (e.g. 8192 rows x 64 entries, 4096 x 128, 352 x 1480).
+//     Larger problems are rejected with TFC_ERR_INVALID_ARGUMENT; use tfc_pmf_to_quantized_cdf.
+//   * In host code `g_static_scratch` is only a host-side stand-in for the symbol, NOT a device
+//     address: the address the kernel gets comes from cudaGetSymbolAddress, looked up once per
+//     device with that device current (static_scratch_ptr below).
+//   * Nothing here calls cudaMalloc / cudaFree or an allocating library routine.  The first call
+//     on a device does the one-time set-up (symbol address; the log2 table upload of ensure_lut,
+//     a cudaMemcpyToSymbol into another file-scope array).
+//   * Every call shares the one array and finds the previous call's contents in it.  Nothing has
+//     to start at zero: the kernel writes item i of a row (rebalance: acc.set for all i < n)
+//     before anything reads it, and never reads past n.  Calls that overlap on the GPU (two
+//     streams, two host threads) RACE on the array: serialise them, one stream at a time.
+namespace {
+
+constexpr size_t kStaticScratchBytes = size_t(8) << 20;
+constexpr int64_t kStaticScratchItems = (int64_t)(kStaticScratchBytes / sizeof(tfc::SortItem));
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+// device address of g_static_scratch on the CURRENT device (cached per device)
+int static_scratch_ptr(tfc::SortItem** out) {
+  static std::mutex mu;
+  static void* ptrs[64] = {nullptr};
+  int dev = 0;
+  TFC_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64)
+    return tfc::fail(TFC_ERR_CUDA, "static scratch: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess) return tfc::cuda_fail(e, "cudaGetSymbolAddress(g_static_scratch)");
+    if (p == nullptr || (reinterpret_cast<uintptr_t>(p) & 255) != 0)
+      return tfc::fail(TFC_ERR_CUDA, "static scratch: bad device address %p", p);
+    ptrs[dev] = p;
+  }
+  *out = static_cast<tfc::SortItem*>(ptrs[dev]);
+  return TFC_OK;
+}
+
+}  // namespace
+
+extern "C" size_t tfc_pmf_to_quantized_cdf_static_capacity(void) { return kStaticScratchBytes; }
+
+extern "C" int tfc_pmf_to_quantized_cdf_static(const float* d_pmf, int64_t rows, int32_t n,
+                                               int precision, int32_t* d_cdf, void* stream) {
+  if (precision < 1 || precision > 16)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "`precision` must be in [1, 16]: %d", precision);
+  if (n < 2)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT,
+                     "`pmf` size should be at least 2 in the last axis.");
+  if (rows <= 0) return TFC_OK;
+  if (d_pmf == nullptr || d_cdf == nullptr)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "pmf_to_quantized_cdf_static: null buffer");
+  const int64_t stride = (rows + 31) / 32 * 32;
+  if (stride > kStaticScratchItems || stride * (int64_t)n > kStaticScratchItems)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT,
+                     "pmf_to_quantized_cdf_static: %lld rows x %d entries need %lld scratch items, "
+                     "the static scratch array holds %lld (%zu bytes); use "
+                     "tfc_pmf_to_quantized_cdf with a caller-provided workspace",
+                     (long long)rows, n, (long long)(stride * (int64_t)n),
+                     (long long)kStaticScratchItems, kStaticScratchBytes);
+  int rc = ensure_lut();
+  if (rc) return rc;
+  tfc::SortItem* scratch = nullptr;
+  rc = static_scratch_ptr(&scratch);
+  if (rc) return rc;
+  const int threads = 32;
+  pmf_to_cdf_kernel<<<(unsigned)((rows + threads - 1) / threads), threads, 0,
+                      static_cast<cudaStream_t>(stream)>>>(d_pmf, rows, n, precision, d_cdf,
+                                                           scratch, stride);
+  TFC_LAUNCHED("pmf_to_cdf_kernel");
+  return TFC_OK;
+}

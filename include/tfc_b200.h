@@ -134,6 +134,22 @@ int tfc_pmf_to_quantized_cdf(const float* d_pmf, int64_t rows, int32_t n, int pr
                              int32_t* d_cdf, void* d_workspace, size_t workspace_bytes,
                              void* stream);
 
+/* The same op for callers that cannot allocate device memory (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * It takes no workspace: the scratch of the
+ * thread-per-row kernel lives in a file-scope `static __device__` array of
+ * tfc_pmf_to_quantized_cdf_static_capacity() = 8 MiB that every GPU loading this library holds
+ * until exit.  Limit: round_up(rows, 32) * n <= 524 288 sort items of 16 bytes (e.g. 8192 rows x
+ * 64 entries, 352 rows x 1480); anything larger returns TFC_ERR_INVALID_ARGUMENT — use
+ * tfc_pmf_to_quantized_cdf.  Calls no cudaMalloc / cudaFree / allocating library routine; the
+ * first call on a device looks up the array's device address (cudaGetSymbolAddress) and uploads
+ * the log2 table.  All calls share the one array (nothing in it needs to start at zero: every
+ * item is written before it is read), so calls that OVERLAP on the GPU race: issue them on one
+ * stream at a time.  Results are identical to tfc_pmf_to_quantized_cdf. */
+size_t tfc_pmf_to_quantized_cdf_static_capacity(void);
+int tfc_pmf_to_quantized_cdf_static(const float* d_pmf, int64_t rows, int32_t n, int precision,
+                                    int32_t* d_cdf, void* stream);
+
 /* Host-side helper shared by the bounded ops: the reference's MergeAxes
  * (range_coding_kernels_util.cc:36-92).  Writes the merged shapes (at most rank entries, and
  * one more for the cdf) and returns their count through *merged_rank. */
