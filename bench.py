@@ -86,6 +86,15 @@ def parse_args():
                   help="transform kernels: tiles per CTA when depth > 1 (0: persistent grid)")
   ap.add_argument("--coder-lanes", type=int, default=0,
                   help="range coder design: 0 automatic, 1 warps per stream, 2 one stream per lane")
+  ap.add_argument("--c3", default="", help="c3 block overrides: micro,depth,pack (e.g. 16,16,8)")
+  ap.add_argument("--conv-pair", type=int, default=0,
+                  help="implicit-GEMM kernel on CTA pairs (cta_group::2): 0 auto, 1 off, 2 on")
+  ap.add_argument("--conv-stages", type=int, default=0,
+                  help="operand-ring stages of the implicit-GEMM kernel in the pipeline (0: 4)")
+  ap.add_argument("--coder-smem-kb", type=int, default=0,
+                  help="shared memory per coder CTA in the pipeline (0: 226 KB)")
+  ap.add_argument("--coder-table-kb", type=int, default=0,
+                  help="shared memory for the coder's staged tables in the pipeline (0: 72 KB)")
   ap.add_argument("--coder-pack", type=int, default=0,
                   help="coder streams per CTA when depth > 1 (0: by the number of streams in "
                        "flight: 4 at batch 64 x 12, 2 at batch 32 x 8)")
@@ -366,23 +375,30 @@ def c3_block(args, model, world, rank, dev, barrier, allmax):
   import torch
   h, w, total = 1080, 1920, 256
   share = total // world
-  micro = max(4, min(16, share // 8))       # images per micro-batch: 8 micro-batches per pass
+  # One 1080p stream is 1.57 M symbols = 85 ms of serial decode: the coder is latency bound per
+  # image, so throughput needs ~300 images in flight per GPU whatever the share of the batch;
+  # every batch in flight keeps its own activation pool (0.46 GB per image), which is what stops
+  # at 18 micro-batches of 16 (134 GB reserved).  Measured (profiles/r2d_c3_sweep.txt): micro 16,
+  # 14 in flight, 8 streams per coder CTA 1008 MPix/s; 18 in flight 1315; 4 per CTA 1539.
+  micro, depth, pack = min(16, share), 18, 4
+  if args.c3:
+    micro, depth, pack = [int(v) for v in args.c3.split(",")]
+    micro = min(micro, share)
   nmicro = share // micro
   passes = 2 * world                        # every rank codes 512 images in the timed region
-  depth = 8
   g = torch.Generator().manual_seed(3000 + rank)
   xs_u8 = [torch.randint(0, 256, (micro, h, w, 3), generator=g, dtype=torch.uint8).pin_memory()
            for _ in range(2)]
   xs_dev = [(x.to(dev).float() / 255).contiguous() for x in xs_u8]
-  pack = max(1, min(4, int(round(micro * depth / 150.0))))
-  pipe = model.pipeline(depth, args.tiles_per_cta, pack, back_lag=6, host_slots=12)
+  pipe = model.pipeline(depth, args.tiles_per_cta, pack, back_lag=max(2, depth // 2),
+                        host_slots=depth + 6)
   out = {"workload": "bmshj2018-192 encode+decode 1920x1080, batch 256 split over %d GPU(s)" % world,
          "images_per_gpu": share, "micro_batch": micro, "passes_timed": passes,
-         "batches_in_flight": depth, "scaling": "strong"}
+         "batches_in_flight": depth, "coder_streams_per_cta": pack, "scaling": "strong"}
   with pipe:
     n = nmicro * passes
     seq = [xs_dev[k % 2] for k in range(n)]
-    pipe.roundtrip_device(seq[:depth + 1])
+    pipe.roundtrip_device(seq[:min(n, depth + 1)])
     barrier()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
@@ -411,6 +427,7 @@ def c3_block(args, model, world, rank, dev, barrier, allmax):
                   "h2d_bytes_per_micro_batch": int(pipe.h2d_bytes),
                   "d2h_bytes_per_micro_batch": int(pipe.d2h_bytes)}
   out["unit"] = "MPix/s"
+  out["hbm_peak_reserved_gb"] = round(torch.cuda.max_memory_reserved(dev) / 1e9, 1)
   if rank == 0:
     out["parity"] = parity_block(model, xs_dev[0][:4].contiguous(), "c3 (4 of a micro-batch)")
   barrier()
@@ -678,6 +695,8 @@ def run_b200(args):
   h, w, batch, nf = WORKLOADS[args.workload]
   if args.coder_lanes:
     tfc.configure(coder_lanes=args.coder_lanes)
+  if args.conv_pair:
+    tfc.configure(conv_pair=args.conv_pair)
   model = bmshj2018.Bmshj2018Model(nf, dev, seed=0, impl=args.conv_impl)
   g = torch.Generator().manual_seed(1000 + rank)
   x_u8_host = torch.randint(0, 256, (batch, h, w, 3), generator=g, dtype=torch.uint8).pin_memory()
@@ -705,7 +724,9 @@ def run_b200(args):
   if args.coder_pack <= 0:
     # streams in flight / CTAs wanted: the coder is latency bound per stream, and 4 streams per
     # CTA is the measured optimum once there are more streams than ~4 per SM
-    args.coder_pack = max(1, min(4, int(round(batch * args.depth / 150.0))))
+    # (measured with the in-kernel occupancy trace, profiles/r2c_pipeline_gantt_coder_trace.jsonl:
+    # coder SM-time per batch 4.1 ms of the GPU at 4 streams per CTA, 2.85 ms at 8)
+    args.coder_pack = max(1, min(8, int(round(batch * args.depth / 150.0))))
   if args.host_slots <= 0:
     # e2e leg: twice as many sets of pinned staging buffers as batches in flight, so that neither
     # host wait (strings of batch k, x_hat of the batch whose buffers are reused) comes before the
@@ -715,7 +736,8 @@ def run_b200(args):
   if args.back_lag <= 0:
     args.back_lag = max(1, min(args.depth, 12, args.host_slots // 2))
   pipe = model.pipeline(args.depth, args.tiles_per_cta, args.coder_pack, args.back_lag,
-                        args.host_slots)
+                        args.host_slots, conv_stages=args.conv_stages,
+                        coder_smem_kb=args.coder_smem_kb, coder_table_kb=args.coder_table_kb)
 
   with pipe:
     # every stream of the pipeline must have run once before the timed region: a stream's first
@@ -792,6 +814,9 @@ def run_b200(args):
   if "parity" in blocks:
     extra["parity"] = parity_block(model, x_dev, args.workload) if rank == 0 else None
     barrier()
+  pipe_back_lag, pipe_host_slots = pipe.back_lag, pipe.host_slots
+  del pipe
+  torch.cuda.empty_cache()          # per-stream activation pools of the C2 leg
   if "c3" in blocks:
     extra["c3"] = c3_block(args, model, world, rank, dev, barrier, allmax)
   torch.cuda.empty_cache()
@@ -830,13 +855,16 @@ def run_b200(args):
       "config": {"workload": workload_name(args),
                  "weights": "random-init seed 0", "l2": "inputs_exceed_l2 (%.0f MB images)"
                  % (x_dev.numel() * 4 / 1e6), "parallelism": "batch-sharded x%d" % world,
-                 "conv_impl": args.conv_impl, "pinned_cores_per_rank": pinned_cores,
+                 "conv_impl": args.conv_impl, "conv_pair": args.conv_pair,
+                 "pinned_cores_per_rank": pinned_cores,
                  "timed_window": "%d steps = %.2f pipeline waves of %d batches in flight"
                  % (args.steps, args.steps / float(args.depth), args.depth),
-                 "pipeline": {"batches_in_flight": args.depth, "e2e_back_lag": pipe.back_lag,
-                              "e2e_host_slots": pipe.host_slots,
+                 "pipeline": {"batches_in_flight": args.depth, "e2e_back_lag": pipe_back_lag,
+                              "e2e_host_slots": pipe_host_slots,
                               "tiles_per_cta": args.tiles_per_cta if args.depth > 1 else 0,
                               "coder_streams_per_cta": args.coder_pack if args.depth > 1 else 0,
+                              "conv_stages": args.conv_stages, "coder_smem_kb": args.coder_smem_kb,
+                              "coder_table_kb": args.coder_table_kb,
                               "hbm_peak_allocated_gb": round(
                                   torch.cuda.max_memory_allocated(dev) / 1e9, 1)}},
       "e2e": {"value": world * pixels / (e2e_ms * 1e-3) / 1e6, "unit": "MPix/s",

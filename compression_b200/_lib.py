@@ -98,10 +98,12 @@ def to_device(x, dtype, device=None):
 
 CFG_SM_BUDGET, CFG_CODER_STREAMS_PER_CTA, CFG_TILES_PER_CTA, CFG_CONV_CLUSTER = 1, 2, 3, 4
 CFG_CODER_LANES = 5
+CFG_CONV_STAGES, CFG_CODER_TABLE_KB, CFG_CODER_SMEM_KB, CFG_CONV_PAIR = 6, 7, 8, 9
 
 
 def configure(sm_budget=None, coder_streams_per_cta=None, tiles_per_cta=None, conv_cluster=None,
-              coder_lanes=None):
+              coder_lanes=None, conv_stages=None, coder_table_kb=None, coder_smem_kb=None,
+              conv_pair=None):
   """Process-wide scheduling knobs of the library (tfc_configure): `sm_budget` = SMs the
   persistent transform kernels may occupy (0: all), `coder_streams_per_cta` = range-coder
   streams packed into one CTA (0: automatic), `tiles_per_cta` = chunked instead of persistent
@@ -119,3 +121,11 @@ def configure(sm_budget=None, coder_streams_per_cta=None, tiles_per_cta=None, co
     check(L.tfc_configure(CFG_CONV_CLUSTER, int(conv_cluster)))
   if coder_lanes is not None:
     check(L.tfc_configure(CFG_CODER_LANES, int(coder_lanes)))
+  if conv_stages is not None:      # operand-ring stages of the implicit-GEMM kernel (0: 4)
+    check(L.tfc_configure(CFG_CONV_STAGES, int(conv_stages)))
+  if conv_pair is not None:        # cta_group::2 implicit GEMM: 0 auto, 1 off, 2 on
+    check(L.tfc_configure(CFG_CONV_PAIR, int(conv_pair)))
+  if coder_smem_kb is not None:    # dynamic shared memory per warps-per-stream coder CTA (0: 226 KB)
+    check(L.tfc_configure(CFG_CODER_SMEM_KB, int(coder_smem_kb)))
+  if coder_table_kb is not None:   # shared-memory budget of the coder's staged tables (0: 72 KB)
+    check(L.tfc_configure(CFG_CODER_TABLE_KB, int(coder_table_kb)))

@@ -1,5 +1,7 @@
 #include "common.cuh"
 
+#include <cstdlib>
+
 namespace tfc {
 std::string& last_error_ref() {
   static thread_local std::string s;
@@ -12,6 +14,17 @@ std::atomic<int> g_coder_lanes{0};
 std::atomic<int> g_tiles_per_cta{0};
 std::atomic<int> g_debug{0};
 std::atomic<int> g_conv_cluster{0};
+std::atomic<int> g_conv_stages{0};
+// TFC_CONV_PAIR in the environment presets the CTA-pair mode (tests run the whole suite with it)
+static int env_int(const char* name, int lo, int hi) {
+  const char* e = getenv(name);
+  if (!e || !*e) return 0;
+  const int v = atoi(e);
+  return (v < lo || v > hi) ? 0 : v;
+}
+std::atomic<int> g_conv_pair{env_int("TFC_CONV_PAIR", 0, 2)};
+std::atomic<int> g_coder_table_kb{0};
+std::atomic<int> g_coder_smem_kb{0};
 }  // namespace tfc
 
 extern "C" const char* tfc_last_error(void) { return tfc::last_error_ref().c_str(); }
@@ -43,6 +56,26 @@ extern "C" int tfc_configure(int key, int value) {
       if (value < 0 || value > 2)
         return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "coder lanes mode must be 0 (auto), 1 (off) or 2 (on)");
       tfc::g_coder_lanes.store(value);
+      return TFC_OK;
+    case TFC_CFG_CONV_STAGES:
+      if (value != 0 && (value < 2 || value > 6))
+        return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "conv stages must be 0 (auto) or 2..6");
+      tfc::g_conv_stages.store(value);
+      return TFC_OK;
+    case TFC_CFG_CODER_TABLE_KB:
+      if (value < 0 || value > 72)
+        return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "coder table budget must be in [0, 72] KB");
+      tfc::g_coder_table_kb.store(value);
+      return TFC_OK;
+    case TFC_CFG_CONV_PAIR:
+      if (value < 0 || value > 2)
+        return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "conv CTA-pair mode must be 0 (auto), 1 (off) or 2 (on)");
+      tfc::g_conv_pair.store(value);
+      return TFC_OK;
+    case TFC_CFG_CODER_SMEM_KB:
+      if (value != 0 && (value < 16 || value > 226))
+        return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "coder shared-memory budget must be 0 or in [16, 226] KB");
+      tfc::g_coder_smem_kb.store(value);
       return TFC_OK;
     case 99:   // kernel experiments (tools/conv_bench.py --debug): results are NOT valid when set
       tfc::g_debug.store(value);

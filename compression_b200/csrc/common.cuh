@@ -58,6 +58,10 @@ inline int persistent_grid() {
 
 extern std::atomic<int> g_debug;
 extern std::atomic<int> g_conv_cluster;
+extern std::atomic<int> g_conv_pair;       // implicit GEMM with cta_group::2 MMAs: 0 auto, 1 off, 2 on
+extern std::atomic<int> g_conv_stages;     // implicit-GEMM operand ring: 0 auto (4), 2..4
+extern std::atomic<int> g_coder_smem_kb;   // dynamic shared memory a warps-per-stream coder CTA may take (0: 226 KB)
+extern std::atomic<int> g_coder_table_kb;  // shared-memory budget of the coder's staged CDF tables (0: 72 KB)
 inline int conv_cluster() { return g_conv_cluster.load(std::memory_order_relaxed); }
 inline int debug_bits() { return g_debug.load(std::memory_order_relaxed); }
 inline int tiles_per_cta() { return g_tiles_per_cta.load(std::memory_order_relaxed); }

@@ -98,7 +98,10 @@ __device__ __forceinline__ void gdn_tile(uint32_t dacc, uint8_t* a2, int r, int 
                                          uint64_t* a2_full, uint64_t* d2_full, uint32_t it,
                                          bool valid, void* out, bool out_f32, bool wide,
                                          int64_t elem0, const CUtensorMap* map_out,
-                                         TileOrigin org, bool leader, int nblocks) {
+                                         TileOrigin org, bool leader, int nblocks,
+                                         uint32_t a2_full_pair = 0) {
+  // a2_full_pair != 0 (CTA-pair MMAs): the "x^2 is in shared memory" arrival goes to the pair
+  // leader's barrier at that shared::cluster address instead of this CTA's a2_full
   uint32_t xs[NCH * 16];                           // x = D1 + bias as packed bf16 pairs
   if (map_out != nullptr && it > 0) {
     if (leader) bulk_wait_read();
@@ -136,7 +139,7 @@ __device__ __forceinline__ void gdn_tile(uint32_t dacc, uint8_t* a2, int r, int 
   }
   tc_fence_before();
   fence_proxy_async_smem();
-  mbar_arrive(a2_full);
+  if (a2_full_pair) mbar_arrive_cluster(a2_full_pair); else mbar_arrive(a2_full);
   mbar_wait(d2_full, it & 1);
   tc_fence_after();
   // phase 2: y = x * rsqrt(beta + D2)  (IGDN: x * sqrt)

@@ -39,7 +39,7 @@ namespace epi = tfc::epi;
 
 constexpr int kTileM = 128;          // output pixels per CTA tile (UMMA M)
 constexpr int kBlockK = 64;          // channels per k-block: 64 bf16 = one 128-byte swizzle row
-constexpr int kStages = 4;
+constexpr int kStages = 6;          // most stages of the operand ring (Params::stages of them used)
 constexpr int kMaxTaps = 81;         // 9x9
 constexpr int kMaxPhases = 16;       // 4x4 upsampling
 constexpr int kThreads = 64 + tfc::epi::kEpilogueThreads;   // producer warp, MMA warp, 8 epilogue warps
@@ -62,6 +62,8 @@ struct Params {
   int32_t num_tiles;
   int32_t chunk;                    // tiles per CTA (0: persistent grid)
   int32_t cs;                       // cluster size: the CTAs of a cluster share the B loads
+  int32_t stages;                   // stages of the TMA operand ring in use (2..kStages)
+  int32_t pair;                     // CTA-pair MMAs (cta_group::2, M = 256 over the cluster of 2)
   int32_t npad;                     // UMMA N (cout rounded up to 16)
   int32_t act;
   int32_t out_f32;
@@ -95,7 +97,9 @@ constexpr int kGdnSlot = 4;   // the GDN GEMM of tile i is issued before k-block
 //              in before k-block kGdnSlot of main(i)
 //   epilogue : phase 1(i): x = D1 + bias kept as packed bf16 in registers, x^2 -> smem (K-major)
 //              phase 2(i): y = x * rsqrt(beta + D2)   (IGDN: * sqrt), overlapping main(i+1)
-template <int MODE, int NC>
+// PAIR: CTA-pair MMAs (tcgen05.mma.cta_group::2, see umma_ptx.cuh).  A separate instantiation: a
+// kernel that contains cta_group::2 instructions can only be launched as a cluster.
+template <int MODE, int NC, bool PAIR>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
                  const __grid_constant__ CUtensorMap map_w,
@@ -106,9 +110,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
   // carve: [stages x (A 16 KB | B npad*128 B)] [A2: cout/64 x 16 KB] [bias|beta] [barriers]
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
-  const int b_bytes = p.npad * kBlockK * 2;
+  // B bytes one CTA holds per stage: all N rows, or its half of them when the pair shares B
+  const int b_bytes = (PAIR ? p.npad / 2 : p.npad) * kBlockK * 2;
   const int stage_bytes = kABytes + ((b_bytes + 1023) & ~1023);
-  uint8_t* a2 = smem + kStages * stage_bytes;
+  uint8_t* a2 = smem + p.stages * stage_bytes;
   constexpr int gdn_kblocks = GDN ? NC / 2 : 0;
   float* s_bias = reinterpret_cast<float*>(a2 + gdn_kblocks * kABytes);
   float* s_beta = s_bias + 256;
@@ -125,13 +130,16 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
     prefetch_tmap(&map_a);
     prefetch_tmap(&map_w);
     if (GDN) prefetch_tmap(&map_g);
-    for (int s = 0; s < kStages; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], p.cs); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], epi::kEpilogueThreads); }
-    mbar_init(&bars->a2_full, epi::kEpilogueThreads);
+    // pair mode: only the leader's MMA warp commits (one multicast arrival per CTA), and the
+    // leader's d1_empty / a2_full collect the epilogue threads of BOTH CTAs
+    const int epi_arrivals = epi::kEpilogueThreads * (PAIR ? 2 : 1);
+    for (int s = 0; s < kStages; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], PAIR ? 1 : p.cs); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], epi_arrivals); }
+    mbar_init(&bars->a2_full, epi_arrivals);
     mbar_init(&bars->d2_full, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(&bars->tmem_base, 512);
+  if (warp == 1) { if (PAIR) tmem_alloc_pair(&bars->tmem_base, 512); else tmem_alloc(&bars->tmem_base, 512); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -154,7 +162,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
   const int tile0 = p.chunk ? cluster_id * p.chunk * p.cs : cluster_id * p.cs;
   const int tile1 = p.chunk ? min(tile0 + p.chunk * p.cs, p.num_tiles) : p.num_tiles;
   const int tile_step = p.chunk ? p.cs : (int)gridDim.x;
-  const uint32_t idesc = make_idesc_bf16(kTileM, p.npad);
+  const uint32_t idesc = make_idesc_bf16(PAIR ? 2 * kTileM : kTileM, p.npad);
 
   auto tile_coords = [&](int tile, int& phase, int& n, int& i0, int& j0) {
     const int per_img = p.tiles_h * p.tiles_w;
@@ -177,13 +185,21 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
         for (int kc = 0; kc < gdn_kblocks; ++kc) {
           mbar_wait(&bars->empty[stage], ph ^ 1);
           uint8_t* sa = smem + stage * stage_bytes;
+          if (PAIR) {
+            // each CTA loads ITS half of gamma's rows; both complete on the leader's barrier
+            if (rank == 0) mbar_expect_tx(&bars->full[stage], 2 * b_bytes);
+            tma_load_2d_pair(sa + kABytes, &map_g, leader_u32(&bars->full[stage]), kc * kBlockK,
+                             rank * b_rows);
+            if (++stage == p.stages) { stage = 0; ph ^= 1; }
+            continue;
+          }
           mbar_expect_tx(&bars->full[stage], b_bytes);
           if (p.cs > 1)
             tma_load_2d_mc(sa + kABytes + rank * b_rows * 128, &map_g, &bars->full[stage],
                            kc * kBlockK, rank * b_rows, mc_mask);
           else
             tma_load_2d(sa + kABytes, &map_g, &bars->full[stage], kc * kBlockK, 0);
-          if (++stage == kStages) { stage = 0; ph ^= 1; }
+          if (++stage == p.stages) { stage = 0; ph ^= 1; }
         }
       };
       for (int g = tile0; g < tile1; g += tile_step, ++it) {
@@ -198,6 +214,16 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
             if (GDN && it > 0 && kb == slot) load_gamma();
             mbar_wait(&bars->empty[stage], ph ^ 1);
             uint8_t* sa = smem + stage * stage_bytes;
+            if (PAIR) {
+              // this CTA's 128 pixels of A and its half of the weight rows, signalled to the leader
+              const uint32_t lb = leader_u32(&bars->full[stage]);
+              if (rank == 0) mbar_expect_tx(&bars->full[stage], 2 * (kABytes + b_bytes));
+              tma_load_5d_pair(sa, &map_a, lb, tap.pw * p.cin + kc * kBlockK, j0 + tap.dw, tap.ph,
+                               i0 + tap.dh, n);
+              tma_load_3d_pair(sa + kABytes, &map_w, lb, kc * kBlockK, rank * b_rows, tap.widx);
+              if (++stage == p.stages) { stage = 0; ph ^= 1; }
+              continue;
+            }
             mbar_expect_tx(&bars->full[stage], kABytes + b_bytes);
             tma_load_5d(sa, &map_a, &bars->full[stage], tap.pw * p.cin + kc * kBlockK,
                         j0 + tap.dw, tap.ph, i0 + tap.dh, n);
@@ -206,7 +232,7 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
                              kc * kBlockK, rank * b_rows, tap.widx, mc_mask);
             else
               tma_load_3d(sa + kABytes, &map_w, &bars->full[stage], kc * kBlockK, 0, tap.widx);
-            if (++stage == kStages) { stage = 0; ph ^= 1; }
+            if (++stage == p.stages) { stage = 0; ph ^= 1; }
           }
         }
         if (GDN && it > 0 && slot == nk) load_gamma();
@@ -214,13 +240,32 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
       if (GDN && it > 0) load_gamma();
     }
   } else if (warp == 1) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
+    // ===== MMA issuer (pair mode: the leader CTA issues for both) =====
+    if (lane == 0 && (!PAIR || rank == 0)) {
       int stage = 0;
       uint32_t ph = 0, it = 0;
+      const uint16_t pair_mask = 0x3;
+      auto mma = [&](uint32_t d, uint64_t da, uint64_t db, uint32_t accumulate) {
+        if (PAIR) umma_bf16_pair(d, da, db, idesc, accumulate);
+        else umma_bf16(d, da, db, idesc, accumulate);
+      };
+      // stage consumed: the producer(s) may refill it
+      auto release = [&](uint64_t* bar) {
+        if (PAIR) umma_commit_pair(bar, pair_mask);
+        else if (p.cs > 1) umma_commit_mc(bar, mc_mask);
+        else umma_commit(bar);
+      };
+      // accumulator finished: the epilogue(s) may read it
+      auto publish = [&](uint64_t* bar) {
+        if (PAIR) umma_commit_pair(bar, pair_mask); else umma_commit(bar);
+      };
+      // barriers the epilogue threads arrive on (those of the peer CTA too in pair mode)
+      auto wait_epilogue = [&](uint64_t* bar, uint32_t parity) {
+        if (PAIR) mbar_wait_cluster(bar, parity); else mbar_wait(bar, parity);
+      };
       // GEMM2 of tile j: acc[j & 1] = x^2 (smem a2) * gamma, overwriting D1 (already consumed)
       auto issue_gdn = [&](uint32_t j) {
-        mbar_wait(&bars->a2_full, j & 1);
+        wait_epilogue(&bars->a2_full, j & 1);
         tc_fence_after();
         const uint32_t d2 = tmem + (j & 1) * 256;
         for (int kc = 0; kc < gdn_kblocks; ++kc) {
@@ -231,18 +276,17 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
           const uint64_t db = make_desc_sw128(sb);
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k)
-            umma_bf16(d2, da + (k * 2), db + (k * 2), idesc, (kc | k) != 0);
-          if (p.cs > 1) umma_commit_mc(&bars->empty[stage], mc_mask);
-          else umma_commit(&bars->empty[stage]);
-          if (++stage == kStages) { stage = 0; ph ^= 1; }
+            mma(d2, da + (k * 2), db + (k * 2), (kc | k) != 0);
+          release(&bars->empty[stage]);
+          if (++stage == p.stages) { stage = 0; ph ^= 1; }
         }
-        umma_commit(&bars->d2_full);
+        publish(&bars->d2_full);
       };
       for (int g = tile0; g < tile1; g += tile_step, ++it) {
         int phase, n, i0, j0;
         tile_coords(min(g + rank, p.num_tiles - 1), phase, n, i0, j0);
         const int acc = it & 1;
-        mbar_wait(&bars->d1_empty[acc], ((it >> 1) & 1) ^ 1);
+        wait_epilogue(&bars->d1_empty[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d1 = tmem + acc * 256;
         const int nk = (p.phase_start[phase + 1] - p.phase_start[phase]) * kchunks;
@@ -255,13 +299,12 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
           const uint64_t da = make_desc_sw128(sa), db = make_desc_sw128(sa + kABytes);
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k)
-            umma_bf16(d1, da + (k * 2), db + (k * 2), idesc, (kb | k) != 0);
-          if (p.cs > 1) umma_commit_mc(&bars->empty[stage], mc_mask);
-          else umma_commit(&bars->empty[stage]);
-          if (++stage == kStages) { stage = 0; ph ^= 1; }
+            mma(d1, da + (k * 2), db + (k * 2), (kb | k) != 0);
+          release(&bars->empty[stage]);
+          if (++stage == p.stages) { stage = 0; ph ^= 1; }
         }
         if (GDN && it > 0 && slot == nk) issue_gdn(it - 1);
-        umma_commit(&bars->d1_full[acc]);
+        publish(&bars->d1_full[acc]);
       }
       if (GDN && it > 0) issue_gdn(it - 1);
     }
@@ -292,18 +335,24 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
                                     p.out_wide != 0, elem0,
                                     p.out_tma ? &maps_out.m[phase] : nullptr,
                                     epi::TileOrigin{j0, i0, dummy ? -1 : n}, threadIdx.x == 64,
-                                    NC / 2);
+                                    NC / 2, PAIR ? leader_u32(&bars->a2_full) : 0u);
       else
         epi::bias_tile(dacc, half, p.npad, p.cout, s_bias, p.act == TFC_ACT_RELU, valid, p.out,
                        p.out_f32 != 0, p.out_wide != 0, elem0);
       tc_fence_before();
-      mbar_arrive(&bars->d1_empty[acc]);
+      if (PAIR) mbar_arrive_cluster(leader_u32(&bars->d1_empty[acc]));
+      else mbar_arrive(&bars->d1_empty[acc]);
     }
     if (GDN && p.out_tma && threadIdx.x == 64) bulk_wait_read();
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem, 512);
+  if (PAIR) {
+    cluster_sync();                  // both CTAs are done with the pair's tensor memory
+    if (warp == 1) tmem_dealloc_pair(tmem, 512);
+  } else if (warp == 1) {
+    tmem_dealloc(tmem, 512);
+  }
   if (p.cs > 1) cluster_sync();      // no CTA leaves while a peer may still signal its barriers
 }
 
@@ -406,11 +455,21 @@ void pick_tile(int hs, int ws, int* th, int* tw) {
   }
 }
 
-size_t smem_bytes(int npad, int cout, bool gdn) {
-  const int b_bytes = npad * kBlockK * 2;
+size_t smem_bytes(int npad, int cout, bool gdn, int stages = 4, bool pair = false) {
+  const int b_bytes = (pair ? npad / 2 : npad) * kBlockK * 2;
   const int stage = kABytes + ((b_bytes + 1023) & ~1023);
-  return 1024 + (size_t)kStages * stage + (gdn ? (size_t)(cout / kBlockK) * kABytes : 0) +
+  return 1024 + (size_t)stages * stage + (gdn ? (size_t)(cout / kBlockK) * kABytes : 0) +
          2 * 256 * sizeof(float) + sizeof(Barriers) + 64;
+}
+
+// stages of the operand ring: tfc_configure(TFC_CFG_CONV_STAGES), else as many as fit (<= 4)
+int pick_stages(int npad, int cout, bool gdn, bool pair) {
+  int want = tfc::g_conv_stages.load(std::memory_order_relaxed);
+  // a CTA of a pair holds half of B per stage (28 KB instead of 40 KB at 192 filters): the same
+  // shared memory carries five stages
+  if (want < 2 || want > kStages) want = pair ? 5 : 4;
+  while (want > 2 && smem_bytes(npad, cout, gdn, want, pair) > 227 * 1024) --want;
+  return want;
 }
 
 }  // namespace
@@ -446,7 +505,7 @@ bool conv_umma_supported(const tfc_conv_desc& d, const char** why) {
   if (d.ho % d.su || d.wo % d.su) { *why = "output size must be a multiple of strides_up"; return false; }
   if (d.kh * d.kw > kMaxTaps || d.kh > 64 || d.kw > 64) { *why = "kernel too large"; return false; }
   const int npad = (d.cout + 15) / 16 * 16;
-  if (smem_bytes(npad, d.cout, gdn) > 227 * 1024) { *why = "shared memory"; return false; }
+  if (smem_bytes(npad, d.cout, gdn, 2) > 227 * 1024) { *why = "shared memory"; return false; }
   if ((int64_t)d.n * d.ho * d.wo / 128 > (1 << 30)) { *why = "too many tiles"; return false; }
   return true;
 }
@@ -491,6 +550,19 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
     if ((want == 2 || want == 4) && per_phase % want == 0 && p.npad % (8 * want) == 0 &&
         p.num_tiles >= 2 * want)
       p.cs = want;
+    // CTA pairs (tfc_configure(TFC_CFG_CONV_PAIR)): one M = 256 tcgen05.mma per two adjacent tiles,
+    // each CTA holding half of B.  Needs an even number of tiles per output phase and N a multiple
+    // of 32 (each half a multiple of 16 rows = whole swizzle atoms).
+    // Automatic = on from 64 tiles (measured at batch 64, 768x512, profiles/r2d_*: A1 2.56 -> 2.40
+    // ms, A2 0.644 -> 0.604, HS2 0.077 -> 0.072, S2 3.01 -> 2.94, S1 0.795 -> 0.789; ncu tensor
+    // pipe of A1 56.4 -> 58.9 %, L2 throughput 59 -> 48 %).
+    const int pair = tfc::g_conv_pair.load(std::memory_order_relaxed);
+    const bool pair_wanted = pair == 2 || (pair == 0 && p.num_tiles >= 64 && want <= 1);
+    if (pair_wanted && per_phase % 2 == 0 && p.npad % 32 == 0 && p.num_tiles >= 4 &&
+        (!gdn || d.cout == 192)) {     // the pair kernel is built for bias-only and 192-filter GDN
+      p.cs = 2;
+      p.pair = 1;
+    }
   }
 
   // weights (+ gamma^T) -> bf16 K-major
@@ -536,7 +608,8 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
   } else {
     map_g = map_w;
   }
-  const size_t smem = smem_bytes(p.npad, d.cout, gdn);
+  p.stages = pick_stages(p.npad, d.cout, gdn, p.pair != 0);
+  const size_t smem = smem_bytes(p.npad, d.cout, gdn, p.stages, p.pair != 0);
   p.chunk = tiles_per_cta();
   const int groups = (p.num_tiles + p.cs - 1) / p.cs;
   const int grid = p.cs * (p.chunk ? (groups + p.chunk - 1) / p.chunk
@@ -561,14 +634,17 @@ int conv_umma(const tfc_conv_desc& d, const void* in, const float* w, const floa
   void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const OutMaps,
                const Params) = nullptr;
   if (!gdn) {
-    kern = conv_umma_kernel<0, 0>;
+    kern = p.pair ? conv_umma_kernel<0, 0, true> : conv_umma_kernel<0, 0, false>;
   } else {
     const bool inv = d.act == TFC_ACT_IGDN;
     switch (d.cout / 32) {
-      case 2: kern = inv ? conv_umma_kernel<2, 2> : conv_umma_kernel<1, 2>; break;
-      case 4: kern = inv ? conv_umma_kernel<2, 4> : conv_umma_kernel<1, 4>; break;
-      case 6: kern = inv ? conv_umma_kernel<2, 6> : conv_umma_kernel<1, 6>; break;
-      case 8: kern = inv ? conv_umma_kernel<2, 8> : conv_umma_kernel<1, 8>; break;
+      case 2: kern = inv ? conv_umma_kernel<2, 2, false> : conv_umma_kernel<1, 2, false>; break;
+      case 4: kern = inv ? conv_umma_kernel<2, 4, false> : conv_umma_kernel<1, 4, false>; break;
+      case 6:
+        if (p.pair) kern = inv ? conv_umma_kernel<2, 6, true> : conv_umma_kernel<1, 6, true>;
+        else kern = inv ? conv_umma_kernel<2, 6, false> : conv_umma_kernel<1, 6, false>;
+        break;
+      case 8: kern = inv ? conv_umma_kernel<2, 8, false> : conv_umma_kernel<1, 8, false>; break;
       default: return fail(TFC_ERR_UNIMPLEMENTED, "GDN needs cout in {64, 128, 192, 256}");
     }
   }

@@ -346,6 +346,11 @@ bool make_plan(const tfc_conv_desc& d, Plan* pl, const char** why) {
                        (size_t)2 * kTileM * pl->ld * 4 + 64 + sizeof(UpBarriers) + 64;
   int stages = (int)((227 * 1024 - fixed) / kABytes);
   stages = std::min(stages, 8);
+  // tfc_configure(TFC_CFG_CONV_STAGES): a caller that wants range-coder CTAs of another batch to
+  // share the SM limits the operand rings; this kernel is HBM bound and its 16 KB stages only
+  // cover latency, so one more than the implicit-GEMM kernel's count is kept
+  const int cfg = tfc::g_conv_stages.load(std::memory_order_relaxed);
+  if (cfg >= 2) stages = std::min(stages, cfg + 1);
   if (stages < 2) { *why = "shared memory"; return false; }
   pl->stages = stages;
   pl->smem = fixed + (size_t)stages * kABytes;

@@ -484,6 +484,13 @@ int run_unbounded_checks(const int32_t* d_index, int64_t index_count, const int3
 // ---- generation-4 unbounded kernels (rc_v4.cuh): launch plumbing -----------------------------
 constexpr int kV4TableBudget = 72 * 1024;
 
+// dynamic shared memory a warps-per-stream coder CTA may take (tfc_configure)
+size_t coder_smem_max() {
+  const int kb = tfc::g_coder_smem_kb.load(std::memory_order_relaxed);
+  return kb > 0 ? (size_t)kb * 1024 : (size_t)(227 * 1024 - 1024);
+}
+constexpr int kCoderSmemAttr = 227 * 1024 - 1024;   // opt-in limit set once per device
+
 int v4_max_puts(int overflow_width) {   // puts (= stream words at most) one symbol can take
   const int ndmax = (32 + overflow_width - 1) / overflow_width;
   const int all1 = (1 << overflow_width) - 1;
@@ -499,9 +506,17 @@ bool v4_usable(int32_t rows) {
   return !disabled && rows >= 1 && rows <= 1024;
 }
 
+// Shared memory reserved for the staged tables: the dense size, at most the budget
+// (tfc_configure(TFC_CFG_CODER_TABLE_KB), 72 KB by default), never less than the row records and
+// row infos (32 bytes per row), which the kernels always stage.  Ragged rows that do not fit are
+// read from the caller's dense table through L1 (stage_tables_v4 decides on the device, where
+// the row lengths are).
 int v4_table_budget(int32_t rows, int32_t cols) {
   const size_t dense = v4::tables_bytes(rows, (int64_t)rows * cols);
-  return (int)((std::min<size_t>(dense, kV4TableBudget) + 15) & ~size_t(15));
+  const int kb = tfc::g_coder_table_kb.load(std::memory_order_relaxed);
+  const size_t budget = std::max<size_t>(kb > 0 ? (size_t)kb * 1024 : (size_t)kV4TableBudget,
+                                         (size_t)rows * 32);
+  return (int)((std::min<size_t>(dense, budget) + 15) & ~size_t(15));
 }
 
 // ---- one stream per lane (rc_lanes.cuh): thousands of streams ------------------------------
@@ -674,7 +689,7 @@ extern "C" int tfc_unbounded_index_range_encode(
     q.streams_per_cta = (int)std::max<int64_t>(1, std::min<int64_t>(pack > 0 ? pack : 1, S));
     const int min_cap = (32 * v4_max_puts(overflow_width) + 31) / 32 * 32;   // one 32-symbol round
     q.put_cap = std::max(v4::kPutCap, min_cap);
-    const size_t smem_max = 227 * 1024 - 1024;
+    const size_t smem_max = coder_smem_max();
     while (q.put_cap / 2 >= std::max(256, min_cap) &&
            (size_t)q.table_bytes + q.streams_per_cta * v4::enc_bytes(q.put_cap) > smem_max)
       q.put_cap /= 2;
@@ -688,9 +703,9 @@ extern "C" int tfc_unbounded_index_range_encode(
     static tfc::PerDeviceOnce attr;
     if (attr.first()) {
       TFC_CUDA(cudaFuncSetAttribute(v4::encode_unbounded_v4<false>,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, kCoderSmemAttr));
       TFC_CUDA(cudaFuncSetAttribute(v4::encode_unbounded_v4<true>,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, kCoderSmemAttr));
     }
     const int64_t blocks = (S + q.streams_per_cta - 1) / q.streams_per_cta;
     if (q.streams_per_cta == 1)
@@ -775,7 +790,7 @@ extern "C" int tfc_unbounded_index_range_decode(
     const int pack = tfc::g_coder_pack.load(std::memory_order_relaxed);
     if (pack > 0) q.streams_per_cta = (int)std::max<int64_t>(1, std::min<int64_t>(pack, S));
     // rounds as long as shared memory allows (fewer barriers), shorter when streams are packed
-    const size_t smem_max = 227 * 1024 - 1024;
+    const size_t smem_max = coder_smem_max();
     auto geometry = [&](int round) {
       q.round = round;
       q.round_words = (round * mp + 3) / 4 * 4;
@@ -792,7 +807,7 @@ extern "C" int tfc_unbounded_index_range_decode(
     static tfc::PerDeviceOnce attr;
     if (attr.first()) {
       TFC_CUDA(cudaFuncSetAttribute(v4::decode_unbounded_v4,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max));
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, kCoderSmemAttr));
     }
     const int64_t blocks = (S + q.streams_per_cta - 1) / q.streams_per_cta;
     v4::decode_unbounded_v4<<<(unsigned)blocks, 64 * q.streams_per_cta, smem, st>>>(q);
@@ -938,5 +953,20 @@ extern "C" int tfc_range_decode(const uint8_t* d_enc, int64_t cap, const int32_t
   const int wpb = warps_per_block(S);
   decode_bounded_kernel<<<(unsigned)((S + wpb - 1) / wpb), wpb * 32, 0, st>>>(p);
   TFC_LAUNCHED("decode_bounded_kernel");
+  return TFC_OK;
+}
+
+// Debug: the occupancy trace of the warps-per-stream coder kernels (rc_v4.cuh g_trace):
+// out4 = {encode ns, encode streams, decode ns, decode streams} summed since the last reset.
+// Synchronises the device.
+extern "C" int tfc_debug_coder_trace(uint64_t* h_out4, int reset) {
+  TFC_CUDA(cudaDeviceSynchronize());
+  unsigned long long v[4] = {0, 0, 0, 0};
+  TFC_CUDA(cudaMemcpyFromSymbol(v, v4::g_trace, sizeof(v)));
+  if (h_out4) for (int i = 0; i < 4; ++i) h_out4[i] = v[i];
+  if (reset) {
+    unsigned long long z[4] = {0, 0, 0, 0};
+    TFC_CUDA(cudaMemcpyToSymbol(v4::g_trace, z, sizeof(z)));
+  }
   return TFC_OK;
 }

@@ -27,6 +27,17 @@ constexpr int kMaxRows = 65535;
 
 extern __shared__ __align__(16) uint8_t smem_v4[];
 
+// Occupancy trace (tfc_debug_coder_trace): nanoseconds between a stream's first and last
+// instruction, summed per kernel kind — how long coder CTAs really HOLD their SM when other
+// kernels share the GPU (end-of-phase events on the stream cannot tell waiting for an SM from
+// running on it).  [0] encode ns, [1] encode streams, [2] decode ns, [3] decode streams.
+__device__ unsigned long long g_trace[4];
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 struct Tables {          // shared-memory image of the CDF tables
   const uint4* rowrec;   // {c1<<16, c2<<16, c3<<16, row} (precision 16) for 5-entry rows, else c=0
   const int4* rowinfo;   // {start, len, offset, 0}
@@ -246,6 +257,7 @@ __host__ __device__ inline size_t dec_pair_bytes(int round, int lin) {
 // position round r started at (the only position known by then); a round consumes at most
 // p.round_words words, so 2 * round_words + 8 words cover every position round r+1 can need.
 __global__ void __launch_bounds__(512, 1) decode_unbounded_v4(const DecParamsV4 p) {
+  const unsigned long long trace_t0 = global_ns();
   Tables t;
   stage_tables_v4(p.cdf, p.rows, p.cols, p.cdf_size, p.offset, p.precision, smem_v4,
                   p.table_bytes, &t);
@@ -572,6 +584,10 @@ __global__ void __launch_bounds__(512, 1) decode_unbounded_v4(const DecParamsV4 
     p_cur = p_next;
   }
   if (lane == 0 && p.status) p.status[s] = d.corrupt ? TFC_STREAM_CORRUPT : TFC_STREAM_OK;
+  if (lane == 0) {
+    atomicAdd(&g_trace[2], global_ns() - trace_t0);
+    atomicAdd(&g_trace[3], 1ull);
+  }
 }
 
 
@@ -629,6 +645,7 @@ __device__ __forceinline__ void put_byte(uint8_t* out, uint32_t cap, uint32_t at
 // warps synchronise on their own named barrier, so streams never wait for each other.
 template <bool MULTI>
 __global__ void __launch_bounds__(MULTI ? 768 : 96) encode_unbounded_v4(const EncParamsV4 p) {
+  const unsigned long long trace_t0 = global_ns();
   Tables t;
   stage_tables_v4(p.cdf, p.rows, p.cols, p.cdf_size, p.offset, p.precision, smem_v4,
                   p.table_bytes, &t);
@@ -887,6 +904,8 @@ __global__ void __launch_bounds__(MULTI ? 768 : 96) encode_unbounded_v4(const En
       p.nbytes[s] = (int32_t)nbytes;
       if (p.status) p.status[s] = (nbytes > cap || 2u * total > cap) ? TFC_STREAM_CAPACITY
                                                                     : TFC_STREAM_OK;
+      atomicAdd(&g_trace[0], global_ns() - trace_t0);
+      atomicAdd(&g_trace[1], 1ull);
     }
   }
 }

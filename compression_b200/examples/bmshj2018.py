@@ -148,7 +148,13 @@ class Pipeline(object):
   """
 
   def __init__(self, model, depth=3, tiles_per_cta=8, coder_streams_per_cta=4, back_lag=None,
-               host_slots=None):
+               host_slots=None, conv_stages=0, coder_smem_kb=0, coder_table_kb=0):
+    """`conv_stages`, `coder_smem_kb`, `coder_table_kb` (0: library defaults) size the transform
+    and coder CTAs so that they can share an SM: a 3-stage implicit-GEMM CTA takes 172 KB of the
+    SM's 228 KB of shared memory and 54 K of its 64 K registers, which leaves room for ONE
+    one-stream coder CTA of at most ~54 KB (`coder_streams_per_cta=1`, tables beyond
+    `coder_table_kb` read through L1) — the latency-bound coder of batch k then runs in the idle
+    issue slots of the SMs that convolve batch k+1 instead of taking SMs away from them."""
     from compression_b200 import _lib
     self.model = model
     self.depth = max(1, int(depth))
@@ -161,17 +167,22 @@ class Pipeline(object):
     self._lib = _lib
     self.tiles_per_cta = int(tiles_per_cta) if self.depth > 1 else 0
     self.pack = int(coder_streams_per_cta) if self.depth > 1 else 0
+    self.share = (int(conv_stages), int(coder_smem_kb), int(coder_table_kb)) if self.depth > 1 \
+        else (0, 0, 0)
     self.h2d_bytes = self.d2h_bytes = 0
     self.host_busy_s = self.host_wait_s = 0.0
     self._cap = None          # (string, side string) slab bytes per image, learnt from traffic
 
   def __enter__(self):
     if self.depth > 1:
-      self._lib.configure(coder_streams_per_cta=self.pack, tiles_per_cta=self.tiles_per_cta)
+      self._lib.configure(coder_streams_per_cta=self.pack, tiles_per_cta=self.tiles_per_cta,
+                          conv_stages=self.share[0], coder_smem_kb=self.share[1],
+                          coder_table_kb=self.share[2])
     return self
 
   def __exit__(self, *exc):
-    self._lib.configure(coder_streams_per_cta=0, tiles_per_cta=0)
+    self._lib.configure(coder_streams_per_cta=0, tiles_per_cta=0, conv_stages=0, coder_smem_kb=0,
+                        coder_table_kb=0)
     return False
 
   def _fork(self):
@@ -438,8 +449,9 @@ class Bmshj2018Model(object):
                 z_likelihoods=z_lik, eval_bpp=float(bpp))
 
   def pipeline(self, depth=3, tiles_per_cta=8, coder_streams_per_cta=4, back_lag=None,
-               host_slots=None):
-    return Pipeline(self, depth, tiles_per_cta, coder_streams_per_cta, back_lag, host_slots)
+               host_slots=None, **share):
+    return Pipeline(self, depth, tiles_per_cta, coder_streams_per_cta, back_lag, host_slots,
+                    **share)
 
   # ---- host-side strings --------------------------------------------------------------------
   @staticmethod

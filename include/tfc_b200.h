@@ -66,7 +66,33 @@ int64_t tfc_launch_count(void);
 #define TFC_CFG_TILES_PER_CTA 3
 #define TFC_CFG_CONV_CLUSTER 4
 #define TFC_CFG_CODER_LANES 5
+/*   TFC_CFG_CONV_STAGES            stages of the implicit-GEMM kernel's TMA operand ring: 0 = automatic
+ *                                  (4), 2, 3, 4.  Three stages take 172 KB instead of 216 KB of shared
+ *                                  memory per CTA, which leaves room on the SM for a one-stream
+ *                                  range-coder CTA of another batch (co-residency)
+ *   TFC_CFG_CODER_TABLE_KB         shared-memory budget (KB) of the range coder's staged CDF tables:
+ *                                  0 = automatic (72); tables that do not fit are read through L1
+ *                                  from the caller's dense table (rows of 5 entries — the fast path —
+ *                                  live in the 32-byte row records, which are always staged)
+ *   TFC_CFG_CODER_SMEM_KB          dynamic shared memory (KB) a warps-per-stream coder CTA may take:
+ *                                  0 = automatic (226), else 16..226; the per-stream round buffers
+ *                                  shrink (shorter rounds) until the CTA fits
+ *   TFC_CFG_CONV_PAIR              implicit-GEMM kernel on CTA pairs: one tcgen05.mma.cta_group::2 of
+ *                                  M = 256 covers two adjacent 128-pixel tiles, the two CTAs of the
+ *                                  cluster each hold half of the weight tile (half the shared-memory
+ *                                  operand reads per FLOP).  0 = automatic, 1 = off, 2 = on where the
+ *                                  shape allows (even tile count per phase, filters a multiple of 32) */
+#define TFC_CFG_CONV_STAGES 6
+#define TFC_CFG_CODER_TABLE_KB 7
+#define TFC_CFG_CODER_SMEM_KB 8
+#define TFC_CFG_CONV_PAIR 9
 int tfc_configure(int key, int value);
+
+/* Debug aid (no reference counterpart): how long the warps-per-stream coder kernels held their
+ * SMs.  h_out4 = {encode ns, encode streams, decode ns, decode streams}, each stream's time from
+ * its CTA's first instruction to its last, summed since the last reset.  Synchronises the
+ * device.  tools/pipe_gantt.py uses it to tell "waiting for an SM" from "running on it". */
+int tfc_debug_coder_trace(uint64_t* h_out4, int reset);
 
 /* ------------------------------------------------------------------------------------------
  * Entropy coding — replaces the five custom ops of cc/ops/range_coding_ops.cc

@@ -606,3 +606,42 @@ def test_entropy_models_training_true_is_differentiable(tfc):
   _, lik2 = gc(y2, training=True)
   torch.log(lik2).sum().backward()
   assert float(y2.grad.abs().sum()) > 0 and float(sigma.grad.abs().sum()) > 0
+
+
+@pytest.mark.parametrize("corr,sd,su,act", [(True, 2, 1, "gdn"), (False, 1, 2, "igdn"),
+                                            (True, 1, 1, "relu"), (True, 2, 1, None)])
+def test_cta_pair_conv_equals_single_cta(tfc, corr, sd, su, act):
+  """TFC_CFG_CONV_PAIR: the implicit GEMM on CTA pairs (tcgen05.mma.cta_group::2, M = 256 over
+  two adjacent tiles, each CTA holding half of the weight tile) sums the same products in the
+  same order as the one-CTA kernel: identical outputs, bit for bit, including ragged tiles and an
+  odd tile count per image (pairs then straddle images)."""
+  rng = np.random.default_rng(41)
+  k, cin, cout = (3 if act == "relu" else 5), 192, 192
+  kern = (rng.integers(-8, 9, size=(k, k, cin, cout)) / 16.0).astype(np.float32)
+  b = (rng.integers(-8, 9, size=cout) / 4.0).astype(np.float32)
+  activation = {"gdn": tfc.GDN(), "igdn": tfc.GDN(inverse=True), "relu": torch.relu, None: None}[act]
+  layer = tfc.SignalConv2D(cout, (k, k), corr=corr, strides_down=sd, strides_up=su,
+                           padding="same_zeros", use_bias=True, activation=activation,
+                           kernel_parameterizer=None, kernel_initializer=_static(kern),
+                           bias_initializer=_static(b), impl=2)
+  layer.build(cin, "cuda")
+  for n, h, w in ((4, 40, 56), (3, 24, 40), (2, 16, 16)):
+    x = torch.from_numpy(rng.integers(-3, 4, size=(n, h, w, cin)).astype(np.float32)).cuda()
+    x = x.to(torch.bfloat16)
+    outs = {}
+    for mode in (1, 2):
+      tfc.configure(conv_pair=mode)
+      try:
+        outs[mode] = layer(x, out_dtype=torch.bfloat16)
+      finally:
+        tfc.configure(conv_pair=0)
+    assert torch.equal(outs[1], outs[2]), (n, h, w)
+  want = tfc_np.signal_conv2d(x.float().cpu().numpy(), kern, b, corr, sd, su, "same_zeros")
+  if act in ("gdn", "igdn"):
+    beta, gamma = [t.cpu().numpy() for t in activation.effective()]
+    want = tfc_np.gdn(want, beta, gamma, act == "igdn")
+  elif act == "relu":
+    want = torch.relu(want)
+  want = want.numpy()
+  got = outs[2].float().cpu().numpy()
+  assert np.abs(got - want).max() / (np.abs(want).max() + 1e-6) <= 2e-2

@@ -349,3 +349,32 @@ def test_decoder_clamps_oversize_nbytes(tfc, oracle, coder_lanes):
   np.testing.assert_array_equal(back.cpu().numpy(), d16)
   with pytest.raises(rc.InvalidArgumentError, match="corrupt"):
     rc.range_decode_batch(o2[:, :16].contiguous(), n2, (200,), cdf1, 16, debug_level=0)
+
+
+@pytest.mark.parametrize("smem_kb,table_kb", [(54, 24), (54, 8), (32, 8)])
+def test_compact_coder_ctas_code_the_same_bytes(tfc, oracle, smem_kb, table_kb):
+  """TFC_CFG_CODER_SMEM_KB / TFC_CFG_CODER_TABLE_KB: small coder CTAs (shorter rounds, long
+  table rows read through L1 instead of staged) produce the reference's bytes and decode them."""
+  from compression_b200.python.layers import entropy_models
+  from compression_b200.python.ops import range_coding_ops as rc
+  dev = torch.device("cuda", 0)
+  table = np.exp(np.linspace(np.log(0.11), np.log(256), 64))
+  gc = entropy_models.GaussianConditional(None, table)
+  gc.build_tables(dev)
+  cdf, size, off = gc._quantized_cdf, gc._cdf_length, gc._offset
+  rng = np.random.default_rng(smem_kb + table_kb)
+  S, n = 6, 20011
+  idx = rng.integers(0, 64, size=(S, n)).astype(np.int32)
+  idx[:3] = np.minimum(rng.geometric(0.6, size=(3, n)) - 1, 12)
+  sym = np.floor(rng.standard_normal((S, n)) * table[idx] * 1.3 + .5).astype(np.int32)
+  tfc.configure(coder_lanes=1, coder_smem_kb=smem_kb, coder_table_kb=table_kb)
+  try:
+    out, nbytes = rc.unbounded_index_range_encode_batch(sym, idx, cdf, size, off, 16, 4, 0)
+    dec = rc.unbounded_index_range_decode_batch(out, nbytes, idx, cdf, size, off, 16, 4, 0)
+  finally:
+    tfc.configure(coder_lanes=0, coder_smem_kb=0, coder_table_kb=0)
+  got = rc.strings_to_host(out, nbytes)
+  c, s_, o = cdf.cpu().numpy(), size.cpu().numpy(), off.cpu().numpy()
+  for s in range(S):
+    assert got[s] == oracle.ui_encode(sym[s], idx[s], c, s_, o, 16, 4), s
+  np.testing.assert_array_equal(dec.cpu().numpy(), sym)

@@ -18,6 +18,9 @@ def main():
   ap.add_argument("--width", type=int, default=768)
   ap.add_argument("--pack", type=int, default=0)
   ap.add_argument("--reps", type=int, default=5)
+  ap.add_argument("--lanes", type=int, default=0, help="0 auto, 1 warps per stream, 2 lane per stream")
+  ap.add_argument("--smem-kb", type=int, default=0)
+  ap.add_argument("--table-kb", type=int, default=0)
   args = ap.parse_args()
   import compression_b200 as tfc
   from compression_b200.examples import bmshj2018
@@ -26,7 +29,9 @@ def main():
   x = torch.rand((args.batch, args.height, args.width, 3), device=dev)
   y, z, sigma = model.analyse(x)
   c = model.compress(x)
-  tfc.configure(coder_streams_per_cta=args.pack)
+  tfc.configure(coder_lanes=args.lanes)
+  tfc.configure(coder_streams_per_cta=args.pack, coder_smem_kb=args.smem_kb,
+                coder_table_kb=args.table_kb)
   eb, gc = model.entropy_bottleneck, model._conditional(sigma)
   nf = 192
 

@@ -26,6 +26,8 @@ def main():
   ap.add_argument("--debug", type=int, default=0, help="kernel experiment bits (timing only)")
   ap.add_argument("--tiles-per-cta", type=int, default=0)
   ap.add_argument("--cluster", type=int, default=0, help="0 auto, 1 off, 2, 4")
+  ap.add_argument("--stages", type=int, default=0, help="operand-ring stages (0: 4)")
+  ap.add_argument("--pair", type=int, default=0, help="cta_group::2 MMAs: 0 auto, 1 off, 2 on")
   args = ap.parse_args()
   from compression_b200.examples import bmshj2018
   from compression_b200.python.layers import gdn as gdn_lib
@@ -34,6 +36,10 @@ def main():
     _lib.check(_lib.lib().tfc_configure(99, args.debug))
   if args.cluster:
     _lib.configure(conv_cluster=args.cluster)
+  if args.stages:
+    _lib.configure(conv_stages=args.stages)
+  if args.pair:
+    _lib.configure(conv_pair=args.pair)
   if args.tiles_per_cta:
     _lib.configure(tiles_per_cta=args.tiles_per_cta)
   dev = torch.device("cuda", 0)
