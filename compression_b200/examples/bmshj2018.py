@@ -148,8 +148,18 @@ class Pipeline(object):
   """
 
   def __init__(self, model, depth=3, tiles_per_cta=8, coder_streams_per_cta=4, back_lag=None,
-               host_slots=None, conv_stages=0, coder_smem_kb=0, coder_table_kb=0):
-    """`conv_stages`, `coder_smem_kb`, `coder_table_kb` (0: library defaults) size the transform
+               host_slots=None, conv_stages=0, coder_smem_kb=0, coder_table_kb=0,
+               stage_streams=True):
+    """`stage_streams` (default): the TRANSFORM phases of all batches share a few "stage" streams
+    (3 for analysis, 2 for the decoder's hyper-synthesis, 3 for synthesis) and only the CODER
+    phases get one stream per batch in flight.  torch's caching allocator keeps one pool per
+    stream, and the big activations (0.46 GB per 1080p image) are transform-phase temporaries: with
+    a stream per batch the memory reserved grows with the batches in flight (134 GB at 18 x 16
+    1080p images), with stage streams it stays at ~8 pools however many batches the latency-bound
+    coder needs in flight.  Tensors that cross streams are handed over with events +
+    `record_stream`.  `stage_streams=False`: one stream per batch for everything.
+
+    `conv_stages`, `coder_smem_kb`, `coder_table_kb` (0: library defaults) size the transform
     and coder CTAs so that they can share an SM: a 3-stage implicit-GEMM CTA takes 172 KB of the
     SM's 228 KB of shared memory and 54 K of its 64 K registers, which leaves room for ONE
     one-stream coder CTA of at most ~54 KB (`coder_streams_per_cta=1`, tables beyond
@@ -164,6 +174,10 @@ class Pipeline(object):
     self.back_lag = (min(self.host_slots - 1, max(1, int(back_lag))) if back_lag
                      else max(1, self.host_slots // 2))
     self.streams = [torch.cuda.Stream(device=model.device) for _ in range(self.depth)]
+    self.stage = None
+    if stage_streams and self.depth > 1:
+      mk = lambda n: [torch.cuda.Stream(device=model.device) for _ in range(n)]
+      self.stage = {"analysis": mk(3), "hyper": mk(2), "synthesis": mk(3)}
     self._lib = _lib
     self.tiles_per_cta = int(tiles_per_cta) if self.depth > 1 else 0
     self.pack = int(coder_streams_per_cta) if self.depth > 1 else 0
@@ -185,15 +199,45 @@ class Pipeline(object):
                         coder_table_kb=0)
     return False
 
+  def _all_streams(self):
+    extra = [s for group in self.stage.values() for s in group] if self.stage else []
+    return self.streams + extra
+
   def _fork(self):
     cur = torch.cuda.current_stream(self.model.device)
-    for s in self.streams:
+    for s in self._all_streams():
       s.wait_stream(cur)
     return cur
 
   def _join(self, cur):
-    for s in self.streams:
+    for s in self._all_streams():
       cur.wait_stream(s)
+
+  def _streams_of(self, k):
+    """(analysis, coder, hyper-synthesis, synthesis) streams of batch k."""
+    e = self.streams[k % self.depth]
+    if not self.stage:
+      return e, e, e, e
+    g = self.stage
+    return (g["analysis"][k % len(g["analysis"])], e, g["hyper"][k % len(g["hyper"])],
+            g["synthesis"][k % len(g["synthesis"])])
+
+  @staticmethod
+  def _hand(src, dst, *tensors):
+    """Hand tensors produced on stream `src` to stream `dst`: dst waits for what src has queued so
+    far, and the allocator is told that dst uses the memory (it must not be given to another
+    tensor of src's pool before dst is done with it)."""
+    if src is dst:
+      return
+    ev = torch.cuda.Event()
+    ev.record(src)
+    dst.wait_event(ev)
+    for t in tensors:
+      if isinstance(t, (tuple, list)):
+        for u in t:
+          u.record_stream(dst)
+      elif t is not None:
+        t.record_stream(dst)
 
   def roundtrip_device(self, batches):
     """batches: device float32 [B,H,W,3] tensors -> list of x_hat (device).  The coder's status
@@ -202,12 +246,39 @@ class Pipeline(object):
     from compression_b200.python.ops import range_coding_ops as rc
     model, outs = self.model, []
     cur = self._fork()
+    done = {}
     with rc.deferred_checks() as checks:
       for k, x in enumerate(batches):
-        st = self.streams[k % self.depth]
         checks.tag = k
-        with torch.cuda.stream(st):
-          outs.append(model.decompress(model.compress(x, self._stagger(k, st))))
+        if not self.stage:
+          st = self.streams[k % self.depth]
+          with torch.cuda.stream(st):
+            outs.append(model.decompress(model.compress(x, self._stagger(k, st))))
+          checks.drain(2 * self.depth)
+          continue
+        a, e, hs, sy = self._streams_of(k)
+        if k - self.depth in done:            # at most `depth` batches between analysis and x_hat
+          a.wait_event(done.pop(k - self.depth))
+        with torch.cuda.stream(a):
+          y, z, sigma = model.analyse(x)
+        self._hand(a, e, y, z, sigma)
+        with torch.cuda.stream(e):
+          string, side_string = model.encode_strings(y, z, sigma)
+          z_hat = model.decode_z(side_string, tuple(z.shape[1:-1]))
+        self._hand(e, hs, z_hat)
+        with torch.cuda.stream(hs):
+          sigma2 = model.hyper_sigma(z_hat, tuple(y.shape[1:-1]))
+        self._hand(hs, e, sigma2)
+        with torch.cuda.stream(e):
+          y_hat = model.decode_y(string, sigma2)
+        self._hand(e, sy, y_hat)
+        with torch.cuda.stream(sy):
+          x_hat = model.synthesize(y_hat, tuple(x.shape[1:-1]))
+          ev = done[k] = torch.cuda.Event()
+          ev.record(sy)
+        x_hat.record_stream(cur)
+        outs.append(x_hat)
+        del y, z, sigma, z_hat, sigma2, y_hat, string, side_string
         checks.drain(2 * self.depth)
       self._join(cur)
     return outs
@@ -290,10 +361,21 @@ class Pipeline(object):
 
     def front_work(k, slot, st, checks, cap):
       checks.tag = ("front", k)
-      with torch.cuda.stream(st):
+      a, e, _, _ = self._streams_of(k)
+      with torch.cuda.stream(a):
         x = batches_u8[k].to(dev, non_blocking=True)
-        c = model.compress(x, self._stagger(k, st) if cap is not False else None,
-                           cap=cap or None)
+        if self.stage:
+          y, z, sigma = model.analyse(x)
+        else:
+          c = model.compress(x, self._stagger(k, st) if cap is not False else None,
+                             cap=cap or None)
+      if self.stage:
+        self._hand(a, e, y, z, sigma)
+      with torch.cuda.stream(e):
+        if self.stage:
+          string, side_string = model.encode_strings(y, z, sigma, cap or None)
+          c = Compressed(string, side_string, tuple(x.shape[1:-1]), tuple(y.shape[1:-1]),
+                         tuple(z.shape[1:-1]))
         staged = []
         for name, (slab, nbytes) in (("y", c.string), ("z", c.side_string)):
           hs = pinned(slot, name + "_slab", slab.shape, torch.uint8)
@@ -332,17 +414,32 @@ class Pipeline(object):
       host = Compressed(HostStrings(*staged[0]), HostStrings(*staged[1]), c.x_shape, c.y_shape,
                         c.z_shape)
       checks.tag = ("back", k)
-      with torch.cuda.stream(st):
+      _, e, hstream, sy = self._streams_of(k)
+      with torch.cuda.stream(e):
         # back to the device straight from the pinned slabs the strings arrived in
         dev_strings = []
         for hs, hn in staged:
           dev_strings.append((hs.to(dev, non_blocking=True), hn.to(dev, non_blocking=True)))
         dc = Compressed(dev_strings[0], dev_strings[1], c.x_shape, c.y_shape, c.z_shape)
-        x_hat = model.decompress(dc, out_dtype=torch.uint8)
+        if not self.stage:
+          x_hat = model.decompress(dc, out_dtype=torch.uint8)
+        else:
+          z_hat = model.decode_z(dc.side_string, dc.z_shape)
+      if self.stage:
+        self._hand(e, hstream, z_hat)
+        with torch.cuda.stream(hstream):
+          sigma2 = model.hyper_sigma(z_hat, dc.y_shape)
+        self._hand(hstream, e, sigma2)
+        with torch.cuda.stream(e):
+          y_hat = model.decode_y(dc.string, sigma2)
+        self._hand(e, sy, y_hat)
+      with torch.cuda.stream(sy):
+        if self.stage:
+          x_hat = model.synthesize(y_hat, dc.x_shape, torch.uint8)
         out = pinned(slot, "x_hat", x_hat.shape, torch.uint8)
         out.copy_(x_hat, non_blocking=True)
         done = torch.cuda.Event()
-        done.record(st)
+        done.record(sy)
       slot["host"], slot["done"], slot["pending"], slot["x_hat_view"] = host, done, k, out
       if k == n - 1:                     # bytes per batch at the steady-state slab size
         strings = sum(hs.numel() + 4 * hn.numel() for hs, hn in staged)
@@ -405,6 +502,31 @@ class Bmshj2018Model(object):
     sigma = sigma[:, :y.shape[1], :y.shape[2], :].contiguous()
     return y, z, sigma
 
+  # ---- the phases of compress / decompress, so that a pipeline can put the transform phases and
+  # the coder phases of a batch on different CUDA streams (see Pipeline) ----------------------
+  def encode_strings(self, y, z, sigma, cap=None):
+    """entropy coding of compress(): (y, z, sigma) -> (string, side_string) on the device."""
+    cap_y, cap_z = cap if cap is not None else (None, None)
+    side_string = self.entropy_bottleneck.compress_device(z, cap=cap_z)
+    string = self._conditional(sigma).compress_device(y, cap=cap_y)
+    return string, side_string
+
+  def decode_z(self, side_string, z_shape):
+    nf = self.num_filters
+    return self.entropy_bottleneck.decompress_device(
+        side_string, tuple(z_shape) + (nf,), channels=nf, out_dtype=torch.bfloat16)
+
+  def hyper_sigma(self, z_hat, y_shape):
+    sigma = self.hyper_synthesis_transform(z_hat)
+    return sigma[:, :y_shape[0], :y_shape[1], :].contiguous()
+
+  def decode_y(self, string, sigma):
+    return self._conditional(sigma).decompress_device(string, out_dtype=torch.bfloat16)
+
+  def synthesize(self, y_hat, x_shape, out_dtype=torch.float32):
+    x_hat = self.synthesis_transform(y_hat, out_dtype=out_dtype)
+    return x_hat[:, :x_shape[0], :x_shape[1], :]
+
   def compress(self, x, after_analysis=None, cap=None):
     """x: float32 [B,H,W,3] in [0,1], or the uint8 image itself (a byte b stands for b / 255 as
     in read_png, bmshj2018.py:53-57; the first analysis layer reads the bytes directly).
@@ -416,9 +538,7 @@ class Bmshj2018Model(object):
     y, z, sigma = self.analyse(x)
     if after_analysis is not None:
       after_analysis()
-    cap_y, cap_z = cap if cap is not None else (None, None)
-    side_string = self.entropy_bottleneck.compress_device(z, cap=cap_z)
-    string = self._conditional(sigma).compress_device(y, cap=cap_y)
+    string, side_string = self.encode_strings(y, z, sigma, cap)
     return Compressed(string, side_string, tuple(x.shape[1:-1]), tuple(y.shape[1:-1]),
                       tuple(z.shape[1:-1]))
 
@@ -426,14 +546,10 @@ class Bmshj2018Model(object):
   def decompress(self, c, out_dtype=torch.float32):
     """-> x_hat [B,H,W,3]: float32, or with out_dtype=torch.uint8 the quantised image
     (quantize_image, bmshj2018.py:60-63, fused into the last synthesis layer)."""
-    nf = self.num_filters
-    z_hat = self.entropy_bottleneck.decompress_device(
-        c.side_string, tuple(c.z_shape) + (nf,), channels=nf, out_dtype=torch.bfloat16)
-    sigma = self.hyper_synthesis_transform(z_hat)
-    sigma = sigma[:, :c.y_shape[0], :c.y_shape[1], :].contiguous()
-    y_hat = self._conditional(sigma).decompress_device(c.string, out_dtype=torch.bfloat16)
-    x_hat = self.synthesis_transform(y_hat, out_dtype=out_dtype)
-    return x_hat[:, :c.x_shape[0], :c.x_shape[1], :]
+    z_hat = self.decode_z(c.side_string, c.z_shape)
+    sigma = self.hyper_sigma(z_hat, c.y_shape)
+    y_hat = self.decode_y(c.string, sigma)
+    return self.synthesize(y_hat, c.x_shape, out_dtype)
 
   # ---- verbose branch of compress (bmshj2018.py:314-333) ----------------------------------
   def evaluate(self, x):
