@@ -38,8 +38,9 @@ extern "C" int tfc_configure(int key, int value) {
       tfc::g_sm_budget.store(value);
       return TFC_OK;
     case TFC_CFG_CODER_STREAMS_PER_CTA:
-      if (value < 0 || value > 8)
-        return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "coder streams per CTA must be in [0, 8]");
+      // warps-per-stream kernels use min(value, 8); the lane-per-stream kernels value / 32 warps
+      if (value < 0 || value > 512)
+        return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "coder streams per CTA must be in [0, 512]");
       tfc::g_coder_pack.store(value);
       return TFC_OK;
     case TFC_CFG_TILES_PER_CTA:

@@ -532,6 +532,11 @@ size_t lanes_geometry(int64_t S, int table_bytes, int* wpc, int64_t* blocks) {
   const int64_t warps = (S + 31) / 32;
   const int sms = tfc::num_sms();
   int w = (int)std::max<int64_t>(1, std::min<int64_t>(lanes::kMaxWarps, (warps + sms - 1) / sms));
+  // packed (tfc_configure TFC_CFG_CODER_STREAMS_PER_CTA >= 32): pack / 32 warps share one CTA, so
+  // that a latency-bound chain warp (about 0.2 instructions per cycle on its own) has 15
+  // neighbours filling the SM's issue slots instead of holding an SM by itself
+  const int pack = tfc::g_coder_pack.load(std::memory_order_relaxed);
+  if (pack >= 32) w = (int)std::min<int64_t>(std::min(lanes::kMaxWarps, pack / 32), warps);
   const size_t smem_max = 227 * 1024 - 1024;
   while (w > 1 && (size_t)table_bytes + w * lanes::kWarpBytes > smem_max) --w;
   *wpc = w;
@@ -686,7 +691,7 @@ extern "C" int tfc_unbounded_index_range_encode(
     // streams per CTA: 1 unless the caller packs the coder (tfc_configure); the per-stream
     // round buffers shrink until the CTA fits in shared memory
     const int pack = tfc::g_coder_pack.load(std::memory_order_relaxed);
-    q.streams_per_cta = (int)std::max<int64_t>(1, std::min<int64_t>(pack > 0 ? pack : 1, S));
+    q.streams_per_cta = (int)std::max<int64_t>(1, std::min<int64_t>(pack > 0 ? std::min(pack, 8) : 1, S));
     const int min_cap = (32 * v4_max_puts(overflow_width) + 31) / 32 * 32;   // one 32-symbol round
     q.put_cap = std::max(v4::kPutCap, min_cap);
     const size_t smem_max = coder_smem_max();
@@ -788,7 +793,7 @@ extern "C" int tfc_unbounded_index_range_decode(
     const int sms = tfc::num_sms();
     q.streams_per_cta = S <= sms ? 1 : (S <= 2 * (int64_t)sms ? 2 : 4);
     const int pack = tfc::g_coder_pack.load(std::memory_order_relaxed);
-    if (pack > 0) q.streams_per_cta = (int)std::max<int64_t>(1, std::min<int64_t>(pack, S));
+    if (pack > 0) q.streams_per_cta = (int)std::max<int64_t>(1, std::min<int64_t>(std::min(pack, 8), S));
     // rounds as long as shared memory allows (fewer barriers), shorter when streams are packed
     const size_t smem_max = coder_smem_max();
     auto geometry = [&](int round) {

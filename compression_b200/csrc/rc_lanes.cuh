@@ -104,6 +104,13 @@ struct Enc {
   }
 };
 
+// A lane walks its own stream as a small state machine, ONE interval update per trip of the
+// loop: phase 0 codes the next symbol (or its escape marker), phase 1 the digit count in unary
+// groups, phase 2 the digits.  The lanes of the warp are therefore only synchronised at tile
+// boundaries: a lane inside an escape (about 11 updates) does not hold the other 31 up, the
+// way a per-symbol loop with the escape expansion in its body does (measured: 44 % of the
+// 32-symbol steps of the Gaussian workload hold at least one escape).
+// The next tile's symbols and indexes are fetched into registers before the chain runs.
 __global__ void __launch_bounds__(kMaxWarps * 32, 1) encode_unbounded_lanes(const Params p) {
   v4::Tables t;
   v4::stage_tables_v4(p.cdf, p.rows, p.cols, p.cdf_size, p.offset, p.precision, v4::smem_v4,
@@ -122,41 +129,69 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) encode_unbounded_lanes(cons
   e.even = (reinterpret_cast<uintptr_t>(e.out) & 1) == 0;
   const int ow = p.overflow_width, dsh = 16 - ow;
   const uint32_t all1 = (1u << ow) - 1u;
-  for (int64_t i0 = 0; i0 < p.n; i0 += kTile) {
+  int32_t pd[kTile], pi[kTile];
+  auto fetch = [&](int64_t i0) {
     const bool col = i0 + lane < p.n;
-#pragma unroll 8
-    for (int r = 0; r < rows_here; ++r) {
-      int32_t dv = 0, iv = 0;
-      if (col) {
-        dv = __ldg(p.data + (s0 + r) * p.n + i0 + lane);
-        iv = __ldg(p.index + (s0 + r) * p.index_stride + i0 + lane);
-      }
-      td[r * kLd + lane] = dv;
-      ti[r * kLd + lane] = iv;
+#pragma unroll
+    for (int r = 0; r < kTile; ++r) {
+      const bool on = col && r < rows_here;
+      pd[r] = on ? __ldg(p.data + (s0 + r) * p.n + i0 + lane) : 0;
+      pi[r] = on ? __ldg(p.index + (s0 + r) * p.index_stride + i0 + lane) : 0;
+    }
+  };
+  fetch(0);
+  for (int64_t i0 = 0; i0 < p.n; i0 += kTile) {
+#pragma unroll
+    for (int r = 0; r < kTile; ++r) {
+      td[r * kLd + lane] = pd[r];
+      ti[r * kLd + lane] = pi[r];
     }
     __syncwarp();
+    if (i0 + kTile < p.n) fetch(i0 + kTile);
     if (active) {
       const int cnt = (int)min((int64_t)kTile, p.n - i0);
-      for (int j = 0; j < cnt; ++j) {
-        const int32_t row = min(max(ti[lane * kLd + j], 0), p.rows - 1);
-        const int4 ri = t.rowinfo[row];                      // {start, len, offset}
-        const int32_t esc = ri.y - 2;                        // escape symbol == #direct values
-        const int32_t v = td[lane * kLd + j] - ri.z;
-        const bool direct = v >= 0 && v < esc;
-        const int32_t k = direct ? v : esc;
-        e.put(t.at(ri.x + k), t.at(ri.x + k + 1));
-        if (!direct) {       // unbounded_index_range_coding_kernels.cc:213-247
-          const uint32_t x = v < 0 ? (uint32_t)(-2 * v - 1) : (uint32_t)(2 * (v - esc));
-          int nd = 0;
-          while (((uint64_t)x >> (nd * ow)) != 0) ++nd;
-          uint32_t u = (uint32_t)nd;
-          for (; u >= all1; u -= all1) e.put(all1 << dsh, (all1 + 1u) << dsh);
-          e.put(u << dsh, (u + 1u) << dsh);
-          for (int q = 0; q < nd; ++q) {
-            const uint32_t d = (x >> (q * ow)) & all1;
-            e.put(d << dsh, (d + 1u) << dsh);
+      int j = 0, phase = 0, nd = 0, q = 0;
+      uint32_t x = 0, u = 0;
+      while (j < cnt || phase != 0) {
+        uint32_t c0, c1;
+        if (phase == 0) {
+          const int32_t row = min(max(ti[lane * kLd + j], 0), p.rows - 1);
+          const int4 ri = t.rowinfo[row];                    // {start, len, offset, entry 0}
+          const uint4 rr = t.rowrec[row];
+          const int32_t esc = ri.y - 2;                      // escape symbol == #direct values
+          const int32_t v = td[lane * kLd + j] - ri.z;
+          const bool direct = v >= 0 && v < esc;
+          ++j;
+          if (direct && rr.z != 0u) {                        // 5-entry row: {e0, c1, c2, c3, top}
+            c0 = v == 0 ? (uint32_t)ri.w : ((v == 1 ? rr.x : rr.y) >> 16);
+            c1 = (v == 0 ? rr.x : (v == 1 ? rr.y : rr.z)) >> 16;
+          } else {
+            const int32_t k = direct ? v : esc;
+            c0 = t.at(ri.x + k);
+            c1 = t.at(ri.x + k + 1);
           }
+          if (!direct) {       // unbounded_index_range_coding_kernels.cc:213-247
+            x = v < 0 ? (uint32_t)(-2 * v - 1) : (uint32_t)(2 * (v - esc));
+            nd = 0;
+            while (((uint64_t)x >> (nd * ow)) != 0) ++nd;
+            u = (uint32_t)nd;
+            q = 0;
+            phase = 1;
+          }
+        } else if (phase == 1) {                             // digit count, all1 per group
+          if (u >= all1) {
+            c0 = all1 << dsh; c1 = (all1 + 1u) << dsh;
+            u -= all1;
+          } else {
+            c0 = u << dsh; c1 = (u + 1u) << dsh;
+            phase = nd > 0 ? 2 : 0;
+          }
+        } else {                                             // digits, least significant first
+          const uint32_t dg = (x >> (q * ow)) & all1;
+          c0 = dg << dsh; c1 = (dg + 1u) << dsh;
+          if (++q == nd) phase = 0;
         }
+        e.put(c0, c1);
       }
     }
     __syncwarp();
@@ -239,6 +274,10 @@ struct Dec {
   }
 };
 
+// Same structure as the encoder: one interval search per trip of the loop (symbol, digit-count
+// group or digit), lanes synchronised only at tile boundaries.  A symbol of a 5-entry row is
+// found with three multiplies (the row record holds c1..c3 scaled so that
+// floor(span * c / 2^16) is one IMAD.HI); everything else is the binary search of Dec::get.
 __global__ void __launch_bounds__(kMaxWarps * 32, 1) decode_unbounded_lanes(const Params p) {
   v4::Tables t;
   v4::stage_tables_v4(p.cdf, p.rows, p.cols, p.cdf_size, p.offset, p.precision, v4::smem_v4,
@@ -265,32 +304,71 @@ __global__ void __launch_bounds__(kMaxWarps * 32, 1) decode_unbounded_lanes(cons
   }
   const int ow = p.overflow_width, dsh = 16 - ow;
   const uint32_t all1 = (1u << ow) - 1u;
+  int32_t pi[kTile];
+  auto fetch = [&](int64_t i0) {
+    const bool col = i0 + lane < p.n;
+#pragma unroll
+    for (int r = 0; r < kTile; ++r)
+      pi[r] = (col && r < rows_here) ? __ldg(p.index + (s0 + r) * p.index_stride + i0 + lane) : 0;
+  };
+  fetch(0);
   for (int64_t i0 = 0; i0 < p.n; i0 += kTile) {
     const bool col = i0 + lane < p.n;
-#pragma unroll 8
-    for (int r = 0; r < rows_here; ++r)
-      ti[r * kLd + lane] = col ? __ldg(p.index + (s0 + r) * p.index_stride + i0 + lane) : 0;
+#pragma unroll
+    for (int r = 0; r < kTile; ++r) ti[r * kLd + lane] = pi[r];
     __syncwarp();
+    if (i0 + kTile < p.n) fetch(i0 + kTile);
     if (active) {
       const int cnt = (int)min((int64_t)kTile, p.n - i0);
-      for (int j = 0; j < cnt; ++j) {
-        const int32_t row = min(max(ti[lane * kLd + j], 0), p.rows - 1);
-        const int4 ri = t.rowinfo[row];
-        const int32_t esc = ri.y - 2;
-        int32_t v = d.get(t, ri.x, ri.y);
-        if (v == esc) {      // unbounded_index_range_coding_kernels.cc:336-360
-          int nd = 0;
-          uint32_t u;
-          do { u = d.digit(dsh, all1); nd += (int)u; } while (u == all1 && nd <= p.max_digits);
-          if (nd > p.max_digits) { d.corrupt = true; nd = p.max_digits; }
-          uint32_t x = 0;
-          for (int q = 0; q < nd; ++q) {
-            const uint32_t dg = d.digit(dsh, all1);
-            if (q * ow < 32) x |= dg << (q * ow);
+      int j = 0, phase = 0, nd = 0, q = 0;
+      int32_t esc = 0, off = 0;
+      uint32_t x = 0;
+      while (j < cnt) {
+        bool done = false;         // symbol j is complete: x / esc / off give its value
+        if (phase == 0) {
+          const int32_t row = min(max(ti[lane * kLd + j], 0), p.rows - 1);
+          const int4 ri = t.rowinfo[row];
+          const uint4 rr = t.rowrec[row];
+          esc = ri.y - 2;
+          off = ri.z;
+          int32_t v = -1;
+          if (rr.z != 0u && d.span1 != 0xFFFFFFFFu) {
+            const uint32_t span = d.span1 + 1u;
+            const uint32_t t1 = __umulhi(span, rr.x), t2 = __umulhi(span, rr.y),
+                           t3 = __umulhi(span, rr.z);
+            if (t3 > d.rem) {      // a direct value; entry 0 is 0 in this class (rc_v4.cuh step)
+              const bool p1 = t1 <= d.rem, p2 = t2 <= d.rem;
+              const uint32_t a = p2 ? t2 : (p1 ? t1 : 0u);
+              const uint32_t b = (p2 ? t3 : (p1 ? t2 : t1)) - 1u;
+              d.narrow(a, b);
+              v = p2 ? 2 : (p1 ? 1 : 0);
+            }
           }
-          v = (x & 1u) ? -(int32_t)(x >> 1) - 1 : (int32_t)(x >> 1) + esc;
+          if (v < 0) v = d.get(t, ri.x, ri.y);
+          if (v == esc) {          // unbounded_index_range_coding_kernels.cc:336-360
+            phase = 1; nd = 0; q = 0; x = 0;
+          } else {
+            tv[lane * kLd + j] = v + off;
+            ++j;
+          }
+        } else if (phase == 1) {   // digit count, groups of all1
+          const uint32_t u = d.digit(dsh, all1);
+          nd += (int)u;
+          if (u != all1 || nd > p.max_digits) {
+            if (nd > p.max_digits) { d.corrupt = true; nd = p.max_digits; }
+            if (nd > 0) phase = 2; else done = true;
+          }
+        } else {                   // digits, least significant first
+          const uint32_t dg = d.digit(dsh, all1);
+          if (q * ow < 32) x |= dg << (q * ow);
+          if (++q == nd) done = true;
         }
-        tv[lane * kLd + j] = v + ri.z;
+        if (done) {
+          const int32_t v = (x & 1u) ? -(int32_t)(x >> 1) - 1 : (int32_t)(x >> 1) + esc;
+          tv[lane * kLd + j] = v + off;
+          ++j;
+          phase = 0;
+        }
       }
     }
     __syncwarp();

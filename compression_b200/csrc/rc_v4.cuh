@@ -40,7 +40,7 @@ __device__ __forceinline__ unsigned long long global_ns() {
 
 struct Tables {          // shared-memory image of the CDF tables
   const uint4* rowrec;   // {c1<<16, c2<<16, c3<<16, row} (precision 16) for 5-entry rows, else c=0
-  const int4* rowinfo;   // {start, len, offset, 0}
+  const int4* rowinfo;   // {start, len, offset, entry 0 << (16 - precision)}
   const uint32_t* tbl;   // ragged rows, entries << (16 - precision); null if they did not fit
   const int32_t* gcdf;   // the caller's dense table (used when tbl is null; start = row*cols)
   int sh;
@@ -76,7 +76,9 @@ __device__ void stage_tables_v4(const int32_t* __restrict__ cdf, int rows, int c
         const int v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
         if (lane >= o) incl += v;
       }
-      if (r < rows) rowinfo[r] = make_int4(carry + incl - len, len, __ldg(offset + r), 0);
+      if (r < rows)   // .w: entry 0 at precision 16 (0 in a well-formed table)
+        rowinfo[r] = make_int4(carry + incl - len, len, __ldg(offset + r),
+                               (int)((uint32_t)__ldg(cdf + (int64_t)r * cols) << (16 - precision)));
       carry += __shfl_sync(0xFFFFFFFFu, incl, 31);
     }
     if (lane == 0) s_total = carry;

@@ -149,7 +149,7 @@ class Pipeline(object):
 
   def __init__(self, model, depth=3, tiles_per_cta=8, coder_streams_per_cta=4, back_lag=None,
                host_slots=None, conv_stages=0, coder_smem_kb=0, coder_table_kb=0,
-               stage_streams=True):
+               stage_streams=True, coder_stream_cap=22):
     """`stage_streams` (default): the TRANSFORM phases of all batches share a few "stage" streams
     (3 for analysis, 2 for the decoder's hyper-synthesis, 3 for synthesis) and only the CODER
     phases get one stream per batch in flight.  torch's caching allocator keeps one pool per
@@ -158,6 +158,13 @@ class Pipeline(object):
     1080p images), with stage streams it stays at ~8 pools however many batches the latency-bound
     coder needs in flight.  Tensors that cross streams are handed over with events +
     `record_stream`.  `stage_streams=False`: one stream per batch for everything.
+    The stage streams come from torch's HIGH-priority pool and the coder streams from the default
+    one: each pool holds 32 streams and hands them out round-robin, so more than 32 draws from
+    one pool alias (a coder stream would silently BE a stage stream, and a 100 ms coder kernel
+    would sit in front of another batch's convolutions); the device also has only 32 hardware
+    queues (CUDA_DEVICE_MAX_CONNECTIONS), hence `coder_stream_cap`: batches k and k + cap share a
+    coder stream.  The priority also makes the block scheduler place waiting transform CTAs before
+    waiting coder CTAs.
 
     `conv_stages`, `coder_smem_kb`, `coder_table_kb` (0: library defaults) size the transform
     and coder CTAs so that they can share an SM: a 3-stage implicit-GEMM CTA takes 172 KB of the
@@ -173,10 +180,13 @@ class Pipeline(object):
     self.host_slots = max(self.depth + 1, int(host_slots)) if host_slots else self.depth + 1
     self.back_lag = (min(self.host_slots - 1, max(1, int(back_lag))) if back_lag
                      else max(1, self.host_slots // 2))
-    self.streams = [torch.cuda.Stream(device=model.device) for _ in range(self.depth)]
+    n_coder = self.depth
+    if stage_streams and self.depth > 1 and coder_stream_cap:
+      n_coder = min(self.depth, max(1, int(coder_stream_cap)))
+    self.streams = [torch.cuda.Stream(device=model.device) for _ in range(n_coder)]
     self.stage = None
     if stage_streams and self.depth > 1:
-      mk = lambda n: [torch.cuda.Stream(device=model.device) for _ in range(n)]
+      mk = lambda n: [torch.cuda.Stream(device=model.device, priority=-1) for _ in range(n)]
       self.stage = {"analysis": mk(3), "hyper": mk(2), "synthesis": mk(3)}
     self._lib = _lib
     self.tiles_per_cta = int(tiles_per_cta) if self.depth > 1 else 0
@@ -215,7 +225,7 @@ class Pipeline(object):
 
   def _streams_of(self, k):
     """(analysis, coder, hyper-synthesis, synthesis) streams of batch k."""
-    e = self.streams[k % self.depth]
+    e = self.streams[k % len(self.streams)]
     if not self.stage:
       return e, e, e, e
     g = self.stage
@@ -388,14 +398,14 @@ class Pipeline(object):
       return c, staged, ev
 
     def issue_front(k, checks):
-      slot, st = slots[k % nslots], self.streams[k % self.depth]
+      slot, st = slots[k % nslots], self._streams_of(k)[1]
       deliver(slot, checks)              # the slot's previous batch must be out of its buffers
       slot["front"] = front_work(k, slot, st, checks, self._cap)
       if k == 0:
         self.h2d_bytes += batches_u8[k].numel()
 
     def issue_back(k, checks):
-      slot, st = slots[k % nslots], self.streams[k % self.depth]
+      slot, st = slots[k % nslots], self._streams_of(k)[1]
       c, staged, ev = slot.pop("front")
       wait(ev)                           # the strings and their status are in host memory now
       try:

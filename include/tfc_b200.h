@@ -50,6 +50,9 @@ int64_t tfc_launch_count(void);
  * and keeps the persistent transform kernels off the SMs the coder occupies.
  *   TFC_CFG_SM_BUDGET              SMs (= CTAs) a persistent transform kernel may use; 0 = all
  *   TFC_CFG_CODER_STREAMS_PER_CTA  1..8 coder streams per CTA; 0 = automatic (1 while S <= #SMs)
+ *                                  values of 32..512 additionally pack value / 32 WARPS of the
+ *                                  lane-per-stream kernels (32 streams each) into one CTA; the
+ *                                  warps-per-stream kernels use min(value, 8)
  *   TFC_CFG_TILES_PER_CTA          0 = persistent transform kernels (one CTA per SM walks the
  *                                  tile list); k > 0 = k consecutive tiles per CTA and as many
  *                                  CTAs as that takes, so the hardware scheduler fills whatever

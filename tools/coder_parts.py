@@ -21,6 +21,8 @@ def main():
   ap.add_argument("--lanes", type=int, default=0, help="0 auto, 1 warps per stream, 2 lane per stream")
   ap.add_argument("--smem-kb", type=int, default=0)
   ap.add_argument("--table-kb", type=int, default=0)
+  ap.add_argument("--repeat", type=int, default=1,
+                  help="code the batch's latents this many times over in ONE launch (batch * repeat streams)")
   args = ap.parse_args()
   import compression_b200 as tfc
   from compression_b200.examples import bmshj2018
@@ -28,7 +30,11 @@ def main():
   model = bmshj2018.Bmshj2018Model(192, dev, seed=0)
   x = torch.rand((args.batch, args.height, args.width, 3), device=dev)
   y, z, sigma = model.analyse(x)
-  c = model.compress(x)
+  if args.repeat > 1:
+    y, z, sigma = (t.repeat(args.repeat, 1, 1, 1) for t in (y, z, sigma))
+  string, side_string = model.encode_strings(y, z, sigma)
+  c = bmshj2018.Compressed(string, side_string, tuple(x.shape[1:-1]), tuple(y.shape[1:-1]),
+                           tuple(z.shape[1:-1]))
   tfc.configure(coder_lanes=args.lanes)
   tfc.configure(coder_streams_per_cta=args.pack, coder_smem_kb=args.smem_kb,
                 coder_table_kb=args.table_kb)
