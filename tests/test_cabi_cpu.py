@@ -96,6 +96,26 @@ def test_stdsort_replay_matches_libstdcxx(tmp_path):
   assert "bad=0" in out.stdout
 
 
+def test_tf_op_shell_compiles_and_links(L, tmp_path):
+  """The GPU kernel registrations a maintainer adds to the reference's op library
+  (integration/tf_ops) compile against the stub of the TF op API and
+  every tfc_* call in them resolves against the built library with the header's signatures."""
+  import subprocess
+  so = str(tmp_path / "b200_tf_kernels.so")
+  cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+  subprocess.check_call([
+      "g++", "-std=c++14", "-Wall", "-Werror", "-fPIC", "-shared",
+      "-I", os.path.join(ROOT, "integration", "tf_stub"), "-I", os.path.join(ROOT, "include"),
+      "-I", os.path.join(cuda, "include"),
+      os.path.join(ROOT, "integration", "tf_ops", "b200_range_coding_kernels.cc"),
+      "-o", so, "-Wl,--no-undefined", "-L", os.path.join(ROOT, "compression_b200"),
+      "-ltfc_b200", "-L", os.path.join(cuda, "lib64"), "-lcudart"])
+  src = open(os.path.join(ROOT, "integration", "tf_ops", "b200_range_coding_kernels.cc")).read()
+  for op in ("UnboundedIndexRangeEncode", "UnboundedIndexRangeDecode", "RangeEncode", "RangeDecode",
+             "PmfToQuantizedCdf"):
+    assert 'Name("%s").Device(DEVICE_GPU)' % op in src
+
+
 def test_no_cpu_fallback():
   import torch
   if torch.cuda.is_available():
