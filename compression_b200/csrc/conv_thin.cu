@@ -67,6 +67,7 @@ struct __align__(8) Barriers {
   uint64_t p_full[2], p_empty[2];
   uint64_t d1_full[2], d1_empty[2];
   uint64_t a2_full, d2_full;
+  uint64_t a2_empty, d2c_full[2], d2c_empty[2];   // split-phase GDN epilogue
   uint32_t tmem_base;
   uint32_t pad;
 };
@@ -212,7 +213,30 @@ __device__ __forceinline__ void build_block(const Params& p, const T* img, int n
 }
 
 // MODE 0: bias (+ReLU).  MODE 1: GDN with cout == 32 * NC.
-template <int MODE, int NC, int KH, int KW, int CIN>
+//
+// SPLIT (GDN only): the epilogue's two phases run on DIFFERENT warps and different tiles at the
+// same time.  With all eight epilogue warps walking one tile through
+//   D1 -> x^2 (shared memory) -> [GEMM2 round trip] -> D2 -> y -> store
+// a tile took 4.3 us of which the tensor pipe worked 0.8 and no warp issued during the round
+// trips (ncu: 18 % tensor, 31 % SM busy): this layer has K = 75, so unlike the 192-channel
+// layers there is no long main GEMM to hide the chain behind.  Here warps 2-5 only square
+// (tile i + 1) while warps 6-9 only normalise and store (tile i):
+//   * x is not kept in registers between the phases: phase 2 re-reads D1 from tensor memory,
+//     so D1 stays double buffered (2 x cout columns) and is released by phase 2;
+//   * GEMM2 runs in 64-column chunks through two 64-column D2 buffers (2 x cout + 128 <= 512
+//     columns), each handed over and returned by its own barrier pair;
+//   * the x^2 tile is free again as soon as GEMM2's last chunk has been issued and completed
+//     (tcgen05.commit -> a2_empty), not when the tile's output has left: y goes to global memory
+//     straight from registers (each thread owns one pixel: 64-byte runs per 32 channels).
+// Same arithmetic as the unsplit epilogue (x rounded to bfloat16 before the multiply).
+// MEASURED (profiles/r2i_thin_split_epilogue.txt, 64 x 512 x 768 float32 input): 1.75 ms against
+// 1.62 ms unsplit, results identical.  Without the im2col builders nothing changes (1.74), so they
+// are not the limit; without the stores 1.22 ms.  What the split adds is a second read of D1 from
+// tensor memory (295 KB instead of 196 KB per tile), and tensor-memory reads are what the
+// epilogue of this layer is made of: 196 KB per 128-pixel tile is ~1.5 us at the 64-128 B/clk an
+// SM reads TMEM with, against 0.4 us of tensor-pipe work.  Kept as an experiment (debug bit 32),
+// not the default; the unsplit epilogue reads every accumulator once.
+template <int MODE, int NC, int KH, int KW, int CIN, bool SPLIT>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
                  const __grid_constant__ CUtensorMap map_g,
@@ -252,9 +276,12 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
     mbar_init(&bars->w_full, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&bars->p_full[s], 1); mbar_init(&bars->p_empty[s], kBuilders / 32); }
     if (p.patch) prefetch_tmap(&map_img);
-    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], kEpiThreads); }
-    mbar_init(&bars->a2_full, kEpiThreads);
+    constexpr int kPhaseThreads = SPLIT ? kEpiThreads / 2 : kEpiThreads;
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], kPhaseThreads); }
+    mbar_init(&bars->a2_full, kPhaseThreads);
     mbar_init(&bars->d2_full, 1);
+    mbar_init(&bars->a2_empty, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d2c_full[s], 1); mbar_init(&bars->d2c_empty[s], kPhaseThreads); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(&bars->tmem_base, 512);
@@ -266,6 +293,10 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
   const int tile1 = p.chunk ? min(tile0 + p.chunk, p.num_tiles) : p.num_tiles;
   const int tile_step = p.chunk ? 1 : (int)gridDim.x;
   const uint32_t idesc = make_idesc_bf16(128, p.npad);
+  // tensor-memory columns: D1[acc] at acc * d1_cols; SPLIT: two 64-column D2 chunk buffers behind
+  constexpr uint32_t d1_cols = SPLIT ? NC * 32 : 256;
+  constexpr uint32_t d2c_base = 2 * d1_cols;
+  constexpr int gdn_chunks = NC / 2;            // 64-column chunks of GEMM2's output
 
   auto tile_coords = [&](int tile, int& n, int& i0, int& j0) {
     const int per_img = p.tiles_h * p.tiles_w;
@@ -307,9 +338,30 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
     if (lane == 0) {
       int stage = 0;
       uint32_t ph = 0, it = 0;
+      uint32_t gchunk = 0;
+      const uint32_t idesc64 = make_idesc_bf16(128, 64);
       auto issue_gdn = [&](uint32_t j) {
         mbar_wait(&bars->a2_full, j & 1);
         tc_fence_after();
+        if constexpr (SPLIT) {
+          for (int ch = 0; ch < gdn_chunks; ++ch, ++gchunk) {
+            const uint32_t buf = gchunk & 1;
+            mbar_wait(&bars->d2c_empty[buf], ((gchunk >> 1) & 1) ^ 1);
+            tc_fence_after();
+            const uint32_t d2 = tmem + d2c_base + buf * 64;
+            for (int kc = 0; kc < gdn_kblocks; ++kc) {
+              const uint64_t da = make_desc_sw128(smem_u32(a2 + kc * kABytes));
+              // rows [64 ch, 64 ch + 64) of the K-major gamma block: 8 swizzle atoms of 1 KB
+              const uint64_t db = make_desc_sw128(smem_u32(g_res + kc * b_slot + ch * 8192));
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                umma_bf16(d2, da + (k * 2), db + (k * 2), idesc64, (kc | k) != 0);
+            }
+            umma_commit(&bars->d2c_full[buf]);
+          }
+          umma_commit(&bars->a2_empty);
+          return;
+        }
         const uint32_t d2 = tmem + (j & 1) * 256;
         for (int kc = 0; kc < gdn_kblocks; ++kc) {
           const uint64_t da = make_desc_sw128(smem_u32(a2 + kc * kABytes));
@@ -325,7 +377,7 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
         const int acc = it & 1;
         mbar_wait(&bars->d1_empty[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t d1 = tmem + acc * 256;
+        const uint32_t d1 = tmem + acc * d1_cols;
 #pragma unroll
         for (int kb = 0; kb < KB; ++kb) {
           const int nm = (K - kb * 64 >= 64) ? 4 : (K - kb * 64 + 15) / 16;
@@ -345,6 +397,103 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
         if (GDN && it > 0) issue_gdn(it - 1);
       }
       if (GDN && it > 0) issue_gdn(it - 1);
+    }
+  } else if (SPLIT && warp < 2 + epi::kEpilogueWarps / 2) {
+    // ===== phase 1 (warps 2-5): x = D1 + bias, x^2 -> bf16 K-major SW128 tile =====
+    if constexpr (SPLIT) {
+      const int quad = warp & 3;
+      const int r = quad * 32 + lane;
+      const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+      uint32_t it = 0;
+      for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
+        const int acc = it & 1;
+        const uint32_t dacc = tmem + acc * d1_cols + lane_addr;
+        mbar_wait(&bars->d1_full[acc], (it >> 1) & 1);
+        mbar_wait(&bars->a2_empty, (it & 1) ^ 1);      // GEMM2 of the previous tile has read a2
+        tc_fence_after();
+#pragma unroll
+        for (int cc = 0; cc < NC; ++cc) {
+          uint32_t v[32];
+          tmem_ld_32x32(dacc + cc * 32, v);
+          tmem_ld_wait();
+          uint8_t* row = a2 + (cc >> 1) * kABytes + r * 128;
+          const float4* bs = reinterpret_cast<const float4*>(s_bias + cc * 32);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float4 b0 = bs[2 * q], b1 = bs[2 * q + 1];
+            const float x0 = __uint_as_float(v[8 * q + 0]) + b0.x;
+            const float x1 = __uint_as_float(v[8 * q + 1]) + b0.y;
+            const float x2 = __uint_as_float(v[8 * q + 2]) + b0.z;
+            const float x3 = __uint_as_float(v[8 * q + 3]) + b0.w;
+            const float x4 = __uint_as_float(v[8 * q + 4]) + b1.x;
+            const float x5 = __uint_as_float(v[8 * q + 5]) + b1.y;
+            const float x6 = __uint_as_float(v[8 * q + 6]) + b1.z;
+            const float x7 = __uint_as_float(v[8 * q + 7]) + b1.w;
+            const int physc = ((cc & 1) * 4 + q) ^ (r & 7);
+            *reinterpret_cast<uint4*>(row + physc * 16) =
+                make_uint4(epi::pack_bf16(x0 * x0, x1 * x1), epi::pack_bf16(x2 * x2, x3 * x3),
+                           epi::pack_bf16(x4 * x4, x5 * x5), epi::pack_bf16(x6 * x6, x7 * x7));
+          }
+        }
+        tc_fence_before();
+        fence_proxy_async_smem();
+        mbar_arrive(&bars->a2_full);
+      }
+    }
+  } else if (SPLIT && warp < 2 + epi::kEpilogueWarps) {
+    // ===== phase 2 (warps 6-9): y = bf16(x) * rsqrt(beta + D2), stored from registers =====
+    if constexpr (SPLIT) {
+      const int quad = warp & 3;
+      const int r = quad * 32 + lane;
+      const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+      uint32_t it = 0, gchunk = 0;
+      for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
+        int n, i0, j0;
+        tile_coords(tile, n, i0, j0);
+        const int acc = it & 1;
+        const int li = r / p.tw, lj = r - li * p.tw;
+        const int i2 = i0 + li, j2 = j0 + lj;
+        const bool valid = i2 < p.ho && j2 < p.wo && !(p.debug & 2);
+        const int64_t elem0 = (((int64_t)n * p.ho + i2) * p.wo + j2) * p.cout;
+        const uint32_t dacc = tmem + acc * d1_cols + lane_addr;
+        for (int ch = 0; ch < gdn_chunks; ++ch, ++gchunk) {
+          const uint32_t buf = gchunk & 1;
+          mbar_wait(&bars->d2c_full[buf], (gchunk >> 1) & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int piece = 0; piece < 2; ++piece) {
+            const int cc = ch * 2 + piece;
+            uint32_t g[32], xv[32];
+            tmem_ld_32x32(tmem + d2c_base + buf * 64 + piece * 32 + lane_addr, g);
+            tmem_ld_32x32(dacc + cc * 32, xv);
+            tmem_ld_wait();
+            const float4* be = reinterpret_cast<const float4*>(s_beta + cc * 32);
+            const float4* bs = reinterpret_cast<const float4*>(s_bias + cc * 32);
+            float y[32];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              const float4 b4 = be[q], s4 = bs[q];
+              const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
+              const float sb[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+              for (int e = 0; e < 4; e += 2) {
+                const uint32_t pr = epi::pack_bf16(__uint_as_float(xv[4 * q + e]) + sb[e],
+                                                   __uint_as_float(xv[4 * q + e + 1]) + sb[e + 1]);
+                const float xa = __uint_as_float(pr << 16);
+                const float xb = __uint_as_float(pr & 0xFFFF0000u);
+                const float na = __uint_as_float(g[4 * q + e]) + bb[e];
+                const float nb = __uint_as_float(g[4 * q + e + 1]) + bb[e + 1];
+                y[4 * q + e] = xa * epi::rsqrt_approx(na);
+                y[4 * q + e + 1] = xb * epi::rsqrt_approx(nb);
+              }
+            }
+            if (valid) epi::store_chunk(p.out, p.out_f32 != 0, p.out_wide != 0, elem0 + cc * 32, y);
+          }
+          tc_fence_before();
+          mbar_arrive(&bars->d2c_empty[buf]);
+        }
+        mbar_arrive(&bars->d1_empty[acc]);
+      }
     }
   } else if (warp < 2 + epi::kEpilogueWarps) {
     // ===== epilogue: 8 warps, thread <-> TMEM lane <-> tile pixel, two column halves =====
@@ -461,6 +610,7 @@ struct Plan {
   int patch_rows, patch_pitch, patch_slot, vec;
   size_t smem;
   bool gdn;
+  bool split;               // split-phase GDN epilogue (experiment: debug bit 32 turns it on)
 };
 
 bool shape_ok(const tfc_conv_desc& d) {
@@ -469,6 +619,7 @@ bool shape_ok(const tfc_conv_desc& d) {
 
 bool make_plan(const tfc_conv_desc& d, const void* in, Plan* pl) {
   pl->gdn = d.act == TFC_ACT_GDN;
+  pl->split = pl->gdn && (tfc::debug_bits() & 32) != 0;   // measured slower: see the kernel comment
   const int K = d.kh * d.kw * d.cin;
   pl->kblocks = (K + 63) / 64;
   pl->npad = (d.cout + 15) / 16 * 16;
@@ -513,11 +664,17 @@ int launch(const tfc_conv_desc& d, const Plan& pl, const CUtensorMap& map_w,
   void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap,
                const Params) = nullptr;
   if (!pl.gdn) {
-    kern = conv_thin_kernel<0, 0, KH, KW, 3>;
+    kern = conv_thin_kernel<0, 0, KH, KW, 3, false>;
+  } else if (pl.split) {
+    switch (d.cout / 32) {
+      case 4: kern = conv_thin_kernel<1, 4, KH, KW, 3, true>; break;
+      case 6: kern = conv_thin_kernel<1, 6, KH, KW, 3, true>; break;
+      default: return tfc::fail(TFC_ERR_UNIMPLEMENTED, "thin-input GDN needs 128 or 192 filters");
+    }
   } else {
     switch (d.cout / 32) {
-      case 4: kern = conv_thin_kernel<1, 4, KH, KW, 3>; break;
-      case 6: kern = conv_thin_kernel<1, 6, KH, KW, 3>; break;
+      case 4: kern = conv_thin_kernel<1, 4, KH, KW, 3, false>; break;
+      case 6: kern = conv_thin_kernel<1, 6, KH, KW, 3, false>; break;
       default: return tfc::fail(TFC_ERR_UNIMPLEMENTED, "thin-input GDN needs 128 or 192 filters");
     }
   }
@@ -622,7 +779,7 @@ int conv_thin(const tfc_conv_desc& d, const void* in, const float* w, const floa
   } else {
     map_img = map_w;
   }
-  p.out_tma = pl.gdn && !p.out_f32 && d.cout % 64 == 0 && !(debug_bits() & 16);
+  p.out_tma = pl.gdn && !pl.split && !p.out_f32 && d.cout % 64 == 0 && !(debug_bits() & 16);
   if (p.out_tma) {
     cuuint64_t dims[4] = {(cuuint64_t)d.cout, (cuuint64_t)d.wo, (cuuint64_t)d.ho, (cuuint64_t)d.n};
     cuuint64_t str[3] = {(cuuint64_t)d.cout * 2, (cuuint64_t)d.wo * d.cout * 2,

@@ -1,9 +1,8 @@
 mkdir -p gpurun_out
-L=gpurun_out/r2t_lanes_packed.log
+L=gpurun_out/r2i_thin_split2.log
 : > $L
-for cfg in "1 0" "2 64" "4 128" "8 256" "8 512" "16 512"; do
-  set -- $cfg
-  echo "== coder_parts --lanes 2 --repeat $1 --pack $2   (streams = 64 x $1)" >> $L
-  timeout 300 python tools/coder_parts.py --lanes 2 --repeat $1 --pack $2 --reps 2 2>&1 | tail -4 >> $L
+for dbg in 0 1 2 3 32 33 34 35; do
+  echo "== A0 debug $dbg (1: no im2col build, 2: no stores, 32: unsplit epilogue)" >> $L
+  timeout 120 python tools/conv_bench.py --layers A0 --debug $dbg 2>&1 | tail -1 >> $L
 done
 cat $L
