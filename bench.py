@@ -95,6 +95,8 @@ def parse_args():
                   help="shared memory per coder CTA in the pipeline (0: 226 KB)")
   ap.add_argument("--coder-table-kb", type=int, default=0,
                   help="shared memory for the coder's staged tables in the pipeline (0: 72 KB)")
+  ap.add_argument("--stage-priority", type=int, default=1,
+                  help="transform stage streams from the high-priority pool (1) or the default one (0)")
   ap.add_argument("--coder-pack", type=int, default=0,
                   help="coder streams per CTA when depth > 1 (0: by the number of streams in "
                        "flight: 4 at batch 64 x 12, 2 at batch 32 x 8)")
@@ -199,7 +201,11 @@ class ConvTimer(object):
 
 # ---- clocks -------------------------------------------------------------------------------------
 class ClockSampler(object):
-  QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+  """`nvidia-smi -lms 100` in the background.  The process is started BEFORE the warm-up (its
+  NVML start-up takes a few hundred ms on a fresh box and holds driver locks that can stall
+  kernel launches: inside a 0.27 s timed window that is the whole measurement) and only the
+  samples stamped inside [mark(), stop()] are used."""
+  QUERY = ("timestamp,index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
            "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -207,6 +213,7 @@ class ClockSampler(object):
     self.index = index
     self.proc = None
     self.path = None
+    self.t0 = None
 
   def start(self):
     try:
@@ -219,28 +226,42 @@ class ClockSampler(object):
     except OSError:
       self.proc = None
 
+  def mark(self):
+    import datetime
+    self.t0 = datetime.datetime.now()
+
   def stop(self):
+    import datetime
     if self.proc is None:
       return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+    t1 = datetime.datetime.now()
     self.proc.terminate()
     try:
       self.proc.wait(timeout=5)
     except subprocess.TimeoutExpired:
       self.proc.kill()
-    sm, mx, reasons = [], [], set()
     names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    rows = []
     for line in open(self.path):
       f = [t.strip() for t in line.split(",")]
-      if len(f) < 9:
+      if len(f) < 10:
         continue
       try:
-        sm.append(float(f[1])); mx.append(float(f[2]))
+        ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f")
+        rows.append((ts, float(f[2]), float(f[3]), f[6:10]))
       except ValueError:
         continue
-      for n, v in zip(names, f[5:9]):
+    os.unlink(self.path)
+    if self.t0 is not None:
+      inside = [r for r in rows if self.t0 <= r[0] <= t1]
+      if not inside and rows:            # a window shorter than the sampling period
+        inside = [min(rows, key=lambda r: abs((r[0] - self.t0).total_seconds()))]
+      rows = inside
+    sm, mx, reasons = [r[1] for r in rows], [r[2] for r in rows], set()
+    for r in rows:
+      for n, v in zip(names, r[3]):
         if v.lower().startswith("active"):
           reasons.add(n)
-    os.unlink(self.path)
     return {"sm_mhz": float(np.median(sm)) if sm else None,
             "sm_max_mhz": float(max(mx)) if mx else None, "reasons": sorted(reasons),
             "samples": len(sm)}
@@ -380,7 +401,8 @@ def c3_block(args, model, world, rank, dev, barrier, allmax):
   # every batch in flight keeps its own activation pool (0.46 GB per image), which is what stops
   # at 18 micro-batches of 16 (134 GB reserved).  Measured (profiles/r2d_c3_sweep.txt): micro 16,
   # 14 in flight, 8 streams per coder CTA 1008 MPix/s; 18 in flight 1315; 4 per CTA 1539.
-  micro, depth, pack = min(16, share), 18, 4
+  # after the stream-aliasing fix (profiles/r2l_c3_sweep.txt): 24 in flight 1464 / 1461 e2e
+  micro, depth, pack = min(16, share), 24, 4
   if args.c3:
     micro, depth, pack = [int(v) for v in args.c3.split(",")]
     micro = min(micro, share)
@@ -737,18 +759,20 @@ def run_b200(args):
     args.back_lag = max(1, min(args.depth, 12, args.host_slots // 2))
   pipe = model.pipeline(args.depth, args.tiles_per_cta, args.coder_pack, args.back_lag,
                         args.host_slots, conv_stages=args.conv_stages,
-                        coder_smem_kb=args.coder_smem_kb, coder_table_kb=args.coder_table_kb)
+                        coder_smem_kb=args.coder_smem_kb, coder_table_kb=args.coder_table_kb,
+                        stage_priority=bool(args.stage_priority))
 
   with pipe:
     # every stream of the pipeline must have run once before the timed region: a stream's first
     # batch allocates its activation pool (cudaMalloc synchronises the device) and stages its
     # weight copies
     n_warm = max(args.warmup, 3, args.depth + 1)
-    pipe.roundtrip_device([x_dev] * n_warm)
-    barrier()
     clocks = ClockSampler(local)
     if rank == 0:
       clocks.start()
+    pipe.roundtrip_device([x_dev] * n_warm)
+    barrier()
+    clocks.mark()
     launches0 = tfc.launch_count()
     timer.on = True
     start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -94,10 +94,10 @@ __global__ void pmf_to_cdf_kernel(const float* __restrict__ pmf, int64_t rows, i
 // One thread per row leaves the GPU empty when there are few long rows (a Gaussian scale table
 // is 64 rows of up to 1481 entries) and walks its row through global memory one dependent load
 // at a time.  Here the row's items {key, index, count} live in shared memory; the keys are
-// computed and the result is scanned by the whole warp; lane 0 replays std::sort (its decision
-// sequence is what fixes the order of equal keys and cannot be reordered); the re-insertion of
-// the adjusted head — `find_if` + `rotate` in the reference (:165-181, :182-199) — is a ballot
-// over 32 candidates at a time and a cooperative shift.
+// computed and the result is scanned by the whole warp; std::sort is replayed by the warp
+// together (warp_sort below: same permutation as libstdc++'s, ties included); the re-insertion
+// of the adjusted head — `find_if` + `rotate` in the reference (:165-181, :182-199) — is a
+// 32-way search and a cooperative shift of the shorter side of a ring.
 struct SmemAcc {
   tfc::SortItem* base;
   __device__ __forceinline__ tfc::SortItem get(int i) const { return base[i]; }
@@ -105,10 +105,118 @@ struct SmemAcc {
 };
 
 constexpr int kWarpRowBytesPerEntry = (int)sizeof(tfc::SortItem) + 8;   // item + pmf + count
+// (the two uint16 position lists of the sort live in the count array: the counts are in the items
+// from the moment the keys are built until they are written back)
+constexpr int kCoopMin = 64;    // ranges above this many items are partitioned by the whole warp
 
+// The unguarded Hoare partition of std::sort on [first + 1, last) around the pivot at `first`,
+// by the whole warp: StdSortReplay::partition_ranked (stdsort_replay.cuh; checked against the
+// real std::sort on the host) with its candidate lists built by ballots.  Returns the cut.
+template <bool DESC>
+__device__ int partition_warp(tfc::SortItem* it, uint16_t* lpos, uint16_t* rasc, int first,
+                              int last, int lane) {
+  const double pk = it[first].key;
+  const unsigned below = (1u << lane) - 1u;
+  int nl = 0, nr = 0;
+  for (int base = first; base < last; base += 32) {
+    const int i = base + lane;
+    bool fl = false, fr = false;
+    if (i < last) {
+      const double k = it[i].key;
+      fl = i > first && !(DESC ? k > pk : k < pk);
+      fr = !(DESC ? pk > k : pk < k);
+    }
+    const unsigned ml = __ballot_sync(0xFFFFFFFFu, fl), mr = __ballot_sync(0xFFFFFFFFu, fr);
+    if (fl) lpos[nl + __popc(ml & below)] = (uint16_t)i;
+    if (fr) rasc[nr + __popc(mr & below)] = (uint16_t)i;
+    nl += __popc(ml);
+    nr += __popc(mr);
+  }
+  __syncwarp();
+  // K = number of leading pairs with L[k] < R[k] (monotone in k)
+  const int pairs = min(nl, nr);
+  int K = 0;
+  for (int base = 0; base < pairs; base += 32) {
+    const int k = base + lane;
+    const bool ok = k < pairs && (int)lpos[k] < (int)rasc[nr - 1 - k];
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, ok);
+    K += __popc(m);
+    if (m != 0xFFFFFFFFu) break;
+  }
+  for (int k = lane; k < K; k += 32) {
+    const int i = lpos[k], j = rasc[nr - 1 - k];
+    const tfc::SortItem t = it[i];
+    it[i] = it[j];
+    it[j] = t;
+  }
+  int cut = 0x7FFFFFFF;
+  if (K < nl) cut = lpos[K];
+  if (K > 0) cut = min(cut, (int)rasc[nr - K]);
+  __syncwarp();
+  return cut;
+}
+
+// std::sort of it[0, n) with the tie order of libstdc++ (StdSortReplay), by one warp: the big
+// partitions are done by all lanes together, ranges of at most kCoopMin items are handed out one
+// per lane and finished serially (introsort loop + leaf insertion sorts) 32 at a time.  The
+// decomposition is StdSortReplay::sort_decomposed, which tests/cpp/stdsort_check.cc compares with
+// the real std::sort (ties, adversarial inputs that hit the heap-sort fallback).
+template <bool DESC>
+__device__ void warp_sort(tfc::SortItem* it, uint16_t* lpos, uint16_t* rasc, int n, int lane) {
+  tfc::StdSortReplay<SmemAcc, DESC> ser(SmemAcc{it});
+  if (n <= kCoopMin) {
+    if (lane == 0) ser.sort(n);
+    __syncwarp();
+    return;
+  }
+  int lg = 0;
+  for (int m = n; m > 1; m >>= 1) ++lg;
+  int sf[48], sl[48], sd[48];
+  int sp = 1;
+  sf[0] = 0; sl[0] = n; sd[0] = 2 * lg;
+  int myf = 0, myl = 0, myd = 0, pending = 0;   // this lane's small range; ranges handed out
+  auto flush = [&]() {
+    __syncwarp();
+    if (lane < pending) ser.sort_range(myf, myl, myd);
+    __syncwarp();
+    pending = 0;
+  };
+  while (sp > 0) {
+    --sp;
+    const int first = sf[sp], last = sl[sp];
+    int depth = sd[sp];
+    if (last - first <= kCoopMin) {
+      if (last - first >= 2) {
+        if (lane == pending) { myf = first; myl = last; myd = depth; }
+        if (++pending == 32) flush();
+      }
+      continue;
+    }
+    if (depth == 0) {
+      __syncwarp();
+      if (lane == 0) ser.heap_sort(first, last);
+      __syncwarp();
+      continue;
+    }
+    --depth;
+    if (lane == 0) ser.median_to_first(first, first + 1, first + (last - first) / 2, last - 1);
+    __syncwarp();
+    const int cut = partition_warp<DESC>(it, lpos, rasc, first, last, lane);
+    sf[sp] = cut; sl[sp] = last; sd[sp] = depth; ++sp;
+    sf[sp] = first; sl[sp] = cut; sd[sp] = depth; ++sp;
+  }
+  flush();
+}
+
+// The queue of the reference (`std::sort`, then per adjustment `find_if` + `rotate`,
+// range_coding_helper_kernels.cc:165-199) as a RING over the sorted items: logical position j is
+// physical (start + j) mod n.  The adjusted head is re-inserted before the first item it
+// compares less than; the items are sorted, so that position comes from a 32-way search instead
+// of a walk, and the rotate moves whichever side of the ring is shorter — an item whose count
+// drops to 1 gets an infinite key and goes to the back, which in the ring is its own slot.
 template <bool OVER>
-__device__ void rebalance_warp(tfc::SortItem* it, const float* sp, int32_t* cnt, int n, int todo,
-                               int lane) {
+__device__ void rebalance_warp(tfc::SortItem* it, uint16_t* lpos, uint16_t* rasc, const float* sp,
+                               int32_t* cnt, int n, int todo, int lane) {
   for (int i = lane; i < n; i += 32) {
     tfc::SortItem v;
     v.idx = i; v.pad = cnt[i];
@@ -116,33 +224,62 @@ __device__ void rebalance_warp(tfc::SortItem* it, const float* sp, int32_t* cnt,
     it[i] = v;
   }
   __syncwarp();
-  if (lane == 0) {
-    tfc::StdSortReplay<SmemAcc, !OVER> sorter(SmemAcc{it});
-    sorter.sort(n);
-  }
-  __syncwarp();
+  warp_sort<!OVER>(it, lpos, rasc, n, lane);
+  int start = 0;
+  auto phys = [&](int j) { const int q = start + j; return q >= n ? q - n : q; };
   for (; todo > 0; --todo) {
-    tfc::SortItem head = it[0];
+    tfc::SortItem head = it[start];
     head.pad += OVER ? -1 : 1;
     head.key = OVER ? steal_cost((double)sp[head.idx], head.pad)
                     : give_gain((double)sp[head.idx], head.pad);
-    int pos = n;
-    for (int base = 1; base < n; base += 32) {
-      const int j = base + lane;
-      tfc::SortItem o;
-      bool stop = false;
-      if (j < n) {
-        o = it[j];
-        stop = OVER ? head.key < o.key : head.key > o.key;
+    // pos = first logical j in [1, n) whose item stops the head, n if none
+    // (the first round looks at the next 32 items one by one: an adjusted head usually moves a
+    // few places; only then does the search widen to 32 evenly spaced probes)
+    int lo = 1, hi = n;
+    bool near = true;
+    while (lo < hi) {
+      const int step = near ? 1 : (hi - lo + 31) / 32;
+      near = false;
+      const int j = lo + lane * step;
+      bool stop = true;
+      if (j < hi) {
+        const double k = it[phys(j)].key;
+        stop = OVER ? head.key < k : head.key > k;
       }
       const unsigned m = __ballot_sync(0xFFFFFFFFu, stop);
-      const int lim = m ? base + __ffs(m) - 1 : min(base + 32, n);
-      __syncwarp();
-      if (j < lim) it[j - 1] = o;
-      __syncwarp();
-      if (m) { pos = lim; break; }
+      const int f = m ? __ffs(m) - 1 : 32;
+      if (f == 0) { hi = lo; break; }
+      const int nlo = lo + (f - 1) * step + 1;
+      if (f < 32) hi = min(hi, lo + f * step);     // f == 32: every probe was before the stop
+      lo = nlo;
     }
-    if (lane == 0) it[pos - 1] = head;
+    const int pos = lo;
+    __syncwarp();
+    if (pos - 1 <= n - pos) {
+      // logical [1, pos) one place towards the front, the head lands at pos - 1
+      for (int base = 1; base < pos; base += 32) {
+        const int j = base + lane;
+        tfc::SortItem o;
+        if (j < pos) o = it[phys(j)];
+        __syncwarp();
+        if (j < pos) it[phys(j - 1)] = o;
+        __syncwarp();
+      }
+      if (lane == 0) it[phys(pos - 1)] = head;
+    } else {
+      // drop the head's slot from the front (start + 1: every logical index goes down by one)
+      // and move the new logical [pos - 1, n - 1) one place towards the back, into that slot
+      start = start + 1 == n ? 0 : start + 1;
+      for (int top = n - 1; top > pos - 1; top -= 32) {
+        const int j = top - 1 - lane;                // source, going down from n - 2
+        tfc::SortItem o;
+        if (j >= pos - 1) o = it[phys(j)];
+        __syncwarp();
+        if (j >= pos - 1) it[phys(j + 1)] = o;
+        __syncwarp();
+      }
+      if (lane == 0) it[phys(pos - 1)] = head;
+    }
     __syncwarp();
   }
   for (int i = lane; i < n; i += 32) cnt[it[i].idx] = it[i].pad;
@@ -160,6 +297,8 @@ __global__ void pmf_to_cdf_warp_kernel(const float* __restrict__ pmf, int64_t ro
   tfc::SortItem* it = reinterpret_cast<tfc::SortItem*>(mine);
   float* sp = reinterpret_cast<float*>(it + npad);
   int32_t* cnt = reinterpret_cast<int32_t*>(sp + npad);
+  uint16_t* lpos = reinterpret_cast<uint16_t*>(cnt);
+  uint16_t* rasc = lpos + npad;
   const float* p = pmf + r * n;
   int32_t* c = cdf + r * (int64_t)(n + 1);
   const int32_t total = 1 << precision;
@@ -173,8 +312,8 @@ __global__ void pmf_to_cdf_warp_kernel(const float* __restrict__ pmf, int64_t ro
   }
   sum = __reduce_add_sync(0xFFFFFFFFu, sum);
   __syncwarp();
-  if (sum > total) rebalance_warp<true>(it, sp, cnt, n, sum - total, lane);
-  else if (sum < total) rebalance_warp<false>(it, sp, cnt, n, total - sum, lane);
+  if (sum > total) rebalance_warp<true>(it, lpos, rasc, sp, cnt, n, sum - total, lane);
+  else if (sum < total) rebalance_warp<false>(it, lpos, rasc, sp, cnt, n, total - sum, lane);
   // cdf = [0, cumsum(count)]
   int32_t run = 0;
   if (lane == 0) c[0] = 0;
@@ -236,7 +375,16 @@ extern "C" int tfc_pmf_to_quantized_cdf(const float* d_pmf, int64_t rows, int32_
   // and walk its row through global memory — the EntropyBottleneck table of a training step is
   // 128 rows of 22 entries)
   if ((n >= 64 || rows <= 2048) && row_bytes <= 200 * 1024) {
-    const int wpc = (int)std::max<size_t>(1, std::min<size_t>(4, (200 * 1024) / row_bytes));
+    // warps per CTA: the re-insertion loop is one dependent chain per row, so what matters is
+    // how many rows an SM holds at once: the CTA size (1, 2 or 4 rows) that packs most rows
+    // into the SM's 227 KB (1 KB reserved per CTA)
+    int wpc = 1;
+    size_t best = 0;
+    for (int w : {4, 2, 1}) {
+      if (w * row_bytes > 200 * 1024) continue;
+      const size_t per_sm = std::min<size_t>(32 / w, (227 * 1024) / (w * row_bytes + 1024)) * w;
+      if (per_sm > best) { best = per_sm; wpc = w; }
+    }
     const size_t smem = wpc * row_bytes;
     static tfc::PerDeviceOnce attr;
     if (attr.first()) {

@@ -128,6 +128,89 @@ struct StdSortReplay {
     }
   }
 
+  // ---- decomposition used by the warp-cooperative sort (pmf_to_cdf.cu) ----------------------
+  // std::sort's result is fixed by (a) the sequence of partitions, each of which only touches its
+  // own range, and (b) the final insertion sort, which never moves an item across a partition
+  // boundary (left <= pivot <= right and the insertion compares strictly), i.e. it is a stable
+  // insertion sort of every leaf range (<= 16 items) on its own.  So disjoint ranges can be
+  // finished independently and in any order: `sort_range` is the serial introsort loop on one
+  // range with the leaves insertion-sorted on the spot, and `partition_ranked` is the same
+  // unguarded Hoare partition computed from candidate lists instead of two walking pointers.
+
+  // [first, last) with `depth` levels left before the heap-sort fallback
+  TFC_HD void sort_range(int first0, int last0, int depth0) {
+    int sf[48], sl[48], sd[48];
+    int sp = 0;
+    sf[0] = first0; sl[0] = last0; sd[0] = depth0; sp = 1;
+    while (sp > 0) {
+      --sp;
+      int first = sf[sp], last = sl[sp], depth = sd[sp];
+      bool heap = false;
+      while (last - first > 16) {
+        if (depth == 0) { heap_sort(first, last); heap = true; break; }
+        --depth;
+        const int mid = first + (last - first) / 2;
+        median_to_first(first, first + 1, mid, last - 1);
+        const int cut = partition(first + 1, last, first);
+        sf[sp] = cut; sl[sp] = last; sd[sp] = depth; ++sp;
+        last = cut;
+      }
+      if (!heap) insertion_sort(first, last);
+    }
+  }
+
+  // The partition of `partition(first + 1, last, first)` without walking: in the ORIGINAL range
+  // let L[0] < L[1] < ... be the positions in [first + 1, last) whose item is not less than the
+  // pivot and R[0] > R[1] > ... the positions in [first, last) whose item the pivot is not less
+  // than (position `first`, the pivot itself, is the right scan's sentinel).  The two pointers of
+  // the serial loop only ever read untouched positions, so its k-th swap is (L[k], R[k]) for as
+  // long as L[k] < R[k] (K swaps; the predicate is monotone in k), and it returns the next left
+  // stop: L[K] unless the swapped-in item at R[K-1] comes first.  `lpos` / `rasc` are scratch for
+  // the candidate positions (rasc ascending: R[k] = rasc[nr - 1 - k]).
+  template <typename Idx>
+  TFC_HD int partition_ranked(int first, int last, Idx* lpos, Idx* rasc) {
+    const double pk = a.get(first).key;
+    int nl = 0, nr = 0;
+    for (int i = first; i < last; ++i) {
+      const double k = a.get(i).key;
+      if (i > first && !lt(k, pk)) lpos[nl++] = (Idx)i;
+      if (!lt(pk, k)) rasc[nr++] = (Idx)i;
+    }
+    int K = 0;
+    while (K < nl && K < nr && (int)lpos[K] < (int)rasc[nr - 1 - K]) ++K;
+    for (int k = 0; k < K; ++k) swap((int)lpos[k], (int)rasc[nr - 1 - k]);
+    int cut = 0x7FFFFFFF;
+    if (K < nl) cut = (int)lpos[K];
+    if (K > 0 && (int)rasc[nr - K] < cut) cut = (int)rasc[nr - K];
+    return cut;
+  }
+
+  // serial model of the warp algorithm: ranges above `coop` items are split with
+  // partition_ranked (the warp does that step together), smaller ones go to sort_range (one
+  // lane each).  Host tests compare it with the real std::sort.
+  template <typename Idx>
+  TFC_HD void sort_decomposed(int n, int coop, Idx* lpos, Idx* rasc) {
+    if (n <= 0) return;
+    int lg = 0;
+    for (int m = n; m > 1; m >>= 1) ++lg;
+    int sf[64], sl[64], sd[64];
+    int sp = 0;
+    sf[0] = 0; sl[0] = n; sd[0] = 2 * lg; sp = 1;
+    while (sp > 0) {
+      --sp;
+      const int first = sf[sp], last = sl[sp];
+      int depth = sd[sp];
+      if (last - first <= coop || last - first <= 16) { sort_range(first, last, depth); continue; }
+      if (depth == 0) { heap_sort(first, last); continue; }
+      --depth;
+      const int mid = first + (last - first) / 2;
+      median_to_first(first, first + 1, mid, last - 1);
+      const int cut = partition_ranked(first, last, lpos, rasc);
+      sf[sp] = cut; sl[sp] = last; sd[sp] = depth; ++sp;
+      sf[sp] = first; sl[sp] = cut; sd[sp] = depth; ++sp;
+    }
+  }
+
   TFC_HD void sort(int n) {
     if (n <= 0) return;
     int lg = 0;

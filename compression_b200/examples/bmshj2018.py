@@ -149,7 +149,7 @@ class Pipeline(object):
 
   def __init__(self, model, depth=3, tiles_per_cta=8, coder_streams_per_cta=4, back_lag=None,
                host_slots=None, conv_stages=0, coder_smem_kb=0, coder_table_kb=0,
-               stage_streams=True, coder_stream_cap=22):
+               stage_streams=True, coder_stream_cap=22, stage_priority=True):
     """`stage_streams` (default): the TRANSFORM phases of all batches share a few "stage" streams
     (3 for analysis, 2 for the decoder's hyper-synthesis, 3 for synthesis) and only the CODER
     phases get one stream per batch in flight.  torch's caching allocator keeps one pool per
@@ -186,7 +186,8 @@ class Pipeline(object):
     self.streams = [torch.cuda.Stream(device=model.device) for _ in range(n_coder)]
     self.stage = None
     if stage_streams and self.depth > 1:
-      mk = lambda n: [torch.cuda.Stream(device=model.device, priority=-1) for _ in range(n)]
+      prio = -1 if stage_priority else 0
+      mk = lambda n: [torch.cuda.Stream(device=model.device, priority=prio) for _ in range(n)]
       self.stage = {"analysis": mk(3), "hyper": mk(2), "synthesis": mk(3)}
     self._lib = _lib
     self.tiles_per_cta = int(tiles_per_cta) if self.depth > 1 else 0

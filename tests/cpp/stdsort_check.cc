@@ -33,10 +33,21 @@ static bool run_case(const std::vector<double>& keys) {
   }
   if (DESC) std::sort(ref.begin(), ref.end(), [](const Item& a, const Item& b) { return a.key > b.key; });
   else std::sort(ref.begin(), ref.end(), [](const Item& a, const Item& b) { return a.key < b.key; });
+  const std::vector<tfc::SortItem> unsorted = mine;
   tfc::StdSortReplay<VecAcc, DESC> s(VecAcc{mine.data()});
   s.sort(n);
   for (int i = 0; i < n; ++i)
     if ((int)(ref[i].ptr - dummy.data()) != mine[i].idx) return false;
+  // the decomposition the warp-cooperative device sort uses (candidate-list partitions above
+  // `coop` items, independent serial ranges below) must give the same permutation
+  std::vector<uint16_t> lpos(n + 1), rasc(n + 1);
+  for (int coop : {16, 24, 64, 200}) {
+    std::vector<tfc::SortItem> again = unsorted;
+    tfc::StdSortReplay<VecAcc, DESC> d(VecAcc{again.data()});
+    d.sort_decomposed(n, coop, lpos.data(), rasc.data());
+    for (int i = 0; i < n; ++i)
+      if (again[i].idx != mine[i].idx) return false;
+  }
   return true;
 }
 

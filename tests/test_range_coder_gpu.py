@@ -298,6 +298,33 @@ def test_pmf_to_quantized_cdf_matches_checker(tfc, oracle):
       assert (np.diff(got, axis=-1) > 0).all()
 
 
+def test_pmf_long_rows_warp_sort(tfc, oracle):
+  """Rows long enough for the warp-cooperative replay of std::sort (ranges above 64 items are
+  partitioned by the whole warp, csrc/pmf_to_cdf.cu warp_sort) and for the ring re-insertion:
+  few distinct masses (almost every comparison is a tie), uniform rows, sorted and reversed
+  masses, and totals far above / below 2^precision so that hundreds of adjustments are replayed."""
+  rng = np.random.default_rng(61)
+  for n in (65, 129, 700, 1480, 3000):
+    rows = [np.full(n, 1.0 / n)]
+    for distinct in (2, 5, 40):
+      r = rng.integers(1, distinct + 1, n).astype(np.float64)
+      rows.append(r / r.sum())
+    r = np.sort(rng.random(n) + 1e-3)
+    rows.append(r / r.sum())
+    rows.append(r[::-1] / r.sum())
+    k = np.arange(n, dtype=np.float64) - (n - 1) / 2
+    for sigma in (1.5, n / 10.0):
+      p = np.exp(-0.5 * (k / sigma) ** 2) + 1e-9
+      rows.append(p / p.sum())
+    pmf = np.array(rows, np.float32)
+    for precision, scale in ((16, 1.0), (16, 1.02), (16, 0.97), (13, 1.0)):
+      if 2 * n > (1 << precision):
+        continue
+      got = tfc.pmf_to_quantized_cdf(pmf * scale, precision).cpu().numpy()
+      want = oracle.pmf_to_cdf(pmf * np.float32(scale), precision)
+      np.testing.assert_array_equal(got, want)
+
+
 def test_pmf_gaussian_model_table(tfc, oracle):
   """The 64-level bmshj2018 scale table (bmshj2018.py:46-48, entropy_models.py:827-858): the
   rows on which a stable sort is known to differ from std::sort (SURVEY probe 4)."""
