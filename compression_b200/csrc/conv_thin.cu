@@ -13,7 +13,8 @@
 //     128-byte-swizzled K-major layout tcgen05.mma expects (row = pixel, 16-byte chunk c of
 //     row r stored at chunk c ^ (r & 7)), through a ring of 16 KB stages.  The k -> (a, b, c)
 //     decomposition is resolved at compile time (kernel templated on kh, kw, cin).
-//   * warp 0: one-time TMA; warp 1: MMA issuer; warps 2-9: epilogue; warps 10-11: builders.
+//   * warp 0: one-time TMA; warp 1: MMA issuer; warps 2-3: builders; warps 4-11: epilogue (two
+//     whole warpgroups, so that setmaxnreg can move registers to them).
 // Compared with the space-to-depth formulation (conv_s2d.cu, 9 k-blocks of 64 mostly-zero
 // channels per tile, weights streamed per tile) this issues 5 instead of 36 MMAs per tile and
 // takes the shared-memory fill traffic per tile from 360 KB to the 8 KB image patch.
@@ -38,6 +39,9 @@ constexpr int kThreads = 64 + kEpiThreads + 64;
 constexpr int kBuilders = 64;         // two warps, two tile rows per thread
 constexpr int kABytes = epi::kABytes;
 constexpr int kMaxStages = 4;
+// PIPE: registers per thread of the epilogue warpgroups / of the TMA + MMA + builder warpgroup
+// (256 x 200 + 128 x 96 = 63 488 of the SM's 65 536)
+constexpr int kEpiRegs = 200, kOtherRegs = 96;
 
 struct Params {
   int32_t n, h, w;                  // input [n, h, w, CIN]
@@ -67,7 +71,6 @@ struct __align__(8) Barriers {
   uint64_t p_full[2], p_empty[2];
   uint64_t d1_full[2], d1_empty[2];
   uint64_t a2_full, d2_full;
-  uint64_t a2_empty, d2c_full[2], d2c_empty[2];   // split-phase GDN epilogue
   uint32_t tmem_base;
   uint32_t pad;
 };
@@ -214,29 +217,27 @@ __device__ __forceinline__ void build_block(const Params& p, const T* img, int n
 
 // MODE 0: bias (+ReLU).  MODE 1: GDN with cout == 32 * NC.
 //
-// SPLIT (GDN only): the epilogue's two phases run on DIFFERENT warps and different tiles at the
-// same time.  With all eight epilogue warps walking one tile through
+// PIPE (GDN only; an experiment kept behind debug bit 32): the GDN epilogue software-pipelined
+// over two tiles.  This layer has K = 75: there is no long main GEMM to hide the epilogue's chain
 //   D1 -> x^2 (shared memory) -> [GEMM2 round trip] -> D2 -> y -> store
-// a tile took 4.3 us of which the tensor pipe worked 0.8 and no warp issued during the round
-// trips (ncu: 18 % tensor, 31 % SM busy): this layer has K = 75, so unlike the 192-channel
-// layers there is no long main GEMM to hide the chain behind.  Here warps 2-5 only square
-// (tile i + 1) while warps 6-9 only normalise and store (tile i):
-//   * x is not kept in registers between the phases: phase 2 re-reads D1 from tensor memory,
-//     so D1 stays double buffered (2 x cout columns) and is released by phase 2;
-//   * GEMM2 runs in 64-column chunks through two 64-column D2 buffers (2 x cout + 128 <= 512
-//     columns), each handed over and returned by its own barrier pair;
-//   * the x^2 tile is free again as soon as GEMM2's last chunk has been issued and completed
-//     (tcgen05.commit -> a2_empty), not when the tile's output has left: y goes to global memory
-//     straight from registers (each thread owns one pixel: 64-byte runs per 32 channels).
-// Same arithmetic as the unsplit epilogue (x rounded to bfloat16 before the multiply).
-// MEASURED (profiles/r2i_thin_split_epilogue.txt, 64 x 512 x 768 float32 input): 1.75 ms against
-// 1.62 ms unsplit, results identical.  Without the im2col builders nothing changes (1.74), so they
-// are not the limit; without the stores 1.22 ms.  What the split adds is a second read of D1 from
-// tensor memory (295 KB instead of 196 KB per tile), and tensor-memory reads are what the
-// epilogue of this layer is made of: 196 KB per 128-pixel tile is ~1.5 us at the 64-128 B/clk an
-// SM reads TMEM with, against 0.4 us of tensor-pipe work.  Kept as an experiment (debug bit 32),
-// not the default; the unsplit epilogue reads every accumulator once.
-template <int MODE, int NC, int KH, int KW, int CIN, bool SPLIT>
+// behind, and a tile takes 4 us against 0.4 us of tensor-pipe work (ncu: 18 % tensor pipe).  The
+// pipelined order
+//     [square tile i+1: D1 -> x (registers), x^2 -> shared memory]  while GEMM2(i) has long finished
+//     [normalise tile i: D2 -> y -> global memory]                   while GEMM2(i+1) runs
+// removes every wait on the tensor pipe from the epilogue warps: the x of two tiles is live at
+// once (2 x 48 packed registers per thread, so the epilogue warpgroups take registers from the
+// TMA / MMA / builder warpgroup with setmaxnreg), y leaves from registers (the x^2 tile of the
+// next image tile sits where the unpipelined epilogue stages its TMA store), tensor-memory loads
+// are 16 columns wide with the next one in flight, and the MMA warp issues GEMM2(i) right after
+// the main GEMM of tile i.  MEASURED (profiles/r2n_thin_pipelined_epilogue.txt): 1.48 ms against
+// 1.33 ms for the unpipelined epilogue, results identical — the waits were not the limit.  The
+// ncu capture that came with it shows what is: the LSU data pipe (63 %: bias / beta vectors read
+// from shared memory by every thread, x^2 stores, the im2col builders' patch reads) ahead of
+// issue slots (31 %) and XU (21 %).  A split by PHASE (four warps squaring, four normalising, x
+// re-read from TMEM) was slower still (profiles/r2i_thin_split_epilogue.txt).  What did help
+// came out of the same capture: the epilogues' shared-memory traffic was compiled as GENERIC
+// loads and stores (see the `smem` pointer below) — fixed for all four tcgen05 kernels.
+template <int MODE, int NC, int KH, int KW, int CIN, bool PIPE>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
                  const __grid_constant__ CUtensorMap map_g,
@@ -249,8 +250,10 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [A ring: stages x 16 KB] [W: KB x npad*128 B] [gamma: cout/64 x npad*128 B]
   //        [A2: cout/64 x 16 KB] [2 image patches] [bias|beta] [barriers]
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~uintptr_t(1023));
+  // aligned with pointer arithmetic on the __shared__ array (not through an integer): the
+  // compiler then knows every pointer derived from `smem` is a shared-memory address and emits
+  // LDS / STS instead of generic LD / ST (twice the wavefronts for a broadcast 128-bit load)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int b_bytes = p.npad * 128;
   const int b_slot = (b_bytes + 1023) & ~1023;
   uint8_t* w_res = smem + p.stages * kABytes;
@@ -276,12 +279,9 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
     mbar_init(&bars->w_full, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&bars->p_full[s], 1); mbar_init(&bars->p_empty[s], kBuilders / 32); }
     if (p.patch) prefetch_tmap(&map_img);
-    constexpr int kPhaseThreads = SPLIT ? kEpiThreads / 2 : kEpiThreads;
-    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], kPhaseThreads); }
-    mbar_init(&bars->a2_full, kPhaseThreads);
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], kEpiThreads); }
+    mbar_init(&bars->a2_full, kEpiThreads);
     mbar_init(&bars->d2_full, 1);
-    mbar_init(&bars->a2_empty, 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d2c_full[s], 1); mbar_init(&bars->d2c_empty[s], kPhaseThreads); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(&bars->tmem_base, 512);
@@ -293,10 +293,6 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
   const int tile1 = p.chunk ? min(tile0 + p.chunk, p.num_tiles) : p.num_tiles;
   const int tile_step = p.chunk ? 1 : (int)gridDim.x;
   const uint32_t idesc = make_idesc_bf16(128, p.npad);
-  // tensor-memory columns: D1[acc] at acc * d1_cols; SPLIT: two 64-column D2 chunk buffers behind
-  constexpr uint32_t d1_cols = SPLIT ? NC * 32 : 256;
-  constexpr uint32_t d2c_base = 2 * d1_cols;
-  constexpr int gdn_chunks = NC / 2;            // 64-column chunks of GEMM2's output
 
   auto tile_coords = [&](int tile, int& n, int& i0, int& j0) {
     const int per_img = p.tiles_h * p.tiles_w;
@@ -307,7 +303,170 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
     j0 = (r - ti * p.tiles_w) * p.tw;
   };
 
-  if (warp == 0) {
+  if (warp >= 4) {
+    // ===== epilogue: 8 warps, thread <-> TMEM lane <-> tile pixel, two column halves =====
+    if constexpr (PIPE) setmaxnreg_inc<kEpiRegs>();
+    const int quad = warp & 3;
+    const int half = (warp - 4) >> 2;
+    const int r = quad * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+    if constexpr (PIPE) {
+      constexpr int NCH = NC / 2;                     // 32-column chunks of this thread's half
+      const int cbase = half * NCH;
+      const int ntiles = tile1 > tile0 ? (tile1 - tile0 + tile_step - 1) / tile_step : 0;
+      // Both phases walk their 96 columns in 16-column pieces with the tensor-memory load of
+      // the next piece in flight behind the piece being worked on (ncu of the one-load-at-a-time
+      // form: a third of all warp samples sat on LDTM and its first consumer).
+      constexpr int NP = NCH * 2;
+      // phase 1 of tile number `it`: x = D1 + bias -> xs (packed bf16), x^2 -> a2
+      auto square = [&](uint32_t it, uint32_t (&xs)[NCH * 16]) {
+        const int acc = it & 1;
+        const uint32_t dacc = tmem + acc * 256 + lane_addr + cbase * 32;
+        mbar_wait(&bars->d1_full[acc], (it >> 1) & 1);
+        tc_fence_after();
+        auto piece = [&](int pc, const uint32_t (&v)[16]) {
+          const int cc = cbase + (pc >> 1);
+          uint8_t* row = a2 + (cc >> 1) * kABytes + r * 128;
+          const float4* bs = reinterpret_cast<const float4*>(s_bias + cc * 32 + (pc & 1) * 16);
+#pragma unroll
+          for (int q2 = 0; q2 < 2; ++q2) {
+            const float4 b0 = bs[2 * q2], b1 = bs[2 * q2 + 1];
+            const float x0 = __uint_as_float(v[8 * q2 + 0]) + b0.x;
+            const float x1 = __uint_as_float(v[8 * q2 + 1]) + b0.y;
+            const float x2 = __uint_as_float(v[8 * q2 + 2]) + b0.z;
+            const float x3 = __uint_as_float(v[8 * q2 + 3]) + b0.w;
+            const float x4 = __uint_as_float(v[8 * q2 + 4]) + b1.x;
+            const float x5 = __uint_as_float(v[8 * q2 + 5]) + b1.y;
+            const float x6 = __uint_as_float(v[8 * q2 + 6]) + b1.z;
+            const float x7 = __uint_as_float(v[8 * q2 + 7]) + b1.w;
+            const int q = (pc & 1) * 2 + q2;
+            xs[pc * 8 + 4 * q2 + 0] = epi::pack_bf16(x0, x1);
+            xs[pc * 8 + 4 * q2 + 1] = epi::pack_bf16(x2, x3);
+            xs[pc * 8 + 4 * q2 + 2] = epi::pack_bf16(x4, x5);
+            xs[pc * 8 + 4 * q2 + 3] = epi::pack_bf16(x6, x7);
+            const int physc = ((cc & 1) * 4 + q) ^ (r & 7);
+            *reinterpret_cast<uint4*>(row + physc * 16) =
+                make_uint4(epi::pack_bf16(x0 * x0, x1 * x1), epi::pack_bf16(x2 * x2, x3 * x3),
+                           epi::pack_bf16(x4 * x4, x5 * x5), epi::pack_bf16(x6 * x6, x7 * x7));
+          }
+        };
+        uint32_t va[16], vb[16];
+        tmem_ld_32x16(dacc, va);
+        tmem_ld_wait();
+#pragma unroll
+        for (int pc = 0; pc < NP; pc += 2) {
+          tmem_ld_32x16(dacc + (pc + 1) * 16, vb);
+          piece(pc, va);
+          tmem_ld_wait();
+          if (pc + 2 < NP) tmem_ld_32x16(dacc + (pc + 2) * 16, va);
+          piece(pc + 1, vb);
+          tmem_ld_wait();
+        }
+        tc_fence_before();
+        fence_proxy_async_smem();
+        mbar_arrive(&bars->a2_full);
+      };
+      // phase 2 of tile number `it` (its d2_full has been waited for): y = x * rsqrt(beta + D2)
+      auto normalise = [&](uint32_t it, const uint32_t (&xs)[NCH * 16]) {
+        int n, i0, j0;
+        tile_coords(tile0 + (int)it * tile_step, n, i0, j0);
+        const int acc = it & 1;
+        const int li = r / p.tw, lj = r - li * p.tw;
+        const int i2 = i0 + li, j2 = j0 + lj;
+        const bool valid = i2 < p.ho && j2 < p.wo && !(p.debug & 2);
+        const int64_t elem0 = (((int64_t)n * p.ho + i2) * p.wo + j2) * p.cout + cbase * 32;
+        const uint32_t dacc = tmem + acc * 256 + lane_addr + cbase * 32;
+        tc_fence_after();
+        auto piece = [&](int pc, const uint32_t (&g)[16]) {
+          const float4* be = reinterpret_cast<const float4*>(s_beta + cbase * 32 + pc * 16);
+          uint32_t w[8];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float4 b4 = be[q];
+            const uint32_t p0 = xs[pc * 8 + 2 * q], p1 = xs[pc * 8 + 2 * q + 1];
+            const float y0 = __uint_as_float(p0 << 16) *
+                             epi::rsqrt_approx(__uint_as_float(g[4 * q + 0]) + b4.x);
+            const float y1 = __uint_as_float(p0 & 0xFFFF0000u) *
+                             epi::rsqrt_approx(__uint_as_float(g[4 * q + 1]) + b4.y);
+            const float y2 = __uint_as_float(p1 << 16) *
+                             epi::rsqrt_approx(__uint_as_float(g[4 * q + 2]) + b4.z);
+            const float y3 = __uint_as_float(p1 & 0xFFFF0000u) *
+                             epi::rsqrt_approx(__uint_as_float(g[4 * q + 3]) + b4.w);
+            if (p.out_f32) {
+              if (valid)
+                reinterpret_cast<float4*>(static_cast<float*>(p.out) + elem0 + pc * 16)[q] =
+                    make_float4(y0, y1, y2, y3);
+            } else {
+              w[2 * q] = epi::pack_bf16(y0, y1);
+              w[2 * q + 1] = epi::pack_bf16(y2, y3);
+            }
+          }
+          if (!p.out_f32 && valid) {
+            __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(p.out) + elem0 + pc * 16;
+            if (p.out_wide) {
+              epi::st_global_v8(dst, w[0], w[1], w[2], w[3], w[4], w[5], w[6], w[7]);
+            } else {
+              reinterpret_cast<uint4*>(dst)[0] = make_uint4(w[0], w[1], w[2], w[3]);
+              reinterpret_cast<uint4*>(dst)[1] = make_uint4(w[4], w[5], w[6], w[7]);
+            }
+          }
+        };
+        uint32_t ga[16], gb[16];
+        tmem_ld_32x16(dacc, ga);
+        tmem_ld_wait();
+#pragma unroll
+        for (int pc = 0; pc < NP; pc += 2) {
+          tmem_ld_32x16(dacc + (pc + 1) * 16, gb);
+          piece(pc, ga);
+          tmem_ld_wait();
+          if (pc + 2 < NP) tmem_ld_32x16(dacc + (pc + 2) * 16, ga);
+          piece(pc + 1, gb);
+          tmem_ld_wait();
+        }
+        tc_fence_before();
+        mbar_arrive(&bars->d1_empty[acc]);
+      };
+      uint32_t xa[NCH * 16], xb[NCH * 16];
+      if (ntiles > 0) square(0, xa);
+      for (int it = 0; it < ntiles; it += 2) {
+        // d2_full(it) completing also means GEMM2(it) has read a2: the next x^2 may go in
+        mbar_wait(&bars->d2_full, it & 1);
+        if (it + 1 < ntiles) square(it + 1, xb);
+        normalise(it, xa);
+        if (it + 1 < ntiles) {
+          mbar_wait(&bars->d2_full, (it + 1) & 1);
+          if (it + 2 < ntiles) square(it + 2, xa);
+          normalise(it + 1, xb);
+        }
+      }
+    } else {
+    uint32_t it = 0;
+    for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
+      int n, i0, j0;
+      tile_coords(tile, n, i0, j0);
+      const int acc = it & 1;
+      const int li = r / p.tw, lj = r - li * p.tw;
+      const int i2 = i0 + li, j2 = j0 + lj;
+      const bool valid = i2 < p.ho && j2 < p.wo && !(p.debug & 2);
+      const int64_t elem0 = (((int64_t)n * p.ho + i2) * p.wo + j2) * p.cout;
+      const uint32_t dacc = tmem + acc * 256 + lane_addr;
+      mbar_wait(&bars->d1_full[acc], (it >> 1) & 1);
+      tc_fence_after();
+      if constexpr (GDN)
+        epi::gdn_tile<MODE, NC / 2>(dacc, a2, r, half * (NC / 2), s_bias, s_beta, &bars->a2_full,
+                                    &bars->d2_full, it, valid, p.out, p.out_f32 != 0,
+                                    p.out_wide != 0, elem0, p.out_tma ? &map_out : nullptr,
+                                    epi::TileOrigin{j0, i0, n}, threadIdx.x == 128, NC / 2);
+      else
+        epi::bias_tile(dacc, half, p.npad, p.cout, s_bias, p.act == TFC_ACT_RELU, valid, p.out,
+                       p.out_f32 != 0, p.out_wide != 0, elem0);
+      tc_fence_before();
+      mbar_arrive(&bars->d1_empty[acc]);
+    }
+    if (GDN && p.out_tma && threadIdx.x == 128) bulk_wait_read();
+    }
+  } else if (warp == 0) {
+    if constexpr (PIPE) setmaxnreg_dec<kOtherRegs>();
     // ===== one-time TMA: resident weights and gamma =====
     if (lane == 0) {
       mbar_expect_tx(&bars->w_full, (KB + gdn_kblocks) * b_bytes);
@@ -334,34 +493,14 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
       }
     }
   } else if (warp == 1) {
+    if constexpr (PIPE) setmaxnreg_dec<kOtherRegs>();
     // ===== MMA issuer =====
     if (lane == 0) {
       int stage = 0;
       uint32_t ph = 0, it = 0;
-      uint32_t gchunk = 0;
-      const uint32_t idesc64 = make_idesc_bf16(128, 64);
       auto issue_gdn = [&](uint32_t j) {
         mbar_wait(&bars->a2_full, j & 1);
         tc_fence_after();
-        if constexpr (SPLIT) {
-          for (int ch = 0; ch < gdn_chunks; ++ch, ++gchunk) {
-            const uint32_t buf = gchunk & 1;
-            mbar_wait(&bars->d2c_empty[buf], ((gchunk >> 1) & 1) ^ 1);
-            tc_fence_after();
-            const uint32_t d2 = tmem + d2c_base + buf * 64;
-            for (int kc = 0; kc < gdn_kblocks; ++kc) {
-              const uint64_t da = make_desc_sw128(smem_u32(a2 + kc * kABytes));
-              // rows [64 ch, 64 ch + 64) of the K-major gamma block: 8 swizzle atoms of 1 KB
-              const uint64_t db = make_desc_sw128(smem_u32(g_res + kc * b_slot + ch * 8192));
-#pragma unroll
-              for (int k = 0; k < 4; ++k)
-                umma_bf16(d2, da + (k * 2), db + (k * 2), idesc64, (kc | k) != 0);
-            }
-            umma_commit(&bars->d2c_full[buf]);
-          }
-          umma_commit(&bars->a2_empty);
-          return;
-        }
         const uint32_t d2 = tmem + (j & 1) * 256;
         for (int kc = 0; kc < gdn_kblocks; ++kc) {
           const uint64_t da = make_desc_sw128(smem_u32(a2 + kc * kABytes));
@@ -377,7 +516,7 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
         const int acc = it & 1;
         mbar_wait(&bars->d1_empty[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t d1 = tmem + acc * d1_cols;
+        const uint32_t d1 = tmem + acc * 256;
 #pragma unroll
         for (int kb = 0; kb < KB; ++kb) {
           const int nm = (K - kb * 64 >= 64) ? 4 : (K - kb * 64 + 15) / 16;
@@ -392,142 +531,20 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
           if (++stage == p.stages) { stage = 0; ph ^= 1; }
         }
         umma_commit(&bars->d1_full[acc]);
-        // GEMM2 of the previous tile goes AFTER this tile's main GEMM: the main GEMM is short
-        // and its operands are ready long before the epilogue has squared the previous tile
-        if (GDN && it > 0) issue_gdn(it - 1);
-      }
-      if (GDN && it > 0) issue_gdn(it - 1);
-    }
-  } else if (SPLIT && warp < 2 + epi::kEpilogueWarps / 2) {
-    // ===== phase 1 (warps 2-5): x = D1 + bias, x^2 -> bf16 K-major SW128 tile =====
-    if constexpr (SPLIT) {
-      const int quad = warp & 3;
-      const int r = quad * 32 + lane;
-      const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
-      uint32_t it = 0;
-      for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
-        const int acc = it & 1;
-        const uint32_t dacc = tmem + acc * d1_cols + lane_addr;
-        mbar_wait(&bars->d1_full[acc], (it >> 1) & 1);
-        mbar_wait(&bars->a2_empty, (it & 1) ^ 1);      // GEMM2 of the previous tile has read a2
-        tc_fence_after();
-#pragma unroll
-        for (int cc = 0; cc < NC; ++cc) {
-          uint32_t v[32];
-          tmem_ld_32x32(dacc + cc * 32, v);
-          tmem_ld_wait();
-          uint8_t* row = a2 + (cc >> 1) * kABytes + r * 128;
-          const float4* bs = reinterpret_cast<const float4*>(s_bias + cc * 32);
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const float4 b0 = bs[2 * q], b1 = bs[2 * q + 1];
-            const float x0 = __uint_as_float(v[8 * q + 0]) + b0.x;
-            const float x1 = __uint_as_float(v[8 * q + 1]) + b0.y;
-            const float x2 = __uint_as_float(v[8 * q + 2]) + b0.z;
-            const float x3 = __uint_as_float(v[8 * q + 3]) + b0.w;
-            const float x4 = __uint_as_float(v[8 * q + 4]) + b1.x;
-            const float x5 = __uint_as_float(v[8 * q + 5]) + b1.y;
-            const float x6 = __uint_as_float(v[8 * q + 6]) + b1.z;
-            const float x7 = __uint_as_float(v[8 * q + 7]) + b1.w;
-            const int physc = ((cc & 1) * 4 + q) ^ (r & 7);
-            *reinterpret_cast<uint4*>(row + physc * 16) =
-                make_uint4(epi::pack_bf16(x0 * x0, x1 * x1), epi::pack_bf16(x2 * x2, x3 * x3),
-                           epi::pack_bf16(x4 * x4, x5 * x5), epi::pack_bf16(x6 * x6, x7 * x7));
-          }
+        if constexpr (PIPE) {
+          issue_gdn(it);        // waits for the epilogue to have squared this tile
+        } else {
+          // GEMM2 of the previous tile goes AFTER this tile's main GEMM: the main GEMM is short
+          // and its operands are ready long before the epilogue has squared the previous tile
+          if (GDN && it > 0) issue_gdn(it - 1);
         }
-        tc_fence_before();
-        fence_proxy_async_smem();
-        mbar_arrive(&bars->a2_full);
       }
+      if (!PIPE && GDN && it > 0) issue_gdn(it - 1);
     }
-  } else if (SPLIT && warp < 2 + epi::kEpilogueWarps) {
-    // ===== phase 2 (warps 6-9): y = bf16(x) * rsqrt(beta + D2), stored from registers =====
-    if constexpr (SPLIT) {
-      const int quad = warp & 3;
-      const int r = quad * 32 + lane;
-      const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
-      uint32_t it = 0, gchunk = 0;
-      for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
-        int n, i0, j0;
-        tile_coords(tile, n, i0, j0);
-        const int acc = it & 1;
-        const int li = r / p.tw, lj = r - li * p.tw;
-        const int i2 = i0 + li, j2 = j0 + lj;
-        const bool valid = i2 < p.ho && j2 < p.wo && !(p.debug & 2);
-        const int64_t elem0 = (((int64_t)n * p.ho + i2) * p.wo + j2) * p.cout;
-        const uint32_t dacc = tmem + acc * d1_cols + lane_addr;
-        for (int ch = 0; ch < gdn_chunks; ++ch, ++gchunk) {
-          const uint32_t buf = gchunk & 1;
-          mbar_wait(&bars->d2c_full[buf], (gchunk >> 1) & 1);
-          tc_fence_after();
-#pragma unroll
-          for (int piece = 0; piece < 2; ++piece) {
-            const int cc = ch * 2 + piece;
-            uint32_t g[32], xv[32];
-            tmem_ld_32x32(tmem + d2c_base + buf * 64 + piece * 32 + lane_addr, g);
-            tmem_ld_32x32(dacc + cc * 32, xv);
-            tmem_ld_wait();
-            const float4* be = reinterpret_cast<const float4*>(s_beta + cc * 32);
-            const float4* bs = reinterpret_cast<const float4*>(s_bias + cc * 32);
-            float y[32];
-#pragma unroll
-            for (int q = 0; q < 8; ++q) {
-              const float4 b4 = be[q], s4 = bs[q];
-              const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
-              const float sb[4] = {s4.x, s4.y, s4.z, s4.w};
-#pragma unroll
-              for (int e = 0; e < 4; e += 2) {
-                const uint32_t pr = epi::pack_bf16(__uint_as_float(xv[4 * q + e]) + sb[e],
-                                                   __uint_as_float(xv[4 * q + e + 1]) + sb[e + 1]);
-                const float xa = __uint_as_float(pr << 16);
-                const float xb = __uint_as_float(pr & 0xFFFF0000u);
-                const float na = __uint_as_float(g[4 * q + e]) + bb[e];
-                const float nb = __uint_as_float(g[4 * q + e + 1]) + bb[e + 1];
-                y[4 * q + e] = xa * epi::rsqrt_approx(na);
-                y[4 * q + e + 1] = xb * epi::rsqrt_approx(nb);
-              }
-            }
-            if (valid) epi::store_chunk(p.out, p.out_f32 != 0, p.out_wide != 0, elem0 + cc * 32, y);
-          }
-          tc_fence_before();
-          mbar_arrive(&bars->d2c_empty[buf]);
-        }
-        mbar_arrive(&bars->d1_empty[acc]);
-      }
-    }
-  } else if (warp < 2 + epi::kEpilogueWarps) {
-    // ===== epilogue: 8 warps, thread <-> TMEM lane <-> tile pixel, two column halves =====
-    const int quad = warp & 3;
-    const int half = (warp - 2) >> 2;
-    const int r = quad * 32 + lane;
-    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
-    uint32_t it = 0;
-    for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
-      int n, i0, j0;
-      tile_coords(tile, n, i0, j0);
-      const int acc = it & 1;
-      const int li = r / p.tw, lj = r - li * p.tw;
-      const int i2 = i0 + li, j2 = j0 + lj;
-      const bool valid = i2 < p.ho && j2 < p.wo && !(p.debug & 2);
-      const int64_t elem0 = (((int64_t)n * p.ho + i2) * p.wo + j2) * p.cout;
-      const uint32_t dacc = tmem + acc * 256 + lane_addr;
-      mbar_wait(&bars->d1_full[acc], (it >> 1) & 1);
-      tc_fence_after();
-      if constexpr (GDN)
-        epi::gdn_tile<MODE, NC / 2>(dacc, a2, r, half * (NC / 2), s_bias, s_beta, &bars->a2_full,
-                                    &bars->d2_full, it, valid, p.out, p.out_f32 != 0,
-                                    p.out_wide != 0, elem0, p.out_tma ? &map_out : nullptr,
-                                    epi::TileOrigin{j0, i0, n}, threadIdx.x == 64, NC / 2);
-      else
-        epi::bias_tile(dacc, half, p.npad, p.cout, s_bias, p.act == TFC_ACT_RELU, valid, p.out,
-                       p.out_f32 != 0, p.out_wide != 0, elem0);
-      tc_fence_before();
-      mbar_arrive(&bars->d1_empty[acc]);
-    }
-    if (GDN && p.out_tma && threadIdx.x == 64) bulk_wait_read();
   } else {
-    // ===== im2col builders =====
-    const int t = threadIdx.x - (64 + kEpiThreads);
+    if constexpr (PIPE) setmaxnreg_dec<kOtherRegs>();
+    // ===== im2col builders (warps 2-3) =====
+    const int t = threadIdx.x - 64;
     int stage = 0;
     uint32_t ph = 0;
     const uint8_t* patch = nullptr;
@@ -610,7 +627,7 @@ struct Plan {
   int patch_rows, patch_pitch, patch_slot, vec;
   size_t smem;
   bool gdn;
-  bool split;               // split-phase GDN epilogue (experiment: debug bit 32 turns it on)
+  bool pipe;                // software-pipelined GDN epilogue (experiment: debug bit 32 turns it on)
 };
 
 bool shape_ok(const tfc_conv_desc& d) {
@@ -619,7 +636,7 @@ bool shape_ok(const tfc_conv_desc& d) {
 
 bool make_plan(const tfc_conv_desc& d, const void* in, Plan* pl) {
   pl->gdn = d.act == TFC_ACT_GDN;
-  pl->split = pl->gdn && (tfc::debug_bits() & 32) != 0;   // measured slower: see the kernel comment
+  pl->pipe = pl->gdn && (tfc::debug_bits() & 32) != 0;   // measured slower: see the kernel comment
   const int K = d.kh * d.kw * d.cin;
   pl->kblocks = (K + 63) / 64;
   pl->npad = (d.cout + 15) / 16 * 16;
@@ -665,7 +682,7 @@ int launch(const tfc_conv_desc& d, const Plan& pl, const CUtensorMap& map_w,
                const Params) = nullptr;
   if (!pl.gdn) {
     kern = conv_thin_kernel<0, 0, KH, KW, 3, false>;
-  } else if (pl.split) {
+  } else if (pl.pipe) {
     switch (d.cout / 32) {
       case 4: kern = conv_thin_kernel<1, 4, KH, KW, 3, true>; break;
       case 6: kern = conv_thin_kernel<1, 6, KH, KW, 3, true>; break;
@@ -779,7 +796,7 @@ int conv_thin(const tfc_conv_desc& d, const void* in, const float* w, const floa
   } else {
     map_img = map_w;
   }
-  p.out_tma = pl.gdn && !pl.split && !p.out_f32 && d.cout % 64 == 0 && !(debug_bits() & 16);
+  p.out_tma = pl.gdn && !pl.pipe && !p.out_f32 && d.cout % 64 == 0 && !(debug_bits() & 16);
   if (p.out_tma) {
     cuuint64_t dims[4] = {(cuuint64_t)d.cout, (cuuint64_t)d.wo, (cuuint64_t)d.ho, (cuuint64_t)d.n};
     cuuint64_t str[3] = {(cuuint64_t)d.cout * 2, (cuuint64_t)d.wo * d.cout * 2,

@@ -108,8 +108,10 @@ conv_umma_kernel(const __grid_constant__ CUtensorMap map_a,
   constexpr bool GDN = MODE != 0;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [stages x (A 16 KB | B npad*128 B)] [A2: cout/64 x 16 KB] [bias|beta] [barriers]
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~uintptr_t(1023));
+  // aligned with pointer arithmetic on the __shared__ array (not through an integer): the
+  // compiler then knows every pointer derived from `smem` is a shared-memory address and emits
+  // LDS / STS instead of generic LD / ST (twice the wavefronts for a broadcast 128-bit load)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   // B bytes one CTA holds per stage: all N rows, or its half of them when the pair shares B
   const int b_bytes = (PAIR ? p.npad / 2 : p.npad) * kBlockK * 2;
   const int stage_bytes = kABytes + ((b_bytes + 1023) & ~1023);

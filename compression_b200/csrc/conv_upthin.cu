@@ -89,8 +89,10 @@ __global__ void __launch_bounds__(kThreads, 1)
 conv_upthin_kernel(const __grid_constant__ CUtensorMap map_a,
                    const __grid_constant__ CUtensorMap map_w, const UpParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~uintptr_t(1023));
+  // aligned with pointer arithmetic on the __shared__ array (not through an integer): the
+  // compiler then knows every pointer derived from `smem` is a shared-memory address and emits
+  // LDS / STS instead of generic LD / ST (twice the wavefronts for a broadcast 128-bit load)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   // carve: [W: kchunks x npad*128 B (1 KB aligned)] [A ring: stages x 16 KB] [D: 2 x 128 x ld
   // floats] [bias] [barriers]
   const int w_chunk = (p.npad * kBlockK * 2 + 1023) & ~1023;

@@ -610,6 +610,29 @@ def test_entropy_models_training_true_is_differentiable(tfc):
 
 @pytest.mark.parametrize("corr,sd,su,act", [(True, 2, 1, "gdn"), (False, 1, 2, "igdn"),
                                             (True, 1, 1, "relu"), (True, 2, 1, None)])
+def test_thin_conv_pipelined_epilogue_equals_default():
+  """conv_thin_kernel's software-pipelined GDN epilogue (an experiment behind debug bit 32:
+  setmaxnreg, two tiles in flight, y stored from registers) computes exactly what the default
+  epilogue computes, float32 and uint8 images, bfloat16 and float32 outputs."""
+  from compression_b200 import _lib
+  from compression_b200.examples import bmshj2018
+  model = bmshj2018.Bmshj2018Model(192, "cuda", seed=5)
+  layer = model.analysis_transform.layers[0]
+  g = torch.Generator().manual_seed(9)
+  xf = torch.rand((3, 72, 104, 3), generator=g).cuda()
+  xu = torch.randint(0, 256, (3, 72, 104, 3), generator=g, dtype=torch.uint8).cuda()
+  for x in (xf, xu):
+    for out_dtype in (torch.bfloat16, torch.float32):
+      want = layer(x, out_dtype=out_dtype)
+      _lib.check(_lib.lib().tfc_configure(99, 32))
+      try:
+        got = layer(x, out_dtype=out_dtype)
+        torch.cuda.synchronize()
+      finally:
+        _lib.check(_lib.lib().tfc_configure(99, 0))
+      assert torch.equal(got, want)
+
+
 def test_cta_pair_conv_equals_single_cta(tfc, corr, sd, su, act):
   """TFC_CFG_CONV_PAIR: the implicit GEMM on CTA pairs (tcgen05.mma.cta_group::2, M = 256 over
   two adjacent tiles, each CTA holding half of the weight tile) sums the same products in the
