@@ -95,8 +95,10 @@ def parse_args():
                   help="shared memory per coder CTA in the pipeline (0: 226 KB)")
   ap.add_argument("--coder-table-kb", type=int, default=0,
                   help="shared memory for the coder's staged tables in the pipeline (0: 72 KB)")
-  ap.add_argument("--stage-priority", type=int, default=1,
-                  help="transform stage streams from the high-priority pool (1) or the default one (0)")
+  ap.add_argument("--stage-priority", default="1",
+                  help="transform stage streams from the high-priority pool (1) or the default one "
+                       "(0), or 'a,h,s': stream priority levels (0, -1, -2, -3) of the analysis, "
+                       "hyper-synthesis and synthesis stages")
   ap.add_argument("--coder-pack", type=int, default=0,
                   help="coder streams per CTA when depth > 1 (0: by the number of streams in "
                        "flight: 4 at batch 64 x 12, 2 at batch 32 x 8)")
@@ -760,7 +762,8 @@ def run_b200(args):
   pipe = model.pipeline(args.depth, args.tiles_per_cta, args.coder_pack, args.back_lag,
                         args.host_slots, conv_stages=args.conv_stages,
                         coder_smem_kb=args.coder_smem_kb, coder_table_kb=args.coder_table_kb,
-                        stage_priority=bool(args.stage_priority))
+                        stage_priority=(tuple(int(v) for v in args.stage_priority.split(","))
+                                        if "," in args.stage_priority else bool(int(args.stage_priority))))
 
   with pipe:
     # every stream of the pipeline must have run once before the timed region: a stream's first

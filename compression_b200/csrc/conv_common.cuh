@@ -53,6 +53,10 @@ int conv_upthin(const tfc_conv_desc& d, const void* in, const float* w, const fl
 // filter gradient on tcgen05 with MN-major operands (conv_wgrad_umma.cu): both channel counts
 // multiples of 64, the M side exactly 128; `dw` must be zeroed (slices add atomically)
 bool conv_wgrad_umma_supported(const tfc_conv_desc& d);
+// the same for the layers with 3 channels on one side (conv_thin.cu: software im2col as A operand)
+bool conv_thin_wgrad_supported(const tfc_conv_desc& d, const void* x_bf16, const void* dy_bf16);
+int conv_thin_wgrad(const tfc_conv_desc& d, const void* x_bf16, const void* dy_bf16, float* dw,
+                    cudaStream_t st);
 int conv_wgrad_umma(const tfc_conv_desc& d, const void* x_bf16, const void* dy_bf16, float* dw,
                     cudaStream_t st);
 

@@ -620,6 +620,210 @@ __global__ void repack_gamma_kernel(const float* __restrict__ g, int c_count, in
   }
 }
 
+// =========================================================================================
+// Filter gradient of the thin layers on tcgen05 (training step, examples/bls2017.py:156-185)
+// =========================================================================================
+// In the normalised form of tfc_b200.h the gradient of a layer with 3 channels on one side is
+//     G[(a, b, c)][o] = sum_{n,i,j} big[n, s*i + a - p, s*j + b - q, c] * small[n, i, j, o]
+// (big = the 3-channel tensor: the image for the first analysis layer, the output gradient for
+// the last synthesis layer; small = the 128-channel one on the coarse grid): a GEMM
+//     G[K = kh*kw*3, cs] = im2col(big)^T [K x pixels] . small [pixels x cs]
+// whose reduction dimension is the pixel index.  Its A operand is the SAME shared-memory tile the
+// forward kernel above feeds its main GEMM with — 128 pixels x 64 im2col columns per 16 KB slab,
+// 128-byte rows, 128-byte swizzle — read MN-major instead of K-major (the major bit of the
+// instruction descriptor), so the forward kernel's builders are reused as they are; `small`
+// arrives by TMA exactly as in conv_wgrad_umma.cu.  K = 243 needs two M = 128 accumulators
+// (2 x cs <= 512 TMEM columns), which live for the whole CTA; at the end four warps add them to
+// dw with float atomics (148 CTAs meet there).  Replaces the mma.sync kernel of conv_wgrad.cu for
+// these layers: 0.46 ms -> see profiles/ for the 9x9x3 <-> 128 layers of bls2017 at batch 64.
+constexpr int kWgThreads = 256;       // TMA, MMA, 2 builder warps, 4 epilogue warps
+
+struct WgParams {
+  Params b;                 // geometry of the forward-like view: (h, w) = big, (ho, wo) = small
+  float* dw;
+  int32_t cs;               // channels of `small`
+  int32_t transposed;       // 0: dw[k][o] = G[k][o];  1: dw[(taps-1-tap)][o][c] = G[(tap, c)][o]
+  int32_t ntiles_cta_step;
+};
+
+struct __align__(8) WgBarriers {
+  uint64_t full[2], empty[2], p_full[2], p_empty[2];
+  uint64_t d_full;
+  uint32_t tmem_base;
+  uint32_t pad;
+};
+
+__device__ __forceinline__ uint64_t make_desc_mn_sw128(uint32_t smem_addr, uint32_t lbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFFu) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+template <int KH, int KW, int CIN>
+__global__ void __launch_bounds__(kWgThreads, 1)
+conv_thin_wgrad_kernel(const __grid_constant__ CUtensorMap map_img,
+                       const __grid_constant__ CUtensorMap map_small, const WgParams q) {
+  constexpr int K = KH * KW * CIN;
+  constexpr int KB = (K + 63) / 64;            // 16 KB slabs of the A tile
+  constexpr int MH = (KB + 1) / 2;             // M = 128 halves of the accumulator
+  const Params& p = q.b;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const int ns = q.cs / 64;
+  const int stage_bytes = (2 * MH + ns) * kABytes;
+  uint8_t* patches = smem + 2 * stage_bytes;
+  WgBarriers* bars = reinterpret_cast<WgBarriers*>(patches + 2 * p.patch_slot);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t tmem_cols = MH * q.cs <= 64 ? 64 : (MH * q.cs <= 128 ? 128 : (MH * q.cs <= 256 ? 256 : 512));
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&map_img);
+    prefetch_tmap(&map_small);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&bars->full[s], 1 + kBuilders / 32);
+      mbar_init(&bars->empty[s], 1);
+      mbar_init(&bars->p_full[s], 1);
+      mbar_init(&bars->p_empty[s], kBuilders / 32);
+    }
+    mbar_init(&bars->d_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&bars->tmem_base, tmem_cols);
+  // slabs the builders never write (odd KB) must not hold NaN patterns: zero the A tiles once
+  for (int i = threadIdx.x * 16; i < 2 * stage_bytes; i += kWgThreads * 16)
+    *reinterpret_cast<uint4*>(smem + i) = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bars->tmem_base;
+  const int tile0 = (int)blockIdx.x, tile_step = (int)gridDim.x;
+
+  auto tile_coords = [&](int tile, int& n, int& i0, int& j0) {
+    const int per_img = p.tiles_h * p.tiles_w;
+    n = tile / per_img;
+    const int r = tile - n * per_img;
+    const int ti = r / p.tiles_w;
+    i0 = ti * p.th;
+    j0 = (r - ti * p.tiles_w) * p.tw;
+  };
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int tile = tile0; tile < p.num_tiles; tile += tile_step, ++it) {
+        int n, i0, j0;
+        tile_coords(tile, n, i0, j0);
+        const int sb = it & 1;
+        const uint32_t par = ((it >> 1) & 1) ^ 1;
+        mbar_wait(&bars->p_empty[sb], par);
+        mbar_expect_tx(&bars->p_full[sb], p.patch_bytes);
+        int c0 = (j0 * p.sd - p.pl) * CIN;
+        c0 -= c0 & (p.per16 - 1);
+        tma_load_3d(patches + sb * p.patch_slot, &map_img, &bars->p_full[sb], c0, i0 * p.sd - p.pt, n);
+        mbar_wait(&bars->empty[sb], par);
+        uint8_t* sbase = smem + sb * stage_bytes + 2 * MH * kABytes;
+        mbar_expect_tx(&bars->full[sb], (uint32_t)(ns * kABytes));
+        for (int c = 0; c < ns; ++c) {
+          asm volatile(
+              "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
+              " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(smem_u32(sbase + c * kABytes)),
+              "l"(reinterpret_cast<uint64_t>(&map_small)), "r"(smem_u32(&bars->full[sb])),
+              "r"(c * 64), "r"(j0), "r"(i0), "r"(n)
+              : "memory");
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // kind::f16, bf16 x bf16 -> f32, A and B MN-major (bits 15, 16)
+      const uint32_t idesc = make_idesc_bf16(128, q.cs) | (1u << 15) | (1u << 16);
+      uint32_t it = 0;
+      for (int tile = tile0; tile < p.num_tiles; tile += tile_step, ++it) {
+        const int sb = it & 1;
+        mbar_wait(&bars->full[sb], (it >> 1) & 1);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + sb * stage_bytes);
+        const uint64_t db = make_desc_mn_sw128(sa + 2 * MH * kABytes, kABytes);
+#pragma unroll
+        for (int half = 0; half < MH; ++half) {
+          const uint64_t da = make_desc_mn_sw128(sa + half * 2 * kABytes, kABytes);
+#pragma unroll
+          for (int k = 0; k < 8; ++k)          // 16 pixel rows = 2048 bytes per step
+            umma_bf16(tmem + half * q.cs, da + (uint64_t)(k * 128), db + (uint64_t)(k * 128), idesc,
+                      it != 0 || k != 0);
+        }
+        umma_commit(&bars->empty[sb]);
+      }
+      umma_commit(&bars->d_full);
+    }
+  } else if (warp < 4) {
+    // ===== im2col builders: the forward kernel's, all KB blocks of a tile into one stage =====
+    const int t = threadIdx.x - 64;
+    uint32_t it = 0;
+    for (int tile = tile0; tile < p.num_tiles; tile += tile_step, ++it) {
+      int n, i0, j0;
+      tile_coords(tile, n, i0, j0);
+      const int sb = it & 1;
+      mbar_wait(&bars->p_full[sb], (it >> 1) & 1);
+      mbar_wait(&bars->empty[sb], ((it >> 1) & 1) ^ 1);
+      const int skip = ((j0 * p.sd - p.pl) * CIN) & (p.per16 - 1);
+      const __nv_bfloat16* patch = reinterpret_cast<const __nv_bfloat16*>(
+          patches + sb * p.patch_slot + skip * p.esize);
+      uint8_t* sa = smem + sb * stage_bytes;
+      auto block = [&](auto kbi) {
+        constexpr int KBI = decltype(kbi)::value;
+        if constexpr (KBI < KB)
+          build_block_patch<KH, KW, CIN, KBI>(p, patch, t, sa + KBI * kABytes);
+      };
+      block(std::integral_constant<int, 0>{});
+      block(std::integral_constant<int, 1>{});
+      block(std::integral_constant<int, 2>{});
+      block(std::integral_constant<int, 3>{});
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&bars->full[sb]);
+        mbar_arrive(&bars->p_empty[sb]);
+      }
+    }
+  } else {
+    // ===== epilogue: warp w reads TMEM lanes 32*(w%4) .. +31 (= im2col column), all cs columns =====
+    if (tile0 < p.num_tiles) {
+      const int quad = warp & 3;
+      mbar_wait(&bars->d_full, 0);
+      tc_fence_after();
+      constexpr int taps = KH * KW;
+      for (int half = 0; half < MH; ++half) {
+        const int m = half * 128 + quad * 32 + lane;          // (tap, c) = (m / CIN, m % CIN)
+        for (int c0 = 0; c0 < q.cs; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(tmem + ((uint32_t)(quad * 32) << 16) + (uint32_t)(half * q.cs + c0), v);
+          tmem_ld_wait();
+          if (m < K) {
+            const int tap = m / CIN, c = m - tap * CIN;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int o = c0 + j;
+              const int64_t at = q.transposed ? ((int64_t)(taps - 1 - tap) * q.cs + o) * CIN + c
+                                              : (int64_t)m * q.cs + o;
+              atomicAdd(q.dw + at, __uint_as_float(v[j]));
+            }
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, tmem_cols);
+}
+
+
 struct Plan {
   int kblocks, npad, stages;
   int th, tw;
@@ -814,6 +1018,109 @@ int conv_thin(const tfc_conv_desc& d, const void* in, const float* w, const floa
                            : std::min(p.num_tiles, persistent_grid());
   if (d.kh == 5) return launch<5, 5>(d, pl, map_w, map_g, map_img, map_out, p, grid, st);
   return launch<9, 9>(d, pl, map_w, map_g, map_img, map_out, p, grid, st);
+}
+
+}  // namespace tfc
+
+// ---- thin-layer filter gradient (kernel above) -------------------------------------------
+namespace {
+
+struct WgPlan {
+  tfc_conv_desc fwd;        // the forward-like view the builders walk
+  const void* big;
+  const void* small;
+  int cs, transposed;
+  Plan pl;
+  size_t smem;
+};
+
+bool make_wg_plan(const tfc_conv_desc& d, const void* x, const void* dy, WgPlan* w) {
+  if (d.sd > 1 && d.su > 1) return false;
+  const bool up = d.su > 1;
+  const int cb = up ? d.cout : d.cin, cs = up ? d.cin : d.cout;
+  if (cb != 3 || d.kh != d.kw || (d.kh != 5 && d.kh != 9)) return false;
+  if (cs % 64 || cs < 64 || cs > 256) return false;
+  const int K = d.kh * d.kw * 3, MH = ((K + 63) / 64 + 1) / 2;
+  if (MH * cs > 512) return false;
+  tfc_conv_desc f = d;
+  f.h = up ? d.ho : d.h;   f.w = up ? d.wo : d.w;
+  f.ho = up ? d.h : d.ho;  f.wo = up ? d.w : d.wo;
+  f.cin = 3; f.cout = cs;
+  f.sd = up ? d.su : d.sd; f.su = 1;
+  f.pad_top = up ? d.kh - 1 - d.pad_top : d.pad_top;
+  f.pad_left = up ? d.kw - 1 - d.pad_left : d.pad_left;
+  f.act = TFC_ACT_NONE; f.in_dtype = TFC_BF16; f.out_dtype = TFC_F32;
+  if (f.sd > 8 || (int64_t)f.n * f.ho * f.wo < 128) return false;
+  w->fwd = f;
+  w->big = up ? dy : x;
+  w->small = up ? x : dy;
+  w->cs = cs;
+  w->transposed = up ? 1 : 0;
+  if (!make_plan(f, w->big, &w->pl) || !w->pl.patch) return false;
+  const size_t stage = (size_t)(2 * MH + cs / 64) * kABytes;
+  w->smem = 1024 + 2 * stage + 2 * (size_t)w->pl.patch_slot + sizeof(WgBarriers) + 64;
+  return w->smem <= 227 * 1024;
+}
+
+template <int KH, int KW>
+int launch_wg(const WgPlan& w, const CUtensorMap& map_img, const CUtensorMap& map_small,
+              const WgParams& q, int grid, cudaStream_t st) {
+  auto kern = conv_thin_wgrad_kernel<KH, KW, 3>;
+  TFC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w.smem));
+  kern<<<grid, kWgThreads, w.smem, st>>>(map_img, map_small, q);
+  TFC_LAUNCHED("conv_thin_wgrad_kernel");
+  return TFC_OK;
+}
+
+}  // namespace
+
+namespace tfc {
+
+bool conv_thin_wgrad_supported(const tfc_conv_desc& d, const void* x, const void* dy) {
+  WgPlan w;
+  return make_wg_plan(d, x, dy, &w);
+}
+
+// dw must be zero on entry (tfc_signal_conv2d_wgrad clears it): the CTAs add their partial sums
+int conv_thin_wgrad(const tfc_conv_desc& d, const void* x, const void* dy, float* dw,
+                    cudaStream_t st) {
+  WgPlan w;
+  if (!make_wg_plan(d, x, dy, &w))
+    return fail(TFC_ERR_UNIMPLEMENTED, "thin-layer filter gradient: shape not supported");
+  const tfc_conv_desc& f = w.fwd;
+  const Plan& pl = w.pl;
+  WgParams q{};
+  Params& p = q.b;
+  p.n = f.n; p.h = f.h; p.w = f.w; p.ho = f.ho; p.wo = f.wo; p.cout = f.cout; p.npad = f.cout;
+  p.sd = f.sd; p.pt = f.pad_top; p.pl = f.pad_left;
+  p.in_dtype = TFC_BF16; p.esize = 2; p.per16 = 8;
+  p.th = pl.th; p.tw = pl.tw;
+  p.patch = 1; p.patch_pitch = pl.patch_pitch; p.patch_slot = pl.patch_slot; p.vec = pl.vec;
+  p.patch_bytes = pl.patch_rows * pl.patch_pitch * p.esize;
+  p.tiles_h = (f.ho + p.th - 1) / p.th;
+  p.tiles_w = (f.wo + p.tw - 1) / p.tw;
+  p.num_tiles = f.n * p.tiles_h * p.tiles_w;
+  q.dw = dw; q.cs = w.cs; q.transposed = w.transposed;
+
+  CUtensorMap map_img, map_small;
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)f.w * 3, (cuuint64_t)f.h, (cuuint64_t)f.n};
+    cuuint64_t str[2] = {(cuuint64_t)f.w * 3 * 2, (cuuint64_t)f.h * f.w * 3 * 2};
+    cuuint32_t box[3] = {(cuuint32_t)pl.patch_pitch, (cuuint32_t)pl.patch_rows, 1};
+    int rc = make_tensor_map_plain(&map_img, TFC_BF16, const_cast<void*>(w.big), 3, dims, str, box);
+    if (rc) return rc;
+  }
+  {
+    const cuuint64_t C = w.cs;
+    cuuint64_t dims[4] = {C, (cuuint64_t)f.wo, (cuuint64_t)f.ho, (cuuint64_t)f.n};
+    cuuint64_t str[3] = {C * 2, (cuuint64_t)f.wo * C * 2, (cuuint64_t)f.ho * f.wo * C * 2};
+    cuuint32_t box[4] = {64, (cuuint32_t)p.tw, (cuuint32_t)p.th, 1};
+    int rc = make_tensor_map_bf16(&map_small, const_cast<void*>(w.small), 4, dims, str, box);
+    if (rc) return rc;
+  }
+  const int grid = std::min(p.num_tiles, num_sms());
+  if (d.kh == 5) return launch_wg<5, 5>(w, map_img, map_small, q, grid, st);
+  return launch_wg<9, 9>(w, map_img, map_small, q, grid, st);
 }
 
 }  // namespace tfc

@@ -333,6 +333,8 @@ extern "C" int tfc_signal_conv2d_wgrad(const tfc_conv_desc* d, const void* d_x_b
     }
     if (!force_wmma && tfc::conv_wgrad_umma_supported(*d))
       return tfc::conv_wgrad_umma(*d, d_x_bf16, d_dy_bf16, d_dw, st);
+    if (!force_wmma && tfc::conv_thin_wgrad_supported(*d, d_x_bf16, d_dy_bf16))
+      return tfc::conv_thin_wgrad(*d, d_x_bf16, d_dy_bf16, d_dw, st);
   }
   WgradParams p{};
   p.n = d->n; p.h = d->h; p.w = d->w; p.cin = d->cin; p.ho = d->ho; p.wo = d->wo;

@@ -8,6 +8,8 @@
 //                  (IGDN: gx1 = gy * sqrt(norm) ; gnorm = 1/2 * gy * x / sqrt(norm))
 //   backward, post gx = gx1 + 2 * x * (gnorm . gamma^T)
 // The bias-like gradient d beta = column sums of gnorm uses tfc_column_sums.
+#include <cuda_bf16.h>
+
 #include <algorithm>
 
 #include "common.cuh"
@@ -72,6 +74,41 @@ gdn_train_backward_pre_kernel(const float4* __restrict__ gy, const float4* __res
     bwd1<INV>(g.w, v.w, n.w, a.w, b.w);
     gx1[i] = a;
     gnorm[i] = b;
+  }
+}
+
+// x -> bf16(x^2): the A operand of the contraction when it runs on the tcgen05 1x1 convolution
+__global__ void __launch_bounds__(kThreads)
+gdn_train_square_kernel(const float4* __restrict__ x, int64_t nvec, uint2* __restrict__ x2) {
+  for (int64_t i = blockIdx.x * (int64_t)kThreads + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * kThreads) {
+    const float4 v = __ldg(x + i);
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x * v.x, v.y * v.y);
+    const __nv_bfloat162 hi = __floats2bfloat162_rn(v.z * v.z, v.w * v.w);
+    x2[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
+  }
+}
+
+// backward, pre with a second, bfloat16 copy of gnorm (the operand of the two gradient GEMMs)
+template <bool INV>
+__global__ void __launch_bounds__(kThreads)
+gdn_train_backward_pre2_kernel(const float4* __restrict__ gy, const float4* __restrict__ x,
+                               const float4* __restrict__ norm, int64_t nvec,
+                               float4* __restrict__ gx1, float4* __restrict__ gnorm,
+                               uint2* __restrict__ gnorm_bf16) {
+  for (int64_t i = blockIdx.x * (int64_t)kThreads + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * kThreads) {
+    const float4 g = __ldg(gy + i), v = __ldg(x + i), n = __ldg(norm + i);
+    float4 a, b;
+    bwd1<INV>(g.x, v.x, n.x, a.x, b.x);
+    bwd1<INV>(g.y, v.y, n.y, a.y, b.y);
+    bwd1<INV>(g.z, v.z, n.z, a.z, b.z);
+    bwd1<INV>(g.w, v.w, n.w, a.w, b.w);
+    gx1[i] = a;
+    gnorm[i] = b;
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(b.x, b.y), hi = __floats2bfloat162_rn(b.z, b.w);
+    gnorm_bf16[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&lo),
+                               *reinterpret_cast<const uint32_t*>(&hi));
   }
 }
 
@@ -156,5 +193,45 @@ extern "C" int tfc_gdn_train_backward_post(float* d_gx, const float* d_x, const 
       reinterpret_cast<float4*>(d_gx), reinterpret_cast<const float4*>(d_x),
       reinterpret_cast<const float4*>(d_gx2), nvec);
   TFC_LAUNCHED("gdn_train_backward_post_kernel");
+  return TFC_OK;
+}
+
+extern "C" int tfc_gdn_train_square(const float* d_x, int64_t pixels, int32_t channels,
+                                    void* d_x2_bf16, void* stream) {
+  int rc = check_vec(pixels, channels, {d_x});
+  if (rc) return rc;
+  if (reinterpret_cast<uintptr_t>(d_x2_bf16) & 7)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "GDN training buffers must be 16-byte aligned");
+  const int64_t nvec = pixels * channels / 4;
+  if (nvec == 0) return TFC_OK;
+  gdn_train_square_kernel<<<grid_vec(nvec), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const float4*>(d_x), nvec, static_cast<uint2*>(d_x2_bf16));
+  TFC_LAUNCHED("gdn_train_square_kernel");
+  return TFC_OK;
+}
+
+extern "C" int tfc_gdn_train_backward_pre2(const float* d_gy, const float* d_x, const float* d_norm,
+                                           int64_t pixels, int32_t channels, int inverse,
+                                           float* d_gx1, float* d_gnorm, void* d_gnorm_bf16,
+                                           void* stream) {
+  int rc = check_vec(pixels, channels, {d_gy, d_x, d_norm, d_gx1, d_gnorm});
+  if (rc) return rc;
+  if (d_gnorm_bf16 == nullptr || (reinterpret_cast<uintptr_t>(d_gnorm_bf16) & 7))
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "GDN training buffers must be 16-byte aligned");
+  const int64_t nvec = pixels * channels / 4;
+  if (nvec == 0) return TFC_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  auto a = reinterpret_cast<const float4*>(d_gy);
+  auto b = reinterpret_cast<const float4*>(d_x);
+  auto c = reinterpret_cast<const float4*>(d_norm);
+  if (inverse)
+    gdn_train_backward_pre2_kernel<true><<<grid_vec(nvec), kThreads, 0, st>>>(
+        a, b, c, nvec, reinterpret_cast<float4*>(d_gx1), reinterpret_cast<float4*>(d_gnorm),
+        static_cast<uint2*>(d_gnorm_bf16));
+  else
+    gdn_train_backward_pre2_kernel<false><<<grid_vec(nvec), kThreads, 0, st>>>(
+        a, b, c, nvec, reinterpret_cast<float4*>(d_gx1), reinterpret_cast<float4*>(d_gnorm),
+        static_cast<uint2*>(d_gnorm_bf16));
+  TFC_LAUNCHED("gdn_train_backward_pre_kernel");
   return TFC_OK;
 }

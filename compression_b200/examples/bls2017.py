@@ -210,9 +210,12 @@ class _GdnContraction(torch.autograd.Function):
 
 
 class _GdnTrain(torch.autograd.Function):
-  """GDN / IGDN of the training graph (gdn.py:171-202): contraction and its gradients as TF32
-  GEMMs, everything around them as three elementwise CUDA passes (csrc/gdn_train.cu) instead of
-  ~12 autograd launches per layer over the largest activations of the step."""
+  """GDN / IGDN of the training graph (gdn.py:171-202): three elementwise CUDA passes
+  (csrc/gdn_train.cu) around the C x C contraction and its two gradients.  With 128 channels
+  the contraction runs on the tcgen05 kernels as a 1x1 convolution over bfloat16 operands
+  (x^2 and gnorm rounded to bfloat16, float32 accumulation: the arithmetic of the inference
+  epilogue) — norm = conv1x1(x^2, gamma), gx2 = conv1x1(gnorm, gamma^T), d gamma = the 1x1
+  filter gradient of (x^2, gnorm); other widths keep the TF32 library GEMMs."""
 
   @staticmethod
   def forward(ctx, x, beta, gamma, inverse):
@@ -220,23 +223,34 @@ class _GdnTrain(torch.autograd.Function):
     from compression_b200 import _lib
     shape, c = x.shape, x.shape[-1]
     x2d = x.reshape(-1, c).contiguous()
-    x2 = x2d * x2d
-    with _tf32_matmul():
-      nraw = x2 @ gamma
+    p = x2d.shape[0]
+    L, st = _lib.lib(), _lib.stream_ptr(x.device)
+    umma = c == 128 and x.dim() == 4 and p >= 128
+    if umma:
+      x2 = torch.empty((p, c), dtype=torch.bfloat16, device=x.device)
+      _lib.check(L.tfc_gdn_train_square(_lib.ptr(x2d), ctypes.c_int64(p), ctypes.c_int32(c),
+                                        _lib.ptr(x2), st))
+      n, h, w, _ = shape
+      nraw = train_ops._conv_raw(x2.view(shape), gamma.view(1, 1, c, c), None, 1, 1, 1, 1, 0, 0,
+                                 h, w, torch.float32).view(p, c)
+    else:
+      x2 = x2d * x2d
+      with _tf32_matmul():
+        nraw = x2 @ gamma
     y = torch.empty_like(x2d)
     b = beta.detach().float().contiguous()
-    _lib.check(_lib.lib().tfc_gdn_train_forward(
-        _lib.ptr(x2d), _lib.ptr(nraw), _lib.ptr(b), ctypes.c_int64(x2d.shape[0]),
-        ctypes.c_int32(c), int(bool(inverse)), _lib.ptr(y), _lib.ptr(nraw),
-        _lib.stream_ptr(x.device)))
+    _lib.check(L.tfc_gdn_train_forward(
+        _lib.ptr(x2d), _lib.ptr(nraw), _lib.ptr(b), ctypes.c_int64(p), ctypes.c_int32(c),
+        int(bool(inverse)), _lib.ptr(y), _lib.ptr(nraw), st))
     ctx.save_for_backward(x2d, x2, nraw, gamma)
-    ctx.inverse, ctx.shape = bool(inverse), shape
+    ctx.inverse, ctx.shape, ctx.umma = bool(inverse), shape, umma
     return y.reshape(shape)
 
   @staticmethod
   def backward(ctx, gy):
     import ctypes
     from compression_b200 import _lib
+    from compression_b200.python.layers.signal_conv import ConvDesc
     x2d, x2, norm, gamma = ctx.saved_tensors
     p, c = x2d.shape
     gy2d = gy.reshape(p, c).float().contiguous()
@@ -244,12 +258,27 @@ class _GdnTrain(torch.autograd.Function):
     gnorm = torch.empty_like(x2d)
     L = _lib.lib()
     st = _lib.stream_ptr(x2d.device)
-    _lib.check(L.tfc_gdn_train_backward_pre(
-        _lib.ptr(gy2d), _lib.ptr(x2d), _lib.ptr(norm), ctypes.c_int64(p), ctypes.c_int32(c),
-        int(ctx.inverse), _lib.ptr(gx), _lib.ptr(gnorm), st))
-    with _tf32_matmul():
-      gx2 = gnorm @ gamma.t()
-      ggamma = x2.t() @ gnorm
+    if ctx.umma:
+      n, h, w, _ = ctx.shape
+      gnb = torch.empty((p, c), dtype=torch.bfloat16, device=x2d.device)
+      _lib.check(L.tfc_gdn_train_backward_pre2(
+          _lib.ptr(gy2d), _lib.ptr(x2d), _lib.ptr(norm), ctypes.c_int64(p), ctypes.c_int32(c),
+          int(ctx.inverse), _lib.ptr(gx), _lib.ptr(gnorm), _lib.ptr(gnb), st))
+      gx2 = train_ops._conv_raw(gnb.view(ctx.shape), gamma.t().contiguous().view(1, 1, c, c), None,
+                                1, 1, 1, 1, 0, 0, h, w, torch.float32).view(p, c)
+      ggamma = torch.empty((1, 1, c, c), dtype=torch.float32, device=x2d.device)
+      d = ConvDesc(n=n, h=h, w=w, cin=c, ho=h, wo=w, cout=c, kh=1, kw=1, sd=1, su=1, pad_top=0,
+                   pad_left=0, act=0, in_dtype=1, out_dtype=0, impl=0, flags=0)
+      _lib.check(L.tfc_signal_conv2d_wgrad(ctypes.byref(d), _lib.ptr(x2), _lib.ptr(gnb),
+                                           _lib.ptr(ggamma), st))
+      ggamma = ggamma.view(c, c)
+    else:
+      _lib.check(L.tfc_gdn_train_backward_pre(
+          _lib.ptr(gy2d), _lib.ptr(x2d), _lib.ptr(norm), ctypes.c_int64(p), ctypes.c_int32(c),
+          int(ctx.inverse), _lib.ptr(gx), _lib.ptr(gnorm), st))
+      with _tf32_matmul():
+        gx2 = gnorm @ gamma.t()
+        ggamma = x2.t() @ gnorm
     _lib.check(L.tfc_gdn_train_backward_post(
         _lib.ptr(gx), _lib.ptr(x2d), _lib.ptr(gx2), ctypes.c_int64(p), ctypes.c_int32(c), st))
     gbeta = torch.empty((c,), dtype=torch.float32, device=x2d.device)

@@ -186,9 +186,16 @@ class Pipeline(object):
     self.streams = [torch.cuda.Stream(device=model.device) for _ in range(n_coder)]
     self.stage = None
     if stage_streams and self.depth > 1:
-      prio = -1 if stage_priority else 0
-      mk = lambda n: [torch.cuda.Stream(device=model.device, priority=prio) for _ in range(n)]
-      self.stage = {"analysis": mk(3), "hyper": mk(2), "synthesis": mk(3)}
+      # stage_priority: True = all transform stages one level above the coder streams; a triple
+      # gives the levels of (analysis, hyper-synthesis, synthesis) separately (0 = default pool,
+      # -1, -2, -3 = higher; torch keeps one pool of 32 streams per level)
+      if isinstance(stage_priority, (tuple, list)):
+        pa, ph, ps = (int(v) for v in stage_priority)
+      else:
+        pa = ph = ps = -1 if stage_priority else 0
+      mk = lambda n, prio: [torch.cuda.Stream(device=model.device, priority=prio)
+                            for _ in range(n)]
+      self.stage = {"analysis": mk(3, pa), "hyper": mk(2, ph), "synthesis": mk(3, ps)}
     self._lib = _lib
     self.tiles_per_cta = int(tiles_per_cta) if self.depth > 1 else 0
     self.pack = int(coder_streams_per_cta) if self.depth > 1 else 0

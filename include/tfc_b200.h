@@ -367,6 +367,16 @@ int tfc_gdn_train_backward_pre(const float* d_gy, const float* d_x, const float*
                                float* d_gnorm, void* stream);
 int tfc_gdn_train_backward_post(float* d_gx, const float* d_x, const float* d_gx2, int64_t pixels,
                                 int32_t channels, void* stream);
+/* The same passes for a caller that runs the contraction and its two gradients as tcgen05 1x1
+ * convolutions (tfc_signal_conv2d / tfc_signal_conv2d_wgrad on bfloat16 operands, the arithmetic
+ * of the inference epilogue) instead of float32 library GEMMs:
+ *   square:        d_x2_bf16 = bfloat16(x * x)
+ *   backward_pre2: as backward_pre, plus a bfloat16 copy of gnorm in d_gnorm_bf16 */
+int tfc_gdn_train_square(const float* d_x, int64_t pixels, int32_t channels, void* d_x2_bf16,
+                         void* stream);
+int tfc_gdn_train_backward_pre2(const float* d_gy, const float* d_x, const float* d_norm,
+                                int64_t pixels, int32_t channels, int inverse, float* d_gx1,
+                                float* d_gnorm, void* d_gnorm_bf16, void* stream);
 
 /* Stand-alone GDN / IGDN on a channels_last tensor of `pixels` x `channels` (gdn.py:171-206). */
 int tfc_gdn(const void* d_x, int64_t pixels, int32_t channels, const float* d_beta,

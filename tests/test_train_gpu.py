@@ -147,10 +147,10 @@ def test_training_step_gradients_and_descent(tfc):
   ref = _ref_losses(trainer, x, noise)
   ref.backward()
   want = trainer.main.grad.clone()
-  assert abs(float(out["loss"]) - float(ref)) <= 2e-2 * abs(float(ref))
+  assert abs(float(out["loss"]) - float(ref)) <= 1e-3 * abs(float(ref))
   cos = torch.dot(got, want) / (got.norm() * want.norm())
-  assert cos > 0.995, float(cos)
-  assert (got - want).norm() <= 0.1 * want.norm()
+  assert cos > 0.9995, float(cos)                  # measured 1.0000 (relative L2 error 5e-4)
+  assert (got - want).norm() <= 0.01 * want.norm()
   # a few steps on a fixed batch: the R-D loss goes down, the aux loss too, tables stay valid
   first = trainer.step(x, noise)
   for _ in range(30):
