@@ -338,7 +338,7 @@ class SignalConv2D(object):
       if x.dtype == torch.uint8 and path != 4:
         scale_before, d.in_dtype = True, _dtype_code(torch.float32)
         path = int(L.tfc_signal_conv2d_path(ctypes.byref(d)))
-      if out_dtype == torch.uint8 and (path != 3 or post is not None):
+      if out_dtype == torch.uint8 and (path not in (3, 6) or post is not None):
         quantize_after, d.out_dtype = True, _dtype_code(torch.float32)
         path = int(L.tfc_signal_conv2d_path(ctypes.byref(d)))
       need = int(L.tfc_signal_conv2d_workspace(ctypes.byref(d)))

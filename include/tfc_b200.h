@@ -320,7 +320,8 @@ typedef struct {
 /* Which kernel tfc_signal_conv2d will run for this descriptor (it depends on in_dtype and on
  * h % sd / w % sd, not only on the layer): 0 CUDA-core tiled kernel, 1 tcgen05 implicit GEMM,
  * 2 space-to-depth + tcgen05, 3 scatter GEMM (thin output), 4 software im2col + tcgen05 (thin
- * input), 5 zero-extended copy + tcgen05 implicit GEMM; -1 for an invalid descriptor.  Each path
+ * input), 5 zero-extended copy + tcgen05 implicit GEMM, 6 sub-pixel correlation + depth-to-space (thin
+ * output, transposed, more than 128 scatter columns); -1 for an invalid descriptor.  Each path
  * keeps its own weight layout at the start of the workspace, and path 0 uses the workspace as
  * plain scratch: TFC_CONV_WEIGHTS_STAGED is only valid when the previous call on the same
  * workspace took the same non-zero path with the same weights. */

@@ -608,8 +608,52 @@ def test_entropy_models_training_true_is_differentiable(tfc):
   assert float(y2.grad.abs().sum()) > 0 and float(sigma.grad.abs().sum()) > 0
 
 
-@pytest.mark.parametrize("corr,sd,su,act", [(True, 2, 1, "gdn"), (False, 1, 2, "igdn"),
-                                            (True, 1, 1, "relu"), (True, 2, 1, None)])
+@pytest.mark.parametrize("k,su,corr,act", [(9, 4, False, None), (9, 4, True, "relu"),
+                                           (5, 4, False, None), (7, 3, False, None),
+                                           (9, 2, False, None)])
+def test_sub_pixel_path_matches_oracle(tfc, k, su, corr, act):
+  """Thin-output transposed layers whose kh * kw * cout exceeds the scatter kernel's 128 columns
+  (the 9x9 stride-4 last synthesis layer of bls2017) run as a stride-1 correlation with
+  su * su * cout output channels + depth-to-space (kernel path 6): exact integer-valued operands
+  (every product and sum is exact in bfloat16 x bfloat16 -> float32), so the result must EQUAL
+  the numpy oracle, for float32 / bfloat16 / uint8 outputs, non-square images and batch > 1."""
+  import ctypes
+  from compression_b200 import _lib
+  from compression_b200.python.layers.signal_conv import ConvDesc
+  rng = np.random.default_rng(77)
+  cin, cout = 128, 3
+  kern = (rng.integers(-4, 5, size=(k, k, cin, cout)) / 8.0).astype(np.float32)
+  b = (rng.integers(-8, 9, size=cout) / 4.0).astype(np.float32)
+  layer = tfc.SignalConv2D(cout, (k, k), corr=corr, strides_up=su, padding="same_zeros",
+                           use_bias=True, activation=torch.relu if act == "relu" else None,
+                           kernel_parameterizer=None, kernel_initializer=_static(kern),
+                           bias_initializer=_static(b))
+  layer.build(cin, "cuda")
+  for n, h, w in ((2, 16, 24), (3, 9, 5)):
+    x = torch.from_numpy(rng.integers(-2, 3, size=(n, h, w, cin)).astype(np.float32)).cuda()
+    xb = x.to(torch.bfloat16)
+    want = tfc_np.signal_conv2d(x.cpu().numpy(), kern, b, corr, 1, su, "same_zeros")
+    want = torch.relu(want).numpy() if act == "relu" else want.numpy()
+    got = layer(xb, out_dtype=torch.float32)
+    assert got.shape == (n, h * su, w * su, cout)
+    np.testing.assert_array_equal(got.cpu().numpy(), want)
+    got16 = layer(xb, out_dtype=torch.bfloat16)
+    assert torch.equal(got16, torch.from_numpy(want).to(torch.bfloat16).cuda())
+  # the path really is 6 for the bls2017 shape and the uint8 image comes out of it quantised
+  d = ConvDesc(n=2, h=16, w=24, cin=cin, ho=16 * 4, wo=24 * 4, cout=3, kh=9, kw=9, sd=1, su=4,
+               pad_top=4, pad_left=4, act=0, in_dtype=1, out_dtype=0, impl=0, flags=0)
+  assert _lib.lib().tfc_signal_conv2d_path(ctypes.byref(d)) == 6
+  if k == 9 and su == 4 and act is None:
+    small = tfc.SignalConv2D(cout, (k, k), corr=corr, strides_up=su, padding="same_zeros",
+                             use_bias=True, kernel_parameterizer=None,
+                             kernel_initializer=_static(kern / 64), bias_initializer=_static(b / 8 + .5))
+    small.build(cin, "cuda")
+    y = small(xb, out_dtype=torch.float32)
+    y8 = small(xb, out_dtype=torch.uint8)
+    assert y8.dtype == torch.uint8
+    assert torch.equal(y8, torch.clamp(torch.round(y * 255), 0, 255).to(torch.uint8))
+
+
 def test_thin_conv_pipelined_epilogue_equals_default():
   """conv_thin_kernel's software-pipelined GDN epilogue (an experiment behind debug bit 32:
   setmaxnreg, two tiles in flight, y stored from registers) computes exactly what the default
@@ -633,6 +677,8 @@ def test_thin_conv_pipelined_epilogue_equals_default():
       assert torch.equal(got, want)
 
 
+@pytest.mark.parametrize("corr,sd,su,act", [(True, 2, 1, "gdn"), (False, 1, 2, "igdn"),
+                                            (True, 1, 1, "relu"), (True, 2, 1, None)])
 def test_cta_pair_conv_equals_single_cta(tfc, corr, sd, su, act):
   """TFC_CFG_CONV_PAIR: the implicit GEMM on CTA pairs (tcgen05.mma.cta_group::2, M = 256 over
   two adjacent tiles, each CTA holding half of the weight tile) sums the same products in the
