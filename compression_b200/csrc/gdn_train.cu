@@ -29,11 +29,22 @@ __device__ __forceinline__ float fwd1(float x, float n) {
   return INV ? x * sqrtf(n) : x * rsqrtf(n);
 }
 
-template <bool INV>
+__device__ __forceinline__ uint2 pack4_bf16(float a, float b, float c, float d) {
+  const __nv_bfloat162 lo = __floats2bfloat162_rn(a, b), hi = __floats2bfloat162_rn(c, d);
+  return make_uint2(*reinterpret_cast<const uint32_t*>(&lo), *reinterpret_cast<const uint32_t*>(&hi));
+}
+__device__ __forceinline__ float4 unpack4_bf16(uint2 v) {
+  const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&v.x));
+  const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&v.y));
+  return make_float4(lo.x, lo.y, hi.x, hi.y);
+}
+
+// YB16: y leaves as bfloat16 (the next layer's convolution reads bfloat16: no cast pass)
+template <bool INV, bool YB16>
 __global__ void __launch_bounds__(kThreads)
 gdn_train_forward_kernel(const float4* __restrict__ x, const float4* nraw,
                          const float4* __restrict__ beta, int64_t nvec, int cvec,
-                         float4* __restrict__ y, float4* norm) {   // norm may alias nraw
+                         void* __restrict__ y, float4* norm) {   // norm may alias nraw
   for (int64_t i = blockIdx.x * (int64_t)kThreads + threadIdx.x; i < nvec;
        i += (int64_t)gridDim.x * kThreads) {
     const float4 b = __ldg(beta + (int)(i % cvec));
@@ -41,8 +52,10 @@ gdn_train_forward_kernel(const float4* __restrict__ x, const float4* nraw,
     float4 n = nraw[i];
     n.x += b.x; n.y += b.y; n.z += b.z; n.w += b.w;
     norm[i] = n;
-    y[i] = make_float4(fwd1<INV>(v.x, n.x), fwd1<INV>(v.y, n.y), fwd1<INV>(v.z, n.z),
-                       fwd1<INV>(v.w, n.w));
+    const float4 r = make_float4(fwd1<INV>(v.x, n.x), fwd1<INV>(v.y, n.y), fwd1<INV>(v.z, n.z),
+                                 fwd1<INV>(v.w, n.w));
+    if (YB16) static_cast<uint2*>(y)[i] = pack4_bf16(r.x, r.y, r.z, r.w);
+    else static_cast<float4*>(y)[i] = r;
   }
 }
 
@@ -90,15 +103,17 @@ gdn_train_square_kernel(const float4* __restrict__ x, int64_t nvec, uint2* __res
 }
 
 // backward, pre with a second, bfloat16 copy of gnorm (the operand of the two gradient GEMMs)
-template <bool INV>
+template <bool INV, bool GB16>
 __global__ void __launch_bounds__(kThreads)
-gdn_train_backward_pre2_kernel(const float4* __restrict__ gy, const float4* __restrict__ x,
+gdn_train_backward_pre2_kernel(const void* __restrict__ gy, const float4* __restrict__ x,
                                const float4* __restrict__ norm, int64_t nvec,
                                float4* __restrict__ gx1, float4* __restrict__ gnorm,
                                uint2* __restrict__ gnorm_bf16) {
   for (int64_t i = blockIdx.x * (int64_t)kThreads + threadIdx.x; i < nvec;
        i += (int64_t)gridDim.x * kThreads) {
-    const float4 g = __ldg(gy + i), v = __ldg(x + i), n = __ldg(norm + i);
+    const float4 g = GB16 ? unpack4_bf16(__ldg(static_cast<const uint2*>(gy) + i))
+                          : __ldg(static_cast<const float4*>(gy) + i);
+    const float4 v = __ldg(x + i), n = __ldg(norm + i);
     float4 a, b;
     bwd1<INV>(g.x, v.x, n.x, a.x, b.x);
     bwd1<INV>(g.y, v.y, n.y, a.y, b.y);
@@ -106,9 +121,7 @@ gdn_train_backward_pre2_kernel(const float4* __restrict__ gy, const float4* __re
     bwd1<INV>(g.w, v.w, n.w, a.w, b.w);
     gx1[i] = a;
     gnorm[i] = b;
-    const __nv_bfloat162 lo = __floats2bfloat162_rn(b.x, b.y), hi = __floats2bfloat162_rn(b.z, b.w);
-    gnorm_bf16[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&lo),
-                               *reinterpret_cast<const uint32_t*>(&hi));
+    gnorm_bf16[i] = pack4_bf16(b.x, b.y, b.z, b.w);
   }
 }
 
@@ -150,13 +163,35 @@ extern "C" int tfc_gdn_train_forward(const float* d_x, const float* d_x2_gamma,
   auto b = reinterpret_cast<const float4*>(d_x2_gamma);
   auto c = reinterpret_cast<const float4*>(d_beta);
   if (inverse)
-    gdn_train_forward_kernel<true><<<grid_vec(nvec), kThreads, 0, st>>>(
-        a, b, c, nvec, channels / 4, reinterpret_cast<float4*>(d_y),
-        reinterpret_cast<float4*>(d_norm));
+    gdn_train_forward_kernel<true, false><<<grid_vec(nvec), kThreads, 0, st>>>(
+        a, b, c, nvec, channels / 4, d_y, reinterpret_cast<float4*>(d_norm));
   else
-    gdn_train_forward_kernel<false><<<grid_vec(nvec), kThreads, 0, st>>>(
-        a, b, c, nvec, channels / 4, reinterpret_cast<float4*>(d_y),
-        reinterpret_cast<float4*>(d_norm));
+    gdn_train_forward_kernel<false, false><<<grid_vec(nvec), kThreads, 0, st>>>(
+        a, b, c, nvec, channels / 4, d_y, reinterpret_cast<float4*>(d_norm));
+  TFC_LAUNCHED("gdn_train_forward_kernel");
+  return TFC_OK;
+}
+
+extern "C" int tfc_gdn_train_forward_bf16(const float* d_x, const float* d_x2_gamma,
+                                          const float* d_beta, int64_t pixels, int32_t channels,
+                                          int inverse, void* d_y_bf16, float* d_norm,
+                                          void* stream) {
+  int rc = check_vec(pixels, channels, {d_x, d_x2_gamma, d_beta, d_norm});
+  if (rc) return rc;
+  if (reinterpret_cast<uintptr_t>(d_y_bf16) & 7)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "GDN training buffers must be 16-byte aligned");
+  const int64_t nvec = pixels * channels / 4;
+  if (nvec == 0) return TFC_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  auto a = reinterpret_cast<const float4*>(d_x);
+  auto b = reinterpret_cast<const float4*>(d_x2_gamma);
+  auto c = reinterpret_cast<const float4*>(d_beta);
+  if (inverse)
+    gdn_train_forward_kernel<true, true><<<grid_vec(nvec), kThreads, 0, st>>>(
+        a, b, c, nvec, channels / 4, d_y_bf16, reinterpret_cast<float4*>(d_norm));
+  else
+    gdn_train_forward_kernel<false, true><<<grid_vec(nvec), kThreads, 0, st>>>(
+        a, b, c, nvec, channels / 4, d_y_bf16, reinterpret_cast<float4*>(d_norm));
   TFC_LAUNCHED("gdn_train_forward_kernel");
   return TFC_OK;
 }
@@ -210,10 +245,12 @@ extern "C" int tfc_gdn_train_square(const float* d_x, int64_t pixels, int32_t ch
   return TFC_OK;
 }
 
-extern "C" int tfc_gdn_train_backward_pre2(const float* d_gy, const float* d_x, const float* d_norm,
-                                           int64_t pixels, int32_t channels, int inverse,
-                                           float* d_gx1, float* d_gnorm, void* d_gnorm_bf16,
-                                           void* stream) {
+extern "C" int tfc_gdn_train_backward_pre2(const void* d_gy, int gy_dtype, const float* d_x,
+                                           const float* d_norm, int64_t pixels, int32_t channels,
+                                           int inverse, float* d_gx1, float* d_gnorm,
+                                           void* d_gnorm_bf16, void* stream) {
+  if (gy_dtype != TFC_F32 && gy_dtype != TFC_BF16)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "gy must be float32 or bfloat16");
   int rc = check_vec(pixels, channels, {d_gy, d_x, d_norm, d_gx1, d_gnorm});
   if (rc) return rc;
   if (d_gnorm_bf16 == nullptr || (reinterpret_cast<uintptr_t>(d_gnorm_bf16) & 7))
@@ -221,17 +258,17 @@ extern "C" int tfc_gdn_train_backward_pre2(const float* d_gy, const float* d_x, 
   const int64_t nvec = pixels * channels / 4;
   if (nvec == 0) return TFC_OK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  auto a = reinterpret_cast<const float4*>(d_gy);
   auto b = reinterpret_cast<const float4*>(d_x);
   auto c = reinterpret_cast<const float4*>(d_norm);
-  if (inverse)
-    gdn_train_backward_pre2_kernel<true><<<grid_vec(nvec), kThreads, 0, st>>>(
-        a, b, c, nvec, reinterpret_cast<float4*>(d_gx1), reinterpret_cast<float4*>(d_gnorm),
-        static_cast<uint2*>(d_gnorm_bf16));
-  else
-    gdn_train_backward_pre2_kernel<false><<<grid_vec(nvec), kThreads, 0, st>>>(
-        a, b, c, nvec, reinterpret_cast<float4*>(d_gx1), reinterpret_cast<float4*>(d_gnorm),
-        static_cast<uint2*>(d_gnorm_bf16));
+  auto o1 = reinterpret_cast<float4*>(d_gx1);
+  auto o2 = reinterpret_cast<float4*>(d_gnorm);
+  auto o3 = static_cast<uint2*>(d_gnorm_bf16);
+  const int g = grid_vec(nvec);
+  const bool b16 = gy_dtype == TFC_BF16;
+  if (inverse && b16) gdn_train_backward_pre2_kernel<true, true><<<g, kThreads, 0, st>>>(d_gy, b, c, nvec, o1, o2, o3);
+  else if (inverse) gdn_train_backward_pre2_kernel<true, false><<<g, kThreads, 0, st>>>(d_gy, b, c, nvec, o1, o2, o3);
+  else if (b16) gdn_train_backward_pre2_kernel<false, true><<<g, kThreads, 0, st>>>(d_gy, b, c, nvec, o1, o2, o3);
+  else gdn_train_backward_pre2_kernel<false, false><<<g, kThreads, 0, st>>>(d_gy, b, c, nvec, o1, o2, o3);
   TFC_LAUNCHED("gdn_train_backward_pre_kernel");
   return TFC_OK;
 }

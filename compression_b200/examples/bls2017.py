@@ -237,11 +237,18 @@ class _GdnTrain(torch.autograd.Function):
       x2 = x2d * x2d
       with _tf32_matmul():
         nraw = x2 @ gamma
-    y = torch.empty_like(x2d)
     b = beta.detach().float().contiguous()
-    _lib.check(L.tfc_gdn_train_forward(
-        _lib.ptr(x2d), _lib.ptr(nraw), _lib.ptr(b), ctypes.c_int64(p), ctypes.c_int32(c),
-        int(bool(inverse)), _lib.ptr(y), _lib.ptr(nraw), st))
+    if umma:
+      # y feeds the next layer's convolution, which reads bfloat16: written as such
+      y = torch.empty((p, c), dtype=torch.bfloat16, device=x.device)
+      _lib.check(L.tfc_gdn_train_forward_bf16(
+          _lib.ptr(x2d), _lib.ptr(nraw), _lib.ptr(b), ctypes.c_int64(p), ctypes.c_int32(c),
+          int(bool(inverse)), _lib.ptr(y), _lib.ptr(nraw), st))
+    else:
+      y = torch.empty_like(x2d)
+      _lib.check(L.tfc_gdn_train_forward(
+          _lib.ptr(x2d), _lib.ptr(nraw), _lib.ptr(b), ctypes.c_int64(p), ctypes.c_int32(c),
+          int(bool(inverse)), _lib.ptr(y), _lib.ptr(nraw), st))
     ctx.save_for_backward(x2d, x2, nraw, gamma)
     ctx.inverse, ctx.shape, ctx.umma = bool(inverse), shape, umma
     return y.reshape(shape)
@@ -253,17 +260,21 @@ class _GdnTrain(torch.autograd.Function):
     from compression_b200.python.layers.signal_conv import ConvDesc
     x2d, x2, norm, gamma = ctx.saved_tensors
     p, c = x2d.shape
-    gy2d = gy.reshape(p, c).float().contiguous()
     gx = torch.empty_like(x2d)
     gnorm = torch.empty_like(x2d)
     L = _lib.lib()
     st = _lib.stream_ptr(x2d.device)
     if ctx.umma:
       n, h, w, _ = ctx.shape
+      gy2d = gy.reshape(p, c)
+      if gy2d.dtype not in (torch.float32, torch.bfloat16):
+        gy2d = gy2d.float()
+      gy2d = gy2d.contiguous()
       gnb = torch.empty((p, c), dtype=torch.bfloat16, device=x2d.device)
       _lib.check(L.tfc_gdn_train_backward_pre2(
-          _lib.ptr(gy2d), _lib.ptr(x2d), _lib.ptr(norm), ctypes.c_int64(p), ctypes.c_int32(c),
-          int(ctx.inverse), _lib.ptr(gx), _lib.ptr(gnorm), _lib.ptr(gnb), st))
+          _lib.ptr(gy2d), 1 if gy2d.dtype == torch.bfloat16 else 0, _lib.ptr(x2d), _lib.ptr(norm),
+          ctypes.c_int64(p), ctypes.c_int32(c), int(ctx.inverse), _lib.ptr(gx), _lib.ptr(gnorm),
+          _lib.ptr(gnb), st))
       gx2 = train_ops._conv_raw(gnb.view(ctx.shape), gamma.t().contiguous().view(1, 1, c, c), None,
                                 1, 1, 1, 1, 0, 0, h, w, torch.float32).view(p, c)
       ggamma = torch.empty((1, 1, c, c), dtype=torch.float32, device=x2d.device)
@@ -273,6 +284,7 @@ class _GdnTrain(torch.autograd.Function):
                                            _lib.ptr(ggamma), st))
       ggamma = ggamma.view(c, c)
     else:
+      gy2d = gy.reshape(p, c).float().contiguous()
       _lib.check(L.tfc_gdn_train_backward_pre(
           _lib.ptr(gy2d), _lib.ptr(x2d), _lib.ptr(norm), ctypes.c_int64(p), ctypes.c_int32(c),
           int(ctx.inverse), _lib.ptr(gx), _lib.ptr(gnorm), st))

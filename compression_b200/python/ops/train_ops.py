@@ -72,8 +72,9 @@ class _SignalConv(torch.autograd.Function):
     dx = dw = db = None
     if ctx.needs_input_grad[0]:
       wt = torch.flip(w, dims=(0, 1)).transpose(2, 3).contiguous()     # [kh,kw,cout,cin]
-      dx = _conv_raw(dy, wt, None, kh, kw, su, sd, kh - 1 - pt, kw - 1 - pl, h, wd,
-                     torch.float32).to(x.dtype)
+      # the gradient leaves the kernel in the dtype of the activation it belongs to (bfloat16
+      # between the layers of a transform): no cast pass after it
+      dx = _conv_raw(dy, wt, None, kh, kw, su, sd, kh - 1 - pt, kw - 1 - pl, h, wd, x.dtype)
     if ctx.needs_input_grad[1]:
       xb = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
       xb = xb.contiguous()

@@ -372,12 +372,17 @@ int tfc_gdn_train_backward_post(float* d_gx, const float* d_x, const float* d_gx
  * convolutions (tfc_signal_conv2d / tfc_signal_conv2d_wgrad on bfloat16 operands, the arithmetic
  * of the inference epilogue) instead of float32 library GEMMs:
  *   square:        d_x2_bf16 = bfloat16(x * x)
- *   backward_pre2: as backward_pre, plus a bfloat16 copy of gnorm in d_gnorm_bf16 */
+ *   forward_bf16:  as forward, y written as bfloat16 (what the next layer's convolution reads)
+ *   backward_pre2: as backward_pre, gy float32 or bfloat16 (gy_dtype: tfc_dtype), plus a
+ *                  bfloat16 copy of gnorm in d_gnorm_bf16 */
 int tfc_gdn_train_square(const float* d_x, int64_t pixels, int32_t channels, void* d_x2_bf16,
                          void* stream);
-int tfc_gdn_train_backward_pre2(const float* d_gy, const float* d_x, const float* d_norm,
-                                int64_t pixels, int32_t channels, int inverse, float* d_gx1,
-                                float* d_gnorm, void* d_gnorm_bf16, void* stream);
+int tfc_gdn_train_forward_bf16(const float* d_x, const float* d_x2_gamma, const float* d_beta,
+                               int64_t pixels, int32_t channels, int inverse, void* d_y_bf16,
+                               float* d_norm, void* stream);
+int tfc_gdn_train_backward_pre2(const void* d_gy, int gy_dtype, const float* d_x,
+                                const float* d_norm, int64_t pixels, int32_t channels, int inverse,
+                                float* d_gx1, float* d_gnorm, void* d_gnorm_bf16, void* stream);
 
 /* Stand-alone GDN / IGDN on a channels_last tensor of `pixels` x `channels` (gdn.py:171-206). */
 int tfc_gdn(const void* d_x, int64_t pixels, int32_t channels, const float* d_beta,

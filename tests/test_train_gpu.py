@@ -117,7 +117,11 @@ def _ref_losses(trainer, x, noise):
       t = _ref_conv(t, layer.kernel, layer.bias, layer.corr, layer.strides_down[0],
                     layer.strides_up[0])
       if isinstance(layer.activation, gdn.GDN):
-        t = trainer._gdn(layer.activation, t)
+        act = layer.activation
+        beta = act.beta_parameterizer(act.reparam_beta)
+        gamma = act.gamma_parameterizer(act.reparam_gamma).float()
+        norm = ((t * t).reshape(-1, t.shape[-1]) @ gamma + beta).reshape(t.shape)   # gdn.py:183-202
+        t = t * (torch.sqrt(norm) if act.inverse else torch.rsqrt(norm))
     return t
 
   y = run(model.analysis_transform, x)
