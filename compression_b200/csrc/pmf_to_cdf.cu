@@ -286,21 +286,27 @@ __device__ void rebalance_warp(tfc::SortItem* it, uint16_t* lpos, uint16_t* rasc
   __syncwarp();
 }
 
-__global__ void pmf_to_cdf_warp_kernel(const float* __restrict__ pmf, int64_t rows, int n,
-                                       int precision, int32_t* __restrict__ cdf) {
+// `lens` (ragged form): row r has lens[r] entries (clamped to [2, nmax]) at pmf + r * pmf_stride
+// and its cdf goes to cdf + r * cdf_stride, zero-filled behind its lens[r] + 1 entries; without
+// `lens` every row has nmax entries and the strides are nmax / nmax + 1.
+__global__ void pmf_to_cdf_warp_kernel(const float* __restrict__ pmf, int64_t rows, int nmax,
+                                       int precision, int32_t* __restrict__ cdf,
+                                       const int32_t* __restrict__ lens, int pmf_stride,
+                                       int cdf_stride) {
   extern __shared__ __align__(16) uint8_t smem_rows[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpc = blockDim.x >> 5;
   const int64_t r = (int64_t)blockIdx.x * wpc + warp;
   if (r >= rows) return;
-  const int npad = (n + 3) & ~3;
+  const int n = lens ? min(max(__ldg(lens + r), 2), nmax) : nmax;
+  const int npad = (nmax + 3) & ~3;
   uint8_t* mine = smem_rows + (size_t)warp * npad * kWarpRowBytesPerEntry;
   tfc::SortItem* it = reinterpret_cast<tfc::SortItem*>(mine);
   float* sp = reinterpret_cast<float*>(it + npad);
   int32_t* cnt = reinterpret_cast<int32_t*>(sp + npad);
   uint16_t* lpos = reinterpret_cast<uint16_t*>(cnt);
   uint16_t* rasc = lpos + npad;
-  const float* p = pmf + r * n;
-  int32_t* c = cdf + r * (int64_t)(n + 1);
+  const float* p = pmf + r * (int64_t)pmf_stride;
+  int32_t* c = cdf + r * (int64_t)cdf_stride;
   const int32_t total = 1 << precision;
   int32_t sum = 0;
   for (int i = lane; i < n; i += 32) {
@@ -328,6 +334,7 @@ __global__ void pmf_to_cdf_warp_kernel(const float* __restrict__ pmf, int64_t ro
     if (i < n) c[i + 1] = run + v;
     run += __shfl_sync(0xFFFFFFFFu, v, 31);
   }
+  for (int i = n + 1 + lane; i < cdf_stride; i += 32) c[i] = 0;
 }
 
 int ensure_lut() {
@@ -392,7 +399,7 @@ extern "C" int tfc_pmf_to_quantized_cdf(const float* d_pmf, int64_t rows, int32_
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     }
     pmf_to_cdf_warp_kernel<<<(unsigned)((rows + wpc - 1) / wpc), wpc * 32, smem, st>>>(
-        d_pmf, rows, n, precision, d_cdf);
+        d_pmf, rows, n, precision, d_cdf, nullptr, n, n + 1);
     TFC_LAUNCHED("pmf_to_cdf_kernel");
     return TFC_OK;
   }
@@ -400,6 +407,44 @@ extern "C" int tfc_pmf_to_quantized_cdf(const float* d_pmf, int64_t rows, int32_
   const int threads = 32;
   pmf_to_cdf_kernel<<<(unsigned)((rows + threads - 1) / threads), threads, 0, st>>>(
       d_pmf, rows, n, precision, d_cdf, static_cast<tfc::SortItem*>(d_workspace), stride);
+  TFC_LAUNCHED("pmf_to_cdf_kernel");
+  return TFC_OK;
+}
+
+
+// Rows of different lengths in one launch (the EntropyBottleneck table rebuild of a training
+// step, entropy_models.py:131-146: row r is pmf[r, :len_r] ++ [tail_r], zero-padded to the longest
+// row): the lengths stay on the device, so the caller neither reads them back nor groups rows.
+extern "C" int tfc_pmf_to_quantized_cdf_ragged(const float* d_pmf, int64_t rows,
+                                               int32_t pmf_stride, const int32_t* d_n,
+                                               int32_t max_n, int precision, int32_t* d_cdf,
+                                               int32_t cdf_stride, void* stream) {
+  if (precision < 1 || precision > 16)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT, "`precision` must be in [1, 16]: %d", precision);
+  if (max_n < 2 || pmf_stride < max_n || cdf_stride < max_n + 1 || d_n == nullptr)
+    return tfc::fail(TFC_ERR_INVALID_ARGUMENT,
+                     "ragged pmf: need max_n >= 2, pmf_stride >= max_n, cdf_stride >= max_n + 1");
+  if (rows <= 0) return TFC_OK;
+  const size_t row_bytes = (size_t)((max_n + 3) & ~3) * kWarpRowBytesPerEntry;
+  if (row_bytes > 200 * 1024)
+    return tfc::fail(TFC_ERR_UNIMPLEMENTED, "ragged pmf rows of up to %d entries", max_n);
+  int rc = ensure_lut();
+  if (rc) return rc;
+  int wpc = 1;
+  size_t best = 0;
+  for (int w : {4, 2, 1}) {
+    if (w * row_bytes > 200 * 1024) continue;
+    const size_t per_sm = std::min<size_t>(32 / w, (227 * 1024) / (w * row_bytes + 1024)) * w;
+    if (per_sm > best) { best = per_sm; wpc = w; }
+  }
+  static tfc::PerDeviceOnce attr;
+  if (attr.first()) {
+    TFC_CUDA(cudaFuncSetAttribute(pmf_to_cdf_warp_kernel,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  }
+  pmf_to_cdf_warp_kernel<<<(unsigned)((rows + wpc - 1) / wpc), wpc * 32, wpc * row_bytes,
+                           static_cast<cudaStream_t>(stream)>>>(
+      d_pmf, rows, max_n, precision, d_cdf, d_n, pmf_stride, cdf_stride);
   TFC_LAUNCHED("pmf_to_cdf_kernel");
   return TFC_OK;
 }

@@ -295,20 +295,97 @@ class EntropyBottleneck(EntropyModel):
     logits = self._logits_cumulative(self.quantiles, stop_gradient=True)
     return [torch.sum(torch.abs(logits - t))]
 
-  def update(self):
-    """The reference's update op (entropy_models.py:588-596): rebuild quantized_cdf and
-    cdf_length from the current variables."""
-    self.refresh()
-    max_length = int(self._pmf_length.max().item())
-    samples = torch.arange(max_length, dtype=torch.float32, device=self._medians.device)
+  # ---- the CDF tables and the update op ------------------------------------------------------
+  # The table is [channels, max_length + 2] with max_length = max(_pmf_length), a function of the
+  # quantiles: data-dependent, and the reference's update op runs in EVERY training step
+  # (bls2017.py:173-180).  Reading max_length back each step stalls the step on the host, so
+  # update() builds the tables for the max_length it saw LAST (a host integer), queues an
+  # asynchronous copy of the true one, and the check is settled by whoever reads the tables
+  # next: if the guess was wrong (the quantiles moved a table boundary) the tables are rebuilt
+  # with the right size before anybody sees them.  Observable results are those of the
+  # synchronous form; a training loop that only updates never waits.
+  @property
+  def _quantized_cdf(self):
+    self._settle_tables()
+    return self._tables[0]
+
+  @_quantized_cdf.setter
+  def _quantized_cdf(self, value):        # tables set from outside (build, a checkpoint) are final
+    self._pending_max = None
+    self._tables = (value, getattr(self, "_tables", (None, None))[1])
+
+  @property
+  def _cdf_length(self):
+    self._settle_tables()
+    return self._tables[1]
+
+  @_cdf_length.setter
+  def _cdf_length(self, value):
+    self._pending_max = None
+    self._tables = (getattr(self, "_tables", (None, None))[0], value)
+
+  def _settle_tables(self):
+    pending = getattr(self, "_pending_max", None)
+    if pending is None:
+      return
+    host, event, used = pending
+    self._pending_max = None
+    event.synchronize()
+    true = int(host.item())
+    self._max_length_seen = true
+    if true != used:
+      self._build_tables(true)          # rare: sized for the real max_length this time
+
+  def _build_tables(self, max_length):
+    """entropy_models.py:540-559 + :131-146 for the current variables, tables of width
+    max_length + 2; no host round trip (row lengths stay on the device)."""
+    dev = self._medians.device
+    c, L = self.channels, int(max_length)
+    samples = torch.arange(L, dtype=torch.float32, device=dev)
     samples = samples[None, :] + self._pmf_start[:, None]
     lower = self._logits_cumulative_kernel(samples - .5)
     upper = self._logits_cumulative_kernel(samples + .5)
     sign = -torch.sign(lower + upper)
     pmf = torch.abs(torch.sigmoid(sign * upper) - torch.sigmoid(sign * lower))
+    # tail mass as the reference takes it (:556-560): below the first sample of the row and
+    # above the LAST sample of the padded grid
     tail = torch.sigmoid(lower[:, :1]) + torch.sigmoid(-upper[:, -1:])
-    self._quantized_cdf = self._pmf_to_cdf(pmf, tail, self._pmf_length, max_length)
-    self._cdf_length = (self._pmf_length + 2).to(torch.int32).contiguous()
+    length = torch.clamp(self._pmf_length, max=L).to(torch.int64)
+    # row r of the op's input: pmf[r, :len_r] ++ [tail_r]
+    prob = torch.cat([pmf, torch.zeros((c, 1), dtype=pmf.dtype, device=dev)], dim=1)
+    prob.scatter_(1, length[:, None], tail)
+    prob = prob.contiguous()
+    n = (length + 1).to(torch.int32).contiguous()
+    cdf = torch.empty((c, L + 2), dtype=torch.int32, device=dev)
+    _lib.check(_lib.lib().tfc_pmf_to_quantized_cdf_ragged(
+        _lib.ptr(prob), _i64(c), _i32(L + 1), _lib.ptr(n), _i32(L + 1),
+        int(self.range_coder_precision), _lib.ptr(cdf), _i32(L + 2), _lib.stream_ptr(dev)))
+    self._tables = (cdf, (self._pmf_length + 2).to(torch.int32).contiguous())
+
+  def update(self):
+    """The reference's update op (entropy_models.py:588-596): rebuild quantized_cdf and
+    cdf_length from the current variables."""
+    self.refresh()
+    pending = getattr(self, "_pending_max", None)
+    if pending is not None and pending[1].query():       # an older check that nobody needed
+      self._max_length_seen = int(pending[0].item())
+    self._pending_max = None
+    dev_max = self._pmf_length.max()
+    guess = getattr(self, "_max_length_seen", None)
+    if guess is None:
+      guess = self._max_length_seen = int(dev_max.item())    # first update: one round trip
+      self._build_tables(guess)
+      return
+    self._build_tables(guess)
+    ring = self.__dict__.setdefault("_max_ring", [])
+    if len(ring) < 4:
+      ring.append(torch.empty((1,), dtype=torch.int32, pin_memory=True))
+    host = ring[self.__dict__.setdefault("_max_ring_at", 0) % len(ring)]
+    self._max_ring_at += 1
+    host.copy_(dev_max.reshape(1).to(torch.int32), non_blocking=True)
+    event = torch.cuda.Event()
+    event.record(torch.cuda.current_stream(self._medians.device))
+    self._pending_max = (host, event, guess)
 
   @property
   def updates(self):

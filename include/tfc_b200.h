@@ -163,6 +163,16 @@ int tfc_pmf_to_quantized_cdf(const float* d_pmf, int64_t rows, int32_t n, int pr
                              int32_t* d_cdf, void* d_workspace, size_t workspace_bytes,
                              void* stream);
 
+/* The same op over rows of DIFFERENT lengths in one launch (the table rebuild of
+ * python/layers/entropy_models.py:131-146 builds row r from pmf[r, :len_r] ++ [tail_r] and
+ * zero-pads to the longest row): row r reads d_n[r] entries (clamped to [2, max_n]) at
+ * d_pmf + r * pmf_stride and writes d_n[r] + 1 entries at d_cdf + r * cdf_stride, zeros behind
+ * them up to cdf_stride.  The lengths stay on the device.  One warp per row in shared memory:
+ * max_n up to ~7000. */
+int tfc_pmf_to_quantized_cdf_ragged(const float* d_pmf, int64_t rows, int32_t pmf_stride,
+                                    const int32_t* d_n, int32_t max_n, int precision,
+                                    int32_t* d_cdf, int32_t cdf_stride, void* stream);
+
 /* The same op for callers that cannot allocate device memory (code under CUDA graph capture,
  * tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
  * It takes no workspace: the scratch of the

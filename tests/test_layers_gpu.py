@@ -654,6 +654,36 @@ def test_sub_pixel_path_matches_oracle(tfc, k, su, corr, act):
     assert torch.equal(y8, torch.clamp(torch.round(y * 255), 0, 255).to(torch.uint8))
 
 
+def test_entropy_bottleneck_update_without_readback():
+  """update() builds the tables for the max_length it saw last and checks the true one
+  asynchronously (no host round trip in a training loop); a reader of the tables settles the
+  check.  When the quantiles move the longest row — wider AND narrower — the tables read
+  afterwards must be those of a layer that updates synchronously from the same variables."""
+  from compression_b200.python.layers import entropy_models
+  g = torch.Generator().manual_seed(21)
+  eb = entropy_models.EntropyBottleneck()
+  eb.build(16, "cuda", g)
+  eb.update()                                    # first update: the one synchronous read
+  for scale, shift in ((3.0, 0.0), (0.4, 0.0), (1.0, 2.5), (1.0, 0.0)):
+    q = eb.quantiles.clone()
+    q[:, 0, 0] = -10.0 * scale + shift
+    q[:, 0, 2] = 10.0 * scale + shift
+    q[3, 0, 2] += 7.0                            # one row longer than the others
+    eb.quantiles = q
+    eb.update()                                  # sized by the previous max_length
+    eb.update()                                  # twice in a row: an unread check is dropped
+    fresh = entropy_models.EntropyBottleneck()
+    fresh.build(16, "cuda", torch.Generator().manual_seed(21))
+    for name in ("matrices", "biases", "factors"):
+      setattr(fresh, name, [t.clone() for t in getattr(eb, name)])
+    fresh.quantiles = q.clone()
+    fresh.update()                               # first update of a new layer: synchronous
+    assert torch.equal(eb._cdf_length, fresh._cdf_length)
+    assert eb._quantized_cdf.shape == fresh._quantized_cdf.shape
+    assert torch.equal(eb._quantized_cdf, fresh._quantized_cdf)
+    assert int(eb._cdf_length.max()) == eb._quantized_cdf.shape[1]
+
+
 def test_thin_conv_pipelined_epilogue_equals_default():
   """conv_thin_kernel's software-pipelined GDN epilogue (an experiment behind debug bit 32:
   setmaxnreg, two tiles in flight, y stored from registers) computes exactly what the default
