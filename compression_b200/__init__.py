@@ -22,7 +22,7 @@ from compression_b200.python.ops.spectral_ops import irdft_matrix
 from compression_b200.python.layers.parameterizers import (
     Parameterizer, StaticParameterizer, RDFTParameterizer, NonnegativeParameterizer)
 from compression_b200.python.layers.gdn import GDN
-from compression_b200.python.layers.signal_conv import SignalConv2D
+from compression_b200.python.layers.signal_conv import SignalConv1D, SignalConv2D
 from compression_b200.python.layers.entropy_models import (
     EntropyModel, EntropyBottleneck, SymmetricConditional, GaussianConditional,
     LogisticConditional, LaplacianConditional)

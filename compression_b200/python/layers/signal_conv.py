@@ -6,8 +6,9 @@ padding geometry (`:742-758`, `ops/padding_ops.py`), correlation + downsampling 
 padding (`:487-524`) and upsampled convolution via the transposed-conv formulation
 (`:629-707`) — and reduces each case to the one normalised form the CUDA kernels implement
 (see `tfc_conv_desc` in include/tfc_b200.h).  Combinations the reference itself does not
-implement, and those outside the codecs' hot path (1-D/3-D, `channel_separable`), raise
-NotImplementedError like `:393-401`; `same_reflect` and `channels_first` are reduced on the host
+implement raise NotImplementedError like `:393-401`; `channel_separable` (2-D and 1-D) runs on a
+CUDA-core depthwise kernel and 1-D layers run as 2-D layers of height 1 (neither is on the
+codecs' hot path); 3-D raises; `same_reflect` and `channels_first` are reduced on the host
 side to the same kernels (reflection pre-pad by gather, layout conversion in and out).
 """
 import ctypes
@@ -21,7 +22,7 @@ from compression_b200.python.layers import gdn as gdn_lib
 from compression_b200.python.layers import parameterizers
 from compression_b200.python.ops import padding_ops
 
-__all__ = ["SignalConv2D", "ConvDesc"]
+__all__ = ["SignalConv1D", "SignalConv2D", "ConvDesc"]
 
 ACT_NONE, ACT_RELU, ACT_GDN, ACT_IGDN = 0, 1, 2, 3
 
@@ -129,8 +130,10 @@ class SignalConv2D(object):
   def build(self, input_channels, device="cuda", generator=None):
     cin = int(input_channels)
     kshape = self.kernel_support + (cin, self.filters)
-    if self.channel_separable:
-      self._raise_notimplemented()
+    # channel_separable (signal_conv.py:405-411): `filters` per input channel, cin * filters outputs
+    self.out_channels = cin * self.filters if self.channel_separable else self.filters
+    if self.channel_separable and max(self.strides_up) > 1 and self.filters != 1:
+      self._raise_notimplemented()           # the reference's transposed depthwise op (:590-596)
     init = (self.kernel_initializer(kshape) if self.kernel_initializer is not None
             else variance_scaling_init(kshape, generator))
     init = torch.as_tensor(init, dtype=self.dtype).to(device)
@@ -140,15 +143,15 @@ class SignalConv2D(object):
     else:
       self.kernel_var = kp.init(init)  # variable "kernel_rdft"
     if self.use_bias:
-      b0 = (self.bias_initializer((self.filters,)) if self.bias_initializer is not None
-            else torch.zeros(self.filters))
+      b0 = (self.bias_initializer((self.out_channels,)) if self.bias_initializer is not None
+            else torch.zeros(self.out_channels))
       b0 = torch.as_tensor(b0, dtype=self.dtype).to(device)
       bp = self.bias_parameterizer
       self.bias_var = b0 if bp is None else bp.init(b0)
     else:
       self.bias_var = None
     if isinstance(self.activation, gdn_lib.GDN) and not self.activation.built:
-      self.activation.build(self.filters, device)
+      self.activation.build(self.out_channels, device)
     self.input_channels = cin
     self.built = True
     self._eff = None
@@ -225,7 +228,10 @@ class SignalConv2D(object):
       if self.padding == "valid":
         s -= self.kernel_support[i] - 1
       out.append((s - 1) // self.strides_down[i] + 1)
-    return (n, out[0], out[1], self.filters)
+    channels = getattr(self, "out_channels", None)
+    if channels is None:
+      channels = input_shape[-1] * self.filters if self.channel_separable else self.filters
+    return (n, out[0], out[1], channels)
 
   def _activation_code(self):
     a = self.activation
@@ -279,6 +285,33 @@ class SignalConv2D(object):
       self._raise_notimplemented()
     return x, "same_zeros", (pad[0][0] * su, pad[1][0] * su)
 
+  def _call_separable(self, x, pad_begin, ho, wo, crop, want_shape, out_dtype):
+    """channel_separable=True: the depthwise kernel (float32), then the activation as its own
+    op — the reference's structure (tf.nn.depthwise_conv2d_native, bias_add, activation)."""
+    n, h, w, cin = x.shape
+    if x.dtype == torch.uint8:
+      x = x.float() / 255
+    x = x.float().contiguous()
+    wgt, bias = self.effective_weights()
+    d = ConvDesc(n=n, h=h, w=w, cin=cin, ho=ho, wo=wo, cout=self.out_channels,
+                 kh=self.kernel_support[0], kw=self.kernel_support[1],
+                 sd=self.strides_down[0], su=self.strides_up[0], pad_top=pad_begin[0],
+                 pad_left=pad_begin[1], act=ACT_NONE, in_dtype=_dtype_code(torch.float32),
+                 out_dtype=_dtype_code(torch.float32), impl=0, flags=0)
+    out = torch.empty((n, ho, wo, self.out_channels), dtype=torch.float32, device=x.device)
+    _lib.check(_lib.lib().tfc_depthwise_conv2d(
+        ctypes.byref(d), _lib.ptr(x), _lib.ptr(wgt), _lib.ptr(bias), _lib.ptr(out),
+        _lib.stream_ptr(x.device)))
+    if crop is not None:
+      out = out[:, crop[0]:crop[0] + want_shape[1], crop[1]:crop[1] + want_shape[2], :].contiguous()
+    if self.activation is not None:
+      a = self.activation
+      out = torch.relu(out) if a == "relu" else a(out)
+    out_dtype = out_dtype or self.out_dtype
+    if out_dtype == torch.uint8:
+      return quantize_image(out)
+    return out if out.dtype == out_dtype else out.to(out_dtype)
+
   def __call__(self, inputs, out_dtype=None):
     """inputs: [batch, height, width, channels] (channels_last) or [batch, channels, height,
     width] (channels_first; converted on the way in and out — the kernels are channels_last)."""
@@ -312,8 +345,10 @@ class SignalConv2D(object):
     n, h, w, cin = x.shape
     ho, wo = out_len(h, 0), out_len(w, 1)
     if crop is None:
-      assert (n, ho, wo, self.filters) == want_shape, \
+      assert (n, ho, wo, self.out_channels) == want_shape, \
           "internal: output geometry disagrees with compute_output_shape"
+    if self.channel_separable:
+      return self._call_separable(x, pad_begin, ho, wo, crop, want_shape, out_dtype)
     act, post = self._activation_code()
     out_dtype = out_dtype or self.out_dtype
     wgt, bias = self.effective_weights()
@@ -379,3 +414,40 @@ class SignalConv2D(object):
     if quantize_after:
       out = quantize_image(out)
     return out
+
+
+class SignalConv1D(SignalConv2D):
+  """1-D signal convolution layer (signal_conv.py:848-863): inputs [batch, length, channels]
+  (channels_last) or [batch, channels, length].  Runs as the 2-D layer over an image of height 1
+  with a kernel of height 1 — the reference inserts the same extra dimension where TF has no 1-D
+  op (:459-471, :498-516, :565-589); an upsampled layer computes `strides_up` rows of which the
+  first is the 1-D result.  Not on the codecs' hot path."""
+
+  _rank = 1
+
+  def __init__(self, filters, kernel_support, corr=False, strides_down=1, strides_up=1, **kwargs):
+    def one(v, what):
+      v = tuple(v) if isinstance(v, (tuple, list)) else (v,)
+      if len(v) != 1:
+        raise ValueError("`%s` must be an int or a 1-tuple" % what)
+      return int(v[0])
+    k, sd, su = one(kernel_support, "kernel_support"), one(strides_down, "strides_down"), \
+        one(strides_up, "strides_up")
+    super(SignalConv1D, self).__init__(filters, (1, k), corr=corr, strides_down=(sd, sd),
+                                       strides_up=(su, su), **kwargs)
+
+  def compute_output_shape(self, input_shape):
+    if len(input_shape) == 3:
+      n, l, c = input_shape
+      full = super(SignalConv1D, self).compute_output_shape((n, 1, l, c))
+      return (n, full[2], full[3])
+    return super(SignalConv1D, self).compute_output_shape(input_shape)
+
+  def __call__(self, inputs, out_dtype=None):
+    if inputs.dim() != 3:
+      raise ValueError("SignalConv1D expects a 3-D input")
+    if self.data_format == "channels_first":
+      out = self._call_nhwc(inputs.permute(0, 2, 1)[:, None], out_dtype)
+      return out[:, 0].permute(0, 2, 1).contiguous()
+    out = self._call_nhwc(inputs[:, None], out_dtype)
+    return out[:, 0].contiguous()

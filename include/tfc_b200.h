@@ -342,6 +342,14 @@ int tfc_signal_conv2d(const tfc_conv_desc* desc, const void* d_in, const float* 
                       const float* d_bias, const float* d_beta, const float* d_gamma,
                       void* d_out, void* d_workspace, size_t workspace_bytes, void* stream);
 
+/* Channel-separable form of the same layer (signal_conv.py:466-485, :590-596; the layout of
+ * tf.nn.depthwise_conv2d_native): desc->cin channels, desc->cout = cin * multiplier outputs,
+ * output channel c * multiplier + q = input channel c with its filter q,
+ *   d_w [kh, kw, cin, multiplier], d_bias [cout] or NULL, float32 in and out, no fused activation.
+ * Not on the codecs' hot path: a CUDA-core kernel. */
+int tfc_depthwise_conv2d(const tfc_conv_desc* desc, const float* d_in, const float* d_w,
+                         const float* d_bias, float* d_out, void* stream);
+
 /* Filter gradient of the same convolution (training step of examples/bls2017.py:156-185; in the
  * reference TF derives it from tf.nn.conv2d / conv2d_backprop_input):
  *   d_dw[a,b,c,o] = sum_{n,i,j} U[n, i*sd + a - pad_top, j*sd + b - pad_left, c] * dout[n,i,j,o]

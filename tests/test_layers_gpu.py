@@ -654,6 +654,78 @@ def test_sub_pixel_path_matches_oracle(tfc, k, su, corr, act):
     assert torch.equal(y8, torch.clamp(torch.round(y * 255), 0, 255).to(torch.uint8))
 
 
+def _separable_expected(x, kern, bias, corr, sd, su, padding, extra_pad_end=True):
+  """signal_conv_test.py:47-78: channel c with its filter q lands in output channel c * M + q."""
+  c, m = kern.shape[2], kern.shape[3]
+  cols = []
+  for ci in range(c):
+    y = tfc_np.signal_conv2d(x[..., ci:ci + 1], kern[:, :, ci:ci + 1, :], None, corr, sd, su,
+                             padding, extra_pad_end)
+    cols.append(y)
+  out = torch.stack(cols, dim=3).reshape(cols[0].shape[:3] + (c * m,))
+  return out + (torch.as_tensor(bias, dtype=out.dtype) if bias is not None else 0)
+
+
+@pytest.mark.parametrize("corr,sd,su,mult,padding,k", [
+    (True, 1, 1, 2, "same_zeros", 3), (False, 2, 1, 3, "same_zeros", 5), (True, 2, 1, 1, "valid", 4),
+    (False, 1, 2, 1, "same_zeros", 5), (True, 1, 3, 1, "valid", 3), (False, 1, 1, 2, "same_reflect", 3)])
+def test_channel_separable_matches_oracle(tfc, corr, sd, su, mult, padding, k):
+  """signal_conv.py:466-485 / :590-596: the depthwise layer against the dense oracle
+  applied channel by channel, as the reference's own test builds its expectation."""
+  rng = np.random.default_rng(5)
+  cin = 6
+  kern = rng.normal(size=(k, k, cin, mult)).astype(np.float32)
+  b = rng.normal(size=cin * mult).astype(np.float32)
+  layer = tfc.SignalConv2D(mult, (k, k), corr=corr, strides_down=sd, strides_up=su, padding=padding,
+                           channel_separable=True, use_bias=True, kernel_parameterizer=None,
+                           kernel_initializer=_static(kern), bias_initializer=_static(b))
+  x = rng.normal(size=(2, 11, 14, cin)).astype(np.float32)
+  got = layer(torch.from_numpy(x).cuda())
+  want = _separable_expected(x, kern, b, corr, sd, su, padding)
+  assert tuple(got.shape) == tuple(want.shape) == tuple(layer.compute_output_shape(x.shape))
+  np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), rtol=1e-4, atol=1e-4)
+
+
+def test_channel_separable_upsampled_needs_one_filter(tfc):
+  layer = tfc.SignalConv2D(2, (3, 3), strides_up=2, channel_separable=True, padding="same_zeros")
+  with pytest.raises(NotImplementedError):
+    layer.build(4, "cuda")
+
+
+@pytest.mark.parametrize("corr,sd,su,padding,k,sep", [
+    (True, 1, 1, "same_zeros", 5, False), (False, 2, 1, "same_zeros", 5, False),
+    (False, 1, 2, "same_zeros", 4, False), (False, 1, 3, "valid", 3, False),
+    (True, 3, 1, "valid", 5, False), (False, 2, 1, "same_zeros", 3, True),
+    (True, 1, 2, "same_zeros", 5, True)])
+def test_signal_conv1d_matches_oracle(tfc, corr, sd, su, padding, k, sep):
+  """signal_conv.py:848-863: 1-D layers, dense and channel separable, against the 2-D
+  oracle over an image of height 1 with a kernel of height 1 (what the reference itself does
+  where TF has no 1-D op)."""
+  rng = np.random.default_rng(8)
+  cin, filters = 5, (1 if sep else 7)
+  kern = rng.normal(size=(1, k, cin, filters)).astype(np.float32)
+  cout = cin * filters if sep else filters
+  b = rng.normal(size=cout).astype(np.float32)
+  layer = tfc.SignalConv1D(filters, k, corr=corr, strides_down=sd, strides_up=su, padding=padding,
+                           channel_separable=sep, use_bias=True, kernel_parameterizer=None,
+                           kernel_initializer=_static(kern), bias_initializer=_static(b))
+  x = rng.normal(size=(3, 23, cin)).astype(np.float32)
+  got = layer(torch.from_numpy(x).cuda())
+  if sep:
+    want = _separable_expected(x[:, None], kern, b, corr, sd, su, padding)[:, 0]
+  else:
+    want = tfc_np.signal_conv2d(x[:, None], kern, b, corr, sd, su, padding)[:, 0]
+  assert tuple(got.shape) == tuple(want.shape) == tuple(layer.compute_output_shape(x.shape))
+  np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), rtol=2e-2 if not sep else 1e-4,
+                             atol=2e-2 if not sep else 1e-4)
+  cf = tfc.SignalConv1D(filters, k, corr=corr, strides_down=sd, strides_up=su, padding=padding,
+                        channel_separable=sep, use_bias=True, kernel_parameterizer=None,
+                        kernel_initializer=_static(kern), bias_initializer=_static(b),
+                        data_format="channels_first")
+  got_cf = cf(torch.from_numpy(x).cuda().permute(0, 2, 1).contiguous())
+  assert torch.equal(got_cf.permute(0, 2, 1), got)
+
+
 def test_entropy_bottleneck_update_without_readback():
   """update() builds the tables for the max_length it saw last and checks the true one
   asynchronously (no host round trip in a training loop); a reader of the tables settles the

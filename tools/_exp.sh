@@ -1,2 +1,2 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_layers_gpu.py -x -q -m gpu -k "update_without_readback" 2>&1 | tail -15
+timeout 900 python -m pytest tests/test_layers_gpu.py -x -q -m gpu -k "separable or conv1d" 2>&1 | tail -25
