@@ -99,6 +99,9 @@ def parse_args():
                   help="transform stage streams from the high-priority pool (1) or the default one "
                        "(0), or 'a,h,s': stream priority levels (0, -1, -2, -3) of the analysis, "
                        "hyper-synthesis and synthesis stages")
+  ap.add_argument("--c3-tail", default="", help="the same for the c3 block's micro-batches")
+  ap.add_argument("--tail", default="",
+                  help="'batches,pack': coder streams per CTA for the last batches of a run")
   ap.add_argument("--coder-pack", type=int, default=0,
                   help="coder streams per CTA when depth > 1 (0: by the number of streams in "
                        "flight: 4 at batch 64 x 12, 2 at batch 32 x 8)")
@@ -414,8 +417,11 @@ def c3_block(args, model, world, rank, dev, barrier, allmax):
   xs_u8 = [torch.randint(0, 256, (micro, h, w, 3), generator=g, dtype=torch.uint8).pin_memory()
            for _ in range(2)]
   xs_dev = [(x.to(dev).float() / 255).contiguous() for x in xs_u8]
+  c3_tail = None
+  if args.c3_tail:
+    c3_tail = tuple(int(v) for v in args.c3_tail.split(","))
   pipe = model.pipeline(depth, args.tiles_per_cta, pack, back_lag=max(2, depth // 2),
-                        host_slots=depth + 6)
+                        host_slots=depth + 6, tail=c3_tail)
   out = {"workload": "bmshj2018-192 encode+decode 1920x1080, batch 256 split over %d GPU(s)" % world,
          "images_per_gpu": share, "micro_batch": micro, "passes_timed": passes,
          "batches_in_flight": depth, "coder_streams_per_cta": pack, "scaling": "strong"}
@@ -762,6 +768,7 @@ def run_b200(args):
   pipe = model.pipeline(args.depth, args.tiles_per_cta, args.coder_pack, args.back_lag,
                         args.host_slots, conv_stages=args.conv_stages,
                         coder_smem_kb=args.coder_smem_kb, coder_table_kb=args.coder_table_kb,
+                        tail=(tuple(int(v) for v in args.tail.split(",")) if args.tail else None),
                         stage_priority=(tuple(int(v) for v in args.stage_priority.split(","))
                                         if "," in args.stage_priority else bool(int(args.stage_priority))))
 

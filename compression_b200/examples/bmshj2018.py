@@ -149,7 +149,7 @@ class Pipeline(object):
 
   def __init__(self, model, depth=3, tiles_per_cta=8, coder_streams_per_cta=4, back_lag=None,
                host_slots=None, conv_stages=0, coder_smem_kb=0, coder_table_kb=0,
-               stage_streams=True, coder_stream_cap=22, stage_priority=True):
+               stage_streams=True, coder_stream_cap=22, stage_priority=True, tail=None):
     """`stage_streams` (default): the TRANSFORM phases of all batches share a few "stage" streams
     (3 for analysis, 2 for the decoder's hyper-synthesis, 3 for synthesis) and only the CODER
     phases get one stream per batch in flight.  torch's caching allocator keeps one pool per
@@ -158,6 +158,11 @@ class Pipeline(object):
     1080p images), with stage streams it stays at ~8 pools however many batches the latency-bound
     coder needs in flight.  Tensors that cross streams are handed over with events +
     `record_stream`.  `stage_streams=False`: one stream per batch for everything.
+    `tail` = (batches, coder_streams_per_cta): the coder calls of the LAST `batches` batches of a
+    roundtrip_* call use this packing instead — packing trades a stream's latency for SMs, which
+    is the wrong trade for the batches whose coder chain is the end of the job (nothing is left
+    to use the SMs it saves).
+
     The stage streams come from torch's HIGH-priority pool and the coder streams from the default
     one: each pool holds 32 streams and hands them out round-robin, so more than 32 draws from
     one pool alias (a coder stream would silently BE a stage stream, and a 100 ms coder kernel
@@ -199,6 +204,8 @@ class Pipeline(object):
     self._lib = _lib
     self.tiles_per_cta = int(tiles_per_cta) if self.depth > 1 else 0
     self.pack = int(coder_streams_per_cta) if self.depth > 1 else 0
+    self.tail = (int(tail[0]), int(tail[1])) if tail and self.depth > 1 else None
+    self._pack_now = None
     self.share = (int(conv_stages), int(coder_smem_kb), int(coder_table_kb)) if self.depth > 1 \
         else (0, 0, 0)
     self.h2d_bytes = self.d2h_bytes = 0
@@ -210,12 +217,20 @@ class Pipeline(object):
       self._lib.configure(coder_streams_per_cta=self.pack, tiles_per_cta=self.tiles_per_cta,
                           conv_stages=self.share[0], coder_smem_kb=self.share[1],
                           coder_table_kb=self.share[2])
+      self._pack_now = self.pack
     return self
 
   def __exit__(self, *exc):
     self._lib.configure(coder_streams_per_cta=0, tiles_per_cta=0, conv_stages=0, coder_smem_kb=0,
                         coder_table_kb=0)
     return False
+
+  def _pack_for(self, k, n):
+    """Coder packing for batch k of n (the library reads it at launch time)."""
+    want = self.tail[1] if self.tail and k >= n - self.tail[0] else self.pack
+    if want != self._pack_now:
+      self._lib.configure(coder_streams_per_cta=want)
+      self._pack_now = want
 
   def _all_streams(self):
     extra = [s for group in self.stage.values() for s in group] if self.stage else []
@@ -275,6 +290,7 @@ class Pipeline(object):
           checks.drain(2 * self.depth)
           continue
         a, e, hs, sy = self._streams_of(k)
+        self._pack_for(k, len(batches))
         if k - self.depth in done:            # at most `depth` batches between analysis and x_hat
           a.wait_event(done.pop(k - self.depth))
         with torch.cuda.stream(a):
@@ -379,6 +395,7 @@ class Pipeline(object):
 
     def front_work(k, slot, st, checks, cap):
       checks.tag = ("front", k)
+      self._pack_for(k, n)
       a, e, _, _ = self._streams_of(k)
       with torch.cuda.stream(a):
         x = batches_u8[k].to(dev, non_blocking=True)
@@ -432,6 +449,7 @@ class Pipeline(object):
       host = Compressed(HostStrings(*staged[0]), HostStrings(*staged[1]), c.x_shape, c.y_shape,
                         c.z_shape)
       checks.tag = ("back", k)
+      self._pack_for(k, n)
       _, e, hstream, sy = self._streams_of(k)
       with torch.cuda.stream(e):
         # back to the device straight from the pinned slabs the strings arrived in

@@ -1,2 +1,3 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_layers_gpu.py -x -q -m gpu -k "separable or conv1d" 2>&1 | tail -25
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/r2x_launches_bench_step.csv python bench.py --steps 2 --warmup 1 --blocks parity --no-cpu-baseline > gpurun_out/r2x_launches.log 2>&1
+echo "rc=$?"; tail -2 gpurun_out/r2x_launches.log | cut -c1-300; wc -l gpurun_out/r2x_launches_bench_step.csv
