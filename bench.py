@@ -99,6 +99,8 @@ def parse_args():
                   help="transform stage streams from the high-priority pool (1) or the default one "
                        "(0), or 'a,h,s': stream priority levels (0, -1, -2, -3) of the analysis, "
                        "hyper-synthesis and synthesis stages")
+  ap.add_argument("--debug-bits", type=int, default=0,
+                  help="library experiment bits (tfc_configure key 99), for A/B runs")
   ap.add_argument("--c3-tail", default="", help="the same for the c3 block's micro-batches")
   ap.add_argument("--tail", default="",
                   help="'batches,pack': coder streams per CTA for the last batches of a run")
@@ -723,6 +725,9 @@ def run_b200(args):
     dist.init_process_group("nccl", device_id=dev)
   blocks = wanted_blocks(args)
   h, w, batch, nf = WORKLOADS[args.workload]
+  if args.debug_bits:
+    from compression_b200 import _lib as _tfc_lib
+    _tfc_lib.check(_tfc_lib.lib().tfc_configure(99, args.debug_bits))
   if args.coder_lanes:
     tfc.configure(coder_lanes=args.coder_lanes)
   if args.conv_pair:

@@ -95,6 +95,43 @@ def test_unbounded_random_sweep(tfc, oracle, coder_lanes):
   assert total_streams >= 5000
 
 
+@pytest.mark.parametrize("pack", [2, 3, 4, 8])
+def test_packed_coder_ctas_match_reference(tfc, oracle, pack):
+  """Packed coder CTAs (tfc.configure coder_streams_per_cta >= 2, what the pipeline runs): same
+  bytes as the reference for odd and even stream counts (a last CTA that is not full), empty
+  streams, streams whose put counts differ widely inside one CTA (escape bursts in some streams
+  only), several rounds per stream, every overflow width; the decoder returns the symbols."""
+  from compression_b200.python.ops import range_coding_ops as rc
+  rng = np.random.default_rng(100 + pack)
+  tfc.configure(coder_lanes=1, coder_streams_per_cta=pack)
+  try:
+    for trial in range(24):
+      precision = int(rng.integers(8, 17))
+      ow = int(rng.choice([1, 2, 4, 7, 16]))
+      rows = int(rng.integers(1, 7))
+      cdf, size, offset = _random_tables(rng, rows, int(rng.integers(3, 40)), precision)
+      S = int(rng.choice([1, 2, 3, 5, 7, 8, 17, 64]))
+      n = int(rng.choice([0, 1, 33, 500, 3000, 9000]))
+      index = rng.integers(0, rows, size=(S, n)).astype(np.int32)
+      limit = 1 << (ow * (31 // ow))
+      data = rng.integers(-2, 3, size=(S, n))
+      burst = rng.integers(0, S, size=max(1, S // 2))          # these streams escape all the time
+      data[burst] = rng.integers(-min(50000, limit // 4 - 8), min(50000, limit // 4 - 8) + 1,
+                                 size=(len(burst), n))
+      data = (data + offset[index]).astype(np.int32)
+      out, nbytes = rc.unbounded_index_range_encode_batch(data, index, cdf, size, offset,
+                                                          precision, ow, debug_level=0)
+      got = rc.strings_to_host(out, nbytes)
+      for s_ in range(0, S, max(1, S // 6)):
+        want = oracle.ui_encode(data[s_], index[s_], cdf, size, offset, precision, ow)
+        assert got[s_] == want, (trial, s_, S, n, precision, ow)
+      dec = rc.unbounded_index_range_decode_batch(out, nbytes, index, cdf, size, offset,
+                                                  precision, ow, debug_level=0)
+      np.testing.assert_array_equal(dec.cpu().numpy(), data)
+  finally:
+    tfc.configure(coder_lanes=0, coder_streams_per_cta=0)
+
+
 def test_unbounded_many_streams_capacity_retry(tfc, oracle):
   """2100 ragged streams (the automatic lane-per-stream path), output slab deliberately too
   small: the kernel reports the size it needs per stream and the retry produces the

@@ -21,6 +21,7 @@ def main():
   ap.add_argument("--lanes", type=int, default=0, help="0 auto, 1 warps per stream, 2 lane per stream")
   ap.add_argument("--smem-kb", type=int, default=0)
   ap.add_argument("--table-kb", type=int, default=0)
+  ap.add_argument("--debug", type=int, default=0, help="library experiment bits (64: packed encoder with one stream per chain warp)")
   ap.add_argument("--repeat", type=int, default=1,
                   help="code the batch's latents this many times over in ONE launch (batch * repeat streams)")
   args = ap.parse_args()
@@ -36,6 +37,9 @@ def main():
   c = bmshj2018.Compressed(string, side_string, tuple(x.shape[1:-1]), tuple(y.shape[1:-1]),
                            tuple(z.shape[1:-1]))
   tfc.configure(coder_lanes=args.lanes)
+  if args.debug:
+    from compression_b200 import _lib
+    _lib.check(_lib.lib().tfc_configure(99, args.debug))
   tfc.configure(coder_streams_per_cta=args.pack, coder_smem_kb=args.smem_kb,
                 coder_table_kb=args.table_kb)
   eb, gc = model.entropy_bottleneck, model._conditional(sigma)
