@@ -694,6 +694,7 @@ extern "C" int tfc_unbounded_index_range_encode(
     q.streams_per_cta = (int)std::max<int64_t>(1, std::min<int64_t>(pack > 0 ? std::min(pack, 8) : 1, S));
     const int min_cap = (32 * v4_max_puts(overflow_width) + 31) / 32 * 32;   // one 32-symbol round
     q.put_cap = std::max(v4::kPutCap, min_cap);
+    q.max_puts = v4_max_puts(overflow_width);
     const size_t smem_max = coder_smem_max();
     while (q.put_cap / 2 >= std::max(256, min_cap) &&
            (size_t)q.table_bytes + q.streams_per_cta * v4::enc_bytes(q.put_cap) > smem_max)
@@ -704,6 +705,7 @@ extern "C" int tfc_unbounded_index_range_encode(
     q.round = std::max(32, std::min(v4::kRoundMax, q.put_cap / v4_max_puts(overflow_width) / 32 * 32));
     if (q.round * v4_max_puts(overflow_width) > q.put_cap)
       return tfc::fail(TFC_ERR_UNIMPLEMENTED, "overflow_width %d needs larger round buffers", overflow_width);
+    q.fixed_round = (tfc::debug_bits() & 128) ? q.round : 0;   // A/B: the worst-case-sized rounds
     const size_t smem = (size_t)q.table_bytes + q.streams_per_cta * v4::enc_bytes(q.put_cap);
     static tfc::PerDeviceOnce attr;
     if (attr.first()) {

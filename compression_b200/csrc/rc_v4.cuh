@@ -605,6 +605,14 @@ __global__ void __launch_bounds__(512, 1) decode_unbounded_v4(const DecParamsV4 
 //   warp 1  low    : lo += a with immediate carry propagation into the words already produced
 //                    (the reference delays the carry, range_coder.cc:169-265; the bytes are the
 //                    same big-number sum), one 16-bit word per flag; flushes coalesced.
+// A round is as many 32-symbol groups as are CERTAIN to fit in the put buffer (a group is
+// started while put_cap - fill >= 32 * max_puts), not a fixed number of symbols sized for the
+// worst case: a symbol takes ~1.02 puts on the codec's streams and up to 11 in the worst case,
+// and when streams are packed into a CTA the buffers shrink to 512 puts — fixed rounds were then
+// 32 symbols long, one barrier of the three warps per 32 symbols (y encode of 64 streams:
+// 21.7 ms at 8 per CTA against 13.5 at 2; see profiles/r2z_encoder_variable_rounds.txt).  The
+// stager announces its last round in shared memory; the other two warps follow one and two
+// rounds behind.
 constexpr int kPutCap = 2048;          // puts per round (upper bound)
 
 struct EncParamsV4 {
@@ -625,6 +633,8 @@ struct EncParamsV4 {
   int32_t table_bytes;
   int32_t put_cap;        // puts per round (<= kPutCap, multiple of 32)
   int32_t streams_per_cta;
+  int32_t max_puts;       // puts one symbol can take at most (escape with all its digits)
+  int32_t fixed_round;    // > 0 (experiments): rounds of exactly this many symbols, as before
 };
 
 __host__ __device__ inline size_t enc_bytes(int put_cap) {
@@ -661,10 +671,10 @@ __global__ void __launch_bounds__(MULTI ? 768 : 96) encode_unbounded_v4(const En
   uint16_t* words = reinterpret_cast<uint16_t*>(avals + 2 * kCap);               // [kCap + 2]
   volatile uint32_t* counts = reinterpret_cast<volatile uint32_t*>(words + kCap + 2);  // [4]
   volatile uint32_t* fin = counts + 4;                                           // final span1
+  volatile int32_t* last_round = reinterpret_cast<volatile int32_t*>(counts + 5);  // -1: not yet
 
   const int warp = (int)((threadIdx.x - slot * 96) >> 5), lane = threadIdx.x & 31;
-  const int R = p.round;
-  const int64_t rounds = (p.n + R - 1) / R;
+  if (warp == 2 && lane == 0) last_round[0] = -1;     // read by the others after the first barrier
   const int32_t* idx = p.index + s * p.index_stride;
   const int32_t* data = p.data + s * p.n;
   uint8_t* out = p.out + s * p.cap;
@@ -686,25 +696,27 @@ __global__ void __launch_bounds__(MULTI ? 768 : 96) encode_unbounded_v4(const En
     }
   }
 
-  for (int64_t r = 0; r < rounds + 2; ++r) {
+  int64_t staged = 0;                    // warp 2: symbols turned into puts so far
+  const uint32_t group_puts = 32u * (uint32_t)p.max_puts;
+  for (int64_t r = 0;; ++r) {
+    const int64_t L = last_round[0];     // the stager's last round, -1 while it is not known
     if (warp == 2) {
-      if (r < rounds) {
-        // ---- stager ----
-        const int64_t base = r * R;
-        const int cnt = (int)min((int64_t)R, p.n - base);
+      if (L < 0) {
+        // ---- stager: 32-symbol groups for as long as the next one is certain to fit ----
         uint2* dst = puts + (r & 1) * kCap;
         uint32_t fill = 0;
-        for (int j0 = 0; j0 < cnt; j0 += 32) {
-          const int j = j0 + lane;
+        const int64_t stop = p.fixed_round > 0 ? staged + p.fixed_round : p.n;
+        while (staged < p.n && staged < stop && fill + group_puts <= (uint32_t)kCap) {
+          const int64_t j = staged + lane;
           uint32_t c0 = 0, c1 = 0, x = 0;
           int np = 0, nd = 0;
           const int32_t cur_idx = pf_idx[0], cur_dat = pf_dat[0];
           pf_idx[0] = pf_idx[1]; pf_dat[0] = pf_dat[1];
           {
-            const int64_t at = base + j + 64;
+            const int64_t at = j + 64;
             if (at < p.n) { pf_idx[1] = __ldg(idx + at); pf_dat[1] = __ldg(data + at); }
           }
-          if (j < cnt) {
+          if (j < p.n) {
             const int4 ri = t.rowinfo[cur_idx];
             const int32_t top = ri.y - 2;
             int32_t v = cur_dat - ri.z;
@@ -739,11 +751,15 @@ __global__ void __launch_bounds__(MULTI ? 768 : 96) encode_unbounded_v4(const En
             }
           }
           fill += (uint32_t)__shfl_sync(0xFFFFFFFFu, incl, 31);
+          staged += 32;
         }
-        if (lane == 0) counts[r & 3] = fill;
+        if (lane == 0) {
+          counts[r & 3] = fill;
+          if (staged >= p.n) last_round[0] = (int32_t)r;
+        }
       }
     } else if (warp == 0) {
-      if (r >= 1 && r <= rounds) {
+      if (r >= 1 && (L < 0 || r - 1 <= L)) {
         // ---- span chain (replicated in all lanes; lane 0 stores) ----
         const int64_t q = r - 1;
         const uint32_t cnt = counts[q & 3];
@@ -765,10 +781,10 @@ __global__ void __launch_bounds__(MULTI ? 768 : 96) encode_unbounded_v4(const En
           cur = nxt;
           nxt = nn;
         }
-        if (r == rounds && lane == 0) fin[0] = span1;
+        if (q == L && lane == 0) fin[0] = span1;       // L is settled by the time q reaches it
       }
     } else {
-      if (r >= 2) {
+      if (r >= 2 && (L < 0 || r - 2 <= L)) {
         // ---- low chain + emission (replicated; lane 0 does the rare global fix-ups) ----
         const int64_t q = r - 2;
         const uint32_t cnt = counts[q & 3];
@@ -850,7 +866,7 @@ __global__ void __launch_bounds__(MULTI ? 768 : 96) encode_unbounded_v4(const En
         }
         __syncwarp();
         // flush all but the newest word (everything after the last round)
-        const uint32_t keep = (q + 1 < rounds && nw > 0) ? 1u : 0u;
+        const uint32_t keep = ((L < 0 || q < L) && nw > 0) ? 1u : 0u;
         const uint32_t nflush = nw - keep;
         for (uint32_t k = lane; k < nflush; k += 32) {
           const uint32_t wv = words[k];
@@ -865,6 +881,8 @@ __global__ void __launch_bounds__(MULTI ? 768 : 96) encode_unbounded_v4(const En
       }
     }
     if (MULTI) trio_barrier(1 + slot); else __syncthreads();
+    const int64_t L2 = last_round[0];
+    if (L2 >= 0 && r >= L2 + 2) break;
   }
 
   if (warp == 1) {
