@@ -255,7 +255,11 @@ class ClockSampler(object):
         continue
       try:
         ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f")
-        rows.append((ts, float(f[2]), float(f[3]), f[6:10]))
+        try:
+          watts = float(f[4])
+        except ValueError:
+          watts = None
+        rows.append((ts, float(f[2]), float(f[3]), f[6:10], watts))
       except ValueError:
         continue
     os.unlink(self.path)
@@ -269,9 +273,10 @@ class ClockSampler(object):
       for n, v in zip(names, r[3]):
         if v.lower().startswith("active"):
           reasons.add(n)
+    watts = [r[4] for r in rows if r[4] is not None]
     return {"sm_mhz": float(np.median(sm)) if sm else None,
             "sm_max_mhz": float(max(mx)) if mx else None, "reasons": sorted(reasons),
-            "samples": len(sm)}
+            "samples": len(sm), "power_w": float(np.median(watts)) if watts else None}
 
 
 # ---- CPU arm (cpu_baseline and --impl reference) ---------------------------------------------------
