@@ -28,6 +28,7 @@ collective on the data path), so scaling is weak.  One JSON line is printed by r
                 step with its NCCL all-reduce at the N the run was launched with
 """
 import argparse
+import gc as pygc
 import glob
 import json
 import os
@@ -792,6 +793,11 @@ def run_b200(args):
       clocks.start()
     pipe.roundtrip_device([x_dev] * n_warm)
     barrier()
+    # no cyclic garbage collection inside the timed windows: a generation-2 pass over the heap of
+    # this process takes tens of ms, which is a visible share of a 0.27 s window when it lands
+    # while the GPU's queue is still short
+    pygc.collect()
+    pygc.disable()
     clocks.mark()
     launches0 = tfc.launch_count()
     timer.on = True
@@ -825,6 +831,7 @@ def run_b200(args):
     h2d_bytes, d2h_bytes = int(pipe.h2d_bytes), int(pipe.d2h_bytes)
     host_busy_ms = pipe.host_busy_s * 1e3 / args.steps
     host_wait_ms = pipe.host_wait_s * 1e3 / args.steps
+    pygc.enable()
 
   # the conv kernels alone, one batch, nothing else on the GPU (explains the roofline figure
   # measured under concurrency above)
