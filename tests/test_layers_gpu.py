@@ -67,8 +67,8 @@ def test_signal_conv_not_implemented(tfc):
   with pytest.raises(NotImplementedError):        # upsampling + downsampling over a reflection
     tfc.SignalConv2D(2, (5, 5), corr=False, strides_up=2, strides_down=2,
                      padding="same_reflect")(x)
-  with pytest.raises(NotImplementedError):
-    tfc.SignalConv2D(2, (3, 3), corr=True, channel_separable=True)(x)
+  with pytest.raises(NotImplementedError):        # upsampled separable layers: one filter only (:590-596)
+    tfc.SignalConv2D(2, (3, 3), corr=False, strides_up=2, channel_separable=True)(x)
 
 
 def test_signal_conv_channels_first(tfc):
