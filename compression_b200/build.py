@@ -13,7 +13,7 @@ FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-O3", "--expt-relaxed-constexpr",
     "-I", os.path.join(ROOT, "include"), "-I", CSRC,
-]
+] + os.environ.get("TFC_NVCC_EXTRA", "").split()   # e.g. -DTFC_A0_KNOCKOUT for tools/conv_bench.py --debug
 
 
 def _stale(obj, srcs):

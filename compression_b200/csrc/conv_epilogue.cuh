@@ -92,7 +92,8 @@ constexpr int kEpilogueThreads = kEpilogueWarps * 32;
 // tile's x^2 goes in.  Without `map_out` every thread stores its own channels (store_chunk).
 struct TileOrigin { int j, i, n; };   // tensor-map coordinates of the tile's first pixel (n < 0: no store)
 
-template <int MODE, int NCH>
+// KO: knock-out bits of the bottleneck hunt (profiles/r3f_*): results are WRONG when non-zero
+template <int MODE, int NCH, int KO = 0>
 __device__ __forceinline__ void gdn_tile(uint32_t dacc, uint8_t* a2, int r, int cbase,
                                          const float* s_bias, const float* s_beta,
                                          uint64_t* a2_full, uint64_t* d2_full, uint32_t it,
@@ -118,7 +119,8 @@ __device__ __forceinline__ void gdn_tile(uint32_t dacc, uint8_t* a2, int r, int 
     const float4* bs = reinterpret_cast<const float4*>(s_bias + cc * 32);
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      const float4 b0 = bs[2 * q], b1 = bs[2 * q + 1];
+      const float4 kz = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4 b0 = (KO & 1) ? kz : bs[2 * q], b1 = (KO & 1) ? kz : bs[2 * q + 1];
       const float x0 = __uint_as_float(v[8 * q + 0]) + b0.x;
       const float x1 = __uint_as_float(v[8 * q + 1]) + b0.y;
       const float x2 = __uint_as_float(v[8 * q + 2]) + b0.z;
@@ -132,6 +134,7 @@ __device__ __forceinline__ void gdn_tile(uint32_t dacc, uint8_t* a2, int r, int 
       xs[c * 16 + 4 * q + 2] = pack_bf16(x4, x5);
       xs[c * 16 + 4 * q + 3] = pack_bf16(x6, x7);
       const int physc = ((cc & 1) * 4 + q) ^ (r & 7);
+      if (!(KO & 8) || x0 == 12345.f)
       *reinterpret_cast<uint4*>(row + physc * 16) =
           make_uint4(pack_bf16(x0 * x0, x1 * x1), pack_bf16(x2 * x2, x3 * x3),
                      pack_bf16(x4 * x4, x5 * x5), pack_bf16(x6 * x6, x7 * x7));
@@ -147,20 +150,25 @@ __device__ __forceinline__ void gdn_tile(uint32_t dacc, uint8_t* a2, int r, int 
   for (int c = 0; c < NCH; ++c) {
     const int cc = cbase + c;
     uint32_t g[32];
-    tmem_ld_32x32(dacc + cc * 32, g);
-    tmem_ld_wait();
+    if (KO & 32) {
+#pragma unroll
+      for (int e = 0; e < 32; ++e) g[e] = xs[c * 16 + (e >> 1)];
+    } else {
+      tmem_ld_32x32(dacc + cc * 32, g);
+      tmem_ld_wait();
+    }
     const float4* be = reinterpret_cast<const float4*>(s_beta + cc * 32);
     float y[32];
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
-      const float4 b4 = be[q];
+      const float4 b4 = (KO & 1) ? make_float4(1.f, 1.f, 1.f, 1.f) : be[q];
       const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
         const uint32_t pr = xs[c * 16 + 2 * q + (e >> 1)];
         const float x = __uint_as_float((e & 1) ? (pr & 0xFFFF0000u) : (pr << 16));
         const float nrm = __uint_as_float(g[4 * q + e]) + bb[e];
-        y[4 * q + e] = x * (MODE == 2 ? sqrt_approx(nrm) : rsqrt_approx(nrm));
+        y[4 * q + e] = (KO & 4) ? x * nrm : x * (MODE == 2 ? sqrt_approx(nrm) : rsqrt_approx(nrm));
       }
     }
     if (map_out != nullptr) {
@@ -168,6 +176,7 @@ __device__ __forceinline__ void gdn_tile(uint32_t dacc, uint8_t* a2, int r, int 
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const int physc = ((cc & 1) * 4 + q) ^ (r & 7);
+        if (!(KO & 16) || y[8 * q] == 12345.f)
         *reinterpret_cast<uint4*>(row + physc * 16) =
             make_uint4(pack_bf16(y[8 * q], y[8 * q + 1]), pack_bf16(y[8 * q + 2], y[8 * q + 3]),
                        pack_bf16(y[8 * q + 4], y[8 * q + 5]), pack_bf16(y[8 * q + 6], y[8 * q + 7]));
@@ -179,7 +188,7 @@ __device__ __forceinline__ void gdn_tile(uint32_t dacc, uint8_t* a2, int r, int 
   if (map_out != nullptr) {
     fence_proxy_async_smem();
     named_barrier(1, kEpilogueThreads);
-    if (leader) {
+    if (leader && !(KO & 16)) {
       for (int kc = 0; kc < nblocks && org.n >= 0; ++kc)
         tma_store_4d(map_out, a2 + kc * kABytes, kc * 64, org.j, org.i, org.n);
       bulk_commit();

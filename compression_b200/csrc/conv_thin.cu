@@ -36,12 +36,25 @@ namespace epi = tfc::epi;
 
 constexpr int kEpiThreads = tfc::epi::kEpilogueThreads;
 constexpr int kThreads = 64 + kEpiThreads + 64;
+// the tensor-memory (TS) GDN epilogue: sixteen warps, four per lane quadrant
+constexpr int kEpiThreadsTs = 512;
+constexpr int kThreadsTs = 64 + 64 + kEpiThreadsTs;
 constexpr int kBuilders = 64;         // two warps, two tile rows per thread
 constexpr int kABytes = epi::kABytes;
 constexpr int kMaxStages = 4;
-// PIPE: registers per thread of the epilogue warpgroups / of the TMA + MMA + builder warpgroup
-// (256 x 200 + 128 x 96 = 63 488 of the SM's 65 536)
-constexpr int kEpiRegs = 200, kOtherRegs = 96;
+
+// Bias and beta folded into the GEMMs (TS form).  The last k-block of W uses `tail` of its 64
+// K columns; the three bfloat16 pieces of the bias sit in the next three (inside the padding of
+// the last 16-wide K step, where the im2col matrix carries 1.0), and the pieces of beta at
+// positions 13..15 of the 16-wide slice starting at `beta_slice` — columns no main-GEMM step
+// multiplies by anything but zero.
+namespace fold {
+__host__ __device__ constexpr int tail(int K) { return K - (K - 1) / 64 * 64; }
+__host__ __device__ constexpr int beta_slice(int K) { return (tail(K) + 5) / 16 * 16; }
+__host__ __device__ constexpr bool fits(int K) {
+  return tail(K) + 3 <= (tail(K) + 15) / 16 * 16 && beta_slice(K) + 16 <= 64;
+}
+}  // namespace fold
 
 struct Params {
   int32_t n, h, w;                  // input [n, h, w, CIN]
@@ -59,6 +72,7 @@ struct Params {
   int32_t esize;                    // bytes per image element
   int32_t out_tma;                  // GDN output leaves by TMA tile stores
   int32_t debug;
+  uint32_t rcp_per_img, rcp_tiles_w;  // ceil(2^32 / divisor) when exact for every tile, else 0
   const void* in;
   const float* bias;
   const float* beta;
@@ -92,7 +106,7 @@ __device__ __forceinline__ float lds1(const uint8_t* p) { return (float)(*p) * k
 
 // One tile row (= output pixel) of k-block KBI: K-columns [64*KBI, 64*KBI + 16*NM) of the im2col
 // matrix, k = (a*KW + b)*CIN + c.  `src` points at the top-left tap of the pixel's window.
-template <int KH, int KW, int CIN, int KBI, int NM, bool CHECK, typename T>
+template <int KH, int KW, int CIN, int KBI, int NM, bool CHECK, bool FOLD, typename T>
 __device__ __forceinline__ void build_row(const T* __restrict__ src, int64_t row_stride, int y0,
                                           int x0, int h, int w, uint8_t* row, int r) {
   constexpr int K = KH * KW * CIN;
@@ -110,7 +124,7 @@ __device__ __forceinline__ void build_row(const T* __restrict__ src, int64_t row
         v[e] = ldf(src + a * row_stride + t);
       }
     } else {
-      v[e] = 0.f;
+      v[e] = (FOLD && k < K + 3) ? 1.f : 0.f;      // the columns that meet the bias rows of W
     }
   }
 #pragma unroll
@@ -138,14 +152,15 @@ __device__ __forceinline__ void lds_vec(const uint8_t* p, float (&o)[2]) {
 // The same row from the TMA-staged patch in shared memory (zero padding already applied by the
 // TMA unit).  `src` points at the top-left tap inside the patch; V = 2 reads element pairs
 // (LDS.64 / LDS.32), which needs an even sd*CIN.
-template <int KH, int KW, int CIN, int KBI, int NM, int V, typename T>
+template <int KH, int KW, int CIN, int KBI, int NM, int V, bool FOLD, typename T>
 __device__ __forceinline__ void build_row_patch(const T* src, int pitch, uint8_t* row, int r) {
   constexpr int K = KH * KW * CIN;
   constexpr int L = KW * CIN;
   constexpr int lo = KBI * 64, hi = (lo + NM * 16 < K) ? lo + NM * 16 : K;
   float v[NM * 16];
 #pragma unroll
-  for (int e = 0; e < NM * 16; ++e) v[e] = 0.f;
+  for (int e = 0; e < NM * 16; ++e)
+    v[e] = (FOLD && lo + e >= K && lo + e < K + 3) ? 1.f : 0.f;   // 1.0 against the bias rows of W
 #pragma unroll
   for (int a = 0; a < KH; ++a) {
 #pragma unroll
@@ -172,7 +187,7 @@ __device__ __forceinline__ void build_row_patch(const T* src, int pitch, uint8_t
   }
 }
 
-template <int KH, int KW, int CIN, int KBI, typename T>
+template <int KH, int KW, int CIN, int KBI, bool FOLD = false, typename T>
 __device__ __forceinline__ void build_block_patch(const Params& p, const T* patch, int t,
                                                   uint8_t* sa) {
   constexpr int NM = (KH * KW * CIN - KBI * 64 >= 64) ? 4 : (KH * KW * CIN - KBI * 64 + 15) / 16;
@@ -183,9 +198,9 @@ __device__ __forceinline__ void build_block_patch(const Params& p, const T* patc
     const T* src = patch + li * p.sd * p.patch_pitch + lj * p.sd * CIN;
     uint8_t* row = sa + r * 128;
     if (p.vec == 2)
-      build_row_patch<KH, KW, CIN, KBI, NM, 2>(src, p.patch_pitch, row, r);
+      build_row_patch<KH, KW, CIN, KBI, NM, 2, FOLD>(src, p.patch_pitch, row, r);
     else
-      build_row_patch<KH, KW, CIN, KBI, NM, 1>(src, p.patch_pitch, row, r);
+      build_row_patch<KH, KW, CIN, KBI, NM, 1, FOLD>(src, p.patch_pitch, row, r);
   }
 }
 
@@ -195,7 +210,7 @@ struct BlockMmas {   // 16-wide MMA K-steps that k-block KBI really needs
   static constexpr int value = rest >= 64 ? 4 : (rest + 15) / 16;
 };
 
-template <int KH, int KW, int CIN, int KBI, typename T>
+template <int KH, int KW, int CIN, int KBI, bool FOLD = false, typename T>
 __device__ __forceinline__ void build_block(const Params& p, const T* img, int n, int i0, int j0,
                                             int t, uint8_t* sa) {
   constexpr int NM = BlockMmas<KH * KW * CIN, KBI>::value;
@@ -209,47 +224,55 @@ __device__ __forceinline__ void build_block(const Params& p, const T* img, int n
     uint8_t* row = sa + r * 128;
     const bool inside = y0 >= 0 && x0 >= 0 && y0 + KH <= p.h && x0 + KW <= p.w;
     if (inside)
-      build_row<KH, KW, CIN, KBI, NM, false>(src, row_stride, y0, x0, p.h, p.w, row, r);
+      build_row<KH, KW, CIN, KBI, NM, false, FOLD>(src, row_stride, y0, x0, p.h, p.w, row, r);
     else
-      build_row<KH, KW, CIN, KBI, NM, true>(src, row_stride, y0, x0, p.h, p.w, row, r);
+      build_row<KH, KW, CIN, KBI, NM, true, FOLD>(src, row_stride, y0, x0, p.h, p.w, row, r);
   }
 }
 
 // MODE 0: bias (+ReLU).  MODE 1: GDN with cout == 32 * NC.
 //
-// PIPE (GDN only; an experiment kept behind debug bit 32): the GDN epilogue software-pipelined
-// over two tiles.  This layer has K = 75: there is no long main GEMM to hide the epilogue's chain
-//   D1 -> x^2 (shared memory) -> [GEMM2 round trip] -> D2 -> y -> store
-// behind, and a tile takes 4 us against 0.4 us of tensor-pipe work (ncu: 18 % tensor pipe).  The
-// pipelined order
-//     [square tile i+1: D1 -> x (registers), x^2 -> shared memory]  while GEMM2(i) has long finished
-//     [normalise tile i: D2 -> y -> global memory]                   while GEMM2(i+1) runs
-// removes every wait on the tensor pipe from the epilogue warps: the x of two tiles is live at
-// once (2 x 48 packed registers per thread, so the epilogue warpgroups take registers from the
-// TMA / MMA / builder warpgroup with setmaxnreg), y leaves from registers (the x^2 tile of the
-// next image tile sits where the unpipelined epilogue stages its TMA store), tensor-memory loads
-// are 16 columns wide with the next one in flight, and the MMA warp issues GEMM2(i) right after
-// the main GEMM of tile i.  MEASURED (profiles/r2n_thin_pipelined_epilogue.txt): 1.48 ms against
-// 1.33 ms for the unpipelined epilogue, results identical — the waits were not the limit.  The
-// ncu capture that came with it shows what is: the LSU data pipe (63 %: bias / beta vectors read
-// from shared memory by every thread, x^2 stores, the im2col builders' patch reads) ahead of
-// issue slots (31 %) and XU (21 %).  A split by PHASE (four warps squaring, four normalising, x
-// re-read from TMEM) was slower still (profiles/r2i_thin_split_epilogue.txt).  What did help
-// came out of the same capture: the epilogues' shared-memory traffic was compiled as GENERIC
-// loads and stores (see the `smem` pointer below) — fixed for all four tcgen05 kernels.
-template <int MODE, int NC, int KH, int KW, int CIN, bool PIPE>
-__global__ void __launch_bounds__(kThreads, 1)
+// TS (GDN with a bfloat16 output; the default): this layer has K = 75, so there is no long main
+// GEMM to hide the epilogue's chain  D1 -> x^2 -> [GEMM2 round trip] -> D2 -> y -> store  behind:
+// a tile takes 4 us against 0.4 us of tensor-pipe work, and warp-state sampling of the 8-warp
+// epilogue (profiles/r3f_*) puts 23 % of its time on the GEMM2 round trip, 14 % on waiting for
+// the previous tile's TMA store to leave the buffer x^2 is about to be written to, 8 % on the
+// tile-coordinate divisions, and shows the bias / beta loads' latency exposed in front of every
+// FADD.  The TS form removes those:
+//   * x^2 goes to TENSOR MEMORY (tcgen05.st, 96 columns of packed bfloat16 next to the two
+//     accumulators) and GEMM2 takes its A operand from there (tcgen05.mma with A in TMEM): no x^2
+//     tile in shared memory, so the 48 KB buffer only stages y and the wait for the previous
+//     store moves behind the GEMM2 round trip, where it is free;
+//   * bias and beta are FOLDED INTO THE GEMMS: the im2col matrix carries 1.0 in three of its
+//     padding columns (K = 75 is padded to 80 anyway) against three bfloat16 pieces of the bias
+//     (hi + mid + lo = the float32 value to 2^-24) in the matching rows of W, and GEMM2 gets one
+//     more K = 16 step whose A is a constant block of tensor memory and whose B rows hold the
+//     three pieces of beta in an unused corner of W's last k-block — the epilogue has no
+//     shared-memory loads and no adds left;
+//   * sixteen epilogue warps (four per tensor-memory lane quadrant, a quarter of the channels
+//     each) instead of eight, and the tile coordinates by multiply-high instead of division.
+// Rounds 1-2 tried a split by phase and a software-pipelined 8-warp epilogue first (slower:
+// profiles/r2i_*, r2n_*); the older epilogue stays as the float32-output / debug-bit-32 form.
+template <int MODE, int NC, int KH, int KW, int CIN, bool TS, int KO = 0>
+__global__ void __launch_bounds__(TS ? kThreadsTs : kThreads, 1)
 conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
                  const __grid_constant__ CUtensorMap map_g,
                  const __grid_constant__ CUtensorMap map_img,
                  const __grid_constant__ CUtensorMap map_out, const Params p) {
   constexpr bool GDN = MODE != 0;
+  static_assert(!TS || GDN, "the tensor-memory epilogue is the GDN epilogue");
   constexpr int K = KH * KW * CIN;
   constexpr int KB = (K + 63) / 64;
   constexpr int gdn_kblocks = GDN ? NC / 2 : 0;
+  constexpr int kEpi = TS ? kEpiThreadsTs : kEpiThreads;
+  constexpr int kAll = TS ? kThreadsTs : kThreads;
+  // tensor memory (TS): [accumulator 0][accumulator 1][x^2 as bf16 pairs][constant block]
+  constexpr int ACC = TS ? NC * 32 : 256;
+  constexpr int X2COL = 2 * ACC, ONESCOL = X2COL + NC * 16;
+  static_assert(!TS || ONESCOL + 8 <= 512, "tensor memory");
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [A ring: stages x 16 KB] [W: KB x npad*128 B] [gamma: cout/64 x npad*128 B]
-  //        [A2: cout/64 x 16 KB] [2 image patches] [bias|beta] [barriers]
+  //        [A2 / y staging: cout/64 x 16 KB] [2 image patches] [bias|beta] [barriers]
   // aligned with pointer arithmetic on the __shared__ array (not through an integer): the
   // compiler then knows every pointer derived from `smem` is a shared-memory address and emits
   // LDS / STS instead of generic LD / ST (twice the wavefronts for a broadcast 128-bit load)
@@ -265,9 +288,11 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
   Barriers* bars = reinterpret_cast<Barriers*>(s_beta + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int i = threadIdx.x; i < 256; i += kThreads) {
-    s_bias[i] = (p.bias && i < p.cout) ? p.bias[i] : 0.f;
-    s_beta[i] = (GDN && i < p.cout) ? p.beta[i] : 1.f;
+  if constexpr (!TS) {
+    for (int i = threadIdx.x; i < 256; i += kAll) {
+      s_bias[i] = (p.bias && i < p.cout) ? p.bias[i] : 0.f;
+      s_beta[i] = (GDN && i < p.cout) ? p.beta[i] : 1.f;
+    }
   }
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&map_w);
@@ -279,8 +304,8 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
     mbar_init(&bars->w_full, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&bars->p_full[s], 1); mbar_init(&bars->p_empty[s], kBuilders / 32); }
     if (p.patch) prefetch_tmap(&map_img);
-    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], kEpiThreads); }
-    mbar_init(&bars->a2_full, kEpiThreads);
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], kEpi); }
+    mbar_init(&bars->a2_full, kEpi);
     mbar_init(&bars->d2_full, 1);
     fence_barrier_init();
   }
@@ -294,158 +319,118 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
   const int tile_step = p.chunk ? 1 : (int)gridDim.x;
   const uint32_t idesc = make_idesc_bf16(128, p.npad);
 
+  // tile -> (image, first output row, first output column); the quotients by multiply-high with
+  // host-made reciprocals (exact for every tile index: checked by the host before it sets them)
   auto tile_coords = [&](int tile, int& n, int& i0, int& j0) {
     const int per_img = p.tiles_h * p.tiles_w;
-    n = tile / per_img;
+    n = p.rcp_per_img ? (int)__umulhi((uint32_t)tile, p.rcp_per_img) : tile / per_img;
     const int r = tile - n * per_img;
-    const int ti = r / p.tiles_w;
+    const int ti = p.rcp_tiles_w ? (int)__umulhi((uint32_t)r, p.rcp_tiles_w) : r / p.tiles_w;
     i0 = ti * p.th;
     j0 = (r - ti * p.tiles_w) * p.tw;
   };
 
   if (warp >= 4) {
+    if constexpr (TS) {
+      // ===== epilogue (TS): 16 warps, thread <-> TMEM lane <-> tile pixel, four column parts =====
+      constexpr int CP = NC * 8;                      // channels per thread
+      constexpr int NPC = CP / 16;                    // 16-column pieces
+      const int quad = warp & 3;
+      const int part = (warp - 4) >> 2;
+      const int r = quad * 32 + lane;
+      const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+      const bool leader = threadIdx.x == 128;
+      if (part == 0) {
+        // A of the beta step of GEMM2: 1.0 at K positions 13, 14, 15 of its 16 (written once)
+        const uint32_t ones[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0x3F800000u, 0x3F803F80u};
+        tmem_st_32x8(tmem + ONESCOL + lane_addr, ones);
+        tmem_st_wait();
+      }
+      uint32_t it = 0;
+      for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
+        const int acc = it & 1;
+        const uint32_t dacc = tmem + acc * ACC + lane_addr + part * CP;
+        uint32_t xs[CP / 2];                          // x as packed bf16 pairs
+        // phase 1: x = D1 (bias already in it) -> registers, x^2 -> tensor memory
+        mbar_wait(&bars->d1_full[acc], (it >> 1) & 1);
+        tc_fence_after();
+        {
+          uint32_t v[CP];
+#pragma unroll
+          for (int pc = 0; pc < NPC; ++pc) tmem_ld_32x16p(dacc + pc * 16, v + pc * 16);
+          tmem_ld_wait();
+#pragma unroll
+          for (int pc = 0; pc < NPC; ++pc) {
+            uint32_t sq[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float x0 = __uint_as_float(v[pc * 16 + 2 * e]);
+              const float x1 = __uint_as_float(v[pc * 16 + 2 * e + 1]);
+              xs[pc * 8 + e] = epi::pack_bf16(x0, x1);
+              sq[e] = epi::pack_bf16(x0 * x0, x1 * x1);
+            }
+            tmem_st_32x8(tmem + X2COL + lane_addr + part * (CP / 2) + pc * 8, sq);
+          }
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        mbar_arrive(&bars->a2_full);
+        // the previous tile's store must have left the staging buffer; this sits behind the
+        // GEMM2 round trip, so it does not wait in practice
+        if (it > 0) {
+          if (leader) bulk_wait_read();
+          named_barrier(1, kEpi);
+        }
+        mbar_wait(&bars->d2_full, it & 1);
+        tc_fence_after();
+        // phase 2: y = x * rsqrt(D2) (beta already in it) -> staging -> TMA store
+        {
+          uint32_t g[CP];
+#pragma unroll
+          for (int pc = 0; pc < NPC; ++pc) tmem_ld_32x16p(dacc + pc * 16, g + pc * 16);
+          tmem_ld_wait();
+#pragma unroll
+          for (int h = 0; h < CP / 8; ++h) {          // 16-byte chunks of 8 channels
+            uint32_t w[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const uint32_t pr = xs[h * 4 + e];
+              const float y0 = __uint_as_float(pr << 16) *
+                               epi::rsqrt_approx(__uint_as_float(g[h * 8 + 2 * e]));
+              const float y1 = __uint_as_float(pr & 0xFFFF0000u) *
+                               epi::rsqrt_approx(__uint_as_float(g[h * 8 + 2 * e + 1]));
+              w[e] = epi::pack_bf16(y0, y1);
+            }
+            const int gc = part * (CP / 8) + h;       // chunk of the 128-byte-swizzled tile row
+            *reinterpret_cast<uint4*>(a2 + (gc >> 3) * kABytes + r * 128 + (((gc & 7) ^ (r & 7)) * 16)) =
+                make_uint4(w[0], w[1], w[2], w[3]);
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&bars->d1_empty[acc]);
+        fence_proxy_async_smem();
+        named_barrier(1, kEpi);
+        if (leader) {
+          int n, i0, j0;
+          tile_coords(tile, n, i0, j0);
+          for (int kc = 0; kc < gdn_kblocks; ++kc)
+            tma_store_4d(&map_out, a2 + kc * kABytes, kc * 64, j0, i0, n);
+          bulk_commit();
+        }
+      }
+      if (leader) bulk_wait_read();
+    } else {
     // ===== epilogue: 8 warps, thread <-> TMEM lane <-> tile pixel, two column halves =====
-    if constexpr (PIPE) setmaxnreg_inc<kEpiRegs>();
     const int quad = warp & 3;
     const int half = (warp - 4) >> 2;
     const int r = quad * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
-    if constexpr (PIPE) {
-      constexpr int NCH = NC / 2;                     // 32-column chunks of this thread's half
-      const int cbase = half * NCH;
-      const int ntiles = tile1 > tile0 ? (tile1 - tile0 + tile_step - 1) / tile_step : 0;
-      // Both phases walk their 96 columns in 16-column pieces with the tensor-memory load of
-      // the next piece in flight behind the piece being worked on (ncu of the one-load-at-a-time
-      // form: a third of all warp samples sat on LDTM and its first consumer).
-      constexpr int NP = NCH * 2;
-      // phase 1 of tile number `it`: x = D1 + bias -> xs (packed bf16), x^2 -> a2
-      auto square = [&](uint32_t it, uint32_t (&xs)[NCH * 16]) {
-        const int acc = it & 1;
-        const uint32_t dacc = tmem + acc * 256 + lane_addr + cbase * 32;
-        mbar_wait(&bars->d1_full[acc], (it >> 1) & 1);
-        tc_fence_after();
-        auto piece = [&](int pc, const uint32_t (&v)[16]) {
-          const int cc = cbase + (pc >> 1);
-          uint8_t* row = a2 + (cc >> 1) * kABytes + r * 128;
-          const float4* bs = reinterpret_cast<const float4*>(s_bias + cc * 32 + (pc & 1) * 16);
-#pragma unroll
-          for (int q2 = 0; q2 < 2; ++q2) {
-            const float4 b0 = bs[2 * q2], b1 = bs[2 * q2 + 1];
-            const float x0 = __uint_as_float(v[8 * q2 + 0]) + b0.x;
-            const float x1 = __uint_as_float(v[8 * q2 + 1]) + b0.y;
-            const float x2 = __uint_as_float(v[8 * q2 + 2]) + b0.z;
-            const float x3 = __uint_as_float(v[8 * q2 + 3]) + b0.w;
-            const float x4 = __uint_as_float(v[8 * q2 + 4]) + b1.x;
-            const float x5 = __uint_as_float(v[8 * q2 + 5]) + b1.y;
-            const float x6 = __uint_as_float(v[8 * q2 + 6]) + b1.z;
-            const float x7 = __uint_as_float(v[8 * q2 + 7]) + b1.w;
-            const int q = (pc & 1) * 2 + q2;
-            xs[pc * 8 + 4 * q2 + 0] = epi::pack_bf16(x0, x1);
-            xs[pc * 8 + 4 * q2 + 1] = epi::pack_bf16(x2, x3);
-            xs[pc * 8 + 4 * q2 + 2] = epi::pack_bf16(x4, x5);
-            xs[pc * 8 + 4 * q2 + 3] = epi::pack_bf16(x6, x7);
-            const int physc = ((cc & 1) * 4 + q) ^ (r & 7);
-            *reinterpret_cast<uint4*>(row + physc * 16) =
-                make_uint4(epi::pack_bf16(x0 * x0, x1 * x1), epi::pack_bf16(x2 * x2, x3 * x3),
-                           epi::pack_bf16(x4 * x4, x5 * x5), epi::pack_bf16(x6 * x6, x7 * x7));
-          }
-        };
-        uint32_t va[16], vb[16];
-        tmem_ld_32x16(dacc, va);
-        tmem_ld_wait();
-#pragma unroll
-        for (int pc = 0; pc < NP; pc += 2) {
-          tmem_ld_32x16(dacc + (pc + 1) * 16, vb);
-          piece(pc, va);
-          tmem_ld_wait();
-          if (pc + 2 < NP) tmem_ld_32x16(dacc + (pc + 2) * 16, va);
-          piece(pc + 1, vb);
-          tmem_ld_wait();
-        }
-        tc_fence_before();
-        fence_proxy_async_smem();
-        mbar_arrive(&bars->a2_full);
-      };
-      // phase 2 of tile number `it` (its d2_full has been waited for): y = x * rsqrt(beta + D2)
-      auto normalise = [&](uint32_t it, const uint32_t (&xs)[NCH * 16]) {
-        int n, i0, j0;
-        tile_coords(tile0 + (int)it * tile_step, n, i0, j0);
-        const int acc = it & 1;
-        const int li = r / p.tw, lj = r - li * p.tw;
-        const int i2 = i0 + li, j2 = j0 + lj;
-        const bool valid = i2 < p.ho && j2 < p.wo && !(p.debug & 2);
-        const int64_t elem0 = (((int64_t)n * p.ho + i2) * p.wo + j2) * p.cout + cbase * 32;
-        const uint32_t dacc = tmem + acc * 256 + lane_addr + cbase * 32;
-        tc_fence_after();
-        auto piece = [&](int pc, const uint32_t (&g)[16]) {
-          const float4* be = reinterpret_cast<const float4*>(s_beta + cbase * 32 + pc * 16);
-          uint32_t w[8];
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const float4 b4 = be[q];
-            const uint32_t p0 = xs[pc * 8 + 2 * q], p1 = xs[pc * 8 + 2 * q + 1];
-            const float y0 = __uint_as_float(p0 << 16) *
-                             epi::rsqrt_approx(__uint_as_float(g[4 * q + 0]) + b4.x);
-            const float y1 = __uint_as_float(p0 & 0xFFFF0000u) *
-                             epi::rsqrt_approx(__uint_as_float(g[4 * q + 1]) + b4.y);
-            const float y2 = __uint_as_float(p1 << 16) *
-                             epi::rsqrt_approx(__uint_as_float(g[4 * q + 2]) + b4.z);
-            const float y3 = __uint_as_float(p1 & 0xFFFF0000u) *
-                             epi::rsqrt_approx(__uint_as_float(g[4 * q + 3]) + b4.w);
-            if (p.out_f32) {
-              if (valid)
-                reinterpret_cast<float4*>(static_cast<float*>(p.out) + elem0 + pc * 16)[q] =
-                    make_float4(y0, y1, y2, y3);
-            } else {
-              w[2 * q] = epi::pack_bf16(y0, y1);
-              w[2 * q + 1] = epi::pack_bf16(y2, y3);
-            }
-          }
-          if (!p.out_f32 && valid) {
-            __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(p.out) + elem0 + pc * 16;
-            if (p.out_wide) {
-              epi::st_global_v8(dst, w[0], w[1], w[2], w[3], w[4], w[5], w[6], w[7]);
-            } else {
-              reinterpret_cast<uint4*>(dst)[0] = make_uint4(w[0], w[1], w[2], w[3]);
-              reinterpret_cast<uint4*>(dst)[1] = make_uint4(w[4], w[5], w[6], w[7]);
-            }
-          }
-        };
-        uint32_t ga[16], gb[16];
-        tmem_ld_32x16(dacc, ga);
-        tmem_ld_wait();
-#pragma unroll
-        for (int pc = 0; pc < NP; pc += 2) {
-          tmem_ld_32x16(dacc + (pc + 1) * 16, gb);
-          piece(pc, ga);
-          tmem_ld_wait();
-          if (pc + 2 < NP) tmem_ld_32x16(dacc + (pc + 2) * 16, ga);
-          piece(pc + 1, gb);
-          tmem_ld_wait();
-        }
-        tc_fence_before();
-        mbar_arrive(&bars->d1_empty[acc]);
-      };
-      uint32_t xa[NCH * 16], xb[NCH * 16];
-      if (ntiles > 0) square(0, xa);
-      for (int it = 0; it < ntiles; it += 2) {
-        // d2_full(it) completing also means GEMM2(it) has read a2: the next x^2 may go in
-        mbar_wait(&bars->d2_full, it & 1);
-        if (it + 1 < ntiles) square(it + 1, xb);
-        normalise(it, xa);
-        if (it + 1 < ntiles) {
-          mbar_wait(&bars->d2_full, (it + 1) & 1);
-          if (it + 2 < ntiles) square(it + 2, xa);
-          normalise(it + 1, xb);
-        }
-      }
-    } else {
+    const int li = r / p.tw, lj = r - li * p.tw;
     uint32_t it = 0;
     for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
       int n, i0, j0;
       tile_coords(tile, n, i0, j0);
       const int acc = it & 1;
-      const int li = r / p.tw, lj = r - li * p.tw;
       const int i2 = i0 + li, j2 = j0 + lj;
       const bool valid = i2 < p.ho && j2 < p.wo && !(p.debug & 2);
       const int64_t elem0 = (((int64_t)n * p.ho + i2) * p.wo + j2) * p.cout;
@@ -453,7 +438,7 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
       mbar_wait(&bars->d1_full[acc], (it >> 1) & 1);
       tc_fence_after();
       if constexpr (GDN)
-        epi::gdn_tile<MODE, NC / 2>(dacc, a2, r, half * (NC / 2), s_bias, s_beta, &bars->a2_full,
+        epi::gdn_tile<MODE, NC / 2, KO>(dacc, a2, r, half * (NC / 2), s_bias, s_beta, &bars->a2_full,
                                     &bars->d2_full, it, valid, p.out, p.out_f32 != 0,
                                     p.out_wide != 0, elem0, p.out_tma ? &map_out : nullptr,
                                     epi::TileOrigin{j0, i0, n}, threadIdx.x == 128, NC / 2);
@@ -466,7 +451,6 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
     if (GDN && p.out_tma && threadIdx.x == 128) bulk_wait_read();
     }
   } else if (warp == 0) {
-    if constexpr (PIPE) setmaxnreg_dec<kOtherRegs>();
     // ===== one-time TMA: resident weights and gamma =====
     if (lane == 0) {
       mbar_expect_tx(&bars->w_full, (KB + gdn_kblocks) * b_bytes);
@@ -493,7 +477,6 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
       }
     }
   } else if (warp == 1) {
-    if constexpr (PIPE) setmaxnreg_dec<kOtherRegs>();
     // ===== MMA issuer =====
     if (lane == 0) {
       int stage = 0;
@@ -501,13 +484,24 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
       auto issue_gdn = [&](uint32_t j) {
         mbar_wait(&bars->a2_full, j & 1);
         tc_fence_after();
-        const uint32_t d2 = tmem + (j & 1) * 256;
+        const uint32_t d2 = tmem + (j & 1) * ACC;
         for (int kc = 0; kc < gdn_kblocks; ++kc) {
-          const uint64_t da = make_desc_sw128(smem_u32(a2 + kc * kABytes));
           const uint64_t db = make_desc_sw128(smem_u32(g_res + kc * b_slot));
+          if constexpr (TS) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            umma_bf16(d2, da + (k * 2), db + (k * 2), idesc, (kc | k) != 0);
+            for (int k = 0; k < 4; ++k)
+              umma_bf16_ts(d2, tmem + X2COL + (kc * 4 + k) * 8, db + (k * 2), idesc, (kc | k) != 0);
+          } else {
+            const uint64_t da = make_desc_sw128(smem_u32(a2 + kc * kABytes));
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              umma_bf16(d2, da + (k * 2), db + (k * 2), idesc, (kc | k) != 0);
+          }
+        }
+        if constexpr (TS) {
+          // + beta: the constant A block against the beta rows kept in W's last k-block
+          const uint64_t db = make_desc_sw128(smem_u32(w_res + (KB - 1) * b_slot));
+          umma_bf16_ts(d2, tmem + ONESCOL, db + (uint64_t)(fold::beta_slice(K) / 8), idesc, 1);
         }
         umma_commit(&bars->d2_full);
       };
@@ -516,7 +510,7 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
         const int acc = it & 1;
         mbar_wait(&bars->d1_empty[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t d1 = tmem + acc * 256;
+        const uint32_t d1 = tmem + acc * ACC;
 #pragma unroll
         for (int kb = 0; kb < KB; ++kb) {
           const int nm = (K - kb * 64 >= 64) ? 4 : (K - kb * 64 + 15) / 16;
@@ -531,18 +525,13 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
           if (++stage == p.stages) { stage = 0; ph ^= 1; }
         }
         umma_commit(&bars->d1_full[acc]);
-        if constexpr (PIPE) {
-          issue_gdn(it);        // waits for the epilogue to have squared this tile
-        } else {
-          // GEMM2 of the previous tile goes AFTER this tile's main GEMM: the main GEMM is short
-          // and its operands are ready long before the epilogue has squared the previous tile
-          if (GDN && it > 0) issue_gdn(it - 1);
-        }
+        // GEMM2 of the previous tile goes AFTER this tile's main GEMM: the main GEMM is short
+        // and its operands are ready long before the epilogue has squared the previous tile
+        if (GDN && it > 0) issue_gdn(it - 1);
       }
-      if (!PIPE && GDN && it > 0) issue_gdn(it - 1);
+      if (GDN && it > 0) issue_gdn(it - 1);
     }
   } else {
-    if constexpr (PIPE) setmaxnreg_dec<kOtherRegs>();
     // ===== im2col builders (warps 2-3) =====
     const int t = threadIdx.x - 64;
     int stage = 0;
@@ -556,17 +545,17 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
         if (p.debug & 1) {
         } else if (p.patch) {
           if (p.in_dtype == TFC_F32)
-            build_block_patch<KH, KW, CIN, KBI>(p, reinterpret_cast<const float*>(patch), t, sa);
+            build_block_patch<KH, KW, CIN, KBI, TS>(p, reinterpret_cast<const float*>(patch), t, sa);
           else if (p.in_dtype == TFC_U8)
-            build_block_patch<KH, KW, CIN, KBI>(p, patch, t, sa);
+            build_block_patch<KH, KW, CIN, KBI, TS>(p, patch, t, sa);
           else
-            build_block_patch<KH, KW, CIN, KBI>(p, reinterpret_cast<const __nv_bfloat16*>(patch), t, sa);
+            build_block_patch<KH, KW, CIN, KBI, TS>(p, reinterpret_cast<const __nv_bfloat16*>(patch), t, sa);
         } else if (p.in_dtype == TFC_F32)
-          build_block<KH, KW, CIN, KBI>(p, static_cast<const float*>(p.in), n, i0, j0, t, sa);
+          build_block<KH, KW, CIN, KBI, TS>(p, static_cast<const float*>(p.in), n, i0, j0, t, sa);
         else if (p.in_dtype == TFC_U8)
-          build_block<KH, KW, CIN, KBI>(p, static_cast<const uint8_t*>(p.in), n, i0, j0, t, sa);
+          build_block<KH, KW, CIN, KBI, TS>(p, static_cast<const uint8_t*>(p.in), n, i0, j0, t, sa);
         else
-          build_block<KH, KW, CIN, KBI>(p, static_cast<const __nv_bfloat16*>(p.in), n, i0, j0, t, sa);
+          build_block<KH, KW, CIN, KBI, TS>(p, static_cast<const __nv_bfloat16*>(p.in), n, i0, j0, t, sa);
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->a_full[stage]);
@@ -599,14 +588,27 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
 }
 
 // w fp32 [K][cout] -> bf16 [KB][npad][64] (K-major blocks, zero padded)
+// `folded`: rows K..K+2 hold the bias and rows beta_k..beta_k+2 beta, each as three bfloat16
+// pieces hi + mid + lo (namespace fold)
+__device__ __forceinline__ float bf16_piece(float v, int i) {
+  for (int j = 0; j < i; ++j) v -= __bfloat162float(__float2bfloat16_rn(v));
+  return v;
+}
 __global__ void repack_thin_weights_kernel(const float* __restrict__ w, int K, int cout, int npad,
-                                           int kblocks, __nv_bfloat16* __restrict__ out) {
+                                           int kblocks, __nv_bfloat16* __restrict__ out,
+                                           const float* __restrict__ bias,
+                                           const float* __restrict__ beta, int folded, int beta_k) {
   const int total = kblocks * npad * 64;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int kk = i & 63;
     const int o = (i >> 6) % npad;
     const int k = (i / (64 * npad)) * 64 + kk;
-    out[i] = __float2bfloat16_rn((k < K && o < cout) ? w[(int64_t)k * cout + o] : 0.f);
+    float v = (k < K && o < cout) ? w[(int64_t)k * cout + o] : 0.f;
+    if (folded && o < cout) {
+      if (k >= K && k < K + 3) v = bias ? bf16_piece(bias[o], k - K) : 0.f;
+      if (k >= beta_k && k < beta_k + 3) v = bf16_piece(beta[o], k - beta_k);
+    }
+    out[i] = __float2bfloat16_rn(v);
   }
 }
 
@@ -831,7 +833,7 @@ struct Plan {
   int patch_rows, patch_pitch, patch_slot, vec;
   size_t smem;
   bool gdn;
-  bool pipe;                // software-pipelined GDN epilogue (experiment: debug bit 32 turns it on)
+  bool ts;                  // GDN epilogue through tensor memory (debug bit 32 turns it off)
 };
 
 bool shape_ok(const tfc_conv_desc& d) {
@@ -840,8 +842,9 @@ bool shape_ok(const tfc_conv_desc& d) {
 
 bool make_plan(const tfc_conv_desc& d, const void* in, Plan* pl) {
   pl->gdn = d.act == TFC_ACT_GDN;
-  pl->pipe = pl->gdn && (tfc::debug_bits() & 32) != 0;   // measured slower: see the kernel comment
   const int K = d.kh * d.kw * d.cin;
+  pl->ts = pl->gdn && d.out_dtype == TFC_BF16 && d.cout % 64 == 0 && fold::fits(K) &&
+           !(tfc::debug_bits() & (32 | 16));
   pl->kblocks = (K + 63) / 64;
   pl->npad = (d.cout + 15) / 16 * 16;
   tfc::conv_pick_tile(d.ho, d.wo, &pl->th, &pl->tw);
@@ -884,9 +887,11 @@ int launch(const tfc_conv_desc& d, const Plan& pl, const CUtensorMap& map_w,
            const Params& p, int grid, cudaStream_t st) {
   void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap,
                const Params) = nullptr;
+  int threads = kThreads;
   if (!pl.gdn) {
     kern = conv_thin_kernel<0, 0, KH, KW, 3, false>;
-  } else if (pl.pipe) {
+  } else if (pl.ts) {
+    threads = kThreadsTs;
     switch (d.cout / 32) {
       case 4: kern = conv_thin_kernel<1, 4, KH, KW, 3, true>; break;
       case 6: kern = conv_thin_kernel<1, 6, KH, KW, 3, true>; break;
@@ -898,9 +903,24 @@ int launch(const tfc_conv_desc& d, const Plan& pl, const CUtensorMap& map_w,
       case 6: kern = conv_thin_kernel<1, 6, KH, KW, 3, false>; break;
       default: return tfc::fail(TFC_ERR_UNIMPLEMENTED, "thin-input GDN needs 128 or 192 filters");
     }
+#ifdef TFC_A0_KNOCKOUT
+    if (KH == 5 && d.cout == 192) {
+      switch (tfc::debug_bits() >> 16) {
+        case 1: kern = conv_thin_kernel<1, 6, KH, KW, 3, false, 1>; break;
+        case 4: kern = conv_thin_kernel<1, 6, KH, KW, 3, false, 4>; break;
+        case 8: kern = conv_thin_kernel<1, 6, KH, KW, 3, false, 8>; break;
+        case 16: kern = conv_thin_kernel<1, 6, KH, KW, 3, false, 16>; break;
+        case 32: kern = conv_thin_kernel<1, 6, KH, KW, 3, false, 32>; break;
+        case 5: kern = conv_thin_kernel<1, 6, KH, KW, 3, false, 5>; break;
+        case 21: kern = conv_thin_kernel<1, 6, KH, KW, 3, false, 21>; break;
+        case 61: kern = conv_thin_kernel<1, 6, KH, KW, 3, false, 61>; break;
+        default: break;
+      }
+    }
+#endif
   }
   TFC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
-  kern<<<grid, kThreads, pl.smem, st>>>(map_w, map_g, map_img, map_out, p);
+  kern<<<grid, threads, pl.smem, st>>>(map_w, map_g, map_img, map_out, p);
   TFC_LAUNCHED("conv_thin_kernel");
   return TFC_OK;
 }
@@ -959,6 +979,15 @@ int conv_thin(const tfc_conv_desc& d, const void* in, const float* w, const floa
   p.tiles_h = (d.ho + p.th - 1) / p.th;
   p.tiles_w = (d.wo + p.tw - 1) / p.tw;
   p.num_tiles = d.n * p.tiles_h * p.tiles_w;
+  {
+    // q = umulhi(x, ceil(2^32 / d)) equals x / d for every x with x * d < 2^32
+    auto rcp = [&](int divisor, int64_t max_x) -> uint32_t {
+      if (divisor <= 1 || max_x * divisor >= (int64_t(1) << 32)) return 0;
+      return (uint32_t)(((uint64_t(1) << 32) + divisor - 1) / divisor);
+    };
+    p.rcp_per_img = rcp(p.tiles_h * p.tiles_w, p.num_tiles);
+    p.rcp_tiles_w = rcp(p.tiles_w, p.tiles_h * p.tiles_w);
+  }
 
   const int K = d.kh * d.kw * d.cin;
   __nv_bfloat16* wb = static_cast<__nv_bfloat16*>(ws);
@@ -966,7 +995,8 @@ int conv_thin(const tfc_conv_desc& d, const void* in, const float* w, const floa
   __nv_bfloat16* gb = reinterpret_cast<__nv_bfloat16*>(static_cast<uint8_t*>(ws) + wbytes);
   if (!(d.flags & TFC_CONV_WEIGHTS_STAGED)) {
     repack_thin_weights_kernel<<<(pl.kblocks * pl.npad * 64 + 255) / 256, 256, 0, st>>>(
-        w, K, d.cout, pl.npad, pl.kblocks, wb);
+        w, K, d.cout, pl.npad, pl.kblocks, wb, bias, beta, (pl.gdn && fold::fits(K)) ? 1 : 0,
+        (pl.kblocks - 1) * 64 + fold::beta_slice(K) + 13);
     TFC_LAUNCHED("repack_thin_weights_kernel");
     if (pl.gdn) {
       repack_gamma_kernel<<<(pl.npad * d.cout + 255) / 256, 256, 0, st>>>(gamma, d.cout, pl.npad, gb);
@@ -1000,7 +1030,7 @@ int conv_thin(const tfc_conv_desc& d, const void* in, const float* w, const floa
   } else {
     map_img = map_w;
   }
-  p.out_tma = pl.gdn && !pl.pipe && !p.out_f32 && d.cout % 64 == 0 && !(debug_bits() & 16);
+  p.out_tma = pl.gdn && !p.out_f32 && d.cout % 64 == 0 && !(debug_bits() & 16);
   if (p.out_tma) {
     cuuint64_t dims[4] = {(cuuint64_t)d.cout, (cuuint64_t)d.wo, (cuuint64_t)d.ho, (cuuint64_t)d.n};
     cuuint64_t str[3] = {(cuuint64_t)d.cout * 2, (cuuint64_t)d.wo * d.cout * 2,

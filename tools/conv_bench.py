@@ -64,12 +64,16 @@ def main():
         y = layer(x, out_dtype=out_dtype)
         torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.reps + 1)]
         a.record()
-        for _ in range(args.reps):
+        evs[0].record()
+        for i_rep in range(args.reps):
           y = layer(x, out_dtype=out_dtype)
+          evs[i_rep + 1].record()
         b.record()
         torch.cuda.synchronize()
         ms = a.elapsed_time(b) / args.reps
+        each = sorted(evs[k].elapsed_time(evs[k + 1]) for k in range(args.reps))
         kk = layer.kernel_support[0] * layer.kernel_support[1]
         if layer.strides_up[0] > 1:
           fl = 2.0 * h * w * c * co * kk
@@ -79,6 +83,8 @@ def main():
           fl += 2.0 * ho * wo * co * co
         fl *= B
         rec = {"layer": name, "in": list(shape), "out": [B, ho, wo, co], "ms": round(ms, 4),
+               "ms_min": round(each[0], 4), "ms_med": round(each[len(each) // 2], 4),
+               "ms_max": round(each[-1], 4),
                "tflops": round(fl / ms / 1e9, 1),
                "io_gbs": round((x.numel() * x.element_size() + y.numel() * y.element_size())
                                / ms / 1e6, 1)}
