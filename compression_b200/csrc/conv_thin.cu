@@ -48,6 +48,14 @@ constexpr int kMaxStages = 4;
 // the last 16-wide K step, where the im2col matrix carries 1.0), and the pieces of beta at
 // positions 13..15 of the 16-wide slice starting at `beta_slice` — columns no main-GEMM step
 // multiplies by anything but zero.
+#ifdef TFC_A0_TRACE
+// poor man's timeline (tools/a0_trace.py): clock64() of CTA 0's phase boundaries, tiles 8..15
+__device__ unsigned long long g_a0_trace[8 * 64];
+#define TR(it, slot) do { if (blockIdx.x == 0 && (it) >= 8 && (it) < 16) g_a0_trace[((it) - 8) * 64 + (slot)] = clock64(); } while (0)
+#else
+#define TR(it, slot) do { } while (0)
+#endif
+
 namespace fold {
 __host__ __device__ constexpr int tail(int K) { return K - (K - 1) / 64 * 64; }
 __host__ __device__ constexpr int beta_slice(int K) { return (tail(K) + 5) / 16 * 16; }
@@ -84,7 +92,8 @@ struct __align__(8) Barriers {
   uint64_t w_full;
   uint64_t p_full[2], p_empty[2];
   uint64_t d1_full[2], d1_empty[2];
-  uint64_t a2_full, d2_full;
+  uint64_t a2_full, d2_full[1];
+  uint64_t y_full, y_free;          // TS: the staged y tile is complete / has been read by its store
   uint32_t tmem_base;
   uint32_t pad;
 };
@@ -304,9 +313,12 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
     mbar_init(&bars->w_full, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&bars->p_full[s], 1); mbar_init(&bars->p_empty[s], kBuilders / 32); }
     if (p.patch) prefetch_tmap(&map_img);
-    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], kEpi); }
-    mbar_init(&bars->a2_full, kEpi);
-    mbar_init(&bars->d2_full, 1);
+    constexpr int kEpiArrivals = kEpi;
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->d1_full[s], 1); mbar_init(&bars->d1_empty[s], kEpiArrivals); }
+    mbar_init(&bars->a2_full, kEpiArrivals);
+    mbar_init(&bars->d2_full[0], 1);
+    mbar_init(&bars->y_full, kEpi);
+    mbar_init(&bars->y_free, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(&bars->tmem_base, 512);
@@ -339,86 +351,97 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
       const int part = (warp - 4) >> 2;
       const int r = quad * 32 + lane;
       const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
-      const bool leader = threadIdx.x == 128;
+      const bool tr = quad == 0 && lane == 0;
+      const int ts0 = part * 12;
       if (part == 0) {
         // A of the beta step of GEMM2: 1.0 at K positions 13, 14, 15 of its 16 (written once)
         const uint32_t ones[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0x3F800000u, 0x3F803F80u};
         tmem_st_32x8(tmem + ONESCOL + lane_addr, ones);
         tmem_st_wait();
       }
-      uint32_t it = 0;
-      for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
+      const int ntiles = tile1 > tile0 ? (tile1 - tile0 + tile_step - 1) / tile_step : 0;
+      // phase 1 of tile number `it`: x = D1 (bias already in it) -> registers (packed bf16),
+      // x^2 -> tensor memory; 8 columns at a time so that the x of two tiles fits in registers
+      auto square = [&](uint32_t it, uint32_t (&xs)[CP / 2]) {
         const int acc = it & 1;
         const uint32_t dacc = tmem + acc * ACC + lane_addr + part * CP;
-        uint32_t xs[CP / 2];                          // x as packed bf16 pairs
-        // phase 1: x = D1 (bias already in it) -> registers, x^2 -> tensor memory
         mbar_wait(&bars->d1_full[acc], (it >> 1) & 1);
         tc_fence_after();
-        {
-          uint32_t v[CP];
+        if (tr) TR(it, ts0 + 0);
 #pragma unroll
-          for (int pc = 0; pc < NPC; ++pc) tmem_ld_32x16p(dacc + pc * 16, v + pc * 16);
+        for (int pc = 0; pc < CP / 8; ++pc) {
+          uint32_t v[8], sq[4];
+          tmem_ld_32x8(dacc + pc * 8, v);
           tmem_ld_wait();
 #pragma unroll
-          for (int pc = 0; pc < NPC; ++pc) {
-            uint32_t sq[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const float x0 = __uint_as_float(v[pc * 16 + 2 * e]);
-              const float x1 = __uint_as_float(v[pc * 16 + 2 * e + 1]);
-              xs[pc * 8 + e] = epi::pack_bf16(x0, x1);
-              sq[e] = epi::pack_bf16(x0 * x0, x1 * x1);
-            }
-            tmem_st_32x8(tmem + X2COL + lane_addr + part * (CP / 2) + pc * 8, sq);
+          for (int e = 0; e < 4; ++e) {
+            const float x0 = __uint_as_float(v[2 * e]), x1 = __uint_as_float(v[2 * e + 1]);
+            xs[pc * 4 + e] = epi::pack_bf16(x0, x1);
+            sq[e] = epi::pack_bf16(x0 * x0, x1 * x1);
           }
+          tmem_st_32x4(tmem + X2COL + lane_addr + part * (CP / 2) + pc * 4, sq);
         }
         tmem_st_wait();
         tc_fence_before();
         mbar_arrive(&bars->a2_full);
-        // the previous tile's store must have left the staging buffer; this sits behind the
-        // GEMM2 round trip, so it does not wait in practice
-        if (it > 0) {
-          if (leader) bulk_wait_read();
-          named_barrier(1, kEpi);
-        }
-        mbar_wait(&bars->d2_full, it & 1);
+        if (tr) TR(it, ts0 + 2);
+      };
+      // phase 2 of tile number `it` (its d2_full has been waited for): y = x * rsqrt(D2) (beta
+      // already in it), computed IN PLACE over x; only then does the thread need the staging
+      // tile, so the previous tile's TMA store drains behind square() and this arithmetic
+      auto normalise = [&](uint32_t it, uint32_t (&xs)[CP / 2]) {
+        const int acc = it & 1;
+        const uint32_t dacc = tmem + acc * ACC + lane_addr + part * CP;
         tc_fence_after();
-        // phase 2: y = x * rsqrt(D2) (beta already in it) -> staging -> TMA store
-        {
-          uint32_t g[CP];
+        if (tr) TR(it, ts0 + 3);
 #pragma unroll
-          for (int pc = 0; pc < NPC; ++pc) tmem_ld_32x16p(dacc + pc * 16, g + pc * 16);
+        for (int pc = 0; pc < CP / 8; ++pc) {
+          uint32_t g[8];
+          tmem_ld_32x8(dacc + pc * 8, g);
           tmem_ld_wait();
+          if (pc == CP / 8 - 1) {
+            // D2 is in registers: hand the accumulator back now
+            tc_fence_before();
+            mbar_arrive(&bars->d1_empty[acc]);
+            if (tr) TR(it, ts0 + 4);
+          }
 #pragma unroll
-          for (int h = 0; h < CP / 8; ++h) {          // 16-byte chunks of 8 channels
-            uint32_t w[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const uint32_t pr = xs[h * 4 + e];
-              const float y0 = __uint_as_float(pr << 16) *
-                               epi::rsqrt_approx(__uint_as_float(g[h * 8 + 2 * e]));
-              const float y1 = __uint_as_float(pr & 0xFFFF0000u) *
-                               epi::rsqrt_approx(__uint_as_float(g[h * 8 + 2 * e + 1]));
-              w[e] = epi::pack_bf16(y0, y1);
-            }
-            const int gc = part * (CP / 8) + h;       // chunk of the 128-byte-swizzled tile row
-            *reinterpret_cast<uint4*>(a2 + (gc >> 3) * kABytes + r * 128 + (((gc & 7) ^ (r & 7)) * 16)) =
-                make_uint4(w[0], w[1], w[2], w[3]);
+          for (int e = 0; e < 4; ++e) {
+            const uint32_t pr = xs[pc * 4 + e];
+            const float y0 = __uint_as_float(pr << 16) *
+                             epi::rsqrt_approx(__uint_as_float(g[2 * e]));
+            const float y1 = __uint_as_float(pr & 0xFFFF0000u) *
+                             epi::rsqrt_approx(__uint_as_float(g[2 * e + 1]));
+            xs[pc * 4 + e] = epi::pack_bf16(y0, y1);
           }
         }
-        tc_fence_before();
-        mbar_arrive(&bars->d1_empty[acc]);
+        if (tr) TR(it, ts0 + 5);
+        if (it > 0) mbar_wait(&bars->y_free, (it - 1) & 1);
+        if (tr) TR(it, ts0 + 6);
+#pragma unroll
+        for (int h = 0; h < CP / 8; ++h) {            // 16-byte chunks of 8 channels
+          const int gc = part * (CP / 8) + h;         // chunk of the 128-byte-swizzled tile row
+          *reinterpret_cast<uint4*>(a2 + (gc >> 3) * kABytes + r * 128 + (((gc & 7) ^ (r & 7)) * 16)) =
+              make_uint4(xs[h * 4], xs[h * 4 + 1], xs[h * 4 + 2], xs[h * 4 + 3]);
+        }
         fence_proxy_async_smem();
-        named_barrier(1, kEpi);
-        if (leader) {
-          int n, i0, j0;
-          tile_coords(tile, n, i0, j0);
-          for (int kc = 0; kc < gdn_kblocks; ++kc)
-            tma_store_4d(&map_out, a2 + kc * kABytes, kc * 64, j0, i0, n);
-          bulk_commit();
+        mbar_arrive(&bars->y_full);
+        if (tr) TR(it, ts0 + 7);
+      };
+      // square(i + 1) goes between the end of GEMM2(i) and normalise(i): GEMM2(i + 1) then runs
+      // while this tile is normalised, and no epilogue warp waits for the tensor pipe
+      uint32_t xa[CP / 2], xb[CP / 2];
+      if (ntiles > 0) square(0, xa);
+      for (int it = 0; it < ntiles; it += 2) {
+        mbar_wait(&bars->d2_full[0], it & 1);         // also: GEMM2(it) has read x^2
+        if (it + 1 < ntiles) square(it + 1, xb);
+        normalise(it, xa);
+        if (it + 1 < ntiles) {
+          mbar_wait(&bars->d2_full[0], (it + 1) & 1);
+          if (it + 2 < ntiles) square(it + 2, xa);
+          normalise(it + 1, xb);
         }
       }
-      if (leader) bulk_wait_read();
     } else {
     // ===== epilogue: 8 warps, thread <-> TMEM lane <-> tile pixel, two column halves =====
     const int quad = warp & 3;
@@ -439,7 +462,7 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
       tc_fence_after();
       if constexpr (GDN)
         epi::gdn_tile<MODE, NC / 2, KO>(dacc, a2, r, half * (NC / 2), s_bias, s_beta, &bars->a2_full,
-                                    &bars->d2_full, it, valid, p.out, p.out_f32 != 0,
+                                    &bars->d2_full[0], it, valid, p.out, p.out_f32 != 0,
                                     p.out_wide != 0, elem0, p.out_tma ? &map_out : nullptr,
                                     epi::TileOrigin{j0, i0, n}, threadIdx.x == 128, NC / 2);
       else
@@ -453,26 +476,58 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
   } else if (warp == 0) {
     // ===== one-time TMA: resident weights and gamma =====
     if (lane == 0) {
+      // TS: this thread also sends the staged y tiles off (issuing the three tensor stores takes
+      // ~500 cycles and seeing them leave shared memory another ~1200: kept off the epilogue
+      // warps)
+      auto store_tile = [&](uint32_t j) {
+        int n, i0, j0;
+        tile_coords(tile0 + (int)j * tile_step, n, i0, j0);
+        TR(j, 61);
+        for (int kc = 0; kc < gdn_kblocks; ++kc)
+          tma_store_4d(&map_out, a2 + kc * kABytes, kc * 64, j0, i0, n);
+        bulk_commit();
+        TR(j, 62);
+        bulk_wait_read();
+        mbar_arrive(&bars->y_free);
+        TR(j, 60);
+      };
       mbar_expect_tx(&bars->w_full, (KB + gdn_kblocks) * b_bytes);
       for (int kb = 0; kb < KB; ++kb)
         tma_load_3d(w_res + kb * b_slot, &map_w, &bars->w_full, 0, 0, kb);
       for (int kc = 0; kc < gdn_kblocks; ++kc)
         tma_load_2d(g_res + kc * b_slot, &map_g, &bars->w_full, kc * 64, 0);
-      if (p.patch) {
+      const uint32_t ntiles = tile1 > tile0 ? (tile1 - tile0 + tile_step - 1) / tile_step : 0;
+      auto load_patch = [&](uint32_t it) {
         // ===== image patches: one TMA box per tile, borders zero-filled by the TMA unit =====
-        uint32_t it = 0;
-        for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
-          int n, i0, j0;
-          tile_coords(tile, n, i0, j0);
-          const int pb = it & 1;
-          mbar_wait(&bars->p_empty[pb], ((it >> 1) & 1) ^ 1);
-          mbar_expect_tx(&bars->p_full[pb], p.patch_bytes);
-          // the box must start on a 16-byte boundary of the image row: round the first column
-          // down, the builders skip the difference
-          int c0 = (j0 * p.sd - p.pl) * CIN;
-          c0 -= c0 & (p.per16 - 1);
-          tma_load_3d(patches + pb * p.patch_slot, &map_img, &bars->p_full[pb], c0,
-                      i0 * p.sd - p.pt, n);
+        int n, i0, j0;
+        tile_coords(tile0 + (int)it * tile_step, n, i0, j0);
+        const int pb = it & 1;
+        mbar_expect_tx(&bars->p_full[pb], p.patch_bytes);
+        // the box must start on a 16-byte boundary of the image row: round the first column
+        // down, the builders skip the difference
+        int c0 = (j0 * p.sd - p.pl) * CIN;
+        c0 -= c0 & (p.per16 - 1);
+        tma_load_3d(patches + pb * p.patch_slot, &map_img, &bars->p_full[pb], c0,
+                    i0 * p.sd - p.pt, n);
+      };
+      if constexpr (TS) {
+        // two duties, whichever is ready: the patch of the next tile (two buffers ahead of the
+        // builders) and the store of the next staged y tile
+        uint32_t np = p.patch ? 0 : ntiles, ns = 0;
+        while (ns < ntiles || np < ntiles) {
+          if (np < ntiles && mbar_test(&bars->p_empty[np & 1], ((np >> 1) & 1) ^ 1)) {
+            load_patch(np);
+            ++np;
+          }
+          if (ns < ntiles && mbar_test(&bars->y_full, ns & 1)) {
+            store_tile(ns);
+            ++ns;
+          }
+        }
+      } else if (p.patch) {
+        for (uint32_t it = 0; it < ntiles; ++it) {
+          mbar_wait(&bars->p_empty[it & 1], ((it >> 1) & 1) ^ 1);
+          load_patch(it);
         }
       }
     }
@@ -484,32 +539,40 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
       auto issue_gdn = [&](uint32_t j) {
         mbar_wait(&bars->a2_full, j & 1);
         tc_fence_after();
+        TR(j, 50);
         const uint32_t d2 = tmem + (j & 1) * ACC;
-        for (int kc = 0; kc < gdn_kblocks; ++kc) {
-          const uint64_t db = make_desc_sw128(smem_u32(g_res + kc * b_slot));
-          if constexpr (TS) {
+        if constexpr (TS) {
+          // A from tensor memory; the last step adds beta: the constant A block against the beta
+          // rows in W's last k-block.  (Issued in two or four column parts with a commit each, so
+          // that the epilogue could start on the first columns early, GEMM2 takes as long per
+          // part as it does whole — 89 cycles per MMA at N = 96 as at N = 192: r3m_*.)
+          for (int kc = 0; kc < gdn_kblocks; ++kc) {
+            const uint64_t db = make_desc_sw128(smem_u32(g_res + kc * b_slot));
 #pragma unroll
             for (int k = 0; k < 4; ++k)
               umma_bf16_ts(d2, tmem + X2COL + (kc * 4 + k) * 8, db + (k * 2), idesc, (kc | k) != 0);
-          } else {
+          }
+          const uint64_t db = make_desc_sw128(smem_u32(w_res + (KB - 1) * b_slot));
+          umma_bf16_ts(d2, tmem + ONESCOL, db + (uint64_t)(fold::beta_slice(K) / 8), idesc, 1);
+          umma_commit(&bars->d2_full[0]);
+          TR(j, 51);
+        } else {
+          for (int kc = 0; kc < gdn_kblocks; ++kc) {
             const uint64_t da = make_desc_sw128(smem_u32(a2 + kc * kABytes));
+            const uint64_t db = make_desc_sw128(smem_u32(g_res + kc * b_slot));
 #pragma unroll
             for (int k = 0; k < 4; ++k)
               umma_bf16(d2, da + (k * 2), db + (k * 2), idesc, (kc | k) != 0);
           }
+          umma_commit(&bars->d2_full[0]);
         }
-        if constexpr (TS) {
-          // + beta: the constant A block against the beta rows kept in W's last k-block
-          const uint64_t db = make_desc_sw128(smem_u32(w_res + (KB - 1) * b_slot));
-          umma_bf16_ts(d2, tmem + ONESCOL, db + (uint64_t)(fold::beta_slice(K) / 8), idesc, 1);
-        }
-        umma_commit(&bars->d2_full);
       };
       mbar_wait(&bars->w_full, 0);
-      for (int tile = tile0; tile < tile1; tile += tile_step, ++it) {
+      auto main_gemm = [&](uint32_t it) {
         const int acc = it & 1;
         mbar_wait(&bars->d1_empty[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
+        TR(it, 52);
         const uint32_t d1 = tmem + acc * ACC;
 #pragma unroll
         for (int kb = 0; kb < KB; ++kb) {
@@ -525,11 +588,29 @@ conv_thin_kernel(const __grid_constant__ CUtensorMap map_w,
           if (++stage == p.stages) { stage = 0; ph ^= 1; }
         }
         umma_commit(&bars->d1_full[acc]);
-        // GEMM2 of the previous tile goes AFTER this tile's main GEMM: the main GEMM is short
-        // and its operands are ready long before the epilogue has squared the previous tile
+        TR(it, 53);
+      };
+      const uint32_t ntiles = tile1 > tile0 ? (tile1 - tile0 + tile_step - 1) / tile_step : 0;
+      if constexpr (TS) {
+        // In the order the epilogue makes things ready (square(it+1), normalise(it), ...):
+        // GEMM2(it+1) as soon as tile it+1 is squared, the main GEMM of tile it+2 once tile it's
+        // accumulator has been read by normalise().
+        if (ntiles > 0) main_gemm(0);
+        if (ntiles > 1) main_gemm(1);
+        if (ntiles > 0) issue_gdn(0);
+        for (it = 0; it < ntiles; ++it) {
+          if (it + 1 < ntiles) issue_gdn(it + 1);
+          if (it + 2 < ntiles) main_gemm(it + 2);
+        }
+      } else {
+        for (it = 0; it < ntiles; ++it) {
+          main_gemm(it);
+          // GEMM2 of the previous tile goes AFTER this tile's main GEMM: the main GEMM is short
+          // and its operands are ready long before the epilogue has squared the previous tile
+          if (GDN && it > 0) issue_gdn(it - 1);
+        }
         if (GDN && it > 0) issue_gdn(it - 1);
       }
-      if (GDN && it > 0) issue_gdn(it - 1);
     }
   } else {
     // ===== im2col builders (warps 2-3) =====
@@ -1154,3 +1235,10 @@ int conv_thin_wgrad(const tfc_conv_desc& d, const void* x, const void* dy, float
 }
 
 }  // namespace tfc
+
+#ifdef TFC_A0_TRACE
+extern "C" int tfc_debug_a0_trace(unsigned long long* dst, int n) {
+  if (n > 8 * 64) n = 8 * 64;
+  return (int)cudaMemcpyFromSymbol(dst, g_a0_trace, sizeof(unsigned long long) * n);
+}
+#endif
