@@ -13,8 +13,9 @@
 //     128-byte-swizzled K-major layout tcgen05.mma expects (row = pixel, 16-byte chunk c of
 //     row r stored at chunk c ^ (r & 7)), through a ring of 16 KB stages.  The k -> (a, b, c)
 //     decomposition is resolved at compile time (kernel templated on kh, kw, cin).
-//   * warp 0: one-time TMA; warp 1: MMA issuer; warps 2-3: builders; warps 4-11: epilogue (two
-//     whole warpgroups, so that setmaxnreg can move registers to them).
+//   * warp 0: TMA (weights once, an image patch per tile, and — TS form — the stores of the
+//     staged output tiles); warp 1: MMA issuer; warps 2-3: builders; warps 4-11 (4-19 in the TS
+//     form: GDN with a bfloat16 output, see the kernel comment): epilogue.
 // Compared with the space-to-depth formulation (conv_s2d.cu, 9 k-blocks of 64 mostly-zero
 // channels per tile, weights streamed per tile) this issues 5 instead of 36 MMAs per tile and
 // takes the shared-memory fill traffic per tile from 360 KB to the 8 KB image patch.
@@ -259,7 +260,10 @@ __device__ __forceinline__ void build_block(const Params& p, const T* img, int n
 //     three pieces of beta in an unused corner of W's last k-block — the epilogue has no
 //     shared-memory loads and no adds left;
 //   * sixteen epilogue warps (four per tensor-memory lane quadrant, a quarter of the channels
-//     each) instead of eight, and the tile coordinates by multiply-high instead of division.
+//     each) instead of eight, pipelined over two tiles — square(i+1) between the end of GEMM2(i)
+//     and normalise(i), so that GEMM2(i+1) runs behind normalise(i); the stores issued by the
+//     patch-loading thread; tile coordinates by multiply-high instead of division.
+// 1.31 -> 0.76 ms at the bmshj2018 bench shape (profiles/r3g_a0_stall_breakdown.md, r3o_a0_trace.txt).
 // Rounds 1-2 tried a split by phase and a software-pipelined 8-warp epilogue first (slower:
 // profiles/r2i_*, r2n_*); the older epilogue stays as the float32-output / debug-bit-32 form.
 template <int MODE, int NC, int KH, int KW, int CIN, bool TS, int KO = 0>
