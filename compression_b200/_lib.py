@@ -9,7 +9,8 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libtfc_b200.so")
+# TFC_B200_SO: another build of the same library (A/B timing of kernel variants)
+SO_PATH = os.environ.get("TFC_B200_SO") or os.path.join(_HERE, "libtfc_b200.so")
 
 OK, INVALID_ARGUMENT, CUDA_ERROR, CAPACITY, DECODE, UNIMPLEMENTED = range(6)
 STREAM_CAPACITY, STREAM_CORRUPT = 1, 2

@@ -163,9 +163,14 @@ __device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* m
 // see is ordered by the fence in front of every call (fence.proxy.async for shared-memory operands,
 // tcgen05.fence::before_thread_sync for tensor-memory reads).  With .release.cluster ptxas emits
 // MEMBAR.ALL.GPU + ERRBAR in front of the arrive — 1600-1700 cycles per tile and arrival in the
-// IGDN epilogue of S2, 21 % of the epilogue warps' samples (profiles/r3t_*).
+// IGDN epilogue of S2, 21 % of the epilogue warps' samples (profiles/r3t_*; S0-S2 3 % faster without).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_addr) {
+#ifdef TFC_RELEASE_CLUSTER_ARRIVE   // the A/B partner of profiles/r3y_*
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_addr)
+               : "memory");
+#else
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar_addr) : "memory");
+#endif
 }
 // wait on a local mbarrier whose arrivals may come from the peer CTA
 __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
