@@ -761,7 +761,7 @@ def test_thin_conv_tmem_epilogue_matches_smem_epilogue():
   tensor memory, bias and beta folded into the GEMMs as three bfloat16 pieces each, sixteen
   epilogue warps) against the older one (debug bit 32: x^2 through shared memory, bias and beta
   added in float32 by the epilogue): the same values up to the float32 summation order, i.e. the
-  bfloat16 outputs are equal except where x sat on a rounding boundary, and then one ulp apart.
+  bfloat16 outputs are equal except where x sat on a rounding boundary, and then one or two ulps apart.
   float32 and uint8 images; float32 outputs take the older epilogue either way."""
   from compression_b200 import _lib
   from compression_b200.examples import bmshj2018
@@ -787,7 +787,48 @@ def test_thin_conv_tmem_epilogue_matches_smem_epilogue():
         continue
       g32, w32 = got.float(), want.float()
       assert (g32 == w32).float().mean().item() > 0.995
-      assert ((g32 - w32).abs() <= w32.abs() * 2.0 ** -7 + 1e-30).all()
+      assert ((g32 - w32).abs() <= w32.abs() * 2.0 ** -6 + 2e-6).all()
+
+
+@pytest.mark.parametrize("model_name,shape", [
+    ("bmshj2018", (1, 40, 40)),      # fewer tiles than CTAs: most CTAs run zero tiles
+    ("bmshj2018", (40, 72, 104)),    # 800 tiles on 148 CTAs: five or six per CTA (odd and even counts)
+    ("bmshj2018", (23, 100, 60)),    # ragged tiles on both borders, three or four per CTA
+    ("bmshj2018", (9, 250, 330)),    # many tiles per CTA
+    ("bls2017", (16, 128, 192)),     # 9x9 stride 4, 128 filters: the beta rows share W's last K step
+    ("bls2017", (5, 100, 76)),
+])
+def test_thin_conv_tmem_epilogue_tile_counts(model_name, shape):
+  """The pipelined tensor-memory epilogue of the thin-input GDN layer over CTAs with zero, one, odd
+  and even numbers of tiles and ragged borders, both first layers (5x5 / 192 filters, 9x9 / 128
+  filters), against the older epilogue (debug bit 32): equal except where x sat on a bfloat16
+  rounding boundary (a few outputs in ten million), and then at most two ulps apart."""
+  from compression_b200 import _lib
+  from compression_b200.examples import bls2017, bmshj2018
+  if model_name == "bmshj2018":
+    layer = bmshj2018.Bmshj2018Model(192, "cuda", seed=3).analysis_transform.layers[0]
+  else:
+    layer = bls2017.Bls2017Model(128, "cuda", seed=3).analysis_transform.layers[0]
+  with torch.no_grad():
+    layer.bias_var.copy_(torch.linspace(-0.21, 0.33, layer.bias_var.numel()))
+  layer.invalidate()
+  g = torch.Generator().manual_seed(17)
+  x = torch.rand(shape + (3,), generator=g).cuda()
+  got = layer(x, out_dtype=torch.bfloat16)
+  again = layer(x, out_dtype=torch.bfloat16)
+  _lib.check(_lib.lib().tfc_configure(99, 32))
+  try:
+    want = layer(x, out_dtype=torch.bfloat16)
+    torch.cuda.synchronize()
+  finally:
+    _lib.check(_lib.lib().tfc_configure(99, 0))
+  assert torch.equal(got, again)
+  g32, w32 = got.float(), want.float()
+  assert torch.isfinite(g32).all()
+  assert (g32 == w32).float().mean().item() > 0.995
+  # x one bfloat16 ulp apart gives y up to two ulps apart after its own rounding; where bias and
+  # the convolution sum cancel, x itself is only defined to the float32 rounding of its terms
+  assert ((g32 - w32).abs() <= w32.abs() * 2.0 ** -6 + 2e-6).all()
 
 
 @pytest.mark.parametrize("corr,sd,su,act", [(True, 2, 1, "gdn"), (False, 1, 2, "igdn"),
