@@ -49,8 +49,17 @@ constexpr int kMaxStages = 4;
 // the last 16-wide K step, where the im2col matrix carries 1.0), and the pieces of beta at
 // positions 13..15 of the 16-wide slice starting at `beta_slice` — columns no main-GEMM step
 // multiplies by anything but zero.
-#ifdef TFC_A0_TRACE
-// poor man's timeline (tools/a0_trace.py): clock64() of CTA 0's phase boundaries, tiles 8..15
+// Phase stamps (tools/a0_trace.py): clock64() of CTA 0's phase boundaries over tiles 8..15 of the
+// tensor-memory GDN epilogue, 64 predicated 8-byte stores per launch into a 4 KB device buffer
+// (concurrent launches overwrite each other's stamps: it is a debugging aid).  Compiled in by
+// default (-DTFC_A0_STAMPS=0 removes them) because the kernel is FASTER with them: A/B on one box,
+// two builds alternated twice, 0.760 against 0.876 ms at the bmshj2018 bench shape with identical
+// results (profiles/r4h_trace_ab.txt) — ptxas schedules the epilogue's two phases differently around
+// the clock reads; what exactly it does better has not been tracked down.
+#ifndef TFC_A0_STAMPS
+#define TFC_A0_STAMPS 1
+#endif
+#if TFC_A0_STAMPS
 __device__ unsigned long long g_a0_trace[8 * 64];
 #define TR(it, slot) do { if (blockIdx.x == 0 && (it) >= 8 && (it) < 16) g_a0_trace[((it) - 8) * 64 + (slot)] = clock64(); } while (0)
 #else
@@ -1240,7 +1249,7 @@ int conv_thin_wgrad(const tfc_conv_desc& d, const void* x, const void* dy, float
 
 }  // namespace tfc
 
-#ifdef TFC_A0_TRACE
+#if TFC_A0_STAMPS
 extern "C" int tfc_debug_a0_trace(unsigned long long* dst, int n) {
   if (n > 8 * 64) n = 8 * 64;
   return (int)cudaMemcpyFromSymbol(dst, g_a0_trace, sizeof(unsigned long long) * n);

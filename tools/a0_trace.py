@@ -1,5 +1,5 @@
 """Timeline of conv_thin_kernel's tensor-memory GDN epilogue (A0): clock64() stamps of CTA 0's phase
-boundaries over tiles 8..15.  Needs a build with TFC_NVCC_EXTRA=-DTFC_A0_TRACE.
+boundaries over tiles 8..15 (the stamps are compiled in by default: TFC_A0_STAMPS in csrc/conv_thin.cu).
 Usage: python tools/a0_trace.py [--debug BITS]"""
 import argparse
 import ctypes
