@@ -272,7 +272,8 @@ __device__ __forceinline__ void build_block(const Params& p, const T* img, int n
 //     each) instead of eight, pipelined over two tiles — square(i+1) between the end of GEMM2(i)
 //     and normalise(i), so that GEMM2(i+1) runs behind normalise(i); the stores issued by the
 //     patch-loading thread; tile coordinates by multiply-high instead of division.
-// 1.31 -> 0.76 ms at the bmshj2018 bench shape (profiles/r3g_a0_stall_breakdown.md, r3o_a0_trace.txt).
+// 1.28 -> 0.76 ms at the bmshj2018 bench shape (0.88 without the phase stamps below:
+// profiles/r3g_a0_stall_breakdown.md, r3o_a0_trace.txt, r4h_trace_ab.txt).
 // Rounds 1-2 tried a split by phase and a software-pipelined 8-warp epilogue first (slower:
 // profiles/r2i_*, r2n_*); the older epilogue stays as the float32-output / debug-bit-32 form.
 template <int MODE, int NC, int KH, int KW, int CIN, bool TS, int KO = 0>
