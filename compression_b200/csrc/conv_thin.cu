@@ -1250,9 +1250,12 @@ int conv_thin_wgrad(const tfc_conv_desc& d, const void* x, const void* dy, float
 
 }  // namespace tfc
 
-#if TFC_A0_STAMPS
 extern "C" int tfc_debug_a0_trace(unsigned long long* dst, int n) {
+#if TFC_A0_STAMPS
   if (n > 8 * 64) n = 8 * 64;
   return (int)cudaMemcpyFromSymbol(dst, g_a0_trace, sizeof(unsigned long long) * n);
-}
+#else
+  (void)dst; (void)n;
+  return (int)cudaErrorNotSupported;   // built with -DTFC_A0_STAMPS=0
 #endif
+}

@@ -91,6 +91,12 @@ int64_t tfc_launch_count(void);
 #define TFC_CFG_CONV_PAIR 9
 int tfc_configure(int key, int value);
 
+/* Debug aid (no reference counterpart): phase stamps of the thin-input GDN layer's kernel
+ * (csrc/conv_thin.cu, TFC_A0_STAMPS): clock64() of CTA 0's phase boundaries over its tiles 8..15 of
+ * the most recent launch, 8 x 64 values (tools/a0_trace.py names the slots).  Copies min(n, 512)
+ * values to host memory; returns a cudaError_t.  Call after synchronising the launch's stream. */
+int tfc_debug_a0_trace(unsigned long long* h_dst, int n);
+
 /* Debug aid (no reference counterpart): how long the warps-per-stream coder kernels held their
  * SMs.  h_out4 = {encode ns, encode streams, decode ns, decode streams}, each stream's time from
  * its CTA's first instruction to its last, summed since the last reset.  Synchronises the
