@@ -23,6 +23,15 @@ def _stale(obj, srcs):
   return any(os.path.getmtime(s) > t for s in srcs)
 
 
+def _flags_changed(obj):
+  """An object remembers the nvcc flags it was built with (obj + ".flags"): a build with other
+  flags (TFC_NVCC_EXTRA) rebuilds it instead of silently linking the old variant."""
+  try:
+    return open(obj + ".flags").read() != " ".join(FLAGS)
+  except OSError:
+    return True
+
+
 def build(verbose=False, force=False):
   srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
   hdrs = glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(ROOT, "include", "*.h"))
@@ -32,16 +41,19 @@ def build(verbose=False, force=False):
   for s in srcs:
     o = os.path.join(objdir, os.path.basename(s)[:-3] + ".o")
     objs.append(o)
-    if force or _stale(o, [s] + hdrs):
+    if force or _stale(o, [s] + hdrs) or _flags_changed(o):
       cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
-      procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
+      procs.append((s, o, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
   failed = False
-  for s, p in procs:
+  for s, o, p in procs:
     out, _ = p.communicate()
     if p.returncode != 0 or verbose:
       sys.stderr.write(out.decode())
     if p.returncode != 0:
       failed = True
+    else:
+      with open(o + ".flags", "w") as f:
+        f.write(" ".join(FLAGS))
   if failed:
     raise RuntimeError("nvcc failed")
   if force or procs or _stale(OUT, objs):
